@@ -1,0 +1,339 @@
+"""ctypes front-end of the CPU oracle (oracle/abm_oracle.cpp).
+
+TEST INFRASTRUCTURE ONLY.  May be imported from tests/, __graft_entry__.smoke()
+and bench.py's cpu_baseline / --impl reference legs — never from the product
+package (agents.jl_b200/).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "liboracle.so")
+_lib = None
+
+METRICS = {"chebyshev": 0, "manhattan": 1, "euclidean": 2}
+
+
+def build(force: bool = False) -> str:
+    src = os.path.join(_HERE, "abm_oracle.cpp")
+    if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "-B", "liboracle.so"], stdout=subprocess.DEVNULL)
+    return _LIB_PATH
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB_PATH):
+            build()
+        _lib = C.CDLL(_LIB_PATH)
+        L = _lib
+        L.orc_mod_f64.restype = C.c_double
+        L.orc_mod_f64.argtypes = [C.c_double, C.c_double]
+        L.orc_mod_f32.restype = C.c_float
+        L.orc_mod_f32.argtypes = [C.c_float, C.c_float]
+        L.orc_mod1.restype = C.c_int64
+        L.orc_mod1.argtypes = [C.c_int64, C.c_int64]
+        L.orc_grid_offsets.restype = C.c_int64
+        L.orc_cs_create.restype = C.c_void_p
+        L.orc_last_error.restype = C.c_char_p
+        L.orc_last_error.argtypes = [C.c_void_p]
+        L.orc_destroy.argtypes = [C.c_void_p]
+        L.orc_grid_create.restype = C.c_void_p
+        L.orc_cs_euclidean_distance.restype = C.c_double
+        for name in ("orc_cs_nagents", "orc_cs_add_agents", "orc_cs_cell_ids", "orc_cs_grid_r",
+                     "orc_cs_nearby_ids", "orc_cs_nearby_ids_agent", "orc_cs_pairs_all",
+                     "orc_cs_nearest_neighbor", "orc_grid_add_agents", "orc_grid_nearby_positions",
+                     "orc_grid_nearby_ids", "orc_grid_nearby_ids_agent"):
+            getattr(L, name).restype = C.c_int64
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def jl_mod(x, y, dtype=np.float64):
+    if np.dtype(dtype) == np.float32:
+        return float(lib().orc_mod_f32(C.c_float(x), C.c_float(y)))
+    return float(lib().orc_mod_f64(x, y))
+
+
+def grid_offsets(dims, periodic, metric, r, no_zero=False):
+    D = len(dims)
+    d = np.asarray(dims, dtype=np.int64)
+    per = _periodic(periodic, D)
+    n = lib().orc_grid_offsets(D, _p(d), _p(per), METRICS[metric], C.c_double(r), int(no_zero), None, C.c_int64(0))
+    out = np.zeros((n, D), dtype=np.int64)
+    lib().orc_grid_offsets(D, _p(d), _p(per), METRICS[metric], C.c_double(r), int(no_zero), _p(out), C.c_int64(n))
+    return out
+
+
+def _periodic(periodic, D):
+    if isinstance(periodic, (bool, np.bool_)):
+        periodic = (bool(periodic),) * D
+    return np.asarray(periodic, dtype=np.uint8)
+
+
+class OracleError(RuntimeError):
+    pass
+
+
+class ContinuousOracle:
+    """Reference-semantics ContinuousSpace model (src/spaces/continuous.jl)."""
+
+    def __init__(self, extent, spacing=None, periodic=True, dtype=np.float64):
+        self.D = len(extent)
+        self.dtype = np.dtype(dtype)
+        ext = np.asarray(extent, dtype=np.float64)
+        if spacing is None:
+            spacing = float(ext.min()) / 20.0  # continuous.jl:95
+        self.spacing = float(spacing)
+        self.extent = ext
+        self.periodic = _periodic(periodic, self.D)
+        err = C.create_string_buffer(256)
+        self.h = lib().orc_cs_create(self.D, _p(ext), C.c_double(self.spacing), _p(self.periodic),
+                                     0 if self.dtype == np.float64 else 1, err, 256)
+        if not self.h:
+            raise OracleError(err.value.decode())
+        self.h = C.c_void_p(self.h)
+        dims = np.zeros(3, dtype=np.int64)
+        lib().orc_cs_dims(self.h, _p(dims))
+        self.dims = tuple(int(x) for x in dims[: self.D])
+
+    def __del__(self):
+        try:
+            if getattr(self, "h", None):
+                lib().orc_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    def _err(self):
+        return lib().orc_last_error(self.h).decode()
+
+    def _arr(self, a):
+        return np.ascontiguousarray(np.asarray(a, dtype=self.dtype))
+
+    @property
+    def n(self):
+        return int(lib().orc_cs_nagents(self.h))
+
+    def add_agents(self, pos, vel=None):
+        pos = self._arr(pos).reshape(-1, self.D)
+        vel = self._arr(vel).reshape(-1, self.D) if vel is not None else None
+        rc = lib().orc_cs_add_agents(self.h, _p(pos), _p(vel), C.c_int64(pos.shape[0]))
+        if rc < 0:
+            raise OracleError(self._err())
+        return int(rc)
+
+    def add_agent(self, pos, vel=None):
+        return self.add_agents([pos], [vel] if vel is not None else None)
+
+    def state(self):
+        n = self.n
+        pos = np.zeros((n, self.D), dtype=self.dtype)
+        vel = np.zeros((n, self.D), dtype=self.dtype)
+        lib().orc_cs_get_state(self.h, _p(pos), _p(vel))
+        return pos, vel
+
+    def set_vel(self, vel):
+        vel = self._arr(vel).reshape(-1, self.D)
+        assert vel.shape[0] == self.n
+        lib().orc_cs_set_vel(self.h, _p(vel))
+
+    def pos2cell(self, pos):
+        pos = self._arr(pos).reshape(-1, self.D)
+        out = np.zeros((pos.shape[0], self.D), dtype=np.int32)
+        lib().orc_cs_pos2cell(self.h, _p(pos), C.c_int64(pos.shape[0]), _p(out))
+        return out
+
+    def cell_ids(self, cell):
+        c = np.asarray(cell, dtype=np.int64)
+        n = lib().orc_cs_cell_ids(self.h, _p(c), None, C.c_int64(0))
+        out = np.zeros(n, dtype=np.int64)
+        lib().orc_cs_cell_ids(self.h, _p(c), _p(out), C.c_int64(n))
+        return out
+
+    def grid_r(self, pos, r):
+        return int(lib().orc_cs_grid_r(self.h, _p(self._arr(pos)), C.c_double(r)))
+
+    def nearby_ids(self, pos, r=1.0, search="approximate"):
+        q = self._arr(pos)
+        ex = int(search == "exact")
+        n = lib().orc_cs_nearby_ids(self.h, _p(q), C.c_double(r), ex, None, C.c_int64(0))
+        out = np.zeros(n, dtype=np.int64)
+        lib().orc_cs_nearby_ids(self.h, _p(q), C.c_double(r), ex, _p(out), C.c_int64(n))
+        return out
+
+    def nearby_ids_agent(self, id, r=1.0, search="approximate"):
+        ex = int(search == "exact")
+        n = lib().orc_cs_nearby_ids_agent(self.h, C.c_int64(id), C.c_double(r), ex, None, C.c_int64(0))
+        out = np.zeros(n, dtype=np.int64)
+        lib().orc_cs_nearby_ids_agent(self.h, C.c_int64(id), C.c_double(r), ex, _p(out), C.c_int64(n))
+        return out
+
+    def nearby_counts_all(self, r, search="approximate"):
+        out = np.zeros(self.n, dtype=np.int64)
+        lib().orc_cs_nearby_counts_all(self.h, C.c_double(r), int(search == "exact"), _p(out))
+        return out
+
+    def interacting_pairs_all(self, r, search="exact"):
+        ex = int(search == "exact")
+        n = lib().orc_cs_pairs_all(self.h, C.c_double(r), ex, None, C.c_int64(0))
+        out = np.zeros((n, 2), dtype=np.int64)
+        lib().orc_cs_pairs_all(self.h, C.c_double(r), ex, _p(out), C.c_int64(n))
+        return out
+
+    def nearest_neighbor(self, id, r):
+        j = int(lib().orc_cs_nearest_neighbor(self.h, C.c_int64(id), C.c_double(r)))
+        return j or None
+
+    def move_agent_dt(self, id, dt):
+        if lib().orc_cs_move_agent_dt(self.h, C.c_int64(id), C.c_double(dt)):
+            raise OracleError(self._err())
+
+    def move_agent_to(self, id, pos):
+        if lib().orc_cs_move_agent_to(self.h, C.c_int64(id), _p(self._arr(pos))):
+            raise OracleError(self._err())
+
+    def walk(self, id, direction):
+        if lib().orc_cs_walk(self.h, C.c_int64(id), _p(self._arr(direction))):
+            raise OracleError(self._err())
+
+    def normalize_position(self, pos):
+        p = self._arr(pos).copy()
+        lib().orc_cs_normalize_position(self.h, _p(p))
+        return p
+
+    def euclidean_distance(self, a, b):
+        return float(lib().orc_cs_euclidean_distance(self.h, _p(self._arr(a)), _p(self._arr(b))))
+
+    def get_direction(self, a, b):
+        out = np.zeros(self.D, dtype=self.dtype)
+        lib().orc_cs_get_direction(self.h, _p(self._arr(a)), _p(self._arr(b)), _p(out))
+        return out
+
+    @staticmethod
+    def _params(params):
+        keys = ("speed", "cohere_factor", "separation", "separate_factor", "match_factor", "visual_distance")
+        return np.asarray([float(params[k]) for k in keys], dtype=np.float64)
+
+    def flock_step_sync(self, params, nsteps=1, search="approximate", per_agent=None, return_counts=False):
+        p = self._params(params)
+        pa = np.ascontiguousarray(per_agent, dtype=np.float64) if per_agent is not None else None
+        cnt = np.zeros(self.n, dtype=np.int64) if return_counts else None
+        rc = lib().orc_flock_step_sync(self.h, _p(p), _p(pa), int(search == "exact"), C.c_int64(nsteps), _p(cnt))
+        if rc:
+            raise OracleError(self._err())
+        return cnt
+
+    def flock_step_async(self, params, nsteps=1, search="approximate", per_agent=None, order=None):
+        p = self._params(params)
+        pa = np.ascontiguousarray(per_agent, dtype=np.float64) if per_agent is not None else None
+        n = self.n
+        o = np.ascontiguousarray(order, dtype=np.int64) if order is not None else None
+        rc = lib().orc_flock_step_async(self.h, _p(p), _p(pa), int(search == "exact"), _p(o),
+                                        C.c_int64(len(o) if o is not None else n), C.c_int64(nsteps))
+        if rc:
+            raise OracleError(self._err())
+
+    def pairforce_step(self, radius, k, mass, dt, cutoff, nsteps=1):
+        r = np.ascontiguousarray(radius, dtype=np.float64)
+        kk = np.ascontiguousarray(k, dtype=np.float64)
+        m = np.ascontiguousarray(mass, dtype=np.float64)
+        rc = lib().orc_pairforce_step(self.h, _p(r), _p(kk), _p(m), C.c_double(dt), C.c_double(cutoff), C.c_int64(nsteps))
+        if rc:
+            raise OracleError(self._err())
+
+
+class GridOracle:
+    """Reference-semantics GridSpace / GridSpaceSingle (src/spaces/grid_multi.jl, grid_single.jl)."""
+
+    def __init__(self, dims, periodic=True, metric="chebyshev", single=False):
+        self.D = len(dims)
+        self.dims = tuple(int(x) for x in dims)
+        self.periodic = _periodic(periodic, self.D)
+        self.metric = metric
+        self.single = bool(single)
+        d = np.asarray(dims, dtype=np.int64)
+        self.h = C.c_void_p(lib().orc_grid_create(self.D, _p(d), _p(self.periodic), METRICS[metric], int(single)))
+        self.n = 0
+
+    def __del__(self):
+        try:
+            if getattr(self, "h", None):
+                lib().orc_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    def _err(self):
+        return lib().orc_last_error(self.h).decode()
+
+    def add_agents(self, pos):
+        p = np.ascontiguousarray(pos, dtype=np.int64).reshape(-1, self.D)
+        rc = lib().orc_grid_add_agents(self.h, _p(p), C.c_int64(p.shape[0]))
+        if rc < 0:
+            raise OracleError(self._err())
+        self.n = int(rc)
+        return self.n
+
+    def add_agent(self, pos):
+        return self.add_agents([pos])
+
+    def positions(self):
+        out = np.zeros((self.n, self.D), dtype=np.int64)
+        lib().orc_grid_get_pos(self.h, _p(out))
+        return out
+
+    def stored_single(self):
+        out = np.zeros(int(np.prod(self.dims)), dtype=np.int64)
+        lib().orc_grid_get_stored_single(self.h, _p(out))
+        return out.reshape(self.dims[::-1]).T if self.D > 1 else out  # column-major → [x, y, ...]
+
+    def move_agent_to(self, id, pos):
+        if lib().orc_grid_move_agent_to(self.h, C.c_int64(id), _p(np.asarray(pos, dtype=np.int64))):
+            raise OracleError(self._err())
+
+    def walk(self, id, direction, ifempty=True):
+        if lib().orc_grid_walk(self.h, C.c_int64(id), _p(np.asarray(direction, dtype=np.int64)), int(ifempty)):
+            raise OracleError(self._err())
+
+    def _collect(self, fn, first, r, width):
+        n = fn(self.h, first, C.c_double(r), None, C.c_int64(0))
+        out = np.zeros((n, width) if width > 1 else n, dtype=np.int64)
+        fn(self.h, first, C.c_double(r), _p(out), C.c_int64(n))
+        return out
+
+    def nearby_positions(self, pos, r=1):
+        o = np.asarray(pos, dtype=np.int64)
+        out = self._collect(lib().orc_grid_nearby_positions, _p(o), r, self.D)
+        return out.reshape(-1, self.D)
+
+    def nearby_ids(self, pos, r=1):
+        o = np.asarray(pos, dtype=np.int64)
+        return self._collect(lib().orc_grid_nearby_ids, _p(o), r, 1)
+
+    def nearby_ids_agent(self, id, r=1):
+        return self._collect(lib().orc_grid_nearby_ids_agent, C.c_int64(id), r, 1)
+
+    def schelling_happiness(self, group, min_to_be_happy):
+        g = np.ascontiguousarray(group, dtype=np.int32)
+        cnt = np.zeros(self.n, dtype=np.int32)
+        mood = np.zeros(self.n, dtype=np.uint8)
+        if lib().orc_schelling_happiness(self.h, _p(g), int(min_to_be_happy), _p(cnt), _p(mood)):
+            raise OracleError(self._err())
+        return cnt, mood
+
+    def schelling_step_async(self, group, min_to_be_happy, seed=42, nsteps=1):
+        g = np.ascontiguousarray(group, dtype=np.int32)
+        mood = np.zeros(self.n, dtype=np.uint8)
+        if lib().orc_schelling_step_async(self.h, _p(g), int(min_to_be_happy), _p(mood), C.c_uint64(seed), C.c_int64(nsteps)):
+            raise OracleError(self._err())
+        return mood
