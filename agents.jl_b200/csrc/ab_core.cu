@@ -1,0 +1,660 @@
+// ab_core.cu — lifecycle, agent columns, and the per-step cell-list build.
+//
+// The cell list replaces the reference's persistent Array{Vector{Int},D} index
+// and its incremental upkeep (src/spaces/continuous.jl:133-153,
+// src/spaces/grid_multi.jl:68-105).  Build = counting sort by column-major
+// cell key:
+//   k_count   key = pos2cell (continuous.jl:112-113); arrival rank by atomicAdd
+//   k_scan    single-pass decoupled-look-back exclusive scan → cell_start
+//   k_bucket  ids into their cell segment in arrival order
+//   k_place   canonical slot = cell_start + #(ids in the cell smaller than mine);
+//             moves pos/vel/id/key to the other buffer (and records perm)
+// so a cell's agents are always stored in id order whatever the atomic order was.
+#include <cstdio>
+#include <cstring>
+
+#include "ab_internal.cuh"
+
+// ---------------------------------------------------------------------------
+// error helpers / bookkeeping
+// ---------------------------------------------------------------------------
+static std::string g_create_error;
+
+int ab_fail(ab_handle* h, int code, const std::string& msg) {
+    if (h) h->err = msg; else g_create_error = msg;
+    return code;
+}
+int ab_cuda_fail(ab_handle* h, cudaError_t e, const char* what) {
+    std::string m = std::string("CUDA error: ") + cudaGetErrorString(e) + " in " + what;
+    return ab_fail(h, AB_ERR_CUDA, m);
+}
+size_t ab_dtype_size(int dtype) {
+    switch (dtype) {
+        case AB_F64: case AB_I64: return 8;
+        case AB_F32: case AB_I32: return 4;
+        case AB_U8: return 1;
+    }
+    return 0;
+}
+
+ab_launch_scope::ab_launch_scope(ab_handle* h_, const char* name_) : h(h_), name(name_) {
+    h->launches++;
+    if (h->profiling) {
+        cudaEventCreate(&a);
+        cudaEventCreate(&b);
+        cudaEventRecord(a, h->stream);
+    }
+}
+ab_launch_scope::~ab_launch_scope() {
+    if (h->profiling && a) {
+        cudaEventRecord(b, h->stream);
+        cudaEventSynchronize(b);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, a, b);
+        bool found = false;
+        for (auto& k : h->kstats)
+            if (k.name == name || strcmp(k.name, name) == 0) { k.ms += ms; k.launches++; found = true; break; }
+        if (!found) h->kstats.push_back({name, (double)ms, 1});
+        cudaEventDestroy(a);
+        cudaEventDestroy(b);
+    }
+}
+
+static int grow(ab_handle* h, void** p, size_t* have, size_t bytes) {
+    if (bytes <= *have) return AB_OK;
+    if (*p) { AB_CUDA(h, cudaStreamSynchronize(h->stream)); AB_CUDA(h, cudaFree(*p)); *p = nullptr; *have = 0; }
+    size_t want = bytes + bytes / 4 + 256;
+    AB_CUDA(h, cudaMalloc(p, want));
+    *have = want;
+    return AB_OK;
+}
+int ab_scratch(ab_handle* h, size_t bytes, void** out) {
+    AB_TRY(grow(h, &h->scratch, &h->scratch_bytes, bytes));
+    *out = h->scratch;
+    return AB_OK;
+}
+int ab_scratch2(ab_handle* h, size_t bytes, void** out) {
+    AB_TRY(grow(h, &h->scratch2, &h->scratch2_bytes, bytes));
+    *out = h->scratch2;
+    return AB_OK;
+}
+
+int ab_check_device_errors(ab_handle* h) {
+    AB_CUDA(h, cudaMemcpyAsync(h->h_err, h->d_err, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    AB_CUDA(h, cudaStreamSynchronize(h->stream));
+    int e = *h->h_err;
+    if (!e) return AB_OK;
+    AB_CUDA(h, cudaMemsetAsync(h->d_err, 0, sizeof(int), h->stream));
+    h->index_valid = false;
+    if (e & AB_EF_NUMERIC) return ab_fail(h, AB_ERR_NUMERIC, "InexactError: a NaN/Inf position reached a cell computation");
+    if (e & AB_EF_OUTSIDE) return ab_fail(h, AB_ERR_OUTSIDE, "position is outside space extent!");
+    if (e & AB_EF_OCCUPIED) return ab_fail(h, AB_ERR_OCCUPIED, "Cannot add agent to occupied position");
+    return ab_fail(h, AB_ERR_INVALID, "device-side failure");
+}
+
+// ---------------------------------------------------------------------------
+// kernels
+// ---------------------------------------------------------------------------
+template <class T, int D>
+__global__ void k_count(SpaceDev<T, D> sp, const T* __restrict__ pos, int64_t cap, int n,
+                        uint32_t* __restrict__ newkey, uint32_t* __restrict__ rank,
+                        uint32_t* __restrict__ cell_count, int* __restrict__ err) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    T p[D];
+    int c[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d) p[d] = pos[(size_t)d * cap + s];
+    bool ok = pos2cell0<T, D>(sp, p, c);
+    if (!ok) {
+        bool nan = false;
+#pragma unroll
+        for (int d = 0; d < D; ++d) nan = nan || !(p[d] == p[d]) || isinf(p[d]);
+        atomicOr(err, nan ? AB_EF_NUMERIC : AB_EF_OUTSIDE);
+    }
+    uint32_t k = lin_cell<D>(sp.dims, c);
+    newkey[s] = k;
+    rank[s] = atomicAdd(&cell_count[k], 1u);
+}
+
+// Single-pass exclusive scan (decoupled look-back) of cell_count[0..n) into
+// cell_start[0..n]; zeroes cell_count behind itself.  status word:
+// [epoch:30 | flag:2 | value:32]; flag 1 = tile aggregate, 2 = inclusive prefix.
+#define SCAN_THREADS 256
+#define SCAN_ITEMS 8
+#define SCAN_TILE (SCAN_THREADS * SCAN_ITEMS)
+__global__ void __launch_bounds__(SCAN_THREADS)
+k_scan(uint32_t* __restrict__ count, uint32_t* __restrict__ start, uint32_t n, uint32_t ntiles,
+       volatile unsigned long long* status, uint32_t* ticket, uint32_t epoch) {
+    __shared__ uint32_t s_tile;
+    __shared__ uint32_t s_warp[SCAN_THREADS / 32];
+    __shared__ uint32_t s_excl;
+    if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const uint32_t base = tile * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+    uint32_t v[SCAN_ITEMS];
+    {
+        uint4 a = *reinterpret_cast<const uint4*>(count + base);
+        uint4 b = *reinterpret_cast<const uint4*>(count + base + 4);
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+        *reinterpret_cast<uint4*>(count + base) = make_uint4(0, 0, 0, 0);
+        *reinterpret_cast<uint4*>(count + base + 4) = make_uint4(0, 0, 0, 0);
+    }
+    uint32_t tsum = 0;
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; ++i) { uint32_t t = v[i]; v[i] = tsum; tsum += t; }
+    // block exclusive scan of tsum
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint32_t inc = tsum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+    if (lane == 31) s_warp[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        uint32_t w = lane < SCAN_THREADS / 32 ? s_warp[lane] : 0;
+        uint32_t wi = w;
+#pragma unroll
+        for (int o = 1; o < SCAN_THREADS / 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, wi, o); if (lane >= o) wi += t; }
+        if (lane < SCAN_THREADS / 32) s_warp[lane] = wi - w;      // exclusive per warp
+        uint32_t aggregate = __shfl_sync(0xffffffffu, wi, SCAN_THREADS / 32 - 1);
+        const unsigned long long ep = (unsigned long long)epoch << 34;
+        uint32_t excl = 0;
+        if (tile == 0) {
+            if (lane == 0) status[0] = ep | (2ull << 32) | aggregate;
+        } else {
+            if (lane == 0) status[tile] = ep | (1ull << 32) | aggregate;
+            int p = (int)tile - 1;
+            for (;;) {
+                int idx = p - lane;
+                unsigned long long st;
+                bool valid;
+                do {
+                    st = idx >= 0 ? status[idx] : (ep | (2ull << 32));
+                    valid = ((st >> 34) == (unsigned long long)epoch) && (((st >> 32) & 3ull) != 0);
+                } while (__any_sync(0xffffffffu, !valid));
+                unsigned incl_mask = __ballot_sync(0xffffffffu, ((st >> 32) & 3ull) == 2ull);
+                uint32_t val = (uint32_t)st;
+                if (incl_mask) {
+                    int first = __ffs(incl_mask) - 1;
+                    if (lane > first) val = 0;
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
+                excl += val;
+                if (incl_mask) break;
+                p -= 32;
+            }
+            if (lane == 0) status[tile] = ep | (2ull << 32) | (unsigned long long)(excl + aggregate);
+        }
+        if (lane == 0) {
+            s_excl = excl;
+            if (tile == ntiles - 1) { start[n] = excl + aggregate; *ticket = 0; }
+        }
+    }
+    __syncthreads();
+    const uint32_t off = s_excl + s_warp[wid] + (inc - tsum);
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; ++i)
+        if (base + i < n) start[base + i] = off + v[i];
+}
+
+__global__ void k_bucket(const uint32_t* __restrict__ newkey, const uint32_t* __restrict__ rank,
+                         const uint32_t* __restrict__ cell_start, const int32_t* __restrict__ id_old, int n,
+                         int32_t* __restrict__ idtmp) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    idtmp[cell_start[newkey[s]] + rank[s]] = id_old[s];
+}
+
+#define AB_CANON_MAX 4096   // cells fuller than this keep arrival order (still correct, not canonical)
+template <class T, int D, bool HAS_VEL>
+__global__ void k_place(const uint32_t* __restrict__ newkey, const uint32_t* __restrict__ rank,
+                        const uint32_t* __restrict__ cell_start, const int32_t* __restrict__ id_old,
+                        const int32_t* __restrict__ idtmp, const T* __restrict__ src_pos,
+                        const T* __restrict__ src_vel, int64_t cap, int n, T* __restrict__ dst_pos,
+                        T* __restrict__ dst_vel, int32_t* __restrict__ id_new, uint32_t* __restrict__ key_new,
+                        int32_t* __restrict__ perm, int32_t* __restrict__ slot_of_id) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    const uint32_t k = newkey[s];
+    const uint32_t b = cell_start[k], e = cell_start[k + 1];
+    const int32_t me = id_old[s];
+    uint32_t r;
+    if (e - b <= AB_CANON_MAX) {
+        r = 0;
+        for (uint32_t t = b; t < e; ++t) r += (idtmp[t] < me) ? 1u : 0u;
+    } else r = rank[s];
+    const uint32_t dst = b + r;
+#pragma unroll
+    for (int d = 0; d < D; ++d) dst_pos[(size_t)d * cap + dst] = src_pos[(size_t)d * cap + s];
+    if (HAS_VEL) {
+#pragma unroll
+        for (int d = 0; d < D; ++d) dst_vel[(size_t)d * cap + dst] = src_vel[(size_t)d * cap + s];
+    }
+    id_new[dst] = me;
+    key_new[dst] = k;
+    if (perm) perm[dst] = s;
+    if (slot_of_id) slot_of_id[me] = (int32_t)dst;
+}
+
+template <class E>
+__global__ void k_permute(const E* __restrict__ src, E* __restrict__ dst, const int32_t* __restrict__ perm,
+                          int64_t cap, int n, int ncomp) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    int o = perm[s];
+    for (int c = 0; c < ncomp; ++c) dst[(size_t)c * cap + s] = src[(size_t)c * cap + o];
+}
+
+__global__ void k_iota(int32_t* a, int32_t* b, int n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { a[i] = i; if (b) b[i] = i; }
+}
+__global__ void k_slot_map(const int32_t* __restrict__ id, int32_t* __restrict__ slot_of_id, int n) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s < n) slot_of_id[id[s]] = s;
+}
+
+// host row-per-agent (id order) -> device SoA at the agent's slot, and back
+template <class E>
+__global__ void k_upload(const E* __restrict__ host_rows, E* __restrict__ dst, const int32_t* __restrict__ slot_of_id,
+                         int64_t cap, int n, int ncomp) {
+    int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= (int64_t)n * ncomp) return;
+    int i = (int)(t / ncomp), c = (int)(t - (int64_t)i * ncomp);
+    dst[(size_t)c * cap + slot_of_id[i]] = host_rows[t];
+}
+template <class E>
+__global__ void k_download(const E* __restrict__ src, E* __restrict__ host_rows, const int32_t* __restrict__ id,
+                           int64_t cap, int n, int ncomp) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    int i = id[s];
+    for (int c = 0; c < ncomp; ++c) host_rows[(size_t)i * ncomp + c] = src[(size_t)c * cap + s];
+}
+template <class T, int D>
+__global__ void k_cells(SpaceDev<T, D> sp, const T* __restrict__ pos, const int32_t* __restrict__ id, int64_t cap,
+                        int n, int32_t* __restrict__ out) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    T p[D];
+    int c[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d) p[d] = pos[(size_t)d * cap + s];
+    pos2cell0<T, D>(sp, p, c);
+    int i = id[s];
+#pragma unroll
+    for (int d = 0; d < D; ++d) out[(size_t)i * D + d] = c[d] + 1;
+}
+
+// ---------------------------------------------------------------------------
+// index build
+// ---------------------------------------------------------------------------
+static int run_scan(ab_handle* h) {
+    uint32_t n = (uint32_t)h->ncells;
+    uint32_t ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+    h->scan_epoch = (h->scan_epoch + 1) & 0x3fffffffu;
+    if (h->scan_epoch == 0) {   // epoch wrapped: clear stale status words once
+        AB_CUDA(h, cudaMemsetAsync(h->scan_status, 0, h->scan_status_len * sizeof(unsigned long long), h->stream));
+        h->scan_epoch = 1;
+    }
+    AB_LAUNCH(h, "k_scan");
+    k_scan<<<ntiles, SCAN_THREADS, 0, h->stream>>>(h->cell_count, h->cell_start, n, ntiles, h->scan_status,
+                                                   h->scan_ticket, h->scan_epoch);
+    return AB_OK;
+}
+
+template <class T, int D>
+static int reindex_t(ab_handle* h, const void* src_pos, const void* src_vel, bool count_done) {
+    const int n = (int)h->n;
+    const int cur = h->cur, nxt = cur ^ 1;
+    const int TB = 256;
+    SpaceDev<T, D> sp = make_space<T, D>(h);
+    const bool has_vel = h->desc.kind == AB_SPACE_CONTINUOUS;
+    if (n > 0 && !count_done) {
+        AB_LAUNCH(h, "k_count");
+        k_count<T, D><<<ab_blocks(n, TB), TB, 0, h->stream>>>(sp, (const T*)src_pos, h->cap, n, h->newkey, h->rank,
+                                                              h->cell_count, h->d_err);
+    }
+    AB_TRY(run_scan(h));
+    if (n > 0) {
+        {
+            AB_LAUNCH(h, "k_bucket");
+            k_bucket<<<ab_blocks(n, TB), TB, 0, h->stream>>>(h->newkey, h->rank, h->cell_start, h->id[cur], n, h->idtmp);
+        }
+        const bool extra = h->fields.size() > (has_vel ? 2u : 1u);
+        {
+            AB_LAUNCH(h, "k_place");
+            if (has_vel)
+                k_place<T, D, true><<<ab_blocks(n, TB), TB, 0, h->stream>>>(
+                    h->newkey, h->rank, h->cell_start, h->id[cur], h->idtmp, (const T*)src_pos, (const T*)src_vel,
+                    h->cap, n, (T*)h->fields[0].buf[nxt], (T*)h->fields[1].buf[nxt], h->id[nxt], h->key[nxt],
+                    extra ? h->perm : nullptr, nullptr);
+            else
+                k_place<T, D, false><<<ab_blocks(n, TB), TB, 0, h->stream>>>(
+                    h->newkey, h->rank, h->cell_start, h->id[cur], h->idtmp, (const T*)src_pos, nullptr, h->cap, n,
+                    (T*)h->fields[0].buf[nxt], nullptr, h->id[nxt], h->key[nxt], extra ? h->perm : nullptr, nullptr);
+        }
+        for (size_t f = has_vel ? 2 : 1; f < h->fields.size(); ++f) {
+            ab_field& fl = h->fields[f];
+            AB_LAUNCH(h, "k_permute");
+            if (fl.esize == 8)
+                k_permute<uint64_t><<<ab_blocks(n, TB), TB, 0, h->stream>>>((const uint64_t*)fl.buf[cur], (uint64_t*)fl.buf[nxt], h->perm, h->cap, n, fl.ncomp);
+            else if (fl.esize == 4)
+                k_permute<uint32_t><<<ab_blocks(n, TB), TB, 0, h->stream>>>((const uint32_t*)fl.buf[cur], (uint32_t*)fl.buf[nxt], h->perm, h->cap, n, fl.ncomp);
+            else
+                k_permute<uint8_t><<<ab_blocks(n, TB), TB, 0, h->stream>>>((const uint8_t*)fl.buf[cur], (uint8_t*)fl.buf[nxt], h->perm, h->cap, n, fl.ncomp);
+        }
+    }
+    h->cur = nxt;
+    h->slot_map_valid = false;
+    h->index_valid = true;
+    h->pairs_n = -1;
+    return AB_OK;
+}
+
+// Moves the population into the other buffer in the sorted order given by
+// src_pos (src_* are indexed by the CURRENT slot order).  count_done: a fused
+// step kernel already produced newkey/rank/cell_count.
+int ab_reindex_from(ab_handle* h, const void* src_pos, const void* src_vel, bool count_done) {
+    if (h->dtype == AB_F64) {
+        return h->D == 2 ? reindex_t<double, 2>(h, src_pos, src_vel, count_done)
+                         : reindex_t<double, 3>(h, src_pos, src_vel, count_done);
+    }
+    return h->D == 2 ? reindex_t<float, 2>(h, src_pos, src_vel, count_done)
+                     : reindex_t<float, 3>(h, src_pos, src_vel, count_done);
+}
+
+int ab_ensure_index(ab_handle* h) {
+    if (h->index_valid) return AB_OK;
+    if (h->desc.kind != AB_SPACE_CONTINUOUS) return ab_fail(h, AB_ERR_INVALID, "cell-list index is for ContinuousSpace handles");
+    AB_TRY(ab_reindex_from(h, h->fields[0].buf[h->cur], h->fields[1].buf[h->cur], false));
+    return ab_check_device_errors(h);
+}
+
+int ab_ensure_slot_map(ab_handle* h) {
+    if (h->slot_map_valid) return AB_OK;
+    if (h->n > 0) {
+        AB_LAUNCH(h, "k_slot_map");
+        k_slot_map<<<ab_blocks(h->n, 256), 256, 0, h->stream>>>(h->id[h->cur], h->slot_of_id, (int)h->n);
+    }
+    h->slot_map_valid = true;
+    return AB_OK;
+}
+
+// ---------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------
+extern "C" {
+
+int ab_version(void) { return AB_VERSION; }
+
+const char* ab_last_error(const ab_handle* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+static void free_population(ab_handle* h) {
+    for (auto& f : h->fields)
+        for (int b = 0; b < 2; ++b) { if (f.buf[b]) cudaFree(f.buf[b]); f.buf[b] = nullptr; }
+    void** ptrs[] = {&h->tmp_pos, &h->tmp_vel, (void**)&h->id[0], (void**)&h->id[1], (void**)&h->key[0],
+                     (void**)&h->key[1], (void**)&h->newkey, (void**)&h->rank, (void**)&h->idtmp, (void**)&h->perm,
+                     (void**)&h->slot_of_id, (void**)&h->ncount};
+    for (void** p : ptrs) { if (*p) cudaFree(*p); *p = nullptr; }
+    h->cap = 0;
+    h->n = 0;
+}
+
+int ab_create(ab_space_desc* desc, int device, ab_handle** out) {
+    if (!desc || !out) return ab_fail(nullptr, AB_ERR_INVALID, "null argument");
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t ce = cudaGetDeviceCount(&ndev);
+    if (ce != cudaSuccess || ndev == 0)
+        return ab_fail(nullptr, AB_ERR_CUDA, std::string("no CUDA device available (there is no CPU fallback): ") +
+                                                 (ce != cudaSuccess ? cudaGetErrorString(ce) : "device count is 0"));
+    if (device < 0 || device >= ndev) return ab_fail(nullptr, AB_ERR_INVALID, "bad device ordinal");
+    if (desc->D < 2 || desc->D > 3) return ab_fail(nullptr, AB_ERR_INVALID, "D must be 2 or 3 on the device");
+    ab_handle* h = new ab_handle();
+    h->device = device;
+    h->D = desc->D;
+    int64_t ncells = 1;
+    if (desc->kind == AB_SPACE_CONTINUOUS) {
+        if (desc->dtype != AB_F64 && desc->dtype != AB_F32) { delete h; return ab_fail(nullptr, AB_ERR_INVALID, "dtype must be AB_F64 or AB_F32"); }
+        if (!(desc->spacing > 0)) { delete h; return ab_fail(nullptr, AB_ERR_INVALID, "spacing must be positive"); }
+        for (int d = 0; d < desc->D; ++d) {
+            if (!(desc->extent[d] > 0)) { delete h; return ab_fail(nullptr, AB_ERR_INVALID, "ArgumentError: extent must be positive"); }
+            double q = desc->extent[d] / desc->spacing;
+            if (q != floor(q)) {   // src/spaces/continuous.jl:99-101
+                delete h;
+                return ab_fail(nullptr, AB_ERR_SPACING, "All dimensions in `extent` must be completely divisible by `spacing`");
+            }
+            desc->grid_dims[d] = (int64_t)floor(q);
+        }
+        h->dtype = desc->dtype;
+    } else if (desc->kind == AB_SPACE_GRID_MULTI || desc->kind == AB_SPACE_GRID_SINGLE) {
+        h->dtype = AB_I32;
+        if (desc->metric < 0 || desc->metric > 2) { delete h; return ab_fail(nullptr, AB_ERR_INVALID, "Unknown metric type"); }
+    } else { delete h; return ab_fail(nullptr, AB_ERR_INVALID, "unknown space kind"); }
+    for (int d = 0; d < desc->D; ++d) {
+        if (desc->grid_dims[d] < 1 || desc->grid_dims[d] > 2000000000LL) { delete h; return ab_fail(nullptr, AB_ERR_INVALID, "bad grid size"); }
+        h->dims[d] = (int)desc->grid_dims[d];
+        ncells *= desc->grid_dims[d];
+    }
+    if (ncells > 2000000000LL) { delete h; return ab_fail(nullptr, AB_ERR_INVALID, "more than 2e9 cells"); }
+    h->ncells = ncells;
+    h->tsize = ab_dtype_size(h->dtype);
+    h->desc = *desc;
+
+    cudaError_t e;
+#define CK(call) if ((e = (call)) != cudaSuccess) { std::string m = std::string("CUDA error: ") + cudaGetErrorString(e) + " in " #call; ab_destroy(h); return ab_fail(nullptr, AB_ERR_CUDA, m); }
+    CK(cudaSetDevice(device));
+    CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    CK(cudaEventCreate(&h->ev0));
+    CK(cudaEventCreate(&h->ev1));
+    size_t padded = ((size_t)ncells + SCAN_TILE - 1) / SCAN_TILE * SCAN_TILE;
+    CK(cudaMalloc((void**)&h->cell_count, padded * sizeof(uint32_t)));
+    CK(cudaMemset(h->cell_count, 0, padded * sizeof(uint32_t)));
+    CK(cudaMalloc((void**)&h->cell_start, (padded + 1) * sizeof(uint32_t)));
+    CK(cudaMemset(h->cell_start, 0, (padded + 1) * sizeof(uint32_t)));
+    h->scan_status_len = padded / SCAN_TILE + 1;
+    CK(cudaMalloc((void**)&h->scan_status, h->scan_status_len * sizeof(unsigned long long)));
+    CK(cudaMemset(h->scan_status, 0, h->scan_status_len * sizeof(unsigned long long)));
+    CK(cudaMalloc((void**)&h->scan_ticket, sizeof(uint32_t)));
+    CK(cudaMemset(h->scan_ticket, 0, sizeof(uint32_t)));
+    CK(cudaMalloc((void**)&h->d_err, sizeof(int)));
+    CK(cudaMemset(h->d_err, 0, sizeof(int)));
+    CK(cudaMallocHost((void**)&h->h_err, sizeof(int)));
+    if (desc->kind == AB_SPACE_GRID_SINGLE) {
+        CK(cudaMalloc((void**)&h->grid_ids, (size_t)ncells * sizeof(int32_t)));
+        CK(cudaMemset(h->grid_ids, 0, (size_t)ncells * sizeof(int32_t)));
+    }
+#undef CK
+    ab_field pos;
+    pos.name = "pos"; pos.dtype = h->dtype; pos.ncomp = h->D; pos.esize = h->tsize;
+    h->fields.push_back(pos);
+    if (desc->kind == AB_SPACE_CONTINUOUS) {
+        ab_field vel = pos;
+        vel.name = "vel";
+        h->fields.push_back(vel);
+    }
+    *out = h;
+    return AB_OK;
+}
+
+int ab_destroy(ab_handle* h) {
+    if (!h) return AB_OK;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    ab_comm_free(h);
+    free_population(h);
+    void* ptrs[] = {h->cell_count, h->cell_start, h->scan_status, h->scan_ticket, h->d_err, h->scratch, h->scratch2,
+                    h->cell_sums, h->pairs_offsets, h->grid_ids};
+    for (void* p : ptrs) if (p) cudaFree(p);
+    if (h->h_err) cudaFreeHost(h->h_err);
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+    return AB_OK;
+}
+
+int ab_sync(ab_handle* h) {
+    AB_CUDA(h, cudaStreamSynchronize(h->stream));
+    return AB_OK;
+}
+int64_t ab_nagents(const ab_handle* h) { return h ? h->n : 0; }
+int64_t ab_launch_count(const ab_handle* h) { return h ? h->launches : 0; }
+double ab_last_step_ms(const ab_handle* h) { return h ? h->last_step_ms : 0; }
+
+void* ab_alloc_pinned(int64_t bytes) {
+    void* p = nullptr;
+    if (bytes <= 0 || cudaMallocHost(&p, (size_t)bytes) != cudaSuccess) return nullptr;
+    return p;
+}
+void ab_free_pinned(void* p) { if (p) cudaFreeHost(p); }
+
+int ab_set_profiling(ab_handle* h, int on) {
+    h->profiling = on != 0;
+    h->kstats.clear();
+    return AB_OK;
+}
+int ab_kernel_times(ab_handle* h, const char** names, double* ms, int64_t* launches, int cap) {
+    int k = 0;
+    for (auto& s : h->kstats) {
+        if (k < cap) { if (names) names[k] = s.name; if (ms) ms[k] = s.ms; if (launches) launches[k] = s.launches; }
+        ++k;
+    }
+    return k;
+}
+
+int ab_field_id(const ab_handle* h, const char* name) {
+    for (size_t i = 0; i < h->fields.size(); ++i) if (h->fields[i].name == name) return (int)i;
+    return AB_ERR_INVALID;
+}
+
+static int alloc_field(ab_handle* h, ab_field& f) {
+    for (int b = 0; b < 2; ++b) {
+        if (f.buf[b]) continue;
+        size_t bytes = (size_t)f.ncomp * h->cap * f.esize;
+        AB_CUDA(h, cudaMalloc(&f.buf[b], bytes ? bytes : 16));
+        AB_CUDA(h, cudaMemsetAsync(f.buf[b], 0, bytes ? bytes : 16, h->stream));
+    }
+    return AB_OK;
+}
+
+int ab_register_field(ab_handle* h, const char* name, int dtype, int ncomp) {
+    if (!name || ncomp < 1 || ncomp > 16 || ab_dtype_size(dtype) == 0) return ab_fail(h, AB_ERR_INVALID, "bad field spec");
+    if (ab_field_id(h, name) >= 0) return ab_fail(h, AB_ERR_INVALID, std::string("field already registered: ") + name);
+    AB_CUDA(h, cudaSetDevice(h->device));
+    ab_field f;
+    f.name = name; f.dtype = dtype; f.ncomp = ncomp; f.esize = ab_dtype_size(dtype);
+    if (h->cap > 0) AB_TRY(alloc_field(h, f));
+    h->fields.push_back(f);
+    return (int)h->fields.size() - 1;
+}
+
+int ab_resize(ab_handle* h, int64_t n) {
+    if (n < 0 || n > 2000000000LL) return ab_fail(h, AB_ERR_INVALID, "bad agent count");
+    AB_CUDA(h, cudaSetDevice(h->device));
+    AB_CUDA(h, cudaStreamSynchronize(h->stream));
+    if (n > h->cap) {
+        free_population(h);
+        h->cap = (n + 63) / 64 * 64;    // 64-agent multiple keeps every component array 256 B aligned
+        for (auto& f : h->fields) AB_TRY(alloc_field(h, f));
+        size_t tb = (size_t)h->D * h->cap * h->tsize;
+        AB_CUDA(h, cudaMalloc(&h->tmp_pos, tb));
+        AB_CUDA(h, cudaMalloc(&h->tmp_vel, tb));
+        size_t ib = (size_t)h->cap * 4;
+        void** ints[] = {(void**)&h->id[0], (void**)&h->id[1], (void**)&h->key[0], (void**)&h->key[1],
+                         (void**)&h->newkey, (void**)&h->rank, (void**)&h->idtmp, (void**)&h->perm,
+                         (void**)&h->slot_of_id, (void**)&h->ncount};
+        for (void** p : ints) { AB_CUDA(h, cudaMalloc(p, ib)); AB_CUDA(h, cudaMemsetAsync(*p, 0, ib, h->stream)); }
+    }
+    h->n = n;
+    if (n > 0) {
+        AB_LAUNCH(h, "k_iota");
+        k_iota<<<ab_blocks(n, 256), 256, 0, h->stream>>>(h->id[h->cur], h->slot_of_id, (int)n);
+    }
+    h->slot_map_valid = true;
+    h->index_valid = false;
+    h->pairs_n = -1;
+    if (h->grid_ids) AB_CUDA(h, cudaMemsetAsync(h->grid_ids, 0, (size_t)h->ncells * sizeof(int32_t), h->stream));
+    AB_CUDA(h, cudaStreamSynchronize(h->stream));
+    return AB_OK;
+}
+
+int ab_upload(ab_handle* h, int field, const void* host, int64_t n) {
+    if (field < 0 || field >= (int)h->fields.size()) return ab_fail(h, AB_ERR_INVALID, "bad field id");
+    if (n != h->n) return ab_fail(h, AB_ERR_INVALID, "upload length must equal the agent count (ab_resize first)");
+    if (n == 0) return AB_OK;
+    if (!host) return ab_fail(h, AB_ERR_INVALID, "null host pointer");
+    AB_CUDA(h, cudaSetDevice(h->device));
+    ab_field& f = h->fields[field];
+    size_t bytes = (size_t)n * f.ncomp * f.esize;
+    void* stage;
+    AB_TRY(ab_scratch(h, bytes, &stage));
+    AB_CUDA(h, cudaMemcpyAsync(stage, host, bytes, cudaMemcpyHostToDevice, h->stream));
+    AB_TRY(ab_ensure_slot_map(h));
+    int64_t total = n * f.ncomp;
+    {
+        AB_LAUNCH(h, "k_upload");
+        if (f.esize == 8) k_upload<uint64_t><<<ab_blocks(total, 256), 256, 0, h->stream>>>((const uint64_t*)stage, (uint64_t*)f.buf[h->cur], h->slot_of_id, h->cap, (int)n, f.ncomp);
+        else if (f.esize == 4) k_upload<uint32_t><<<ab_blocks(total, 256), 256, 0, h->stream>>>((const uint32_t*)stage, (uint32_t*)f.buf[h->cur], h->slot_of_id, h->cap, (int)n, f.ncomp);
+        else k_upload<uint8_t><<<ab_blocks(total, 256), 256, 0, h->stream>>>((const uint8_t*)stage, (uint8_t*)f.buf[h->cur], h->slot_of_id, h->cap, (int)n, f.ncomp);
+    }
+    AB_CUDA(h, cudaStreamSynchronize(h->stream));
+    if (field == 0) { h->index_valid = false; h->pairs_n = -1; }
+    return AB_OK;
+}
+
+int ab_download(ab_handle* h, int field, void* host, int64_t n) {
+    if (field < 0 || field >= (int)h->fields.size()) return ab_fail(h, AB_ERR_INVALID, "bad field id");
+    if (n != h->n) return ab_fail(h, AB_ERR_INVALID, "download length must equal the agent count");
+    if (n == 0) return AB_OK;
+    if (!host) return ab_fail(h, AB_ERR_INVALID, "null host pointer");
+    AB_CUDA(h, cudaSetDevice(h->device));
+    ab_field& f = h->fields[field];
+    size_t bytes = (size_t)n * f.ncomp * f.esize;
+    void* stage;
+    AB_TRY(ab_scratch(h, bytes, &stage));
+    {
+        AB_LAUNCH(h, "k_download");
+        if (f.esize == 8) k_download<uint64_t><<<ab_blocks(n, 256), 256, 0, h->stream>>>((const uint64_t*)f.buf[h->cur], (uint64_t*)stage, h->id[h->cur], h->cap, (int)n, f.ncomp);
+        else if (f.esize == 4) k_download<uint32_t><<<ab_blocks(n, 256), 256, 0, h->stream>>>((const uint32_t*)f.buf[h->cur], (uint32_t*)stage, h->id[h->cur], h->cap, (int)n, f.ncomp);
+        else k_download<uint8_t><<<ab_blocks(n, 256), 256, 0, h->stream>>>((const uint8_t*)f.buf[h->cur], (uint8_t*)stage, h->id[h->cur], h->cap, (int)n, f.ncomp);
+    }
+    AB_CUDA(h, cudaMemcpyAsync(host, stage, bytes, cudaMemcpyDeviceToHost, h->stream));
+    AB_CUDA(h, cudaStreamSynchronize(h->stream));
+    return AB_OK;
+}
+
+int ab_build_index(ab_handle* h) {
+    AB_CUDA(h, cudaSetDevice(h->device));
+    if (h->desc.kind != AB_SPACE_CONTINUOUS) {
+        return ab_grid_build(h);
+    }
+    h->index_valid = false;
+    return ab_ensure_index(h);
+}
+
+int ab_cells(ab_handle* h, int32_t* out_cells, int64_t n) {
+    if (h->desc.kind != AB_SPACE_CONTINUOUS) return ab_fail(h, AB_ERR_INVALID, "ab_cells is for ContinuousSpace handles");
+    if (n != h->n) return ab_fail(h, AB_ERR_INVALID, "length must equal the agent count");
+    if (n == 0) return AB_OK;
+    AB_CUDA(h, cudaSetDevice(h->device));
+    size_t bytes = (size_t)n * h->D * sizeof(int32_t);
+    void* stage;
+    AB_TRY(ab_scratch(h, bytes, &stage));
+    {
+        AB_LAUNCH(h, "k_cells");
+        const int TB = 256;
+#define CELLS(T, DD) k_cells<T, DD><<<ab_blocks(n, TB), TB, 0, h->stream>>>(make_space<T, DD>(h), (const T*)h->fields[0].buf[h->cur], h->id[h->cur], h->cap, (int)n, (int32_t*)stage)
+        if (h->dtype == AB_F64) { if (h->D == 2) CELLS(double, 2); else CELLS(double, 3); }
+        else { if (h->D == 2) CELLS(float, 2); else CELLS(float, 3); }
+#undef CELLS
+    }
+    AB_CUDA(h, cudaMemcpyAsync(out_cells, stage, bytes, cudaMemcpyDeviceToHost, h->stream));
+    AB_CUDA(h, cudaStreamSynchronize(h->stream));
+    return AB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,306 @@
+// ab_flock.cu — fused flock step (examples/flock.jl:79-108) and bulk movement
+// (src/spaces/continuous.jl:157-194, src/spaces/walk.jl:58-91).
+//
+// One step of `ab_step_flock` = [sweep] + [k_scan, k_bucket, k_place] (ab_core.cu):
+// the sweep reads the current cell-sorted state, computes every bird's new
+// velocity and position from the OLD state (synchronous update), and already
+// emits the next step's cell key and arrival rank, so the re-sort that follows
+// never touches positions again before the final placement.
+//
+// Two sweeps:
+//   k_flock_generic  any space the reference accepts (mixed periodicity, tiny
+//                    grids, clipped offset tables, per-agent parameters).  One
+//                    thread per bird, walks the reference's cell offsets as runs
+//                    of the sorted arrays through L1/L2.
+//   k_flock_tiled    (ab_flock_tiled.cuh) shared-memory tiles for large 2-D/3-D
+//                    spaces with uniform parameters — the throughput path.
+#include "ab_internal.cuh"
+
+template <class T> struct FlockU {
+    T speed, cohere_factor, separation, separate_factor, match_factor;
+    double visual_distance;
+};
+
+template <class T, int D>
+__device__ __forceinline__ void flock_epilogue(const SpaceDev<T, D>& sp, const T* p, const T* v, const T* cohere,
+                                               const T* separate, const T* match, int N, const FlockU<T>& fp,
+                                               T* np, T* nv, int* err) {
+    // flock.jl:100-105
+    T s = 0;
+    const T denom = (T)(N > 1 ? N : 1);
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        T c = cohere[d] * fp.cohere_factor;
+        T sp_ = separate[d] * fp.separate_factor;
+        T m = match[d] * fp.match_factor;
+        nv[d] = v[d] + ((c + sp_) + m) / denom;
+        T sq = nv[d] * nv[d];
+        s = (d == 0) ? sq : s + sq;
+    }
+    const T nrm = ab_sqrt(s);
+    bool bad = false;
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        nv[d] = nv[d] / nrm;
+        // move_agent!(bird, model, speed): continuous.jl:186-194, walk.jl:58-66
+        T t = p[d] + fp.speed * nv[d];
+        t = normalize_coord(t, sp.extent[d], sp.periodic[d]);
+        if (!(t >= T(0) && t <= sp.extent[d])) bad = true;    // continuous.jl:160 (NaN lands here too)
+        np[d] = t;
+    }
+    if (bad) atomicOr(err, AB_EF_OUTSIDE);
+}
+
+template <class T, int D, bool EXACT>
+__global__ void __launch_bounds__(128)
+k_flock_generic(SpaceDev<T, D> sp, FlockU<T> uni, const T* __restrict__ per_agent, const T* __restrict__ pos,
+                const T* __restrict__ vel, const uint32_t* __restrict__ key, const uint32_t* __restrict__ cell_start,
+                int64_t cap, int n, T* __restrict__ npos, T* __restrict__ nvel, uint32_t* __restrict__ newkey,
+                uint32_t* __restrict__ rank, uint32_t* __restrict__ cell_count, const int32_t* __restrict__ ids,
+                int32_t* __restrict__ ncount, int* __restrict__ err) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    FlockU<T> fp = uni;
+    if (per_agent) {
+        fp.speed = per_agent[(size_t)0 * cap + s];
+        fp.cohere_factor = per_agent[(size_t)1 * cap + s];
+        fp.separation = per_agent[(size_t)2 * cap + s];
+        fp.separate_factor = per_agent[(size_t)3 * cap + s];
+        fp.match_factor = per_agent[(size_t)4 * cap + s];
+        fp.visual_distance = (double)per_agent[(size_t)5 * cap + s];
+    }
+    T p[D], v[D];
+    int c[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d) { p[d] = pos[(size_t)d * cap + s]; v[d] = vel[(size_t)d * cap + s]; }
+    unlin_cell<D>(sp.dims, key[s], c);
+    const int gr = grid_radius<T, D>(sp, p, c, fp.visual_distance);
+    const T thr = EXACT ? exact_threshold<T>(fp.visual_distance) : T(0);
+    const T sep2 = fp.separation * fp.separation;
+    // min-image shortcut: inside the box and far from wrap, heading == direct
+    int permask = 0, slowmask = 0;
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        if (sp.periodic[d]) {
+            permask |= 1 << d;
+            if (!((long long)sp.dims[d] >= 2LL * gr + 3)) slowmask |= 1 << d;
+        }
+    }
+    T cohere[D], separate[D], match[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d) cohere[d] = separate[d] = match[d] = T(0);
+    int N = 0;
+    for_each_run<D>(sp.dims, sp.periodic, AB_METRIC_EUCLIDEAN, c, gr, cell_start, false,
+                    [&](uint32_t b, uint32_t e, int wrap) {
+        const int full = (wrap | slowmask) & permask;
+        for (uint32_t j = b; j < e; ++j) {
+            if ((int)j == s) continue;       // nearby_ids(agent, ...) drops the agent's own id
+            T h[D];
+            T d2 = 0;
+#pragma unroll
+            for (int d = 0; d < D; ++d) {
+                T direct = pos[(size_t)d * cap + j] - p[d];
+                if (full & (1 << d)) direct = min_image(direct, sp.extent[d]);   // utilities.jl:185-193
+                h[d] = direct;
+                T sq = direct * direct;
+                d2 = (d == 0) ? sq : d2 + sq;
+            }
+            if (EXACT && !(d2 <= thr)) continue;    // continuous.jl:237-238
+            ++N;
+            const bool close = d2 < sep2;           // flock.jl:93
+#pragma unroll
+            for (int d = 0; d < D; ++d) {
+                cohere[d] += h[d];
+                match[d] += vel[(size_t)d * cap + j];
+                if (close) separate[d] -= h[d];
+            }
+        }
+    });
+    T np[D], nv[D];
+    flock_epilogue<T, D>(sp, p, v, cohere, separate, match, N, fp, np, nv, err);
+    int nc[D];
+    bool ok = pos2cell0<T, D>(sp, np, nc);
+    if (!ok) atomicOr(err, AB_EF_NUMERIC);
+    const uint32_t k = lin_cell<D>(sp.dims, nc);
+#pragma unroll
+    for (int d = 0; d < D; ++d) { npos[(size_t)d * cap + s] = np[d]; nvel[(size_t)d * cap + s] = nv[d]; }
+    newkey[s] = k;
+    rank[s] = atomicAdd(&cell_count[k], 1u);
+    if (ncount) ncount[ids[s]] = N;     // diagnostic, last step of a call only
+}
+
+#include "ab_flock_tiled.cuh"
+
+// Bulk Euler move / walk for a set of slots (NULL = all):
+// move_agent!(agent, model, dt) continuous.jl:186-194 and walk! walk.jl:58-66.
+template <class T, int D>
+__global__ void k_move(SpaceDev<T, D> sp, T* __restrict__ pos, const T* __restrict__ vel, int64_t cap, int n,
+                       const int32_t* __restrict__ slots, int nactive, T dt, const T* __restrict__ directions,
+                       int* __restrict__ err) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nactive) return;
+    int s = slots ? slots[t] : t;
+    if (s < 0 || s >= n) return;
+    bool bad = false;
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        T dir = directions ? directions[(size_t)t * D + d] : dt * vel[(size_t)d * cap + s];
+        T x = pos[(size_t)d * cap + s] + dir;
+        x = normalize_coord(x, sp.extent[d], sp.periodic[d]);
+        if (!(x >= T(0) && x <= sp.extent[d])) bad = true;
+        pos[(size_t)d * cap + s] = x;
+    }
+    if (bad) atomicOr(err, AB_EF_OUTSIDE);
+}
+
+__global__ void k_ids_to_slots(const int64_t* __restrict__ ids, const int32_t* __restrict__ slot_of_id, int n,
+                               int nactive, int32_t* __restrict__ slots, int* __restrict__ err) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nactive) return;
+    int64_t id = ids[t];
+    if (id < 1 || id > n) { slots[t] = -1; atomicOr(err, AB_EF_OVERFLOW); return; }
+    slots[t] = slot_of_id[id - 1];
+}
+
+template <class T, int D>
+static int move_t(ab_handle* h, double dt, const void* directions_dev, const int32_t* slots, int nactive) {
+    if (nactive == 0) return AB_OK;
+    AB_LAUNCH(h, "k_move");
+    k_move<T, D><<<ab_blocks(nactive, 256), 256, 0, h->stream>>>(make_space<T, D>(h), (T*)h->fields[0].buf[h->cur],
+                                                                 (const T*)h->fields[1].buf[h->cur], h->cap, (int)h->n,
+                                                                 slots, nactive, (T)dt, (const T*)directions_dev, h->d_err);
+    return AB_OK;
+}
+
+static int move_common(ab_handle* h, double dt, const void* directions, const int64_t* active_ids, int64_t nactive) {
+    if (h->desc.kind != AB_SPACE_CONTINUOUS) return ab_fail(h, AB_ERR_INVALID, "continuous-space call on a grid handle");
+    AB_CUDA(h, cudaSetDevice(h->device));
+    if (h->n == 0) return AB_OK;
+    int32_t* slots = nullptr;
+    void* dir_dev = nullptr;
+    int na = active_ids ? (int)nactive : (int)h->n;
+    if (active_ids && nactive < 0) return ab_fail(h, AB_ERR_INVALID, "negative nactive");
+    size_t dir_bytes = directions ? (size_t)na * h->D * h->tsize : 0;
+    if (active_ids || directions) {
+        size_t ids_bytes = active_ids ? (size_t)na * sizeof(int64_t) : 0;
+        size_t slots_bytes = active_ids ? (size_t)na * sizeof(int32_t) : 0;
+        size_t o1 = (ids_bytes + 255) / 256 * 256, o2 = o1 + (slots_bytes + 255) / 256 * 256;
+        char* base;
+        AB_TRY(ab_scratch(h, o2 + dir_bytes + 256, (void**)&base));
+        if (active_ids && na > 0) {
+            AB_CUDA(h, cudaMemcpyAsync(base, active_ids, ids_bytes, cudaMemcpyHostToDevice, h->stream));
+            AB_TRY(ab_ensure_slot_map(h));
+            slots = (int32_t*)(base + o1);
+            AB_LAUNCH(h, "k_ids_to_slots");
+            k_ids_to_slots<<<ab_blocks(na, 256), 256, 0, h->stream>>>((const int64_t*)base, h->slot_of_id, (int)h->n, na, slots, h->d_err);
+        }
+        if (directions && na > 0) {
+            dir_dev = base + o2;
+            AB_CUDA(h, cudaMemcpyAsync(dir_dev, directions, dir_bytes, cudaMemcpyHostToDevice, h->stream));
+        }
+    }
+    if (directions && !active_ids) {
+        // directions are given in id order: address slots through the id→slot map
+        AB_TRY(ab_ensure_slot_map(h));
+        slots = h->slot_of_id;
+    }
+    int rc;
+    if (h->dtype == AB_F64) rc = h->D == 2 ? move_t<double, 2>(h, dt, dir_dev, slots, na) : move_t<double, 3>(h, dt, dir_dev, slots, na);
+    else rc = h->D == 2 ? move_t<float, 2>(h, dt, dir_dev, slots, na) : move_t<float, 3>(h, dt, dir_dev, slots, na);
+    AB_TRY(rc);
+    h->index_valid = false;
+    h->pairs_n = -1;
+    int e = ab_check_device_errors(h);
+    if (e == AB_ERR_INVALID) return ab_fail(h, AB_ERR_INVALID, "agent id out of range");
+    return e;
+}
+
+template <class T, int D>
+static int flock_steps_t(ab_handle* h, const ab_flock_params* p, int64_t nsteps) {
+    const int n = (int)h->n;
+    SpaceDev<T, D> sp = make_space<T, D>(h);
+    FlockU<T> u;
+    u.speed = (T)p->speed; u.cohere_factor = (T)p->cohere_factor; u.separation = (T)p->separation;
+    u.separate_factor = (T)p->separate_factor; u.match_factor = (T)p->match_factor;
+    u.visual_distance = p->visual_distance;
+    const bool exact = p->search == AB_SEARCH_EXACT;
+    int pa_field = p->per_agent_field;
+    if (pa_field >= 0) {
+        if (pa_field >= (int)h->fields.size() || h->fields[pa_field].ncomp != 6 || h->fields[pa_field].dtype != h->dtype)
+            return ab_fail(h, AB_ERR_INVALID, "per_agent_field must be a 6-component column of the space's float type");
+    }
+    // kernel choice
+    bool tiled = false;
+    TiledPlan plan;
+    if (p->kernel != 1 && pa_field < 0) tiled = plan_tiled<T, D>(h, p->visual_distance, (double)u.separation, exact, &plan);
+    if (p->kernel == 2 && !tiled) return ab_fail(h, AB_ERR_INVALID, "tiled flock kernel not applicable to this configuration");
+    for (int64_t st = 0; st < nsteps; ++st) {
+        const int cur = h->cur;
+        const T* pos = (const T*)h->fields[0].buf[cur];
+        const T* vel = (const T*)h->fields[1].buf[cur];
+        int32_t* ncount = (st == nsteps - 1) ? h->ncount : nullptr;   // neighbour counts by id (diagnostic)
+        if (tiled) {
+            AB_TRY((launch_tiled<T, D>(h, sp, u, exact, plan, ncount)));
+        } else {
+            const T* pa = pa_field >= 0 ? (const T*)h->fields[pa_field].buf[cur] : nullptr;
+            AB_LAUNCH(h, "k_flock_generic");
+            const int TB = 128;
+            if (exact)
+                k_flock_generic<T, D, true><<<ab_blocks(n, TB), TB, 0, h->stream>>>(
+                    sp, u, pa, pos, vel, h->key[cur], h->cell_start, h->cap, n, (T*)h->tmp_pos, (T*)h->tmp_vel,
+                    h->newkey, h->rank, h->cell_count, h->id[cur], ncount, h->d_err);
+            else
+                k_flock_generic<T, D, false><<<ab_blocks(n, TB), TB, 0, h->stream>>>(
+                    sp, u, pa, pos, vel, h->key[cur], h->cell_start, h->cap, n, (T*)h->tmp_pos, (T*)h->tmp_vel,
+                    h->newkey, h->rank, h->cell_count, h->id[cur], ncount, h->d_err);
+        }
+        AB_TRY(ab_reindex_from(h, h->tmp_pos, h->tmp_vel, true));
+    }
+    return AB_OK;
+}
+
+extern "C" {
+
+int ab_move(ab_handle* h, double dt, const int64_t* active_ids, int64_t nactive) {
+    return move_common(h, dt, nullptr, active_ids, nactive);
+}
+
+int ab_walk(ab_handle* h, const void* directions, const int64_t* active_ids, int64_t nactive, int ifempty) {
+    if (h->desc.kind != AB_SPACE_CONTINUOUS) {
+        return ab_grid_walk(h, directions, active_ids, nactive, ifempty);
+    }
+    if (!directions) return ab_fail(h, AB_ERR_INVALID, "null directions");
+    return move_common(h, 0.0, directions, active_ids, nactive);
+}
+
+int ab_step_flock(ab_handle* h, const ab_flock_params* p, int64_t nsteps) {
+    if (!p) return ab_fail(h, AB_ERR_INVALID, "null params");
+    if (h->desc.kind != AB_SPACE_CONTINUOUS) return ab_fail(h, AB_ERR_INVALID, "flock rule needs a ContinuousSpace handle");
+    if (nsteps < 0) return ab_fail(h, AB_ERR_INVALID, "negative nsteps");
+    AB_CUDA(h, cudaSetDevice(h->device));
+    if (h->n == 0 || nsteps == 0) return AB_OK;
+    AB_TRY(ab_ensure_index(h));
+    if (ab_comm_active(h)) return ab_comm_step_flock(h, p, nsteps);
+    AB_CUDA(h, cudaEventRecord(h->ev0, h->stream));
+    int rc;
+    if (h->dtype == AB_F64) rc = h->D == 2 ? flock_steps_t<double, 2>(h, p, nsteps) : flock_steps_t<double, 3>(h, p, nsteps);
+    else rc = h->D == 2 ? flock_steps_t<float, 2>(h, p, nsteps) : flock_steps_t<float, 3>(h, p, nsteps);
+    AB_TRY(rc);
+    AB_CUDA(h, cudaEventRecord(h->ev1, h->stream));
+    AB_TRY(ab_check_device_errors(h));
+    float ms = 0;
+    AB_CUDA(h, cudaEventElapsedTime(&ms, h->ev0, h->ev1));
+    h->last_step_ms = ms;
+    return AB_OK;
+}
+
+int ab_flock_last_counts(ab_handle* h, int32_t* counts, int64_t n) {
+    if (n != h->n) return ab_fail(h, AB_ERR_INVALID, "length must equal the agent count");
+    if (n == 0) return AB_OK;
+    AB_CUDA(h, cudaSetDevice(h->device));
+    AB_CUDA(h, cudaMemcpyAsync(counts, h->ncount, (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
+    AB_CUDA(h, cudaStreamSynchronize(h->stream));
+    return AB_OK;
+}
+
+}  // extern "C"

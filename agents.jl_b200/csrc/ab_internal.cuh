@@ -1,0 +1,455 @@
+// ab_internal.cuh — shared definitions of the B200-native Agents.jl hot path.
+//
+// Data layout in HBM (one population per handle, capacity `cap` agents):
+//   * every agent column ("field") is stored SoA *per component* and in
+//     CELL-SORTED order: comp c of field f lives at buf[cur] + c*cap.  Slot s
+//     holds the agent id[cur][s] (0-based).  The sorted order is persistent:
+//     a step writes the next state directly into the other buffer in the next
+//     step's sorted order, so there is no per-step gather/scatter by id.
+//   * cell_start[ncells+1]: first slot of each cell (column-major linear cell,
+//     like Julia's stored_ids[c...] — src/spaces/grid_multi.jl:73).  Within a
+//     cell, slots are ordered by id, so every floating-point sum over a
+//     cell's agents has one canonical order (bitwise reproducible runs).
+//   * key[cur][s]: linear cell of slot s.
+// Compiled with --fmad=false: predicates that decide neighbour sets and cells
+// must round exactly like the reference (Julia never contracts a*b+c here);
+// fma() is used explicitly only where results are tolerance-checked.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/agents_b200.h"
+
+#define AB_VERSION 100
+
+enum { AB_EF_OUTSIDE = 1, AB_EF_NUMERIC = 2, AB_EF_OCCUPIED = 4, AB_EF_OVERFLOW = 8 };
+
+struct ab_field {
+    std::string name;
+    int dtype = AB_F64;
+    int ncomp = 1;
+    size_t esize = 8;
+    void* buf[2] = {nullptr, nullptr};
+};
+
+struct ab_kernel_stat {
+    const char* name;
+    double ms;
+    int64_t launches;
+};
+
+struct ab_comm;   // multi-GPU state (ab_comm.cu)
+
+struct ab_handle {
+    ab_space_desc desc{};
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    int D = 2;
+    int dtype = AB_F64;
+    size_t tsize = 8;
+    int64_t n = 0, cap = 0;
+    int64_t ncells = 1;
+    int dims[3] = {1, 1, 1};
+
+    std::vector<ab_field> fields;      // 0 = pos, 1 = vel (continuous); 0 = pos (grids)
+    int cur = 0;
+    void* tmp_pos = nullptr;           // D*cap of T: new state in OLD slot order
+    void* tmp_vel = nullptr;
+    int32_t* id[2] = {nullptr, nullptr};
+    uint32_t* key[2] = {nullptr, nullptr};
+    uint32_t* newkey = nullptr;        // per old slot
+    uint32_t* rank = nullptr;          // arrival rank inside the new cell (atomic order)
+    uint32_t* cell_count = nullptr;    // ncells (zero between uses)
+    uint32_t* cell_start = nullptr;    // ncells + 1
+    int32_t* idtmp = nullptr;          // ids bucketed by cell, arrival order
+    int32_t* perm = nullptr;           // new slot -> old slot (for extra fields)
+    int32_t* slot_of_id = nullptr;
+    bool slot_map_valid = false;
+    bool index_valid = false;
+    int32_t* ncount = nullptr;         // neighbour count per slot of the last flock step
+
+    // cell sums for the approximate-search fast path (ab_flock.cu)
+    void* cell_sums = nullptr;         // ncells * 2*D of T
+    size_t cell_sums_bytes = 0;
+
+    // single-pass scan state
+    unsigned long long* scan_status = nullptr;
+    size_t scan_status_len = 0;
+    uint32_t* scan_ticket = nullptr;
+    uint32_t scan_epoch = 0;
+
+    int* d_err = nullptr;              // device error flag word
+    int* h_err = nullptr;              // pinned mirror
+
+    void* scratch = nullptr;           // grow-only device scratch for uploads / queries
+    size_t scratch_bytes = 0;
+    void* scratch2 = nullptr;
+    size_t scratch2_bytes = 0;
+
+    // pairs query memo
+    double pairs_r = 0;
+    int pairs_search = 0;
+    int64_t pairs_n = -1;
+    unsigned long long* pairs_offsets = nullptr;   // per slot exclusive offsets (device)
+    size_t pairs_offsets_len = 0;
+
+    // grid spaces
+    int32_t* grid_ids = nullptr;       // GridSpaceSingle: id per cell (0 = empty), 1-based
+    int64_t last_moved = 0;
+
+    ab_comm* comm = nullptr;
+
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    double last_step_ms = 0;
+    int64_t launches = 0;
+    bool profiling = false;
+    std::vector<ab_kernel_stat> kstats;
+    std::string err;
+};
+
+// ---------------------------------------------------------------------------
+// host helpers
+// ---------------------------------------------------------------------------
+int ab_fail(ab_handle* h, int code, const std::string& msg);
+int ab_cuda_fail(ab_handle* h, cudaError_t e, const char* what);
+#define AB_CUDA(h, call)                                              \
+    do {                                                              \
+        cudaError_t _e = (call);                                      \
+        if (_e != cudaSuccess) return ab_cuda_fail((h), _e, #call);   \
+    } while (0)
+#define AB_TRY(expr)                \
+    do {                            \
+        int _rc = (expr);           \
+        if (_rc != AB_OK) return _rc; \
+    } while (0)
+
+int ab_scratch(ab_handle* h, size_t bytes, void** out);     // scratch  (grow-only)
+int ab_scratch2(ab_handle* h, size_t bytes, void** out);    // scratch2 (grow-only)
+int ab_check_device_errors(ab_handle* h);                   // reads + clears d_err
+int ab_ensure_index(ab_handle* h);
+int ab_ensure_slot_map(ab_handle* h);
+int ab_reindex_from(ab_handle* h, const void* src_pos, const void* src_vel, bool count_done);
+size_t ab_dtype_size(int dtype);
+// cross-file internals (C++ linkage)
+void ab_comm_free(ab_handle* h);
+int ab_comm_active(const ab_handle* h);
+int ab_comm_step_flock(ab_handle* h, const ab_flock_params* p, int64_t nsteps);
+int ab_grid_build(ab_handle* h);
+int ab_grid_walk(ab_handle* h, const void* directions, const int64_t* active_ids, int64_t nactive, int ifempty);
+int ab_grid_nearby(ab_handle* h, const void* qpos, const int64_t* qids, int64_t nq, double r, int exclude_self,
+                   int64_t* counts, const int64_t* offsets, int64_t* ids_out);
+
+// launch bookkeeping: every kernel launch of the library goes through this
+struct ab_launch_scope {
+    ab_handle* h;
+    const char* name;
+    cudaEvent_t a = nullptr, b = nullptr;
+    ab_launch_scope(ab_handle* h_, const char* name_);
+    ~ab_launch_scope();
+};
+#define AB_CAT2(a, b) a##b
+#define AB_CAT(a, b) AB_CAT2(a, b)
+#define AB_LAUNCH(h, name) ab_launch_scope AB_CAT(_scope_, __LINE__)((h), (name))
+
+static inline int ab_blocks(int64_t n, int threads) { return (int)((n + threads - 1) / threads); }
+
+// ---------------------------------------------------------------------------
+// device-side space description and reference arithmetic
+// ---------------------------------------------------------------------------
+template <class T, int D> struct SpaceDev {
+    T extent[D];
+    T spacing;
+    double extent_d[D];
+    double spacing_d;
+    int dims[D];
+    bool periodic[D];
+    int metric;
+};
+
+template <class T, int D> static inline SpaceDev<T, D> make_space(const ab_handle* h) {
+    SpaceDev<T, D> s;
+    for (int d = 0; d < D; ++d) {
+        s.extent[d] = (T)h->desc.extent[d];
+        s.extent_d[d] = (double)s.extent[d];
+        s.dims[d] = h->dims[d];
+        s.periodic[d] = h->desc.periodic[d] != 0;
+    }
+    s.spacing = (T)h->desc.spacing;
+    s.spacing_d = (double)s.spacing;
+    s.metric = h->desc.kind == AB_SPACE_CONTINUOUS ? AB_METRIC_EUCLIDEAN : h->desc.metric;
+    return s;
+}
+
+#ifdef __CUDACC__
+
+__device__ __forceinline__ double ab_sqrt(double x) { return sqrt(x); }
+__device__ __forceinline__ float ab_sqrt(float x) { return sqrtf(x); }
+__device__ __forceinline__ double ab_fmod(double x, double y) { return fmod(x, y); }
+__device__ __forceinline__ float ab_fmod(float x, float y) { return fmodf(x, y); }
+__device__ __forceinline__ double ab_next(double x, double dir) { return nextafter(x, dir); }
+__device__ __forceinline__ float ab_next(float x, float dir) { return nextafterf(x, dir); }
+
+// Julia mod(x::T, y::T) for floats — base/float.jl; used by normalize_position
+// (src/spaces/walk.jl:77-79).  Can return exactly y.
+template <class T> __device__ __forceinline__ T jl_mod(T x, T y) {
+    // fast exact cases for 0 <= x < 2y (the common Euler step): fmod(x,y) == x or x - y
+    T r;
+    if (x >= T(0) && x < y) r = x;
+    else r = ab_fmod(x, y);
+    if (r == T(0)) return copysign(r, y);
+    if ((r > T(0)) != (y > T(0))) return r + y;
+    return r;
+}
+template <class T> __device__ __forceinline__ T jl_sign(T x) { return x > T(0) ? T(1) : (x < T(0) ? T(-1) : x); }
+__device__ __forceinline__ int jl_mod1(int x, int y) {
+    int m = x % y;
+    if (m < 0) m += y;
+    return m == 0 ? y : m;
+}
+
+// pos2cell — src/spaces/continuous.jl:112-113: max(1, ceil(Int, p / spacing)),
+// returned 0-based.  IEEE division (never p * (1/spacing)).  Sets *bad when the
+// reference would throw (NaN/Inf → InexactError) or index out of the grid.
+template <class T, int D>
+__device__ __forceinline__ bool pos2cell0(const SpaceDev<T, D>& sp, const T* p, int* c) {
+    bool ok = true;
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        T q = p[d] / sp.spacing;
+        T cq = ceil(q);
+        if (!(cq <= T(2147483000.0)) || !(cq >= T(-2147483000.0))) { ok = false; cq = T(1); }   // NaN / Inf / huge
+        int ci = (int)cq;
+        ci = ci < 1 ? 1 : ci;
+        if (ci > sp.dims[d]) { ok = false; ci = sp.dims[d]; }
+        c[d] = ci - 1;
+    }
+    return ok;
+}
+template <int D> __device__ __forceinline__ uint32_t lin_cell(const int* dims, const int* c) {
+    uint32_t lin = (uint32_t)c[D - 1];
+#pragma unroll
+    for (int d = D - 2; d >= 0; --d) lin = lin * (uint32_t)dims[d] + (uint32_t)c[d];
+    return lin;
+}
+template <int D> __device__ __forceinline__ void unlin_cell(const int* dims, uint32_t lin, int* c) {
+#pragma unroll
+    for (int d = 0; d < D - 1; ++d) {
+        uint32_t q = lin / (uint32_t)dims[d];
+        c[d] = (int)(lin - q * (uint32_t)dims[d]);
+        lin = q;
+    }
+    c[D - 1] = (int)lin;
+}
+
+// grid_r = ceil(Int, (r + δ)/spacing), δ = distance_from_cell_center —
+// src/spaces/continuous.jl:116-121, :221-225.  `cell .- 0.5` is Float64 in
+// Julia whatever T is, so this is double arithmetic on promoted values.
+template <class T, int D>
+__device__ __forceinline__ int grid_radius(const SpaceDev<T, D>& sp, const T* p, const int* c0, double r) {
+    double s = 0;
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        double centre = sp.spacing_d * ((double)(c0[d] + 1) - 0.5);
+        double direct = fabs((double)p[d] - centre);
+        double m = sp.periodic[d] ? fmin(direct, sp.extent_d[d] - direct) : direct;
+        double sq = m * m;
+        s = (d == 0) ? sq : s + sq;
+    }
+    double delta = sqrt(s);
+    double g = ceil((r + delta) / sp.spacing_d);
+    if (!(g < 1.0e9)) g = 1.0e9;      // r = Inf etc.: clipped by the hyper-rectangle rule anyway
+    if (!(g > -1.0e9)) g = -1.0e9;
+    return (int)g;
+}
+
+// Largest s (of type T) with (double)sqrt_T(s) <= r.  The reference's exact
+// filter is `euclidean_distance(...) <= r` = sqrt(Σ m²) <= r
+// (src/spaces/continuous.jl:237-238); sqrt is monotone, so comparing the sum of
+// squares with this threshold is bit-identical and needs no sqrt per candidate.
+template <class T> __device__ __forceinline__ T exact_threshold(double r) {
+    if (!(r >= 0.0)) return T(-1);
+    if (isinf(r)) return (T)r;
+    T s = (T)(r * r);
+    const T inf = (T)INFINITY;
+    while ((double)ab_sqrt(s) > r) s = ab_next(s, -inf);
+    for (;;) {
+        T nx = ab_next(s, inf);
+        if (nx == s || !((double)ab_sqrt(nx) <= r)) break;
+        s = nx;
+    }
+    return s;
+}
+
+// Per-dimension offset range of calculate_hyperrectangle for integer radius r0
+// (src/spaces/grid_general.jl:47-89).
+template <int D>
+__device__ __forceinline__ void hyper_ranges(const int* dims, const bool* periodic, int r0, int* lo, int* hi) {
+    bool all_notover = true;
+#pragma unroll
+    for (int d = 0; d < D; ++d) all_notover = all_notover && (periodic[d] ? (r0 < dims[d] / 2) : (r0 < dims[d]));
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        if (all_notover) { lo[d] = -r0; hi[d] = r0; }
+        else if (periodic[d]) {
+            int half = dims[d] / 2;
+            int rm = r0 < half ? r0 : half;
+            lo[d] = -rm;
+            hi[d] = rm - ((rm == half && (dims[d] % 2) == 0) ? 1 : 0);
+        } else {
+            int rm = r0 < dims[d] ? r0 : dims[d];
+            lo[d] = -rm; hi[d] = rm;
+        }
+    }
+}
+
+__device__ __forceinline__ int isqrt_floor(long long v) {
+    if (v <= 0) return 0;
+    long long w = (long long)sqrt((double)v);
+    while (w * w > v) --w;
+    while ((w + 1) * (w + 1) <= v) ++w;
+    return (int)w;
+}
+
+// Emits the slot runs of the cells [a, b] (inclusive, unwrapped x cell
+// coordinates, at most dims0 of them) of one cell row, in ascending-offset
+// order, wrapping (periodic) or clipping (non-periodic) at the x boundary.
+template <class F>
+__device__ __forceinline__ void emit_xrange(int dims0, bool periodic0, const uint32_t* __restrict__ cell_start,
+                                            uint32_t rowbase, int a, int b, int wrap, F&& f) {
+    if (a > b) return;
+    if (!periodic0) {
+        if (a < 0) a = 0;
+        if (b >= dims0) b = dims0 - 1;
+        if (a <= b) f(cell_start[rowbase + a], cell_start[rowbase + b + 1], wrap);
+        return;
+    }
+    if (a < 0) {
+        int e = b < -1 ? b : -1;
+        f(cell_start[rowbase + a + dims0], cell_start[rowbase + e + dims0 + 1], wrap | 1);
+        a = 0;
+    }
+    if (a <= b) {
+        int e = b < dims0 - 1 ? b : dims0 - 1;
+        if (a <= e) f(cell_start[rowbase + a], cell_start[rowbase + e + 1], wrap);
+        if (b >= dims0) {
+            int s2 = a > dims0 ? a : dims0;
+            f(cell_start[rowbase + s2 - dims0], cell_start[rowbase + b - dims0 + 1], wrap | 1);
+        }
+    }
+}
+
+// Walks the cells of offsets_within_radius(space, r0) around cell c0 in the
+// reference's order (Iterators.product: first dimension fastest —
+// src/spaces/grid_general.jl:138-151) applying the wrap / skip rules of
+// GridSpaceIdIterator (src/spaces/grid_multi.jl:203-232).  Cells with
+// consecutive x are consecutive in the sorted layout, so the walk yields RUNS:
+// f(slot_begin, slot_end, wrapmask) where bit d of wrapmask says the run was
+// reached across the periodic boundary of dimension d.  skip_zero drops the
+// zero offset (offsets_within_radius_no_0, grid_general.jl:165-179).
+template <int D, class F>
+__device__ __forceinline__ void for_each_run(const int* dims, const bool* periodic, int metric, const int* c0,
+                                             int r0, const uint32_t* __restrict__ cell_start, bool skip_zero,
+                                             F&& f) {
+    if (r0 < 0) {   // empty product → calculate_offsets pushes the zero offset (grid_general.jl:149)
+        if (skip_zero) return;
+        uint32_t l = lin_cell<D>(dims, c0);
+        f(cell_start[l], cell_start[l + 1], 0);
+        return;
+    }
+    int lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
+    hyper_ranges<D>(dims, periodic, r0, lo, hi);
+    const long long r2 = (long long)r0 * r0;
+    for (int bz = lo[2]; bz <= hi[2]; ++bz) {      // lo[2] == hi[2] == 0 when D == 2
+        int wrapz = 0, cz = 0;
+        if (D == 3) {
+            cz = c0[2] + bz;
+            if (cz < 0 || cz >= dims[2]) {
+                if (!periodic[2]) continue;
+                cz = cz < 0 ? cz + dims[2] : cz - dims[2];
+                wrapz = 4;
+            }
+        }
+        for (int by = lo[1]; by <= hi[1]; ++by) {
+            int w;   // x half-width the metric allows on this row
+            if (metric == AB_METRIC_EUCLIDEAN) {
+                long long rem = r2 - (long long)by * by - (long long)bz * bz;
+                if (rem < 0) continue;
+                w = isqrt_floor(rem);
+            } else if (metric == AB_METRIC_MANHATTAN) {
+                w = r0 - (by < 0 ? -by : by) - (bz < 0 ? -bz : bz);
+                if (w < 0) continue;
+            } else w = 0x3fffffff;
+            int xl = lo[0] > -w ? lo[0] : -w;
+            int xh = hi[0] < w ? hi[0] : w;
+            if (xl > xh) continue;
+            int wrap = wrapz;
+            int cy = c0[1] + by;
+            if (cy < 0 || cy >= dims[1]) {
+                if (!periodic[1]) continue;
+                cy = cy < 0 ? cy + dims[1] : cy - dims[1];
+                wrap |= 2;
+            }
+            uint32_t rowbase = (D == 3) ? ((uint32_t)cz * (uint32_t)dims[1] + (uint32_t)cy) * (uint32_t)dims[0]
+                                        : (uint32_t)cy * (uint32_t)dims[0];
+            if (skip_zero && by == 0 && bz == 0 && xl <= 0 && xh >= 0) {
+                emit_xrange(dims[0], periodic[0], cell_start, rowbase, c0[0] + xl, c0[0] - 1, wrap, f);
+                emit_xrange(dims[0], periodic[0], cell_start, rowbase, c0[0] + 1, c0[0] + xh, wrap, f);
+            } else {
+                emit_xrange(dims[0], periodic[0], cell_start, rowbase, c0[0] + xl, c0[0] + xh, wrap, f);
+            }
+        }
+    }
+}
+
+// Is cell `ct` visited by the walk above when started from cell `cf` with
+// radius r0?  (Used to reproduce the asymmetric pair set of all_pairs!,
+// src/spaces/continuous.jl:438-452, without a hash set.)
+template <int D>
+__device__ __forceinline__ bool cell_reachable(const int* dims, const bool* periodic, int metric, const int* cf,
+                                               const int* ct, int r0) {
+    int lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
+    if (r0 < 0) {
+        bool same = true;
+#pragma unroll
+        for (int d = 0; d < D; ++d) same = same && (cf[d] == ct[d]);
+        return same;
+    }
+    hyper_ranges<D>(dims, periodic, r0, lo, hi);
+    long long s2 = 0, s1 = 0;
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        int diff = ct[d] - cf[d];
+        int b = diff;
+        bool found = (b >= lo[d] && b <= hi[d]);
+        if (!found && periodic[d]) {
+            b = diff + dims[d];
+            found = (b >= lo[d] && b <= hi[d]);
+            if (!found) { b = diff - dims[d]; found = (b >= lo[d] && b <= hi[d]); }
+        }
+        if (!found) return false;
+        s2 += (long long)b * b;
+        s1 += b < 0 ? -b : b;
+    }
+    if (metric == AB_METRIC_EUCLIDEAN) return s2 <= (long long)r0 * r0;
+    if (metric == AB_METRIC_MANHATTAN) return s1 <= r0;
+    return true;
+}
+
+// get_direction — src/spaces/utilities.jl:185-216 (one dimension)
+template <class T> __device__ __forceinline__ T min_image(T direct, T L) {
+    T inverse = direct - jl_sign(direct) * L;
+    return (fabs(direct) <= fabs(inverse)) ? direct : inverse;
+}
+
+// normalize_position — src/spaces/walk.jl:77-91 (one dimension)
+template <class T> __device__ __forceinline__ T normalize_coord(T x, T L, bool periodic) {
+    if (periodic) return jl_mod(x, L);
+    T hi = ab_next(L, -(T)INFINITY);            // prevfloat(L)
+    return x > hi ? hi : (x < T(0) ? T(0) : x); // clamp
+}
+
+#endif  // __CUDACC__

@@ -1,0 +1,344 @@
+"""Host mirror of the Agents.jl surface that sits on the hot path.
+
+Names and argument meaning follow the reference (Agents.jl v7.0.3):
+  ContinuousSpace(extent; spacing, periodic)     src/spaces/continuous.jl:93-105
+  GridSpace / GridSpaceSingle(dims; periodic, metric)   src/spaces/grid_multi.jl:68-86, grid_single.jl:33-45
+  StandardABM(space; model_step!, properties)    src/core/model_standard.jl:134-177
+  nearby_ids / interacting_pairs / nearest_neighbor / move_agent! / walk! / step!
+Agent ids are 1-based and dense (the Vector-container rule,
+src/core/model_accessing_API.jl:29-32).  All work happens in the CUDA library.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib as L
+
+
+class AgentsError(RuntimeError):
+    """Raised where the reference would throw (ErrorException, BoundsError, ...)."""
+
+    def __init__(self, code, msg):
+        super().__init__(msg)
+        self.code = code
+
+
+def _periodic(periodic, D):
+    if isinstance(periodic, (bool, np.bool_)):
+        periodic = (bool(periodic),) * D
+    if len(periodic) != D:
+        raise ValueError("periodic must be a Bool or a D-tuple")
+    return tuple(bool(p) for p in periodic)
+
+
+class ContinuousSpace:
+    """ContinuousSpace(extent; spacing = minimum(extent)/20, periodic = true) — continuous.jl:93-105."""
+
+    kind = L.SPACE_CONTINUOUS
+
+    def __init__(self, extent, spacing=None, periodic=True, dtype=np.float64):
+        self.D = len(extent)
+        self.extent = tuple(float(x) for x in extent)
+        self.spacing = float(min(self.extent) / 20.0 if spacing is None else spacing)
+        self.periodic = _periodic(periodic, self.D)
+        self.dtype = np.dtype(dtype)
+        if self.dtype not in (np.dtype(np.float64), np.dtype(np.float32)):
+            raise TypeError("eltype must be Float64 or Float32 on the device")
+        self.metric = "euclidean"
+        self.dims = None
+
+    def _desc(self):
+        d = L.SpaceDesc()
+        d.kind, d.D = self.kind, self.D
+        for i in range(self.D):
+            d.extent[i] = self.extent[i]
+            d.periodic[i] = int(self.periodic[i])
+        d.spacing = self.spacing
+        d.metric = L.METRICS["euclidean"]
+        d.dtype = L.F64 if self.dtype == np.float64 else L.F32
+        return d
+
+
+class GridSpace:
+    """GridSpace(d; periodic = true, metric = :chebyshev) — grid_multi.jl:68-86."""
+
+    kind = L.SPACE_GRID_MULTI
+
+    def __init__(self, dims, periodic=True, metric="chebyshev"):
+        self.D = len(dims)
+        self.dims = tuple(int(x) for x in dims)
+        self.periodic = _periodic(periodic, self.D)
+        if metric not in L.METRICS:
+            raise ValueError("Unknown metric type")
+        self.metric = metric
+        self.dtype = np.dtype(np.int32)
+
+    def _desc(self):
+        d = L.SpaceDesc()
+        d.kind, d.D = self.kind, self.D
+        for i in range(self.D):
+            d.periodic[i] = int(self.periodic[i])
+            d.grid_dims[i] = self.dims[i]
+        d.metric = L.METRICS[self.metric]
+        d.dtype = L.I32
+        return d
+
+
+class GridSpaceSingle(GridSpace):
+    """GridSpaceSingle(d; periodic, metric): at most one agent per position — grid_single.jl:33-45."""
+
+    kind = L.SPACE_GRID_SINGLE
+
+
+_NP2AB = {np.dtype(np.float64): L.F64, np.dtype(np.float32): L.F32, np.dtype(np.int32): L.I32,
+          np.dtype(np.int64): L.I64, np.dtype(np.uint8): L.U8, np.dtype(np.bool_): L.U8}
+
+
+class FlockRule:
+    """`agent_step!` of examples/flock.jl:79-108 as a fused synchronous model step.
+    Scalars are uniform; pass `per_agent=` (n×6 array: speed, cohere_factor, separation,
+    separate_factor, match_factor, visual_distance) for per-bird fields (flock.jl:21-28)."""
+
+    def __init__(self, speed=1.0, cohere_factor=0.1, separation=2.0, separate_factor=0.25, match_factor=0.04,
+                 visual_distance=5.0, search="approximate", per_agent=None, kernel="auto"):
+        self.p = dict(speed=speed, cohere_factor=cohere_factor, separation=separation,
+                      separate_factor=separate_factor, match_factor=match_factor, visual_distance=visual_distance)
+        self.search = search
+        self.per_agent = per_agent
+        self.kernel = {"auto": 0, "generic": 1, "tiled": 2}[kernel]
+        self._field = -1
+
+    def _bind(self, model):
+        if self.per_agent is not None and self._field < 0:
+            self._field = model.add_column("_flock_params", np.asarray(self.per_agent, dtype=model.space.dtype))
+
+    def __call__(self, model, nsteps=1):
+        self._bind(model)
+        fp = L.FlockParams(search=L.SEARCH[self.search], per_agent_field=self._field, kernel=self.kernel, **self.p)
+        model._ck(L.lib().ab_step_flock(model.h, C.byref(fp), int(nsteps)))
+
+
+class PairForceRule:
+    """Force law + integrator of examples/celllistmap.jl:143-155, :176-191 (columns r, k, mass)."""
+
+    def __init__(self, dt=0.001, cutoff=20.0):
+        self.dt, self.cutoff = dt, cutoff
+
+    def __call__(self, model, nsteps=1):
+        pp = L.PairForceParams(dt=self.dt, cutoff=self.cutoff, field_r=model.field_id("r"),
+                               field_k=model.field_id("k"), field_mass=model.field_id("mass"))
+        model._ck(L.lib().ab_step_pairforce(model.h, C.byref(pp), int(nsteps)))
+
+
+class SchellingRule:
+    """schelling_step! of docs/src/tutorial.jl:351-376, synchronous (columns group::Int32, mood::UInt8)."""
+
+    def __init__(self, min_to_be_happy=3, relocate=True, seed=42):
+        self.min_to_be_happy, self.relocate, self.seed = min_to_be_happy, relocate, seed
+        self.last_moved = 0
+
+    def __call__(self, model, nsteps=1):
+        sp = L.SchellingParams(min_to_be_happy=self.min_to_be_happy, relocate=int(self.relocate), seed=self.seed)
+        moved = C.c_int64(0)
+        model._ck(L.lib().ab_step_schelling(model.h, C.byref(sp), int(nsteps), C.byref(moved)))
+        self.last_moved = moved.value
+
+
+class StandardABM:
+    """StandardABM(space; model_step!, properties) with a device-resident SoA container.
+
+    `model_step` is a rule object (FlockRule, PairForceRule, SchellingRule) — the
+    B200Step of INTEGRATION.md; `step(n)` is `step!(model, n)`
+    (src/simulations/step_standard.jl:24-31)."""
+
+    def __init__(self, space, model_step=None, properties=None, device=0):
+        self.space = space
+        self.model_step = model_step
+        self.properties = properties or {}
+        self.time = 0
+        self.lib = L.lib()
+        desc = space._desc()
+        h = C.c_void_p()
+        rc = self.lib.ab_create(C.byref(desc), int(device), C.byref(h))
+        if rc != L.AB_OK:
+            raise AgentsError(rc, self.lib.ab_last_error(None).decode())
+        self.h = h
+        space.dims = tuple(int(desc.grid_dims[i]) for i in range(space.D))
+        self.D = space.D
+        self._columns = {"pos": 0}
+        if space.kind == L.SPACE_CONTINUOUS:
+            self._columns["vel"] = 1
+        self._dtypes = {"pos": space.dtype, "vel": space.dtype}
+        self._ncomp = {"pos": space.D, "vel": space.D}
+
+    # -- plumbing ---------------------------------------------------------
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.ab_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc < 0:
+            raise AgentsError(rc, self.lib.ab_last_error(self.h).decode())
+        return rc
+
+    @staticmethod
+    def _ptr(a):
+        return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+    # -- population (add_agent! at setup; src/core/space_interaction_API.jl:174-179) ----
+    def nagents(self):
+        return int(self.lib.ab_nagents(self.h))
+
+    def field_id(self, name):
+        if name not in self._columns:
+            raise KeyError(name)
+        return self._columns[name]
+
+    def add_agents(self, pos, vel=None, **columns):
+        """Bulk add_agent!: ids 1..n in the given order; replaces the population."""
+        dt = self.space.dtype
+        pos = np.ascontiguousarray(pos, dtype=dt).reshape(-1, self.D)
+        n = pos.shape[0]
+        self._ck(self.lib.ab_resize(self.h, n))
+        self._ck(self.lib.ab_upload(self.h, 0, self._ptr(pos), n))
+        if "vel" in self._columns:
+            v = np.zeros((n, self.D), dtype=dt) if vel is None else np.ascontiguousarray(vel, dtype=dt).reshape(n, self.D)
+            self._ck(self.lib.ab_upload(self.h, 1, self._ptr(v), n))
+        for name, col in columns.items():
+            self.add_column(name, col)
+        self._ck(self.lib.ab_build_index(self.h))
+        return n
+
+    def add_column(self, name, values):
+        """One device column per isbits field of the @agent struct (src/core/agents.jl:199-231)."""
+        a = np.ascontiguousarray(values)
+        if a.dtype == np.bool_:
+            a = a.astype(np.uint8)
+        n = self.nagents()
+        a = a.reshape(n, -1)
+        if name not in self._columns:
+            fid = self._ck(self.lib.ab_register_field(self.h, name.encode(), _NP2AB[a.dtype], a.shape[1]))
+            self._columns[name] = fid
+            self._dtypes[name] = a.dtype
+            self._ncomp[name] = a.shape[1]
+        a = np.ascontiguousarray(a, dtype=self._dtypes[name])
+        self._ck(self.lib.ab_upload(self.h, self._columns[name], self._ptr(a), n))
+        return self._columns[name]
+
+    def set_column(self, name, values):
+        n = self.nagents()
+        a = np.ascontiguousarray(values, dtype=self._dtypes[name]).reshape(n, self._ncomp[name])
+        self._ck(self.lib.ab_upload(self.h, self._columns[name], self._ptr(a), n))
+
+    def column(self, name):
+        n = self.nagents()
+        out = np.zeros((n, self._ncomp[name]), dtype=self._dtypes[name])
+        self._ck(self.lib.ab_download(self.h, self._columns[name], self._ptr(out), n))
+        return out if self._ncomp[name] > 1 else out[:, 0]
+
+    @property
+    def pos(self):
+        return self.column("pos")
+
+    @property
+    def vel(self):
+        return self.column("vel")
+
+    def cells(self):
+        """pos2cell of every agent, 1-based (continuous.jl:112-113)."""
+        n = self.nagents()
+        out = np.zeros((n, self.D), dtype=np.int32)
+        self._ck(self.lib.ab_cells(self.h, self._ptr(out), n))
+        return out
+
+    # -- neighbour queries ---------------------------------------------------
+    def nearby_ids_batch(self, positions=None, ids=None, r=1.0, search="approximate", exclude_self=True):
+        """Batched nearby_ids.  Returns (offsets[nq+1], ids) CSR with 1-based ids."""
+        if (positions is None) == (ids is None):
+            raise ValueError("give positions or ids")
+        if search not in L.SEARCH:
+            raise AgentsError(L.ERR_INVALID, "`search` keyword should be either `:approximate` or `:exact`")
+        if positions is not None:
+            q = np.ascontiguousarray(positions, dtype=self.space.dtype).reshape(-1, self.D)
+            nq, qp, qi = q.shape[0], self._ptr(q), None
+        else:
+            q = np.ascontiguousarray(ids, dtype=np.int64).reshape(-1)
+            nq, qp, qi = q.shape[0], None, self._ptr(q)
+        counts = np.zeros(nq, dtype=np.int64)
+        self._ck(self.lib.ab_nearby_count(self.h, qp, qi, nq, float(r), L.SEARCH[search], int(exclude_self), self._ptr(counts)))
+        offsets = np.zeros(nq + 1, dtype=np.int64)
+        np.cumsum(counts, out=offsets[1:])
+        out = np.zeros(max(int(offsets[-1]), 1), dtype=np.int64)
+        self._ck(self.lib.ab_nearby_fill(self.h, qp, qi, nq, float(r), L.SEARCH[search], int(exclude_self),
+                                         self._ptr(offsets), self._ptr(out)))
+        return offsets, out[: int(offsets[-1])]
+
+    def nearby_ids(self, x, r=1.0, search="approximate"):
+        """nearby_ids(pos, model, r; search) for a position, nearby_ids(agent, ...) for an id
+        (the agent form drops the agent's own id, space_interaction_API.jl:284-287)."""
+        if isinstance(x, (int, np.integer)):
+            _, ids = self.nearby_ids_batch(ids=[int(x)], r=r, search=search, exclude_self=True)
+        else:
+            _, ids = self.nearby_ids_batch(positions=[x], r=r, search=search)
+        return ids
+
+    def interacting_pairs(self, r, method="all", search="exact"):
+        """interacting_pairs(model, r, :all; search) → (P, 2) array of id pairs (continuous.jl:418-452)."""
+        if method != "all":
+            raise NotImplementedError("only method = :all runs on the device")
+        npairs = C.c_int64(0)
+        self._ck(self.lib.ab_pairs_count(self.h, float(r), L.SEARCH[search], C.byref(npairs)))
+        P = npairs.value
+        lo = np.zeros(max(P, 1), dtype=np.int64)
+        hi = np.zeros(max(P, 1), dtype=np.int64)
+        self._ck(self.lib.ab_pairs_fill(self.h, self._ptr(lo), self._ptr(hi), P))
+        return np.stack([lo[:P], hi[:P]], axis=1)
+
+    def nearest_neighbor(self, r):
+        """nearest_neighbor(agent, model, r) for every agent: id or 0 for `nothing` (continuous.jl:298-307)."""
+        n = self.nagents()
+        out = np.zeros(n, dtype=np.int64)
+        self._ck(self.lib.ab_nearest_neighbor(self.h, float(r), self._ptr(out), n))
+        return out
+
+    # -- movement --------------------------------------------------------------
+    def move_agent(self, dt, ids=None):
+        """move_agent!(agent, model, dt) for `ids` (all agents when None) — continuous.jl:186-194."""
+        a = np.ascontiguousarray(ids, dtype=np.int64) if ids is not None else None
+        self._ck(self.lib.ab_move(self.h, float(dt), self._ptr(a), 0 if a is None else a.shape[0]))
+
+    def walk(self, directions, ids=None, ifempty=True):
+        """walk!(agent, direction, model) — walk.jl:33-66."""
+        dt = self.space.dtype
+        d = np.ascontiguousarray(directions, dtype=dt).reshape(-1, self.D)
+        a = np.ascontiguousarray(ids, dtype=np.int64) if ids is not None else None
+        self._ck(self.lib.ab_walk(self.h, self._ptr(d), self._ptr(a), d.shape[0] if a is None else a.shape[0], int(ifempty)))
+
+    # -- stepping (src/simulations/step_standard.jl:24-31) --------------------
+    def step(self, n=1):
+        if self.model_step is None:
+            raise AgentsError(L.ERR_STATE, "no model_step! rule")
+        self.model_step(self, int(n))      # n ticks batched into one ccall
+        self.time += int(n)
+        return self
+
+    def last_neighbor_counts(self):
+        n = self.nagents()
+        out = np.zeros(n, dtype=np.int32)
+        self._ck(self.lib.ab_flock_last_counts(self.h, self._ptr(out), n))
+        return out
+
+    def launch_count(self):
+        return int(self.lib.ab_launch_count(self.h))
+
+    def last_step_ms(self):
+        return float(self.lib.ab_last_step_ms(self.h))

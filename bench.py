@@ -1,0 +1,332 @@
+#!/usr/bin/env python
+"""bench.py — agent-updates/s of the fused flock step (BASELINE.json metric).
+
+  python bench.py --gpus N --steps K --warmup W            # our arm (CUDA, C ABI)
+  python bench.py --impl reference --gpus N --steps K ...  # CPU arm (oracle port of Agents.jl)
+
+Workload (config.workload = "F2D-1M", BASELINE configs[1]): 1,000,000 boids,
+ContinuousSpace((2000,2000)) periodic, spacing = visual_distance = 5, f64,
+examples/flock.jl rule constants, `search = :approximate` (the reference's
+default), synthetic counter-based initial state, synchronous update.
+A "step" = one flock step over the whole population.
+
+value  : agents*steps / device time, state resident in HBM (CUDA events on the
+         library's stream, L2 flushed between timed steps).
+e2e    : same metric through the public API with HOST (pinned) buffers: every
+         step uploads pos+vel, steps once, downloads pos+vel.
+roofline: dominant kernel (the sweep) — algorithmic 128 B/agent-update
+          x agents per launch / its CUDA-event duration, against the
+         measured HBM copy bandwidth in MEASURED_PEAKS.json.
+cpu_baseline: the CPU oracle's reference-faithful asynchronous step
+         (vector-per-cell index, in-place sequential update, 1 thread — the
+         reference's step! is single-threaded) on a bounded sample.
+With --gpus N > 1 (torchrun): weak scaling, 1M boids per GPU, slab decomposition
+along y with NCCL halo / migration exchange.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+ALG_BYTES = {"flock2d_f64": 128.0, "flock3d_f64": 160.0, "flock2d_f32": 72.0}
+N_PER_GPU = 1_000_000
+EXTENT = (2000.0, 2000.0)
+SPACING = 5.0
+FLOCK = dict(speed=1.0, cohere_factor=0.1, separation=2.0, separate_factor=0.25, match_factor=0.04,
+             visual_distance=5.0)
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p)).get("hbm_gbs", 6650.0), "measured"
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled DURING the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                pass
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+                for nm, v in zip(names, r[2:6]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def flock_state(n, extent, seed=42):
+    from helpers import flock_init
+
+    return flock_init(n, extent, seed)
+
+
+# ---------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference's own (asynchronous, 1-thread) step
+# ---------------------------------------------------------------------------
+def cpu_flock_rate(n, extent, steps, warmup=0):
+    from oracle.pyoracle import ContinuousOracle
+
+    pos, vel = flock_state(n, extent)
+    o = ContinuousOracle(extent, spacing=SPACING)
+    o.add_agents(pos, vel)
+    rng_order = np.random.default_rng(1)
+    for _ in range(warmup):
+        o.flock_step_async(FLOCK, order=rng_order.permutation(n) + 1)     # Schedulers.Randomly (flock.jl:59)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        o.flock_step_async(FLOCK, order=rng_order.permutation(n) + 1)
+    dt = time.perf_counter() - t0
+    return n * steps / dt, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    n = N_PER_GPU
+    # bounded sample: the full 1M-boid population, few steps (each ~10 s on one core)
+    steps = max(1, min(args.steps, 3))
+    warm = 1 if args.warmup > 0 else 0
+    rate, dt = cpu_flock_rate(n, EXTENT, steps, warm)
+    sample = f"{n} boids x {steps} asynchronous steps (Schedulers.Randomly order), 1 thread"
+    line = {
+        "impl": "reference", "metric": "agent-updates/sec", "value": rate, "unit": "agent-updates/s",
+        "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": dt / steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "F2D-1M", "agents": n, "extent": list(EXTENT), "spacing": SPACING,
+                   "search": "approximate", "update": "asynchronous in place (reference semantics)"},
+        "cpu_baseline": {"value": rate, "unit": "agent-updates/s", "cores": 1, "kind": "port", "sample": sample,
+                         "note": "Julia is not installed; this is the CPU oracle port of Agents.jl's step! "
+                                 "(single-threaded by design: src/simulations/step_standard.jl:9-23)"},
+        "e2e": {"value": rate, "unit": "agent-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ---------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------
+def run_gpu(args):
+    import torch
+
+    import agents_jl_b200 as ab
+    from agents_jl_b200 import _lib as L
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    n = N_PER_GPU
+    search = args.search
+    extent = EXTENT if world == 1 else (EXTENT[0], EXTENT[1] * world)     # weak scaling: slabs along y
+    lib = L.lib()
+    sampler = ClockSampler(local)
+
+    rule = ab.FlockRule(search=search, kernel=args.kernel, **FLOCK)
+    space = ab.ContinuousSpace(extent, spacing=SPACING, periodic=True)
+    model = ab.StandardABM(space, model_step=rule, device=local)
+    if world == 1:
+        pos, vel = flock_state(n, extent)
+        model.add_agents(pos, vel)
+    else:
+        from agents_jl_b200.parallel import init_slabs
+
+        pos, vel = init_slabs(model, dist, n * world, extent, flock_state)
+    nloc = n
+
+    flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device="cuda")
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed_steps(k, flush_l2=True):
+        tot = 0.0
+        for _ in range(k):
+            if flush_l2:
+                flush.add_(1.0)                  # > L2 (126 MB): next step starts cold
+                torch.cuda.synchronize()
+            model.step(1)
+            tot += model.last_step_ms()
+        return tot
+
+    # ---- device-resident throughput -------------------------------------------
+    timed_steps(args.warmup)
+    barrier()
+    sampler.start()
+    launches0 = model.launch_count()
+    ms = timed_steps(args.steps)
+    launches = model.launch_count() - launches0
+    barrier()
+    # back-to-back steps in ONE call, warm L2 (what step!(model, K) does in production)
+    model.step(args.steps)
+    ms_warm = model.last_step_ms()
+    clocks = sampler.stop()
+    t = torch.tensor([ms, ms_warm], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, ms_warm = float(t[0]), float(t[1])
+    total_agents = n * world
+    value = total_agents * args.steps / (ms * 1e-3)
+    value_warm = total_agents * args.steps / (ms_warm * 1e-3)
+
+    # ---- per-kernel times (CUDA events around each launch on the library's stream) ----
+    lib.ab_set_profiling(model.h, 1)
+    timed_steps(args.steps)
+    names = (C.c_char_p * 32)()
+    kms = (C.c_double * 32)()
+    kl = (C.c_int64 * 32)()
+    nk = lib.ab_kernel_times(model.h, names, kms, kl, 32)
+    lib.ab_set_profiling(model.h, 0)
+    kernels = {names[i].decode(): {"ms_per_launch": kms[i] / max(kl[i], 1), "launches": int(kl[i]), "ms": kms[i]}
+               for i in range(min(nk, 32))}
+    step_kernel_ms = sum(v["ms"] for v in kernels.values()) / args.steps
+    dom = max(kernels, key=lambda k: kernels[k]["ms"]) if kernels else None
+    peak, peak_src = measured_peaks()
+    alg = ALG_BYTES["flock2d_f64"]
+    roofline = None
+    if dom:
+        dur = kernels[dom]["ms_per_launch"] * 1e-3
+        ach = alg * nloc / dur / 1e9
+        roofline = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
+                    "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                    "algorithmic_bytes_per_agent_update": alg, "kernel_ms": kernels[dom]["ms_per_launch"],
+                    "kernel_share_of_step": kernels[dom]["ms"] / max(sum(v["ms"] for v in kernels.values()), 1e-12),
+                    "whole_step": {"achieved": alg * nloc / (ms / args.steps * 1e-3) / 1e9,
+                                   "frac": alg * nloc / (ms / args.steps * 1e-3) / 1e9 / peak}}
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")      # dram bytes per launch from an ncu --set full capture
+        if os.path.exists(tpath):
+            try:
+                roofline["traffic"] = json.load(open(tpath)).get(dom)
+            except Exception:
+                pass
+
+    # ---- end to end through the public API with host buffers --------------------
+    e2e = None
+    if world == 1:
+        hp = torch.empty((n, 2), dtype=torch.float64, pin_memory=True).numpy()
+        hv = torch.empty((n, 2), dtype=torch.float64, pin_memory=True).numpy()
+        hp[:] = model.pos
+        hv[:] = model.vel
+        ptr = lambda a: a.ctypes.data_as(C.c_void_p)
+
+        def e2e_step():
+            model._ck(lib.ab_upload(model.h, 0, ptr(hp), n))
+            model._ck(lib.ab_upload(model.h, 1, ptr(hv), n))
+            model.step(1)
+            model._ck(lib.ab_download(model.h, 0, ptr(hp), n))
+            model._ck(lib.ab_download(model.h, 1, ptr(hv), n))
+
+        for _ in range(max(args.warmup, 3)):
+            e2e_step()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_step()
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        e2e = {"value": n * args.steps / dt, "unit": "agent-updates/s", "h2d_bytes_per_step": int(hp.nbytes + hv.nbytes),
+               "d2h_bytes_per_step": int(hp.nbytes + hv.nbytes), "ms_per_step": dt / args.steps * 1e3}
+
+    # ---- CPU baseline on this box's host cores (rank 0, N = 1 only) ------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        csteps = 2
+        rate, dt = cpu_flock_rate(n, EXTENT, csteps)
+        cpu = {"value": rate, "unit": "agent-updates/s", "cores": 1, "kind": "port",
+               "sample": f"{n} boids x {csteps} asynchronous steps (reference semantics), {dt:.1f} s, 1 thread"}
+
+    if rank == 0:
+        line = {
+            "metric": "agent-updates/sec", "value": value, "unit": "agent-updates/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "F2D-1M", "agents_per_gpu": n, "agents": total_agents, "extent": list(extent),
+                       "spacing": SPACING, "periodic": True, "search": search, "update": "synchronous",
+                       "l2": "flushed between timed steps (256 MB write)", "kernel": args.kernel,
+                       "parallelism": "single GPU" if world == 1 else f"{world} slabs along y, NCCL halo+migration"},
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+            "warm_l2": {"value": value_warm, "ms_per_step": ms_warm / args.steps,
+                        "note": "K steps in one ab_step_flock call, no L2 flush"},
+            "kernels": kernels, "kernel_ms_per_step": step_kernel_ms,
+        }
+        print(json.dumps(line))
+    model.close()
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--search", default="approximate", choices=["approximate", "exact"])
+    ap.add_argument("--kernel", default="auto", choices=["auto", "generic", "tiled"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_gpu(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,200 @@
+/* agents_b200.h — C ABI of the B200-native Agents.jl hot path.
+ *
+ * One shared library (libagents_b200.so), plain C types only: this is what a
+ * Julia `ccall` (or ctypes / cgo / JNI) binds.  Agents.jl v7.0.3 has no FFI of
+ * its own; every entry point below replaces the body of a Julia function of
+ * the reference and cites it (paths relative to the Agents.jl tree).  The
+ * Julia-side glue a maintainer would add is shown in INTEGRATION.md.
+ *
+ * Conventions
+ *  - every call returns 0 (AB_OK) or a negative ab_status; ab_last_error()
+ *    returns the message of the last failing call on that handle.  Nothing
+ *    throws or aborts across the ABI.
+ *  - agent ids are 1-based and dense (1..n), exactly the Vector / StructVector
+ *    container rule of the reference (src/core/model_accessing_API.jl:29-32).
+ *  - cell coordinates returned to the caller are 1-based like Julia's.
+ *  - host arrays are row-per-agent: n x ncomp values of the column's dtype —
+ *    the memory layout of a Julia Vector{SVector{D,T}} / Vector{NTuple{D,T}}.
+ *  - a handle owns one CUDA stream; calls are synchronous on return unless
+ *    documented otherwise.  A handle is not thread-safe; handles are
+ *    independent.  There is no CPU fallback: without a CUDA device
+ *    ab_create() fails with AB_ERR_CUDA.
+ */
+#ifndef AGENTS_B200_H
+#define AGENTS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ab_handle ab_handle;
+
+typedef enum {
+    AB_OK = 0,
+    AB_ERR_INVALID = -1,      /* bad argument / unsupported configuration        */
+    AB_ERR_CUDA = -2,         /* CUDA runtime error (message has the CUDA text)   */
+    AB_ERR_OUTSIDE = -3,      /* "position is outside space extent!" continuous.jl:160 */
+    AB_ERR_SPACING = -4,      /* extent not divisible by spacing, continuous.jl:99-101 */
+    AB_ERR_OCCUPIED = -5,     /* GridSpaceSingle cell already occupied, grid_single.jl:49 */
+    AB_ERR_NUMERIC = -6,      /* NaN/Inf position reached a cell computation (InexactError in Julia) */
+    AB_ERR_STATE = -7,        /* call not valid in the current state (e.g. no agents) */
+    AB_ERR_COMM = -8          /* NCCL / multi-GPU exchange failure */
+} ab_status;
+
+enum { AB_SPACE_CONTINUOUS = 0, AB_SPACE_GRID_MULTI = 1, AB_SPACE_GRID_SINGLE = 2 };
+enum { AB_F64 = 0, AB_F32 = 1, AB_I32 = 2, AB_I64 = 3, AB_U8 = 4 };
+enum { AB_METRIC_CHEBYSHEV = 0, AB_METRIC_MANHATTAN = 1, AB_METRIC_EUCLIDEAN = 2 };
+enum { AB_SEARCH_APPROXIMATE = 0, AB_SEARCH_EXACT = 1 };   /* continuous.jl:212-219 */
+
+/* Mirrors ContinuousSpace{D,P,T} (src/spaces/continuous.jl:4-10, ctor :93-105)
+ * and GridSpace / GridSpaceSingle (src/spaces/grid_multi.jl:4-12,
+ * grid_single.jl:11-18). */
+typedef struct {
+    int32_t kind;          /* AB_SPACE_*                                         */
+    int32_t D;             /* 2 or 3 on the device                               */
+    double extent[3];      /* continuous: extent; ignored for grids              */
+    double spacing;        /* continuous: cell spacing; must divide every extent */
+    uint8_t periodic[3];   /* per-dimension periodicity (P)                      */
+    uint8_t _pad[5];
+    int32_t metric;        /* grids: AB_METRIC_*; continuous is always euclidean (continuous.jl:102) */
+    int32_t dtype;         /* continuous: AB_F64 or AB_F32 (eltype T)            */
+    int64_t grid_dims[3];  /* grids: size; continuous: filled in by ab_create (extent/spacing) */
+} ab_space_desc;
+
+/* Per-agent fields of `Bird` (examples/flock.jl:21-28).  Uniform values are
+ * passed here; when `per_agent_field` >= 0 it names a registered 6-component
+ * column (speed, cohere_factor, separation, separate_factor, match_factor,
+ * visual_distance) that overrides them agent by agent. */
+typedef struct {
+    double speed, cohere_factor, separation, separate_factor, match_factor, visual_distance;
+    int32_t search;            /* AB_SEARCH_*: the `search` keyword of nearby_agents   */
+    int32_t per_agent_field;   /* -1, or field id of a 6-component column            */
+    int32_t kernel;            /* 0 auto, 1 force generic kernel, 2 force tiled kernel */
+    int32_t _pad;
+} ab_flock_params;
+
+/* `Particle` fields r, k, mass (examples/celllistmap.jl:39-43) are registered
+ * 1-component columns; dt / cutoff as in celllistmap.jl:73-78. */
+typedef struct {
+    double dt, cutoff;
+    int32_t field_r, field_k, field_mass;
+    int32_t _pad;
+} ab_pairforce_params;
+
+/* Schelling rule (docs/src/tutorial.jl:351-376). */
+typedef struct {
+    int32_t min_to_be_happy;
+    int32_t relocate;          /* 0: happiness pass only; 1: unhappy agents move to empty cells */
+    uint64_t seed;
+} ab_schelling_params;
+
+/* ---- lifecycle ------------------------------------------------------------
+ * ab_create replaces ContinuousSpace(...) / GridSpace(...) / GridSpaceSingle(...)
+ * + construct_agent_container (src/core/agent_containers.jl:53-61): it checks
+ * the spacing rule (continuous.jl:99-101), fills desc->grid_dims and allocates
+ * the device-resident SoA container.  Built-in columns: continuous "pos"
+ * (field 0, D comps of T) and "vel" (field 1); grids "pos" (field 0, D x i32). */
+int ab_create(ab_space_desc* desc, int device, ab_handle** out);
+int ab_destroy(ab_handle* h);
+const char* ab_last_error(const ab_handle* h);   /* h may be NULL: last ab_create error */
+int ab_sync(ab_handle* h);
+int ab_version(void);
+int64_t ab_nagents(const ab_handle* h);
+
+/* pinned host memory for the Julia-side mirror columns (optional, faster copies) */
+void* ab_alloc_pinned(int64_t bytes);
+void ab_free_pinned(void* p);
+
+/* ---- columns ---------------------------------------------------------------
+ * One device column per isbits field of the @agent struct
+ * (src/core/agents.jl:199-231; SoA precedent src/core/agent_containers.jl:8-35). */
+int ab_register_field(ab_handle* h, const char* name, int dtype, int ncomp);  /* returns field id >= 0 */
+int ab_field_id(const ab_handle* h, const char* name);
+/* add_agent! at setup (space_interaction_API.jl:174-179 → push!): (re)sets the
+ * population to n agents with ids 1..n.  Columns must then be uploaded. */
+int ab_resize(ab_handle* h, int64_t n);
+int ab_upload(ab_handle* h, int field, const void* host, int64_t n);    /* id order in */
+int ab_download(ab_handle* h, int field, void* host, int64_t n);        /* id order out */
+
+/* ---- index -----------------------------------------------------------------
+ * Replaces the persistent array-of-vectors index and its incremental upkeep
+ * (continuous.jl:133-153, grid_multi.jl:91-105, grid_single.jl:47-57) by a
+ * per-step cell list: key = column-major cell (pos2cell, continuous.jl:112-113),
+ * counting sort, cell start offsets.  Called implicitly by queries/steps when
+ * positions changed.  Fails with AB_ERR_OUTSIDE / AB_ERR_NUMERIC / AB_ERR_OCCUPIED
+ * exactly where the reference would throw. */
+int ab_build_index(ab_handle* h);
+/* pos2cell for every agent, id order, n x D int32, 1-based (continuous.jl:112-113) */
+int ab_cells(ab_handle* h, int32_t* out_cells, int64_t n);
+
+/* ---- neighbour queries -------------------------------------------------------
+ * nearby_ids(pos, model, r; search) continuous.jl:212-239 and
+ * nearby_ids(agent, model, r) space_interaction_API.jl:284-287; for grids
+ * grid_multi.jl:120-128, grid_single.jl:92-205.  Exactly one of qpos / qids is
+ * non-NULL: qpos = nq x D positions (T for continuous, int32 1-based for
+ * grids); qids = nq agent ids (agent form; exclude_self applies to it).
+ * Two-phase so the caller owns the result: counts, then fill at caller-made
+ * exclusive offsets (offsets[nq] = total).  ids come back 1-based int64. */
+int ab_nearby_count(ab_handle* h, const void* qpos, const int64_t* qids, int64_t nq, double r,
+                    int search, int exclude_self, int64_t* counts);
+int ab_nearby_fill(ab_handle* h, const void* qpos, const int64_t* qids, int64_t nq, double r,
+                   int search, int exclude_self, const int64_t* offsets, int64_t* ids_out);
+
+/* interacting_pairs(model, r, :all; search) continuous.jl:418-452: unique
+ * (lo, hi) id pairs; count then fill (fill re-runs the last counted query). */
+int ab_pairs_count(ab_handle* h, double r, int search, int64_t* npairs);
+int ab_pairs_fill(ab_handle* h, int64_t* lo, int64_t* hi, int64_t npairs);
+
+/* nearest_neighbor(agent, model, r) continuous.jl:298-307 for all agents:
+ * out[i] = id of the nearest agent within r, or 0 (`nothing`). */
+int ab_nearest_neighbor(ab_handle* h, double r, int64_t* out, int64_t n);
+
+/* ---- movement ---------------------------------------------------------------
+ * move_agent!(agent, model, dt) continuous.jl:186-194 → walk! walk.jl:58-66 →
+ * normalize_position walk.jl:77-91, for `active_ids` (NULL = all agents). */
+int ab_move(ab_handle* h, double dt, const int64_t* active_ids, int64_t nactive);
+/* walk!(agent, direction, model): per-agent displacement, nactive x D of T
+ * (continuous) or int32 (grids, walk.jl:33-56 with ifempty). */
+int ab_walk(ab_handle* h, const void* directions, const int64_t* active_ids, int64_t nactive, int ifempty);
+
+/* ---- fused rules (synchronous update) ---------------
+ * step!(model, n) with a B200Step model_step! (step_standard.jl:24-31). */
+int ab_step_flock(ab_handle* h, const ab_flock_params* p, int64_t nsteps);           /* examples/flock.jl:79-108 */
+int ab_step_pairforce(ab_handle* h, const ab_pairforce_params* p, int64_t nsteps);   /* examples/celllistmap.jl:143-191 */
+/* Schelling on GridSpaceSingle.  Columns "group" (i32) and "mood" (u8) must be
+ * registered.  n_moved (optional) receives the movers of the last step. */
+int ab_step_schelling(ab_handle* h, const ab_schelling_params* p, int64_t nsteps, int64_t* n_moved);
+
+/* neighbour count N seen by every bird in the last flock step (id order);
+ * diagnostic used by the parity tests (neighbour-set flips). */
+int ab_flock_last_counts(ab_handle* h, int32_t* counts, int64_t n);
+
+/* ---- multi-GPU slabs (one process per GPU) -----------------------------------
+ * Slab decomposition along the last axis with halo + migration exchange over
+ * NCCL.  nccl_unique_id: 128 bytes produced by ab_comm_unique_id() on rank 0
+ * and broadcast by the host (torch.distributed / MPI / Julia Distributed). */
+int ab_comm_unique_id(void* out128);
+int ab_comm_init(ab_handle* h, int rank, int nranks, const void* nccl_unique_id);
+int ab_comm_slab(const ab_handle* h, int64_t* first_layer, int64_t* n_layers);
+/* global population after migration (sum over ranks is conserved) */
+int64_t ab_nlocal(const ab_handle* h);
+/* download with global ids: ids_out (n_local int64, 1-based global id) */
+int ab_download_local(ab_handle* h, int field, void* host, int64_t* ids_out, int64_t cap, int64_t* n_out);
+int ab_upload_local(ab_handle* h, int field, const void* host, const int64_t* global_ids, int64_t n);
+
+/* ---- instrumentation ----------------------------------------------------------
+ * kernels launched by this handle so far (bench.py's gpu_launches) and device
+ * time of the last step call measured with CUDA events on the handle's stream. */
+int64_t ab_launch_count(const ab_handle* h);
+double ab_last_step_ms(const ab_handle* h);
+/* per-kernel device time of the last ab_step_* call when profiling is on:
+ * names[i] (static strings), ms[i] summed over the steps; returns how many. */
+int ab_set_profiling(ab_handle* h, int on);
+int ab_kernel_times(ab_handle* h, const char** names, double* ms, int64_t* launches, int cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AGENTS_B200_H */

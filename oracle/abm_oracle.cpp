@@ -167,6 +167,16 @@ template <class T> struct CModel : ModelBase {
     std::vector<T> pos, vel;                       // n*D, id order (id = index+1)
     std::vector<std::vector<int64_t>> stored_ids;  // per cell, column-major
     int64_t n = 0;
+    // space.offsets_within_radius: tables cached by floor(r+1) like the reference
+    // (grid_general.jl:98-110) so the timed CPU baseline does not rebuild them per query
+    mutable std::vector<std::vector<Off>> offs_cache;
+    const std::vector<Off>& cached_offsets(int64_t gr) const {
+        size_t i = (size_t)std::max<int64_t>(gr, 0);
+        if (gr < 0 || i > 4096) { static thread_local std::vector<Off> tmp; tmp = offsets_within_radius(D, dims, periodic, 2, (double)gr, false); return tmp; }
+        if (offs_cache.size() <= i) offs_cache.resize(i + 1);
+        if (offs_cache[i].empty()) offs_cache[i] = offsets_within_radius(D, dims, periodic, 2, (double)gr, false);
+        return offs_cache[i];
+    }
 
     // continuous.jl:112-113  pos2cell = max.(1, ceil.(Int, pos ./ spacing))
     void pos2cell(const T* p, int64_t* c) const {
@@ -291,7 +301,7 @@ template <class T> struct CModel : ModelBase {
         int64_t gr = grid_r(p, r);
         int64_t focal[3];
         pos2cell(p, focal);
-        std::vector<Off> offs = offsets_within_radius(D, dims, periodic, /*euclidean*/ 2, (double)gr, false);
+        const std::vector<Off>& offs = cached_offsets(gr);
         int64_t c[3];
         for (const Off& b : offs) {
             if (!combine_position(D, dims, periodic, focal, b, c)) continue;
