@@ -59,6 +59,7 @@ _SIGS = {
     "ab_upload": (C.c_int, [_H, C.c_int, C.c_void_p, C.c_int64]),
     "ab_download": (C.c_int, [_H, C.c_int, C.c_void_p, C.c_int64]),
     "ab_build_index": (C.c_int, [_H]),
+    "ab_set_refinement": (C.c_int, [_H, C.c_int]),
     "ab_cells": (C.c_int, [_H, C.c_void_p, C.c_int64]),
     "ab_nearby_count": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_int64, C.c_double, C.c_int, C.c_int, C.c_void_p]),
     "ab_nearby_fill": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_int64, C.c_double, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),

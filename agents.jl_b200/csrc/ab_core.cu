@@ -89,6 +89,7 @@ int ab_check_device_errors(ab_handle* h) {
     if (e & AB_EF_NUMERIC) return ab_fail(h, AB_ERR_NUMERIC, "InexactError: a NaN/Inf position reached a cell computation");
     if (e & AB_EF_OUTSIDE) return ab_fail(h, AB_ERR_OUTSIDE, "position is outside space extent!");
     if (e & AB_EF_OCCUPIED) return ab_fail(h, AB_ERR_OCCUPIED, "Cannot add agent to occupied position");
+    if (e & AB_EF_OVERFLOW) return ab_fail(h, AB_ERR_INVALID, "device-side failure: id out of range, or an agent left its cell neighbourhood in one tiled step");
     return ab_fail(h, AB_ERR_INVALID, "device-side failure");
 }
 
@@ -112,7 +113,7 @@ __global__ void k_count(SpaceDev<T, D> sp, const T* __restrict__ pos, int64_t ca
         for (int d = 0; d < D; ++d) nan = nan || !(p[d] == p[d]) || isinf(p[d]);
         atomicOr(err, nan ? AB_EF_NUMERIC : AB_EF_OUTSIDE);
     }
-    uint32_t k = lin_cell<D>(sp.dims, c);
+    uint32_t k = device_key<T, D>(sp, p, c);
     newkey[s] = k;
     rank[s] = atomicAdd(&cell_count[k], 1u);
 }
@@ -292,7 +293,7 @@ __global__ void k_cells(SpaceDev<T, D> sp, const T* __restrict__ pos, const int3
 // index build
 // ---------------------------------------------------------------------------
 static int run_scan(ab_handle* h) {
-    uint32_t n = (uint32_t)h->ncells;
+    uint32_t n = (uint32_t)h->nfine;
     uint32_t ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
     h->scan_epoch = (h->scan_epoch + 1) & 0x3fffffffu;
     if (h->scan_epoch == 0) {   // epoch wrapped: clear stale status words once
@@ -302,6 +303,22 @@ static int run_scan(ab_handle* h) {
     AB_LAUNCH(h, "k_scan");
     k_scan<<<ntiles, SCAN_THREADS, 0, h->stream>>>(h->cell_count, h->cell_start, n, ntiles, h->scan_status,
                                                    h->scan_ticket, h->scan_epoch);
+    return AB_OK;
+}
+
+int ab_permute_extra_fields(ab_handle* h) {
+    const int n = (int)h->n, cur = h->cur, nxt = cur ^ 1, TB = 256;
+    const size_t first = h->desc.kind == AB_SPACE_CONTINUOUS ? 2 : 1;
+    for (size_t f = first; f < h->fields.size(); ++f) {
+        ab_field& fl = h->fields[f];
+        AB_LAUNCH(h, "k_permute");
+        if (fl.esize == 8)
+            k_permute<uint64_t><<<ab_blocks(n, TB), TB, 0, h->stream>>>((const uint64_t*)fl.buf[cur], (uint64_t*)fl.buf[nxt], h->perm, h->cap, n, fl.ncomp);
+        else if (fl.esize == 4)
+            k_permute<uint32_t><<<ab_blocks(n, TB), TB, 0, h->stream>>>((const uint32_t*)fl.buf[cur], (uint32_t*)fl.buf[nxt], h->perm, h->cap, n, fl.ncomp);
+        else
+            k_permute<uint8_t><<<ab_blocks(n, TB), TB, 0, h->stream>>>((const uint8_t*)fl.buf[cur], (uint8_t*)fl.buf[nxt], h->perm, h->cap, n, fl.ncomp);
+    }
     return AB_OK;
 }
 
@@ -336,20 +353,12 @@ static int reindex_t(ab_handle* h, const void* src_pos, const void* src_vel, boo
                     h->newkey, h->rank, h->cell_start, h->id[cur], h->idtmp, (const T*)src_pos, nullptr, h->cap, n,
                     (T*)h->fields[0].buf[nxt], nullptr, h->id[nxt], h->key[nxt], extra ? h->perm : nullptr, nullptr);
         }
-        for (size_t f = has_vel ? 2 : 1; f < h->fields.size(); ++f) {
-            ab_field& fl = h->fields[f];
-            AB_LAUNCH(h, "k_permute");
-            if (fl.esize == 8)
-                k_permute<uint64_t><<<ab_blocks(n, TB), TB, 0, h->stream>>>((const uint64_t*)fl.buf[cur], (uint64_t*)fl.buf[nxt], h->perm, h->cap, n, fl.ncomp);
-            else if (fl.esize == 4)
-                k_permute<uint32_t><<<ab_blocks(n, TB), TB, 0, h->stream>>>((const uint32_t*)fl.buf[cur], (uint32_t*)fl.buf[nxt], h->perm, h->cap, n, fl.ncomp);
-            else
-                k_permute<uint8_t><<<ab_blocks(n, TB), TB, 0, h->stream>>>((const uint8_t*)fl.buf[cur], (uint8_t*)fl.buf[nxt], h->perm, h->cap, n, fl.ncomp);
-        }
+        AB_TRY(ab_permute_extra_fields(h));
     }
     h->cur = nxt;
     h->slot_map_valid = false;
     h->index_valid = true;
+    h->agg_valid = false;
     h->pairs_n = -1;
     return AB_OK;
 }
@@ -373,6 +382,24 @@ int ab_ensure_index(ab_handle* h) {
     return ab_check_device_errors(h);
 }
 
+// Device-grid refinement (1 or 2 sub-cells per reference cell and dimension).
+// Pure layout choice: every query walks reference cells, so results do not
+// depend on it; the fused sweeps use the sub-cells to cut candidate counts.
+int ab_set_refine(ab_handle* h, int K) {
+    if (K != 1 && K != 2) return ab_fail(h, AB_ERR_INVALID, "refinement must be 1 or 2");
+    if (h->desc.kind != AB_SPACE_CONTINUOUS && K != 1) return ab_fail(h, AB_ERR_INVALID, "grid spaces are not refined");
+    const int ksh = K == 2 ? h->D : 0;
+    if ((h->ncells << ksh) > h->nfine_cap) return ab_fail(h, AB_ERR_INVALID, "grid too large to refine");
+    if (K == h->K) return AB_OK;
+    h->K = K;
+    h->ksh = ksh;
+    h->nfine = h->ncells << ksh;
+    h->index_valid = false;
+    h->agg_valid = false;
+    h->pairs_n = -1;
+    return AB_OK;
+}
+
 int ab_ensure_slot_map(ab_handle* h) {
     if (h->slot_map_valid) return AB_OK;
     if (h->n > 0) {
@@ -389,6 +416,12 @@ int ab_ensure_slot_map(ab_handle* h) {
 extern "C" {
 
 int ab_version(void) { return AB_VERSION; }
+
+int ab_set_refinement(ab_handle* h, int K) {
+    AB_CUDA(h, cudaSetDevice(h->device));
+    AB_CUDA(h, cudaStreamSynchronize(h->stream));
+    return ab_set_refine(h, K);
+}
 
 const char* ab_last_error(const ab_handle* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
 
@@ -441,6 +474,9 @@ int ab_create(ab_space_desc* desc, int device, ab_handle** out) {
     }
     if (ncells > 2000000000LL) { delete h; return ab_fail(nullptr, AB_ERR_INVALID, "more than 2e9 cells"); }
     h->ncells = ncells;
+    h->nfine = ncells;
+    // continuous spaces may refine every reference cell into 2^D sub-cells (ab_set_refine)
+    const int max_ksh = (desc->kind == AB_SPACE_CONTINUOUS && (ncells << desc->D) < 4000000000LL) ? desc->D : 0;
     h->tsize = ab_dtype_size(h->dtype);
     h->desc = *desc;
 
@@ -450,11 +486,16 @@ int ab_create(ab_space_desc* desc, int device, ab_handle** out) {
     CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     CK(cudaEventCreate(&h->ev0));
     CK(cudaEventCreate(&h->ev1));
-    size_t padded = ((size_t)ncells + SCAN_TILE - 1) / SCAN_TILE * SCAN_TILE;
+    size_t padded = (((size_t)ncells << max_ksh) + SCAN_TILE - 1) / SCAN_TILE * SCAN_TILE;
+    h->nfine_cap = (int64_t)padded;
     CK(cudaMalloc((void**)&h->cell_count, padded * sizeof(uint32_t)));
     CK(cudaMemset(h->cell_count, 0, padded * sizeof(uint32_t)));
     CK(cudaMalloc((void**)&h->cell_start, (padded + 1) * sizeof(uint32_t)));
     CK(cudaMemset(h->cell_start, 0, (padded + 1) * sizeof(uint32_t)));
+    if (desc->kind == AB_SPACE_CONTINUOUS) {
+        CK(cudaMalloc((void**)&h->cell_start_alt, (padded + 1) * sizeof(uint32_t)));
+        CK(cudaMemset(h->cell_start_alt, 0, (padded + 1) * sizeof(uint32_t)));
+    }
     h->scan_status_len = padded / SCAN_TILE + 1;
     CK(cudaMalloc((void**)&h->scan_status, h->scan_status_len * sizeof(unsigned long long)));
     CK(cudaMemset(h->scan_status, 0, h->scan_status_len * sizeof(unsigned long long)));
@@ -487,7 +528,7 @@ int ab_destroy(ab_handle* h) {
     ab_comm_free(h);
     free_population(h);
     void* ptrs[] = {h->cell_count, h->cell_start, h->scan_status, h->scan_ticket, h->d_err, h->scratch, h->scratch2,
-                    h->cell_sums, h->pairs_offsets, h->grid_ids};
+                    h->cell_agg, h->pairs_offsets, h->grid_ids, h->cell_start_alt, h->rs_status};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (h->h_err) cudaFreeHost(h->h_err);
     if (h->ev0) cudaEventDestroy(h->ev0);

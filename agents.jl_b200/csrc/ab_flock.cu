@@ -14,12 +14,31 @@
 //                    of the sorted arrays through L1/L2.
 //   k_flock_tiled    (ab_flock_tiled.cuh) shared-memory tiles for large 2-D/3-D
 //                    spaces with uniform parameters — the throughput path.
+#include <cmath>
+#include <limits>
+
 #include "ab_internal.cuh"
 
 template <class T> struct FlockU {
     T speed, cohere_factor, separation, separate_factor, match_factor;
     double visual_distance;
+    T thr;      // exact_threshold<T>(visual_distance), computed once on the host for uniform parameters
 };
+
+// host twin of exact_threshold (ab_internal.cuh): IEEE sqrt on both sides, same result
+template <class T> static T exact_threshold_host(double r) {
+    if (!(r >= 0.0)) return T(-1);
+    if (std::isinf(r)) return (T)r;
+    T s = (T)(r * r);
+    const T inf = std::numeric_limits<T>::infinity();
+    while ((double)std::sqrt(s) > r) s = std::nextafter(s, -inf);
+    for (;;) {
+        T nx = std::nextafter(s, inf);
+        if (nx == s || !((double)std::sqrt(nx) <= r)) break;
+        s = nx;
+    }
+    return s;
+}
 
 template <class T, int D>
 __device__ __forceinline__ void flock_epilogue(const SpaceDev<T, D>& sp, const T* p, const T* v, const T* cohere,
@@ -51,31 +70,14 @@ __device__ __forceinline__ void flock_epilogue(const SpaceDev<T, D>& sp, const T
     if (bad) atomicOr(err, AB_EF_OUTSIDE);
 }
 
+// The reference walk for one bird: nearby_agents (continuous.jl:212-239, grid_multi.jl:135-232) over
+// the cell-sorted arrays in global memory, accumulating flock.jl:86-99.
 template <class T, int D, bool EXACT>
-__global__ void __launch_bounds__(128)
-k_flock_generic(SpaceDev<T, D> sp, FlockU<T> uni, const T* __restrict__ per_agent, const T* __restrict__ pos,
-                const T* __restrict__ vel, const uint32_t* __restrict__ key, const uint32_t* __restrict__ cell_start,
-                int64_t cap, int n, T* __restrict__ npos, T* __restrict__ nvel, uint32_t* __restrict__ newkey,
-                uint32_t* __restrict__ rank, uint32_t* __restrict__ cell_count, const int32_t* __restrict__ ids,
-                int32_t* __restrict__ ncount, int* __restrict__ err) {
-    const int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= n) return;
-    FlockU<T> fp = uni;
-    if (per_agent) {
-        fp.speed = per_agent[(size_t)0 * cap + s];
-        fp.cohere_factor = per_agent[(size_t)1 * cap + s];
-        fp.separation = per_agent[(size_t)2 * cap + s];
-        fp.separate_factor = per_agent[(size_t)3 * cap + s];
-        fp.match_factor = per_agent[(size_t)4 * cap + s];
-        fp.visual_distance = (double)per_agent[(size_t)5 * cap + s];
-    }
-    T p[D], v[D];
-    int c[D];
-#pragma unroll
-    for (int d = 0; d < D; ++d) { p[d] = pos[(size_t)d * cap + s]; v[d] = vel[(size_t)d * cap + s]; }
-    unlin_cell<D>(sp.dims, key[s], c);
-    const int gr = grid_radius<T, D>(sp, p, c, fp.visual_distance);
-    const T thr = EXACT ? exact_threshold<T>(fp.visual_distance) : T(0);
+__device__ __noinline__ void flock_accumulate_generic(const SpaceDev<T, D>& sp, const FlockU<T>& fp, int s, const T* p,
+                                                      const int* c, int gr, const T* __restrict__ pos,
+                                                      const T* __restrict__ vel, const uint32_t* __restrict__ cell_start,
+                                                      int64_t cap, int* Nout, T* cohere, T* separate, T* match) {
+    const T thr = fp.thr;
     const T sep2 = fp.separation * fp.separation;
     // min-image shortcut: inside the box and far from wrap, heading == direct
     int permask = 0, slowmask = 0;
@@ -86,11 +88,8 @@ k_flock_generic(SpaceDev<T, D> sp, FlockU<T> uni, const T* __restrict__ per_agen
             if (!((long long)sp.dims[d] >= 2LL * gr + 3)) slowmask |= 1 << d;
         }
     }
-    T cohere[D], separate[D], match[D];
-#pragma unroll
-    for (int d = 0; d < D; ++d) cohere[d] = separate[d] = match[d] = T(0);
     int N = 0;
-    for_each_run<D>(sp.dims, sp.periodic, AB_METRIC_EUCLIDEAN, c, gr, cell_start, false,
+    for_each_run<D>(sp.dims, sp.periodic, AB_METRIC_EUCLIDEAN, c, gr, cell_start, sp.ksh, false,
                     [&](uint32_t b, uint32_t e, int wrap) {
         const int full = (wrap | slowmask) & permask;
         for (uint32_t j = b; j < e; ++j) {
@@ -116,12 +115,45 @@ k_flock_generic(SpaceDev<T, D> sp, FlockU<T> uni, const T* __restrict__ per_agen
             }
         }
     });
+    *Nout = N;
+}
+
+template <class T, int D, bool EXACT>
+__global__ void __launch_bounds__(128)
+k_flock_generic(SpaceDev<T, D> sp, FlockU<T> uni, const T* __restrict__ per_agent, const T* __restrict__ pos,
+                const T* __restrict__ vel, const uint32_t* __restrict__ key, const uint32_t* __restrict__ cell_start,
+                int64_t cap, int n, T* __restrict__ npos, T* __restrict__ nvel, uint32_t* __restrict__ newkey,
+                uint32_t* __restrict__ rank, uint32_t* __restrict__ cell_count, const int32_t* __restrict__ ids,
+                int32_t* __restrict__ ncount, int* __restrict__ err) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    FlockU<T> fp = uni;
+    if (per_agent) {
+        fp.speed = per_agent[(size_t)0 * cap + s];
+        fp.cohere_factor = per_agent[(size_t)1 * cap + s];
+        fp.separation = per_agent[(size_t)2 * cap + s];
+        fp.separate_factor = per_agent[(size_t)3 * cap + s];
+        fp.match_factor = per_agent[(size_t)4 * cap + s];
+        fp.visual_distance = (double)per_agent[(size_t)5 * cap + s];
+        if (EXACT) fp.thr = exact_threshold<T>(fp.visual_distance);
+    }
+    T p[D], v[D];
+    int c[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d) { p[d] = pos[(size_t)d * cap + s]; v[d] = vel[(size_t)d * cap + s]; }
+    unlin_cell<D>(sp.dims, key[s] >> sp.ksh, c);
+    const int gr = grid_radius<T, D>(sp, p, c, fp.visual_distance);
+    T cohere[D], separate[D], match[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d) cohere[d] = separate[d] = match[d] = T(0);
+    int N = 0;
+    flock_accumulate_generic<T, D, EXACT>(sp, fp, s, p, c, gr, pos, vel, cell_start, cap, &N, cohere, separate, match);
     T np[D], nv[D];
     flock_epilogue<T, D>(sp, p, v, cohere, separate, match, N, fp, np, nv, err);
     int nc[D];
     bool ok = pos2cell0<T, D>(sp, np, nc);
     if (!ok) atomicOr(err, AB_EF_NUMERIC);
-    const uint32_t k = lin_cell<D>(sp.dims, nc);
+    const uint32_t k = device_key<T, D>(sp, np, nc);
 #pragma unroll
     for (int d = 0; d < D; ++d) { npos[(size_t)d * cap + s] = np[d]; nvel[(size_t)d * cap + s] = nv[d]; }
     newkey[s] = k;
@@ -215,15 +247,34 @@ static int move_common(ab_handle* h, double dt, const void* directions, const in
     return e;
 }
 
+template <class T, int D, bool EXACT>
+static int launch_tiled(ab_handle* h, const SpaceDev<T, D>& sp, const FlockU<T>& u, int32_t* ncount) {
+    using SM = TiledSmem<T, D, EXACT>;
+    constexpr int SWT = TiledCfg<D>::SWT;
+    static bool attr_done = false;
+    if (!attr_done) {
+        AB_CUDA(h, cudaFuncSetAttribute(k_flock_tiled<T, D, EXACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SM::TOTAL));
+        attr_done = true;
+    }
+    const int cur = h->cur;
+    const int n = (int)h->n;
+    AB_LAUNCH(h, EXACT ? "k_flock_tiled_exact" : "k_flock_tiled");
+    k_flock_tiled<T, D, EXACT><<<ab_blocks(n, SWT), SWT, SM::TOTAL, h->stream>>>(
+        sp, u, (const T*)h->fields[0].buf[cur], (const T*)h->fields[1].buf[cur], h->key[cur], h->cell_start,
+        (const T*)h->cell_agg, (int64_t)h->ncells, h->cap, n, (T*)h->tmp_pos, (T*)h->tmp_vel, h->newkey, h->id[cur],
+        ncount, h->d_err);
+    return AB_OK;
+}
+
 template <class T, int D>
 static int flock_steps_t(ab_handle* h, const ab_flock_params* p, int64_t nsteps) {
     const int n = (int)h->n;
-    SpaceDev<T, D> sp = make_space<T, D>(h);
     FlockU<T> u;
     u.speed = (T)p->speed; u.cohere_factor = (T)p->cohere_factor; u.separation = (T)p->separation;
     u.separate_factor = (T)p->separate_factor; u.match_factor = (T)p->match_factor;
     u.visual_distance = p->visual_distance;
     const bool exact = p->search == AB_SEARCH_EXACT;
+    u.thr = exact ? exact_threshold_host<T>(p->visual_distance) : T(0);
     int pa_field = p->per_agent_field;
     if (pa_field >= 0) {
         if (pa_field >= (int)h->fields.size() || h->fields[pa_field].ncomp != 6 || h->fields[pa_field].dtype != h->dtype)
@@ -232,30 +283,40 @@ static int flock_steps_t(ab_handle* h, const ab_flock_params* p, int64_t nsteps)
     // kernel choice
     bool tiled = false;
     TiledPlan plan;
-    if (p->kernel != 1 && pa_field < 0) tiled = plan_tiled<T, D>(h, p->visual_distance, (double)u.separation, exact, &plan);
+    if (p->kernel != 1) tiled = plan_tiled<T, D>(h, p, exact, &plan);
     if (p->kernel == 2 && !tiled) return ab_fail(h, AB_ERR_INVALID, "tiled flock kernel not applicable to this configuration");
+    if (tiled) AB_TRY(ab_set_refine(h, plan.K));
+    AB_TRY(ab_ensure_index(h));
+    if (tiled && !exact) AB_TRY(ab_ensure_agg(h));
+    SpaceDev<T, D> sp = make_space<T, D>(h);
+    AB_CUDA(h, cudaEventRecord(h->ev0, h->stream));
     for (int64_t st = 0; st < nsteps; ++st) {
         const int cur = h->cur;
         const T* pos = (const T*)h->fields[0].buf[cur];
         const T* vel = (const T*)h->fields[1].buf[cur];
         int32_t* ncount = (st == nsteps - 1) ? h->ncount : nullptr;   // neighbour counts by id (diagnostic)
         if (tiled) {
-            AB_TRY((launch_tiled<T, D>(h, sp, u, exact, plan, ncount)));
+            if (exact) AB_TRY((launch_tiled<T, D, true>(h, sp, u, ncount)));
+            else AB_TRY((launch_tiled<T, D, false>(h, sp, u, ncount)));
+            AB_TRY(ab_resort_tiled(h, h->tmp_pos, h->tmp_vel, !exact));
         } else {
             const T* pa = pa_field >= 0 ? (const T*)h->fields[pa_field].buf[cur] : nullptr;
-            AB_LAUNCH(h, "k_flock_generic");
-            const int TB = 128;
-            if (exact)
-                k_flock_generic<T, D, true><<<ab_blocks(n, TB), TB, 0, h->stream>>>(
-                    sp, u, pa, pos, vel, h->key[cur], h->cell_start, h->cap, n, (T*)h->tmp_pos, (T*)h->tmp_vel,
-                    h->newkey, h->rank, h->cell_count, h->id[cur], ncount, h->d_err);
-            else
-                k_flock_generic<T, D, false><<<ab_blocks(n, TB), TB, 0, h->stream>>>(
-                    sp, u, pa, pos, vel, h->key[cur], h->cell_start, h->cap, n, (T*)h->tmp_pos, (T*)h->tmp_vel,
-                    h->newkey, h->rank, h->cell_count, h->id[cur], ncount, h->d_err);
+            {
+                AB_LAUNCH(h, "k_flock_generic");
+                const int TB = 128;
+                if (exact)
+                    k_flock_generic<T, D, true><<<ab_blocks(n, TB), TB, 0, h->stream>>>(
+                        sp, u, pa, pos, vel, h->key[cur], h->cell_start, h->cap, n, (T*)h->tmp_pos, (T*)h->tmp_vel,
+                        h->newkey, h->rank, h->cell_count, h->id[cur], ncount, h->d_err);
+                else
+                    k_flock_generic<T, D, false><<<ab_blocks(n, TB), TB, 0, h->stream>>>(
+                        sp, u, pa, pos, vel, h->key[cur], h->cell_start, h->cap, n, (T*)h->tmp_pos, (T*)h->tmp_vel,
+                        h->newkey, h->rank, h->cell_count, h->id[cur], ncount, h->d_err);
+            }
+            AB_TRY(ab_reindex_from(h, h->tmp_pos, h->tmp_vel, true));
         }
-        AB_TRY(ab_reindex_from(h, h->tmp_pos, h->tmp_vel, true));
     }
+    AB_CUDA(h, cudaEventRecord(h->ev1, h->stream));
     return AB_OK;
 }
 
@@ -279,14 +340,11 @@ int ab_step_flock(ab_handle* h, const ab_flock_params* p, int64_t nsteps) {
     if (nsteps < 0) return ab_fail(h, AB_ERR_INVALID, "negative nsteps");
     AB_CUDA(h, cudaSetDevice(h->device));
     if (h->n == 0 || nsteps == 0) return AB_OK;
-    AB_TRY(ab_ensure_index(h));
     if (ab_comm_active(h)) return ab_comm_step_flock(h, p, nsteps);
-    AB_CUDA(h, cudaEventRecord(h->ev0, h->stream));
     int rc;
     if (h->dtype == AB_F64) rc = h->D == 2 ? flock_steps_t<double, 2>(h, p, nsteps) : flock_steps_t<double, 3>(h, p, nsteps);
     else rc = h->D == 2 ? flock_steps_t<float, 2>(h, p, nsteps) : flock_steps_t<float, 3>(h, p, nsteps);
     AB_TRY(rc);
-    AB_CUDA(h, cudaEventRecord(h->ev1, h->stream));
     AB_TRY(ab_check_device_errors(h));
     float ms = 0;
     AB_CUDA(h, cudaEventElapsedTime(&ms, h->ev0, h->ev1));

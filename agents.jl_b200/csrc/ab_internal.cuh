@@ -20,6 +20,7 @@
 #include <stdint.h>
 
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/agents_b200.h"
@@ -52,8 +53,12 @@ struct ab_handle {
     int dtype = AB_F64;
     size_t tsize = 8;
     int64_t n = 0, cap = 0;
-    int64_t ncells = 1;
+    int64_t ncells = 1;                // reference cells (prod dims)
     int dims[3] = {1, 1, 1};
+    int K = 1;                         // refinement: each reference cell holds K^D device sub-cells
+    int ksh = 0;                       // log2(K^D)
+    int64_t nfine = 1;                 // ncells << ksh : entries of cell_start - 1
+    int64_t nfine_cap = 1;             // allocated (padded) length of cell_count
 
     std::vector<ab_field> fields;      // 0 = pos, 1 = vel (continuous); 0 = pos (grids)
     int cur = 0;
@@ -64,17 +69,25 @@ struct ab_handle {
     uint32_t* newkey = nullptr;        // per old slot
     uint32_t* rank = nullptr;          // arrival rank inside the new cell (atomic order)
     uint32_t* cell_count = nullptr;    // ncells (zero between uses)
-    uint32_t* cell_start = nullptr;    // ncells + 1
+    uint32_t* cell_start = nullptr;    // nfine + 1 (current)
+    uint32_t* cell_start_alt = nullptr; // written by the tiled re-sort, then swapped in
     int32_t* idtmp = nullptr;          // ids bucketed by cell, arrival order
     int32_t* perm = nullptr;           // new slot -> old slot (for extra fields)
     int32_t* slot_of_id = nullptr;
     bool slot_map_valid = false;
     bool index_valid = false;
+    bool agg_valid = false;            // cell_agg matches the current sorted state
     int32_t* ncount = nullptr;         // neighbour count per slot of the last flock step
 
-    // cell sums for the approximate-search fast path (ab_flock.cu)
-    void* cell_sums = nullptr;         // ncells * 2*D of T
-    size_t cell_sums_bytes = 0;
+    // per reference cell Σ(pos - centre), Σ vel of the sorted state (SoA: 2*D arrays
+    // of ncells T) — input of the aggregated approximate-search sweep (ab_flock.cu)
+    void* cell_agg = nullptr;
+    size_t cell_agg_bytes = 0;
+
+    // tiled re-sort look-back state (ab_resort.cu)
+    unsigned long long* rs_status = nullptr;
+    size_t rs_status_len = 0;
+    uint32_t rs_epoch = 0;
 
     // single-pass scan state
     unsigned long long* scan_status = nullptr;
@@ -132,7 +145,12 @@ int ab_scratch2(ab_handle* h, size_t bytes, void** out);    // scratch2 (grow-on
 int ab_check_device_errors(ab_handle* h);                   // reads + clears d_err
 int ab_ensure_index(ab_handle* h);
 int ab_ensure_slot_map(ab_handle* h);
+int ab_set_refine(ab_handle* h, int K);
 int ab_reindex_from(ab_handle* h, const void* src_pos, const void* src_vel, bool count_done);
+int ab_permute_extra_fields(ab_handle* h);     // applies h->perm (new slot -> old slot) to user columns, cur -> cur^1
+bool ab_resort_applicable(const ab_handle* h);
+int ab_resort_tiled(ab_handle* h, const void* src_pos, const void* src_vel, bool want_agg);
+int ab_ensure_agg(ab_handle* h);
 size_t ab_dtype_size(int dtype);
 // cross-file internals (C++ linkage)
 void ab_comm_free(ab_handle* h);
@@ -168,6 +186,8 @@ template <class T, int D> struct SpaceDev {
     int dims[D];
     bool periodic[D];
     int metric;
+    int K;        // sub-cells per reference cell and dimension (1 or 2)
+    int ksh;      // log2(K^D): device key = (reference cell << ksh) | sub-cell
 };
 
 template <class T, int D> static inline SpaceDev<T, D> make_space(const ab_handle* h) {
@@ -181,6 +201,8 @@ template <class T, int D> static inline SpaceDev<T, D> make_space(const ab_handl
     s.spacing = (T)h->desc.spacing;
     s.spacing_d = (double)s.spacing;
     s.metric = h->desc.kind == AB_SPACE_CONTINUOUS ? AB_METRIC_EUCLIDEAN : h->desc.metric;
+    s.K = h->K;
+    s.ksh = h->ksh;
     return s;
 }
 
@@ -243,6 +265,23 @@ template <int D> __device__ __forceinline__ void unlin_cell(const int* dims, uin
         lin = q;
     }
     c[D - 1] = (int)lin;
+}
+
+// Device cell key: reference cell (column-major, like stored_ids[c...]) in the
+// high bits, sub-cell in the low ksh bits.  Sub-cell bit d = position above the
+// reference cell's centre (cell_center, continuous.jl:116-117), so sub-cells
+// nest exactly inside the bit-exact reference cells.
+template <class T, int D>
+__device__ __forceinline__ uint32_t device_key(const SpaceDev<T, D>& sp, const T* p, const int* c) {
+    uint32_t k = lin_cell<D>(sp.dims, c) << sp.ksh;
+    if (sp.K == 2) {
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            T centre = sp.spacing * ((T)(c[d] + 1) - T(0.5));
+            k |= (p[d] > centre ? 1u : 0u) << d;
+        }
+    }
+    return k;
 }
 
 // grid_r = ceil(Int, (r + δ)/spacing), δ = distance_from_cell_center —
@@ -318,26 +357,27 @@ __device__ __forceinline__ int isqrt_floor(long long v) {
 // coordinates, at most dims0 of them) of one cell row, in ascending-offset
 // order, wrapping (periodic) or clipping (non-periodic) at the x boundary.
 template <class F>
-__device__ __forceinline__ void emit_xrange(int dims0, bool periodic0, const uint32_t* __restrict__ cell_start,
-                                            uint32_t rowbase, int a, int b, int wrap, F&& f) {
+__device__ __forceinline__ void emit_xrange(int dims0, bool periodic0, const uint32_t* __restrict__ cell_start_,
+                                            int ksh, uint32_t rowbase, int a, int b, int wrap, F&& f) {
+    auto CS = [&](uint32_t refcell) { return cell_start_[(size_t)refcell << ksh]; };
     if (a > b) return;
     if (!periodic0) {
         if (a < 0) a = 0;
         if (b >= dims0) b = dims0 - 1;
-        if (a <= b) f(cell_start[rowbase + a], cell_start[rowbase + b + 1], wrap);
+        if (a <= b) f(CS(rowbase + a), CS(rowbase + b + 1), wrap);
         return;
     }
     if (a < 0) {
         int e = b < -1 ? b : -1;
-        f(cell_start[rowbase + a + dims0], cell_start[rowbase + e + dims0 + 1], wrap | 1);
+        f(CS(rowbase + a + dims0), CS(rowbase + e + dims0 + 1), wrap | 1);
         a = 0;
     }
     if (a <= b) {
         int e = b < dims0 - 1 ? b : dims0 - 1;
-        if (a <= e) f(cell_start[rowbase + a], cell_start[rowbase + e + 1], wrap);
+        if (a <= e) f(CS(rowbase + a), CS(rowbase + e + 1), wrap);
         if (b >= dims0) {
             int s2 = a > dims0 ? a : dims0;
-            f(cell_start[rowbase + s2 - dims0], cell_start[rowbase + b - dims0 + 1], wrap | 1);
+            f(CS(rowbase + s2 - dims0), CS(rowbase + b - dims0 + 1), wrap | 1);
         }
     }
 }
@@ -352,12 +392,12 @@ __device__ __forceinline__ void emit_xrange(int dims0, bool periodic0, const uin
 // zero offset (offsets_within_radius_no_0, grid_general.jl:165-179).
 template <int D, class F>
 __device__ __forceinline__ void for_each_run(const int* dims, const bool* periodic, int metric, const int* c0,
-                                             int r0, const uint32_t* __restrict__ cell_start, bool skip_zero,
-                                             F&& f) {
+                                             int r0, const uint32_t* __restrict__ cell_start, int ksh,
+                                             bool skip_zero, F&& f) {
     if (r0 < 0) {   // empty product → calculate_offsets pushes the zero offset (grid_general.jl:149)
         if (skip_zero) return;
         uint32_t l = lin_cell<D>(dims, c0);
-        f(cell_start[l], cell_start[l + 1], 0);
+        f(cell_start[(size_t)l << ksh], cell_start[(size_t)(l + 1) << ksh], 0);
         return;
     }
     int lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
@@ -396,10 +436,10 @@ __device__ __forceinline__ void for_each_run(const int* dims, const bool* period
             uint32_t rowbase = (D == 3) ? ((uint32_t)cz * (uint32_t)dims[1] + (uint32_t)cy) * (uint32_t)dims[0]
                                         : (uint32_t)cy * (uint32_t)dims[0];
             if (skip_zero && by == 0 && bz == 0 && xl <= 0 && xh >= 0) {
-                emit_xrange(dims[0], periodic[0], cell_start, rowbase, c0[0] + xl, c0[0] - 1, wrap, f);
-                emit_xrange(dims[0], periodic[0], cell_start, rowbase, c0[0] + 1, c0[0] + xh, wrap, f);
+                emit_xrange(dims[0], periodic[0], cell_start, ksh, rowbase, c0[0] + xl, c0[0] - 1, wrap, f);
+                emit_xrange(dims[0], periodic[0], cell_start, ksh, rowbase, c0[0] + 1, c0[0] + xh, wrap, f);
             } else {
-                emit_xrange(dims[0], periodic[0], cell_start, rowbase, c0[0] + xl, c0[0] + xh, wrap, f);
+                emit_xrange(dims[0], periodic[0], cell_start, ksh, rowbase, c0[0] + xl, c0[0] + xh, wrap, f);
             }
         }
     }

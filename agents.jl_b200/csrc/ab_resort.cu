@@ -1,0 +1,428 @@
+// ab_resort.cu — tile-based, deterministic re-sort of the population after a
+// fused step, and the per-reference-cell aggregates of the sorted state.
+//
+// The reference keeps its index current by moving one id between two cell
+// vectors per moved agent (src/spaces/continuous.jl:133-153, :161-166).  Here a
+// step leaves the new state in OLD slot order (tmp_pos / tmp_vel / newkey); this
+// kernel brings it into the next step's cell-sorted order in ONE pass:
+//
+//   tile  = a run of `tw` reference cells of one cell row = a contiguous range of
+//           device keys = a contiguous range of output slots.
+//   CTA   = one tile (taken by ticket, so tile t only ever waits for tiles < t
+//           that are already running).  It scans the OLD slots of the 3^D
+//           neighbouring reference cells of its tile (agents move less than one
+//           reference cell per step on this path), keeps those whose new key
+//           falls into the tile, histograms them per device cell in shared
+//           memory, publishes the tile total and obtains its output base by
+//           decoupled look-back, orders every cell's agents by id (canonical
+//           order: bitwise reproducible runs whatever the atomic order was),
+//           and writes pos / vel / id / key coalesced, the tile's slice of
+//           cell_start, and (optionally) Σ(pos - centre), Σ vel of every
+//           reference cell of the tile in that canonical order.
+//
+// Nothing here is specific to the flock rule: any fused rule that bounds the
+// per-step displacement by one reference cell can use it.
+#include "ab_internal.cuh"
+
+#define RS_THREADS 256
+#define RS_MAXSEG 27
+#define RS_FC_MAX 1024          // device cells per tile (shared histogram)
+#define RS_CAP 2048             // agents per tile handled in shared memory; larger tiles use global scratch
+
+struct ResortArgs {
+    int tw, tpr, ntiles, nrows;
+    uint32_t epoch;
+    int has_vel, want_agg;
+};
+
+template <class T, int D>
+__global__ void __launch_bounds__(RS_THREADS)
+k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, const uint32_t* __restrict__ newkey,
+         const int32_t* __restrict__ id_old, const T* __restrict__ src_pos, const T* __restrict__ src_vel,
+         int64_t cap, int n, T* __restrict__ dst_pos, T* __restrict__ dst_vel, int32_t* __restrict__ id_new,
+         uint32_t* __restrict__ key_new, uint32_t* __restrict__ cs_new, int32_t* __restrict__ perm,
+         T* __restrict__ agg, int64_t agg_stride, int32_t* __restrict__ g_ent_id, int32_t* __restrict__ g_ent_s,
+         volatile unsigned long long* status, uint32_t* ticket, int* __restrict__ err) {
+    __shared__ uint32_t s_tile;
+    __shared__ uint32_t s_seg_beg[RS_MAXSEG], s_seg_end[RS_MAXSEG];
+    __shared__ int s_nseg;
+    __shared__ uint32_t s_cnt[RS_FC_MAX];        // histogram, then cursor
+    __shared__ uint32_t s_start[RS_FC_MAX + 1];  // exclusive scan
+    __shared__ uint32_t s_warp[RS_THREADS / 32];
+    __shared__ uint32_t s_base;
+    __shared__ int32_t s_ent_id[RS_CAP], s_ent_s[RS_CAP];
+    __shared__ uint16_t s_ent_lc[RS_CAP];
+    __shared__ int32_t s_sorted_s[RS_CAP];
+
+    const int tid = threadIdx.x;
+    if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const int tile = (int)s_tile;
+    const int row = tile / a.tpr, seg = tile - row * a.tpr;
+    const int x0 = seg * a.tw;
+    const int x1 = min(sp.dims[0], x0 + a.tw);          // exclusive
+    const int ksh = sp.ksh;
+    const uint32_t kbeg = ((uint32_t)row * (uint32_t)sp.dims[0] + (uint32_t)x0) << ksh;
+    const uint32_t kend = ((uint32_t)row * (uint32_t)sp.dims[0] + (uint32_t)x1) << ksh;
+    const int fc = (int)(kend - kbeg);
+
+    // ---- source segments: old slots of the neighbouring reference cells -------------
+    if (tid == 0) {
+        int cy = D == 2 ? row : row % sp.dims[1];
+        int cz = D == 2 ? 0 : row / sp.dims[1];
+        int ns = 0;
+        for (int dz = (D == 3 ? -1 : 0); dz <= (D == 3 ? 1 : 0); ++dz) {
+            int z = cz + dz;
+            if (D == 3 && (z < 0 || z >= sp.dims[2])) {
+                if (!sp.periodic[2]) continue;
+                z = z < 0 ? z + sp.dims[2] : z - sp.dims[2];
+            }
+            for (int dy = -1; dy <= 1; ++dy) {
+                int y = cy + dy;
+                if (y < 0 || y >= sp.dims[1]) {
+                    if (!sp.periodic[1]) continue;
+                    y = y < 0 ? y + sp.dims[1] : y - sp.dims[1];
+                }
+                const uint32_t rb = (D == 3 ? (uint32_t)z * (uint32_t)sp.dims[1] + (uint32_t)y : (uint32_t)y) * (uint32_t)sp.dims[0];
+                const int lo = max(x0 - 1, 0), hi = min(x1, sp.dims[0] - 1);      // inclusive reference cells
+                s_seg_beg[ns] = cs_old[(size_t)(rb + lo) << ksh];
+                s_seg_end[ns] = cs_old[(size_t)(rb + hi + 1) << ksh];
+                ++ns;
+                if (sp.periodic[0]) {
+                    if (x0 == 0 && hi < sp.dims[0] - 1) {        // left neighbour wraps to the last cell of the row
+                        s_seg_beg[ns] = cs_old[(size_t)(rb + sp.dims[0] - 1) << ksh];
+                        s_seg_end[ns] = cs_old[(size_t)(rb + sp.dims[0]) << ksh];
+                        ++ns;
+                    }
+                    if (x1 == sp.dims[0] && lo > 0) {            // right neighbour wraps to the first cell
+                        s_seg_beg[ns] = cs_old[(size_t)rb << ksh];
+                        s_seg_end[ns] = cs_old[(size_t)(rb + 1) << ksh];
+                        ++ns;
+                    }
+                }
+            }
+        }
+        s_nseg = ns;
+    }
+    for (int i = tid; i < fc; i += RS_THREADS) s_cnt[i] = 0;
+    __syncthreads();
+    const int nseg = s_nseg;
+
+    // ---- pass 1: histogram of the agents that land in this tile ----------------------
+    for (int sg = 0; sg < nseg; ++sg) {
+        const uint32_t e = s_seg_end[sg];
+        for (uint32_t s = s_seg_beg[sg] + tid; s < e; s += RS_THREADS) {
+            const uint32_t k = newkey[s];
+            if (k >= kbeg && k < kend) atomicAdd(&s_cnt[k - kbeg], 1u);
+        }
+    }
+    __syncthreads();
+
+    // ---- block exclusive scan of s_cnt[0..fc) -> s_start ------------------------------
+    const int per = (fc + RS_THREADS - 1) / RS_THREADS;     // <= 4
+    uint32_t loc[RS_FC_MAX / RS_THREADS];
+    uint32_t tsum = 0;
+#pragma unroll
+    for (int i = 0; i < RS_FC_MAX / RS_THREADS; ++i) {
+        const int idx = tid * per + i;
+        uint32_t v = (i < per && idx < fc) ? s_cnt[idx] : 0u;
+        loc[i] = tsum;
+        tsum += v;
+    }
+    const int lane = tid & 31, wid = tid >> 5;
+    uint32_t inc = tsum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+    if (lane == 31) s_warp[wid] = inc;
+    __syncthreads();
+    uint32_t woff = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < RS_THREADS / 32; ++w) { uint32_t t = s_warp[w]; if (w < wid) woff += t; total += t; }
+    const uint32_t toff = woff + inc - tsum;
+#pragma unroll
+    for (int i = 0; i < RS_FC_MAX / RS_THREADS; ++i) {
+        const int idx = tid * per + i;
+        if (i < per && idx < fc) { s_start[idx] = toff + loc[i]; s_cnt[idx] = toff + loc[i]; }   // cursor = start
+    }
+    if (tid == 0) s_start[fc] = total;
+
+    // ---- output base of the tile: decoupled look-back over the tile totals -------------
+    if (wid == 0) {
+        const unsigned long long ep = (unsigned long long)a.epoch << 34;
+        uint32_t excl = 0;
+        if (tile == 0) {
+            if (lane == 0) status[0] = ep | (2ull << 32) | total;
+        } else {
+            if (lane == 0) status[tile] = ep | (1ull << 32) | total;
+            int p = tile - 1;
+            for (;;) {
+                const int idx = p - lane;
+                unsigned long long st;
+                bool valid;
+                do {
+                    st = idx >= 0 ? status[idx] : (ep | (2ull << 32));
+                    valid = ((st >> 34) == (unsigned long long)a.epoch) && (((st >> 32) & 3ull) != 0);
+                } while (__any_sync(0xffffffffu, !valid));
+                const unsigned incl_mask = __ballot_sync(0xffffffffu, ((st >> 32) & 3ull) == 2ull);
+                uint32_t val = (uint32_t)st;
+                if (incl_mask) { const int first = __ffs(incl_mask) - 1; if (lane > first) val = 0; }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
+                excl += val;
+                if (incl_mask) break;
+                p -= 32;
+            }
+            if (lane == 0) status[tile] = ep | (2ull << 32) | (unsigned long long)(excl + total);
+        }
+        if (lane == 0) {
+            s_base = excl;
+            if (tile == a.ntiles - 1) {
+                cs_new[(size_t)kend] = excl + total;
+                *ticket = 0;
+                if (excl + total != (uint32_t)n) atomicOr(err, AB_EF_OVERFLOW);     // an agent left its 3^D neighbourhood
+            }
+        }
+    }
+    __syncthreads();
+    const uint32_t base = s_base;
+    const bool small = total <= RS_CAP;
+    int32_t* ent_id = small ? s_ent_id : g_ent_id + base;
+    int32_t* ent_s = small ? s_ent_s : g_ent_s + base;
+
+    // this tile's slice of the new cell_start
+    for (int i = tid; i < fc; i += RS_THREADS) cs_new[(size_t)kbeg + i] = base + s_start[i];
+
+    // ---- pass 2: entries into their cell segment (arrival order) -------------------------
+    for (int sg = 0; sg < nseg; ++sg) {
+        const uint32_t e = s_seg_end[sg];
+        for (uint32_t s = s_seg_beg[sg] + tid; s < e; s += RS_THREADS) {
+            const uint32_t k = newkey[s];
+            if (k >= kbeg && k < kend) {
+                const uint32_t lc = k - kbeg;
+                const uint32_t p = atomicAdd(&s_cnt[lc], 1u);
+                ent_id[p] = id_old[s];
+                ent_s[p] = (int32_t)s;
+                if (small) s_ent_lc[p] = (uint16_t)lc;
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- canonical order inside every cell (by id), then coalesced output ------------------
+    if (small) {
+        for (uint32_t p = tid; p < total; p += RS_THREADS) {
+            const uint32_t lc = s_ent_lc[p];
+            const uint32_t b = s_start[lc], e = s_start[lc + 1];
+            const int32_t me = s_ent_id[p];
+            uint32_t r = 0;
+            for (uint32_t t = b; t < e; ++t) r += (s_ent_id[t] < me) ? 1u : 0u;
+            s_sorted_s[b + r] = (int32_t)p;        // sorted position -> entry
+        }
+        __syncthreads();
+        for (uint32_t t = tid; t < total; t += RS_THREADS) {
+            const int p = s_sorted_s[t];
+            const int s = s_ent_s[p];
+            const size_t o = (size_t)base + t;
+#pragma unroll
+            for (int d = 0; d < D; ++d) dst_pos[(size_t)d * cap + o] = src_pos[(size_t)d * cap + s];
+            if (a.has_vel) {
+#pragma unroll
+                for (int d = 0; d < D; ++d) dst_vel[(size_t)d * cap + o] = src_vel[(size_t)d * cap + s];
+            }
+            id_new[o] = s_ent_id[p];
+            key_new[o] = kbeg + s_ent_lc[p];
+            if (perm) perm[o] = s;
+        }
+    } else {
+        // crowded tile: entries live in global scratch at [base, base + total); same steps through L2
+        for (uint32_t p = tid; p < total; p += RS_THREADS) {
+            const uint32_t k = newkey[ent_s[p]];
+            const uint32_t lc = k - kbeg;
+            const uint32_t b = s_start[lc], e = s_start[lc + 1];
+            const int32_t me = ent_id[p];
+            uint32_t r = p - b;                                  // arrival order for very crowded cells
+            if (e - b <= 4096u) { r = 0; for (uint32_t t = b; t < e; ++t) r += (ent_id[t] < me) ? 1u : 0u; }
+            const int s = ent_s[p];
+            const size_t o = (size_t)base + b + r;
+#pragma unroll
+            for (int d = 0; d < D; ++d) dst_pos[(size_t)d * cap + o] = src_pos[(size_t)d * cap + s];
+            if (a.has_vel) {
+#pragma unroll
+                for (int d = 0; d < D; ++d) dst_vel[(size_t)d * cap + o] = src_vel[(size_t)d * cap + s];
+            }
+            id_new[o] = me;
+            key_new[o] = k;
+            if (perm) perm[o] = s;
+        }
+    }
+
+    // ---- per reference cell Σ(pos - centre), Σ vel in canonical order --------------------------
+    if (a.want_agg) {
+        __syncthreads();     // the tile's output slots are complete (global writes of this CTA are visible to it)
+        const int ncell = x1 - x0;
+        const int grp = tid >> 3, gl = tid & 7;               // 8 lanes per reference cell
+        for (int c = grp; c < ncell; c += RS_THREADS / 8) {
+            const uint32_t b = base + s_start[(size_t)c << ksh], e = base + s_start[(size_t)(c + 1) << ksh];
+            const uint32_t refcell = (uint32_t)row * (uint32_t)sp.dims[0] + (uint32_t)(x0 + c);
+            int cc[D];
+            unlin_cell<D>(sp.dims, refcell, cc);
+            T acc[2 * D];
+#pragma unroll
+            for (int d = 0; d < 2 * D; ++d) acc[d] = T(0);
+            for (uint32_t t = b + gl; t < e; t += 8) {
+#pragma unroll
+                for (int d = 0; d < D; ++d) {
+                    const T centre = sp.spacing * ((T)(cc[d] + 1) - T(0.5));
+                    acc[d] += dst_pos[(size_t)d * cap + t] - centre;
+                    acc[D + d] += dst_vel[(size_t)d * cap + t];
+                }
+            }
+#pragma unroll
+            for (int d = 0; d < 2 * D; ++d) {
+                acc[d] += __shfl_xor_sync(0xffffffffu, acc[d], 4);
+                acc[d] += __shfl_xor_sync(0xffffffffu, acc[d], 2);
+                acc[d] += __shfl_xor_sync(0xffffffffu, acc[d], 1);
+            }
+            if (gl == 0) {
+#pragma unroll
+                for (int d = 0; d < 2 * D; ++d) agg[(size_t)d * agg_stride + refcell] = acc[d];
+            }
+        }
+    }
+}
+
+// Aggregates of an already sorted state (after a generic index build): one
+// 8-lane group per reference cell, same summation order as k_resort.
+template <class T, int D>
+__global__ void __launch_bounds__(256)
+k_cell_agg(SpaceDev<T, D> sp, const uint32_t* __restrict__ cs, const T* __restrict__ pos, const T* __restrict__ vel,
+           int64_t cap, uint32_t ncells, T* __restrict__ agg, int64_t agg_stride) {
+    const uint32_t g = (blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+    const int gl = threadIdx.x & 7;
+    const bool live = g < ncells;
+    const uint32_t c = live ? g : 0;
+    const uint32_t b = cs[(size_t)c << sp.ksh], e = live ? cs[(size_t)(c + 1) << sp.ksh] : b;
+    int cc[D];
+    unlin_cell<D>(sp.dims, c, cc);
+    T acc[2 * D];
+#pragma unroll
+    for (int d = 0; d < 2 * D; ++d) acc[d] = T(0);
+    for (uint32_t t = b + gl; t < e; t += 8) {
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            const T centre = sp.spacing * ((T)(cc[d] + 1) - T(0.5));
+            acc[d] += pos[(size_t)d * cap + t] - centre;
+            acc[D + d] += vel[(size_t)d * cap + t];
+        }
+    }
+#pragma unroll
+    for (int d = 0; d < 2 * D; ++d) {
+        acc[d] += __shfl_xor_sync(0xffffffffu, acc[d], 4);
+        acc[d] += __shfl_xor_sync(0xffffffffu, acc[d], 2);
+        acc[d] += __shfl_xor_sync(0xffffffffu, acc[d], 1);
+    }
+    if (live && gl == 0) {
+#pragma unroll
+        for (int d = 0; d < 2 * D; ++d) agg[(size_t)d * agg_stride + c] = acc[d];
+    }
+}
+
+// ---------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------
+bool ab_resort_applicable(const ab_handle* h) {
+    if (h->desc.kind != AB_SPACE_CONTINUOUS) return false;
+    for (int d = 0; d < h->D; ++d) if (h->dims[d] < 3) return false;     // 3 distinct neighbour rows / cells
+    return h->n > 0;
+}
+
+static int ensure_agg(ab_handle* h) {
+    size_t need = (size_t)2 * h->D * h->ncells * h->tsize;
+    if (h->cell_agg_bytes >= need) return AB_OK;
+    if (h->cell_agg) { AB_CUDA(h, cudaStreamSynchronize(h->stream)); AB_CUDA(h, cudaFree(h->cell_agg)); h->cell_agg = nullptr; }
+    AB_CUDA(h, cudaMalloc(&h->cell_agg, need));
+    h->cell_agg_bytes = need;
+    h->agg_valid = false;
+    return AB_OK;
+}
+
+template <class T, int D>
+static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool want_agg) {
+    const int cur = h->cur, nxt = cur ^ 1;
+    SpaceDev<T, D> sp = make_space<T, D>(h);
+    ResortArgs a;
+    // tile width: ~768 agents per tile on average, at most RS_FC_MAX device cells
+    const double dens = (double)h->n / (double)h->ncells;
+    int tw = (int)(768.0 / (dens > 1e-9 ? dens : 1e-9));
+    const int twmax = RS_FC_MAX >> h->ksh;
+    if (tw > twmax) tw = twmax;
+    if (tw < 4) tw = 4;
+    if (tw > h->dims[0]) tw = h->dims[0];
+    a.tpr = (h->dims[0] + tw - 1) / tw;
+    a.tw = (h->dims[0] + a.tpr - 1) / a.tpr;          // even split of the row
+    a.nrows = (int)(h->ncells / h->dims[0]);
+    a.ntiles = a.nrows * a.tpr;
+    a.has_vel = h->desc.kind == AB_SPACE_CONTINUOUS;
+    a.want_agg = want_agg ? 1 : 0;
+    if ((size_t)a.ntiles + 1 > h->rs_status_len) {
+        if (h->rs_status) { AB_CUDA(h, cudaStreamSynchronize(h->stream)); AB_CUDA(h, cudaFree(h->rs_status)); h->rs_status = nullptr; }
+        AB_CUDA(h, cudaMalloc((void**)&h->rs_status, ((size_t)a.ntiles + 1) * sizeof(unsigned long long)));
+        AB_CUDA(h, cudaMemsetAsync(h->rs_status, 0, ((size_t)a.ntiles + 1) * sizeof(unsigned long long), h->stream));
+        h->rs_status_len = (size_t)a.ntiles + 1;
+        h->rs_epoch = 0;
+    }
+    h->rs_epoch = (h->rs_epoch + 1) & 0x3fffffffu;
+    if (h->rs_epoch == 0) {
+        AB_CUDA(h, cudaMemsetAsync(h->rs_status, 0, h->rs_status_len * sizeof(unsigned long long), h->stream));
+        h->rs_epoch = 1;
+    }
+    a.epoch = h->rs_epoch;
+    if (want_agg) AB_TRY(ensure_agg(h));
+    const bool extra = h->fields.size() > 2u;
+    {
+        AB_LAUNCH(h, "k_resort");
+        k_resort<T, D><<<a.ntiles, RS_THREADS, 0, h->stream>>>(
+            sp, a, h->cell_start, h->newkey, h->id[cur], (const T*)src_pos, (const T*)src_vel, h->cap, (int)h->n,
+            (T*)h->fields[0].buf[nxt], (T*)h->fields[1].buf[nxt], h->id[nxt], h->key[nxt], h->cell_start_alt,
+            extra ? h->perm : nullptr, (T*)h->cell_agg, (int64_t)h->ncells, h->idtmp, (int32_t*)h->rank, h->rs_status,
+            h->scan_ticket, h->d_err);
+    }
+    std::swap(h->cell_start, h->cell_start_alt);
+    AB_TRY(ab_permute_extra_fields(h));
+    h->cur = nxt;
+    h->slot_map_valid = false;
+    h->index_valid = true;
+    h->agg_valid = want_agg;
+    h->pairs_n = -1;
+    return AB_OK;
+}
+
+// Re-sorts from (src_pos, src_vel, h->newkey) — all in the CURRENT slot order —
+// into the other buffer.  Requires that no agent moved further than one
+// reference cell (checked on the device: AB_EF_OVERFLOW otherwise).
+int ab_resort_tiled(ab_handle* h, const void* src_pos, const void* src_vel, bool want_agg) {
+    if (h->dtype == AB_F64) return h->D == 2 ? resort_t<double, 2>(h, src_pos, src_vel, want_agg) : resort_t<double, 3>(h, src_pos, src_vel, want_agg);
+    return h->D == 2 ? resort_t<float, 2>(h, src_pos, src_vel, want_agg) : resort_t<float, 3>(h, src_pos, src_vel, want_agg);
+}
+
+template <class T, int D>
+static int agg_t(ab_handle* h) {
+    AB_LAUNCH(h, "k_cell_agg");
+    const uint32_t nc = (uint32_t)h->ncells;
+    k_cell_agg<T, D><<<ab_blocks((int64_t)nc * 8, 256), 256, 0, h->stream>>>(
+        make_space<T, D>(h), h->cell_start, (const T*)h->fields[0].buf[h->cur], (const T*)h->fields[1].buf[h->cur], h->cap, nc,
+        (T*)h->cell_agg, (int64_t)h->ncells);
+    return AB_OK;
+}
+
+int ab_ensure_agg(ab_handle* h) {
+    AB_TRY(ab_ensure_index(h));
+    AB_TRY(ensure_agg(h));
+    if (h->agg_valid) return AB_OK;
+    int rc;
+    if (h->dtype == AB_F64) rc = h->D == 2 ? agg_t<double, 2>(h) : agg_t<double, 3>(h);
+    else rc = h->D == 2 ? agg_t<float, 2>(h) : agg_t<float, 3>(h);
+    AB_TRY(rc);
+    h->agg_valid = true;
+    return AB_OK;
+}

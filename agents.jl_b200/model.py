@@ -253,6 +253,10 @@ class StandardABM:
     def vel(self):
         return self.column("vel")
 
+    def set_refinement(self, K):
+        """Device-grid refinement (1 or 2 sub-cells per reference cell and dimension); results do not depend on it."""
+        self._ck(self.lib.ab_set_refinement(self.h, int(K)))
+
     def cells(self):
         """pos2cell of every agent, 1-based (continuous.jl:112-113)."""
         n = self.nagents()

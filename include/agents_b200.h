@@ -126,6 +126,10 @@ int ab_download(ab_handle* h, int field, void* host, int64_t n);        /* id or
  * positions changed.  Fails with AB_ERR_OUTSIDE / AB_ERR_NUMERIC / AB_ERR_OCCUPIED
  * exactly where the reference would throw. */
 int ab_build_index(ab_handle* h);
+/* Device-grid refinement: K = 1 or 2 sub-cells per reference cell and dimension
+ * (default 1; the fused steps pick it themselves).  A pure layout choice —
+ * neighbour sets and cells are defined on the reference cells either way. */
+int ab_set_refinement(ab_handle* h, int K);
 /* pos2cell for every agent, id order, n x D int32, 1-based (continuous.jl:112-113) */
 int ab_cells(ab_handle* h, int32_t* out_cells, int64_t n);
 

@@ -359,3 +359,117 @@ def test_flock_zero_velocity_is_an_error_not_a_fix():
     m.add_agents([(50.0, 50.0)], [(0.0, 0.0)])
     with pytest.raises(ab.AgentsError):
         m.step(1)
+
+
+# ---------------------------------------------------------------------------
+# tiled flock path (aggregated approximate sweep / block exact sweep + tiled re-sort)
+# ---------------------------------------------------------------------------
+TILED_CASES = [
+    ((400.0, 400.0), 5.0, True, 40000),
+    ((400.0, 300.0), 5.0, False, 30000),
+    ((300.0, 400.0), 5.0, (True, False), 30000),
+    ((60.0, 60.0, 60.0), 5.0, True, 8000),
+    ((60.0, 45.0, 50.0), 5.0, (True, False, True), 6000),
+    ((400.0, 400.0), 8.0, True, 20000),             # visual_distance 5 < spacing: grid_r 1 and 2 both occur
+]
+
+
+@pytest.mark.parametrize("extent,spacing,periodic,n", TILED_CASES)
+@pytest.mark.parametrize("search", ["approximate", "exact"])
+def test_flock_tiled_parity(extent, spacing, periodic, n, search):
+    o, m, _, _ = make_pair(extent, spacing, periodic, n, seed=11)
+    m.model_step = ab.FlockRule(search=search, kernel="tiled", **FLOCK)
+    for _ in range(3):
+        cnt = o.flock_step_sync(FLOCK, nsteps=1, search=search, return_counts=True)
+        m.step(1)
+        assert np.array_equal(m.last_neighbor_counts(), cnt)
+        p, v = o.state()
+        assert periodic_rel_err(m.pos, p, extent) <= ONE_STEP_TOL_F64
+        assert rel_err(m.vel, v) <= ONE_STEP_TOL_F64
+        assert np.array_equal(m.cells(), o.pos2cell(p))
+        m.add_agents(p, v)
+
+
+@pytest.mark.parametrize("search", ["approximate", "exact"])
+def test_flock_tiled_trajectory_and_index_consistency(search):
+    """20 chained tiled steps (no re-synchronisation): the index the tiled re-sort leaves behind must
+    answer neighbour queries exactly like a fresh build, and the trajectory must follow the oracle."""
+    extent = (300.0, 300.0)
+    o, m, _, _ = make_pair(extent, 5.0, True, 25000, seed=3)
+    m.model_step = ab.FlockRule(search=search, kernel="tiled", **FLOCK)
+    flips = 0
+    for _ in range(20):
+        cnt = o.flock_step_sync(FLOCK, search=search, return_counts=True)
+        m.step(1)
+        flips += int(np.sum(m.last_neighbor_counts() != cnt))
+    p, v = o.state()
+    assert flips == 0
+    assert periodic_rel_err(m.pos, p, extent) <= 1e-10
+    q = np.arange(1, 2001)
+    off, ids = m.nearby_ids_batch(ids=q, r=5.0, search="exact")
+    got = csr_sets(off, ids)
+    m2 = ab.StandardABM(ab.ContinuousSpace(extent, spacing=5.0))
+    m2.add_agents(m.pos, m.vel)
+    off2, ids2 = m2.nearby_ids_batch(ids=q, r=5.0, search="exact")
+    want = csr_sets(off2, ids2)
+    assert all(np.array_equal(a, b) for a, b in zip(got, want))
+
+
+def test_flock_tiled_equals_generic_and_is_reproducible():
+    extent = (400.0, 400.0)
+    pos, vel = flock_init(40000, extent, 5)
+    out = []
+    for kernel in ("tiled", "tiled", "generic"):
+        m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=5.0), model_step=ab.FlockRule(kernel=kernel, **FLOCK))
+        m.add_agents(pos, vel)
+        m.step(5)
+        out.append((m.pos, m.vel, m.last_neighbor_counts()))
+        m.close()
+    assert np.array_equal(out[0][0], out[1][0]) and np.array_equal(out[0][1], out[1][1])     # bitwise reproducible
+    assert np.array_equal(out[0][2], out[2][2])
+    assert periodic_rel_err(out[0][0], out[2][0], extent) <= 1e-12
+
+
+@pytest.mark.parametrize("search", ["approximate", "exact"])
+def test_flock_tiled_crowded_and_sparse_states(search):
+    """States the tiles do not fit (crowded cells, nearly empty rows) take the in-kernel fallbacks."""
+    extent = (200.0, 200.0)
+    rng = np.random.default_rng(5)
+    n = 12000
+    pos = rng.uniform(0, 200.0, size=(n, 2))
+    pos[:6000] = 100.0 + rng.normal(0, 3.0, size=(6000, 2))          # ~6000 birds in a few cells
+    pos[6000:6050, 1] = 37.5                                          # and a thin line
+    pos = np.mod(pos, 200.0)
+    vel = rng.uniform(-1, 1, size=(n, 2))
+    o = ContinuousOracle(extent, spacing=5.0)
+    o.add_agents(pos, vel)
+    m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=5.0), model_step=ab.FlockRule(search=search, kernel="tiled", **FLOCK))
+    m.add_agents(pos, vel)
+    for _ in range(2):
+        cnt = o.flock_step_sync(FLOCK, search=search, return_counts=True)
+        m.step(1)
+        assert np.array_equal(m.last_neighbor_counts(), cnt)
+        assert periodic_rel_err(m.pos, o.state()[0], extent) <= 1e-12
+    # sparse: 300 birds in 160x160 cells
+    extent = (800.0, 800.0)
+    o2, m2, _, _ = make_pair(extent, 5.0, True, 300, seed=8)
+    m2.model_step = ab.FlockRule(search=search, kernel="tiled", **FLOCK)
+    cnt = o2.flock_step_sync(FLOCK, search=search, return_counts=True)
+    m2.step(1)
+    assert np.array_equal(m2.last_neighbor_counts(), cnt)
+    assert periodic_rel_err(m2.pos, o2.state()[0], extent) <= ONE_STEP_TOL_F64
+
+
+def test_refinement_does_not_change_queries():
+    extent = (100.0, 100.0)
+    o, m, pos, _ = make_pair(extent, 5.0, True, 3000, seed=12)
+    m.set_refinement(2)
+    q = np.arange(1, 501)
+    for search in ("approximate", "exact"):
+        off, ids = m.nearby_ids_batch(ids=q, r=6.5, search=search)
+        for i, got in zip(q, csr_sets(off, ids)):
+            assert np.array_equal(got, np.sort(o.nearby_ids_agent(int(i), 6.5, search)))
+    got = m.interacting_pairs(3.0)
+    want = o.interacting_pairs_all(3.0)
+    assert np.array_equal(np.unique(got, axis=0), np.unique(want, axis=0))
+    assert np.array_equal(m.cells(), o.pos2cell(pos))
