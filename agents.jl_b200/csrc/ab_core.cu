@@ -392,6 +392,7 @@ int ab_set_refine(ab_handle* h, int K) {
     if ((h->ncells << ksh) > h->nfine_cap) return ab_fail(h, AB_ERR_INVALID, "grid too large to refine");
     if (K == h->K) return AB_OK;
     h->K = K;
+    h->kb = K == 2 ? 1 : 0;
     h->ksh = ksh;
     h->nfine = h->ncells << ksh;
     h->index_valid = false;
@@ -528,7 +529,7 @@ int ab_destroy(ab_handle* h) {
     ab_comm_free(h);
     free_population(h);
     void* ptrs[] = {h->cell_count, h->cell_start, h->scan_status, h->scan_ticket, h->d_err, h->scratch, h->scratch2,
-                    h->cell_agg, h->pairs_offsets, h->grid_ids, h->cell_start_alt, h->rs_status};
+                    h->cell_agg, h->cell_M, h->pairs_offsets, h->grid_ids, h->cell_start_alt, h->rs_status};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (h->h_err) cudaFreeHost(h->h_err);
     if (h->ev0) cudaEventDestroy(h->ev0);

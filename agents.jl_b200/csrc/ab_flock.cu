@@ -12,8 +12,8 @@
 //                    grids, clipped offset tables, per-agent parameters).  One
 //                    thread per bird, walks the reference's cell offsets as runs
 //                    of the sorted arrays through L1/L2.
-//   k_flock_tiled    (ab_flock_tiled.cuh) shared-memory tiles for large 2-D/3-D
-//                    spaces with uniform parameters — the throughput path.
+//   k_flock_fine     (ab_flock_fine.cuh) fine-grid sweep for large 2-D/3-D spaces
+//                    with uniform parameters — the throughput path.
 #include <cmath>
 #include <limits>
 
@@ -89,7 +89,7 @@ __device__ __noinline__ void flock_accumulate_generic(const SpaceDev<T, D>& sp, 
         }
     }
     int N = 0;
-    for_each_run<D>(sp.dims, sp.periodic, AB_METRIC_EUCLIDEAN, c, gr, cell_start, sp.ksh, false,
+    for_each_run<D>(sp.dims, sp.periodic, AB_METRIC_EUCLIDEAN, c, gr, cell_start, sp.kb, false,
                     [&](uint32_t b, uint32_t e, int wrap) {
         const int full = (wrap | slowmask) & permask;
         for (uint32_t j = b; j < e; ++j) {
@@ -141,7 +141,7 @@ k_flock_generic(SpaceDev<T, D> sp, FlockU<T> uni, const T* __restrict__ per_agen
     int c[D];
 #pragma unroll
     for (int d = 0; d < D; ++d) { p[d] = pos[(size_t)d * cap + s]; v[d] = vel[(size_t)d * cap + s]; }
-    unlin_cell<D>(sp.dims, key[s] >> sp.ksh, c);
+    key_to_cell<T, D>(sp, key[s], c);
     const int gr = grid_radius<T, D>(sp, p, c, fp.visual_distance);
     T cohere[D], separate[D], match[D];
 #pragma unroll
@@ -161,7 +161,7 @@ k_flock_generic(SpaceDev<T, D> sp, FlockU<T> uni, const T* __restrict__ per_agen
     if (ncount) ncount[ids[s]] = N;     // diagnostic, last step of a call only
 }
 
-#include "ab_flock_tiled.cuh"
+#include "ab_flock_fine.cuh"
 
 // Bulk Euler move / walk for a set of slots (NULL = all):
 // move_agent!(agent, model, dt) continuous.jl:186-194 and walk! walk.jl:58-66.
@@ -247,21 +247,28 @@ static int move_common(ab_handle* h, double dt, const void* directions, const in
     return e;
 }
 
-template <class T, int D, bool EXACT>
-static int launch_tiled(ab_handle* h, const SpaceDev<T, D>& sp, const FlockU<T>& u, int32_t* ncount) {
-    using SM = TiledSmem<T, D, EXACT>;
-    constexpr int SWT = TiledCfg<D>::SWT;
-    static bool attr_done = false;
-    if (!attr_done) {
-        AB_CUDA(h, cudaFuncSetAttribute(k_flock_tiled<T, D, EXACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SM::TOTAL));
-        attr_done = true;
+template <class T, int D>
+static int launch_cell_M(ab_handle* h, const SpaceDev<T, D>& sp) {
+    const size_t need = (size_t)2 * FineCfg<D>::NC * h->ncells * sizeof(T);
+    if (h->cell_M_bytes < need) {
+        if (h->cell_M) { AB_CUDA(h, cudaStreamSynchronize(h->stream)); AB_CUDA(h, cudaFree(h->cell_M)); h->cell_M = nullptr; }
+        AB_CUDA(h, cudaMalloc(&h->cell_M, need));
+        h->cell_M_bytes = need;
     }
+    AB_LAUNCH(h, "k_cell_M");
+    k_cell_M<T, D><<<ab_blocks(h->ncells, 128), 128, 0, h->stream>>>(sp, (const T*)h->cell_agg, (int64_t)h->ncells, (T*)h->cell_M);
+    return AB_OK;
+}
+
+template <class T, int D, bool EXACT>
+static int launch_fine(ab_handle* h, const SpaceDev<T, D>& sp, const FlockU<T>& u, int32_t* ncount) {
     const int cur = h->cur;
     const int n = (int)h->n;
-    AB_LAUNCH(h, EXACT ? "k_flock_tiled_exact" : "k_flock_tiled");
-    k_flock_tiled<T, D, EXACT><<<ab_blocks(n, SWT), SWT, SM::TOTAL, h->stream>>>(
+    const int TB = 128;
+    AB_LAUNCH(h, EXACT ? "k_flock_fine_exact" : "k_flock_fine");
+    k_flock_fine<T, D, EXACT><<<ab_blocks(n, TB), TB, 0, h->stream>>>(
         sp, u, (const T*)h->fields[0].buf[cur], (const T*)h->fields[1].buf[cur], h->key[cur], h->cell_start,
-        (const T*)h->cell_agg, (int64_t)h->ncells, h->cap, n, (T*)h->tmp_pos, (T*)h->tmp_vel, h->newkey, h->id[cur],
+        (const T*)h->cell_M, (int64_t)h->ncells, h->cap, n, (T*)h->tmp_pos, (T*)h->tmp_vel, h->newkey, h->id[cur],
         ncount, h->d_err);
     return AB_OK;
 }
@@ -281,24 +288,28 @@ static int flock_steps_t(ab_handle* h, const ab_flock_params* p, int64_t nsteps)
             return ab_fail(h, AB_ERR_INVALID, "per_agent_field must be a 6-component column of the space's float type");
     }
     // kernel choice
-    bool tiled = false;
-    TiledPlan plan;
-    if (p->kernel != 1) tiled = plan_tiled<T, D>(h, p, exact, &plan);
-    if (p->kernel == 2 && !tiled) return ab_fail(h, AB_ERR_INVALID, "tiled flock kernel not applicable to this configuration");
-    if (tiled) AB_TRY(ab_set_refine(h, plan.K));
+    bool fine = false;
+    FinePlan plan;
+    if (p->kernel != 1) fine = plan_fine<T, D>(h, p, exact, &plan);
+    if (p->kernel == 2 && !fine) return ab_fail(h, AB_ERR_INVALID, "fine-grid flock kernel not applicable to this configuration");
+    if (fine) AB_TRY(ab_set_refine(h, plan.K));
     AB_TRY(ab_ensure_index(h));
-    if (tiled && !exact) AB_TRY(ab_ensure_agg(h));
     SpaceDev<T, D> sp = make_space<T, D>(h);
+    if (fine && !exact) {
+        AB_TRY(ab_ensure_agg(h));
+        AB_TRY((launch_cell_M<T, D>(h, sp)));
+    }
     AB_CUDA(h, cudaEventRecord(h->ev0, h->stream));
     for (int64_t st = 0; st < nsteps; ++st) {
         const int cur = h->cur;
         const T* pos = (const T*)h->fields[0].buf[cur];
         const T* vel = (const T*)h->fields[1].buf[cur];
         int32_t* ncount = (st == nsteps - 1) ? h->ncount : nullptr;   // neighbour counts by id (diagnostic)
-        if (tiled) {
-            if (exact) AB_TRY((launch_tiled<T, D, true>(h, sp, u, ncount)));
-            else AB_TRY((launch_tiled<T, D, false>(h, sp, u, ncount)));
+        if (fine) {
+            if (exact) AB_TRY((launch_fine<T, D, true>(h, sp, u, ncount)));
+            else AB_TRY((launch_fine<T, D, false>(h, sp, u, ncount)));
             AB_TRY(ab_resort_tiled(h, h->tmp_pos, h->tmp_vel, !exact));
+            if (!exact) AB_TRY((launch_cell_M<T, D>(h, sp)));
         } else {
             const T* pa = pa_field >= 0 ? (const T*)h->fields[pa_field].buf[cur] : nullptr;
             {

@@ -1,0 +1,264 @@
+// ab_flock_fine.cuh — the throughput path of the fused flock step
+// (examples/flock.jl:79-108) for large spaces with uniform rule parameters.
+//
+// One thread per bird, 32 consecutive slots of the cell-sorted state per warp.
+// The state is sorted by FINE cell in fine-row-major order (ab_internal.cuh), so
+// the short-range part of the rule reads a few contiguous slot runs straight
+// from the sorted arrays (L1/L2) — no restaging, no shared memory, no barriers —
+// and the lanes of a warp, being neighbours in space, walk (nearly) the same
+// runs: in a crowded region every lane of a warp sits in the same fine cell and
+// every candidate load is a single broadcast transaction.
+//
+//   `:approximate` search (the reference's default).  nearby_ids returns EVERY
+//      agent of the cells of the offset table of radius grid_r around the
+//      bird's cell (continuous.jl:221-230), so cohere = Σ heading and
+//      match = Σ vel of flock.jl:88-91 are sums over whole cells:
+//         cohere_i = M.C - M.N * (pos_i - centre_i),  match_i = M.V - vel_i,
+//         N_i = M.N - 1,
+//      with M = per-reference-cell sums over the offset tables of radius 1 and 2
+//      (k_cell_M, built from the aggregates the re-sort leaves behind).  Only
+//      `separate` (flock.jl:93-96, pairs closer than `separation`) needs a pair
+//      sweep, over the fine cells fx-1..fx+1 of the fine rows fy-1..fy+1
+//      (fine cell size >= separation).
+//   `:exact` search.  The pair sweep covers the cells of the bird's offset
+//      table (grid_r in {1,2}), clipped to the fine cells within K of the
+//      bird's (fine cell size * K = spacing >= visual_distance), and applies
+//      the reference's distance filter (continuous.jl:232-238).
+// Birds whose grid_r is not 1 or 2 take the reference walk (flock_accumulate_generic),
+// so the kernel is correct for every state; only its speed depends on the state.
+#pragma once
+
+template <int D> struct FineCfg { static constexpr int NC = 1 + 2 * D; };   // count, Σ(pos-centre)[D], Σvel[D]
+
+// row offsets (dy, dz) with dy² + dz² ≤ 4 (3-D) — summation order of k_cell_M
+__constant__ int8_t c_ro3[13][2] = {{0, -2}, {-1, -1}, {0, -1}, {1, -1}, {-2, 0}, {-1, 0}, {0, 0},
+                                    {1, 0},  {2, 0},   {-1, 1}, {0, 1},  {1, 1},  {0, 2}};
+template <int D> __device__ __forceinline__ void ro_offset(int ro, int* dy, int* dz) {
+    if (D == 2) { *dy = ro - 2; *dz = 0; }
+    else { *dy = c_ro3[ro][0]; *dz = c_ro3[ro][1]; }
+}
+
+struct FinePlan {
+    int K;
+};
+
+// wrap (periodic) or invalidate (-1) a cell coordinate
+__device__ __forceinline__ int wrap_coord(int c, int n, bool periodic) {
+    if (c >= 0 && c < n) return c;
+    if (!periodic) return -1;
+    return c < 0 ? c + n : c - n;
+}
+
+// M[g-1][c][cell] = Σ over the offset table of radius g (Σβ² ≤ g², grid_general.jl:138-151) of the
+// per-cell aggregates, with neighbour positions re-expressed relative to THIS cell's centre
+// (+ β·spacing per neighbour agent).  aggp holds one partial per fine row of a reference cell
+// (written by k_resort / k_cell_agg); they are added in fixed order.
+template <class T, int D>
+__global__ void __launch_bounds__(128)
+k_cell_M(SpaceDev<T, D> sp, const T* __restrict__ aggp, int64_t ncells, T* __restrict__ M) {
+    constexpr int NC = FineCfg<D>::NC;
+    constexpr int NRO = D == 2 ? 5 : 13;
+    const int64_t cell = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (cell >= ncells) return;
+    int c[D];
+    unlin_cell<D>(sp.dims, (uint32_t)cell, c);
+    const int nfr = D == 2 ? sp.K : sp.K * sp.K;
+    T acc1[NC], acc2[NC];
+#pragma unroll
+    for (int i = 0; i < NC; ++i) acc1[i] = acc2[i] = T(0);
+    for (int ro = 0; ro < NRO; ++ro) {
+        int dy, dz;
+        ro_offset<D>(ro, &dy, &dz);
+        const int rem2 = 4 - dy * dy - dz * dz;
+        const int hw2 = rem2 >= 4 ? 2 : (rem2 >= 1 ? 1 : 0);
+        const int rem1 = 1 - dy * dy - dz * dz;
+        const int y = wrap_coord(c[1] + dy, sp.dims[1], sp.periodic[1]);
+        const int z = D == 3 ? wrap_coord(c[2] + dz, sp.dims[2], sp.periodic[2]) : 0;
+        if (y < 0 || z < 0) continue;
+        const uint32_t rb = (D == 3 ? ((uint32_t)z * sp.dims[1] + y) : (uint32_t)y) * (uint32_t)sp.dims[0];
+        for (int bx = -hw2; bx <= hw2; ++bx) {
+            const int x = wrap_coord(c[0] + bx, sp.dims[0], sp.periodic[0]);
+            if (x < 0) continue;
+            const uint32_t nb = rb + (uint32_t)x;
+            T a[NC];
+#pragma unroll
+            for (int i = 0; i < NC; ++i) {
+                T v = aggp[(size_t)i * ncells + nb];
+                for (int t = 1; t < nfr; ++t) v += aggp[((size_t)t * NC + i) * ncells + nb];
+                a[i] = v;
+            }
+            // neighbour sums relative to this cell's centre
+#pragma unroll
+            for (int d = 0; d < D; ++d) {
+                const int beta = d == 0 ? bx : (d == 1 ? dy : dz);
+                a[1 + d] = a[1 + d] + a[0] * ((T)beta * sp.spacing);
+            }
+            const bool in1 = rem1 >= 0 && (bx == 0 || (rem1 >= 1 && (bx == 1 || bx == -1)));
+#pragma unroll
+            for (int i = 0; i < NC; ++i) {
+                acc2[i] += a[i];
+                if (in1) acc1[i] += a[i];
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < NC; ++i) {
+        M[(size_t)i * ncells + cell] = acc1[i];
+        M[((size_t)NC + i) * ncells + cell] = acc2[i];
+    }
+}
+
+template <class T, int D, bool EXACT>
+__global__ void __launch_bounds__(128)
+k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T* __restrict__ vel,
+             const uint32_t* __restrict__ key, const uint32_t* __restrict__ cs, const T* __restrict__ M,
+             int64_t ncells, int64_t cap, int n, T* __restrict__ npos, T* __restrict__ nvel,
+             uint32_t* __restrict__ newkey, const int32_t* __restrict__ ids, int32_t* __restrict__ ncount,
+             int* __restrict__ err) {
+    constexpr int NC = FineCfg<D>::NC;
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    const int K = sp.K, kb = sp.kb;
+    T p[D], v[D];
+    int f[D], c[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d) { p[d] = pos[(size_t)d * cap + s]; v[d] = vel[(size_t)d * cap + s]; }
+    const uint32_t k = key[s];
+    key_to_fine<T, D>(sp, k, f);
+#pragma unroll
+    for (int d = 0; d < D; ++d) c[d] = f[d] >> kb;
+    const int gr = grid_radius<T, D>(sp, p, c, fp.visual_distance);
+    const T sep2 = fp.separation * fp.separation;
+    T cohere[D], separate[D], match[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d) cohere[d] = separate[d] = match[d] = T(0);
+    int N = 0;
+    bool fast = gr == 1 || gr == 2;
+    T q[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d) q[d] = p[d] - sp.spacing * ((T)(c[d] + 1) - T(0.5));
+    if (EXACT && fast) {
+        // birds within tau of a fine-cell boundary could see (in floating point) a neighbour that the
+        // clipped sweep below does not visit: they take the reference walk.
+        const T eps = sizeof(T) == 8 ? T(1.4210854715202004e-14) : T(7.62939453125e-06);     // 2^-46, 2^-17
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            const T tau = sp.extent[d] * eps;
+            const T a = fabs(q[d]);
+            if (fabs(a - sp.spacing * T(0.5)) < tau || (K == 2 && a < tau)) fast = false;
+        }
+    }
+    if (fast) {
+        if (!EXACT) {
+            const uint32_t refc = lin_cell<D>(sp.dims, c);
+            const T* Mg = M + (size_t)(gr - 1) * NC * ncells + refc;
+            const T Nt = Mg[0];
+            N = (int)Nt - 1;
+#pragma unroll
+            for (int d = 0; d < D; ++d) {
+                cohere[d] = Mg[(size_t)(1 + d) * ncells] - Nt * q[d];
+                match[d] = Mg[(size_t)(1 + D + d) * ncells] - v[d];
+            }
+        }
+        const T thr = fp.thr;
+        const int R = EXACT ? K : 1;                   // fine-cell reach of the sweep
+        const int fd0 = sp.dims[0] << kb, fd1 = sp.dims[1] << kb, fd2 = D == 3 ? (sp.dims[2] << kb) : 1;
+        auto sweep = [&](uint32_t jb, uint32_t je, int wrap) {
+#pragma unroll 2
+            for (uint32_t j = jb; j < je; ++j) {
+                T h[D];
+                T d2 = 0;
+#pragma unroll
+                for (int d = 0; d < D; ++d) {
+                    T direct = pos[(size_t)d * cap + j] - p[d];
+                    if (wrap & (1 << d)) direct = min_image(direct, sp.extent[d]);     // utilities.jl:185-193
+                    h[d] = direct;
+                    const T sq = direct * direct;
+                    d2 = (d == 0) ? sq : d2 + sq;
+                }
+                if (EXACT) {
+                    if ((int)j == s || !(d2 <= thr)) continue;                            // continuous.jl:237-238
+                    ++N;
+#pragma unroll
+                    for (int d = 0; d < D; ++d) { cohere[d] += h[d]; match[d] += vel[(size_t)d * cap + j]; }
+                }
+                // the bird itself (h == 0) passes this test and contributes exactly nothing
+                if (d2 < sep2) {                                                         // flock.jl:93
+#pragma unroll
+                    for (int d = 0; d < D; ++d) separate[d] -= h[d];
+                }
+            }
+        };
+        for (int rz = (D == 3 ? -R : 0); rz <= (D == 3 ? R : 0); ++rz) {
+            int fz = 0, wz = 0, dz = 0;
+            if (D == 3) {
+                fz = f[2] + rz;
+                dz = (fz >> kb) - c[2];            // arithmetic shift: floor for fz = -1, -2
+                if (fz < 0 || fz >= fd2) {
+                    if (!sp.periodic[2]) continue;
+                    fz = fz < 0 ? fz + fd2 : fz - fd2;
+                    wz = 4;
+                }
+            }
+            for (int ry = -R; ry <= R; ++ry) {
+                int fy = f[1] + ry;
+                const int dy = (fy >> kb) - c[1];
+                int ulo = f[0] - R, uhi = f[0] + R;          // inclusive fine cells, unwrapped
+                if (EXACT) {
+                    // only cells of the bird's offset table (Σβ² ≤ grid_r²)
+                    const int rem2 = gr * gr - dy * dy - dz * dz;
+                    if (rem2 < 0) continue;
+                    const int hw = rem2 >= 4 ? 2 : (rem2 >= 1 ? 1 : 0);
+                    ulo = max(ulo, (c[0] - hw) * K);
+                    uhi = min(uhi, (c[0] + hw + 1) * K - 1);
+                }
+                int wy = 0;
+                if (fy < 0 || fy >= fd1) {
+                    if (!sp.periodic[1]) continue;
+                    fy = fy < 0 ? fy + fd1 : fy - fd1;
+                    wy = 2;
+                }
+                const uint32_t rb = (D == 3 ? ((uint32_t)fz * (uint32_t)fd1 + (uint32_t)fy) : (uint32_t)fy) * (uint32_t)fd0;
+                const int wyz = wy | wz;
+                if (ulo < 0) {
+                    if (sp.periodic[0]) sweep(cs[rb + (uint32_t)(ulo + fd0)], cs[rb + (uint32_t)fd0], wyz | 1);
+                    ulo = 0;
+                }
+                int uhi_main = uhi;
+                if (uhi >= fd0) uhi_main = fd0 - 1;
+                if (ulo <= uhi_main) sweep(cs[rb + (uint32_t)ulo], cs[rb + (uint32_t)uhi_main + 1], wyz);
+                if (uhi >= fd0 && sp.periodic[0]) sweep(cs[rb], cs[rb + (uint32_t)(uhi - fd0) + 1], wyz | 1);
+            }
+        }
+    } else {
+        flock_accumulate_generic<T, D, EXACT>(sp, fp, s, p, c, gr, pos, vel, cs, cap, &N, cohere, separate, match);
+    }
+    T np_[D], nv[D];
+    flock_epilogue<T, D>(sp, p, v, cohere, separate, match, N, fp, np_, nv, err);
+    int nc[D];
+    if (!pos2cell0<T, D>(sp, np_, nc)) atomicOr(err, AB_EF_NUMERIC);
+    const uint32_t nk = device_key<T, D>(sp, np_, nc);
+#pragma unroll
+    for (int d = 0; d < D; ++d) { npos[(size_t)d * cap + s] = np_[d]; nvel[(size_t)d * cap + s] = nv[d]; }
+    newkey[s] = nk;
+    if (ncount) ncount[ids[s]] = N;
+}
+
+// Can the fine-grid step (sweep + tiled re-sort) run this configuration?
+template <class T, int D>
+static bool plan_fine(ab_handle* h, const ab_flock_params* p, bool exact, FinePlan* plan) {
+    if (h->desc.kind != AB_SPACE_CONTINUOUS || p->per_agent_field >= 0 || h->n < 1) return false;
+    const double s = (double)(T)h->desc.spacing, r = p->visual_distance, sep = p->separation, margin = 1.0 + 1e-9;
+    for (int d = 0; d < D; ++d) if (h->dims[d] < 6) return false;     // radius-2 offset table unclipped (grid_general.jl:49)
+    if (!(r > 0) || !(sep >= 0) || !(p->speed >= 0)) return false;
+    if (!((r + s * sqrt((double)D) * 0.5) * margin <= 2.0 * s)) return false;   // grid_r ∈ {1, 2} for every bird
+    if (exact && !(r <= s)) return false;                              // ±1 reference cell covers the radius
+    int K = 0;
+    // fine cell >= separation (±1 fine cell covers it) and the per-step displacement stays below one fine cell
+    if (sep * margin <= s * 0.5 && p->speed * margin < s * 0.5 && (h->ncells << D) <= h->nfine_cap) K = 2;
+    else if (sep * margin <= s && p->speed * margin < s) K = 1;
+    if (!K) return false;
+    if (!ab_resort_applicable(h)) return false;
+    plan->K = K;
+    return true;
+}

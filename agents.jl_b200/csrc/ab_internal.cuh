@@ -6,11 +6,19 @@
 //     holds the agent id[cur][s] (0-based).  The sorted order is persistent:
 //     a step writes the next state directly into the other buffer in the next
 //     step's sorted order, so there is no per-step gather/scatter by id.
-//   * cell_start[ncells+1]: first slot of each cell (column-major linear cell,
-//     like Julia's stored_ids[c...] — src/spaces/grid_multi.jl:73).  Within a
-//     cell, slots are ordered by id, so every floating-point sum over a
-//     cell's agents has one canonical order (bitwise reproducible runs).
-//   * key[cur][s]: linear cell of slot s.
+//   * device cells: every reference cell (pos2cell, continuous.jl:112-113) is
+//     split into K^D "fine" cells (K = 1 or 2 per dimension, split at the
+//     reference cell's centre), and the device key of an agent is the
+//     column-major linear index of its fine cell over the fine grid
+//     (dims[d]*K) — x fastest, like Julia's stored_ids[c...]
+//     (src/spaces/grid_multi.jl:73).  A run of fine cells of one fine row is a
+//     contiguous slot range, so both the reference's cell walks (K runs per
+//     reference cell row) and the short-range sweeps of the fused rules
+//     (fine rows fy-1..fy+1) read contiguous memory without restaging.
+//   * cell_start[nfine+1]: first slot of each fine cell.  Within a fine cell,
+//     slots are ordered by id, so every floating-point sum over a cell's
+//     agents has one canonical order (bitwise reproducible runs).
+//   * key[cur][s]: fine-cell key of slot s.
 // Compiled with --fmad=false: predicates that decide neighbour sets and cells
 // must round exactly like the reference (Julia never contracts a*b+c here);
 // fma() is used explicitly only where results are tolerance-checked.
@@ -55,7 +63,8 @@ struct ab_handle {
     int64_t n = 0, cap = 0;
     int64_t ncells = 1;                // reference cells (prod dims)
     int dims[3] = {1, 1, 1};
-    int K = 1;                         // refinement: each reference cell holds K^D device sub-cells
+    int K = 1;                         // refinement: each reference cell holds K^D device (fine) cells
+    int kb = 0;                        // log2(K)
     int ksh = 0;                       // log2(K^D)
     int64_t nfine = 1;                 // ncells << ksh : entries of cell_start - 1
     int64_t nfine_cap = 1;             // allocated (padded) length of cell_count
@@ -79,10 +88,14 @@ struct ab_handle {
     bool agg_valid = false;            // cell_agg matches the current sorted state
     int32_t* ncount = nullptr;         // neighbour count per slot of the last flock step
 
-    // per reference cell Σ(pos - centre), Σ vel of the sorted state (SoA: 2*D arrays
-    // of ncells T) — input of the aggregated approximate-search sweep (ab_flock.cu)
+    // per (fine row of a) reference cell: count, Σ(pos - centre), Σ vel of the sorted state
+    // (SoA: [part][1+2D][ncells] of T) — input of the aggregated approximate-search sweep (ab_flock.cu)
     void* cell_agg = nullptr;
     size_t cell_agg_bytes = 0;
+    // sums of those aggregates over the reference's offset tables of radius 1 and 2 (k_cell_M)
+    void* cell_M = nullptr;
+    size_t cell_M_bytes = 0;
+    int rs_target = 512;               // average agents per re-sort tile (tuning knob)
 
     // tiled re-sort look-back state (ab_resort.cu)
     unsigned long long* rs_status = nullptr;
@@ -186,8 +199,9 @@ template <class T, int D> struct SpaceDev {
     int dims[D];
     bool periodic[D];
     int metric;
-    int K;        // sub-cells per reference cell and dimension (1 or 2)
-    int ksh;      // log2(K^D): device key = (reference cell << ksh) | sub-cell
+    int K;        // fine cells per reference cell and dimension (1 or 2)
+    int kb;       // log2(K): fine coordinate = (reference coordinate << kb) | upper-half bit
+    int ksh;      // log2(K^D)
 };
 
 template <class T, int D> static inline SpaceDev<T, D> make_space(const ab_handle* h) {
@@ -202,6 +216,7 @@ template <class T, int D> static inline SpaceDev<T, D> make_space(const ab_handl
     s.spacing_d = (double)s.spacing;
     s.metric = h->desc.kind == AB_SPACE_CONTINUOUS ? AB_METRIC_EUCLIDEAN : h->desc.metric;
     s.K = h->K;
+    s.kb = h->kb;
     s.ksh = h->ksh;
     return s;
 }
@@ -267,21 +282,44 @@ template <int D> __device__ __forceinline__ void unlin_cell(const int* dims, uin
     c[D - 1] = (int)lin;
 }
 
-// Device cell key: reference cell (column-major, like stored_ids[c...]) in the
-// high bits, sub-cell in the low ksh bits.  Sub-cell bit d = position above the
-// reference cell's centre (cell_center, continuous.jl:116-117), so sub-cells
-// nest exactly inside the bit-exact reference cells.
+// Device cell key: column-major linear index of the agent's FINE cell over the
+// fine grid (dims << kb).  Fine coordinate = reference coordinate * K + (position
+// above the reference cell's centre — cell_center, continuous.jl:116-117), so
+// fine cells nest exactly inside the bit-exact reference cells.
 template <class T, int D>
 __device__ __forceinline__ uint32_t device_key(const SpaceDev<T, D>& sp, const T* p, const int* c) {
-    uint32_t k = lin_cell<D>(sp.dims, c) << sp.ksh;
-    if (sp.K == 2) {
+    uint32_t f[D];
 #pragma unroll
-        for (int d = 0; d < D; ++d) {
+    for (int d = 0; d < D; ++d) {
+        f[d] = (uint32_t)c[d] << sp.kb;
+        if (sp.K == 2) {
             T centre = sp.spacing * ((T)(c[d] + 1) - T(0.5));
-            k |= (p[d] > centre ? 1u : 0u) << d;
+            f[d] |= (p[d] > centre ? 1u : 0u);
         }
     }
-    return k;
+    uint32_t lin = f[D - 1];
+#pragma unroll
+    for (int d = D - 2; d >= 0; --d) lin = lin * ((uint32_t)sp.dims[d] << sp.kb) + f[d];
+    return lin;
+}
+// fine coordinates of a device key
+template <class T, int D>
+__device__ __forceinline__ void key_to_fine(const SpaceDev<T, D>& sp, uint32_t key, int* f) {
+#pragma unroll
+    for (int d = 0; d < D - 1; ++d) {
+        const uint32_t fd = (uint32_t)sp.dims[d] << sp.kb;
+        const uint32_t q = key / fd;
+        f[d] = (int)(key - q * fd);
+        key = q;
+    }
+    f[D - 1] = (int)key;
+}
+// reference cell (0-based coordinates) of a device key
+template <class T, int D>
+__device__ __forceinline__ void key_to_cell(const SpaceDev<T, D>& sp, uint32_t key, int* c) {
+    key_to_fine<T, D>(sp, key, c);
+#pragma unroll
+    for (int d = 0; d < D; ++d) c[d] >>= sp.kb;
 }
 
 // grid_r = ceil(Int, (r + δ)/spacing), δ = distance_from_cell_center —
@@ -353,31 +391,58 @@ __device__ __forceinline__ int isqrt_floor(long long v) {
     return (int)w;
 }
 
-// Emits the slot runs of the cells [a, b] (inclusive, unwrapped x cell
-// coordinates, at most dims0 of them) of one cell row, in ascending-offset
-// order, wrapping (periodic) or clipping (non-periodic) at the x boundary.
+// Fine rows of one reference cell row (cy, cz): their first fine-cell index.
+struct FineRows {
+    uint32_t base[4];
+    int n;
+};
+template <int D>
+__device__ __forceinline__ FineRows fine_rows(const int* dims, int kb, int cy, int cz) {
+    FineRows fr;
+    const int K = 1 << kb;
+    const uint32_t fd0 = (uint32_t)dims[0] << kb;
+    if (D == 2) {
+        fr.n = K;
+        for (int t = 0; t < K; ++t) fr.base[t] = (((uint32_t)cy << kb) + t) * fd0;
+    } else {
+        const uint32_t fd1 = (uint32_t)dims[1] << kb;
+        fr.n = K * K;
+        for (int tz = 0; tz < K; ++tz)
+            for (int ty = 0; ty < K; ++ty)
+                fr.base[tz * K + ty] = ((((uint32_t)cz << kb) + tz) * fd1 + (((uint32_t)cy << kb) + ty)) * fd0;
+    }
+    return fr;
+}
+
+// Emits the slot runs of the reference cells [a, b] (inclusive, unwrapped x cell
+// coordinates, at most dims0 of them) of one reference cell row — one run per
+// fine row — in ascending-offset order, wrapping (periodic) or clipping
+// (non-periodic) at the x boundary.
 template <class F>
 __device__ __forceinline__ void emit_xrange(int dims0, bool periodic0, const uint32_t* __restrict__ cell_start_,
-                                            int ksh, uint32_t rowbase, int a, int b, int wrap, F&& f) {
-    auto CS = [&](uint32_t refcell) { return cell_start_[(size_t)refcell << ksh]; };
+                                            int kb, const FineRows& fr, int a, int b, int wrap, F&& f) {
+    auto R = [&](int xa, int xe, int wr) {      // reference cells [xa, xe) of this row
+        for (int t = 0; t < fr.n; ++t)
+            f(cell_start_[(size_t)fr.base[t] + ((uint32_t)xa << kb)], cell_start_[(size_t)fr.base[t] + ((uint32_t)xe << kb)], wr);
+    };
     if (a > b) return;
     if (!periodic0) {
         if (a < 0) a = 0;
         if (b >= dims0) b = dims0 - 1;
-        if (a <= b) f(CS(rowbase + a), CS(rowbase + b + 1), wrap);
+        if (a <= b) R(a, b + 1, wrap);
         return;
     }
     if (a < 0) {
         int e = b < -1 ? b : -1;
-        f(CS(rowbase + a + dims0), CS(rowbase + e + dims0 + 1), wrap | 1);
+        R(a + dims0, e + dims0 + 1, wrap | 1);
         a = 0;
     }
     if (a <= b) {
         int e = b < dims0 - 1 ? b : dims0 - 1;
-        if (a <= e) f(CS(rowbase + a), CS(rowbase + e + 1), wrap);
+        if (a <= e) R(a, e + 1, wrap);
         if (b >= dims0) {
             int s2 = a > dims0 ? a : dims0;
-            f(CS(rowbase + s2 - dims0), CS(rowbase + b - dims0 + 1), wrap | 1);
+            R(s2 - dims0, b - dims0 + 1, wrap | 1);
         }
     }
 }
@@ -392,12 +457,14 @@ __device__ __forceinline__ void emit_xrange(int dims0, bool periodic0, const uin
 // zero offset (offsets_within_radius_no_0, grid_general.jl:165-179).
 template <int D, class F>
 __device__ __forceinline__ void for_each_run(const int* dims, const bool* periodic, int metric, const int* c0,
-                                             int r0, const uint32_t* __restrict__ cell_start, int ksh,
+                                             int r0, const uint32_t* __restrict__ cell_start, int kb,
                                              bool skip_zero, F&& f) {
     if (r0 < 0) {   // empty product → calculate_offsets pushes the zero offset (grid_general.jl:149)
         if (skip_zero) return;
-        uint32_t l = lin_cell<D>(dims, c0);
-        f(cell_start[(size_t)l << ksh], cell_start[(size_t)(l + 1) << ksh], 0);
+        const FineRows fr = fine_rows<D>(dims, kb, c0[1], D == 3 ? c0[2] : 0);
+        for (int t = 0; t < fr.n; ++t)
+            f(cell_start[(size_t)fr.base[t] + ((uint32_t)c0[0] << kb)],
+              cell_start[(size_t)fr.base[t] + ((uint32_t)(c0[0] + 1) << kb)], 0);
         return;
     }
     int lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
@@ -433,13 +500,12 @@ __device__ __forceinline__ void for_each_run(const int* dims, const bool* period
                 cy = cy < 0 ? cy + dims[1] : cy - dims[1];
                 wrap |= 2;
             }
-            uint32_t rowbase = (D == 3) ? ((uint32_t)cz * (uint32_t)dims[1] + (uint32_t)cy) * (uint32_t)dims[0]
-                                        : (uint32_t)cy * (uint32_t)dims[0];
+            const FineRows fr = fine_rows<D>(dims, kb, cy, cz);
             if (skip_zero && by == 0 && bz == 0 && xl <= 0 && xh >= 0) {
-                emit_xrange(dims[0], periodic[0], cell_start, ksh, rowbase, c0[0] + xl, c0[0] - 1, wrap, f);
-                emit_xrange(dims[0], periodic[0], cell_start, ksh, rowbase, c0[0] + 1, c0[0] + xh, wrap, f);
+                emit_xrange(dims[0], periodic[0], cell_start, kb, fr, c0[0] + xl, c0[0] - 1, wrap, f);
+                emit_xrange(dims[0], periodic[0], cell_start, kb, fr, c0[0] + 1, c0[0] + xh, wrap, f);
             } else {
-                emit_xrange(dims[0], periodic[0], cell_start, ksh, rowbase, c0[0] + xl, c0[0] + xh, wrap, f);
+                emit_xrange(dims[0], periodic[0], cell_start, kb, fr, c0[0] + xl, c0[0] + xh, wrap, f);
             }
         }
     }

@@ -68,7 +68,7 @@ __global__ void k_nearby(SpaceDev<T, D> sp, const T* __restrict__ qpos, const in
     const int gr = grid_radius<T, D>(sp, p, c, r);
     int64_t k = 0;
     int64_t base = FILL ? offsets[q] : 0;
-    for_each_run<D>(sp.dims, sp.periodic, AB_METRIC_EUCLIDEAN, c, gr, cell_start, sp.ksh, false,
+    for_each_run<D>(sp.dims, sp.periodic, AB_METRIC_EUCLIDEAN, c, gr, cell_start, sp.kb, false,
                     [&](uint32_t b, uint32_t e, int) {
         for (uint32_t j = b; j < e; ++j) {
             if ((int)j == self_slot) continue;
@@ -101,12 +101,12 @@ __global__ void k_pairs(SpaceDev<T, D> sp, double r, int exact, const T* __restr
     int c[D];
 #pragma unroll
     for (int d = 0; d < D; ++d) p[d] = pos[(size_t)d * cap + s];
-    unlin_cell<D>(sp.dims, key[s] >> sp.ksh, c);
+    key_to_cell<T, D>(sp, key[s], c);
     const int gr = grid_radius<T, D>(sp, p, c, r);
     const int me = id[s];
     unsigned long long k = 0;
     const unsigned long long base = FILL ? offsets[s] : 0ull;
-    for_each_run<D>(sp.dims, sp.periodic, AB_METRIC_EUCLIDEAN, c, gr, cell_start, sp.ksh, false,
+    for_each_run<D>(sp.dims, sp.periodic, AB_METRIC_EUCLIDEAN, c, gr, cell_start, sp.kb, false,
                     [&](uint32_t b, uint32_t e, int) {
         for (uint32_t j = b; j < e; ++j) {
             if ((int)j == s) continue;
@@ -121,7 +121,7 @@ __global__ void k_pairs(SpaceDev<T, D> sp, double r, int exact, const T* __restr
             if (other < me) {
                 // does `other` see me?  then it emits the pair itself
                 int cj[D];
-                unlin_cell<D>(sp.dims, key[j] >> sp.ksh, cj);
+                key_to_cell<T, D>(sp, key[j], cj);
                 const int grj = grid_radius<T, D>(sp, o, cj, r);
                 if (cell_reachable<D>(sp.dims, sp.periodic, AB_METRIC_EUCLIDEAN, cj, c, grj)) continue;
             }
@@ -145,11 +145,11 @@ __global__ void k_nearest(SpaceDev<T, D> sp, double r, const T* __restrict__ pos
     int c[D];
 #pragma unroll
     for (int d = 0; d < D; ++d) p[d] = pos[(size_t)d * cap + s];
-    unlin_cell<D>(sp.dims, key[s] >> sp.ksh, c);
+    key_to_cell<T, D>(sp, key[s], c);
     const int gr = grid_radius<T, D>(sp, p, c, r);
     double best = INFINITY;
     int bj = -1;
-    for_each_run<D>(sp.dims, sp.periodic, AB_METRIC_EUCLIDEAN, c, gr, cell_start, sp.ksh, false,
+    for_each_run<D>(sp.dims, sp.periodic, AB_METRIC_EUCLIDEAN, c, gr, cell_start, sp.kb, false,
                     [&](uint32_t b, uint32_t e, int) {
         for (uint32_t j = b; j < e; ++j) {
             if ((int)j == s) continue;

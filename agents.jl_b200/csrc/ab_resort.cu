@@ -6,19 +6,20 @@
 // step leaves the new state in OLD slot order (tmp_pos / tmp_vel / newkey); this
 // kernel brings it into the next step's cell-sorted order in ONE pass:
 //
-//   tile  = a run of `tw` reference cells of one cell row = a contiguous range of
+//   tile  = a run of `tw` fine cells of one FINE row = a contiguous range of
 //           device keys = a contiguous range of output slots.
 //   CTA   = one tile (taken by ticket, so tile t only ever waits for tiles < t
 //           that are already running).  It scans the OLD slots of the 3^D
-//           neighbouring reference cells of its tile (agents move less than one
-//           reference cell per step on this path), keeps those whose new key
+//           neighbouring fine cells of its tile (agents move less than one
+//           fine cell per step on this path), keeps those whose new key
 //           falls into the tile, histograms them per device cell in shared
 //           memory, publishes the tile total and obtains its output base by
 //           decoupled look-back, orders every cell's agents by id (canonical
 //           order: bitwise reproducible runs whatever the atomic order was),
 //           and writes pos / vel / id / key coalesced, the tile's slice of
-//           cell_start, and (optionally) Σ(pos - centre), Σ vel of every
-//           reference cell of the tile in that canonical order.
+//           cell_start, and (optionally) count, Σ(pos - centre), Σ vel of the
+//           tile's part of every reference cell it touches (one partial per
+//           fine row of a reference cell, combined in fixed order by k_cell_M).
 //
 // Nothing here is specific to the flock rule: any fused rule that bounds the
 // per-step displacement by one reference cell can use it.
@@ -58,45 +59,46 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, c
     if (tid == 0) s_tile = atomicAdd(ticket, 1u);
     __syncthreads();
     const int tile = (int)s_tile;
-    const int row = tile / a.tpr, seg = tile - row * a.tpr;
+    const int frow = tile / a.tpr, seg = tile - frow * a.tpr;      // fine row, segment of it
+    const int kb = sp.kb;
+    const int fd0 = sp.dims[0] << kb, fd1 = sp.dims[1] << kb, fd2 = D == 3 ? (sp.dims[2] << kb) : 1;
     const int x0 = seg * a.tw;
-    const int x1 = min(sp.dims[0], x0 + a.tw);          // exclusive
-    const int ksh = sp.ksh;
-    const uint32_t kbeg = ((uint32_t)row * (uint32_t)sp.dims[0] + (uint32_t)x0) << ksh;
-    const uint32_t kend = ((uint32_t)row * (uint32_t)sp.dims[0] + (uint32_t)x1) << ksh;
+    const int x1 = min(fd0, x0 + a.tw);          // exclusive, fine cells
+    const uint32_t kbeg = (uint32_t)frow * (uint32_t)fd0 + (uint32_t)x0;
+    const uint32_t kend = (uint32_t)frow * (uint32_t)fd0 + (uint32_t)x1;
     const int fc = (int)(kend - kbeg);
+    const int fy0 = D == 2 ? frow : frow % fd1;
+    const int fz0 = D == 2 ? 0 : frow / fd1;
 
-    // ---- source segments: old slots of the neighbouring reference cells -------------
+    // ---- source segments: old slots of the neighbouring fine cells ----------------------
     if (tid == 0) {
-        int cy = D == 2 ? row : row % sp.dims[1];
-        int cz = D == 2 ? 0 : row / sp.dims[1];
         int ns = 0;
         for (int dz = (D == 3 ? -1 : 0); dz <= (D == 3 ? 1 : 0); ++dz) {
-            int z = cz + dz;
-            if (D == 3 && (z < 0 || z >= sp.dims[2])) {
+            int z = fz0 + dz;
+            if (D == 3 && (z < 0 || z >= fd2)) {
                 if (!sp.periodic[2]) continue;
-                z = z < 0 ? z + sp.dims[2] : z - sp.dims[2];
+                z = z < 0 ? z + fd2 : z - fd2;
             }
             for (int dy = -1; dy <= 1; ++dy) {
-                int y = cy + dy;
-                if (y < 0 || y >= sp.dims[1]) {
+                int y = fy0 + dy;
+                if (y < 0 || y >= fd1) {
                     if (!sp.periodic[1]) continue;
-                    y = y < 0 ? y + sp.dims[1] : y - sp.dims[1];
+                    y = y < 0 ? y + fd1 : y - fd1;
                 }
-                const uint32_t rb = (D == 3 ? (uint32_t)z * (uint32_t)sp.dims[1] + (uint32_t)y : (uint32_t)y) * (uint32_t)sp.dims[0];
-                const int lo = max(x0 - 1, 0), hi = min(x1, sp.dims[0] - 1);      // inclusive reference cells
-                s_seg_beg[ns] = cs_old[(size_t)(rb + lo) << ksh];
-                s_seg_end[ns] = cs_old[(size_t)(rb + hi + 1) << ksh];
+                const uint32_t rb = (D == 3 ? (uint32_t)z * (uint32_t)fd1 + (uint32_t)y : (uint32_t)y) * (uint32_t)fd0;
+                const int lo = max(x0 - 1, 0), hi = min(x1, fd0 - 1);      // inclusive fine cells
+                s_seg_beg[ns] = cs_old[(size_t)rb + lo];
+                s_seg_end[ns] = cs_old[(size_t)rb + hi + 1];
                 ++ns;
                 if (sp.periodic[0]) {
-                    if (x0 == 0 && hi < sp.dims[0] - 1) {        // left neighbour wraps to the last cell of the row
-                        s_seg_beg[ns] = cs_old[(size_t)(rb + sp.dims[0] - 1) << ksh];
-                        s_seg_end[ns] = cs_old[(size_t)(rb + sp.dims[0]) << ksh];
+                    if (x0 == 0 && hi < fd0 - 1) {        // left neighbour wraps to the last cell of the row
+                        s_seg_beg[ns] = cs_old[(size_t)rb + fd0 - 1];
+                        s_seg_end[ns] = cs_old[(size_t)rb + fd0];
                         ++ns;
                     }
-                    if (x1 == sp.dims[0] && lo > 0) {            // right neighbour wraps to the first cell
-                        s_seg_beg[ns] = cs_old[(size_t)rb << ksh];
-                        s_seg_end[ns] = cs_old[(size_t)(rb + 1) << ksh];
+                    if (x1 == fd0 && lo > 0) {            // right neighbour wraps to the first cell
+                        s_seg_beg[ns] = cs_old[(size_t)rb];
+                        s_seg_end[ns] = cs_old[(size_t)rb + 1];
                         ++ns;
                     }
                 }
@@ -256,16 +258,20 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, c
         }
     }
 
-    // ---- per reference cell Σ(pos - centre), Σ vel in canonical order --------------------------
+    // ---- per reference cell: count, Σ(pos - centre), Σ vel of this fine row's part, canonical order ---
     if (a.want_agg) {
         __syncthreads();     // the tile's output slots are complete (global writes of this CTA are visible to it)
-        const int ncell = x1 - x0;
+        constexpr int NC = 1 + 2 * D;
+        const int K = sp.K;
+        const int ncell = (x1 - x0) >> kb;                    // x0 and tw are multiples of K
         const int grp = tid >> 3, gl = tid & 7;               // 8 lanes per reference cell
+        const int cy = fy0 >> kb, cz = fz0 >> kb;
+        const int part = (fy0 & (K - 1)) + K * (fz0 & (K - 1));
         for (int c = grp; c < ncell; c += RS_THREADS / 8) {
-            const uint32_t b = base + s_start[(size_t)c << ksh], e = base + s_start[(size_t)(c + 1) << ksh];
-            const uint32_t refcell = (uint32_t)row * (uint32_t)sp.dims[0] + (uint32_t)(x0 + c);
-            int cc[D];
-            unlin_cell<D>(sp.dims, refcell, cc);
+            const uint32_t b = base + s_start[(size_t)c << kb], e = base + s_start[(size_t)(c + 1) << kb];
+            const int cx = (x0 >> kb) + c;
+            const uint32_t refcell = (D == 3 ? ((uint32_t)cz * sp.dims[1] + cy) : (uint32_t)cy) * (uint32_t)sp.dims[0] + (uint32_t)cx;
+            const int cc[3] = {cx, cy, cz};
             T acc[2 * D];
 #pragma unroll
             for (int d = 0; d < 2 * D; ++d) acc[d] = T(0);
@@ -284,26 +290,34 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, c
                 acc[d] += __shfl_xor_sync(0xffffffffu, acc[d], 1);
             }
             if (gl == 0) {
+                T* dst = agg + (size_t)part * NC * agg_stride + refcell;
+                dst[0] = (T)(e - b);
 #pragma unroll
-                for (int d = 0; d < 2 * D; ++d) agg[(size_t)d * agg_stride + refcell] = acc[d];
+                for (int d = 0; d < 2 * D; ++d) dst[(size_t)(1 + d) * agg_stride] = acc[d];
             }
         }
     }
 }
 
 // Aggregates of an already sorted state (after a generic index build): one
-// 8-lane group per reference cell, same summation order as k_resort.
+// 8-lane group per (reference cell, fine row of it), same summation order as k_resort.
 template <class T, int D>
 __global__ void __launch_bounds__(256)
 k_cell_agg(SpaceDev<T, D> sp, const uint32_t* __restrict__ cs, const T* __restrict__ pos, const T* __restrict__ vel,
            int64_t cap, uint32_t ncells, T* __restrict__ agg, int64_t agg_stride) {
+    constexpr int NC = 1 + 2 * D;
+    const int K = sp.K, kb = sp.kb;
+    const int nfr = D == 2 ? K : K * K;
     const uint32_t g = (blockIdx.x * blockDim.x + threadIdx.x) >> 3;
     const int gl = threadIdx.x & 7;
-    const bool live = g < ncells;
-    const uint32_t c = live ? g : 0;
-    const uint32_t b = cs[(size_t)c << sp.ksh], e = live ? cs[(size_t)(c + 1) << sp.ksh] : b;
+    const bool live = g < ncells * (uint32_t)nfr;
+    const uint32_t c = live ? g / (uint32_t)nfr : 0;
+    const int part = live ? (int)(g - c * (uint32_t)nfr) : 0;
     int cc[D];
     unlin_cell<D>(sp.dims, c, cc);
+    const FineRows fr = fine_rows<D>(sp.dims, kb, cc[1], D == 3 ? cc[2] : 0);
+    const uint32_t b = cs[(size_t)fr.base[part] + ((uint32_t)cc[0] << kb)];
+    const uint32_t e = live ? cs[(size_t)fr.base[part] + ((uint32_t)(cc[0] + 1) << kb)] : b;
     T acc[2 * D];
 #pragma unroll
     for (int d = 0; d < 2 * D; ++d) acc[d] = T(0);
@@ -322,8 +336,10 @@ k_cell_agg(SpaceDev<T, D> sp, const uint32_t* __restrict__ cs, const T* __restri
         acc[d] += __shfl_xor_sync(0xffffffffu, acc[d], 1);
     }
     if (live && gl == 0) {
+        T* dst = agg + (size_t)part * NC * agg_stride + c;
+        dst[0] = (T)(e - b);
 #pragma unroll
-        for (int d = 0; d < 2 * D; ++d) agg[(size_t)d * agg_stride + c] = acc[d];
+        for (int d = 0; d < 2 * D; ++d) dst[(size_t)(1 + d) * agg_stride] = acc[d];
     }
 }
 
@@ -337,7 +353,8 @@ bool ab_resort_applicable(const ab_handle* h) {
 }
 
 static int ensure_agg(ab_handle* h) {
-    size_t need = (size_t)2 * h->D * h->ncells * h->tsize;
+    // one partial (count, Σ(pos - centre), Σ vel) per fine row of every reference cell: 4 = max K^(D-1)
+    size_t need = (size_t)4 * (1 + 2 * h->D) * h->ncells * h->tsize;
     if (h->cell_agg_bytes >= need) return AB_OK;
     if (h->cell_agg) { AB_CUDA(h, cudaStreamSynchronize(h->stream)); AB_CUDA(h, cudaFree(h->cell_agg)); h->cell_agg = nullptr; }
     AB_CUDA(h, cudaMalloc(&h->cell_agg, need));
@@ -351,16 +368,19 @@ static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool
     const int cur = h->cur, nxt = cur ^ 1;
     SpaceDev<T, D> sp = make_space<T, D>(h);
     ResortArgs a;
-    // tile width: ~768 agents per tile on average, at most RS_FC_MAX device cells
-    const double dens = (double)h->n / (double)h->ncells;
-    int tw = (int)(768.0 / (dens > 1e-9 ? dens : 1e-9));
-    const int twmax = RS_FC_MAX >> h->ksh;
-    if (tw > twmax) tw = twmax;
-    if (tw < 4) tw = 4;
-    if (tw > h->dims[0]) tw = h->dims[0];
-    a.tpr = (h->dims[0] + tw - 1) / tw;
-    a.tw = (h->dims[0] + a.tpr - 1) / a.tpr;          // even split of the row
-    a.nrows = (int)(h->ncells / h->dims[0]);
+    // tile width (fine cells of one fine row): ~RS_TARGET agents per tile on average, at most
+    // RS_FC_MAX fine cells, a multiple of K so that tiles hold whole reference cells
+    const int fd0 = h->dims[0] << h->kb;
+    const double dens = (double)h->n / (double)h->nfine;
+    int tw = (int)((double)h->rs_target / (dens > 1e-9 ? dens : 1e-9));
+    if (tw > RS_FC_MAX) tw = RS_FC_MAX;
+    if (tw < 8) tw = 8;
+    if (tw > fd0) tw = fd0;
+    a.tpr = (fd0 + tw - 1) / tw;
+    a.tw = (fd0 + a.tpr - 1) / a.tpr;                 // even split of the row
+    a.tw = (a.tw + h->K - 1) / h->K * h->K;
+    a.tpr = (fd0 + a.tw - 1) / a.tw;
+    a.nrows = (int)(h->nfine / fd0);
     a.ntiles = a.nrows * a.tpr;
     a.has_vel = h->desc.kind == AB_SPACE_CONTINUOUS;
     a.want_agg = want_agg ? 1 : 0;
@@ -409,7 +429,8 @@ template <class T, int D>
 static int agg_t(ab_handle* h) {
     AB_LAUNCH(h, "k_cell_agg");
     const uint32_t nc = (uint32_t)h->ncells;
-    k_cell_agg<T, D><<<ab_blocks((int64_t)nc * 8, 256), 256, 0, h->stream>>>(
+    const int nfr = h->D == 2 ? h->K : h->K * h->K;
+    k_cell_agg<T, D><<<ab_blocks((int64_t)nc * nfr * 8, 256), 256, 0, h->stream>>>(
         make_space<T, D>(h), h->cell_start, (const T*)h->fields[0].buf[h->cur], (const T*)h->fields[1].buf[h->cur], h->cap, nc,
         (T*)h->cell_agg, (int64_t)h->ncells);
     return AB_OK;

@@ -107,7 +107,7 @@ class FlockRule:
                       separate_factor=separate_factor, match_factor=match_factor, visual_distance=visual_distance)
         self.search = search
         self.per_agent = per_agent
-        self.kernel = {"auto": 0, "generic": 1, "tiled": 2}[kernel]
+        self.kernel = {"auto": 0, "generic": 1, "tiled": 2, "fine": 2}[kernel]
         self._field = -1
 
     def _bind(self, model):
