@@ -23,6 +23,7 @@ template <class T> struct FlockU {
     T speed, cohere_factor, separation, separate_factor, match_factor;
     double visual_distance;
     T thr;      // exact_threshold<T>(visual_distance), computed once on the host for uniform parameters
+    double gr_t1, gr_t2;   // (spacing - r)², (2 spacing - r)² (negative: never) — grid_radius_12
 };
 
 // host twin of exact_threshold (ab_internal.cuh): IEEE sqrt on both sides, same result
@@ -45,22 +46,24 @@ __device__ __forceinline__ void flock_epilogue(const SpaceDev<T, D>& sp, const T
                                                const T* separate, const T* match, int N, const FlockU<T>& fp,
                                                T* np, T* nv, int* err) {
     // flock.jl:100-105
+    // (x / N and v / norm(v) are evaluated as multiplications by 1/N and 1/sqrt(Σv²): results are
+    //  tolerance-checked, not bit-compared — they differ from the reference by an ulp or two)
     T s = 0;
-    const T denom = (T)(N > 1 ? N : 1);
+    const T rdenom = T(1) / (T)(N > 1 ? N : 1);
 #pragma unroll
     for (int d = 0; d < D; ++d) {
         T c = cohere[d] * fp.cohere_factor;
         T sp_ = separate[d] * fp.separate_factor;
         T m = match[d] * fp.match_factor;
-        nv[d] = v[d] + ((c + sp_) + m) / denom;
+        nv[d] = v[d] + ((c + sp_) + m) * rdenom;
         T sq = nv[d] * nv[d];
         s = (d == 0) ? sq : s + sq;
     }
-    const T nrm = ab_sqrt(s);
+    const T rnrm = ab_rsqrt(s);
     bool bad = false;
 #pragma unroll
     for (int d = 0; d < D; ++d) {
-        nv[d] = nv[d] / nrm;
+        nv[d] = nv[d] * rnrm;
         // move_agent!(bird, model, speed): continuous.jl:186-194, walk.jl:58-66
         T t = p[d] + fp.speed * nv[d];
         t = normalize_coord(t, sp.extent[d], sp.periodic[d]);
@@ -256,7 +259,10 @@ static int launch_cell_M(ab_handle* h, const SpaceDev<T, D>& sp) {
         h->cell_M_bytes = need;
     }
     AB_LAUNCH(h, "k_cell_M");
-    k_cell_M<T, D><<<ab_blocks(h->ncells, 128), 128, 0, h->stream>>>(sp, (const T*)h->cell_agg, (int64_t)h->ncells, (T*)h->cell_M);
+    const int wpr = (h->dims[0] + CM_OUT - 1) / CM_OUT;                  // warps per reference cell row
+    const int64_t nwarps = (h->ncells / h->dims[0]) * wpr;
+    k_cell_M<T, D><<<ab_blocks(nwarps * 32, 128), 128, 0, h->stream>>>(sp, (const T*)h->cell_agg, (int64_t)h->ncells, wpr,
+                                                                       (int)nwarps, (T*)h->cell_M);
     return AB_OK;
 }
 
@@ -268,8 +274,8 @@ static int launch_fine(ab_handle* h, const SpaceDev<T, D>& sp, const FlockU<T>& 
     AB_LAUNCH(h, EXACT ? "k_flock_fine_exact" : "k_flock_fine");
     k_flock_fine<T, D, EXACT><<<ab_blocks(n, TB), TB, 0, h->stream>>>(
         sp, u, (const T*)h->fields[0].buf[cur], (const T*)h->fields[1].buf[cur], h->key[cur], h->cell_start,
-        (const T*)h->cell_M, (int64_t)h->ncells, h->cap, n, (T*)h->tmp_pos, (T*)h->tmp_vel, h->newkey, h->id[cur],
-        ncount, h->d_err);
+        (const T*)h->cell_M, (int64_t)h->ncells, h->cap, n, (T*)h->tmp_pos, (T*)h->tmp_vel, h->newkey, h->cell_count,
+        h->id[cur], ncount, h->d_err);
     return AB_OK;
 }
 
@@ -282,6 +288,11 @@ static int flock_steps_t(ab_handle* h, const ab_flock_params* p, int64_t nsteps)
     u.visual_distance = p->visual_distance;
     const bool exact = p->search == AB_SEARCH_EXACT;
     u.thr = exact ? exact_threshold_host<T>(p->visual_distance) : T(0);
+    {
+        const double sd = (double)(T)h->desc.spacing, d1 = sd - p->visual_distance, d2 = 2.0 * sd - p->visual_distance;
+        u.gr_t1 = d1 >= 0 ? d1 * d1 : -1.0;
+        u.gr_t2 = d2 >= 0 ? d2 * d2 : -1.0;
+    }
     int pa_field = p->per_agent_field;
     if (pa_field >= 0) {
         if (pa_field >= (int)h->fields.size() || h->fields[pa_field].ncomp != 6 || h->fields[pa_field].dtype != h->dtype)

@@ -27,6 +27,7 @@
 // Birds whose grid_r is not 1 or 2 take the reference walk (flock_accumulate_generic),
 // so the kernel is correct for every state; only its speed depends on the state.
 #pragma once
+#include <type_traits>
 
 template <int D> struct FineCfg { static constexpr int NC = 1 + 2 * D; };   // count, Σ(pos-centre)[D], Σvel[D]
 
@@ -51,61 +52,129 @@ __device__ __forceinline__ int wrap_coord(int c, int n, bool periodic) {
 
 // M[g-1][c][cell] = Σ over the offset table of radius g (Σβ² ≤ g², grid_general.jl:138-151) of the
 // per-cell aggregates, with neighbour positions re-expressed relative to THIS cell's centre
-// (+ β·spacing per neighbour agent).  aggp holds one partial per fine row of a reference cell
-// (written by k_resort / k_cell_agg); they are added in fixed order.
+// (+ β·spacing per neighbour agent: Σ_nb count_nb·β_nb is accumulated as an exact integer).
+// aggp holds one partial per fine row of a reference cell (written by k_resort / k_cell_agg);
+// they are added in fixed order.
+// A warp covers CM_OUT consecutive cells of one reference cell row plus 2 halo cells per side:
+// each lane loads the aggregates of ONE cell per neighbour row and the ±1, ±2 x-neighbours
+// come from warp shuffles, so every aggregate is read once per row offset, not once per offset.
+#define CM_OUT 28
+template <class T> __device__ __forceinline__ T shfl_T(T v, int src) { return __shfl_sync(0xffffffffu, v, src); }
 template <class T, int D>
 __global__ void __launch_bounds__(128)
-k_cell_M(SpaceDev<T, D> sp, const T* __restrict__ aggp, int64_t ncells, T* __restrict__ M) {
+k_cell_M(SpaceDev<T, D> sp, const T* __restrict__ aggp, int64_t ncells, int wpr, int nwarps, T* __restrict__ M) {
     constexpr int NC = FineCfg<D>::NC;
     constexpr int NRO = D == 2 ? 5 : 13;
-    const int64_t cell = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (cell >= ncells) return;
-    int c[D];
-    unlin_cell<D>(sp.dims, (uint32_t)cell, c);
+    const int warp = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    if (warp >= nwarps) return;
+    const int lane = threadIdx.x & 31;
+    const int row = warp / wpr, seg = warp - row * wpr;
+    const int cy = D == 2 ? row : row % sp.dims[1];
+    const int cz = D == 2 ? 0 : row / sp.dims[1];
+    const int xout = seg * CM_OUT + lane - 2;                                  // this lane's output cell (lanes 2..29)
+    const int xl = xout > sp.dims[0] + 1 ? -1 : wrap_coord(xout, sp.dims[0], sp.periodic[0]);   // cell whose aggregates this lane loads
     const int nfr = D == 2 ? sp.K : sp.K * sp.K;
     T acc1[NC], acc2[NC];
+    int cb1[D], cb2[D];
 #pragma unroll
     for (int i = 0; i < NC; ++i) acc1[i] = acc2[i] = T(0);
+#pragma unroll
+    for (int d = 0; d < D; ++d) cb1[d] = cb2[d] = 0;
+#pragma unroll
     for (int ro = 0; ro < NRO; ++ro) {
         int dy, dz;
         ro_offset<D>(ro, &dy, &dz);
         const int rem2 = 4 - dy * dy - dz * dz;
         const int hw2 = rem2 >= 4 ? 2 : (rem2 >= 1 ? 1 : 0);
         const int rem1 = 1 - dy * dy - dz * dz;
-        const int y = wrap_coord(c[1] + dy, sp.dims[1], sp.periodic[1]);
-        const int z = D == 3 ? wrap_coord(c[2] + dz, sp.dims[2], sp.periodic[2]) : 0;
-        if (y < 0 || z < 0) continue;
-        const uint32_t rb = (D == 3 ? ((uint32_t)z * sp.dims[1] + y) : (uint32_t)y) * (uint32_t)sp.dims[0];
-        for (int bx = -hw2; bx <= hw2; ++bx) {
-            const int x = wrap_coord(c[0] + bx, sp.dims[0], sp.periodic[0]);
-            if (x < 0) continue;
-            const uint32_t nb = rb + (uint32_t)x;
-            T a[NC];
+        const int y = wrap_coord(cy + dy, sp.dims[1], sp.periodic[1]);
+        const int z = D == 3 ? wrap_coord(cz + dz, sp.dims[2], sp.periodic[2]) : 0;
+        T a[NC];
+#pragma unroll
+        for (int i = 0; i < NC; ++i) a[i] = T(0);
+        if (y >= 0 && z >= 0 && xl >= 0) {                                       // warp-uniform except xl
+            const size_t nb = (size_t)(D == 3 ? ((uint32_t)z * sp.dims[1] + y) : (uint32_t)y) * (uint32_t)sp.dims[0] + (uint32_t)xl;
 #pragma unroll
             for (int i = 0; i < NC; ++i) {
                 T v = aggp[(size_t)i * ncells + nb];
-                for (int t = 1; t < nfr; ++t) v += aggp[((size_t)t * NC + i) * ncells + nb];
+                if (nfr >= 2) v += aggp[((size_t)NC + i) * ncells + nb];
+                if (nfr == 4) {
+                    v += aggp[((size_t)2 * NC + i) * ncells + nb];
+                    v += aggp[((size_t)3 * NC + i) * ncells + nb];
+                }
                 a[i] = v;
             }
-            // neighbour sums relative to this cell's centre
+        }
+#pragma unroll
+        for (int bx = -2; bx <= 2; ++bx) {
+            if (bx < -hw2 || bx > hw2) continue;                                  // compile-time after unrolling
+            T b[NC];
+#pragma unroll
+            for (int i = 0; i < NC; ++i) b[i] = bx == 0 ? a[i] : shfl_T(a[i], lane + bx);
+            const int cnt = (int)b[0];
+            const bool in1 = rem1 >= 0 && (bx == 0 || (rem1 >= 1 && (bx == 1 || bx == -1)));
+#pragma unroll
+            for (int i = 0; i < NC; ++i) { acc2[i] += b[i]; if (in1) acc1[i] += b[i]; }
 #pragma unroll
             for (int d = 0; d < D; ++d) {
                 const int beta = d == 0 ? bx : (d == 1 ? dy : dz);
-                a[1 + d] = a[1 + d] + a[0] * ((T)beta * sp.spacing);
-            }
-            const bool in1 = rem1 >= 0 && (bx == 0 || (rem1 >= 1 && (bx == 1 || bx == -1)));
-#pragma unroll
-            for (int i = 0; i < NC; ++i) {
-                acc2[i] += a[i];
-                if (in1) acc1[i] += a[i];
+                cb2[d] += cnt * beta;
+                if (in1) cb1[d] += cnt * beta;
             }
         }
     }
+    if (lane >= 2 && lane < 2 + CM_OUT && xout < sp.dims[0]) {
+        const size_t cell = (size_t)(D == 3 ? ((uint32_t)cz * sp.dims[1] + cy) : (uint32_t)cy) * (uint32_t)sp.dims[0] + (uint32_t)xout;
 #pragma unroll
-    for (int i = 0; i < NC; ++i) {
-        M[(size_t)i * ncells + cell] = acc1[i];
-        M[((size_t)NC + i) * ncells + cell] = acc2[i];
+        for (int d = 0; d < D; ++d) {
+            acc1[1 + d] += (T)cb1[d] * sp.spacing;
+            acc2[1 + d] += (T)cb2[d] * sp.spacing;
+        }
+#pragma unroll
+        for (int i = 0; i < NC; ++i) {
+            M[(size_t)i * ncells + cell] = acc1[i];
+            M[((size_t)NC + i) * ncells + cell] = acc2[i];
+        }
     }
+}
+
+// grid_r (continuous.jl:221-225) when the plan guarantees it is 1 or 2: ceil((r + δ)/spacing) is 1 iff
+// δ <= spacing - r and 2 iff δ <= 2 spacing - r, so δ² is compared with the squared thresholds; a bird
+// whose δ² lies within 1e-9 (relative) of a threshold takes the reference arithmetic instead.
+template <class T, int D>
+__device__ __forceinline__ int grid_radius_12(const SpaceDev<T, D>& sp, const T* p, const int* c0, const FlockU<T>& fp) {
+    double s2 = 0;
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        const double centre = sp.spacing_d * ((double)(c0[d] + 1) - 0.5);
+        const double direct = fabs((double)p[d] - centre);
+        const double m = sp.periodic[d] ? fmin(direct, sp.extent_d[d] - direct) : direct;
+        const double sq = m * m;
+        s2 = (d == 0) ? sq : s2 + sq;
+    }
+    const double lo = 1.0 - 1e-9, hi = 1.0 + 1e-9;
+    if (s2 < fp.gr_t1 * lo) return 1;
+    if (s2 > fp.gr_t1 * hi && s2 < fp.gr_t2 * lo) return 2;
+    return grid_radius<T, D>(sp, p, c0, fp.visual_distance);
+}
+
+// pos2cell0 with the division replaced by a multiplication whenever the quotient is provably not
+// within rounding distance of an integer (then ceil of either is the same integer).
+template <class T, int D>
+__device__ __forceinline__ bool pos2cell0_fast(const SpaceDev<T, D>& sp, const T* p, int* c) {
+    const T eps8 = sizeof(T) == 8 ? T(1.7763568394002505e-15) : T(9.5367431640625e-07);   // 8 ulp
+    bool fastok = true;
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        const T qa = p[d] * sp.inv_spacing;
+        const T cq = ceil(qa);
+        const T margin = qa * eps8;
+        // (cq - qa) in (margin, 1 - margin): not near an integer; 0 < cq <= dims
+        if (!(cq - qa > margin && cq - qa < T(1) - margin && cq >= T(1) && cq <= (T)sp.dims[d])) fastok = false;
+        c[d] = (int)cq - 1;
+    }
+    if (fastok) return true;
+    return pos2cell0<T, D>(sp, p, c);
 }
 
 template <class T, int D, bool EXACT>
@@ -113,8 +182,8 @@ __global__ void __launch_bounds__(128)
 k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T* __restrict__ vel,
              const uint32_t* __restrict__ key, const uint32_t* __restrict__ cs, const T* __restrict__ M,
              int64_t ncells, int64_t cap, int n, T* __restrict__ npos, T* __restrict__ nvel,
-             uint32_t* __restrict__ newkey, const int32_t* __restrict__ ids, int32_t* __restrict__ ncount,
-             int* __restrict__ err) {
+             uint32_t* __restrict__ newkey, uint32_t* __restrict__ cell_count, const int32_t* __restrict__ ids,
+             int32_t* __restrict__ ncount, int* __restrict__ err) {
     constexpr int NC = FineCfg<D>::NC;
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
@@ -127,7 +196,7 @@ k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T
     key_to_fine<T, D>(sp, k, f);
 #pragma unroll
     for (int d = 0; d < D; ++d) c[d] = f[d] >> kb;
-    const int gr = grid_radius<T, D>(sp, p, c, fp.visual_distance);
+    const int gr = grid_radius_12<T, D>(sp, p, c, fp);
     const T sep2 = fp.separation * fp.separation;
     T cohere[D], separate[D], match[D];
 #pragma unroll
@@ -163,7 +232,10 @@ k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T
         const T thr = fp.thr;
         const int R = EXACT ? K : 1;                   // fine-cell reach of the sweep
         const int fd0 = sp.dims[0] << kb, fd1 = sp.dims[1] << kb, fd2 = D == 3 ? (sp.dims[2] << kb) : 1;
-        auto sweep = [&](uint32_t jb, uint32_t je, int wrap) {
+        // two instantiations of the pair loop: runs reached across a periodic boundary apply the
+        // reference's minimum-image rule (utilities.jl:185-193); all other runs are plain differences
+        auto sweep_t = [&](uint32_t jb, uint32_t je, int wrap, auto wrapped) {
+            constexpr bool WRAP = decltype(wrapped)::value;
 #pragma unroll 2
             for (uint32_t j = jb; j < je; ++j) {
                 T h[D];
@@ -171,7 +243,7 @@ k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T
 #pragma unroll
                 for (int d = 0; d < D; ++d) {
                     T direct = pos[(size_t)d * cap + j] - p[d];
-                    if (wrap & (1 << d)) direct = min_image(direct, sp.extent[d]);     // utilities.jl:185-193
+                    if (WRAP && (wrap & (1 << d))) direct = min_image(direct, sp.extent[d]);
                     h[d] = direct;
                     const T sq = direct * direct;
                     d2 = (d == 0) ? sq : d2 + sq;
@@ -189,6 +261,11 @@ k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T
                 }
             }
         };
+        auto sweep = [&](uint32_t jb, uint32_t je, int wrap) {
+            if (wrap == 0) sweep_t(jb, je, 0, std::false_type{});
+            else sweep_t(jb, je, wrap, std::true_type{});
+        };
+        constexpr int NROW = EXACT ? 5 : 3;            // fine rows per z-slab: 2R+1
         for (int rz = (D == 3 ? -R : 0); rz <= (D == 3 ? R : 0); ++rz) {
             int fz = 0, wz = 0, dz = 0;
             if (D == 3) {
@@ -200,7 +277,15 @@ k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T
                     wz = 4;
                 }
             }
-            for (int ry = -R; ry <= R; ++ry) {
+            // phase 1: slot bounds of the main run of every row — independent loads, all in flight together
+            uint32_t rbv[NROW], jb[NROW], je[NROW];
+            int ulov[NROW], uhiv[NROW], wrv[NROW];
+#pragma unroll
+            for (int i = 0; i < NROW; ++i) {
+                wrv[i] = -1;                                 // row not visited
+                jb[i] = je[i] = 0;
+                const int ry = i - R;
+                if (i > 2 * R) continue;
                 int fy = f[1] + ry;
                 const int dy = (fy >> kb) - c[1];
                 int ulo = f[0] - R, uhi = f[0] + R;          // inclusive fine cells, unwrapped
@@ -219,15 +304,19 @@ k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T
                     wy = 2;
                 }
                 const uint32_t rb = (D == 3 ? ((uint32_t)fz * (uint32_t)fd1 + (uint32_t)fy) : (uint32_t)fy) * (uint32_t)fd0;
-                const int wyz = wy | wz;
-                if (ulo < 0) {
-                    if (sp.periodic[0]) sweep(cs[rb + (uint32_t)(ulo + fd0)], cs[rb + (uint32_t)fd0], wyz | 1);
-                    ulo = 0;
+                rbv[i] = rb; ulov[i] = ulo; uhiv[i] = uhi; wrv[i] = wy | wz;
+                const int a0 = max(ulo, 0), a1 = min(uhi, fd0 - 1);
+                if (a0 <= a1) { jb[i] = cs[rb + (uint32_t)a0]; je[i] = cs[rb + (uint32_t)a1 + 1]; }
+            }
+            // phase 2: the pair loops
+#pragma unroll
+            for (int i = 0; i < NROW; ++i) {
+                if (wrv[i] < 0) continue;
+                sweep(jb[i], je[i], wrv[i]);
+                if (sp.periodic[0]) {                        // parts reached across the x boundary (rare)
+                    if (ulov[i] < 0) sweep(cs[rbv[i] + (uint32_t)(ulov[i] + fd0)], cs[rbv[i] + (uint32_t)fd0], wrv[i] | 1);
+                    if (uhiv[i] >= fd0) sweep(cs[rbv[i]], cs[rbv[i] + (uint32_t)(uhiv[i] - fd0) + 1], wrv[i] | 1);
                 }
-                int uhi_main = uhi;
-                if (uhi >= fd0) uhi_main = fd0 - 1;
-                if (ulo <= uhi_main) sweep(cs[rb + (uint32_t)ulo], cs[rb + (uint32_t)uhi_main + 1], wyz);
-                if (uhi >= fd0 && sp.periodic[0]) sweep(cs[rb], cs[rb + (uint32_t)(uhi - fd0) + 1], wyz | 1);
             }
         }
     } else {
@@ -236,11 +325,12 @@ k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T
     T np_[D], nv[D];
     flock_epilogue<T, D>(sp, p, v, cohere, separate, match, N, fp, np_, nv, err);
     int nc[D];
-    if (!pos2cell0<T, D>(sp, np_, nc)) atomicOr(err, AB_EF_NUMERIC);
+    if (!pos2cell0_fast<T, D>(sp, np_, nc)) atomicOr(err, AB_EF_NUMERIC);
     const uint32_t nk = device_key<T, D>(sp, np_, nc);
 #pragma unroll
     for (int d = 0; d < D; ++d) { npos[(size_t)d * cap + s] = np_[d]; nvel[(size_t)d * cap + s] = nv[d]; }
     newkey[s] = nk;
+    atomicAdd(&cell_count[nk], 1u);       // histogram of the new keys (k_scan turns it into the next cell_start)
     if (ncount) ncount[ids[s]] = N;
 }
 

@@ -97,11 +97,6 @@ struct ab_handle {
     size_t cell_M_bytes = 0;
     int rs_target = 512;               // average agents per re-sort tile (tuning knob)
 
-    // tiled re-sort look-back state (ab_resort.cu)
-    unsigned long long* rs_status = nullptr;
-    size_t rs_status_len = 0;
-    uint32_t rs_epoch = 0;
-
     // single-pass scan state
     unsigned long long* scan_status = nullptr;
     size_t scan_status_len = 0;
@@ -164,6 +159,7 @@ int ab_permute_extra_fields(ab_handle* h);     // applies h->perm (new slot -> o
 bool ab_resort_applicable(const ab_handle* h);
 int ab_resort_tiled(ab_handle* h, const void* src_pos, const void* src_vel, bool want_agg);
 int ab_ensure_agg(ab_handle* h);
+int ab_run_scan(ab_handle* h, uint32_t* dst);             // cell_count -> exclusive offsets in dst (zeroes cell_count)
 size_t ab_dtype_size(int dtype);
 // cross-file internals (C++ linkage)
 void ab_comm_free(ab_handle* h);
@@ -194,6 +190,7 @@ static inline int ab_blocks(int64_t n, int threads) { return (int)((n + threads 
 template <class T, int D> struct SpaceDev {
     T extent[D];
     T spacing;
+    T inv_spacing;   // rounded 1/spacing — only for guarded shortcuts, never for a cell decision on its own
     double extent_d[D];
     double spacing_d;
     int dims[D];
@@ -213,6 +210,7 @@ template <class T, int D> static inline SpaceDev<T, D> make_space(const ab_handl
         s.periodic[d] = h->desc.periodic[d] != 0;
     }
     s.spacing = (T)h->desc.spacing;
+    s.inv_spacing = T(1) / s.spacing;
     s.spacing_d = (double)s.spacing;
     s.metric = h->desc.kind == AB_SPACE_CONTINUOUS ? AB_METRIC_EUCLIDEAN : h->desc.metric;
     s.K = h->K;
@@ -225,6 +223,8 @@ template <class T, int D> static inline SpaceDev<T, D> make_space(const ab_handl
 
 __device__ __forceinline__ double ab_sqrt(double x) { return sqrt(x); }
 __device__ __forceinline__ float ab_sqrt(float x) { return sqrtf(x); }
+__device__ __forceinline__ double ab_rsqrt(double x) { return rsqrt(x); }
+__device__ __forceinline__ float ab_rsqrt(float x) { return 1.0f / sqrtf(x); }
 __device__ __forceinline__ double ab_fmod(double x, double y) { return fmod(x, y); }
 __device__ __forceinline__ float ab_fmod(float x, float y) { return fmodf(x, y); }
 __device__ __forceinline__ double ab_next(double x, double dir) { return nextafter(x, dir); }

@@ -8,16 +8,18 @@
 //
 //   tile  = a run of `tw` fine cells of one FINE row = a contiguous range of
 //           device keys = a contiguous range of output slots.
-//   CTA   = one tile (taken by ticket, so tile t only ever waits for tiles < t
-//           that are already running).  It scans the OLD slots of the 3^D
+//   before  the fused step kernel has counted the new keys per fine cell
+//           (red.add into cell_count) and k_scan has turned the counts into the
+//           NEW cell_start, so every tile knows its output range up front and
+//           tiles are independent of each other (a first version chained the
+//           tiles by decoupled look-back: ~55 % of its time was spent waiting).
+//   CTA   = one tile.  It scans the OLD slots of the 3^D
 //           neighbouring fine cells of its tile (agents move less than one
 //           fine cell per step on this path), keeps those whose new key
-//           falls into the tile, histograms them per device cell in shared
-//           memory, publishes the tile total and obtains its output base by
-//           decoupled look-back, orders every cell's agents by id (canonical
+//           falls into the tile, buckets them per device cell in shared
+//           memory, orders every cell's agents by id (canonical
 //           order: bitwise reproducible runs whatever the atomic order was),
-//           and writes pos / vel / id / key coalesced, the tile's slice of
-//           cell_start, and (optionally) count, Σ(pos - centre), Σ vel of the
+//           and writes pos / vel / id / key coalesced and (optionally) count, Σ(pos - centre), Σ vel of the
 //           tile's part of every reference cell it touches (one partial per
 //           fine row of a reference cell, combined in fixed order by k_cell_M).
 //
@@ -32,7 +34,6 @@
 
 struct ResortArgs {
     int tw, tpr, ntiles, nrows;
-    uint32_t epoch;
     int has_vel, want_agg;
 };
 
@@ -41,24 +42,20 @@ __global__ void __launch_bounds__(RS_THREADS)
 k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, const uint32_t* __restrict__ newkey,
          const int32_t* __restrict__ id_old, const T* __restrict__ src_pos, const T* __restrict__ src_vel,
          int64_t cap, int n, T* __restrict__ dst_pos, T* __restrict__ dst_vel, int32_t* __restrict__ id_new,
-         uint32_t* __restrict__ key_new, uint32_t* __restrict__ cs_new, int32_t* __restrict__ perm,
+         uint32_t* __restrict__ key_new, const uint32_t* __restrict__ cs_new, int32_t* __restrict__ perm,
          T* __restrict__ agg, int64_t agg_stride, int32_t* __restrict__ g_ent_id, int32_t* __restrict__ g_ent_s,
-         volatile unsigned long long* status, uint32_t* ticket, int* __restrict__ err) {
-    __shared__ uint32_t s_tile;
+         int* __restrict__ err) {
     __shared__ uint32_t s_seg_beg[RS_MAXSEG], s_seg_end[RS_MAXSEG];
     __shared__ int s_nseg;
-    __shared__ uint32_t s_cnt[RS_FC_MAX];        // histogram, then cursor
-    __shared__ uint32_t s_start[RS_FC_MAX + 1];  // exclusive scan
-    __shared__ uint32_t s_warp[RS_THREADS / 32];
-    __shared__ uint32_t s_base;
+    __shared__ uint32_t s_cnt[RS_FC_MAX];        // per-cell cursor
+    __shared__ uint32_t s_start[RS_FC_MAX + 1];  // new cell_start of the tile's cells, relative to the tile's base
+    __shared__ uint32_t s_found;
     __shared__ int32_t s_ent_id[RS_CAP], s_ent_s[RS_CAP];
     __shared__ uint16_t s_ent_lc[RS_CAP];
     __shared__ int32_t s_sorted_s[RS_CAP];
 
     const int tid = threadIdx.x;
-    if (tid == 0) s_tile = atomicAdd(ticket, 1u);
-    __syncthreads();
-    const int tile = (int)s_tile;
+    const int tile = blockIdx.x;
     const int frow = tile / a.tpr, seg = tile - frow * a.tpr;      // fine row, segment of it
     const int kb = sp.kb;
     const int fd0 = sp.dims[0] << kb, fd1 = sp.dims[1] << kb, fd2 = D == 3 ? (sp.dims[2] << kb) : 1;
@@ -106,95 +103,22 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, c
         }
         s_nseg = ns;
     }
-    for (int i = tid; i < fc; i += RS_THREADS) s_cnt[i] = 0;
+    const uint32_t base = cs_new[kbeg];
+    for (int i = tid; i <= fc; i += RS_THREADS) {
+        const uint32_t st = cs_new[(size_t)kbeg + i] - base;
+        s_start[i] = st;
+        if (i < fc) s_cnt[i] = st;                       // cursor = start
+    }
+    if (tid == 0) s_found = 0;
     __syncthreads();
     const int nseg = s_nseg;
-
-    // ---- pass 1: histogram of the agents that land in this tile ----------------------
-    for (int sg = 0; sg < nseg; ++sg) {
-        const uint32_t e = s_seg_end[sg];
-        for (uint32_t s = s_seg_beg[sg] + tid; s < e; s += RS_THREADS) {
-            const uint32_t k = newkey[s];
-            if (k >= kbeg && k < kend) atomicAdd(&s_cnt[k - kbeg], 1u);
-        }
-    }
-    __syncthreads();
-
-    // ---- block exclusive scan of s_cnt[0..fc) -> s_start ------------------------------
-    const int per = (fc + RS_THREADS - 1) / RS_THREADS;     // <= 4
-    uint32_t loc[RS_FC_MAX / RS_THREADS];
-    uint32_t tsum = 0;
-#pragma unroll
-    for (int i = 0; i < RS_FC_MAX / RS_THREADS; ++i) {
-        const int idx = tid * per + i;
-        uint32_t v = (i < per && idx < fc) ? s_cnt[idx] : 0u;
-        loc[i] = tsum;
-        tsum += v;
-    }
-    const int lane = tid & 31, wid = tid >> 5;
-    uint32_t inc = tsum;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
-    if (lane == 31) s_warp[wid] = inc;
-    __syncthreads();
-    uint32_t woff = 0, total = 0;
-#pragma unroll
-    for (int w = 0; w < RS_THREADS / 32; ++w) { uint32_t t = s_warp[w]; if (w < wid) woff += t; total += t; }
-    const uint32_t toff = woff + inc - tsum;
-#pragma unroll
-    for (int i = 0; i < RS_FC_MAX / RS_THREADS; ++i) {
-        const int idx = tid * per + i;
-        if (i < per && idx < fc) { s_start[idx] = toff + loc[i]; s_cnt[idx] = toff + loc[i]; }   // cursor = start
-    }
-    if (tid == 0) s_start[fc] = total;
-
-    // ---- output base of the tile: decoupled look-back over the tile totals -------------
-    if (wid == 0) {
-        const unsigned long long ep = (unsigned long long)a.epoch << 34;
-        uint32_t excl = 0;
-        if (tile == 0) {
-            if (lane == 0) status[0] = ep | (2ull << 32) | total;
-        } else {
-            if (lane == 0) status[tile] = ep | (1ull << 32) | total;
-            int p = tile - 1;
-            for (;;) {
-                const int idx = p - lane;
-                unsigned long long st;
-                bool valid;
-                do {
-                    st = idx >= 0 ? status[idx] : (ep | (2ull << 32));
-                    valid = ((st >> 34) == (unsigned long long)a.epoch) && (((st >> 32) & 3ull) != 0);
-                } while (__any_sync(0xffffffffu, !valid));
-                const unsigned incl_mask = __ballot_sync(0xffffffffu, ((st >> 32) & 3ull) == 2ull);
-                uint32_t val = (uint32_t)st;
-                if (incl_mask) { const int first = __ffs(incl_mask) - 1; if (lane > first) val = 0; }
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
-                excl += val;
-                if (incl_mask) break;
-                p -= 32;
-            }
-            if (lane == 0) status[tile] = ep | (2ull << 32) | (unsigned long long)(excl + total);
-        }
-        if (lane == 0) {
-            s_base = excl;
-            if (tile == a.ntiles - 1) {
-                cs_new[(size_t)kend] = excl + total;
-                *ticket = 0;
-                if (excl + total != (uint32_t)n) atomicOr(err, AB_EF_OVERFLOW);     // an agent left its 3^D neighbourhood
-            }
-        }
-    }
-    __syncthreads();
-    const uint32_t base = s_base;
+    const uint32_t total = s_start[fc];
     const bool small = total <= RS_CAP;
     int32_t* ent_id = small ? s_ent_id : g_ent_id + base;
     int32_t* ent_s = small ? s_ent_s : g_ent_s + base;
-
-    // this tile's slice of the new cell_start
-    for (int i = tid; i < fc; i += RS_THREADS) cs_new[(size_t)kbeg + i] = base + s_start[i];
-
-    // ---- pass 2: entries into their cell segment (arrival order) -------------------------
+    uint32_t found = 0;
+    if (total != 0) {
+    // ---- entries into their cell segment (arrival order) ----------------------------------
     for (int sg = 0; sg < nseg; ++sg) {
         const uint32_t e = s_seg_end[sg];
         for (uint32_t s = s_seg_beg[sg] + tid; s < e; s += RS_THREADS) {
@@ -202,13 +126,22 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, c
             if (k >= kbeg && k < kend) {
                 const uint32_t lc = k - kbeg;
                 const uint32_t p = atomicAdd(&s_cnt[lc], 1u);
-                ent_id[p] = id_old[s];
-                ent_s[p] = (int32_t)s;
-                if (small) s_ent_lc[p] = (uint16_t)lc;
+                if (p < s_start[lc + 1]) {               // (always, unless the counts are inconsistent)
+                    ent_id[p] = id_old[s];
+                    ent_s[p] = (int32_t)s;
+                    if (small) s_ent_lc[p] = (uint16_t)lc;
+                }
+                ++found;
             }
         }
     }
+    // every agent counted into this tile must have been found in the 3^D neighbourhood
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) found += __shfl_xor_sync(0xffffffffu, found, o);
+    if ((tid & 31) == 0 && found) atomicAdd(&s_found, found);
     __syncthreads();
+    if (tid == 0 && s_found != total) atomicOr(err, AB_EF_OVERFLOW);     // an agent left its 3^D neighbourhood
+    if (s_found != total) return;
 
     // ---- canonical order inside every cell (by id), then coalesced output ------------------
     if (small) {
@@ -257,6 +190,8 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, c
             if (perm) perm[o] = s;
         }
     }
+
+    }   // total != 0
 
     // ---- per reference cell: count, Σ(pos - centre), Σ vel of this fine row's part, canonical order ---
     if (a.want_agg) {
@@ -384,19 +319,8 @@ static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool
     a.ntiles = a.nrows * a.tpr;
     a.has_vel = h->desc.kind == AB_SPACE_CONTINUOUS;
     a.want_agg = want_agg ? 1 : 0;
-    if ((size_t)a.ntiles + 1 > h->rs_status_len) {
-        if (h->rs_status) { AB_CUDA(h, cudaStreamSynchronize(h->stream)); AB_CUDA(h, cudaFree(h->rs_status)); h->rs_status = nullptr; }
-        AB_CUDA(h, cudaMalloc((void**)&h->rs_status, ((size_t)a.ntiles + 1) * sizeof(unsigned long long)));
-        AB_CUDA(h, cudaMemsetAsync(h->rs_status, 0, ((size_t)a.ntiles + 1) * sizeof(unsigned long long), h->stream));
-        h->rs_status_len = (size_t)a.ntiles + 1;
-        h->rs_epoch = 0;
-    }
-    h->rs_epoch = (h->rs_epoch + 1) & 0x3fffffffu;
-    if (h->rs_epoch == 0) {
-        AB_CUDA(h, cudaMemsetAsync(h->rs_status, 0, h->rs_status_len * sizeof(unsigned long long), h->stream));
-        h->rs_epoch = 1;
-    }
-    a.epoch = h->rs_epoch;
+    // the step kernel has counted the new keys into cell_count: scan them into the new cell_start
+    AB_TRY(ab_run_scan(h, h->cell_start_alt));
     if (want_agg) AB_TRY(ensure_agg(h));
     const bool extra = h->fields.size() > 2u;
     {
@@ -404,8 +328,7 @@ static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool
         k_resort<T, D><<<a.ntiles, RS_THREADS, 0, h->stream>>>(
             sp, a, h->cell_start, h->newkey, h->id[cur], (const T*)src_pos, (const T*)src_vel, h->cap, (int)h->n,
             (T*)h->fields[0].buf[nxt], (T*)h->fields[1].buf[nxt], h->id[nxt], h->key[nxt], h->cell_start_alt,
-            extra ? h->perm : nullptr, (T*)h->cell_agg, (int64_t)h->ncells, h->idtmp, (int32_t*)h->rank, h->rs_status,
-            h->scan_ticket, h->d_err);
+            extra ? h->perm : nullptr, (T*)h->cell_agg, (int64_t)h->ncells, h->idtmp, (int32_t*)h->rank, h->d_err);
     }
     std::swap(h->cell_start, h->cell_start_alt);
     AB_TRY(ab_permute_extra_fields(h));
@@ -418,8 +341,9 @@ static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool
 }
 
 // Re-sorts from (src_pos, src_vel, h->newkey) — all in the CURRENT slot order —
-// into the other buffer.  Requires that no agent moved further than one
-// reference cell (checked on the device: AB_EF_OVERFLOW otherwise).
+// into the other buffer.  Requires the new keys counted into h->cell_count and
+// that no agent moved further than one fine cell (checked on the device:
+// AB_EF_OVERFLOW otherwise).
 int ab_resort_tiled(ab_handle* h, const void* src_pos, const void* src_vel, bool want_agg) {
     if (h->dtype == AB_F64) return h->D == 2 ? resort_t<double, 2>(h, src_pos, src_vel, want_agg) : resort_t<double, 3>(h, src_pos, src_vel, want_agg);
     return h->D == 2 ? resort_t<float, 2>(h, src_pos, src_vel, want_agg) : resort_t<float, 3>(h, src_pos, src_vel, want_agg);
