@@ -294,19 +294,22 @@ __global__ void k_cells(SpaceDev<T, D> sp, const T* __restrict__ pos, const int3
 // ---------------------------------------------------------------------------
 // index build
 // ---------------------------------------------------------------------------
-int ab_run_scan(ab_handle* h, uint32_t* dst) {
-    uint32_t n = (uint32_t)h->nfine;
+// Exclusive scan of count[0..n) into start[0..n] (start[n] = total); zeroes count.  `count` must be
+// readable / writable up to the next multiple of SCAN_TILE.
+int ab_scan_u32(ab_handle* h, uint32_t* count, uint32_t* start, uint32_t n) {
     uint32_t ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+    if (ntiles == 0) ntiles = 1;
+    if (ntiles > h->scan_status_len) return ab_fail(h, AB_ERR_INVALID, "scan larger than the handle's status buffer");
     h->scan_epoch = (h->scan_epoch + 1) & 0x3fffffffu;
     if (h->scan_epoch == 0) {   // epoch wrapped: clear stale status words once
         AB_CUDA(h, cudaMemsetAsync(h->scan_status, 0, h->scan_status_len * sizeof(unsigned long long), h->stream));
         h->scan_epoch = 1;
     }
     AB_LAUNCH(h, "k_scan");
-    k_scan<<<ntiles, SCAN_THREADS, 0, h->stream>>>(h->cell_count, dst, n, ntiles, h->scan_status,
-                                                   h->scan_ticket, h->scan_epoch);
+    k_scan<<<ntiles, SCAN_THREADS, 0, h->stream>>>(count, start, n, ntiles, h->scan_status, h->scan_ticket, h->scan_epoch);
     return AB_OK;
 }
+int ab_run_scan(ab_handle* h, uint32_t* dst) { return ab_scan_u32(h, h->cell_count, dst, (uint32_t)h->nfine); }
 
 int ab_permute_extra_fields(ab_handle* h) {
     const int n = (int)h->n, cur = h->cur, nxt = cur ^ 1, TB = 256;
@@ -529,6 +532,7 @@ int ab_destroy(ab_handle* h) {
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     ab_comm_free(h);
+    ab_grid_free(h);
     free_population(h);
     void* ptrs[] = {h->cell_count, h->cell_start, h->scan_status, h->scan_ticket, h->d_err, h->scratch, h->scratch2,
                     h->cell_agg, h->cell_M, h->pairs_offsets, h->grid_ids, h->cell_start_alt};
@@ -621,6 +625,8 @@ int ab_resize(ab_handle* h, int64_t n) {
     h->slot_map_valid = true;
     h->index_valid = false;
     h->pairs_n = -1;
+    h->grid_cells_valid = false;
+    h->grid_cols_dirty = false;
     if (h->grid_ids) AB_CUDA(h, cudaMemsetAsync(h->grid_ids, 0, (size_t)h->ncells * sizeof(int32_t), h->stream));
     AB_CUDA(h, cudaStreamSynchronize(h->stream));
     return AB_OK;
@@ -632,6 +638,8 @@ int ab_upload(ab_handle* h, int field, const void* host, int64_t n) {
     if (n == 0) return AB_OK;
     if (!host) return ab_fail(h, AB_ERR_INVALID, "null host pointer");
     AB_CUDA(h, cudaSetDevice(h->device));
+    if (h->grid_cols_dirty) AB_TRY(ab_grid_sync_columns(h));
+    h->grid_cells_valid = false;
     ab_field& f = h->fields[field];
     size_t bytes = (size_t)n * f.ncomp * f.esize;
     void* stage;
@@ -656,6 +664,7 @@ int ab_download(ab_handle* h, int field, void* host, int64_t n) {
     if (n == 0) return AB_OK;
     if (!host) return ab_fail(h, AB_ERR_INVALID, "null host pointer");
     AB_CUDA(h, cudaSetDevice(h->device));
+    if (h->grid_cols_dirty) AB_TRY(ab_grid_sync_columns(h));
     ab_field& f = h->fields[field];
     size_t bytes = (size_t)n * f.ncomp * f.esize;
     void* stage;

@@ -35,6 +35,7 @@
 
 #define AB_VERSION 100
 
+#define AB_SCH_EMPTY INT32_MIN
 enum { AB_EF_OUTSIDE = 1, AB_EF_NUMERIC = 2, AB_EF_OCCUPIED = 4, AB_EF_OVERFLOW = 8 };
 
 struct ab_field {
@@ -120,7 +121,13 @@ struct ab_handle {
 
     // grid spaces
     int32_t* grid_ids = nullptr;       // GridSpaceSingle: id per cell (0 = empty), 1-based
+    int32_t* grid_group = nullptr;     // Schelling: group of the cell's occupant (AB_SCH_EMPTY when empty)
+    uint8_t* grid_mood = nullptr;      // Schelling: mood of the cell's occupant
+    bool grid_cells_valid = false;     // grid_group / grid_mood mirror the agent columns
+    bool grid_cols_dirty = false;      // agent columns (pos, mood) are stale w.r.t. the cell-major arrays
     int64_t last_moved = 0;
+    int64_t* h_moved = nullptr;        // pinned
+    uint64_t sch_tick = 0;             // steps taken so far (decorrelates the per-step permutations)
 
     ab_comm* comm = nullptr;
 
@@ -159,13 +166,16 @@ int ab_permute_extra_fields(ab_handle* h);     // applies h->perm (new slot -> o
 bool ab_resort_applicable(const ab_handle* h);
 int ab_resort_tiled(ab_handle* h, const void* src_pos, const void* src_vel, bool want_agg);
 int ab_ensure_agg(ab_handle* h);
-int ab_run_scan(ab_handle* h, uint32_t* dst);             // cell_count -> exclusive offsets in dst (zeroes cell_count)
+int ab_run_scan(ab_handle* h, uint32_t* dst);
+int ab_scan_u32(ab_handle* h, uint32_t* count, uint32_t* start, uint32_t n);   // count padded to a multiple of 2048             // cell_count -> exclusive offsets in dst (zeroes cell_count)
 size_t ab_dtype_size(int dtype);
 // cross-file internals (C++ linkage)
 void ab_comm_free(ab_handle* h);
 int ab_comm_active(const ab_handle* h);
 int ab_comm_step_flock(ab_handle* h, const ab_flock_params* p, int64_t nsteps);
 int ab_grid_build(ab_handle* h);
+int ab_grid_sync_columns(ab_handle* h);   // cell-major Schelling state -> agent columns (pos, mood)
+void ab_grid_free(ab_handle* h);
 int ab_grid_walk(ab_handle* h, const void* directions, const int64_t* active_ids, int64_t nactive, int ifempty);
 int ab_grid_nearby(ab_handle* h, const void* qpos, const int64_t* qids, int64_t nq, double r, int exclude_self,
                    int64_t* counts, const int64_t* offsets, int64_t* ids_out);
@@ -418,12 +428,19 @@ __device__ __forceinline__ FineRows fine_rows(const int* dims, int kb, int cy, i
 // coordinates, at most dims0 of them) of one reference cell row — one run per
 // fine row — in ascending-offset order, wrapping (periodic) or clipping
 // (non-periodic) at the x boundary.
-template <class F>
-__device__ __forceinline__ void emit_xrange(int dims0, bool periodic0, const uint32_t* __restrict__ cell_start_,
+struct CellStartPtr {            // cell_start lookup
+    const uint32_t* __restrict__ p;
+    __device__ __forceinline__ uint32_t operator()(size_t i) const { return p[i]; }
+};
+struct CellIdentity {            // "slot" = linear cell: the walk then yields runs of cells (dense grids)
+    __device__ __forceinline__ uint32_t operator()(size_t i) const { return (uint32_t)i; }
+};
+template <class CS, class F>
+__device__ __forceinline__ void emit_xrange(int dims0, bool periodic0, const CS& cell_start_,
                                             int kb, const FineRows& fr, int a, int b, int wrap, F&& f) {
     auto R = [&](int xa, int xe, int wr) {      // reference cells [xa, xe) of this row
         for (int t = 0; t < fr.n; ++t)
-            f(cell_start_[(size_t)fr.base[t] + ((uint32_t)xa << kb)], cell_start_[(size_t)fr.base[t] + ((uint32_t)xe << kb)], wr);
+            f(cell_start_((size_t)fr.base[t] + ((uint32_t)xa << kb)), cell_start_((size_t)fr.base[t] + ((uint32_t)xe << kb)), wr);
     };
     if (a > b) return;
     if (!periodic0) {
@@ -455,16 +472,15 @@ __device__ __forceinline__ void emit_xrange(int dims0, bool periodic0, const uin
 // f(slot_begin, slot_end, wrapmask) where bit d of wrapmask says the run was
 // reached across the periodic boundary of dimension d.  skip_zero drops the
 // zero offset (offsets_within_radius_no_0, grid_general.jl:165-179).
-template <int D, class F>
-__device__ __forceinline__ void for_each_run(const int* dims, const bool* periodic, int metric, const int* c0,
-                                             int r0, const uint32_t* __restrict__ cell_start, int kb,
-                                             bool skip_zero, F&& f) {
+template <int D, class CS, class F>
+__device__ __forceinline__ void for_each_run_cs(const int* dims, const bool* periodic, int metric, const int* c0,
+                                                int r0, const CS& cell_start, int kb, bool skip_zero, F&& f) {
     if (r0 < 0) {   // empty product → calculate_offsets pushes the zero offset (grid_general.jl:149)
         if (skip_zero) return;
         const FineRows fr = fine_rows<D>(dims, kb, c0[1], D == 3 ? c0[2] : 0);
         for (int t = 0; t < fr.n; ++t)
-            f(cell_start[(size_t)fr.base[t] + ((uint32_t)c0[0] << kb)],
-              cell_start[(size_t)fr.base[t] + ((uint32_t)(c0[0] + 1) << kb)], 0);
+            f(cell_start((size_t)fr.base[t] + ((uint32_t)c0[0] << kb)),
+              cell_start((size_t)fr.base[t] + ((uint32_t)(c0[0] + 1) << kb)), 0);
         return;
     }
     int lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
@@ -509,6 +525,13 @@ __device__ __forceinline__ void for_each_run(const int* dims, const bool* period
             }
         }
     }
+}
+
+template <int D, class F>
+__device__ __forceinline__ void for_each_run(const int* dims, const bool* periodic, int metric, const int* c0,
+                                             int r0, const uint32_t* __restrict__ cell_start, int kb,
+                                             bool skip_zero, F&& f) {
+    for_each_run_cs<D>(dims, periodic, metric, c0, r0, CellStartPtr{cell_start}, kb, skip_zero, f);
 }
 
 // Is cell `ct` visited by the walk above when started from cell `cf` with
