@@ -507,9 +507,9 @@ int ab_create(ab_space_desc* desc, int device, ab_handle** out) {
     CK(cudaMemset(h->scan_status, 0, h->scan_status_len * sizeof(unsigned long long)));
     CK(cudaMalloc((void**)&h->scan_ticket, sizeof(uint32_t)));
     CK(cudaMemset(h->scan_ticket, 0, sizeof(uint32_t)));
-    CK(cudaMalloc((void**)&h->d_err, sizeof(int)));
-    CK(cudaMemset(h->d_err, 0, sizeof(int)));
-    CK(cudaMallocHost((void**)&h->h_err, sizeof(int)));
+    CK(cudaMalloc((void**)&h->d_err, 4 * sizeof(int)));      // [0] error flags, [1] "moved further than one cell" flag
+    CK(cudaMemset(h->d_err, 0, 4 * sizeof(int)));
+    CK(cudaMallocHost((void**)&h->h_err, 4 * sizeof(int)));
     if (desc->kind == AB_SPACE_GRID_SINGLE) {
         CK(cudaMalloc((void**)&h->grid_ids, (size_t)ncells * sizeof(int32_t)));
         CK(cudaMemset(h->grid_ids, 0, (size_t)ncells * sizeof(int32_t)));
