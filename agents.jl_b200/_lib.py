@@ -74,7 +74,9 @@ _SIGS = {
     "ab_flock_last_counts": (C.c_int, [_H, C.c_void_p, C.c_int64]),
     "ab_comm_unique_id": (C.c_int, [C.c_void_p]),
     "ab_comm_init": (C.c_int, [_H, C.c_int, C.c_int, C.c_void_p]),
+    "ab_comm_set_capacity": (C.c_int, [_H, C.c_int64]),
     "ab_comm_slab": (C.c_int, [_H, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "ab_comm_halo": (C.c_int, [_H]),
     "ab_nlocal": (C.c_int64, [_H]),
     "ab_download_local": (C.c_int, [_H, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]),
     "ab_upload_local": (C.c_int, [_H, C.c_int, C.c_void_p, C.c_void_p, C.c_int64]),

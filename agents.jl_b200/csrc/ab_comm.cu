@@ -1,15 +1,469 @@
-// ab_comm.cu — multi-GPU slab decomposition (one process per GPU).
+// ab_comm.cu — multi-GPU slab decomposition of a ContinuousSpace (one process per GPU).
+//
+// The reference is single-task (src/simulations/step_standard.jl:9-23); this is the
+// scale-out of its hot path.  The space is cut into slabs of whole
+// reference-cell LAYERS along the last axis — the slowest axis of the column-major cell
+// key (src/spaces/grid_multi.jl:73), so a slab is one contiguous key range and the owned
+// agents are one contiguous slot range of the cell-sorted state.
+//
+// A rank's handle stores a WINDOW of nl + 2W layers: its nl owned layers, then the W
+// layers above (upper halo, owned by rank+1), then the W layers below (lower halo, owned
+// by rank-1); local layer = (global layer - first owned layer) mod (nl + 2W), so every
+// kernel's ordinary periodic index arithmetic finds the halo (ab_internal.cuh, SpaceDev).
+// Positions stay global: pos2cell (continuous.jl:112-113) is evaluated on the same
+// numbers as on one GPU, and cell centres / minimum images use global coordinates.
+//
+// One step on a rank (flock_steps_t, ab_flock.cu):
+//   sweep     owned birds AND the first halo layer on each side (a few % redundant work):
+//             the halo layer's birds that fly into the slab are this step's immigrants,
+//             computed locally from the halo instead of being received
+//   scan + re-sort of the owned rows (emigrants fall out: no owned tile collects them)
+//   exchange  (this file) the W top and W bottom owned layers of the NEW sorted state go
+//             to the neighbours in one NCCL group of two sends + two receives and replace
+//             their halo layers wholesale — halo refresh and migration in a single message.
+// Messages have a fixed capacity (header with the live count; no size round trip through
+// the host, the whole step stays asynchronous on the stream).  Because agents keep their
+// global ids and cells are id-ordered, an N-GPU run is bitwise identical to the 1-GPU run.
+#include <dlfcn.h>
+
+#include <algorithm>
+#include <cstring>
+
 #include "ab_internal.cuh"
 
-void ab_comm_free(ab_handle* h) {}
-int ab_comm_active(const ab_handle* h) { return 0; }
-int ab_comm_step_flock(ab_handle* h, const ab_flock_params*, int64_t) { return ab_fail(h, AB_ERR_COMM, "not implemented yet"); }
+#define AB_HALO_W 3   // radius-2 offset table (approximate search) of the recomputed first halo layer
+
+// ---- NCCL, bound at run time (dlopen: the process may already hold torch's libnccl.so.2) ----------
+typedef struct { char internal[128]; } nccl_uid_t;
+typedef void* nccl_comm_t;
+enum { NCCL_UINT8 = 1 };
+struct nccl_api {
+    void* lib = nullptr;
+    int (*GetUniqueId)(nccl_uid_t*) = nullptr;
+    int (*CommInitRank)(nccl_comm_t*, int, nccl_uid_t, int) = nullptr;
+    int (*CommDestroy)(nccl_comm_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    int (*Send)(const void*, size_t, int, int, nccl_comm_t, cudaStream_t) = nullptr;
+    int (*Recv)(void*, size_t, int, int, nccl_comm_t, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+};
+static nccl_api g_nccl;
+static std::string g_nccl_err;
+
+static bool nccl_load() {
+    if (g_nccl.lib) return true;
+    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    void* lib = nullptr;
+    for (const char* nm : names) {
+        lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+        if (lib) break;
+    }
+    if (!lib) { g_nccl_err = std::string("cannot load NCCL: ") + dlerror(); return false; }
+#define SYM(field, name)                                                    \
+    *(void**)(&g_nccl.field) = dlsym(lib, name);                            \
+    if (!g_nccl.field) { g_nccl_err = std::string("NCCL symbol missing: ") + name; return false; }
+    SYM(GetUniqueId, "ncclGetUniqueId");
+    SYM(CommInitRank, "ncclCommInitRank");
+    SYM(CommDestroy, "ncclCommDestroy");
+    SYM(GroupStart, "ncclGroupStart");
+    SYM(GroupEnd, "ncclGroupEnd");
+    SYM(Send, "ncclSend");
+    SYM(Recv, "ncclRecv");
+    SYM(GetErrorString, "ncclGetErrorString");
+#undef SYM
+    g_nccl.lib = lib;
+    return true;
+}
+
+struct ab_comm {
+    nccl_comm_t comm = nullptr;
+    int rank = 0, nranks = 1, lower = 0, upper = 0;
+    int64_t cap_agents = 0;          // message capacity C (agents)
+    int64_t want_cap = 0;            // requested by ab_comm_set_capacity (0 = derive from the population)
+    size_t msg_bytes = 0;
+    int msg_K = 0;
+    void* sendbuf[2] = {nullptr, nullptr};   // [0] bottom layers -> lower neighbour, [1] top layers -> upper neighbour
+    void* recvbuf[2] = {nullptr, nullptr};   // [0] from the upper neighbour (its bottom layers), [1] from the lower one
+    int64_t n_own = 0;
+    uint32_t* h_counts = nullptr;    // pinned {n_own, n_window}
+    int64_t exchanges = 0;
+};
+
+#define AB_NCCL(h, call)                                                                                   \
+    do {                                                                                                   \
+        int _r = (call);                                                                                   \
+        if (_r != 0) return ab_fail((h), AB_ERR_COMM, std::string("NCCL error: ") + g_nccl.GetErrorString(_r) + " in " #call); \
+    } while (0)
+
+// slab layout: gdl layers over nranks ranks, the first (gdl % nranks) ranks hold one layer more
+static void slab_of(int gdl, int nranks, int rank, int* first, int* count) {
+    const int base = gdl / nranks, rem = gdl % nranks;
+    *count = base + (rank < rem ? 1 : 0);
+    *first = rank * base + (rank < rem ? rank : rem);
+}
+
+// fine keys of one reference-cell layer of the window
+static int64_t keys_per_layer(const ab_handle* h) { return (h->nfine / h->dims[h->D - 1]); }
+static int64_t cells_per_layer(const ab_handle* h) { return (h->ncells / h->dims[h->D - 1]); }
+
+// ---------------------------------------------------------------------------------------------------
+// message: [hdr 16 B][cs slice (ncs + 1) u32, padded to 16 B][pos D x C][vel D x C][id C][key C]
+// ---------------------------------------------------------------------------------------------------
+struct MsgLayout {
+    size_t off_cs, off_pos, off_vel, off_id, off_key, bytes;
+    uint32_t ncs;
+    int64_t C;
+};
+static MsgLayout msg_layout(int D, size_t tsize, int64_t C, uint32_t ncs) {
+    MsgLayout m;
+    m.ncs = ncs;
+    m.C = C;
+    m.off_cs = 16;
+    m.off_pos = (m.off_cs + ((size_t)ncs + 1) * 4 + 15) / 16 * 16;
+    m.off_vel = m.off_pos + (size_t)D * C * tsize;
+    m.off_id = m.off_vel + (size_t)D * C * tsize;
+    m.off_key = m.off_id + (size_t)C * 4;
+    m.bytes = (m.off_key + (size_t)C * 4 + 15) / 16 * 16;
+    return m;
+}
+
+// Packs the boundary layers of the CURRENT sorted state: blockIdx.y = 0 bottom W owned layers (keys
+// [0, ncs)), 1 = top W owned layers (keys [kown - ncs, kown)).
+template <class E, int D>
+__global__ void __launch_bounds__(256)
+k_halo_pack(MsgLayout m, uint32_t kown, const uint32_t* __restrict__ cs, const E* __restrict__ pos,
+            const E* __restrict__ vel, const int32_t* __restrict__ id, const uint32_t* __restrict__ key, int64_t cap,
+            char* __restrict__ buf0, char* __restrict__ buf1, int* __restrict__ err) {
+    const int dir = blockIdx.y;
+    char* buf = dir == 0 ? buf0 : buf1;
+    const uint32_t k0 = dir == 0 ? 0u : kown - m.ncs;
+    const uint32_t s0 = cs[k0], s1 = cs[k0 + m.ncs];
+    uint32_t cnt = s1 - s0;
+    if (cnt > (uint32_t)m.C) {
+        if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(err, AB_EF_COMM);
+        cnt = (uint32_t)m.C;
+    }
+    const uint32_t t0 = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
+    if (t0 == 0) {
+        uint32_t* hdr = reinterpret_cast<uint32_t*>(buf);
+        hdr[0] = cnt; hdr[1] = k0; hdr[2] = m.ncs; hdr[3] = 0xAB200u;
+    }
+    uint32_t* mcs = reinterpret_cast<uint32_t*>(buf + m.off_cs);
+    for (uint32_t i = t0; i <= m.ncs; i += stride) mcs[i] = min(cs[k0 + i] - s0, cnt);
+    E* mpos = reinterpret_cast<E*>(buf + m.off_pos);
+    E* mvel = reinterpret_cast<E*>(buf + m.off_vel);
+    int32_t* mid = reinterpret_cast<int32_t*>(buf + m.off_id);
+    uint32_t* mkey = reinterpret_cast<uint32_t*>(buf + m.off_key);
+    for (uint32_t t = t0; t < cnt; t += stride) {
+        const size_t s = (size_t)s0 + t;
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            mpos[(size_t)d * m.C + t] = pos[(size_t)d * cap + s];
+            mvel[(size_t)d * m.C + t] = vel[(size_t)d * cap + s];
+        }
+        mid[t] = id[s];
+        mkey[t] = key[s];
+    }
+}
+
+// Installs the received layers as this rank's halo: blockIdx.y = 0 the upper neighbour's bottom layers
+// (keys [kown, kown + ncs)), 1 = the lower neighbour's top layers (keys [kown + ncs, kown + 2 ncs)).
+// Halo slots follow the owned ones: [n_own, n_own + cnt_u) and [n_own + cnt_u, n_own + cnt_u + cnt_l).
+template <class E, int D>
+__global__ void __launch_bounds__(256)
+k_halo_unpack(MsgLayout m, uint32_t kown, uint32_t* __restrict__ cs, E* __restrict__ pos, E* __restrict__ vel,
+              int32_t* __restrict__ id, uint32_t* __restrict__ key, int64_t cap, const char* __restrict__ buf0,
+              const char* __restrict__ buf1, int* __restrict__ err) {
+    const int src = blockIdx.y;
+    const uint32_t* h0 = reinterpret_cast<const uint32_t*>(buf0);
+    const uint32_t* h1 = reinterpret_cast<const uint32_t*>(buf1);
+    const char* buf = src == 0 ? buf0 : buf1;
+    const uint32_t* hdr = src == 0 ? h0 : h1;
+    const uint32_t n_own = cs[kown];                     // written by the scan of this step; never rewritten here
+    uint32_t cnt_u = h0[0], cnt_l = h1[0];
+    bool bad = h0[3] != 0xAB200u || h1[3] != 0xAB200u || h0[2] != m.ncs || h1[2] != m.ncs;
+    if ((uint64_t)n_own + cnt_u + cnt_l > (uint64_t)cap) bad = true;       // window does not fit the handle's capacity
+    if (bad) {
+        if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(err, AB_EF_COMM);
+        cnt_u = cnt_l = 0;
+    }
+    const uint32_t cnt = src == 0 ? cnt_u : cnt_l;
+    const uint32_t base = src == 0 ? n_own : n_own + cnt_u;
+    const uint32_t kdst = src == 0 ? kown : kown + m.ncs;
+    const uint32_t kdelta = kdst - hdr[1];               // sender's key frame -> this window's (mod 2^32)
+    const uint32_t t0 = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
+    const uint32_t* mcs = reinterpret_cast<const uint32_t*>(buf + m.off_cs);
+    for (uint32_t i = t0 + 1; i <= m.ncs; i += stride) cs[kdst + i] = base + (bad ? 0u : mcs[i]);
+    const E* mpos = reinterpret_cast<const E*>(buf + m.off_pos);
+    const E* mvel = reinterpret_cast<const E*>(buf + m.off_vel);
+    const int32_t* mid = reinterpret_cast<const int32_t*>(buf + m.off_id);
+    const uint32_t* mkey = reinterpret_cast<const uint32_t*>(buf + m.off_key);
+    for (uint32_t t = t0; t < cnt; t += stride) {
+        const size_t s = (size_t)base + t;
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            pos[(size_t)d * cap + s] = mpos[(size_t)d * m.C + t];
+            vel[(size_t)d * cap + s] = mvel[(size_t)d * m.C + t];
+        }
+        id[s] = mid[t];
+        key[s] = mkey[t] + kdelta;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------
+void ab_comm_free(ab_handle* h) {
+    ab_comm* c = h->comm;
+    if (!c) return;
+    for (int i = 0; i < 2; ++i) {
+        if (c->sendbuf[i]) cudaFree(c->sendbuf[i]);
+        if (c->recvbuf[i]) cudaFree(c->recvbuf[i]);
+    }
+    if (c->h_counts) cudaFreeHost(c->h_counts);
+    if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+    delete c;
+    h->comm = nullptr;
+}
+
+static int ensure_buffers(ab_handle* h) {
+    ab_comm* c = h->comm;
+    const uint32_t ncs = (uint32_t)(AB_HALO_W * keys_per_layer(h));
+    int64_t C = c->want_cap;
+    if (C <= 0) {
+        // default: 3x the mean population of W layers of this window (all ranks hold the same number of
+        // agents per layer on average; ranks MUST agree on C — callers with skewed states set it explicitly)
+        return ab_fail(h, AB_ERR_STATE, "ab_comm_set_capacity must be called before stepping a sharded handle");
+    }
+    C = (C + 63) / 64 * 64;
+    if (c->cap_agents == C && c->msg_K == h->K && c->sendbuf[0]) return AB_OK;
+    AB_CUDA(h, cudaStreamSynchronize(h->stream));
+    const MsgLayout m = msg_layout(h->D, h->tsize, C, ncs);
+    for (int i = 0; i < 2; ++i) {
+        if (c->sendbuf[i]) { AB_CUDA(h, cudaFree(c->sendbuf[i])); c->sendbuf[i] = nullptr; }
+        if (c->recvbuf[i]) { AB_CUDA(h, cudaFree(c->recvbuf[i])); c->recvbuf[i] = nullptr; }
+        AB_CUDA(h, cudaMalloc(&c->sendbuf[i], m.bytes));
+        AB_CUDA(h, cudaMalloc(&c->recvbuf[i], m.bytes));
+    }
+    c->cap_agents = C;
+    c->msg_bytes = m.bytes;
+    c->msg_K = h->K;
+    return AB_OK;
+}
+
+template <class E, int D>
+static int exchange_t(ab_handle* h, bool want_agg) {
+    ab_comm* c = h->comm;
+    AB_TRY(ensure_buffers(h));
+    const int cur = h->cur;
+    const uint32_t ncs = (uint32_t)(AB_HALO_W * keys_per_layer(h));
+    const uint32_t kown = (uint32_t)(h->win_nl * keys_per_layer(h));
+    const MsgLayout m = msg_layout(D, sizeof(E), c->cap_agents, ncs);
+    const int nb = (int)std::min<int64_t>(std::max<int64_t>((std::max<int64_t>(c->cap_agents / 4, ncs) + 255) / 256, 1), 592);
+    E* pos = (E*)h->fields[0].buf[cur];
+    E* vel = (E*)h->fields[1].buf[cur];
+    {
+        AB_LAUNCH(h, "k_halo_pack");
+        k_halo_pack<E, D><<<dim3(nb, 2), 256, 0, h->stream>>>(m, kown, h->cell_start, pos, vel, h->id[cur], h->key[cur],
+                                                             h->cap, (char*)c->sendbuf[0], (char*)c->sendbuf[1], h->d_err);
+    }
+    // one group: bottom layers -> lower neighbour, top layers -> upper neighbour; receives in the matching
+    // order (with 2 ranks both neighbours are the same peer: first send pairs with first receive)
+    AB_NCCL(h, g_nccl.GroupStart());
+    AB_NCCL(h, g_nccl.Send(c->sendbuf[0], m.bytes, NCCL_UINT8, c->lower, c->comm, h->stream));
+    AB_NCCL(h, g_nccl.Send(c->sendbuf[1], m.bytes, NCCL_UINT8, c->upper, c->comm, h->stream));
+    AB_NCCL(h, g_nccl.Recv(c->recvbuf[0], m.bytes, NCCL_UINT8, c->upper, c->comm, h->stream));
+    AB_NCCL(h, g_nccl.Recv(c->recvbuf[1], m.bytes, NCCL_UINT8, c->lower, c->comm, h->stream));
+    AB_NCCL(h, g_nccl.GroupEnd());
+    c->exchanges++;
+    {
+        AB_LAUNCH(h, "k_halo_unpack");
+        k_halo_unpack<E, D><<<dim3(nb, 2), 256, 0, h->stream>>>(m, kown, h->cell_start, pos, vel, h->id[cur], h->key[cur],
+                                                               h->cap, (const char*)c->recvbuf[0], (const char*)c->recvbuf[1],
+                                                               h->d_err);
+    }
+    if (want_agg) {
+        const int64_t cpl = cells_per_layer(h);
+        AB_TRY(ab_agg_range(h, (int64_t)h->win_nl * cpl, (int64_t)2 * AB_HALO_W * cpl));
+    }
+    return AB_OK;
+}
+
+int ab_comm_exchange(ab_handle* h, bool want_agg) {
+    if (!h->comm || !h->win_W) return ab_fail(h, AB_ERR_STATE, "handle is not sharded");
+    if (h->tsize == 8) return h->D == 2 ? exchange_t<uint64_t, 2>(h, want_agg) : exchange_t<uint64_t, 3>(h, want_agg);
+    return h->D == 2 ? exchange_t<uint32_t, 2>(h, want_agg) : exchange_t<uint32_t, 3>(h, want_agg);
+}
+
+int ab_comm_refresh_counts(ab_handle* h) {
+    ab_comm* c = h->comm;
+    if (!c) return AB_OK;
+    AB_TRY(ab_ensure_index(h));
+    const int64_t kown = h->win_nl * keys_per_layer(h);
+    AB_CUDA(h, cudaMemcpyAsync(&c->h_counts[0], h->cell_start + kown, 4, cudaMemcpyDeviceToHost, h->stream));
+    AB_CUDA(h, cudaMemcpyAsync(&c->h_counts[1], h->cell_start + h->nfine, 4, cudaMemcpyDeviceToHost, h->stream));
+    AB_CUDA(h, cudaStreamSynchronize(h->stream));
+    c->n_own = c->h_counts[0];
+    h->n = c->h_counts[1];
+    return AB_OK;
+}
+
+__global__ void k_rows_to_soa(const char* __restrict__ rows, char* __restrict__ dst, int64_t cap, int n, int ncomp, int esize) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= (int64_t)n * ncomp) return;
+    const int i = (int)(t / ncomp), c = (int)(t - (int64_t)i * ncomp);
+    for (int b = 0; b < esize; ++b) dst[((size_t)c * cap + i) * esize + b] = rows[(size_t)t * esize + b];
+}
+__global__ void k_soa_to_rows(const char* __restrict__ src, char* __restrict__ rows, int64_t cap, int n, int ncomp, int esize) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= (int64_t)n * ncomp) return;
+    const int i = (int)(t / ncomp), c = (int)(t - (int64_t)i * ncomp);
+    for (int b = 0; b < esize; ++b) rows[(size_t)t * esize + b] = src[((size_t)c * cap + i) * esize + b];
+}
+__global__ void k_gids_in(const int64_t* __restrict__ gids, int32_t* __restrict__ id, int n, int* __restrict__ err) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int64_t g = gids[i];
+    if (g < 1 || g > 2147483647LL) { atomicOr(err, AB_EF_OVERFLOW); id[i] = 0; return; }
+    id[i] = (int32_t)(g - 1);
+}
+__global__ void k_gids_out(const int32_t* __restrict__ id, int64_t* __restrict__ gids, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) gids[i] = (int64_t)id[i] + 1;
+}
 
 extern "C" {
-int ab_comm_unique_id(void* out128) { return AB_ERR_COMM; }
-int ab_comm_init(ab_handle* h, int rank, int nranks, const void* id) { return ab_fail(h, AB_ERR_COMM, "multi-GPU: not implemented yet"); }
-int ab_comm_slab(const ab_handle* h, int64_t* first_layer, int64_t* n_layers) { return AB_ERR_COMM; }
-int64_t ab_nlocal(const ab_handle* h) { return h ? h->n : 0; }
-int ab_download_local(ab_handle* h, int field, void* host, int64_t* ids_out, int64_t cap, int64_t* n_out) { return ab_fail(h, AB_ERR_COMM, "multi-GPU: not implemented yet"); }
-int ab_upload_local(ab_handle* h, int field, const void* host, const int64_t* global_ids, int64_t n) { return ab_fail(h, AB_ERR_COMM, "multi-GPU: not implemented yet"); }
+
+int ab_comm_unique_id(void* out128) {
+    if (!out128) return AB_ERR_INVALID;
+    if (!nccl_load()) return ab_fail(nullptr, AB_ERR_COMM, g_nccl_err);
+    nccl_uid_t id;
+    int r = g_nccl.GetUniqueId(&id);
+    if (r != 0) return ab_fail(nullptr, AB_ERR_COMM, std::string("ncclGetUniqueId: ") + g_nccl.GetErrorString(r));
+    memcpy(out128, &id, 128);
+    return AB_OK;
 }
+
+// Turns a freshly created ContinuousSpace handle (no agents yet) into rank `rank` of `nranks` slabs along
+// the last axis.  nccl_unique_id == NULL builds the window without a communicator (layout tests).
+int ab_comm_init(ab_handle* h, int rank, int nranks, const void* nccl_unique_id) {
+    if (!h) return AB_ERR_INVALID;
+    if (h->desc.kind != AB_SPACE_CONTINUOUS) return ab_fail(h, AB_ERR_INVALID, "slab decomposition is for ContinuousSpace handles");
+    if (h->comm || h->win_W) return ab_fail(h, AB_ERR_STATE, "handle is already sharded");
+    if (h->n != 0) return ab_fail(h, AB_ERR_STATE, "ab_comm_init must come before the agents are added");
+    if (nranks < 2 || rank < 0 || rank >= nranks) return ab_fail(h, AB_ERR_INVALID, "need nranks >= 2 and 0 <= rank < nranks");
+    const int D = h->D, gdl = h->dims[D - 1];
+    if (!h->desc.periodic[D - 1]) return ab_fail(h, AB_ERR_INVALID, "slab decomposition needs a periodic last axis");
+    int first, nl;
+    slab_of(gdl, nranks, rank, &first, &nl);
+    const int minl = gdl / nranks;
+    // every slab holds its own boundary layers (W) and the window must not overlap itself
+    if (minl < AB_HALO_W + 1 || minl + 2 * AB_HALO_W + (gdl % nranks ? 1 : 0) > gdl)
+        return ab_fail(h, AB_ERR_INVALID, "too few cell layers per rank for the halo width (need >= 4 layers per rank and >= 2 ranks' worth of space)");
+    AB_CUDA(h, cudaSetDevice(h->device));
+    ab_comm* c = new ab_comm();
+    c->rank = rank; c->nranks = nranks;
+    c->lower = (rank + nranks - 1) % nranks;
+    c->upper = (rank + 1) % nranks;
+    if (cudaMallocHost((void**)&c->h_counts, 2 * sizeof(uint32_t)) != cudaSuccess) { delete c; return ab_fail(h, AB_ERR_CUDA, "cudaMallocHost failed"); }
+    if (nccl_unique_id) {
+        if (!nccl_load()) { cudaFreeHost(c->h_counts); delete c; return ab_fail(h, AB_ERR_COMM, g_nccl_err); }
+        nccl_uid_t id;
+        memcpy(&id, nccl_unique_id, 128);
+        int r = g_nccl.CommInitRank(&c->comm, nranks, id, rank);
+        if (r != 0) { cudaFreeHost(c->h_counts); delete c; return ab_fail(h, AB_ERR_COMM, std::string("ncclCommInitRank: ") + g_nccl.GetErrorString(r)); }
+    }
+    h->comm = c;
+    h->win_gdl = gdl; h->win_goff = first; h->win_nl = nl; h->win_W = AB_HALO_W;
+    h->dims[D - 1] = nl + 2 * AB_HALO_W;
+    int64_t ncells = 1;
+    for (int d = 0; d < D; ++d) ncells *= h->dims[d];
+    h->ncells = ncells;
+    h->K = 1; h->kb = 0; h->ksh = 0;
+    h->nfine = ncells;
+    h->index_valid = false; h->agg_valid = false; h->pairs_n = -1;
+    return AB_OK;
+}
+
+int ab_comm_set_capacity(ab_handle* h, int64_t halo_agents) {
+    if (!h || !h->comm) return ab_fail(h, AB_ERR_STATE, "handle is not sharded");
+    if (halo_agents < 1 || halo_agents > 2000000000LL) return ab_fail(h, AB_ERR_INVALID, "bad halo capacity");
+    h->comm->want_cap = halo_agents;
+    return AB_OK;
+}
+
+int ab_comm_slab(const ab_handle* h, int64_t* first_layer, int64_t* n_layers) {
+    if (!h || !h->win_W) return AB_ERR_STATE;
+    if (first_layer) *first_layer = h->win_goff;
+    if (n_layers) *n_layers = h->win_nl;
+    return AB_OK;
+}
+int ab_comm_halo(const ab_handle* h) { return h ? h->win_W : 0; }
+
+int64_t ab_nlocal(const ab_handle* h) {
+    if (!h) return 0;
+    return h->comm ? h->comm->n_own : h->n;
+}
+
+// Rows in slot order (row i -> slot i).  Field 0 (pos) defines the population: n agents with the given
+// 1-based GLOBAL ids, all inside this rank's window; the other fields must follow with the same rows.
+int ab_upload_local(ab_handle* h, int field, const void* host, const int64_t* global_ids, int64_t n) {
+    if (!h || !h->win_W) return ab_fail(h, AB_ERR_STATE, "handle is not sharded");
+    if (field < 0 || field >= (int)h->fields.size()) return ab_fail(h, AB_ERR_INVALID, "bad field id");
+    if (n < 0 || n > h->cap) return ab_fail(h, AB_ERR_INVALID, "more rows than the handle's capacity (ab_resize first)");
+    if (field != 0 && n != h->n) return ab_fail(h, AB_ERR_INVALID, "upload pos (field 0) first; other fields must have the same rows");
+    if (n && (!host || (field == 0 && !global_ids))) return ab_fail(h, AB_ERR_INVALID, "null pointer");
+    AB_CUDA(h, cudaSetDevice(h->device));
+    ab_field& f = h->fields[field];
+    if (field == 0) { h->n = n; h->comm->n_own = 0; }
+    if (n == 0) return AB_OK;
+    const size_t bytes = (size_t)n * f.ncomp * f.esize, idb = field == 0 ? (size_t)n * 8 : 0;
+    char* stage;
+    AB_TRY(ab_scratch(h, bytes + idb + 512, (void**)&stage));
+    AB_CUDA(h, cudaMemcpyAsync(stage, host, bytes, cudaMemcpyHostToDevice, h->stream));
+    {
+        AB_LAUNCH(h, "k_rows_to_soa");
+        k_rows_to_soa<<<ab_blocks(n * f.ncomp, 256), 256, 0, h->stream>>>(stage, (char*)f.buf[h->cur], h->cap, (int)n, f.ncomp, (int)f.esize);
+    }
+    if (field == 0) {
+        char* ids_dev = stage + (bytes + 255) / 256 * 256;
+        AB_CUDA(h, cudaMemcpyAsync(ids_dev, global_ids, idb, cudaMemcpyHostToDevice, h->stream));
+        AB_LAUNCH(h, "k_gids_in");
+        k_gids_in<<<ab_blocks(n, 256), 256, 0, h->stream>>>((const int64_t*)ids_dev, h->id[h->cur], (int)n, h->d_err);
+        h->index_valid = false; h->agg_valid = false; h->pairs_n = -1;
+    }
+    AB_CUDA(h, cudaStreamSynchronize(h->stream));
+    return ab_check_device_errors(h);
+}
+
+// Owned agents (slot order) with their global ids.  host: cap rows of the field; ids_out: cap int64.
+int ab_download_local(ab_handle* h, int field, void* host, int64_t* ids_out, int64_t cap, int64_t* n_out) {
+    if (!h || !h->win_W) return ab_fail(h, AB_ERR_STATE, "handle is not sharded");
+    if (field < 0 || field >= (int)h->fields.size()) return ab_fail(h, AB_ERR_INVALID, "bad field id");
+    AB_CUDA(h, cudaSetDevice(h->device));
+    AB_TRY(ab_comm_refresh_counts(h));
+    const int64_t n = h->comm->n_own;
+    if (n_out) *n_out = n;
+    if (n > cap) return ab_fail(h, AB_ERR_INVALID, "host buffer smaller than the owned population");
+    if (n == 0) return AB_OK;
+    ab_field& f = h->fields[field];
+    const size_t bytes = (size_t)n * f.ncomp * f.esize, idb = ids_out ? (size_t)n * 8 : 0;
+    char* stage;
+    AB_TRY(ab_scratch(h, bytes + idb + 512, (void**)&stage));
+    {
+        AB_LAUNCH(h, "k_soa_to_rows");
+        k_soa_to_rows<<<ab_blocks(n * f.ncomp, 256), 256, 0, h->stream>>>((const char*)f.buf[h->cur], stage, h->cap, (int)n, f.ncomp, (int)f.esize);
+    }
+    if (host) AB_CUDA(h, cudaMemcpyAsync(host, stage, bytes, cudaMemcpyDeviceToHost, h->stream));
+    if (ids_out) {
+        char* ids_dev = stage + (bytes + 255) / 256 * 256;
+        AB_LAUNCH(h, "k_gids_out");
+        k_gids_out<<<ab_blocks(n, 256), 256, 0, h->stream>>>(h->id[h->cur], (int64_t*)ids_dev, (int)n);
+        AB_CUDA(h, cudaMemcpyAsync(ids_out, ids_dev, idb, cudaMemcpyDeviceToHost, h->stream));
+    }
+    AB_CUDA(h, cudaStreamSynchronize(h->stream));
+    return AB_OK;
+}
+
+}  // extern "C"

@@ -89,6 +89,7 @@ int ab_check_device_errors(ab_handle* h) {
     if (e & AB_EF_NUMERIC) return ab_fail(h, AB_ERR_NUMERIC, "InexactError: a NaN/Inf position reached a cell computation");
     if (e & AB_EF_OUTSIDE) return ab_fail(h, AB_ERR_OUTSIDE, "position is outside space extent!");
     if (e & AB_EF_OCCUPIED) return ab_fail(h, AB_ERR_OCCUPIED, "Cannot add agent to occupied position");
+    if (e & AB_EF_COMM) return ab_fail(h, AB_ERR_COMM, "halo exchange overflow: more agents in the boundary layers than the message capacity (ab_comm_set_capacity) or than the handle's capacity (ab_resize)");
     if (e & AB_EF_OVERFLOW) return ab_fail(h, AB_ERR_INVALID, "device-side failure: id out of range, or an agent left its cell neighbourhood in one tiled step");
     return ab_fail(h, AB_ERR_INVALID, "device-side failure");
 }
@@ -113,7 +114,9 @@ __global__ void k_count(SpaceDev<T, D> sp, const T* __restrict__ pos, int64_t ca
         for (int d = 0; d < D; ++d) nan = nan || !(p[d] == p[d]) || isinf(p[d]);
         atomicOr(err, nan ? AB_EF_NUMERIC : AB_EF_OUTSIDE);
     }
-    uint32_t k = device_key<T, D>(sp, p, c);
+    bool inwin = true;
+    uint32_t k = device_key<T, D>(sp, p, c, &inwin);
+    if (!inwin) { atomicOr(err, AB_EF_OVERFLOW); k = 0; }     // agent uploaded to a rank whose slab window does not hold it
     newkey[s] = k;
     rank[s] = atomicAdd(&cell_count[k], 1u);
 }
@@ -407,6 +410,7 @@ int ab_set_refine(ab_handle* h, int K) {
 }
 
 int ab_ensure_slot_map(ab_handle* h) {
+    if (h->win_W) return ab_fail(h, AB_ERR_STATE, "id-addressed calls are not available on a sharded (slab-window) handle; use ab_upload_local / ab_download_local");
     if (h->slot_map_valid) return AB_OK;
     if (h->n > 0) {
         AB_LAUNCH(h, "k_slot_map");
@@ -660,6 +664,7 @@ int ab_upload(ab_handle* h, int field, const void* host, int64_t n) {
 
 int ab_download(ab_handle* h, int field, void* host, int64_t n) {
     if (field < 0 || field >= (int)h->fields.size()) return ab_fail(h, AB_ERR_INVALID, "bad field id");
+    if (h->win_W) return ab_fail(h, AB_ERR_STATE, "use ab_download_local on a sharded handle");
     if (n != h->n) return ab_fail(h, AB_ERR_INVALID, "download length must equal the agent count");
     if (n == 0) return AB_OK;
     if (!host) return ab_fail(h, AB_ERR_INVALID, "null host pointer");
@@ -691,6 +696,7 @@ int ab_build_index(ab_handle* h) {
 
 int ab_cells(ab_handle* h, int32_t* out_cells, int64_t n) {
     if (h->desc.kind != AB_SPACE_CONTINUOUS) return ab_fail(h, AB_ERR_INVALID, "ab_cells is for ContinuousSpace handles");
+    if (h->win_W) return ab_fail(h, AB_ERR_STATE, "not available on a sharded handle");
     if (n != h->n) return ab_fail(h, AB_ERR_INVALID, "length must equal the agent count");
     if (n == 0) return AB_OK;
     AB_CUDA(h, cudaSetDevice(h->device));

@@ -91,6 +91,7 @@ __device__ __noinline__ void flock_accumulate_generic(const SpaceDev<T, D>& sp, 
             if (!((long long)sp.dims[d] >= 2LL * gr + 3)) slowmask |= 1 << d;
         }
     }
+    if (sp.W) slowmask |= 1 << (D - 1);     // slab window: local wrap says nothing about the global boundary — always minimum image
     int N = 0;
     for_each_run<D>(sp.dims, sp.periodic, AB_METRIC_EUCLIDEAN, c, gr, cell_start, sp.kb, false,
                     [&](uint32_t b, uint32_t e, int wrap) {
@@ -269,13 +270,13 @@ static int launch_cell_M(ab_handle* h, const SpaceDev<T, D>& sp) {
 template <class T, int D, bool EXACT>
 static int launch_fine(ab_handle* h, const SpaceDev<T, D>& sp, const FlockU<T>& u, int32_t* ncount) {
     const int cur = h->cur;
-    const int n = (int)h->n;
+    const int n = h->win_W ? (int)h->cap : (int)h->n;      // slab window: grid over the capacity, live count read on the device
     const int TB = 128;
     AB_LAUNCH(h, EXACT ? "k_flock_fine_exact" : "k_flock_fine");
     k_flock_fine<T, D, EXACT><<<ab_blocks(n, TB), TB, 0, h->stream>>>(
         sp, u, (const T*)h->fields[0].buf[cur], (const T*)h->fields[1].buf[cur], h->key[cur], h->cell_start,
         (const T*)h->cell_M, (int64_t)h->ncells, h->cap, n, (T*)h->tmp_pos, (T*)h->tmp_vel, h->newkey, h->cell_count,
-        h->id[cur], ncount, h->d_err);
+        h->id[cur], ncount, h->d_err, h->win_W ? h->cell_start + h->nfine : nullptr);
     return AB_OK;
 }
 
@@ -303,6 +304,7 @@ static int flock_steps_t(ab_handle* h, const ab_flock_params* p, int64_t nsteps)
     FinePlan plan;
     if (p->kernel != 1) fine = plan_fine<T, D>(h, p, exact, &plan);
     if (p->kernel == 2 && !fine) return ab_fail(h, AB_ERR_INVALID, "fine-grid flock kernel not applicable to this configuration");
+    if (h->win_W && !fine) return ab_fail(h, AB_ERR_INVALID, "a sharded handle runs the fine-grid flock step only (uniform parameters, visual_distance <= spacing, >= 6 cells per axis)");
     if (fine) AB_TRY(ab_set_refine(h, plan.K));
     AB_TRY(ab_ensure_index(h));
     SpaceDev<T, D> sp = make_space<T, D>(h);
@@ -315,11 +317,12 @@ static int flock_steps_t(ab_handle* h, const ab_flock_params* p, int64_t nsteps)
         const int cur = h->cur;
         const T* pos = (const T*)h->fields[0].buf[cur];
         const T* vel = (const T*)h->fields[1].buf[cur];
-        int32_t* ncount = (st == nsteps - 1) ? h->ncount : nullptr;   // neighbour counts by id (diagnostic)
+        int32_t* ncount = (st == nsteps - 1 && !h->win_W) ? h->ncount : nullptr;   // neighbour counts by id (diagnostic)
         if (fine) {
             if (exact) AB_TRY((launch_fine<T, D, true>(h, sp, u, ncount)));
             else AB_TRY((launch_fine<T, D, false>(h, sp, u, ncount)));
             AB_TRY(ab_resort_tiled(h, h->tmp_pos, h->tmp_vel, !exact));
+            if (h->win_W) AB_TRY(ab_comm_exchange(h, !exact));        // halo refresh + migration (ab_comm.cu)
             if (!exact) AB_TRY((launch_cell_M<T, D>(h, sp)));
         } else {
             const T* pa = pa_field >= 0 ? (const T*)h->fields[pa_field].buf[cur] : nullptr;
@@ -362,12 +365,12 @@ int ab_step_flock(ab_handle* h, const ab_flock_params* p, int64_t nsteps) {
     if (nsteps < 0) return ab_fail(h, AB_ERR_INVALID, "negative nsteps");
     AB_CUDA(h, cudaSetDevice(h->device));
     if (h->n == 0 || nsteps == 0) return AB_OK;
-    if (ab_comm_active(h)) return ab_comm_step_flock(h, p, nsteps);
     int rc;
     if (h->dtype == AB_F64) rc = h->D == 2 ? flock_steps_t<double, 2>(h, p, nsteps) : flock_steps_t<double, 3>(h, p, nsteps);
     else rc = h->D == 2 ? flock_steps_t<float, 2>(h, p, nsteps) : flock_steps_t<float, 3>(h, p, nsteps);
     AB_TRY(rc);
     AB_TRY(ab_check_device_errors(h));
+    if (h->win_W) AB_TRY(ab_comm_refresh_counts(h));
     float ms = 0;
     AB_CUDA(h, cudaEventElapsedTime(&ms, h->ev0, h->ev1));
     h->last_step_ms = ms;
@@ -375,6 +378,7 @@ int ab_step_flock(ab_handle* h, const ab_flock_params* p, int64_t nsteps) {
 }
 
 int ab_flock_last_counts(ab_handle* h, int32_t* counts, int64_t n) {
+    if (h->win_W) return ab_fail(h, AB_ERR_STATE, "not available on a sharded handle");
     if (n != h->n) return ab_fail(h, AB_ERR_INVALID, "length must equal the agent count");
     if (n == 0) return AB_OK;
     AB_CUDA(h, cudaSetDevice(h->device));

@@ -170,7 +170,8 @@ __device__ __forceinline__ bool pos2cell0_fast(const SpaceDev<T, D>& sp, const T
         const T cq = ceil(qa);
         const T margin = qa * eps8;
         // (cq - qa) in (margin, 1 - margin): not near an integer; 0 < cq <= dims
-        if (!(cq - qa > margin && cq - qa < T(1) - margin && cq >= T(1) && cq <= (T)sp.dims[d])) fastok = false;
+        const int lim = d == D - 1 ? sp.gdl : sp.dims[d];
+        if (!(cq - qa > margin && cq - qa < T(1) - margin && cq >= T(1) && cq <= (T)lim)) fastok = false;
         c[d] = (int)cq - 1;
     }
     if (fastok) return true;
@@ -183,20 +184,28 @@ k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T
              const uint32_t* __restrict__ key, const uint32_t* __restrict__ cs, const T* __restrict__ M,
              int64_t ncells, int64_t cap, int n, T* __restrict__ npos, T* __restrict__ nvel,
              uint32_t* __restrict__ newkey, uint32_t* __restrict__ cell_count, const int32_t* __restrict__ ids,
-             int32_t* __restrict__ ncount, int* __restrict__ err) {
+             int32_t* __restrict__ ncount, int* __restrict__ err, const uint32_t* __restrict__ nslots) {
     constexpr int NC = FineCfg<D>::NC;
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= n) return;
+    // slab window: the slot count lives on the device (migration changes it without a host round trip)
+    if (s >= (nslots ? (int)*nslots : n)) return;
     const int K = sp.K, kb = sp.kb;
-    T p[D], v[D];
-    int f[D], c[D];
-#pragma unroll
-    for (int d = 0; d < D; ++d) { p[d] = pos[(size_t)d * cap + s]; v[d] = vel[(size_t)d * cap + s]; }
+    int f[D], c[D], cg[D];
     const uint32_t k = key[s];
     key_to_fine<T, D>(sp, k, f);
 #pragma unroll
-    for (int d = 0; d < D; ++d) c[d] = f[d] >> kb;
-    const int gr = grid_radius_12<T, D>(sp, p, c, fp);
+    for (int d = 0; d < D; ++d) cg[d] = c[d] = f[d] >> kb;
+    if (sp.W) {
+        // owned layers plus the first halo layer on each side (recomputed here instead of being
+        // received: its birds may enter the owned layers in this step); outer halo slots are skipped
+        const int l = c[D - 1];
+        if (!(l <= sp.nl || l == sp.nl + 2 * sp.W - 1)) return;
+        cg[D - 1] = local_to_global_last<T, D>(sp, l);
+    }
+    T p[D], v[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d) { p[d] = pos[(size_t)d * cap + s]; v[d] = vel[(size_t)d * cap + s]; }
+    const int gr = grid_radius_12<T, D>(sp, p, cg, fp);
     const T sep2 = fp.separation * fp.separation;
     T cohere[D], separate[D], match[D];
 #pragma unroll
@@ -205,7 +214,7 @@ k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T
     bool fast = gr == 1 || gr == 2;
     T q[D];
 #pragma unroll
-    for (int d = 0; d < D; ++d) q[d] = p[d] - sp.spacing * ((T)(c[d] + 1) - T(0.5));
+    for (int d = 0; d < D; ++d) q[d] = p[d] - sp.spacing * ((T)(cg[d] + 1) - T(0.5));
     if (EXACT && fast) {
         // birds within tau of a fine-cell boundary could see (in floating point) a neighbour that the
         // clipped sweep below does not visit: they take the reference walk.
@@ -232,6 +241,9 @@ k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T
         const T thr = fp.thr;
         const int R = EXACT ? K : 1;                   // fine-cell reach of the sweep
         const int fd0 = sp.dims[0] << kb, fd1 = sp.dims[1] << kb, fd2 = D == 3 ? (sp.dims[2] << kb) : 1;
+        // slab window: rows are indexed in the local (window-periodic) frame, but whether a row lies across
+        // the space's periodic boundary — i.e. needs the minimum image — is decided on GLOBAL fine rows
+        const int gf_last = (cg[D - 1] << kb) | (f[D - 1] & (K - 1)), gfdl = sp.gdl << kb;
         // two instantiations of the pair loop: runs reached across a periodic boundary apply the
         // reference's minimum-image rule (utilities.jl:185-193); all other runs are plain differences
         auto sweep_t = [&](uint32_t jb, uint32_t je, int wrap, auto wrapped) {
@@ -276,6 +288,7 @@ k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T
                     fz = fz < 0 ? fz + fd2 : fz - fd2;
                     wz = 4;
                 }
+                if (sp.W) { const int g = gf_last + rz; wz = (g < 0 || g >= gfdl) ? 4 : 0; }
             }
             // phase 1: slot bounds of the main run of every row — independent loads, all in flight together
             uint32_t rbv[NROW], jb[NROW], je[NROW];
@@ -303,6 +316,7 @@ k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T
                     fy = fy < 0 ? fy + fd1 : fy - fd1;
                     wy = 2;
                 }
+                if (D == 2 && sp.W) { const int g = gf_last + ry; wy = (g < 0 || g >= gfdl) ? 2 : 0; }
                 const uint32_t rb = (D == 3 ? ((uint32_t)fz * (uint32_t)fd1 + (uint32_t)fy) : (uint32_t)fy) * (uint32_t)fd0;
                 rbv[i] = rb; ulov[i] = ulo; uhiv[i] = uhi; wrv[i] = wy | wz;
                 const int a0 = max(ulo, 0), a1 = min(uhi, fd0 - 1);
@@ -326,7 +340,9 @@ k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T
     flock_epilogue<T, D>(sp, p, v, cohere, separate, match, N, fp, np_, nv, err);
     int nc[D];
     if (!pos2cell0_fast<T, D>(sp, np_, nc)) atomicOr(err, AB_EF_NUMERIC);
-    const uint32_t nk = device_key<T, D>(sp, np_, nc);
+    bool inwin = true;
+    uint32_t nk = device_key<T, D>(sp, np_, nc, &inwin);
+    if (!inwin) { atomicOr(err, AB_EF_OVERFLOW); nk = 0; }
 #pragma unroll
     for (int d = 0; d < D; ++d) { npos[(size_t)d * cap + s] = np_[d]; nvel[(size_t)d * cap + s] = nv[d]; }
     newkey[s] = nk;

@@ -36,7 +36,7 @@
 #define AB_VERSION 100
 
 #define AB_SCH_EMPTY INT32_MIN
-enum { AB_EF_OUTSIDE = 1, AB_EF_NUMERIC = 2, AB_EF_OCCUPIED = 4, AB_EF_OVERFLOW = 8 };
+enum { AB_EF_OUTSIDE = 1, AB_EF_NUMERIC = 2, AB_EF_OCCUPIED = 4, AB_EF_OVERFLOW = 8, AB_EF_COMM = 16 };
 
 struct ab_field {
     std::string name;
@@ -130,6 +130,8 @@ struct ab_handle {
     uint64_t sch_tick = 0;             // steps taken so far (decorrelates the per-step permutations)
 
     ab_comm* comm = nullptr;
+    // slab window along the last axis (multi-GPU, ab_comm.cu); W == 0: the handle holds the whole space
+    int win_gdl = 0, win_goff = 0, win_nl = 0, win_W = 0;
 
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     double last_step_ms = 0;
@@ -166,13 +168,14 @@ int ab_permute_extra_fields(ab_handle* h);     // applies h->perm (new slot -> o
 bool ab_resort_applicable(const ab_handle* h);
 int ab_resort_tiled(ab_handle* h, const void* src_pos, const void* src_vel, bool want_agg);
 int ab_ensure_agg(ab_handle* h);
+int ab_agg_range(ab_handle* h, int64_t cell0, int64_t ncell);
 int ab_run_scan(ab_handle* h, uint32_t* dst);
 int ab_scan_u32(ab_handle* h, uint32_t* count, uint32_t* start, uint32_t n);   // count padded to a multiple of 2048             // cell_count -> exclusive offsets in dst (zeroes cell_count)
 size_t ab_dtype_size(int dtype);
 // cross-file internals (C++ linkage)
 void ab_comm_free(ab_handle* h);
-int ab_comm_active(const ab_handle* h);
-int ab_comm_step_flock(ab_handle* h, const ab_flock_params* p, int64_t nsteps);
+int ab_comm_exchange(ab_handle* h, bool want_agg);   // halo refresh + migration after a re-sort (slab window)
+int ab_comm_refresh_counts(ab_handle* h);            // owned / window agent counts back to the host
 int ab_grid_build(ab_handle* h);
 int ab_grid_sync_columns(ab_handle* h);   // cell-major Schelling state -> agent columns (pos, mood)
 void ab_grid_free(ab_handle* h);
@@ -209,6 +212,14 @@ template <class T, int D> struct SpaceDev {
     int K;        // fine cells per reference cell and dimension (1 or 2)
     int kb;       // log2(K): fine coordinate = (reference coordinate << kb) | upper-half bit
     int ksh;      // log2(K^D)
+    // Slab window along the LAST axis (multi-GPU).  dims[D-1] is the number of layers this handle
+    // STORES: nl owned layers, then W upper-halo layers, then W lower-halo layers, so local layer
+    // l = (global layer - goff) mod (nl + 2W) and the ordinary periodic index arithmetic on dims[]
+    // finds every neighbour.  Positions, extents and cell centres stay GLOBAL (bit-exact pos2cell).
+    int gdl;      // global number of layers (== dims[D-1] when W == 0)
+    int goff;     // global layer of local layer 0
+    int nl;       // owned layers (== dims[D-1] when W == 0)
+    int W;        // halo layers on each side; 0 = not windowed
 };
 
 template <class T, int D> static inline SpaceDev<T, D> make_space(const ab_handle* h) {
@@ -226,6 +237,10 @@ template <class T, int D> static inline SpaceDev<T, D> make_space(const ab_handl
     s.K = h->K;
     s.kb = h->kb;
     s.ksh = h->ksh;
+    s.W = h->win_W;
+    s.gdl = h->win_W ? h->win_gdl : h->dims[D - 1];
+    s.goff = h->win_W ? h->win_goff : 0;
+    s.nl = h->win_W ? h->win_nl : h->dims[D - 1];
     return s;
 }
 
@@ -271,7 +286,8 @@ __device__ __forceinline__ bool pos2cell0(const SpaceDev<T, D>& sp, const T* p, 
         if (!(cq <= T(2147483000.0)) || !(cq >= T(-2147483000.0))) { ok = false; cq = T(1); }   // NaN / Inf / huge
         int ci = (int)cq;
         ci = ci < 1 ? 1 : ci;
-        if (ci > sp.dims[d]) { ok = false; ci = sp.dims[d]; }
+        const int lim = d == D - 1 ? sp.gdl : sp.dims[d];       // pos2cell is global; dims[D-1] may be a slab window
+        if (ci > lim) { ok = false; ci = lim; }
         c[d] = ci - 1;
     }
     return ok;
@@ -292,16 +308,39 @@ template <int D> __device__ __forceinline__ void unlin_cell(const int* dims, uin
     c[D - 1] = (int)lin;
 }
 
+// Slab window (multi-GPU): local layer <-> global layer of the last axis.
+template <class T, int D> __device__ __forceinline__ int local_to_global_last(const SpaceDev<T, D>& sp, int l) {
+    if (sp.W == 0) return l;
+    int g = (l >= sp.nl + sp.W ? l - (sp.nl + 2 * sp.W) : l) + sp.goff;    // lower-halo layers sit below layer 0
+    if (g < 0) g += sp.gdl;
+    else if (g >= sp.gdl) g -= sp.gdl;
+    return g;
+}
+template <class T, int D> __device__ __forceinline__ int global_to_local_last(const SpaceDev<T, D>& sp, int g, bool* ok) {
+    if (sp.W == 0) return g;
+    int l = g - sp.goff;
+    if (l < 0) l += sp.gdl;
+    if (l < sp.nl + sp.W) return l;                    // owned or upper halo
+    l -= sp.gdl;
+    if (l >= -sp.W) return l + sp.nl + 2 * sp.W;       // lower halo
+    *ok = false;                                       // outside this rank's window
+    return 0;
+}
+
 // Device cell key: column-major linear index of the agent's FINE cell over the
 // fine grid (dims << kb).  Fine coordinate = reference coordinate * K + (position
 // above the reference cell's centre — cell_center, continuous.jl:116-117), so
 // fine cells nest exactly inside the bit-exact reference cells.
+// `c` are GLOBAL reference-cell coordinates (pos2cell0); *inwin (optional) reports whether the cell lies in
+// this handle's slab window.
 template <class T, int D>
-__device__ __forceinline__ uint32_t device_key(const SpaceDev<T, D>& sp, const T* p, const int* c) {
+__device__ __forceinline__ uint32_t device_key(const SpaceDev<T, D>& sp, const T* p, const int* c, bool* inwin = nullptr) {
     uint32_t f[D];
+    bool ok = true;
 #pragma unroll
     for (int d = 0; d < D; ++d) {
-        f[d] = (uint32_t)c[d] << sp.kb;
+        const int cl = d == D - 1 ? global_to_local_last<T, D>(sp, c[d], &ok) : c[d];
+        f[d] = (uint32_t)cl << sp.kb;
         if (sp.K == 2) {
             T centre = sp.spacing * ((T)(c[d] + 1) - T(0.5));
             f[d] |= (p[d] > centre ? 1u : 0u);
@@ -310,6 +349,7 @@ __device__ __forceinline__ uint32_t device_key(const SpaceDev<T, D>& sp, const T
     uint32_t lin = f[D - 1];
 #pragma unroll
     for (int d = D - 2; d >= 0; --d) lin = lin * ((uint32_t)sp.dims[d] << sp.kb) + f[d];
+    if (inwin) *inwin = ok;
     return lin;
 }
 // fine coordinates of a device key

@@ -206,7 +206,8 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, c
             const uint32_t b = base + s_start[(size_t)c << kb], e = base + s_start[(size_t)(c + 1) << kb];
             const int cx = (x0 >> kb) + c;
             const uint32_t refcell = (D == 3 ? ((uint32_t)cz * sp.dims[1] + cy) : (uint32_t)cy) * (uint32_t)sp.dims[0] + (uint32_t)cx;
-            const int cc[3] = {cx, cy, cz};
+            int cc[3] = {cx, cy, cz};
+            cc[D - 1] = local_to_global_last<T, D>(sp, cc[D - 1]);     // centres are global (slab window)
             T acc[2 * D];
 #pragma unroll
             for (int d = 0; d < 2 * D; ++d) acc[d] = T(0);
@@ -239,20 +240,21 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, c
 template <class T, int D>
 __global__ void __launch_bounds__(256)
 k_cell_agg(SpaceDev<T, D> sp, const uint32_t* __restrict__ cs, const T* __restrict__ pos, const T* __restrict__ vel,
-           int64_t cap, uint32_t ncells, T* __restrict__ agg, int64_t agg_stride) {
+           int64_t cap, uint32_t cell0, uint32_t ncells, T* __restrict__ agg, int64_t agg_stride) {
     constexpr int NC = 1 + 2 * D;
     const int K = sp.K, kb = sp.kb;
     const int nfr = D == 2 ? K : K * K;
     const uint32_t g = (blockIdx.x * blockDim.x + threadIdx.x) >> 3;
     const int gl = threadIdx.x & 7;
     const bool live = g < ncells * (uint32_t)nfr;
-    const uint32_t c = live ? g / (uint32_t)nfr : 0;
-    const int part = live ? (int)(g - c * (uint32_t)nfr) : 0;
+    const uint32_t c = cell0 + (live ? g / (uint32_t)nfr : 0);          // cells [cell0, cell0 + ncells)
+    const int part = live ? (int)(g - (c - cell0) * (uint32_t)nfr) : 0;
     int cc[D];
     unlin_cell<D>(sp.dims, c, cc);
     const FineRows fr = fine_rows<D>(sp.dims, kb, cc[1], D == 3 ? cc[2] : 0);
     const uint32_t b = cs[(size_t)fr.base[part] + ((uint32_t)cc[0] << kb)];
     const uint32_t e = live ? cs[(size_t)fr.base[part] + ((uint32_t)(cc[0] + 1) << kb)] : b;
+    cc[D - 1] = local_to_global_last<T, D>(sp, cc[D - 1]);               // centres are global (slab window)
     T acc[2 * D];
 #pragma unroll
     for (int d = 0; d < 2 * D; ++d) acc[d] = T(0);
@@ -316,6 +318,9 @@ static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool
     a.tw = (a.tw + h->K - 1) / h->K * h->K;
     a.tpr = (fd0 + a.tw - 1) / a.tw;
     a.nrows = (int)(h->nfine / fd0);
+    // slab window: only the owned fine rows (they come first in key order) are re-sorted here; the halo
+    // rows are replaced wholesale by the neighbours' boundary layers (ab_comm.cu)
+    if (h->win_W) a.nrows = (int)((int64_t)a.nrows * h->win_nl / h->dims[D - 1]);
     a.ntiles = a.nrows * a.tpr;
     a.has_vel = h->desc.kind == AB_SPACE_CONTINUOUS;
     a.want_agg = want_agg ? 1 : 0;
@@ -350,24 +355,28 @@ int ab_resort_tiled(ab_handle* h, const void* src_pos, const void* src_vel, bool
 }
 
 template <class T, int D>
-static int agg_t(ab_handle* h) {
+static int agg_t(ab_handle* h, int64_t cell0, int64_t ncell) {
+    if (ncell <= 0) return AB_OK;
     AB_LAUNCH(h, "k_cell_agg");
-    const uint32_t nc = (uint32_t)h->ncells;
     const int nfr = h->D == 2 ? h->K : h->K * h->K;
-    k_cell_agg<T, D><<<ab_blocks((int64_t)nc * nfr * 8, 256), 256, 0, h->stream>>>(
-        make_space<T, D>(h), h->cell_start, (const T*)h->fields[0].buf[h->cur], (const T*)h->fields[1].buf[h->cur], h->cap, nc,
-        (T*)h->cell_agg, (int64_t)h->ncells);
+    k_cell_agg<T, D><<<ab_blocks(ncell * nfr * 8, 256), 256, 0, h->stream>>>(
+        make_space<T, D>(h), h->cell_start, (const T*)h->fields[0].buf[h->cur], (const T*)h->fields[1].buf[h->cur], h->cap,
+        (uint32_t)cell0, (uint32_t)ncell, (T*)h->cell_agg, (int64_t)h->ncells);
     return AB_OK;
+}
+
+// aggregates of the reference cells [cell0, cell0 + ncell) of the current sorted state
+int ab_agg_range(ab_handle* h, int64_t cell0, int64_t ncell) {
+    AB_TRY(ensure_agg(h));
+    if (h->dtype == AB_F64) return h->D == 2 ? agg_t<double, 2>(h, cell0, ncell) : agg_t<double, 3>(h, cell0, ncell);
+    return h->D == 2 ? agg_t<float, 2>(h, cell0, ncell) : agg_t<float, 3>(h, cell0, ncell);
 }
 
 int ab_ensure_agg(ab_handle* h) {
     AB_TRY(ab_ensure_index(h));
     AB_TRY(ensure_agg(h));
     if (h->agg_valid) return AB_OK;
-    int rc;
-    if (h->dtype == AB_F64) rc = h->D == 2 ? agg_t<double, 2>(h) : agg_t<double, 3>(h);
-    else rc = h->D == 2 ? agg_t<float, 2>(h) : agg_t<float, 3>(h);
-    AB_TRY(rc);
+    AB_TRY(ab_agg_range(h, 0, h->ncells));
     h->agg_valid = true;
     return AB_OK;
 }

@@ -1,0 +1,154 @@
+"""Host side of the multi-GPU slab decomposition (one process per GPU).
+
+The reference is single-task (src/simulations/step_standard.jl:9-23); this module is the host
+plumbing of its scale-out: which cell layers of the last axis a rank owns, which agents
+it must hold (owned + halo layers), and how a global id-ordered state is scattered to / gathered
+from the ranks.  `torch.distributed` (NCCL on GPUs, gloo in the CPU tests) only moves the 128-byte
+communicator id and the gathered results; the per-step halo / migration exchange happens inside the
+library (csrc/ab_comm.cu).
+
+Pure-numpy layout functions (`slab_layout`, `window_layers`, `cell_layer`, `select_window`) carry no
+device dependency so they are tested on CPU with world_size > 1.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+HALO_W = 3   # layers per side; must equal AB_HALO_W (csrc/ab_comm.cu) — checked against ab_comm_halo()
+
+
+def slab_layout(n_layers: int, nranks: int):
+    """[(first_layer, count)] per rank: the first (n_layers % nranks) ranks own one layer more."""
+    base, rem = divmod(int(n_layers), int(nranks))
+    out = []
+    for r in range(nranks):
+        out.append((r * base + min(r, rem), base + (1 if r < rem else 0)))
+    return out
+
+
+def window_layers(first: int, count: int, n_layers: int, W: int = HALO_W):
+    """Global layers a rank stores, in its local order: owned, upper halo, lower halo."""
+    own = [(first + i) % n_layers for i in range(count)]
+    up = [(first + count + i) % n_layers for i in range(W)]
+    lo = [(first - W + i) % n_layers for i in range(W)]
+    return own, up, lo
+
+
+def cell_layer(pos_last, spacing, n_layers):
+    """0-based cell layer of the last coordinate: max(1, ceil(p / spacing)) - 1 (continuous.jl:112-113),
+    IEEE division in the column's own precision — the same arithmetic as the device's pos2cell."""
+    p = np.asarray(pos_last)
+    c = np.ceil(p / p.dtype.type(spacing)).astype(np.int64)
+    return np.clip(np.maximum(c, 1) - 1, 0, n_layers - 1)
+
+
+def select_window(layer, first, count, n_layers, W: int = HALO_W):
+    """Indices (into the global arrays) of the agents a rank must hold, and the owned subset mask."""
+    rel = (np.asarray(layer, dtype=np.int64) - first) % n_layers          # 0 .. n_layers-1
+    owned = rel < count
+    halo = ((rel >= count) & (rel < count + W)) | (rel >= n_layers - W)
+    idx = np.nonzero(owned | halo)[0]
+    return idx, owned[idx]
+
+
+def default_halo_capacity(n_global: int, n_layers: int, W: int = HALO_W, factor: float = 3.0) -> int:
+    """Message capacity every rank agrees on: `factor` x the mean population of W layers + slack."""
+    return int(factor * W * (n_global / max(n_layers, 1))) + 4096
+
+
+class Slabs:
+    """Sharded view of a StandardABM over `torch.distributed` ranks."""
+
+    def __init__(self, model, dist=None, rank=None, world=None, init_nccl=True):
+        from . import _lib as L
+
+        self.model, self.dist, self.L = model, dist, L
+        self.rank = int(dist.get_rank() if rank is None else rank)
+        self.world = int(dist.get_world_size() if world is None else world)
+        lib = model.lib
+        uid = None
+        if init_nccl:
+            buf = (C.c_ubyte * 128)()
+            if self.rank == 0:
+                model._ck(lib.ab_comm_unique_id(buf))
+            obj = [bytes(buf) if self.rank == 0 else None]
+            dist.broadcast_object_list(obj, src=0)
+            uid = (C.c_ubyte * 128).from_buffer_copy(obj[0])
+        model._ck(lib.ab_comm_init(model.h, self.rank, self.world, uid))
+        first, count = C.c_int64(0), C.c_int64(0)
+        model._ck(lib.ab_comm_slab(model.h, C.byref(first), C.byref(count)))
+        self.first, self.count = first.value, count.value
+        self.n_layers = model.space.dims[-1]
+        assert (self.first, self.count) == slab_layout(self.n_layers, self.world)[self.rank]
+        assert lib.ab_comm_halo(model.h) == HALO_W
+        self.n_global = 0
+
+    # -- population -----------------------------------------------------------------------------
+    def scatter(self, pos, vel, halo_capacity=None, capacity_factor=1.6):
+        """Every rank passes the same global, id-ordered (1..N) state and keeps its window of it."""
+        m, lib = self.model, self.model.lib
+        dt = m.space.dtype
+        pos = np.ascontiguousarray(pos, dtype=dt).reshape(-1, m.D)
+        vel = np.ascontiguousarray(vel, dtype=dt).reshape(-1, m.D)
+        self.n_global = pos.shape[0]
+        layer = cell_layer(pos[:, -1], m.space.spacing, self.n_layers)
+        idx, owned = select_window(layer, self.first, self.count, self.n_layers)
+        cap = halo_capacity or default_halo_capacity(self.n_global, self.n_layers)
+        m._ck(lib.ab_comm_set_capacity(m.h, int(cap)))
+        m._ck(lib.ab_resize(m.h, int(len(idx) * capacity_factor) + 2 * int(cap) + 1024))
+        gids = (idx + 1).astype(np.int64)
+        p = np.ascontiguousarray(pos[idx])
+        v = np.ascontiguousarray(vel[idx])
+        m._ck(lib.ab_upload_local(m.h, 0, m._ptr(p), m._ptr(gids), len(idx)))
+        m._ck(lib.ab_upload_local(m.h, 1, m._ptr(v), m._ptr(gids), len(idx)))
+        m._ck(lib.ab_build_index(m.h))
+        return int(owned.sum())
+
+    def local_state(self):
+        """(global ids, pos, vel) of the agents this rank owns now."""
+        m, lib = self.model, self.model.lib
+        cap = int(lib.ab_nagents(m.h)) + 1
+        ids = np.zeros(cap, dtype=np.int64)
+        pos = np.zeros((cap, m.D), dtype=m.space.dtype)
+        vel = np.zeros((cap, m.D), dtype=m.space.dtype)
+        n = C.c_int64(0)
+        m._ck(lib.ab_download_local(m.h, 0, m._ptr(pos), m._ptr(ids), cap, C.byref(n)))
+        m._ck(lib.ab_download_local(m.h, 1, m._ptr(vel), None, cap, C.byref(n)))
+        return ids[: n.value], pos[: n.value], vel[: n.value]
+
+    def n_owned(self):
+        return int(self.model.lib.ab_nlocal(self.model.h))
+
+    def gather(self):
+        """Global id-ordered (pos, vel) on every rank (all_gather of the owned parts)."""
+        ids, pos, vel = self.local_state()
+        parts = [None] * self.world
+        self.dist.all_gather_object(parts, (ids, pos, vel))
+        return merge_parts(parts, self.n_global)
+
+
+def merge_parts(parts, n_global):
+    """Assemble per-rank (ids, pos, vel) into id-ordered arrays; every id must appear exactly once."""
+    D = parts[0][1].shape[1]
+    dt = parts[0][1].dtype
+    pos = np.full((n_global, D), np.nan, dtype=dt)
+    vel = np.full((n_global, D), np.nan, dtype=dt)
+    seen = np.zeros(n_global, dtype=np.int64)
+    for ids, p, v in parts:
+        np.add.at(seen, ids - 1, 1)
+        pos[ids - 1] = p
+        vel[ids - 1] = v
+    if not np.all(seen == 1):
+        raise RuntimeError(f"agents lost or duplicated across ranks: {int((seen == 0).sum())} missing, "
+                           f"{int((seen > 1).sum())} duplicated")
+    return pos, vel
+
+
+def init_slabs(model, dist, n_total, extent, state_fn, **kw):
+    """bench.py helper: build the slabs and scatter the deterministic initial state."""
+    s = Slabs(model, dist)
+    pos, vel = state_fn(n_total, extent)
+    s.scatter(pos, vel, **kw)
+    return s

@@ -215,7 +215,7 @@ def run_gpu(args):
     else:
         from agents_jl_b200.parallel import init_slabs
 
-        pos, vel = init_slabs(model, dist, n * world, extent, flock_state)
+        slabs = init_slabs(model, dist, n * world, extent, flock_state)
     nloc = n
 
     flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device="cuda")

@@ -176,17 +176,33 @@ int ab_step_schelling(ab_handle* h, const ab_schelling_params* p, int64_t nsteps
 int ab_flock_last_counts(ab_handle* h, int32_t* counts, int64_t n);
 
 /* ---- multi-GPU slabs (one process per GPU) -----------------------------------
- * Slab decomposition along the last axis with halo + migration exchange over
- * NCCL.  nccl_unique_id: 128 bytes produced by ab_comm_unique_id() on rank 0
- * and broadcast by the host (torch.distributed / MPI / Julia Distributed). */
-int ab_comm_unique_id(void* out128);
+ * The reference is single-task (step_standard.jl:9-23); this is its scale-out
+ * (SURVEY 8e).  Slabs of whole cell layers along the LAST axis (periodic); each
+ * rank stores its owned layers plus 3 halo layers per side and exchanges the
+ * boundary layers (halo refresh + migration in one message per neighbour) over
+ * NCCL after every fused step.  Agents carry GLOBAL ids, so an N-GPU run is
+ * bitwise identical to the 1-GPU run.
+ *   id = ab_comm_unique_id() on rank 0, broadcast by the host (torch.distributed /
+ *   MPI / Julia Distributed); on every rank: ab_create(global space) ->
+ *   ab_comm_init -> ab_comm_set_capacity -> ab_resize(capacity) ->
+ *   ab_upload_local(pos), ab_upload_local(vel) -> ab_step_flock ... ->
+ *   ab_download_local.  Queries addressed by agent id are not available on a
+ *   sharded handle (AB_ERR_STATE). */
+int ab_comm_unique_id(void* out128);                       /* 128 bytes (ncclUniqueId) */
+/* nccl_unique_id may be NULL: window layout only, no communicator (tests) */
 int ab_comm_init(ab_handle* h, int rank, int nranks, const void* nccl_unique_id);
+/* capacity (agents) of one boundary message; every rank must pass the same value */
+int ab_comm_set_capacity(ab_handle* h, int64_t halo_agents);
+/* owned layers of this rank: global index of the first one (0-based) and how many */
 int ab_comm_slab(const ab_handle* h, int64_t* first_layer, int64_t* n_layers);
-/* global population after migration (sum over ranks is conserved) */
+int ab_comm_halo(const ab_handle* h);                      /* halo layers per side */
+/* owned agents of this rank (migration changes it; the sum over ranks is conserved) */
 int64_t ab_nlocal(const ab_handle* h);
-/* download with global ids: ids_out (n_local int64, 1-based global id) */
-int ab_download_local(ab_handle* h, int field, void* host, int64_t* ids_out, int64_t cap, int64_t* n_out);
+/* rows -> slots of this rank's window (owned + halo layers), global ids 1-based.
+ * field 0 (pos) defines the rows; other fields follow with the same rows. */
 int ab_upload_local(ab_handle* h, int field, const void* host, const int64_t* global_ids, int64_t n);
+/* owned agents in slot order with their global ids; cap = rows available in host / ids_out */
+int ab_download_local(ab_handle* h, int field, void* host, int64_t* ids_out, int64_t cap, int64_t* n_out);
 
 /* ---- instrumentation ----------------------------------------------------------
  * kernels launched by this handle so far (bench.py's gpu_launches) and device

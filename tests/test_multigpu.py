@@ -1,0 +1,55 @@
+"""Multi-GPU slab decomposition: N-GPU runs must be bitwise equal to the 1-GPU run (needs >= 2 GPUs;
+run with `gpurun --gpus 2 -- python -m pytest tests/test_multigpu.py -m gpu`)."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _ngpu():
+    try:
+        import torch
+
+        return torch.cuda.device_count()
+    except Exception:
+        return 0
+
+
+def _run(world, port, *wargs):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "mgpu_worker.py"), *wargs]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
+    lines = [l for l in out.stdout.splitlines() if l.startswith("MGPU_RESULT ")]
+    assert out.returncode == 0 and lines, out.stdout[-2000:] + out.stderr[-4000:]
+    return json.loads(lines[-1][len("MGPU_RESULT "):])
+
+
+CASES = [
+    ("2d-approx", ["--agents", "60000", "--extent", "400", "400", "--steps", "12"]),
+    ("2d-exact", ["--agents", "60000", "--extent", "400", "400", "--steps", "12", "--search", "exact"]),
+    ("2d-uneven-layers", ["--agents", "50000", "--extent", "300", "405", "--steps", "9", "--chunk", "3"]),
+    ("3d-approx", ["--agents", "40000", "--extent", "60", "60", "120", "--steps", "8"]),
+    ("2d-f32", ["--agents", "60000", "--extent", "400", "400", "--steps", "6", "--dtype", "float32"]),
+]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,wargs", CASES, ids=[c[0] for c in CASES])
+def test_two_gpus_bitwise_equal_to_one(name, wargs):
+    if _ngpu() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    r = _run(2, 29531, *wargs)
+    assert r["conserved"] and r["pos_bitwise_equal"] and r["vel_bitwise_equal"], r
+    assert r["migrated"], "the test state should make agents cross the slab boundary"
+
+
+@pytest.mark.gpu
+def test_four_gpus_bitwise_equal_to_one():
+    if _ngpu() < 4:
+        pytest.skip("needs >= 4 GPUs")
+    r = _run(4, 29533, "--agents", "120000", "--extent", "400", "800", "--steps", "10")
+    assert r["conserved"] and r["pos_bitwise_equal"] and r["vel_bitwise_equal"], r
