@@ -264,6 +264,7 @@ static int launch_cell_M(ab_handle* h, const SpaceDev<T, D>& sp) {
     const int64_t nwarps = (h->ncells / h->dims[0]) * wpr;
     k_cell_M<T, D><<<ab_blocks(nwarps * 32, 128), 128, 0, h->stream>>>(sp, (const T*)h->cell_agg, (int64_t)h->ncells, wpr,
                                                                        (int)nwarps, (T*)h->cell_M);
+    h->M_epoch = h->agg_epoch;
     return AB_OK;
 }
 
@@ -310,7 +311,7 @@ static int flock_steps_t(ab_handle* h, const ab_flock_params* p, int64_t nsteps)
     SpaceDev<T, D> sp = make_space<T, D>(h);
     if (fine && !exact) {
         AB_TRY(ab_ensure_agg(h));
-        AB_TRY((launch_cell_M<T, D>(h, sp)));
+        if (h->M_epoch != h->agg_epoch || !h->cell_M) AB_TRY((launch_cell_M<T, D>(h, sp)));   // else: left valid by the previous call
     }
     AB_CUDA(h, cudaEventRecord(h->ev0, h->stream));
     for (int64_t st = 0; st < nsteps; ++st) {

@@ -87,6 +87,7 @@ struct ab_handle {
     bool slot_map_valid = false;
     bool index_valid = false;
     bool agg_valid = false;            // cell_agg matches the current sorted state
+    uint64_t agg_epoch = 1, M_epoch = 0; // cell_M was built from cell_agg version M_epoch
     int32_t* ncount = nullptr;         // neighbour count per slot of the last flock step
 
     // per (fine row of a) reference cell: count, Σ(pos - centre), Σ vel of the sorted state

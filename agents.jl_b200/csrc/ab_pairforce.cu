@@ -79,6 +79,33 @@ __device__ __forceinline__ bool pf_integrate(const SpaceDev<T, D>& sp, const PfU
     return !bad;
 }
 
+// Own force of one agent by the reference walk (nearby_ids with the exact filter, continuous.jl:212-239):
+// used by the fine kernel for agents within rounding distance of a cell boundary, whose partners may sit
+// (in floating point) one cell beyond the 3^D block.
+template <class T, int D>
+__device__ __noinline__ void pf_accumulate_walk(const SpaceDev<T, D>& sp, const PfU<T>& u, int s, const T* p, const int* c,
+                                                T ri, T ki, const T* __restrict__ pos, const T* __restrict__ rad,
+                                                const T* __restrict__ kk, const uint32_t* __restrict__ cs, int64_t cap, T* f) {
+    const int gr = grid_radius<T, D>(sp, p, c, u.cutoff);
+    for_each_run<D>(sp.dims, sp.periodic, AB_METRIC_EUCLIDEAN, c, gr, cs, sp.kb, false, [&](uint32_t b, uint32_t e, int) {
+        for (uint32_t j = b; j < e; ++j) {
+            if ((int)j == s) continue;
+            T dr[D];
+            T dd = 0;
+#pragma unroll
+            for (int d = 0; d < D; ++d) {
+                T direct = pos[(size_t)d * cap + j] - p[d];
+                if (sp.periodic[d]) direct = min_image(direct, sp.extent[d]);
+                dr[d] = direct;
+                const T sq = direct * direct;
+                dd = (d == 0) ? sq : dd + sq;
+            }
+            if (!(dd <= u.thr)) continue;
+            pf_pair<T, D>(dr, dd, ri, ki, rad[j], kk[j], f);
+        }
+    });
+}
+
 template <class T, int D>
 __global__ void __launch_bounds__(128)
 k_pf_fine(SpaceDev<T, D> sp, PfU<T> u, const T* __restrict__ pos, const T* __restrict__ vel, const T* __restrict__ rad,
@@ -95,6 +122,18 @@ k_pf_fine(SpaceDev<T, D> sp, PfU<T> u, const T* __restrict__ pos, const T* __res
     const T ri = rad[s], ki = kk[s], mi = mass[s];
     key_to_cell<T, D>(sp, key[s], c);        // K == 1 on this path: fine cell == reference cell
     const int d0 = sp.dims[0], d1 = sp.dims[1], d2n = D == 3 ? sp.dims[2] : 1;
+    // cutoff may equal the spacing: a partner at distance ~cutoff can then sit (by rounding) two cells away,
+    // but only if BOTH agents are within rounding distance of a cell boundary — those take the reference walk
+    bool near = false;
+    {
+        const T eps = sizeof(T) == 8 ? T(1.4210854715202004e-14) : T(7.62939453125e-06);     // 2^-46, 2^-17
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            const T tau = sp.extent[d] * eps;
+            const T a = p[d] - sp.spacing * (T)c[d];
+            if (a < tau || sp.spacing - a < tau) near = true;
+        }
+    }
     auto sweep_t = [&](uint32_t jb, uint32_t je, int wrap, auto wrapped) {
         constexpr bool WRAP = decltype(wrapped)::value;
         for (uint32_t j = jb; j < je; ++j) {
@@ -116,6 +155,8 @@ k_pf_fine(SpaceDev<T, D> sp, PfU<T> u, const T* __restrict__ pos, const T* __res
         if (wrap == 0) sweep_t(jb, je, 0, std::false_type{});
         else sweep_t(jb, je, wrap, std::true_type{});
     };
+    if (near) pf_accumulate_walk<T, D>(sp, u, s, p, c, ri, ki, pos, rad, kk, cs, cap, f);
+    else
     for (int rz = (D == 3 ? -1 : 0); rz <= (D == 3 ? 1 : 0); ++rz) {
         int cz = 0, wz = 0;
         if (D == 3) {
@@ -252,7 +293,7 @@ static int pf_steps_t(ab_handle* h, const ab_pairforce_params* p, int64_t nsteps
     u.cutoff = p->cutoff;
     u.thr = pf_threshold_host<T>(p->cutoff);
     const double s = (double)(T)h->desc.spacing;
-    bool fine = p->cutoff > 0 && p->cutoff * (1.0 + 1e-9) <= s && ab_resort_applicable(h);
+    bool fine = p->cutoff > 0 && p->cutoff <= s && ab_resort_applicable(h);
     for (int d = 0; d < D; ++d) if (h->dims[d] < 3) fine = false;
     if (fine) AB_TRY(ab_set_refine(h, 1));
     AB_TRY(ab_ensure_index(h));

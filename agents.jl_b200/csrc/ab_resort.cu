@@ -341,6 +341,7 @@ static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool
     h->slot_map_valid = false;
     h->index_valid = true;
     h->agg_valid = want_agg;
+    if (want_agg) h->agg_epoch++;
     h->pairs_n = -1;
     return AB_OK;
 }
@@ -368,6 +369,7 @@ static int agg_t(ab_handle* h, int64_t cell0, int64_t ncell) {
 // aggregates of the reference cells [cell0, cell0 + ncell) of the current sorted state
 int ab_agg_range(ab_handle* h, int64_t cell0, int64_t ncell) {
     AB_TRY(ensure_agg(h));
+    h->agg_epoch++;
     if (h->dtype == AB_F64) return h->D == 2 ? agg_t<double, 2>(h, cell0, ncell) : agg_t<double, 3>(h, cell0, ncell);
     return h->D == 2 ? agg_t<float, 2>(h, cell0, ncell) : agg_t<float, 3>(h, cell0, ncell);
 }
