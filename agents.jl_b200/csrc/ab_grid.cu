@@ -438,6 +438,101 @@ k_sch_compact(const int32_t* __restrict__ grid_group, const uint8_t* __restrict_
     if (empty) E[oe + __popc(me & below)] = (uint32_t)k;
 }
 
+// Fast happiness pass for row lengths that are multiples of 128 (one warp = 128 consecutive cells of
+// a row, 4 per lane as one 16-byte load).  A block walks SCH4_R rows top-down keeping three rows in
+// registers, so every cell's group is read ~1.1x from L2/DRAM and the x neighbours come from the
+// adjacent lanes.  Mood byte written per cell: 1 happy, 0 unhappy, 2 empty — the compaction pass
+// then needs this byte only.  chunkU / chunkE: unhappy / empty counts per 128-cell chunk (cell order).
+#define SCH4_R 16
+template <bool RELOC>
+__global__ void __launch_bounds__(256)
+k_sch_happy4(GridDev<2> g, const int32_t* __restrict__ grid_group, uint8_t* __restrict__ grid_mood, int min_happy,
+             int diag, uint32_t* __restrict__ chunkU, uint32_t* __restrict__ chunkE) {
+    const int W = g.dims[0], H = g.dims[1];
+    const int lane = threadIdx.x & 31;
+    const int x0 = (blockIdx.x * 256 + threadIdx.x) * 4;
+    if (x0 >= W) return;                                   // whole warps leave together (W % 128 == 0)
+    const int y0 = blockIdx.y * SCH4_R;
+    const bool px = g.periodic[0], py = g.periodic[1];
+    auto load_row = [&](int yy, int* o) {
+        if (yy < 0) yy = py ? H - 1 : -1;
+        else if (yy >= H) yy = py ? yy - H : -1;
+        if (yy < 0) {
+#pragma unroll
+            for (int i = 0; i < 6; ++i) o[i] = AB_SCH_EMPTY;
+            return;
+        }
+        const int32_t* row = grid_group + (size_t)yy * W;
+        const int4 v = *reinterpret_cast<const int4*>(row + x0);
+        int l = __shfl_up_sync(0xffffffffu, v.w, 1), r = __shfl_down_sync(0xffffffffu, v.x, 1);
+        if (lane == 0) l = x0 > 0 ? row[x0 - 1] : (px ? row[W - 1] : AB_SCH_EMPTY);
+        if (lane == 31) r = x0 + 4 < W ? row[x0 + 4] : (px ? row[0] : AB_SCH_EMPTY);
+        o[0] = l; o[1] = v.x; o[2] = v.y; o[3] = v.z; o[4] = v.w; o[5] = r;
+    };
+    int up[6], cu[6], dn[6];
+    load_row(y0 - 1, up);
+    load_row(y0, cu);
+#pragma unroll 4
+    for (int r = 0; r < SCH4_R; ++r) {
+        const int y = y0 + r;
+        if (y >= H) break;
+        load_row(y + 1, dn);
+        uint32_t out = 0;
+        int nu = 0, ne = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int me = cu[i + 1];
+            int cnt = (up[i + 1] == me) + (dn[i + 1] == me) + (cu[i] == me) + (cu[i + 2] == me);
+            if (diag) cnt += (up[i] == me) + (up[i + 2] == me) + (dn[i] == me) + (dn[i + 2] == me);
+            const bool occupied = me != AB_SCH_EMPTY;
+            const bool happy = occupied && cnt >= min_happy;
+            out |= (occupied ? (happy ? 1u : 0u) : 2u) << (8 * i);
+            nu += occupied && !happy;
+            ne += !occupied;
+        }
+        *reinterpret_cast<uint32_t*>(grid_mood + (size_t)y * W + x0) = out;
+        if (RELOC) {
+            const int tu = __reduce_add_sync(0xffffffffu, nu), te = __reduce_add_sync(0xffffffffu, ne);
+            if (lane == 0) {
+                const size_t chunk = ((size_t)y * W + (size_t)(x0 - lane * 4)) >> 7;
+                chunkU[chunk] = (uint32_t)tu;
+                chunkE[chunk] = (uint32_t)te;
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 6; ++i) { up[i] = cu[i]; cu[i] = dn[i]; }
+    }
+}
+
+// Compaction for the fast path: one warp per 128-cell chunk, reads the mood bytes only.
+__global__ void __launch_bounds__(256)
+k_sch_compact4(const uint8_t* __restrict__ grid_mood, int64_t nchunks, const uint32_t* __restrict__ baseU,
+               const uint32_t* __restrict__ baseE, uint32_t* __restrict__ U, uint32_t* __restrict__ E) {
+    const int64_t chunk = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (chunk >= nchunks) return;
+    const int lane = threadIdx.x & 31;
+    const uint32_t k0 = (uint32_t)(chunk * 128 + lane * 4);
+    const uint32_t m = *reinterpret_cast<const uint32_t*>(grid_mood + k0);
+    uint32_t fu = 0, fe = 0;                                // bit i: cell k0 + i is unhappy / empty
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const uint32_t b = (m >> (8 * i)) & 0xffu;
+        fu |= (b == 0u ? 1u : 0u) << i;
+        fe |= (b == 2u ? 1u : 0u) << i;
+    }
+    const uint32_t mine = (uint32_t)__popc(fu) | ((uint32_t)__popc(fe) << 16);
+    uint32_t inc = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+    const uint32_t exc = inc - mine;
+    uint32_t ou = baseU[chunk] + (exc & 0xffffu), oe = baseE[chunk] + (exc >> 16);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        if (fu & (1u << i)) U[ou++] = k0 + i;
+        if (fe & (1u << i)) E[oe++] = k0 + i;
+    }
+}
+
 // Seeded pseudo-random permutation of [0, n): 4-round Feistel network on 2*hb bits, cycle-walked into range.
 __device__ __forceinline__ uint32_t sch_mix(uint32_t x, uint64_t key) {
     uint64_t z = (uint64_t)x + key + 0x9E3779B97F4A7C15ull;
@@ -545,7 +640,8 @@ extern "C" int ab_step_schelling(ab_handle* h, const ab_schelling_params* p, int
     if (nsteps == 0) return AB_OK;
     AB_TRY(sch_ensure_cells(h, fgroup, fmood));
     const int64_t ncells = h->ncells;
-    const int nblocks = ab_blocks(ncells, SCH_TB);
+    const bool fast = h->dims[0] % 128 == 0;               // whole-warp rows: k_sch_happy4 / k_sch_compact4
+    const int nblocks = fast ? (int)(ncells / 128) : ab_blocks(ncells, SCH_TB);
     const size_t nbpad = ((size_t)nblocks + 2047) / 2048 * 2048 + 2048;
     // scratch: blockU, blockE (padded), baseU, baseE (nblocks + 1), U (<= n), E (<= ncells - n), moved
     uint32_t *blockU = nullptr, *blockE = nullptr, *baseU = nullptr, *baseE = nullptr, *U = nullptr, *E = nullptr;
@@ -565,16 +661,20 @@ extern "C" int ab_step_schelling(ab_handle* h, const ab_schelling_params* p, int
     AB_CUDA(h, cudaEventRecord(h->ev0, h->stream));
     for (int64_t st = 0; st < nsteps; ++st) {
         {
-            AB_LAUNCH(h, "k_sch_happy");
-            if (p->relocate) k_sch_happy<true><<<nblocks, SCH_TB, 0, h->stream>>>(g, h->grid_group, h->grid_mood, ncells, p->min_to_be_happy, diag, blockU, blockE);
+            AB_LAUNCH(h, fast ? "k_sch_happy4" : "k_sch_happy");
+            const dim3 g4((h->dims[0] + 1023) / 1024, (h->dims[1] + SCH4_R - 1) / SCH4_R);
+            if (fast && p->relocate) k_sch_happy4<true><<<g4, 256, 0, h->stream>>>(g, h->grid_group, h->grid_mood, p->min_to_be_happy, diag, blockU, blockE);
+            else if (fast) k_sch_happy4<false><<<g4, 256, 0, h->stream>>>(g, h->grid_group, h->grid_mood, p->min_to_be_happy, diag, nullptr, nullptr);
+            else if (p->relocate) k_sch_happy<true><<<nblocks, SCH_TB, 0, h->stream>>>(g, h->grid_group, h->grid_mood, ncells, p->min_to_be_happy, diag, blockU, blockE);
             else k_sch_happy<false><<<nblocks, SCH_TB, 0, h->stream>>>(g, h->grid_group, h->grid_mood, ncells, p->min_to_be_happy, diag, nullptr, nullptr);
         }
         if (p->relocate) {
             AB_TRY(ab_scan_u32(h, blockU, baseU, (uint32_t)nblocks));
             AB_TRY(ab_scan_u32(h, blockE, baseE, (uint32_t)nblocks));
             {
-                AB_LAUNCH(h, "k_sch_compact");
-                k_sch_compact<<<nblocks, SCH_TB, 0, h->stream>>>(h->grid_group, h->grid_mood, ncells, baseU, baseE, U, E);
+                AB_LAUNCH(h, fast ? "k_sch_compact4" : "k_sch_compact");
+                if (fast) k_sch_compact4<<<ab_blocks((int64_t)nblocks * 32, 256), 256, 0, h->stream>>>(h->grid_mood, nblocks, baseU, baseE, U, E);
+                else k_sch_compact<<<nblocks, SCH_TB, 0, h->stream>>>(h->grid_group, h->grid_mood, ncells, baseU, baseE, U, E);
             }
             {
                 AB_LAUNCH(h, "k_sch_move");

@@ -162,8 +162,8 @@ def schelling_setup(dims, periodic, metric, occupancy=0.75, seed=42):
     return m, o, pos, group
 
 
-@pytest.mark.parametrize("dims", [(64, 48), (33, 7), (300, 257)])
-@pytest.mark.parametrize("periodic", [False, True, (True, False)])
+@pytest.mark.parametrize("dims", [(64, 48), (33, 7), (300, 257), (256, 37), (128, 5), (1152, 20)])   # last three: whole-warp rows (k_sch_happy4)
+@pytest.mark.parametrize("periodic", [False, True, (True, False), (False, True)])
 @pytest.mark.parametrize("metric", ["chebyshev", "manhattan"])
 def test_schelling_happiness_bit_exact(dims, periodic, metric):
     m, o, pos, group = schelling_setup(dims, periodic, metric)
@@ -176,10 +176,10 @@ def test_schelling_happiness_bit_exact(dims, periodic, metric):
     m.close()
 
 
+@pytest.mark.parametrize("dims", [(96, 80), (128, 64)])      # (128, 64): whole-warp rows (k_sch_happy4 / k_sch_compact4)
 @pytest.mark.parametrize("periodic", [False, True])
 @pytest.mark.parametrize("occupancy", [0.75, 0.97])
-def test_schelling_relocation_invariants(periodic, occupancy):
-    dims = (96, 80)
+def test_schelling_relocation_invariants(dims, periodic, occupancy):
     m, o, pos0, group = schelling_setup(dims, periodic, "chebyshev", occupancy=occupancy)
     n = len(pos0)
     ncell = dims[0] * dims[1]
