@@ -10,7 +10,7 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libagents_b200.so")
+LIB_PATH = os.environ.get("AGENTS_B200_LIB") or os.path.join(_HERE, "libagents_b200.so")   # override: kernel-variant experiments
 
 AB_OK = 0
 ERR_INVALID, ERR_CUDA, ERR_OUTSIDE, ERR_SPACING, ERR_OCCUPIED, ERR_NUMERIC, ERR_STATE, ERR_COMM = (

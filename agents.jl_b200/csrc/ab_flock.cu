@@ -272,7 +272,7 @@ template <class T, int D, bool EXACT>
 static int launch_fine(ab_handle* h, const SpaceDev<T, D>& sp, const FlockU<T>& u, int32_t* ncount) {
     const int cur = h->cur;
     const int n = h->win_W ? (int)h->cap : (int)h->n;      // slab window: grid over the capacity, live count read on the device
-    const int TB = 128;
+    const int TB = FINE_TB;
     AB_LAUNCH(h, EXACT ? "k_flock_fine_exact" : "k_flock_fine");
     k_flock_fine<T, D, EXACT><<<ab_blocks(n, TB), TB, 0, h->stream>>>(
         sp, u, (const T*)h->fields[0].buf[cur], (const T*)h->fields[1].buf[cur], h->key[cur], h->cell_start,

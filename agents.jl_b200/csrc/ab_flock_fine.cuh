@@ -29,6 +29,18 @@
 #pragma once
 #include <type_traits>
 
+// launch shape of the sweep (measured on B200, F2D-1M: unroll 4 + 8 resident CTAs/SM is 15 % faster than
+// unroll 2 without an occupancy hint; unroll 8 and 256-thread CTAs are slower)
+#ifndef FINE_UNROLL
+#define FINE_UNROLL 4
+#endif
+#ifndef FINE_TB
+#define FINE_TB 128
+#endif
+#ifndef FINE_MINB
+#define FINE_MINB 8
+#endif
+constexpr int kFineUnroll = FINE_UNROLL;
 template <int D> struct FineCfg { static constexpr int NC = 1 + 2 * D; };   // count, Σ(pos-centre)[D], Σvel[D]
 
 // row offsets (dy, dz) with dy² + dz² ≤ 4 (3-D) — summation order of k_cell_M
@@ -179,7 +191,7 @@ __device__ __forceinline__ bool pos2cell0_fast(const SpaceDev<T, D>& sp, const T
 }
 
 template <class T, int D, bool EXACT>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(FINE_TB, FINE_MINB)
 k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T* __restrict__ vel,
              const uint32_t* __restrict__ key, const uint32_t* __restrict__ cs, const T* __restrict__ M,
              int64_t ncells, int64_t cap, int n, T* __restrict__ npos, T* __restrict__ nvel,
@@ -248,7 +260,7 @@ k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T
         // reference's minimum-image rule (utilities.jl:185-193); all other runs are plain differences
         auto sweep_t = [&](uint32_t jb, uint32_t je, int wrap, auto wrapped) {
             constexpr bool WRAP = decltype(wrapped)::value;
-#pragma unroll 2
+#pragma unroll kFineUnroll
             for (uint32_t j = jb; j < je; ++j) {
                 T h[D];
                 T d2 = 0;
