@@ -86,6 +86,9 @@ struct ab_comm {
     void* sendbuf[2] = {nullptr, nullptr};   // [0] bottom layers -> lower neighbour, [1] top layers -> upper neighbour
     void* recvbuf[2] = {nullptr, nullptr};   // [0] from the upper neighbour (its bottom layers), [1] from the lower one
     int64_t n_own = 0;
+    // in-process peers (ab_comm_link_local): slabs of one process, on the same or on different devices
+    ab_handle *peer_lower = nullptr, *peer_upper = nullptr;
+    cudaEvent_t ev_packed = nullptr, ev_consumed = nullptr;
     uint32_t* h_counts = nullptr;    // pinned {n_own, n_window}
     int64_t exchanges = 0;
 };
@@ -222,6 +225,8 @@ void ab_comm_free(ab_handle* h) {
         if (c->recvbuf[i]) cudaFree(c->recvbuf[i]);
     }
     if (c->h_counts) cudaFreeHost(c->h_counts);
+    if (c->ev_packed) cudaEventDestroy(c->ev_packed);
+    if (c->ev_consumed) cudaEventDestroy(c->ev_consumed);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     delete c;
     h->comm = nullptr;
@@ -253,7 +258,7 @@ static int ensure_buffers(ab_handle* h) {
 }
 
 template <class E, int D>
-static int exchange_t(ab_handle* h, bool want_agg) {
+static int pack_t(ab_handle* h) {
     ab_comm* c = h->comm;
     AB_TRY(ensure_buffers(h));
     const int cur = h->cur;
@@ -261,27 +266,62 @@ static int exchange_t(ab_handle* h, bool want_agg) {
     const uint32_t kown = (uint32_t)(h->win_nl * keys_per_layer(h));
     const MsgLayout m = msg_layout(D, sizeof(E), c->cap_agents, ncs);
     const int nb = (int)std::min<int64_t>(std::max<int64_t>((std::max<int64_t>(c->cap_agents / 4, ncs) + 255) / 256, 1), 592);
-    E* pos = (E*)h->fields[0].buf[cur];
-    E* vel = (E*)h->fields[1].buf[cur];
+    // in-process peers: they must have consumed the previous message before it is overwritten
+    if (c->peer_lower) AB_CUDA(h, cudaStreamWaitEvent(h->stream, c->peer_lower->comm->ev_consumed, 0));
+    if (c->peer_upper) AB_CUDA(h, cudaStreamWaitEvent(h->stream, c->peer_upper->comm->ev_consumed, 0));
     {
         AB_LAUNCH(h, "k_halo_pack");
-        k_halo_pack<E, D><<<dim3(nb, 2), 256, 0, h->stream>>>(m, kown, h->cell_start, pos, vel, h->id[cur], h->key[cur],
-                                                             h->cap, (char*)c->sendbuf[0], (char*)c->sendbuf[1], h->d_err);
+        k_halo_pack<E, D><<<dim3(nb, 2), 256, 0, h->stream>>>(m, kown, h->cell_start, (const E*)h->fields[0].buf[cur],
+                                                             (const E*)h->fields[1].buf[cur], h->id[cur], h->key[cur], h->cap,
+                                                             (char*)c->sendbuf[0], (char*)c->sendbuf[1], h->d_err);
     }
-    // one group: bottom layers -> lower neighbour, top layers -> upper neighbour; receives in the matching
-    // order (with 2 ranks both neighbours are the same peer: first send pairs with first receive)
-    AB_NCCL(h, g_nccl.GroupStart());
-    AB_NCCL(h, g_nccl.Send(c->sendbuf[0], m.bytes, NCCL_UINT8, c->lower, c->comm, h->stream));
-    AB_NCCL(h, g_nccl.Send(c->sendbuf[1], m.bytes, NCCL_UINT8, c->upper, c->comm, h->stream));
-    AB_NCCL(h, g_nccl.Recv(c->recvbuf[0], m.bytes, NCCL_UINT8, c->upper, c->comm, h->stream));
-    AB_NCCL(h, g_nccl.Recv(c->recvbuf[1], m.bytes, NCCL_UINT8, c->lower, c->comm, h->stream));
-    AB_NCCL(h, g_nccl.GroupEnd());
+    if (c->peer_lower) AB_CUDA(h, cudaEventRecord(c->ev_packed, h->stream));
+    return AB_OK;
+}
+
+// Moves the two boundary messages: NCCL between processes, device-to-device copies between in-process peers.
+static int transfer(ab_handle* h) {
+    ab_comm* c = h->comm;
+    const size_t bytes = c->msg_bytes;
+    if (c->peer_lower) {
+        ab_handle *lo = c->peer_lower, *up = c->peer_upper;
+        AB_CUDA(h, cudaStreamWaitEvent(h->stream, up->comm->ev_packed, 0));
+        AB_CUDA(h, cudaStreamWaitEvent(h->stream, lo->comm->ev_packed, 0));
+        if (up->comm->msg_bytes != bytes || lo->comm->msg_bytes != bytes) return ab_fail(h, AB_ERR_COMM, "peers disagree on the message capacity");
+        // my upper halo = the upper peer's bottom layers (its sendbuf[0]); my lower halo = the lower peer's top layers
+        if (up->device == h->device) AB_CUDA(h, cudaMemcpyAsync(c->recvbuf[0], up->comm->sendbuf[0], bytes, cudaMemcpyDeviceToDevice, h->stream));
+        else AB_CUDA(h, cudaMemcpyPeerAsync(c->recvbuf[0], h->device, up->comm->sendbuf[0], up->device, bytes, h->stream));
+        if (lo->device == h->device) AB_CUDA(h, cudaMemcpyAsync(c->recvbuf[1], lo->comm->sendbuf[1], bytes, cudaMemcpyDeviceToDevice, h->stream));
+        else AB_CUDA(h, cudaMemcpyPeerAsync(c->recvbuf[1], h->device, lo->comm->sendbuf[1], lo->device, bytes, h->stream));
+        AB_CUDA(h, cudaEventRecord(c->ev_consumed, h->stream));
+    } else {
+        if (!c->comm) return ab_fail(h, AB_ERR_STATE, "sharded handle without a communicator or in-process peers");
+        // one group: bottom layers -> lower neighbour, top layers -> upper neighbour; receives in the matching
+        // order (with 2 ranks both neighbours are the same peer: first send pairs with first receive)
+        AB_NCCL(h, g_nccl.GroupStart());
+        AB_NCCL(h, g_nccl.Send(c->sendbuf[0], bytes, NCCL_UINT8, c->lower, c->comm, h->stream));
+        AB_NCCL(h, g_nccl.Send(c->sendbuf[1], bytes, NCCL_UINT8, c->upper, c->comm, h->stream));
+        AB_NCCL(h, g_nccl.Recv(c->recvbuf[0], bytes, NCCL_UINT8, c->upper, c->comm, h->stream));
+        AB_NCCL(h, g_nccl.Recv(c->recvbuf[1], bytes, NCCL_UINT8, c->lower, c->comm, h->stream));
+        AB_NCCL(h, g_nccl.GroupEnd());
+    }
     c->exchanges++;
+    return AB_OK;
+}
+
+template <class E, int D>
+static int unpack_t(ab_handle* h, bool want_agg) {
+    ab_comm* c = h->comm;
+    const int cur = h->cur;
+    const uint32_t ncs = (uint32_t)(AB_HALO_W * keys_per_layer(h));
+    const uint32_t kown = (uint32_t)(h->win_nl * keys_per_layer(h));
+    const MsgLayout m = msg_layout(D, sizeof(E), c->cap_agents, ncs);
+    const int nb = (int)std::min<int64_t>(std::max<int64_t>((std::max<int64_t>(c->cap_agents / 4, ncs) + 255) / 256, 1), 592);
     {
         AB_LAUNCH(h, "k_halo_unpack");
-        k_halo_unpack<E, D><<<dim3(nb, 2), 256, 0, h->stream>>>(m, kown, h->cell_start, pos, vel, h->id[cur], h->key[cur],
-                                                               h->cap, (const char*)c->recvbuf[0], (const char*)c->recvbuf[1],
-                                                               h->d_err);
+        k_halo_unpack<E, D><<<dim3(nb, 2), 256, 0, h->stream>>>(m, kown, h->cell_start, (E*)h->fields[0].buf[cur],
+                                                               (E*)h->fields[1].buf[cur], h->id[cur], h->key[cur], h->cap,
+                                                               (const char*)c->recvbuf[0], (const char*)c->recvbuf[1], h->d_err);
     }
     if (want_agg) {
         const int64_t cpl = cells_per_layer(h);
@@ -290,11 +330,17 @@ static int exchange_t(ab_handle* h, bool want_agg) {
     return AB_OK;
 }
 
-int ab_comm_exchange(ab_handle* h, bool want_agg) {
+int ab_comm_pack(ab_handle* h) {
     if (!h->comm || !h->win_W) return ab_fail(h, AB_ERR_STATE, "handle is not sharded");
-    if (h->tsize == 8) return h->D == 2 ? exchange_t<uint64_t, 2>(h, want_agg) : exchange_t<uint64_t, 3>(h, want_agg);
-    return h->D == 2 ? exchange_t<uint32_t, 2>(h, want_agg) : exchange_t<uint32_t, 3>(h, want_agg);
+    if (h->tsize == 8) return h->D == 2 ? pack_t<uint64_t, 2>(h) : pack_t<uint64_t, 3>(h);
+    return h->D == 2 ? pack_t<uint32_t, 2>(h) : pack_t<uint32_t, 3>(h);
 }
+int ab_comm_transfer(ab_handle* h) { return transfer(h); }
+int ab_comm_unpack(ab_handle* h, bool want_agg) {
+    if (h->tsize == 8) return h->D == 2 ? unpack_t<uint64_t, 2>(h, want_agg) : unpack_t<uint64_t, 3>(h, want_agg);
+    return h->D == 2 ? unpack_t<uint32_t, 2>(h, want_agg) : unpack_t<uint32_t, 3>(h, want_agg);
+}
+bool ab_comm_local(const ab_handle* h) { return h->comm && h->comm->peer_lower; }
 
 int ab_comm_refresh_counts(ab_handle* h) {
     ab_comm* c = h->comm;
@@ -383,6 +429,36 @@ int ab_comm_init(ab_handle* h, int rank, int nranks, const void* nccl_unique_id)
     h->K = 1; h->kb = 0; h->ksh = 0;
     h->nfine = ncells;
     h->index_valid = false; h->agg_valid = false; h->pairs_n = -1;
+    return AB_OK;
+}
+
+// In-process slabs: hs[r] is rank r of n (each created with ab_comm_init(h, r, n, NULL)); neighbours
+// exchange their boundary layers by device-to-device copies ordered with CUDA events.  Such handles are
+// stepped together with ab_step_flock_group.
+int ab_comm_link_local(ab_handle** hs, int n) {
+    if (!hs || n < 2) return AB_ERR_INVALID;
+    for (int r = 0; r < n; ++r) {
+        ab_handle* h = hs[r];
+        if (!h || !h->comm || !h->win_W) return ab_fail(h, AB_ERR_STATE, "ab_comm_init(h, rank, n, NULL) first");
+        if (h->comm->rank != r || h->comm->nranks != n) return ab_fail(h, AB_ERR_INVALID, "handles must be passed in rank order");
+        if (h->comm->comm) return ab_fail(h, AB_ERR_STATE, "handle already has an NCCL communicator");
+    }
+    for (int r = 0; r < n; ++r) {
+        ab_handle* h = hs[r];
+        ab_comm* c = h->comm;
+        AB_CUDA(h, cudaSetDevice(h->device));
+        c->peer_lower = hs[(r + n - 1) % n];
+        c->peer_upper = hs[(r + 1) % n];
+        if (!c->ev_packed) AB_CUDA(h, cudaEventCreateWithFlags(&c->ev_packed, cudaEventDisableTiming));
+        if (!c->ev_consumed) AB_CUDA(h, cudaEventCreateWithFlags(&c->ev_consumed, cudaEventDisableTiming));
+        AB_CUDA(h, cudaEventRecord(c->ev_consumed, h->stream));      // "nothing pending" for the first pack
+        for (ab_handle* peer : {c->peer_lower, c->peer_upper})
+            if (peer->device != h->device) {
+                int can = 0;
+                cudaDeviceCanAccessPeer(&can, h->device, peer->device);
+                if (can) { cudaError_t e = cudaDeviceEnablePeerAccess(peer->device, 0); if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError(); }
+            }
+    }
     return AB_OK;
 }
 

@@ -37,6 +37,9 @@ size_t ab_dtype_size(int dtype) {
     return 0;
 }
 
+// Per-launch timing (ab_set_profiling): events are only RECORDED around the launch — no host
+// synchronisation inside the step, so the timed region keeps its shape — and resolved later by
+// ab_kernel_times().
 ab_launch_scope::ab_launch_scope(ab_handle* h_, const char* name_) : h(h_), name(name_) {
     h->launches++;
     if (h->profiling) {
@@ -48,16 +51,24 @@ ab_launch_scope::ab_launch_scope(ab_handle* h_, const char* name_) : h(h_), name
 ab_launch_scope::~ab_launch_scope() {
     if (h->profiling && a) {
         cudaEventRecord(b, h->stream);
-        cudaEventSynchronize(b);
-        float ms = 0;
-        cudaEventElapsedTime(&ms, a, b);
-        bool found = false;
-        for (auto& k : h->kstats)
-            if (k.name == name || strcmp(k.name, name) == 0) { k.ms += ms; k.launches++; found = true; break; }
-        if (!found) h->kstats.push_back({name, (double)ms, 1});
-        cudaEventDestroy(a);
-        cudaEventDestroy(b);
+        h->pending.push_back({name, a, b});
     }
+}
+static void resolve_pending(ab_handle* h) {
+    if (h->pending.empty()) return;
+    cudaStreamSynchronize(h->stream);
+    for (auto& pe : h->pending) {
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, pe.a, pe.b) == cudaSuccess) {
+            bool found = false;
+            for (auto& k : h->kstats)
+                if (k.name == pe.name || strcmp(k.name, pe.name) == 0) { k.ms += ms; k.launches++; found = true; break; }
+            if (!found) h->kstats.push_back({pe.name, (double)ms, 1});
+        }
+        cudaEventDestroy(pe.a);
+        cudaEventDestroy(pe.b);
+    }
+    h->pending.clear();
 }
 
 static int grow(ab_handle* h, void** p, size_t* have, size_t bytes) {
@@ -535,6 +546,7 @@ int ab_destroy(ab_handle* h) {
     if (!h) return AB_OK;
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
+    resolve_pending(h);
     ab_comm_free(h);
     ab_grid_free(h);
     free_population(h);
@@ -565,11 +577,13 @@ void* ab_alloc_pinned(int64_t bytes) {
 void ab_free_pinned(void* p) { if (p) cudaFreeHost(p); }
 
 int ab_set_profiling(ab_handle* h, int on) {
+    resolve_pending(h);
     h->profiling = on != 0;
     h->kstats.clear();
     return AB_OK;
 }
 int ab_kernel_times(ab_handle* h, const char** names, double* ms, int64_t* launches, int cap) {
+    resolve_pending(h);
     int k = 0;
     for (auto& s : h->kstats) {
         if (k < cap) { if (names) names[k] = s.name; if (ms) ms[k] = s.ms; if (launches) launches[k] = s.launches; }

@@ -14,6 +14,7 @@
 //                    of the sorted arrays through L1/L2.
 //   k_flock_fine     (ab_flock_fine.cuh) fine-grid sweep for large 2-D/3-D spaces
 //                    with uniform parameters — the throughput path.
+#include <algorithm>
 #include <cmath>
 #include <limits>
 
@@ -210,6 +211,7 @@ static int move_t(ab_handle* h, double dt, const void* directions_dev, const int
 
 static int move_common(ab_handle* h, double dt, const void* directions, const int64_t* active_ids, int64_t nactive) {
     if (h->desc.kind != AB_SPACE_CONTINUOUS) return ab_fail(h, AB_ERR_INVALID, "continuous-space call on a grid handle");
+    if (h->win_W) return ab_fail(h, AB_ERR_STATE, "bulk moves are not available on a sharded (slab-window) handle");
     AB_CUDA(h, cudaSetDevice(h->device));
     if (h->n == 0) return AB_OK;
     int32_t* slots = nullptr;
@@ -281,23 +283,32 @@ static int launch_fine(ab_handle* h, const SpaceDev<T, D>& sp, const FlockU<T>& 
     return AB_OK;
 }
 
-template <class T, int D>
-static int flock_steps_t(ab_handle* h, const ab_flock_params* p, int64_t nsteps) {
-    const int n = (int)h->n;
+// One flock step is split in two halves so that several slabs (one process, ab_step_flock_group) can be
+// stepped in lockstep:  A = sweep + re-sort (+ pack of the boundary layers on a sharded handle),
+// then the boundary messages move,  B = install the halo (sharded) + per-cell sums for the next sweep.
+template <class T, int D> struct FlockCtx {
     FlockU<T> u;
+    SpaceDev<T, D> sp;
+    bool exact = false, fine = false;
+    int pa_field = -1;
+};
+
+template <class T, int D>
+static int flock_prepare(ab_handle* h, const ab_flock_params* p, FlockCtx<T, D>* cx) {
+    FlockU<T>& u = cx->u;
     u.speed = (T)p->speed; u.cohere_factor = (T)p->cohere_factor; u.separation = (T)p->separation;
     u.separate_factor = (T)p->separate_factor; u.match_factor = (T)p->match_factor;
     u.visual_distance = p->visual_distance;
-    const bool exact = p->search == AB_SEARCH_EXACT;
+    const bool exact = cx->exact = p->search == AB_SEARCH_EXACT;
     u.thr = exact ? exact_threshold_host<T>(p->visual_distance) : T(0);
     {
         const double sd = (double)(T)h->desc.spacing, d1 = sd - p->visual_distance, d2 = 2.0 * sd - p->visual_distance;
         u.gr_t1 = d1 >= 0 ? d1 * d1 : -1.0;
         u.gr_t2 = d2 >= 0 ? d2 * d2 : -1.0;
     }
-    int pa_field = p->per_agent_field;
-    if (pa_field >= 0) {
-        if (pa_field >= (int)h->fields.size() || h->fields[pa_field].ncomp != 6 || h->fields[pa_field].dtype != h->dtype)
+    cx->pa_field = p->per_agent_field;
+    if (cx->pa_field >= 0) {
+        if (cx->pa_field >= (int)h->fields.size() || h->fields[cx->pa_field].ncomp != 6 || h->fields[cx->pa_field].dtype != h->dtype)
             return ab_fail(h, AB_ERR_INVALID, "per_agent_field must be a 6-component column of the space's float type");
     }
     // kernel choice
@@ -306,43 +317,95 @@ static int flock_steps_t(ab_handle* h, const ab_flock_params* p, int64_t nsteps)
     if (p->kernel != 1) fine = plan_fine<T, D>(h, p, exact, &plan);
     if (p->kernel == 2 && !fine) return ab_fail(h, AB_ERR_INVALID, "fine-grid flock kernel not applicable to this configuration");
     if (h->win_W && !fine) return ab_fail(h, AB_ERR_INVALID, "a sharded handle runs the fine-grid flock step only (uniform parameters, visual_distance <= spacing, >= 6 cells per axis)");
+    cx->fine = fine;
     if (fine) AB_TRY(ab_set_refine(h, plan.K));
     AB_TRY(ab_ensure_index(h));
-    SpaceDev<T, D> sp = make_space<T, D>(h);
+    cx->sp = make_space<T, D>(h);
     if (fine && !exact) {
         AB_TRY(ab_ensure_agg(h));
-        if (h->M_epoch != h->agg_epoch || !h->cell_M) AB_TRY((launch_cell_M<T, D>(h, sp)));   // else: left valid by the previous call
+        if (h->M_epoch != h->agg_epoch || !h->cell_M) AB_TRY((launch_cell_M<T, D>(h, cx->sp)));   // else: left valid by the previous call
     }
+    return AB_OK;
+}
+
+template <class T, int D>
+static int flock_half_A(ab_handle* h, const FlockCtx<T, D>& cx, bool last) {
+    const int n = (int)h->n;
+    const int cur = h->cur;
+    int32_t* ncount = (last && !h->win_W) ? h->ncount : nullptr;   // neighbour counts by id (diagnostic)
+    if (cx.fine) {
+        if (cx.exact) AB_TRY((launch_fine<T, D, true>(h, cx.sp, cx.u, ncount)));
+        else AB_TRY((launch_fine<T, D, false>(h, cx.sp, cx.u, ncount)));
+        AB_TRY(ab_resort_tiled(h, h->tmp_pos, h->tmp_vel, !cx.exact));
+        if (h->win_W) AB_TRY(ab_comm_pack(h));
+        return AB_OK;
+    }
+    const T* pos = (const T*)h->fields[0].buf[cur];
+    const T* vel = (const T*)h->fields[1].buf[cur];
+    const T* pa = cx.pa_field >= 0 ? (const T*)h->fields[cx.pa_field].buf[cur] : nullptr;
+    {
+        AB_LAUNCH(h, "k_flock_generic");
+        const int TB = 128;
+        if (cx.exact)
+            k_flock_generic<T, D, true><<<ab_blocks(n, TB), TB, 0, h->stream>>>(
+                cx.sp, cx.u, pa, pos, vel, h->key[cur], h->cell_start, h->cap, n, (T*)h->tmp_pos, (T*)h->tmp_vel,
+                h->newkey, h->rank, h->cell_count, h->id[cur], ncount, h->d_err);
+        else
+            k_flock_generic<T, D, false><<<ab_blocks(n, TB), TB, 0, h->stream>>>(
+                cx.sp, cx.u, pa, pos, vel, h->key[cur], h->cell_start, h->cap, n, (T*)h->tmp_pos, (T*)h->tmp_vel,
+                h->newkey, h->rank, h->cell_count, h->id[cur], ncount, h->d_err);
+    }
+    return ab_reindex_from(h, h->tmp_pos, h->tmp_vel, true);
+}
+
+template <class T, int D>
+static int flock_half_B(ab_handle* h, const FlockCtx<T, D>& cx) {
+    if (!cx.fine) return AB_OK;
+    if (h->win_W) AB_TRY(ab_comm_unpack(h, !cx.exact));            // halo refresh + migration (ab_comm.cu)
+    if (!cx.exact) AB_TRY((launch_cell_M<T, D>(h, cx.sp)));
+    return AB_OK;
+}
+
+template <class T, int D>
+static int flock_steps_t(ab_handle* h, const ab_flock_params* p, int64_t nsteps) {
+    FlockCtx<T, D> cx;
+    AB_TRY((flock_prepare<T, D>(h, p, &cx)));
+    if (ab_comm_local(h)) return ab_fail(h, AB_ERR_STATE, "in-process slabs are stepped together: ab_step_flock_group");
     AB_CUDA(h, cudaEventRecord(h->ev0, h->stream));
     for (int64_t st = 0; st < nsteps; ++st) {
-        const int cur = h->cur;
-        const T* pos = (const T*)h->fields[0].buf[cur];
-        const T* vel = (const T*)h->fields[1].buf[cur];
-        int32_t* ncount = (st == nsteps - 1 && !h->win_W) ? h->ncount : nullptr;   // neighbour counts by id (diagnostic)
-        if (fine) {
-            if (exact) AB_TRY((launch_fine<T, D, true>(h, sp, u, ncount)));
-            else AB_TRY((launch_fine<T, D, false>(h, sp, u, ncount)));
-            AB_TRY(ab_resort_tiled(h, h->tmp_pos, h->tmp_vel, !exact));
-            if (h->win_W) AB_TRY(ab_comm_exchange(h, !exact));        // halo refresh + migration (ab_comm.cu)
-            if (!exact) AB_TRY((launch_cell_M<T, D>(h, sp)));
-        } else {
-            const T* pa = pa_field >= 0 ? (const T*)h->fields[pa_field].buf[cur] : nullptr;
-            {
-                AB_LAUNCH(h, "k_flock_generic");
-                const int TB = 128;
-                if (exact)
-                    k_flock_generic<T, D, true><<<ab_blocks(n, TB), TB, 0, h->stream>>>(
-                        sp, u, pa, pos, vel, h->key[cur], h->cell_start, h->cap, n, (T*)h->tmp_pos, (T*)h->tmp_vel,
-                        h->newkey, h->rank, h->cell_count, h->id[cur], ncount, h->d_err);
-                else
-                    k_flock_generic<T, D, false><<<ab_blocks(n, TB), TB, 0, h->stream>>>(
-                        sp, u, pa, pos, vel, h->key[cur], h->cell_start, h->cap, n, (T*)h->tmp_pos, (T*)h->tmp_vel,
-                        h->newkey, h->rank, h->cell_count, h->id[cur], ncount, h->d_err);
-            }
-            AB_TRY(ab_reindex_from(h, h->tmp_pos, h->tmp_vel, true));
-        }
+        AB_TRY((flock_half_A<T, D>(h, cx, st == nsteps - 1)));
+        if (h->win_W) AB_TRY(ab_comm_transfer(h));
+        AB_TRY((flock_half_B<T, D>(h, cx)));
     }
     AB_CUDA(h, cudaEventRecord(h->ev1, h->stream));
+    return AB_OK;
+}
+
+// All slabs of one process in lockstep (handles in rank order, linked by ab_comm_link_local).
+template <class T, int D>
+static int flock_group_t(ab_handle** hs, int nh, const ab_flock_params* p, int64_t nsteps) {
+    std::vector<FlockCtx<T, D>> cx(nh);
+    for (int r = 0; r < nh; ++r) {
+        AB_CUDA(hs[r], cudaSetDevice(hs[r]->device));
+        AB_TRY((flock_prepare<T, D>(hs[r], p, &cx[r])));
+        if (cx[r].exact != cx[0].exact || hs[r]->K != hs[0]->K) return ab_fail(hs[r], AB_ERR_INVALID, "slabs disagree on the step plan");
+        AB_CUDA(hs[r], cudaEventRecord(hs[r]->ev0, hs[r]->stream));
+    }
+    for (int64_t st = 0; st < nsteps; ++st) {
+        for (int r = 0; r < nh; ++r) {
+            AB_CUDA(hs[r], cudaSetDevice(hs[r]->device));
+            AB_TRY((flock_half_A<T, D>(hs[r], cx[r], false)));
+        }
+        for (int r = 0; r < nh; ++r) {
+            AB_CUDA(hs[r], cudaSetDevice(hs[r]->device));
+            AB_TRY(ab_comm_transfer(hs[r]));
+            AB_TRY((flock_half_B<T, D>(hs[r], cx[r])));
+        }
+    }
+    for (int r = 0; r < nh; ++r) {
+        AB_CUDA(hs[r], cudaSetDevice(hs[r]->device));
+        AB_CUDA(hs[r], cudaEventRecord(hs[r]->ev1, hs[r]->stream));
+    }
     return AB_OK;
 }
 
@@ -375,6 +438,35 @@ int ab_step_flock(ab_handle* h, const ab_flock_params* p, int64_t nsteps) {
     float ms = 0;
     AB_CUDA(h, cudaEventElapsedTime(&ms, h->ev0, h->ev1));
     h->last_step_ms = ms;
+    return AB_OK;
+}
+
+int ab_step_flock_group(ab_handle** hs, int nh, const ab_flock_params* p, int64_t nsteps) {
+    if (!hs || nh < 2 || !p) return AB_ERR_INVALID;
+    ab_handle* h0 = hs[0];
+    if (nsteps < 0) return ab_fail(h0, AB_ERR_INVALID, "negative nsteps");
+    for (int r = 0; r < nh; ++r) {
+        if (!hs[r] || !ab_comm_local(hs[r])) return ab_fail(hs[r] ? hs[r] : h0, AB_ERR_STATE, "link the slabs first (ab_comm_link_local)");
+        if (hs[r]->dtype != h0->dtype || hs[r]->D != h0->D) return ab_fail(hs[r], AB_ERR_INVALID, "slabs of one space must share D and eltype");
+    }
+    if (nsteps == 0) return AB_OK;
+    int rc;
+    if (h0->dtype == AB_F64) rc = h0->D == 2 ? flock_group_t<double, 2>(hs, nh, p, nsteps) : flock_group_t<double, 3>(hs, nh, p, nsteps);
+    else rc = h0->D == 2 ? flock_group_t<float, 2>(hs, nh, p, nsteps) : flock_group_t<float, 3>(hs, nh, p, nsteps);
+    if (rc != AB_OK) { if (h0->err.empty()) for (int r = 0; r < nh; ++r) if (!hs[r]->err.empty()) { h0->err = hs[r]->err; break; } return rc; }
+    double worst = 0;
+    for (int r = 0; r < nh; ++r) {
+        ab_handle* h = hs[r];
+        AB_CUDA(h, cudaSetDevice(h->device));
+        int e = ab_check_device_errors(h);
+        if (e != AB_OK) { h0->err = h->err; return e; }
+        AB_TRY(ab_comm_refresh_counts(h));
+        float ms = 0;
+        AB_CUDA(h, cudaEventElapsedTime(&ms, h->ev0, h->ev1));
+        h->last_step_ms = ms;
+        worst = std::max(worst, (double)ms);
+    }
+    h0->last_step_ms = worst;
     return AB_OK;
 }
 

@@ -52,6 +52,11 @@ struct ab_kernel_stat {
     int64_t launches;
 };
 
+struct ab_pending_event {
+    const char* name;
+    cudaEvent_t a, b;
+};
+
 struct ab_comm;   // multi-GPU state (ab_comm.cu)
 
 struct ab_handle {
@@ -139,6 +144,7 @@ struct ab_handle {
     int64_t launches = 0;
     bool profiling = false;
     std::vector<ab_kernel_stat> kstats;
+    std::vector<ab_pending_event> pending;   // recorded, not yet resolved launch timings
     std::string err;
 };
 
@@ -175,7 +181,12 @@ int ab_scan_u32(ab_handle* h, uint32_t* count, uint32_t* start, uint32_t n);   /
 size_t ab_dtype_size(int dtype);
 // cross-file internals (C++ linkage)
 void ab_comm_free(ab_handle* h);
-int ab_comm_exchange(ab_handle* h, bool want_agg);   // halo refresh + migration after a re-sort (slab window)
+// halo refresh + migration after a re-sort (slab window): pack my boundary layers, move the messages
+// (NCCL between processes / copies between in-process peers), install the received layers as my halo
+int ab_comm_pack(ab_handle* h);
+int ab_comm_transfer(ab_handle* h);
+int ab_comm_unpack(ab_handle* h, bool want_agg);
+bool ab_comm_local(const ab_handle* h);              // linked to in-process peers (ab_comm_link_local)
 int ab_comm_refresh_counts(ab_handle* h);            // owned / window agent counts back to the host
 int ab_grid_build(ab_handle* h);
 int ab_grid_sync_columns(ab_handle* h);   // cell-major Schelling state -> agent columns (pos, mood)

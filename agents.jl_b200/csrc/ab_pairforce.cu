@@ -345,6 +345,7 @@ extern "C" int ab_step_pairforce(ab_handle* h, const ab_pairforce_params* p, int
     if (!p) return ab_fail(h, AB_ERR_INVALID, "null params");
     if (h->desc.kind != AB_SPACE_CONTINUOUS) return ab_fail(h, AB_ERR_INVALID, "pair-force rule needs a ContinuousSpace handle");
     if (nsteps < 0) return ab_fail(h, AB_ERR_INVALID, "negative nsteps");
+    if (h->win_W) return ab_fail(h, AB_ERR_STATE, "the pair-force rule does not run on a sharded (slab-window) handle yet");
     const int fs[3] = {p->field_r, p->field_k, p->field_mass};
     for (int f : fs)
         if (f < 2 || f >= (int)h->fields.size() || h->fields[f].ncomp != 1 || h->fields[f].dtype != h->dtype)

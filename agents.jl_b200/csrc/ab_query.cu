@@ -215,6 +215,7 @@ static int nearby_t(ab_handle* h, const void* qpos_dev, const int64_t* qids_dev,
 
 static int nearby_common(ab_handle* h, const void* qpos, const int64_t* qids, int64_t nq, double r, int search,
                          int exclude_self, int64_t* counts, const int64_t* offsets, int64_t* ids_out) {
+    if (h->win_W) return ab_fail(h, AB_ERR_STATE, "neighbour queries are not available on a sharded (slab-window) handle");
     if ((qpos == nullptr) == (qids == nullptr)) return ab_fail(h, AB_ERR_INVALID, "exactly one of qpos / qids must be given");
     if (search != AB_SEARCH_APPROXIMATE && search != AB_SEARCH_EXACT)
         return ab_fail(h, AB_ERR_INVALID, "`search` keyword should be either `:approximate` or `:exact`");
@@ -286,6 +287,7 @@ int ab_nearby_fill(ab_handle* h, const void* qpos, const int64_t* qids, int64_t 
 }
 
 int ab_pairs_count(ab_handle* h, double r, int search, int64_t* npairs) {
+    if (h->win_W) return ab_fail(h, AB_ERR_STATE, "neighbour queries are not available on a sharded (slab-window) handle");
     if (h->desc.kind != AB_SPACE_CONTINUOUS) return ab_fail(h, AB_ERR_INVALID, "interacting_pairs needs a ContinuousSpace handle");
     if (search != AB_SEARCH_APPROXIMATE && search != AB_SEARCH_EXACT) return ab_fail(h, AB_ERR_INVALID, "bad search mode");
     AB_CUDA(h, cudaSetDevice(h->device));
@@ -348,6 +350,7 @@ int ab_pairs_fill(ab_handle* h, int64_t* lo, int64_t* hi, int64_t npairs) {
 }
 
 int ab_nearest_neighbor(ab_handle* h, double r, int64_t* out, int64_t n) {
+    if (h->win_W) return ab_fail(h, AB_ERR_STATE, "neighbour queries are not available on a sharded (slab-window) handle");
     if (h->desc.kind != AB_SPACE_CONTINUOUS) return ab_fail(h, AB_ERR_INVALID, "nearest_neighbor needs a ContinuousSpace handle");
     if (n != h->n) return ab_fail(h, AB_ERR_INVALID, "length must equal the agent count");
     if (n == 0) return AB_OK;

@@ -152,3 +152,46 @@ def init_slabs(model, dist, n_total, extent, state_fn, **kw):
     pos, vel = state_fn(n_total, extent)
     s.scatter(pos, vel, **kw)
     return s
+
+
+class LocalSlabs:
+    """All slabs in ONE process (the single-session form a Julia host would use; also how the slab code is
+    exercised on a single GPU): `nslabs` handles — on `devices[i]`, which may repeat — linked by
+    ab_comm_link_local and stepped in lockstep by ab_step_flock_group."""
+
+    def __init__(self, space_factory, rule, nslabs, devices=None):
+        from . import _lib as L
+        from .model import StandardABM
+
+        self.L, self.rule, self.n = L, rule, int(nslabs)
+        devices = list(devices) if devices is not None else [0] * self.n
+        self.models = [StandardABM(space_factory(), model_step=rule, device=devices[r]) for r in range(self.n)]
+        self.lib = self.models[0].lib
+        self.slabs = []
+        for r, m in enumerate(self.models):
+            self.slabs.append(Slabs(m, dist=None, rank=r, world=self.n, init_nccl=False))
+        self._hs = (C.c_void_p * self.n)(*[m.h for m in self.models])
+        self.models[0]._ck(self.lib.ab_comm_link_local(self._hs, self.n))
+        self.n_global = 0
+
+    def scatter(self, pos, vel, **kw):
+        self.n_global = len(pos)
+        return [s.scatter(pos, vel, **kw) for s in self.slabs]
+
+    def step(self, nsteps=1):
+        r = self.rule
+        fp = self.L.FlockParams(search=self.L.SEARCH[r.search], per_agent_field=-1, kernel=r.kernel, **r.p)
+        self.models[0]._ck(self.lib.ab_step_flock_group(self._hs, self.n, C.byref(fp), int(nsteps)))
+
+    def n_owned(self):
+        return [s.n_owned() for s in self.slabs]
+
+    def gather(self):
+        return merge_parts([s.local_state() for s in self.slabs], self.n_global)
+
+    def last_step_ms(self):
+        return self.models[0].last_step_ms()
+
+    def close(self):
+        for m in self.models:
+            m.close()

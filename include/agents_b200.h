@@ -191,6 +191,11 @@ int ab_flock_last_counts(ab_handle* h, int32_t* counts, int64_t n);
 int ab_comm_unique_id(void* out128);                       /* 128 bytes (ncclUniqueId) */
 /* nccl_unique_id may be NULL: window layout only, no communicator (tests) */
 int ab_comm_init(ab_handle* h, int rank, int nranks, const void* nccl_unique_id);
+/* Slabs of ONE process (e.g. a Julia session driving several GPUs, or several slabs on one GPU):
+ * handles created with ab_comm_init(h, r, n, NULL), passed in rank order.  Neighbours exchange by
+ * device-to-device copies ordered with CUDA events; step them with ab_step_flock_group. */
+int ab_comm_link_local(ab_handle** handles, int n);
+int ab_step_flock_group(ab_handle** handles, int n, const ab_flock_params* p, int64_t nsteps);
 /* capacity (agents) of one boundary message; every rank must pass the same value */
 int ab_comm_set_capacity(ab_handle* h, int64_t halo_agents);
 /* owned layers of this rank: global index of the first one (0-based) and how many */
