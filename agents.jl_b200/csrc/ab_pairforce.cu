@@ -106,8 +106,15 @@ __device__ __noinline__ void pf_accumulate_walk(const SpaceDev<T, D>& sp, const 
     });
 }
 
+#ifndef PF_UNROLL
+#define PF_UNROLL 2
+#endif
+#ifndef PF_MINB
+#define PF_MINB 8
+#endif
+constexpr int kPfUnroll = PF_UNROLL;
 template <class T, int D>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, PF_MINB)
 k_pf_fine(SpaceDev<T, D> sp, PfU<T> u, const T* __restrict__ pos, const T* __restrict__ vel, const T* __restrict__ rad,
           const T* __restrict__ kk, const T* __restrict__ mass, const uint32_t* __restrict__ key,
           const uint32_t* __restrict__ cs, int64_t cap, int n, T* __restrict__ npos, T* __restrict__ nvel,
@@ -136,6 +143,7 @@ k_pf_fine(SpaceDev<T, D> sp, PfU<T> u, const T* __restrict__ pos, const T* __res
     }
     auto sweep_t = [&](uint32_t jb, uint32_t je, int wrap, auto wrapped) {
         constexpr bool WRAP = decltype(wrapped)::value;
+#pragma unroll kPfUnroll
         for (uint32_t j = jb; j < je; ++j) {
             T dr[D];
             T dd = 0;
