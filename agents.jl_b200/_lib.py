@@ -42,6 +42,15 @@ class SchellingParams(C.Structure):
     _fields_ = [("min_to_be_happy", C.c_int32), ("relocate", C.c_int32), ("seed", C.c_uint64)]
 
 
+class ReduceSpec(C.Structure):
+    _fields_ = [("field", C.c_int32), ("comp", C.c_int32), ("op", C.c_int32), ("filter_field", C.c_int32),
+                ("filter_comp", C.c_int32), ("filter_cmp", C.c_int32), ("filter_value", C.c_double)]
+
+
+RED = {"sum": 0, "mean": 1, "minimum": 2, "min": 2, "maximum": 3, "max": 3, "count": 4, "length": 4}
+CMP = {None: 0, "==": 1, "!=": 2, "<": 3, "<=": 4, ">": 5, ">=": 6}
+
+
 # every symbol include/agents_b200.h declares: name -> (restype, argtypes)
 _H = C.c_void_p
 _SIGS = {
@@ -72,6 +81,7 @@ _SIGS = {
     "ab_step_pairforce": (C.c_int, [_H, C.POINTER(PairForceParams), C.c_int64]),
     "ab_step_schelling": (C.c_int, [_H, C.POINTER(SchellingParams), C.c_int64, C.POINTER(C.c_int64)]),
     "ab_flock_last_counts": (C.c_int, [_H, C.c_void_p, C.c_int64]),
+    "ab_reduce": (C.c_int, [_H, C.POINTER(ReduceSpec), C.c_int, C.c_void_p, C.c_void_p]),
     "ab_comm_unique_id": (C.c_int, [C.c_void_p]),
     "ab_comm_init": (C.c_int, [_H, C.c_int, C.c_int, C.c_void_p]),
     "ab_comm_link_local": (C.c_int, [C.POINTER(_H), C.c_int]),

@@ -1,0 +1,186 @@
+// ab_collect.cu — on-device aggregates of agent columns for data collection.
+//
+// run!(model, n; adata = [(field, aggregator[, filter]), ...]) calls collect_agent_data! after every
+// collected tick (src/simulations/collect.jl:154-183); the tuple form evaluates
+// aggregator(get_data(a, field) for a in allagents(model) if filter(a))  (collect.jl:466-502, 520-560).
+// With device-resident columns that would mean a full column download per tick; here each
+// (field, aggregator, filter) triple is reduced on the device and only one double (+ a count) per triple
+// crosses PCIe.  Supported aggregators: sum, mean, minimum, maximum, count; filters: one comparison of a
+// column component with a constant (the common `a -> a.field == v` / `>` / `<` forms).
+//
+// The reduction order is fixed (slot-strided per thread, tree per block, partials in block order), so a
+// result is reproducible for a given state; it is NOT the reference's left fold in id order, so
+// floating-point sums agree with it to rounding (tests: 1e-12 relative), integer / min / max / count
+// results exactly.  On a sharded handle the aggregate covers the OWNED agents of the rank (the host adds
+// the ranks' partial results).
+#include <algorithm>
+
+#include "ab_internal.cuh"
+
+#define RED_THREADS 256
+#define RED_ITEMS 16
+#define RED_CHUNK (RED_THREADS * RED_ITEMS)
+
+struct RedSpecDev {
+    const void* col;      // column component base (element 0 of that component)
+    int dtype;
+    const void* fcol;     // filter column component base or nullptr
+    int fdtype, fcmp;
+    double fval;
+    int op;
+};
+
+__device__ __forceinline__ double red_load(const void* p, int dtype, int s) {
+    switch (dtype) {
+        case AB_F64: return ((const double*)p)[s];
+        case AB_F32: return (double)((const float*)p)[s];
+        case AB_I32: return (double)((const int32_t*)p)[s];
+        case AB_I64: return (double)((const long long*)p)[s];
+        default: return (double)((const uint8_t*)p)[s];
+    }
+}
+__device__ __forceinline__ bool red_pass(const RedSpecDev& sp, int s) {
+    if (!sp.fcol) return true;
+    const double v = red_load(sp.fcol, sp.fdtype, s);
+    switch (sp.fcmp) {
+        case AB_CMP_EQ: return v == sp.fval;
+        case AB_CMP_NE: return v != sp.fval;
+        case AB_CMP_LT: return v < sp.fval;
+        case AB_CMP_LE: return v <= sp.fval;
+        case AB_CMP_GT: return v > sp.fval;
+        case AB_CMP_GE: return v >= sp.fval;
+    }
+    return true;
+}
+__device__ __forceinline__ double red_combine(int op, double a, double b) {
+    if (op == AB_RED_MIN) return fmin(a, b);
+    if (op == AB_RED_MAX) return fmax(a, b);
+    return a + b;
+}
+__device__ __forceinline__ double red_identity(int op) {
+    if (op == AB_RED_MIN) return INFINITY;
+    if (op == AB_RED_MAX) return -INFINITY;
+    return 0.0;
+}
+
+// blockIdx.y = spec; blockIdx.x = chunk of RED_CHUNK slots.  partial[spec][chunk] = {value, count}
+__global__ void __launch_bounds__(RED_THREADS)
+k_reduce_chunks(const RedSpecDev* __restrict__ specs, int n, int nchunks, double* __restrict__ pval,
+                unsigned long long* __restrict__ pcnt) {
+    __shared__ double s_v[RED_THREADS / 32];
+    __shared__ unsigned long long s_c[RED_THREADS / 32];
+    const RedSpecDev sp = specs[blockIdx.y];
+    const int base = blockIdx.x * RED_CHUNK + threadIdx.x;
+    double acc = red_identity(sp.op);
+    unsigned long long cnt = 0;
+#pragma unroll 4
+    for (int i = 0; i < RED_ITEMS; ++i) {
+        const int s = base + i * RED_THREADS;
+        if (s < n && red_pass(sp, s)) {
+            ++cnt;
+            if (sp.op != AB_RED_COUNT) acc = red_combine(sp.op, acc, red_load(sp.col, sp.dtype, s));
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        acc = red_combine(sp.op, acc, __shfl_xor_sync(0xffffffffu, acc, o));
+        cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    }
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (lane == 0) { s_v[wid] = acc; s_c[wid] = cnt; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = s_v[0];
+        unsigned long long c = s_c[0];
+        for (int w = 1; w < RED_THREADS / 32; ++w) { a = red_combine(sp.op, a, s_v[w]); c += s_c[w]; }
+        pval[(size_t)blockIdx.y * nchunks + blockIdx.x] = a;
+        pcnt[(size_t)blockIdx.y * nchunks + blockIdx.x] = c;
+    }
+}
+
+// one block per spec: partials in chunk order
+__global__ void __launch_bounds__(RED_THREADS)
+k_reduce_final(const RedSpecDev* __restrict__ specs, int nchunks, const double* __restrict__ pval,
+               const unsigned long long* __restrict__ pcnt, double* __restrict__ out, long long* __restrict__ ocnt) {
+    __shared__ double s_v[RED_THREADS];
+    __shared__ unsigned long long s_c[RED_THREADS];
+    const RedSpecDev sp = specs[blockIdx.x];
+    double acc = red_identity(sp.op);
+    unsigned long long cnt = 0;
+    for (int i = threadIdx.x; i < nchunks; i += RED_THREADS) {
+        acc = red_combine(sp.op, acc, pval[(size_t)blockIdx.x * nchunks + i]);
+        cnt += pcnt[(size_t)blockIdx.x * nchunks + i];
+    }
+    s_v[threadIdx.x] = acc;
+    s_c[threadIdx.x] = cnt;
+    __syncthreads();
+    for (int o = RED_THREADS / 2; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) {
+            s_v[threadIdx.x] = red_combine(sp.op, s_v[threadIdx.x], s_v[threadIdx.x + o]);
+            s_c[threadIdx.x] += s_c[threadIdx.x + o];
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        double v = s_v[0];
+        const unsigned long long c = s_c[0];
+        if (sp.op == AB_RED_COUNT) v = (double)c;
+        else if (sp.op == AB_RED_MEAN) v = c ? v / (double)c : __longlong_as_double(0x7ff8000000000000LL);   // mean of nothing: NaN
+        out[blockIdx.x] = v;
+        ocnt[blockIdx.x] = (long long)c;
+    }
+}
+
+extern "C" int ab_reduce(ab_handle* h, const ab_reduce_spec* specs, int nspec, double* out, int64_t* counts) {
+    if (!h || !specs || !out || nspec < 1 || nspec > 64) return ab_fail(h, AB_ERR_INVALID, "ab_reduce: 1..64 specs and an output array");
+    AB_CUDA(h, cudaSetDevice(h->device));
+    if (h->grid_cols_dirty) AB_TRY(ab_grid_sync_columns(h));
+    int64_t n = h->n;
+    if (h->win_W) { AB_TRY(ab_comm_refresh_counts(h)); n = ab_nlocal(h); }     // owned agents come first
+    std::vector<RedSpecDev> dev(nspec);
+    for (int i = 0; i < nspec; ++i) {
+        const ab_reduce_spec& s = specs[i];
+        if (s.op < AB_RED_SUM || s.op > AB_RED_COUNT) return ab_fail(h, AB_ERR_INVALID, "ab_reduce: unknown aggregator");
+        if (s.field < 0 || s.field >= (int)h->fields.size() || s.comp < 0 || s.comp >= h->fields[s.field].ncomp)
+            return ab_fail(h, AB_ERR_INVALID, "ab_reduce: bad field / component");
+        const ab_field& f = h->fields[s.field];
+        dev[i].col = (const char*)f.buf[h->cur] + (size_t)s.comp * h->cap * f.esize;
+        dev[i].dtype = f.dtype;
+        dev[i].op = s.op;
+        dev[i].fcol = nullptr; dev[i].fdtype = 0; dev[i].fcmp = AB_CMP_NONE; dev[i].fval = s.filter_value;
+        if (s.filter_cmp != AB_CMP_NONE) {
+            if (s.filter_cmp < AB_CMP_EQ || s.filter_cmp > AB_CMP_GE) return ab_fail(h, AB_ERR_INVALID, "ab_reduce: unknown filter comparison");
+            if (s.filter_field < 0 || s.filter_field >= (int)h->fields.size() || s.filter_comp < 0 ||
+                s.filter_comp >= h->fields[s.filter_field].ncomp)
+                return ab_fail(h, AB_ERR_INVALID, "ab_reduce: bad filter field / component");
+            const ab_field& ff = h->fields[s.filter_field];
+            dev[i].fcol = (const char*)ff.buf[h->cur] + (size_t)s.filter_comp * h->cap * ff.esize;
+            dev[i].fdtype = ff.dtype;
+            dev[i].fcmp = s.filter_cmp;
+        }
+    }
+    const int nchunks = (int)std::max<int64_t>((n + RED_CHUNK - 1) / RED_CHUNK, 1);
+    const size_t o_spec = 0, o_pval = (sizeof(RedSpecDev) * nspec + 255) / 256 * 256;
+    const size_t o_pcnt = o_pval + (size_t)nspec * nchunks * 8, o_out = o_pcnt + (size_t)nspec * nchunks * 8;
+    const size_t o_cnt = o_out + (size_t)nspec * 8, total = o_cnt + (size_t)nspec * 8;
+    char* base;
+    AB_TRY(ab_scratch2(h, total + 256, (void**)&base));
+    AB_CUDA(h, cudaMemcpyAsync(base + o_spec, dev.data(), sizeof(RedSpecDev) * nspec, cudaMemcpyHostToDevice, h->stream));
+    {
+        AB_LAUNCH(h, "k_reduce_chunks");
+        k_reduce_chunks<<<dim3(nchunks, nspec), RED_THREADS, 0, h->stream>>>((const RedSpecDev*)(base + o_spec), (int)n, nchunks,
+                                                                           (double*)(base + o_pval), (unsigned long long*)(base + o_pcnt));
+    }
+    {
+        AB_LAUNCH(h, "k_reduce_final");
+        k_reduce_final<<<nspec, RED_THREADS, 0, h->stream>>>((const RedSpecDev*)(base + o_spec), nchunks, (const double*)(base + o_pval),
+                                                            (const unsigned long long*)(base + o_pcnt), (double*)(base + o_out),
+                                                            (long long*)(base + o_cnt));
+    }
+    std::vector<long long> cnt(nspec);
+    AB_CUDA(h, cudaMemcpyAsync(out, base + o_out, (size_t)nspec * 8, cudaMemcpyDeviceToHost, h->stream));
+    AB_CUDA(h, cudaMemcpyAsync(cnt.data(), base + o_cnt, (size_t)nspec * 8, cudaMemcpyDeviceToHost, h->stream));
+    AB_CUDA(h, cudaStreamSynchronize(h->stream));
+    if (counts) for (int i = 0; i < nspec; ++i) counts[i] = cnt[i];
+    return AB_OK;
+}

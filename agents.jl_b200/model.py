@@ -335,6 +335,62 @@ class StandardABM:
         self.time += int(n)
         return self
 
+    # -- data collection (src/simulations/collect.jl:154-183, 466-502) ----------
+    def collect(self, adata):
+        """collect_agent_data! for aggregate specs: adata = [(field, aggregator[, filter])], field = "name" or
+        ("name", component); aggregator in sum / mean / minimum / maximum / count; filter = (field, cmp, value)
+        with cmp in == != < <= > >=.  Reduced on the device; returns one float per spec."""
+        specs = (L.ReduceSpec * len(adata))()
+        for i, item in enumerate(adata):
+            field, agg = item[0], item[1]
+            flt = item[2] if len(item) > 2 else None
+            name, comp = (field, 0) if isinstance(field, str) else field
+            agg = getattr(agg, "__name__", agg)
+            if agg not in L.RED:
+                raise ValueError(f"aggregator {agg!r} does not run on the device")
+            specs[i].field, specs[i].comp, specs[i].op = self.field_id(name), int(comp), L.RED[agg]
+            specs[i].filter_cmp = 0
+            if flt is not None:
+                ff, cmp_, val = flt
+                fname, fcomp = (ff, 0) if isinstance(ff, str) else ff
+                specs[i].filter_field, specs[i].filter_comp = self.field_id(fname), int(fcomp)
+                specs[i].filter_cmp, specs[i].filter_value = L.CMP[cmp_], float(val)
+        out = np.zeros(len(adata), dtype=np.float64)
+        self._ck(self.lib.ab_reduce(self.h, specs, len(adata), self._ptr(out), None))
+        return out
+
+    def run(self, n, adata=None, when=1):
+        """run!(model, n; adata, when): steps n ticks, collecting the aggregates of `adata` at time 0 and after
+        every `when`-th tick (collect.jl:154-183).  Returns {"time": [...], "<agg>_<field>": [...]} —
+        the columns of the reference's agent DataFrame for tuple-form adata."""
+        adata = list(adata or [])
+
+        def label(item):
+            field, agg = item[0], item[1]
+            name = field if isinstance(field, str) else f"{field[0]}[{field[1] + 1}]"
+            return f"{getattr(agg, '__name__', agg)}_{name}" + ("_filtered" if len(item) > 2 else "")
+
+        cols = {"time": []}
+        labels = [label(it) for it in adata]
+        for lb in labels:
+            cols[lb] = []
+
+        def take():
+            cols["time"].append(self.time)
+            if adata:
+                for lb, v in zip(labels, self.collect(adata)):
+                    cols[lb].append(float(v))
+
+        take()
+        done = 0
+        while done < n:
+            k = min(int(when), n - done)
+            self.step(k)                       # `when` ticks batched into one call
+            done += k
+            if done % int(when) == 0:
+                take()
+        return cols
+
     def last_neighbor_counts(self):
         n = self.nagents()
         out = np.zeros(n, dtype=np.int32)

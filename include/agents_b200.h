@@ -175,6 +175,23 @@ int ab_step_schelling(ab_handle* h, const ab_schelling_params* p, int64_t nsteps
  * diagnostic used by the parity tests (neighbour-set flips). */
 int ab_flock_last_counts(ab_handle* h, int32_t* counts, int64_t n);
 
+/* ---- data collection ---------------------------------------------------------
+ * run!(model, n; adata = [(field, aggregator[, filter])]) -> collect_agent_data!
+ * (src/simulations/collect.jl:154-183, 466-502): each triple is reduced on the
+ * device; one double (+ the number of agents that passed the filter) comes back
+ * per triple instead of a column download per collected tick.  Plain symbols in
+ * adata (whole columns) use ab_download.  mean over no agent returns NaN. */
+enum { AB_RED_SUM = 0, AB_RED_MEAN = 1, AB_RED_MIN = 2, AB_RED_MAX = 3, AB_RED_COUNT = 4 };
+enum { AB_CMP_NONE = 0, AB_CMP_EQ = 1, AB_CMP_NE = 2, AB_CMP_LT = 3, AB_CMP_LE = 4, AB_CMP_GT = 5, AB_CMP_GE = 6 };
+typedef struct {
+    int32_t field, comp;               /* column and component to aggregate            */
+    int32_t op;                        /* AB_RED_*                                     */
+    int32_t filter_field, filter_comp; /* filter: column component <cmp> filter_value  */
+    int32_t filter_cmp;                /* AB_CMP_* (AB_CMP_NONE: every agent)          */
+    double filter_value;
+} ab_reduce_spec;
+int ab_reduce(ab_handle* h, const ab_reduce_spec* specs, int nspec, double* out, int64_t* counts_or_null);
+
 /* ---- multi-GPU slabs (one process per GPU) -----------------------------------
  * The reference is single-task (step_standard.jl:9-23); this is its scale-out
  * (SURVEY 8e).  Slabs of whole cell layers along the LAST axis (periodic); each
