@@ -470,7 +470,7 @@ int ab_create(ab_space_desc* desc, int device, ab_handle** out) {
     if (desc->D < 2 || desc->D > 3) return ab_fail(nullptr, AB_ERR_INVALID, "D must be 2 or 3 on the device");
     ab_handle* h = new ab_handle();
     h->device = device;
-    if (const char* e = getenv("AB_RS_TARGET")) { int v = atoi(e); if (v >= 64 && v <= 2048) h->rs_target = v; }   // tuning experiments
+    if (const char* e = getenv("AB_RS_TARGET")) { int v = atoi(e); if (v >= 4 && v <= 2048) h->rs_target = v; }   // tuning experiments
     h->D = desc->D;
     int64_t ncells = 1;
     if (desc->kind == AB_SPACE_CONTINUOUS) {

@@ -102,7 +102,7 @@ struct ab_handle {
     // sums of those aggregates over the reference's offset tables of radius 1 and 2 (k_cell_M)
     void* cell_M = nullptr;
     size_t cell_M_bytes = 0;
-    int rs_target = 512;               // average agents per re-sort tile (tuning knob)
+    int rs_target = 100;               // average agents per re-sort tile (tuning knob)
 
     // single-pass scan state
     unsigned long long* scan_status = nullptr;

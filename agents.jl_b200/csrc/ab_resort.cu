@@ -1,5 +1,5 @@
-// ab_resort.cu — tile-based, deterministic re-sort of the population after a
-// fused step, and the per-reference-cell aggregates of the sorted state.
+// ab_resort.cu — tile-based, deterministic, atomic-free re-sort of the population
+// after a fused step, and the per-reference-cell aggregates of the sorted state.
 //
 // The reference keeps its index current by moving one id between two cell
 // vectors per moved agent (src/spaces/continuous.jl:133-153, :161-166).  Here a
@@ -11,225 +11,280 @@
 //   before  the fused step kernel has counted the new keys per fine cell
 //           (red.add into cell_count) and k_scan has turned the counts into the
 //           NEW cell_start, so every tile knows its output range up front and
-//           tiles are independent of each other (a first version chained the
-//           tiles by decoupled look-back: ~55 % of its time was spent waiting).
-//   CTA   = one tile.  It scans the OLD slots of the 3^D
-//           neighbouring fine cells of its tile (agents move less than one
-//           fine cell per step on this path), keeps those whose new key
-//           falls into the tile, buckets them per device cell in shared
-//           memory, orders every cell's agents by id (canonical
-//           order: bitwise reproducible runs whatever the atomic order was),
-//           and writes pos / vel / id / key coalesced and (optionally) count, Σ(pos - centre), Σ vel of the
-//           tile's part of every reference cell it touches (one partial per
-//           fine row of a reference cell, combined in fixed order by k_cell_M).
+//           tiles are independent of each other.
+//   WARP  = one tile.  It streams the OLD slots of the 3^D neighbouring fine
+//           rows of its tile (agents move less than one fine cell per step on
+//           this path) as ONE concatenated sequence — rows in (dz, dy) order,
+//           slots ascending — keeps those whose new key falls into the tile and
+//           gives each its final slot on the spot:
+//               slot = new cell_start[key] + (agents of that cell seen earlier
+//                      in the sequence),
+//           a STABLE rank computed with match.any inside the warp and a
+//           per-cell cursor in shared memory.  No atomics, no staging, no
+//           sorting pass: source reads are coalesced, each agent's row is read
+//           once and written once.
+//   order   inside a cell = order of the concatenated source sequence.  By
+//           induction over steps (the index build orders cells by id) this is
+//           a pure function of the trajectory: runs are bitwise reproducible
+//           and independent of how the space is cut into slabs (the source
+//           rows are enumerated geometrically, never by slot address).
+//   then    (optionally) count, Σ(pos - centre), Σ vel of the tile's part of
+//           every reference cell it touches (one partial per fine row of a
+//           reference cell, combined in fixed order by k_cell_M).
+//
+// (History, profiles/README.md: a CTA-per-tile version bucketed the entries in
+//  shared memory with atomics and ranked every cell by id with an O(n²) loop —
+//  30 warp instructions per agent, 71 us per 1 M agents; this one needs ~6.)
 //
 // Nothing here is specific to the flock rule: any fused rule that bounds the
-// per-step displacement by one reference cell can use it.
+// per-step displacement by one fine cell can use it.
 #include "ab_internal.cuh"
 
-#define RS_THREADS 256
-#define RS_MAXSEG 27
-#define RS_FC_MAX 1024          // device cells per tile (shared histogram)
-#define RS_CAP 2048             // agents per tile handled in shared memory; larger tiles use global scratch
+#define RS_WARPS 4
+#define RS_THREADS (RS_WARPS * 32)
+#define RS_MAXSEG 27            // 9 source rows x (main run + 2 periodic wrap cells)
+#define RS_TW_MAX 256           // fine cells per tile (cursor array per warp)
 
 struct ResortArgs {
     int tw, tpr, ntiles, nrows;
     int has_vel, want_agg;
 };
 
-template <class T, int D>
+template <class T, int D, int G>
 __global__ void __launch_bounds__(RS_THREADS)
 k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, const uint32_t* __restrict__ newkey,
          const int32_t* __restrict__ id_old, const T* __restrict__ src_pos, const T* __restrict__ src_vel,
-         int64_t cap, int n, T* __restrict__ dst_pos, T* __restrict__ dst_vel, int32_t* __restrict__ id_new,
+         int64_t cap, T* dst_pos, T* dst_vel, int32_t* __restrict__ id_new,
          uint32_t* __restrict__ key_new, const uint32_t* __restrict__ cs_new, int32_t* __restrict__ perm,
-         T* __restrict__ agg, int64_t agg_stride, int32_t* __restrict__ g_ent_id, int32_t* __restrict__ g_ent_s,
-         int* __restrict__ err) {
-    __shared__ uint32_t s_seg_beg[RS_MAXSEG], s_seg_end[RS_MAXSEG];
-    __shared__ int s_nseg;
-    __shared__ uint32_t s_cnt[RS_FC_MAX];        // per-cell cursor
-    __shared__ uint32_t s_start[RS_FC_MAX + 1];  // new cell_start of the tile's cells, relative to the tile's base
-    __shared__ uint32_t s_found;
-    __shared__ int32_t s_ent_id[RS_CAP], s_ent_s[RS_CAP];
-    __shared__ uint16_t s_ent_lc[RS_CAP];
-    __shared__ int32_t s_sorted_s[RS_CAP];
+         T* __restrict__ agg, int64_t agg_stride, int* __restrict__ err) {
+    __shared__ uint32_t s_beg[RS_WARPS][RS_MAXSEG];
+    __shared__ uint32_t s_pre[RS_WARPS][RS_MAXSEG + 1];
+    __shared__ uint32_t s_cur[RS_WARPS][RS_TW_MAX];
 
-    const int tid = threadIdx.x;
-    const int tile = blockIdx.x;
-    const int frow = tile / a.tpr, seg = tile - frow * a.tpr;      // fine row, segment of it
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int tile = blockIdx.x * RS_WARPS + w;
+    if (tile >= a.ntiles) return;                                  // warp-uniform; no CTA barriers below
+    const int frow = tile / a.tpr, seg_x = tile - frow * a.tpr;    // fine row, segment of it
     const int kb = sp.kb;
     const int fd0 = sp.dims[0] << kb, fd1 = sp.dims[1] << kb, fd2 = D == 3 ? (sp.dims[2] << kb) : 1;
-    const int x0 = seg * a.tw;
+    const int x0 = seg_x * a.tw;
     const int x1 = min(fd0, x0 + a.tw);          // exclusive, fine cells
     const uint32_t kbeg = (uint32_t)frow * (uint32_t)fd0 + (uint32_t)x0;
-    const uint32_t kend = (uint32_t)frow * (uint32_t)fd0 + (uint32_t)x1;
-    const int fc = (int)(kend - kbeg);
+    const int fc = x1 - x0;
+    const uint32_t kend = kbeg + (uint32_t)fc;
     const int fy0 = D == 2 ? frow : frow % fd1;
     const int fz0 = D == 2 ? 0 : frow / fd1;
+    const uint32_t base = cs_new[kbeg];
+    const uint32_t total = cs_new[kend] - base;
 
-    // ---- source segments: old slots of the neighbouring fine cells ----------------------
-    if (tid == 0) {
-        int ns = 0;
-        for (int dz = (D == 3 ? -1 : 0); dz <= (D == 3 ? 1 : 0); ++dz) {
-            int z = fz0 + dz;
-            if (D == 3 && (z < 0 || z >= fd2)) {
-                if (!sp.periodic[2]) continue;
-                z = z < 0 ? z + fd2 : z - fd2;
-            }
-            for (int dy = -1; dy <= 1; ++dy) {
-                int y = fy0 + dy;
-                if (y < 0 || y >= fd1) {
-                    if (!sp.periodic[1]) continue;
-                    y = y < 0 ? y + fd1 : y - fd1;
-                }
-                const uint32_t rb = (D == 3 ? (uint32_t)z * (uint32_t)fd1 + (uint32_t)y : (uint32_t)y) * (uint32_t)fd0;
-                const int lo = max(x0 - 1, 0), hi = min(x1, fd0 - 1);      // inclusive fine cells
-                s_seg_beg[ns] = cs_old[(size_t)rb + lo];
-                s_seg_end[ns] = cs_old[(size_t)rb + hi + 1];
-                ++ns;
-                if (sp.periodic[0]) {
-                    if (x0 == 0 && hi < fd0 - 1) {        // left neighbour wraps to the last cell of the row
-                        s_seg_beg[ns] = cs_old[(size_t)rb + fd0 - 1];
-                        s_seg_end[ns] = cs_old[(size_t)rb + fd0];
-                        ++ns;
-                    }
-                    if (x1 == fd0 && lo > 0) {            // right neighbour wraps to the first cell
-                        s_seg_beg[ns] = cs_old[(size_t)rb];
-                        s_seg_end[ns] = cs_old[(size_t)rb + 1];
-                        ++ns;
-                    }
-                }
+    if (total != 0) {
+    // ---- source segments: lane i describes segment i = 3*row + {main, left wrap, right wrap} ----
+    constexpr int NROW = D == 2 ? 3 : 9;
+    constexpr int NSEG = 3 * NROW;
+    uint32_t sb = 0, sl = 0;
+    if (lane < NSEG) {
+        const int r = lane / 3, j = lane - 3 * r;
+        const int dy = r % 3 - 1, dz = D == 3 ? r / 3 - 1 : 0;
+        int y = fy0 + dy, z = fz0 + dz;
+        bool ok = true;
+        if (y < 0 || y >= fd1) { if (!sp.periodic[1]) ok = false; y = y < 0 ? y + fd1 : y - fd1; }
+        if (D == 3 && (z < 0 || z >= fd2)) { if (!sp.periodic[2]) ok = false; z = z < 0 ? z + fd2 : z - fd2; }
+        const int lo = max(x0 - 1, 0), hi = min(x1, fd0 - 1);      // inclusive fine cells of the main run
+        int c0 = lo, c1 = hi + 1;                                  // [c0, c1) cells of this segment
+        if (j == 1) { ok = ok && sp.periodic[0] && x0 == 0 && hi < fd0 - 1; c0 = fd0 - 1; c1 = fd0; }
+        if (j == 2) { ok = ok && sp.periodic[0] && x1 == fd0 && lo > 0; c0 = 0; c1 = 1; }
+        if (ok) {
+            const size_t rb = (size_t)(D == 3 ? (uint32_t)z * (uint32_t)fd1 + (uint32_t)y : (uint32_t)y) * (uint32_t)fd0;
+            sb = cs_old[rb + c0];
+            sl = cs_old[rb + c1] - sb;
+        }
+    }
+    uint32_t inc = sl;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(FULL, inc, o); if (lane >= o) inc += t; }
+    const uint32_t L = __shfl_sync(FULL, inc, 31);                 // length of the concatenated source sequence
+    if (lane < NSEG) { s_beg[w][lane] = sb; s_pre[w][lane] = inc - sl; }
+    if (lane == 0) s_pre[w][NSEG] = L;
+    for (int i = lane; i < fc; i += 32) s_cur[w][i] = cs_new[(size_t)kbeg + i] - base;   // cursor = start
+    __syncwarp();
+
+    uint32_t found = 0;
+    int sg = 0;                                                    // this lane's current segment (monotone)
+    for (uint32_t v0 = 0; v0 < L; v0 += 32u * G) {
+        uint32_t k[G], s[G], o[G];
+        // phase 1: keys of G chunks (independent coalesced loads)
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            const uint32_t v = v0 + 32u * g + lane;
+            k[g] = 0xffffffffu;
+            s[g] = 0;
+            if (v < L) {
+                while (v >= s_pre[w][sg + 1]) ++sg;
+                s[g] = s_beg[w][sg] + (v - s_pre[w][sg]);
+                k[g] = newkey[s[g]];
             }
         }
-        s_nseg = ns;
-    }
-    const uint32_t base = cs_new[kbeg];
-    for (int i = tid; i <= fc; i += RS_THREADS) {
-        const uint32_t st = cs_new[(size_t)kbeg + i] - base;
-        s_start[i] = st;
-        if (i < fc) s_cnt[i] = st;                       // cursor = start
-    }
-    if (tid == 0) s_found = 0;
-    __syncthreads();
-    const int nseg = s_nseg;
-    const uint32_t total = s_start[fc];
-    const bool small = total <= RS_CAP;
-    int32_t* ent_id = small ? s_ent_id : g_ent_id + base;
-    int32_t* ent_s = small ? s_ent_s : g_ent_s + base;
-    uint32_t found = 0;
-    if (total != 0) {
-    // ---- entries into their cell segment (arrival order) ----------------------------------
-    for (int sg = 0; sg < nseg; ++sg) {
-        const uint32_t e = s_seg_end[sg];
-        for (uint32_t s = s_seg_beg[sg] + tid; s < e; s += RS_THREADS) {
-            const uint32_t k = newkey[s];
-            if (k >= kbeg && k < kend) {
-                const uint32_t lc = k - kbeg;
-                const uint32_t p = atomicAdd(&s_cnt[lc], 1u);
-                if (p < s_start[lc + 1]) {               // (always, unless the counts are inconsistent)
-                    ent_id[p] = id_old[s];
-                    ent_s[p] = (int32_t)s;
-                    if (small) s_ent_lc[p] = (uint16_t)lc;
-                }
+        // phase 2: stable rank inside the warp + per-cell cursor
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            const bool in = k[g] >= kbeg && k[g] < kend;
+            const uint32_t lc = in ? k[g] - kbeg : 0xffffffffu;
+            const unsigned m = __match_any_sync(FULL, lc);
+            o[g] = 0xffffffffu;
+            if (in) {
+                const uint32_t cur = s_cur[w][lc];
+                o[g] = base + cur + __popc(m & ((1u << lane) - 1u));
                 ++found;
+            }
+            __syncwarp();
+            if (in && (m >> lane) == 1u) s_cur[w][lc] += __popc(m);      // highest lane of the group advances the cursor
+            __syncwarp();
+        }
+        // phase 3: rows of the matching agents (reads coalesced in s), phase 4: stores
+        T pv[G][2 * D];
+        int32_t idv[G];
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            if (o[g] != 0xffffffffu) {
+#pragma unroll
+                for (int d = 0; d < D; ++d) pv[g][d] = src_pos[(size_t)d * cap + s[g]];
+                if (a.has_vel) {
+#pragma unroll
+                    for (int d = 0; d < D; ++d) pv[g][D + d] = src_vel[(size_t)d * cap + s[g]];
+                }
+                idv[g] = id_old[s[g]];
+            }
+        }
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            if (o[g] != 0xffffffffu) {
+                const size_t oo = o[g];
+#pragma unroll
+                for (int d = 0; d < D; ++d) dst_pos[(size_t)d * cap + oo] = pv[g][d];
+                if (a.has_vel) {
+#pragma unroll
+                    for (int d = 0; d < D; ++d) dst_vel[(size_t)d * cap + oo] = pv[g][D + d];
+                }
+                id_new[oo] = idv[g];
+                key_new[oo] = k[g];
+                if (perm) perm[oo] = (int32_t)s[g];
             }
         }
     }
     // every agent counted into this tile must have been found in the 3^D neighbourhood
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) found += __shfl_xor_sync(0xffffffffu, found, o);
-    if ((tid & 31) == 0 && found) atomicAdd(&s_found, found);
-    __syncthreads();
-    if (tid == 0 && s_found != total) atomicOr(err, AB_EF_OVERFLOW);     // an agent left its 3^D neighbourhood
-    if (s_found != total) return;
-
-    // ---- canonical order inside every cell (by id), then coalesced output ------------------
-    if (small) {
-        for (uint32_t p = tid; p < total; p += RS_THREADS) {
-            const uint32_t lc = s_ent_lc[p];
-            const uint32_t b = s_start[lc], e = s_start[lc + 1];
-            const int32_t me = s_ent_id[p];
-            uint32_t r = 0;
-            for (uint32_t t = b; t < e; ++t) r += (s_ent_id[t] < me) ? 1u : 0u;
-            s_sorted_s[b + r] = (int32_t)p;        // sorted position -> entry
-        }
-        __syncthreads();
-        for (uint32_t t = tid; t < total; t += RS_THREADS) {
-            const int p = s_sorted_s[t];
-            const int s = s_ent_s[p];
-            const size_t o = (size_t)base + t;
-#pragma unroll
-            for (int d = 0; d < D; ++d) dst_pos[(size_t)d * cap + o] = src_pos[(size_t)d * cap + s];
-            if (a.has_vel) {
-#pragma unroll
-                for (int d = 0; d < D; ++d) dst_vel[(size_t)d * cap + o] = src_vel[(size_t)d * cap + s];
-            }
-            id_new[o] = s_ent_id[p];
-            key_new[o] = kbeg + s_ent_lc[p];
-            if (perm) perm[o] = s;
-        }
-    } else {
-        // crowded tile: entries live in global scratch at [base, base + total); same steps through L2
-        for (uint32_t p = tid; p < total; p += RS_THREADS) {
-            const uint32_t k = newkey[ent_s[p]];
-            const uint32_t lc = k - kbeg;
-            const uint32_t b = s_start[lc], e = s_start[lc + 1];
-            const int32_t me = ent_id[p];
-            uint32_t r = p - b;                                  // arrival order for very crowded cells
-            if (e - b <= 4096u) { r = 0; for (uint32_t t = b; t < e; ++t) r += (ent_id[t] < me) ? 1u : 0u; }
-            const int s = ent_s[p];
-            const size_t o = (size_t)base + b + r;
-#pragma unroll
-            for (int d = 0; d < D; ++d) dst_pos[(size_t)d * cap + o] = src_pos[(size_t)d * cap + s];
-            if (a.has_vel) {
-#pragma unroll
-                for (int d = 0; d < D; ++d) dst_vel[(size_t)d * cap + o] = src_vel[(size_t)d * cap + s];
-            }
-            id_new[o] = me;
-            key_new[o] = k;
-            if (perm) perm[o] = s;
-        }
+    for (int o2 = 16; o2 > 0; o2 >>= 1) found += __shfl_xor_sync(FULL, found, o2);
+    if (found != total) {
+        if (lane == 0) atomicOr(err, AB_EF_OVERFLOW);              // an agent left its 3^D neighbourhood
+        return;
     }
-
     }   // total != 0
 
     // ---- per reference cell: count, Σ(pos - centre), Σ vel of this fine row's part, canonical order ---
+    // Canonical sum of a cell's n agents (shared with k_cell_agg): 8 strided partials a_g = Σ_i x[g + 8 i]
+    // combined as ((a0+a4)+(a2+a6)) + ((a1+a5)+(a3+a7)).  Cells with n <= 8 (nearly all of them in a dilute
+    // state) are summed by ONE lane — each partial is a single term — cells with more by an 8-lane group.
     if (a.want_agg) {
-        __syncthreads();     // the tile's output slots are complete (global writes of this CTA are visible to it)
+        __syncwarp();        // the tile's output slots were written by this warp; read them back through L2
         constexpr int NC = 1 + 2 * D;
         const int K = sp.K;
-        const int ncell = (x1 - x0) >> kb;                    // x0 and tw are multiples of K
-        const int grp = tid >> 3, gl = tid & 7;               // 8 lanes per reference cell
+        const int ncell = fc >> kb;                           // x0 and tw are multiples of K
         const int cy = fy0 >> kb, cz = fz0 >> kb;
         const int part = (fy0 & (K - 1)) + K * (fz0 & (K - 1));
-        for (int c = grp; c < ncell; c += RS_THREADS / 8) {
-            const uint32_t b = base + s_start[(size_t)c << kb], e = base + s_start[(size_t)(c + 1) << kb];
-            const int cx = (x0 >> kb) + c;
-            const uint32_t refcell = (D == 3 ? ((uint32_t)cz * sp.dims[1] + cy) : (uint32_t)cy) * (uint32_t)sp.dims[0] + (uint32_t)cx;
-            int cc[3] = {cx, cy, cz};
+        const uint32_t refrow = (D == 3 ? ((uint32_t)cz * sp.dims[1] + cy) : (uint32_t)cy) * (uint32_t)sp.dims[0];
+        T* aggp = agg + (size_t)part * NC * agg_stride + refrow;
+        T ctr[D];                                             // centre of the row's cells in the other dimensions
+        {
+            int cc[3] = {0, cy, cz};
             cc[D - 1] = local_to_global_last<T, D>(sp, cc[D - 1]);     // centres are global (slab window)
-            T acc[2 * D];
 #pragma unroll
-            for (int d = 0; d < 2 * D; ++d) acc[d] = T(0);
-            for (uint32_t t = b + gl; t < e; t += 8) {
+            for (int d = 1; d < D; ++d) ctr[d] = sp.spacing * ((T)(cc[d] + 1) - T(0.5));
+        }
+        for (int c0 = 0; c0 < ncell; c0 += 32) {
+            const int c = c0 + lane;
+            const bool live = c < ncell;
+            uint32_t b = 0, e = 0;
+            if (live) {
+                // after the placement the cursor of a fine cell is its end (= the next cell's start)
+                const int f0 = c << kb, f1 = (c + 1) << kb;
+                b = base + (total && f0 ? s_cur[w][f0 - 1] : 0u);
+                e = base + (total ? s_cur[w][f1 - 1] : 0u);
+            }
+            const uint32_t n = e - b;
+            const int cx = (x0 >> kb) + c;
+            if (live && n <= 8u) {
+                ctr[0] = sp.spacing * ((T)(cx + 1) - T(0.5));
+                // pair(i) = x[i] + x[i + 4] with x[i] = 0 + term i (0 beyond n): the group path's partials
+                auto pair = [&](int i, T* out) {
+                    T u[2 * D], v[2 * D];
 #pragma unroll
-                for (int d = 0; d < D; ++d) {
-                    const T centre = sp.spacing * ((T)(cc[d] + 1) - T(0.5));
-                    acc[d] += dst_pos[(size_t)d * cap + t] - centre;
-                    acc[D + d] += dst_vel[(size_t)d * cap + t];
+                    for (int d = 0; d < 2 * D; ++d) u[d] = v[d] = T(0);
+                    if ((uint32_t)i < n) {
+#pragma unroll
+                        for (int d = 0; d < D; ++d) {
+                            u[d] += __ldcg(dst_pos + (size_t)d * cap + b + i) - ctr[d];
+                            u[D + d] += __ldcg(dst_vel + (size_t)d * cap + b + i);
+                        }
+                    }
+                    if ((uint32_t)(i + 4) < n) {
+#pragma unroll
+                        for (int d = 0; d < D; ++d) {
+                            v[d] += __ldcg(dst_pos + (size_t)d * cap + b + i + 4) - ctr[d];
+                            v[D + d] += __ldcg(dst_vel + (size_t)d * cap + b + i + 4);
+                        }
+                    }
+#pragma unroll
+                    for (int d = 0; d < 2 * D; ++d) out[d] = u[d] + v[d];
+                };
+                T p0[2 * D], p1[2 * D], q[2 * D];
+                pair(0, p0); pair(2, p1);
+#pragma unroll
+                for (int d = 0; d < 2 * D; ++d) q[d] = p0[d] + p1[d];
+                pair(1, p0); pair(3, p1);
+                aggp[cx] = (T)n;
+#pragma unroll
+                for (int d = 0; d < 2 * D; ++d) aggp[(size_t)(1 + d) * agg_stride + cx] = q[d] + (p0[d] + p1[d]);
+            }
+            // crowded cells: 8 lanes per cell, 4 cells at a time
+            unsigned big = __ballot_sync(FULL, live && n > 8u);
+            const int grp = lane >> 3, gl = lane & 7;
+            while (big) {
+                unsigned rest = big;
+                int src = -1;
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                    const int l = rest ? __ffs(rest) - 1 : -1;
+                    if (l >= 0) rest &= rest - 1;
+                    if (g == grp) src = l;
                 }
-            }
+                big = rest;
+                const uint32_t gb = __shfl_sync(FULL, b, src < 0 ? 0 : src), ge = __shfl_sync(FULL, e, src < 0 ? 0 : src);
+                const int gcx = (x0 >> kb) + c0 + src;
+                ctr[0] = sp.spacing * ((T)(gcx + 1) - T(0.5));
+                T acc[2 * D];
 #pragma unroll
-            for (int d = 0; d < 2 * D; ++d) {
-                acc[d] += __shfl_xor_sync(0xffffffffu, acc[d], 4);
-                acc[d] += __shfl_xor_sync(0xffffffffu, acc[d], 2);
-                acc[d] += __shfl_xor_sync(0xffffffffu, acc[d], 1);
-            }
-            if (gl == 0) {
-                T* dst = agg + (size_t)part * NC * agg_stride + refcell;
-                dst[0] = (T)(e - b);
+                for (int d = 0; d < 2 * D; ++d) acc[d] = T(0);
+                if (src >= 0) {
+                    for (uint32_t t = gb + gl; t < ge; t += 8) {
 #pragma unroll
-                for (int d = 0; d < 2 * D; ++d) dst[(size_t)(1 + d) * agg_stride] = acc[d];
+                        for (int d = 0; d < D; ++d) {
+                            acc[d] += __ldcg(dst_pos + (size_t)d * cap + t) - ctr[d];
+                            acc[D + d] += __ldcg(dst_vel + (size_t)d * cap + t);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int d = 0; d < 2 * D; ++d) {
+                    acc[d] += __shfl_xor_sync(FULL, acc[d], 4);
+                    acc[d] += __shfl_xor_sync(FULL, acc[d], 2);
+                    acc[d] += __shfl_xor_sync(FULL, acc[d], 1);
+                }
+                if (src >= 0 && gl == 0) {
+                    aggp[gcx] = (T)(ge - gb);
+#pragma unroll
+                    for (int d = 0; d < 2 * D; ++d) aggp[(size_t)(1 + d) * agg_stride + gcx] = acc[d];
+                }
             }
         }
     }
@@ -305,17 +360,18 @@ static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool
     const int cur = h->cur, nxt = cur ^ 1;
     SpaceDev<T, D> sp = make_space<T, D>(h);
     ResortArgs a;
-    // tile width (fine cells of one fine row): ~RS_TARGET agents per tile on average, at most
-    // RS_FC_MAX fine cells, a multiple of K so that tiles hold whole reference cells
+    // tile width (fine cells of one fine row): ~rs_target agents per tile on average, at most
+    // RS_TW_MAX fine cells, a multiple of K so that tiles hold whole reference cells
     const int fd0 = h->dims[0] << h->kb;
     const double dens = (double)h->n / (double)h->nfine;
     int tw = (int)((double)h->rs_target / (dens > 1e-9 ? dens : 1e-9));
-    if (tw > RS_FC_MAX) tw = RS_FC_MAX;
-    if (tw < 8) tw = 8;
+    if (tw > RS_TW_MAX) tw = RS_TW_MAX;
+    if (tw < 4) tw = 4;
     if (tw > fd0) tw = fd0;
     a.tpr = (fd0 + tw - 1) / tw;
     a.tw = (fd0 + a.tpr - 1) / a.tpr;                 // even split of the row
     a.tw = (a.tw + h->K - 1) / h->K * h->K;
+    if (a.tw > RS_TW_MAX) a.tw = RS_TW_MAX / h->K * h->K;
     a.tpr = (fd0 + a.tw - 1) / a.tw;
     a.nrows = (int)(h->nfine / fd0);
     // slab window: only the owned fine rows (they come first in key order) are re-sorted here; the halo
@@ -330,10 +386,11 @@ static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool
     const bool extra = h->fields.size() > 2u;
     {
         AB_LAUNCH(h, "k_resort");
-        k_resort<T, D><<<a.ntiles, RS_THREADS, 0, h->stream>>>(
-            sp, a, h->cell_start, h->newkey, h->id[cur], (const T*)src_pos, (const T*)src_vel, h->cap, (int)h->n,
+        constexpr int G = (D == 2) ? 4 : 2;           // source chunks in flight per warp
+        k_resort<T, D, G><<<(a.ntiles + RS_WARPS - 1) / RS_WARPS, RS_THREADS, 0, h->stream>>>(
+            sp, a, h->cell_start, h->newkey, h->id[cur], (const T*)src_pos, (const T*)src_vel, h->cap,
             (T*)h->fields[0].buf[nxt], (T*)h->fields[1].buf[nxt], h->id[nxt], h->key[nxt], h->cell_start_alt,
-            extra ? h->perm : nullptr, (T*)h->cell_agg, (int64_t)h->ncells, h->idtmp, (int32_t*)h->rank, h->d_err);
+            extra ? h->perm : nullptr, (T*)h->cell_agg, (int64_t)h->ncells, h->d_err);
     }
     std::swap(h->cell_start, h->cell_start_alt);
     AB_TRY(ab_permute_extra_fields(h));
