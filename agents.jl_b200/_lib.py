@@ -58,6 +58,7 @@ _SIGS = {
     "ab_destroy": (C.c_int, [_H]),
     "ab_last_error": (C.c_char_p, [_H]),
     "ab_sync": (C.c_int, [_H]),
+    "ab_set_async": (C.c_int, [_H, C.c_int]),
     "ab_version": (C.c_int, []),
     "ab_nagents": (C.c_int64, [_H]),
     "ab_alloc_pinned": (C.c_void_p, [C.c_int64]),

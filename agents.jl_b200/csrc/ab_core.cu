@@ -92,6 +92,7 @@ int ab_scratch2(ab_handle* h, size_t bytes, void** out) {
 }
 
 int ab_check_device_errors(ab_handle* h) {
+    if (h->async_mode) return AB_OK;      // deferred to ab_sync
     AB_CUDA(h, cudaMemcpyAsync(h->h_err, h->d_err, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     AB_CUDA(h, cudaStreamSynchronize(h->stream));
     int e = *h->h_err;
@@ -564,7 +565,29 @@ int ab_destroy(ab_handle* h) {
 }
 
 int ab_sync(ab_handle* h) {
+    AB_CUDA(h, cudaSetDevice(h->device));
     AB_CUDA(h, cudaStreamSynchronize(h->stream));
+    if (h->step_pending) {
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, h->ev0, h->ev1) == cudaSuccess) h->last_step_ms = ms;
+        h->step_pending = false;
+    }
+    if (h->async_mode) {                  // device-side failures of everything queued since the last ab_sync
+        h->async_mode = false;
+        const int rc = ab_check_device_errors(h);
+        h->async_mode = true;
+        return rc;
+    }
+    return AB_OK;
+}
+// Asynchronous mode: ab_upload / ab_download / ab_step_flock / ab_build_index return as soon as their
+// copies and kernels are queued on the handle's stream (host buffers must be pinned and stay valid);
+// ab_sync waits and reports what failed on the device in between.  Handles own separate streams, so
+// independent models queued this way overlap their transfers and steps (ensemble runs).
+int ab_set_async(ab_handle* h, int on) {
+    if (h->win_W) return ab_fail(h, AB_ERR_STATE, "not available on a sharded handle");
+    if (!on && h->async_mode) { const int rc = ab_sync(h); h->async_mode = false; return rc; }
+    h->async_mode = on != 0;
     return AB_OK;
 }
 int64_t ab_nagents(const ab_handle* h) { return h ? h->n : 0; }
@@ -673,7 +696,7 @@ int ab_upload(ab_handle* h, int field, const void* host, int64_t n) {
         else if (f.esize == 4) k_upload<uint32_t><<<ab_blocks(total, 256), 256, 0, h->stream>>>((const uint32_t*)stage, (uint32_t*)f.buf[h->cur], h->slot_of_id, h->cap, (int)n, f.ncomp);
         else k_upload<uint8_t><<<ab_blocks(total, 256), 256, 0, h->stream>>>((const uint8_t*)stage, (uint8_t*)f.buf[h->cur], h->slot_of_id, h->cap, (int)n, f.ncomp);
     }
-    AB_CUDA(h, cudaStreamSynchronize(h->stream));
+    if (!h->async_mode) AB_CUDA(h, cudaStreamSynchronize(h->stream));
     if (field == 0) { h->index_valid = false; h->pairs_n = -1; }
     return AB_OK;
 }
@@ -697,7 +720,7 @@ int ab_download(ab_handle* h, int field, void* host, int64_t n) {
         else k_download<uint8_t><<<ab_blocks(n, 256), 256, 0, h->stream>>>((const uint8_t*)f.buf[h->cur], (uint8_t*)stage, h->id[h->cur], h->cap, (int)n, f.ncomp);
     }
     AB_CUDA(h, cudaMemcpyAsync(host, stage, bytes, cudaMemcpyDeviceToHost, h->stream));
-    AB_CUDA(h, cudaStreamSynchronize(h->stream));
+    if (!h->async_mode) AB_CUDA(h, cudaStreamSynchronize(h->stream));
     return AB_OK;
 }
 

@@ -433,6 +433,7 @@ int ab_step_flock(ab_handle* h, const ab_flock_params* p, int64_t nsteps) {
     if (h->dtype == AB_F64) rc = h->D == 2 ? flock_steps_t<double, 2>(h, p, nsteps) : flock_steps_t<double, 3>(h, p, nsteps);
     else rc = h->D == 2 ? flock_steps_t<float, 2>(h, p, nsteps) : flock_steps_t<float, 3>(h, p, nsteps);
     AB_TRY(rc);
+    if (h->async_mode) { h->step_pending = true; return AB_OK; }     // errors and timing: ab_sync
     AB_TRY(ab_check_device_errors(h));
     if (h->win_W) AB_TRY(ab_comm_refresh_counts(h));
     float ms = 0;

@@ -141,6 +141,8 @@ struct ab_handle {
 
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     double last_step_ms = 0;
+    bool async_mode = false;           // ab_set_async: calls return once their work is queued; ab_sync collects errors
+    bool step_pending = false;         // ev0/ev1 of an asynchronous step not read yet
     int64_t launches = 0;
     bool profiling = false;
     std::vector<ab_kernel_stat> kstats;

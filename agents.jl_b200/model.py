@@ -397,6 +397,27 @@ class StandardABM:
         self._ck(self.lib.ab_flock_last_counts(self.h, self._ptr(out), n))
         return out
 
+    def set_async(self, on=True):
+        """Asynchronous mode (ab_set_async): upload / step / download calls return once queued on the
+        model's stream; `sync()` waits and raises what failed on the device in between.  Buffers handed
+        to `upload_rows` / `download_rows` must be pinned and stay alive until `sync()`."""
+        self._ck(self.lib.ab_set_async(self.h, 1 if on else 0))
+        return self
+
+    def sync(self):
+        self._ck(self.lib.ab_sync(self.h))
+        return self
+
+    def upload_rows(self, name, rows):
+        """Column `name` from a caller-owned (ideally pinned) row-per-agent array, id order; no copy is made."""
+        self._ck(self.lib.ab_upload(self.h, self._columns[name], self._ptr(rows), self.nagents()))
+        return self
+
+    def download_rows(self, name, out):
+        """Column `name` into a caller-owned (ideally pinned) row-per-agent array, id order."""
+        self._ck(self.lib.ab_download(self.h, self._columns[name], self._ptr(out), self.nagents()))
+        return out
+
     def launch_count(self):
         return int(self.lib.ab_launch_count(self.h))
 

@@ -100,6 +100,12 @@ int ab_create(ab_space_desc* desc, int device, ab_handle** out);
 int ab_destroy(ab_handle* h);
 const char* ab_last_error(const ab_handle* h);   /* h may be NULL: last ab_create error */
 int ab_sync(ab_handle* h);
+/* Asynchronous mode (no reference counterpart: Agents.jl is single-task; this is what an
+ * ensemblerun!-style driver, src/simulations/ensemblerun.jl, uses to keep several models in flight):
+ * ab_upload / ab_download / ab_step_flock / ab_build_index return once their work is queued on
+ * the handle's stream — host buffers must be pinned (ab_alloc_pinned) and stay valid — and
+ * ab_sync waits and returns the first device-side failure since the previous ab_sync. */
+int ab_set_async(ab_handle* h, int on);
 int ab_version(void);
 int64_t ab_nagents(const ab_handle* h);
 
