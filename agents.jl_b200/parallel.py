@@ -106,6 +106,34 @@ class Slabs:
         m._ck(lib.ab_build_index(m.h))
         return int(owned.sum())
 
+    def scatter_chunks(self, chunks, n_global, halo_capacity=None, capacity_factor=1.6):
+        """Like `scatter` for populations too large to materialise on every rank: `chunks` yields
+        (first_id0, pos_chunk, vel_chunk) pieces of the global id-ordered state; only this rank's window
+        of each piece is kept."""
+        m, lib = self.model, self.model.lib
+        dt = m.space.dtype
+        self.n_global = int(n_global)
+        keep_ids, keep_p, keep_v, owned_n = [], [], [], 0
+        for first, pos, vel in chunks:
+            pos = np.ascontiguousarray(pos, dtype=dt).reshape(-1, m.D)
+            vel = np.ascontiguousarray(vel, dtype=dt).reshape(-1, m.D)
+            layer = cell_layer(pos[:, -1], m.space.spacing, self.n_layers)
+            idx, owned = select_window(layer, self.first, self.count, self.n_layers)
+            keep_ids.append((idx + first + 1).astype(np.int64))
+            keep_p.append(pos[idx])
+            keep_v.append(vel[idx])
+            owned_n += int(owned.sum())
+        gids = np.concatenate(keep_ids)
+        p = np.ascontiguousarray(np.concatenate(keep_p))
+        v = np.ascontiguousarray(np.concatenate(keep_v))
+        cap = halo_capacity or default_halo_capacity(self.n_global, self.n_layers)
+        m._ck(lib.ab_comm_set_capacity(m.h, int(cap)))
+        m._ck(lib.ab_resize(m.h, int(len(gids) * capacity_factor) + 2 * int(cap) + 1024))
+        m._ck(lib.ab_upload_local(m.h, 0, m._ptr(p), m._ptr(gids), len(gids)))
+        m._ck(lib.ab_upload_local(m.h, 1, m._ptr(v), m._ptr(gids), len(gids)))
+        m._ck(lib.ab_build_index(m.h))
+        return owned_n
+
     def local_state(self):
         """(global ids, pos, vel) of the agents this rank owns now."""
         m, lib = self.model, self.model.lib
