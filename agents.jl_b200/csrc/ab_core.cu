@@ -142,9 +142,6 @@ __global__ void k_count(SpaceDev<T, D> sp, const T* __restrict__ pos, int64_t ca
 // aggregates at about the same time, so a 32-wide window needs ntiles/32
 // dependent L2 round trips (measured: 20 us for 313 tiles) where the
 // CTA-wide window needs one or two.
-#define SCAN_THREADS 256
-#define SCAN_ITEMS 8
-#define SCAN_TILE (SCAN_THREADS * SCAN_ITEMS)
 __global__ void __launch_bounds__(SCAN_THREADS)
 k_scan(uint32_t* __restrict__ count, uint32_t* __restrict__ start, uint32_t n, uint32_t ntiles,
        volatile unsigned long long* status, uint32_t* ticket, uint32_t epoch) {
@@ -158,13 +155,13 @@ k_scan(uint32_t* __restrict__ count, uint32_t* __restrict__ start, uint32_t n, u
     const uint32_t tile = s_tile;
     const uint32_t base = tile * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
     uint32_t v[SCAN_ITEMS];
-    {
-        uint4 a = *reinterpret_cast<const uint4*>(count + base);
-        uint4 b = *reinterpret_cast<const uint4*>(count + base + 4);
-        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
-        *reinterpret_cast<uint4*>(count + base) = make_uint4(0, 0, 0, 0);
-        *reinterpret_cast<uint4*>(count + base + 4) = make_uint4(0, 0, 0, 0);
+#pragma unroll
+    for (int q = 0; q < SCAN_ITEMS / 4; ++q) {
+        const uint4 a = *reinterpret_cast<const uint4*>(count + base + 4 * q);
+        v[4 * q] = a.x; v[4 * q + 1] = a.y; v[4 * q + 2] = a.z; v[4 * q + 3] = a.w;
     }
+#pragma unroll
+    for (int q = 0; q < SCAN_ITEMS / 4; ++q) *reinterpret_cast<uint4*>(count + base + 4 * q) = make_uint4(0, 0, 0, 0);
     uint32_t tsum = 0;
 #pragma unroll
     for (int i = 0; i < SCAN_ITEMS; ++i) { uint32_t t = v[i]; v[i] = tsum; tsum += t; }

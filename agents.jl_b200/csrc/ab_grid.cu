@@ -642,7 +642,7 @@ extern "C" int ab_step_schelling(ab_handle* h, const ab_schelling_params* p, int
     const int64_t ncells = h->ncells;
     const bool fast = h->dims[0] % 128 == 0;               // whole-warp rows: k_sch_happy4 / k_sch_compact4
     const int nblocks = fast ? (int)(ncells / 128) : ab_blocks(ncells, SCH_TB);
-    const size_t nbpad = ((size_t)nblocks + 2047) / 2048 * 2048 + 2048;
+    const size_t nbpad = ((size_t)nblocks + SCAN_TILE - 1) / SCAN_TILE * SCAN_TILE + SCAN_TILE;
     // scratch: blockU, blockE (padded), baseU, baseE (nblocks + 1), U (<= n), E (<= ncells - n), moved
     uint32_t *blockU = nullptr, *blockE = nullptr, *baseU = nullptr, *baseE = nullptr, *U = nullptr, *E = nullptr;
     long long* d_moved = nullptr;

@@ -179,7 +179,15 @@ int ab_resort_tiled(ab_handle* h, const void* src_pos, const void* src_vel, bool
 int ab_ensure_agg(ab_handle* h);
 int ab_agg_range(ab_handle* h, int64_t cell0, int64_t ncell);
 int ab_run_scan(ab_handle* h, uint32_t* dst);
-int ab_scan_u32(ab_handle* h, uint32_t* count, uint32_t* start, uint32_t n);   // count padded to a multiple of 2048             // cell_count -> exclusive offsets in dst (zeroes cell_count)
+// tile of the single-pass scan (k_scan, ab_core.cu): CTA size x items per thread
+#ifndef SCAN_THREADS
+#define SCAN_THREADS 256
+#endif
+#ifndef SCAN_ITEMS
+#define SCAN_ITEMS 16
+#endif
+#define SCAN_TILE (SCAN_THREADS * SCAN_ITEMS)
+int ab_scan_u32(ab_handle* h, uint32_t* count, uint32_t* start, uint32_t n);   // count padded to a multiple of SCAN_TILE             // cell_count -> exclusive offsets in dst (zeroes cell_count)
 size_t ab_dtype_size(int dtype);
 // cross-file internals (C++ linkage)
 void ab_comm_free(ab_handle* h);
