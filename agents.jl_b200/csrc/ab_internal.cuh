@@ -141,6 +141,7 @@ struct ab_handle {
 
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     double last_step_ms = 0;
+    std::vector<int64_t> near_lo, near_hi;   // result of the last ab_pairs_nearest
     bool async_mode = false;           // ab_set_async: calls return once their work is queued; ab_sync collects errors
     bool step_pending = false;         // ev0/ev1 of an asynchronous step not read yet
     int64_t launches = 0;

@@ -7,6 +7,9 @@
 // (per-query grid_r, euclidean offset mask, wrap / skip rules), so id sets are
 // bit-identical to the reference's — including its quirks (the approximate set
 // is asymmetric; `:exact` only filters the approximate candidates).
+#include <unordered_map>
+#include <unordered_set>
+
 #include "ab_internal.cuh"
 
 // euclidean_distance² as the reference sums it (utilities.jl:84-116), in T
@@ -138,7 +141,7 @@ __global__ void k_pairs(SpaceDev<T, D> sp, double r, int exact, const T* __restr
 template <class T, int D>
 __global__ void k_nearest(SpaceDev<T, D> sp, double r, const T* __restrict__ pos, const int32_t* __restrict__ id,
                           const uint32_t* __restrict__ key, const uint32_t* __restrict__ cell_start, int64_t cap,
-                          int n, int64_t* __restrict__ out) {
+                          int n, int64_t* __restrict__ out, double* __restrict__ dist) {
     int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
     T p[D];
@@ -161,6 +164,7 @@ __global__ void k_nearest(SpaceDev<T, D> sp, double r, const T* __restrict__ pos
         }
     });
     out[id[s]] = (best > r || bj < 0) ? 0 : (int64_t)id[bj] + 1;     // continuous.jl:306
+    if (dist) dist[id[s]] = best;                                    // euclidean_distance to it (true_pairs!, :469)
 }
 
 // --- small 64-bit exclusive scan (query helper, not on the step path) --------
@@ -349,7 +353,7 @@ int ab_pairs_fill(ab_handle* h, int64_t* lo, int64_t* hi, int64_t npairs) {
     return AB_OK;
 }
 
-int ab_nearest_neighbor(ab_handle* h, double r, int64_t* out, int64_t n) {
+static int nearest_common(ab_handle* h, double r, int64_t* out, double* dist, int64_t n) {
     if (h->win_W) return ab_fail(h, AB_ERR_STATE, "neighbour queries are not available on a sharded (slab-window) handle");
     if (h->desc.kind != AB_SPACE_CONTINUOUS) return ab_fail(h, AB_ERR_INVALID, "nearest_neighbor needs a ContinuousSpace handle");
     if (n != h->n) return ab_fail(h, AB_ERR_INVALID, "length must equal the agent count");
@@ -357,17 +361,95 @@ int ab_nearest_neighbor(ab_handle* h, double r, int64_t* out, int64_t n) {
     AB_CUDA(h, cudaSetDevice(h->device));
     AB_TRY(ab_ensure_index(h));
     int64_t* dev;
-    AB_TRY(ab_scratch(h, (size_t)n * 8 + 256, (void**)&dev));
+    AB_TRY(ab_scratch(h, (size_t)n * 16 + 256, (void**)&dev));
+    double* ddev = dist ? (double*)(dev + n) : nullptr;
     {
         AB_LAUNCH(h, "k_nearest");
         const int cur = h->cur;
-#define NN(T, DD) k_nearest<T, DD><<<ab_blocks(n, 128), 128, 0, h->stream>>>(make_space<T, DD>(h), r, (const T*)h->fields[0].buf[cur], h->id[cur], h->key[cur], h->cell_start, h->cap, (int)n, dev)
+#define NN(T, DD) k_nearest<T, DD><<<ab_blocks(n, 128), 128, 0, h->stream>>>(make_space<T, DD>(h), r, (const T*)h->fields[0].buf[cur], h->id[cur], h->key[cur], h->cell_start, h->cap, (int)n, dev, ddev)
         if (h->dtype == AB_F64) { if (h->D == 2) NN(double, 2); else NN(double, 3); }
         else { if (h->D == 2) NN(float, 2); else NN(float, 3); }
 #undef NN
     }
     AB_CUDA(h, cudaMemcpyAsync(out, dev, (size_t)n * 8, cudaMemcpyDeviceToHost, h->stream));
+    if (dist) AB_CUDA(h, cudaMemcpyAsync(dist, ddev, (size_t)n * 8, cudaMemcpyDeviceToHost, h->stream));
     AB_CUDA(h, cudaStreamSynchronize(h->stream));
+    return AB_OK;
+}
+
+int ab_nearest_neighbor(ab_handle* h, double r, int64_t* out, int64_t n) { return nearest_common(h, r, out, nullptr, n); }
+
+// interacting_pairs(model, r, :nearest; scheduler) — true_pairs!, continuous.jl:454-497.  The nearest
+// neighbours (and their distances) of ALL agents come from one k_nearest launch; the reference's pair
+// bookkeeping is sequential in scheduler order and is restated here on the host with hash maps in place
+// of its linear `findfirst` scans (same results: every id heads at most one pair, :471-479).
+int ab_pairs_nearest(ab_handle* h, double r, const int64_t* order, int64_t norder, int64_t* npairs) {
+    if (!npairs) return ab_fail(h, AB_ERR_INVALID, "null npairs");
+    const int64_t n = h->n;
+    h->near_lo.clear();
+    h->near_hi.clear();
+    *npairs = 0;
+    if (n == 0) return AB_OK;
+    std::vector<int64_t> nn((size_t)n);
+    std::vector<double> dd((size_t)n);
+    AB_TRY(nearest_common(h, r, nn.data(), dd.data(), n));
+    std::vector<int64_t> lo, hi;
+    std::vector<double> dist;
+    std::unordered_map<int64_t, size_t> head;           // first element -> index of its (only) pair
+    std::unordered_set<uint64_t> present;
+    auto key = [](int64_t a, int64_t b) { return ((uint64_t)a << 32) | (uint64_t)b; };
+    const int64_t cnt = order ? norder : n;
+    for (int64_t t = 0; t < cnt; ++t) {
+        const int64_t id = order ? order[t] : t + 1;
+        if (id < 1 || id > n) return ab_fail(h, AB_ERR_INVALID, "scheduled id out of range");
+        const int64_t j = nn[(size_t)id - 1];
+        if (!j) continue;                                // nearest_neighbor === nothing (:459)
+        const int64_t a = id < j ? id : j, b = id < j ? j : id;
+        if (present.count(key(a, b))) continue;          // new_pair ∉ pairs (:462)
+        const double d = dd[(size_t)id - 1];
+        auto it = head.find(a);
+        if (it == head.end()) {
+            head[a] = lo.size();
+            lo.push_back(a); hi.push_back(b); dist.push_back(d);
+            present.insert(key(a, b));
+        } else if (dist[it->second] > d) {               // replace: not the true neighbour (:474-478)
+            const size_t i = it->second;
+            present.erase(key(lo[i], hi[i]));
+            hi[i] = b; dist[i] = d;
+            present.insert(key(a, b));
+        }
+    }
+    // ids that occur in more than one pair keep only their closest pair (:481-496)
+    std::unordered_map<int64_t, int> occ;
+    std::unordered_map<int64_t, std::vector<size_t>> tails;   // last element -> indices, ascending
+    for (size_t i = 0; i < lo.size(); ++i) { occ[lo[i]]++; occ[hi[i]]++; tails[hi[i]].push_back(i); }
+    std::vector<size_t> rm;
+    for (auto& kv : occ) {
+        if (kv.second < 2) continue;
+        auto f = head.find(kv.first);
+        auto& tl = tails[kv.first];
+        if (f != head.end()) {
+            if (tl.empty()) continue;
+            const size_t fidx = f->second, lidx = tl[0];
+            rm.push_back(dist[fidx] <= dist[lidx] ? lidx : fidx);
+        } else {
+            size_t keep = 0;
+            for (size_t q = 1; q < tl.size(); ++q) if (dist[tl[q]] < dist[tl[keep]]) keep = q;   // findmin: first minimum
+            for (size_t q = 0; q < tl.size(); ++q) if (q != keep) rm.push_back(tl[q]);
+        }
+    }
+    std::vector<char> dead(lo.size(), 0);
+    for (size_t i : rm) dead[i] = 1;
+    for (size_t i = 0; i < lo.size(); ++i)
+        if (!dead[i]) { h->near_lo.push_back(lo[i]); h->near_hi.push_back(hi[i]); }
+    *npairs = (int64_t)h->near_lo.size();
+    return AB_OK;
+}
+
+int ab_pairs_nearest_fill(ab_handle* h, int64_t* lo, int64_t* hi, int64_t npairs) {
+    if (npairs != (int64_t)h->near_lo.size()) return ab_fail(h, AB_ERR_INVALID, "npairs does not match the last ab_pairs_nearest");
+    if (npairs && (!lo || !hi)) return ab_fail(h, AB_ERR_INVALID, "null output");
+    for (int64_t i = 0; i < npairs; ++i) { lo[i] = h->near_lo[(size_t)i]; hi[i] = h->near_hi[(size_t)i]; }
     return AB_OK;
 }
 

@@ -295,10 +295,22 @@ class StandardABM:
             _, ids = self.nearby_ids_batch(positions=[x], r=r, search=search)
         return ids
 
-    def interacting_pairs(self, r, method="all", search="exact"):
-        """interacting_pairs(model, r, :all; search) → (P, 2) array of id pairs (continuous.jl:418-452)."""
+    def interacting_pairs(self, r, method="all", search="exact", scheduler=None):
+        """interacting_pairs(model, r, method; search, scheduler) → (P, 2) array of id pairs
+        (continuous.jl:418-436).  `:all` (all_pairs!, :438-452) and `:nearest` (true_pairs!, :454-497;
+        `scheduler` = the id order, default ByID) run on the device; `:types` is not built."""
+        if method == "nearest":
+            order = None if scheduler is None else np.ascontiguousarray(scheduler, dtype=np.int64)
+            npairs = C.c_int64(0)
+            self._ck(self.lib.ab_pairs_nearest(self.h, float(r), self._ptr(order) if order is not None else None,
+                                               0 if order is None else len(order), C.byref(npairs)))
+            P = npairs.value
+            lo = np.zeros(max(P, 1), dtype=np.int64)
+            hi = np.zeros(max(P, 1), dtype=np.int64)
+            self._ck(self.lib.ab_pairs_nearest_fill(self.h, self._ptr(lo), self._ptr(hi), P))
+            return np.stack([lo[:P], hi[:P]], axis=1)
         if method != "all":
-            raise NotImplementedError("only method = :all runs on the device")
+            raise NotImplementedError("method = :types is not built (agent unions are out of scope)")
         npairs = C.c_int64(0)
         self._ck(self.lib.ab_pairs_count(self.h, float(r), L.SEARCH[search], C.byref(npairs)))
         P = npairs.value
@@ -306,6 +318,17 @@ class StandardABM:
         hi = np.zeros(max(P, 1), dtype=np.int64)
         self._ck(self.lib.ab_pairs_fill(self.h, self._ptr(lo), self._ptr(hi), P))
         return np.stack([lo[:P], hi[:P]], axis=1)
+
+    def elastic_collisions(self, pairs, mass=None):
+        """elastic_collision!(a, b, f) for every pair of `pairs` in order (continuous.jl:333-366);
+        `mass` = name of the mass column (the `f` symbol) or None.  Returns the per-pair `happened` flags."""
+        pairs = np.ascontiguousarray(pairs, dtype=np.int64).reshape(-1, 2)
+        a, b = np.ascontiguousarray(pairs[:, 0]), np.ascontiguousarray(pairs[:, 1])
+        hap = np.zeros(max(len(a), 1), dtype=np.uint8)
+        nc = C.c_int64(0)
+        self._ck(self.lib.ab_elastic_collisions(self.h, self._ptr(a), self._ptr(b), len(a),
+                                                -1 if mass is None else self._columns[mass], self._ptr(hap), C.byref(nc)))
+        return hap[: len(a)].astype(bool)
 
     def nearest_neighbor(self, r):
         """nearest_neighbor(agent, model, r) for every agent: id or 0 for `nothing` (continuous.jl:298-307)."""

@@ -161,6 +161,22 @@ int ab_pairs_fill(ab_handle* h, int64_t* lo, int64_t* hi, int64_t npairs);
  * out[i] = id of the nearest agent within r, or 0 (`nothing`). */
 int ab_nearest_neighbor(ab_handle* h, double r, int64_t* out, int64_t n);
 
+/* interacting_pairs(model, r, :nearest; scheduler) continuous.jl:418-436 -> true_pairs! :454-497:
+ * every scheduled agent proposes (itself, its nearest neighbour within r); an id keeps only its
+ * closest pair.  `order` = the scheduler's id sequence (NULL: ByID, 1..n) — the result depends on
+ * it exactly as in the reference (docstring, continuous.jl:400-405).  Count, then fill (list order =
+ * the reference's `pairs` vector). */
+int ab_pairs_nearest(ab_handle* h, double r, const int64_t* order, int64_t norder, int64_t* npairs);
+int ab_pairs_nearest_fill(ab_handle* h, int64_t* lo, int64_t* hi, int64_t npairs);
+
+/* elastic_collision!(a, b, f) continuous.jl:333-366 applied to the pairs (a[k], b[k]) in list order
+ * (2-D only, like the reference).  mass_field = a scalar f64/f32 column id (the `f` symbol, may hold
+ * Inf: immovable agents) or -1 for equal masses.  happened[k] (optional) = the call's return value,
+ * *ncollided = how many returned true.  An agent with infinite mass and nonzero velocity fails with
+ * AB_ERR_INVALID (the reference's @assert, :350 / :355). */
+int ab_elastic_collisions(ab_handle* h, const int64_t* a, const int64_t* b, int64_t npairs, int mass_field,
+                          uint8_t* happened, int64_t* ncollided);
+
 /* ---- movement ---------------------------------------------------------------
  * move_agent!(agent, model, dt) continuous.jl:186-194 → walk! walk.jl:58-66 →
  * normalize_position walk.jl:77-91, for `active_ids` (NULL = all agents). */

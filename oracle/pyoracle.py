@@ -194,6 +194,44 @@ class ContinuousOracle:
         j = int(lib().orc_cs_nearest_neighbor(self.h, C.c_int64(id), C.c_double(r)))
         return j or None
 
+    def interacting_pairs_nearest(self, r, order=None):
+        """true_pairs! (src/spaces/continuous.jl:454-497) restated literally: lists and linear scans, the
+        scheduler's id order (default ByID).  Small populations only (quadratic like the reference)."""
+        pos = self.state()[0]
+        pairs, distances = [], []
+        ids = range(1, int(self.n) + 1) if order is None else [int(i) for i in order]
+        for a in ids:
+            nn = self.nearest_neighbor(a, r)
+            if nn is None:
+                continue
+            new_pair = (a, nn) if a < nn else (nn, a)
+            if new_pair not in pairs:
+                dist = self.euclidean_distance(pos[a - 1], pos[nn - 1])
+                firsts = [p[0] for p in pairs]
+                idx = firsts.index(new_pair[0]) if new_pair[0] in firsts else None
+                if idx is None:
+                    pairs.append(new_pair)
+                    distances.append(dist)
+                elif distances[idx] > dist:
+                    pairs[idx] = new_pair
+                    distances[idx] = dist
+        to_remove = []
+        flat = [i for p in pairs for i in p]
+        for doubles in sorted({i for i in flat if flat.count(i) > 1}):
+            firsts = [p[0] for p in pairs]
+            lasts = [p[1] for p in pairs]
+            if doubles in firsts:
+                fidx, lidx = firsts.index(doubles), lasts.index(doubles)
+                to_remove.append(lidx if distances[fidx] <= distances[lidx] else fidx)
+            else:
+                idxs = [i for i, v in enumerate(lasts) if v == doubles]
+                keep = min(range(len(idxs)), key=lambda q: (distances[idxs[q]], q))
+                del idxs[keep]
+                to_remove.extend(idxs)
+        dead = set(to_remove)
+        return [p for i, p in enumerate(pairs) if i not in dead]
+
+
     def move_agent_dt(self, id, dt):
         if lib().orc_cs_move_agent_dt(self.h, C.c_int64(id), C.c_double(dt)):
             raise OracleError(self._err())
@@ -250,6 +288,42 @@ class ContinuousOracle:
         rc = lib().orc_pairforce_step(self.h, _p(r), _p(kk), _p(m), C.c_double(dt), C.c_double(cutoff), C.c_int64(nsteps))
         if rc:
             raise OracleError(self._err())
+
+
+
+def elastic_collision(x1, v1, x2, v2, m1=1.0, m2=1.0):
+    """elastic_collision!(a, b, f) (src/spaces/continuous.jl:333-366) on plain floats, same operation order.
+    Returns (happened, v1_new, v2_new)."""
+    import math
+
+    r1 = (x1[0] - x2[0], x1[1] - x2[1])
+    n = math.sqrt(r1[0] * r1[0] + r1[1] * r1[1]) ** 2
+    if n == 0:
+        return False, tuple(v1), tuple(v2)
+    dv = (v1[0] - v2[0], v1[1] - v2[1])
+    r2 = (x2[0] - x1[0], x2[1] - x1[1])
+    dot = lambda a, b: a[0] * b[0] + a[1] * b[1]
+    if m1 == math.inf and m2 == math.inf:
+        return False, tuple(v1), tuple(v2)
+    if m1 == math.inf:
+        assert tuple(v1) == (0.0, 0.0), "An agent with ∞ mass cannot have nonzero velocity"
+        if dot(r1, v2) <= 0:
+            return False, tuple(v1), tuple(v2)
+        v1 = (0.0, 0.0)
+        f1, f2 = 0.0, 2.0
+    elif m2 == math.inf:
+        assert tuple(v2) == (0.0, 0.0), "An agent with ∞ mass cannot have nonzero velocity"
+        if dot(r2, v1) <= 0:
+            return False, tuple(v1), tuple(v2)
+        v2 = (0.0, 0.0)
+        f1, f2 = 2.0, 0.0
+    else:
+        if dot(dv, r2) <= 0:
+            return False, tuple(v1), tuple(v2)
+        f1 = 2 * m2 / (m1 + m2)
+        f2 = 2 * m1 / (m1 + m2)
+    q1, q2 = dot(dv, r1) / n, dot(dv, r2) / n
+    return (True, tuple(v1[d] - f1 * q1 * r1[d] for d in range(2)), tuple(v2[d] + f2 * q2 * r2[d] for d in range(2)))
 
 
 class GridOracle:

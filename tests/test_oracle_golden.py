@@ -154,6 +154,32 @@ def test_nearest_neighbor():
     assert m.nearest_neighbor(2, 1e-100) is None
 
 
+def test_interacting_pairs_nearest_and_collision():
+    # continuous_space_tests.jl:244-265: 4 agents, r = 2.0, :nearest -> exactly one pair
+    from oracle.pyoracle import elastic_collision
+
+    pos = [(7.074386436066224, 4.963014649338054), (5.831962448496828, 4.926297135685473),
+           (5.122087781793935, 5.300031210394806), (3.9715633336430156, 4.8106570045816675)]
+    m = ContinuousOracle((10, 10), spacing=0.1, periodic=False)
+    m.add_agents(pos, np.zeros((4, 2)))
+    assert m.interacting_pairs_nearest(2.0) == [(2, 3)]
+    # elastic_collision! (continuous.jl:333-366): head-on equal masses swap velocities; disks moving apart do
+    # not collide; an immovable disk reflects; coincident disks do nothing; two immovable disks do nothing
+    assert elastic_collision((0, 0), (1, 0), (1, 0), (-1, 0)) == (True, (-1.0, 0.0), (1.0, 0.0))
+    assert elastic_collision((0, 0), (-1, 0), (1, 0), (1, 0))[0] is False
+    h, v1, v2 = elastic_collision((0, 0), (0, 0), (1, 0), (-1, 0.5), math.inf, 1.33)
+    assert h and v1 == (0.0, 0.0) and v2 == (1.0, 0.5)
+    assert elastic_collision((2, 2), (1, 0), (2, 2), (-1, 0))[0] is False
+    assert elastic_collision((0, 0), (0, 0), (1, 0), (0, 0), math.inf, math.inf)[0] is False
+    # kinetic energy and momentum of a movable pair are conserved
+    h, v1, v2 = elastic_collision((0.1, 0.2), (0.3, -0.1), (0.4, 0.35), (-0.2, 0.05), 2.0, 0.7)
+    assert h
+    k0 = 2.0 * (0.3 ** 2 + 0.1 ** 2) + 0.7 * (0.2 ** 2 + 0.05 ** 2)
+    k1 = 2.0 * (v1[0] ** 2 + v1[1] ** 2) + 0.7 * (v2[0] ** 2 + v2[1] ** 2)
+    assert abs(k0 - k1) < 1e-15
+    assert abs(2.0 * v1[0] + 0.7 * v2[0] - (2.0 * 0.3 - 0.7 * 0.2)) < 1e-15
+
+
 def test_walk_continuous():
     # continuous_space_tests.jl:351-378
     m = ContinuousOracle((12, 10), periodic=False)
