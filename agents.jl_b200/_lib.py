@@ -91,6 +91,9 @@ _SIGS = {
     "ab_comm_link_local": (C.c_int, [C.POINTER(_H), C.c_int]),
     "ab_step_flock_group": (C.c_int, [C.POINTER(_H), C.c_int, C.POINTER(FlockParams), C.c_int64]),
     "ab_comm_set_capacity": (C.c_int, [_H, C.c_int64]),
+    "ab_comm_ipc_export": (C.c_int, [_H, C.c_void_p]),
+    "ab_comm_ipc_import": (C.c_int, [_H, C.c_void_p, C.c_void_p]),
+    "ab_comm_direct": (C.c_int, [_H]),
     "ab_comm_slab": (C.c_int, [_H, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "ab_comm_halo": (C.c_int, [_H]),
     "ab_nlocal": (C.c_int64, [_H]),

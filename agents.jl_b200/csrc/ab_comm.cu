@@ -91,7 +91,21 @@ struct ab_comm {
     cudaEvent_t ev_packed = nullptr, ev_consumed = nullptr;
     uint32_t* h_counts = nullptr;    // pinned {n_own, n_window}
     int64_t exchanges = 0;
+    // direct exchange over peer memory (ab_comm_ipc_export / _import): every rank owns ONE block of
+    // [2 parities][2 sides] message slots + 4 flags; the neighbours' blocks are mapped through CUDA IPC and
+    // k_halo_pack stores straight into them over NVLink (only the agents present travel, no NCCL call on
+    // the data path); a flag per slot carries the exchange number.
+    char* ipc_block = nullptr;
+    size_t ipc_stride = 0;           // bytes per message slot (layout at the finest refinement)
+    int64_t ipc_cap = 0;             // capacity the block was sized for
+    char *ipc_lower = nullptr, *ipc_upper = nullptr;     // the neighbours' blocks
+    bool ipc_on = false;
+    int cur_par = 0;                 // parity of the exchange in flight (pack -> transfer -> unpack)
 };
+static inline char* ipc_slot(char* block, size_t stride, int par, int side) { return block + (size_t)(par * 2 + side) * stride; }
+static inline uint32_t* ipc_flag(char* block, size_t stride, int par, int side) {
+    return reinterpret_cast<uint32_t*>(block + 4 * stride) + (size_t)(par * 2 + side) * 32;      // 128 B apart
+}
 
 #define AB_NCCL(h, call)                                                                                   \
     do {                                                                                                   \
@@ -137,7 +151,8 @@ template <class E, int D>
 __global__ void __launch_bounds__(256)
 k_halo_pack(MsgLayout m, uint32_t kown, const uint32_t* __restrict__ cs, const E* __restrict__ pos,
             const E* __restrict__ vel, const int32_t* __restrict__ id, const uint32_t* __restrict__ key, int64_t cap,
-            char* __restrict__ buf0, char* __restrict__ buf1, int* __restrict__ err) {
+            char* __restrict__ buf0, char* __restrict__ buf1, int* __restrict__ err,
+            uint32_t* done_ctr, uint32_t* flag0, uint32_t* flag1, uint32_t epoch) {
     const int dir = blockIdx.y;
     char* buf = dir == 0 ? buf0 : buf1;
     const uint32_t k0 = dir == 0 ? 0u : kown - m.ncs;
@@ -168,6 +183,35 @@ k_halo_pack(MsgLayout m, uint32_t kown, const uint32_t* __restrict__ cs, const E
         mid[t] = id[s];
         mkey[t] = key[s];
     }
+    if (flag0) {
+        // direct exchange: the LAST CTA to finish publishes the exchange number in the neighbours' flags
+        // (every thread fences its peer-memory stores at system scope before its CTA is counted)
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const uint32_t total = gridDim.x * gridDim.y;
+            if (atomicAdd(done_ctr, 1u) == total - 1) {
+                __threadfence_system();
+                *done_ctr = 0;
+                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag0), "r"(epoch) : "memory");
+                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag1), "r"(epoch) : "memory");
+            }
+        }
+    }
+}
+
+// Spins until *f == epoch (a neighbour's k_halo_pack has delivered); gives up after ~10 s (dead peer).
+__device__ __forceinline__ bool wait_flag(const uint32_t* f, uint32_t epoch) {
+    unsigned long long t0, t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (;;) {
+        uint32_t v;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+        if (v == epoch) return true;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        if (t - t0 > 10000000000ull) return false;
+        __nanosleep(100);
+    }
 }
 
 // Installs the received layers as this rank's halo: blockIdx.y = 0 the upper neighbour's bottom layers
@@ -177,7 +221,19 @@ template <class E, int D>
 __global__ void __launch_bounds__(256)
 k_halo_unpack(MsgLayout m, uint32_t kown, uint32_t* __restrict__ cs, E* __restrict__ pos, E* __restrict__ vel,
               int32_t* __restrict__ id, uint32_t* __restrict__ key, int64_t cap, const char* __restrict__ buf0,
-              const char* __restrict__ buf1, int* __restrict__ err) {
+              const char* __restrict__ buf1, int* __restrict__ err, const uint32_t* wflag0, const uint32_t* wflag1,
+              uint32_t epoch) {
+    if (wflag0) {
+        // direct exchange: both messages were stored into our memory by the neighbours' pack kernels; they
+        // never wait for us in return (their pack depends only on their own steps; slots alternate by parity)
+        __shared__ int s_ok;
+        if (threadIdx.x == 0) s_ok = wait_flag(wflag0, epoch) && wait_flag(wflag1, epoch);
+        __syncthreads();
+        if (!s_ok) {
+            if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) atomicOr(err, AB_EF_COMM);
+            return;
+        }
+    }
     const int src = blockIdx.y;
     const uint32_t* h0 = reinterpret_cast<const uint32_t*>(buf0);
     const uint32_t* h1 = reinterpret_cast<const uint32_t*>(buf1);
@@ -224,6 +280,9 @@ void ab_comm_free(ab_handle* h) {
         if (c->sendbuf[i]) cudaFree(c->sendbuf[i]);
         if (c->recvbuf[i]) cudaFree(c->recvbuf[i]);
     }
+    if (c->ipc_lower) cudaIpcCloseMemHandle(c->ipc_lower);
+    if (c->ipc_upper && c->ipc_upper != c->ipc_lower) cudaIpcCloseMemHandle(c->ipc_upper);
+    if (c->ipc_block) cudaFree(c->ipc_block);
     if (c->h_counts) cudaFreeHost(c->h_counts);
     if (c->ev_packed) cudaEventDestroy(c->ev_packed);
     if (c->ev_consumed) cudaEventDestroy(c->ev_consumed);
@@ -242,6 +301,13 @@ static int ensure_buffers(ab_handle* h) {
         return ab_fail(h, AB_ERR_STATE, "ab_comm_set_capacity must be called before stepping a sharded handle");
     }
     C = (C + 63) / 64 * 64;
+    if (c->ipc_on) {
+        if (C != c->ipc_cap) return ab_fail(h, AB_ERR_STATE, "message capacity changed after ab_comm_ipc_export");
+        const MsgLayout mi = msg_layout(h->D, h->tsize, C, ncs);
+        if (mi.bytes > c->ipc_stride) return ab_fail(h, AB_ERR_STATE, "message does not fit the exported block");
+        c->cap_agents = C; c->msg_bytes = mi.bytes; c->msg_K = h->K;
+        return AB_OK;
+    }
     if (c->cap_agents == C && c->msg_K == h->K && c->sendbuf[0]) return AB_OK;
     AB_CUDA(h, cudaStreamSynchronize(h->stream));
     const MsgLayout m = msg_layout(h->D, h->tsize, C, ncs);
@@ -269,11 +335,20 @@ static int pack_t(ab_handle* h) {
     // in-process peers: they must have consumed the previous message before it is overwritten
     if (c->peer_lower) AB_CUDA(h, cudaStreamWaitEvent(h->stream, c->peer_lower->comm->ev_consumed, 0));
     if (c->peer_upper) AB_CUDA(h, cudaStreamWaitEvent(h->stream, c->peer_upper->comm->ev_consumed, 0));
+    // my bottom layers are the lower neighbour's "from upper" message (side 0), my top layers the upper
+    // neighbour's "from lower" one (side 1)
+    c->cur_par = (int)(c->exchanges & 1);
+    char* dst0 = c->ipc_on ? ipc_slot(c->ipc_lower, c->ipc_stride, c->cur_par, 0) : (char*)c->sendbuf[0];
+    char* dst1 = c->ipc_on ? ipc_slot(c->ipc_upper, c->ipc_stride, c->cur_par, 1) : (char*)c->sendbuf[1];
     {
         AB_LAUNCH(h, "k_halo_pack");
         k_halo_pack<E, D><<<dim3(nb, 2), 256, 0, h->stream>>>(m, kown, h->cell_start, (const E*)h->fields[0].buf[cur],
                                                              (const E*)h->fields[1].buf[cur], h->id[cur], h->key[cur], h->cap,
-                                                             (char*)c->sendbuf[0], (char*)c->sendbuf[1], h->d_err);
+                                                             dst0, dst1, h->d_err,
+                                                             c->ipc_on ? ipc_flag(c->ipc_block, c->ipc_stride, 2, 0) : nullptr,
+                                                             c->ipc_on ? ipc_flag(c->ipc_lower, c->ipc_stride, c->cur_par, 0) : nullptr,
+                                                             c->ipc_on ? ipc_flag(c->ipc_upper, c->ipc_stride, c->cur_par, 1) : nullptr,
+                                                             (uint32_t)(c->exchanges + 1));
     }
     if (c->peer_lower) AB_CUDA(h, cudaEventRecord(c->ev_packed, h->stream));
     return AB_OK;
@@ -294,6 +369,8 @@ static int transfer(ab_handle* h) {
         if (lo->device == h->device) AB_CUDA(h, cudaMemcpyAsync(c->recvbuf[1], lo->comm->sendbuf[1], bytes, cudaMemcpyDeviceToDevice, h->stream));
         else AB_CUDA(h, cudaMemcpyPeerAsync(c->recvbuf[1], h->device, lo->comm->sendbuf[1], lo->device, bytes, h->stream));
         AB_CUDA(h, cudaEventRecord(c->ev_consumed, h->stream));
+    } else if (c->ipc_on) {
+        // nothing to move: the neighbours' pack kernels store into our block; k_halo_unpack waits for their flags
     } else {
         if (!c->comm) return ab_fail(h, AB_ERR_STATE, "sharded handle without a communicator or in-process peers");
         // one group: bottom layers -> lower neighbour, top layers -> upper neighbour; receives in the matching
@@ -321,7 +398,11 @@ static int unpack_t(ab_handle* h, bool want_agg) {
         AB_LAUNCH(h, "k_halo_unpack");
         k_halo_unpack<E, D><<<dim3(nb, 2), 256, 0, h->stream>>>(m, kown, h->cell_start, (E*)h->fields[0].buf[cur],
                                                                (E*)h->fields[1].buf[cur], h->id[cur], h->key[cur], h->cap,
-                                                               (const char*)c->recvbuf[0], (const char*)c->recvbuf[1], h->d_err);
+                                                               c->ipc_on ? ipc_slot(c->ipc_block, c->ipc_stride, c->cur_par, 0) : (const char*)c->recvbuf[0],
+                                                               c->ipc_on ? ipc_slot(c->ipc_block, c->ipc_stride, c->cur_par, 1) : (const char*)c->recvbuf[1], h->d_err,
+                                                               c->ipc_on ? ipc_flag(c->ipc_block, c->ipc_stride, c->cur_par, 0) : nullptr,
+                                                               c->ipc_on ? ipc_flag(c->ipc_block, c->ipc_stride, c->cur_par, 1) : nullptr,
+                                                               (uint32_t)c->exchanges);
     }
     if (want_agg) {
         const int64_t cpl = cells_per_layer(h);
@@ -461,6 +542,54 @@ int ab_comm_link_local(ab_handle** hs, int n) {
     }
     return AB_OK;
 }
+
+// Direct exchange over peer memory.  Export: allocates this rank's receive block for the capacity set by
+// ab_comm_set_capacity and returns its 64-byte CUDA IPC handle; the host exchanges the handles (any
+// transport) and imports the two neighbours'.  From then on the boundary messages are stored by
+// k_halo_pack straight into the neighbour's memory (NVLink) and NCCL is not used on the data path.
+int ab_comm_ipc_export(ab_handle* h, void* out64) {
+    if (!h || !h->comm || !h->win_W) return ab_fail(h, AB_ERR_STATE, "handle is not sharded");
+    if (!out64) return ab_fail(h, AB_ERR_INVALID, "null output");
+    ab_comm* c = h->comm;
+    if (c->peer_lower) return ab_fail(h, AB_ERR_STATE, "in-process slabs exchange by device copies");
+    if (c->want_cap <= 0) return ab_fail(h, AB_ERR_STATE, "ab_comm_set_capacity first");
+    if (c->ipc_block) return ab_fail(h, AB_ERR_STATE, "already exported");
+    AB_CUDA(h, cudaSetDevice(h->device));
+    const int64_t C = (c->want_cap + 63) / 64 * 64;
+    const int ksh_max = ((h->ncells << h->D) <= h->nfine_cap) ? h->D : 0;            // finest refinement a step may choose
+    const uint32_t ncs_max = (uint32_t)(AB_HALO_W * ((h->ncells << ksh_max) / h->dims[h->D - 1]));
+    c->ipc_stride = (msg_layout(h->D, h->tsize, C, ncs_max).bytes + 255) / 256 * 256;
+    c->ipc_cap = C;
+    AB_CUDA(h, cudaMalloc((void**)&c->ipc_block, 4 * c->ipc_stride + 4096));
+    AB_CUDA(h, cudaMemset(c->ipc_block, 0, 4 * c->ipc_stride + 4096));
+    cudaIpcMemHandle_t mh;
+    AB_CUDA(h, cudaIpcGetMemHandle(&mh, c->ipc_block));
+    static_assert(sizeof(mh) == 64, "CUDA IPC handle size");
+    memcpy(out64, &mh, 64);
+    return AB_OK;
+}
+int ab_comm_ipc_import(ab_handle* h, const void* lower64, const void* upper64) {
+    if (!h || !h->comm || !h->win_W) return ab_fail(h, AB_ERR_STATE, "handle is not sharded");
+    ab_comm* c = h->comm;
+    if (!c->ipc_block) return ab_fail(h, AB_ERR_STATE, "ab_comm_ipc_export first");
+    if (!lower64 || !upper64) return ab_fail(h, AB_ERR_INVALID, "null handle");
+    if (c->ipc_on) return ab_fail(h, AB_ERR_STATE, "already imported");
+    AB_CUDA(h, cudaSetDevice(h->device));
+    cudaIpcMemHandle_t ml, mu;
+    memcpy(&ml, lower64, 64);
+    memcpy(&mu, upper64, 64);
+    void* p = nullptr;
+    AB_CUDA(h, cudaIpcOpenMemHandle(&p, ml, cudaIpcMemLazyEnablePeerAccess));
+    c->ipc_lower = (char*)p;
+    if (c->lower == c->upper) c->ipc_upper = c->ipc_lower;          // two ranks: one neighbour, one mapping
+    else {
+        AB_CUDA(h, cudaIpcOpenMemHandle(&p, mu, cudaIpcMemLazyEnablePeerAccess));
+        c->ipc_upper = (char*)p;
+    }
+    c->ipc_on = true;
+    return AB_OK;
+}
+int ab_comm_direct(const ab_handle* h) { return h && h->comm && h->comm->ipc_on ? 1 : 0; }
 
 int ab_comm_set_capacity(ab_handle* h, int64_t halo_agents) {
     if (!h || !h->comm) return ab_fail(h, AB_ERR_STATE, "handle is not sharded");

@@ -65,6 +65,7 @@ class Slabs:
         from . import _lib as L
 
         self.model, self.dist, self.L = model, dist, L
+        self.init_nccl = init_nccl
         self.rank = int(dist.get_rank() if rank is None else rank)
         self.world = int(dist.get_world_size() if world is None else world)
         lib = model.lib
@@ -85,6 +86,30 @@ class Slabs:
         assert lib.ab_comm_halo(model.h) == HALO_W
         self.n_global = 0
 
+    def _link_direct(self):
+        """Direct halo exchange over peer memory (ab_comm_ipc_*): every rank exports the CUDA IPC handle of
+        its receive block, the handles go round through torch.distributed, every rank maps its two
+        neighbours' blocks.  AB_HALO=nccl keeps the ncclSend/ncclRecv exchange (the baseline)."""
+        import os
+
+        m, lib = self.model, self.model.lib
+        if self.dist is None or not self.init_nccl or os.environ.get("AB_HALO", "direct") == "nccl":
+            return False
+        mine = (C.c_ubyte * 64)()
+        rc = lib.ab_comm_ipc_export(m.h, mine)
+        handles = [None] * self.world
+        self.dist.all_gather_object(handles, bytes(mine) if rc == 0 else None)
+        if any(h is None for h in handles):
+            return False                                    # some rank could not export: everyone stays on NCCL
+        lo = (C.c_ubyte * 64).from_buffer_copy(handles[(self.rank - 1) % self.world])
+        up = (C.c_ubyte * 64).from_buffer_copy(handles[(self.rank + 1) % self.world])
+        rc = lib.ab_comm_ipc_import(m.h, lo, up)
+        oks = [None] * self.world
+        self.dist.all_gather_object(oks, rc == 0)
+        if not all(oks):
+            raise RuntimeError("direct halo exchange: a rank failed to map its neighbours (set AB_HALO=nccl)")
+        return True
+
     # -- population -----------------------------------------------------------------------------
     def scatter(self, pos, vel, halo_capacity=None, capacity_factor=1.6):
         """Every rank passes the same global, id-ordered (1..N) state and keeps its window of it."""
@@ -97,6 +122,7 @@ class Slabs:
         idx, owned = select_window(layer, self.first, self.count, self.n_layers)
         cap = halo_capacity or default_halo_capacity(self.n_global, self.n_layers)
         m._ck(lib.ab_comm_set_capacity(m.h, int(cap)))
+        self.direct = self._link_direct()
         m._ck(lib.ab_resize(m.h, int(len(idx) * capacity_factor) + 2 * int(cap) + 1024))
         gids = (idx + 1).astype(np.int64)
         p = np.ascontiguousarray(pos[idx])
@@ -128,6 +154,7 @@ class Slabs:
         v = np.ascontiguousarray(np.concatenate(keep_v))
         cap = halo_capacity or default_halo_capacity(self.n_global, self.n_layers)
         m._ck(lib.ab_comm_set_capacity(m.h, int(cap)))
+        self.direct = self._link_direct()
         m._ck(lib.ab_resize(m.h, int(len(gids) * capacity_factor) + 2 * int(cap) + 1024))
         m._ck(lib.ab_upload_local(m.h, 0, m._ptr(p), m._ptr(gids), len(gids)))
         m._ck(lib.ab_upload_local(m.h, 1, m._ptr(v), m._ptr(gids), len(gids)))

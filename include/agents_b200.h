@@ -237,6 +237,15 @@ int ab_comm_link_local(ab_handle** handles, int n);
 int ab_step_flock_group(ab_handle** handles, int n, const ab_flock_params* p, int64_t nsteps);
 /* capacity (agents) of one boundary message; every rank must pass the same value */
 int ab_comm_set_capacity(ab_handle* h, int64_t halo_agents);
+/* Direct halo exchange over peer memory (NVLink), replacing the ncclSend/ncclRecv group of the step:
+ * after ab_comm_set_capacity every rank exports the 64-byte CUDA IPC handle of its receive block, the
+ * host passes the handles around (torch.distributed / MPI / any transport) and every rank imports its
+ * lower and upper neighbour's.  From then on the pack kernel of a step stores the boundary layers
+ * straight into the neighbours' memory — only the agents present travel — and a flag per message
+ * carries the exchange number; NCCL stays the fallback for handles that did not import. */
+int ab_comm_ipc_export(ab_handle* h, void* out64);
+int ab_comm_ipc_import(ab_handle* h, const void* lower64, const void* upper64);
+int ab_comm_direct(const ab_handle* h);                    /* 1 when the direct exchange is active */
 /* owned layers of this rank: global index of the first one (0-based) and how many */
 int ab_comm_slab(const ab_handle* h, int64_t* first_layer, int64_t* n_layers);
 int ab_comm_halo(const ab_handle* h);                      /* halo layers per side */

@@ -77,6 +77,7 @@ def main():
             "pos_bitwise_equal": bool(np.array_equal(gp, rp)), "vel_bitwise_equal": bool(np.array_equal(gv, rv)),
             "max_abs_pos_diff": float(np.max(np.abs(gp - rp))), "owned_rank0": owned_hist,
             "migrated": bool(len(set(owned_hist)) > 1), "launches": m.launch_count(),
+            "direct": bool(slabs.direct),
         }
         ref.close()
         print("MGPU_RESULT " + json.dumps(result), flush=True)

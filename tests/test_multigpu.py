@@ -19,10 +19,11 @@ def _ngpu():
         return 0
 
 
-def _run(world, port, *wargs):
+def _run(world, port, *wargs, halo="direct"):
+    env = dict(os.environ, AB_HALO=halo)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "mgpu_worker.py"), *wargs]
-    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT, env=env)
     lines = [l for l in out.stdout.splitlines() if l.startswith("MGPU_RESULT ")]
     assert out.returncode == 0 and lines, out.stdout[-2000:] + out.stderr[-4000:]
     return json.loads(lines[-1][len("MGPU_RESULT "):])
@@ -45,6 +46,16 @@ def test_two_gpus_bitwise_equal_to_one(name, wargs):
     r = _run(2, 29531, *wargs)
     assert r["conserved"] and r["pos_bitwise_equal"] and r["vel_bitwise_equal"], r
     assert r["migrated"], "the test state should make agents cross the slab boundary"
+    assert r["direct"], "the boundary layers should travel by direct peer-memory stores"
+
+
+@pytest.mark.gpu
+def test_two_gpus_nccl_exchange():
+    """The ncclSend/ncclRecv exchange (AB_HALO=nccl) stays available and gives the same bits."""
+    if _ngpu() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    r = _run(2, 29535, "--agents", "60000", "--extent", "400", "400", "--steps", "12", halo="nccl")
+    assert r["conserved"] and r["pos_bitwise_equal"] and r["vel_bitwise_equal"] and not r["direct"], r
 
 
 @pytest.mark.gpu
