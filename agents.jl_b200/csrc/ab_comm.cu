@@ -18,12 +18,15 @@
 //             the halo layer's birds that fly into the slab are this step's immigrants,
 //             computed locally from the halo instead of being received
 //   scan + re-sort of the owned rows (emigrants fall out: no owned tile collects them)
-//   exchange  (this file) the W top and W bottom owned layers of the NEW sorted state go
-//             to the neighbours in one NCCL group of two sends + two receives and replace
-//             their halo layers wholesale — halo refresh and migration in a single message.
-// Messages have a fixed capacity (header with the live count; no size round trip through
-// the host, the whole step stays asynchronous on the stream).  Because agents keep their
-// global ids and cells are id-ordered, an N-GPU run is bitwise identical to the 1-GPU run.
+//   exchange  (this file) the W top and W bottom owned layers of the NEW sorted state replace the
+//             neighbours' halo layers wholesale — halo refresh and migration in a single message.
+//             Default (ab_comm_ipc_export / _import): k_halo_pack stores them straight into the
+//             neighbours' memory over NVLink (CUDA IPC mapping) and publishes a flag; k_halo_unpack
+//             waits for the two flags.  Baseline: one NCCL group of two sends + two receives of the
+//             fixed-capacity messages.
+// There is no size round trip through the host; the whole step stays asynchronous on the stream.
+// Because agents keep their global ids and the in-cell order is canonical, an N-GPU run is bitwise
+// identical to the 1-GPU run.
 #include <dlfcn.h>
 
 #include <algorithm>
@@ -331,7 +334,8 @@ static int pack_t(ab_handle* h) {
     const uint32_t ncs = (uint32_t)(AB_HALO_W * keys_per_layer(h));
     const uint32_t kown = (uint32_t)(h->win_nl * keys_per_layer(h));
     const MsgLayout m = msg_layout(D, sizeof(E), c->cap_agents, ncs);
-    const int nb = (int)std::min<int64_t>(std::max<int64_t>((std::max<int64_t>(c->cap_agents / 4, ncs) + 255) / 256, 1), 592);
+    // one item per thread (up to 592 CTAs per side): the stores are posted writes, the cost is latency
+    const int nb = (int)std::min<int64_t>(std::max<int64_t>((std::max<int64_t>(c->cap_agents, ncs) + 255) / 256, 1), 592);
     // in-process peers: they must have consumed the previous message before it is overwritten
     if (c->peer_lower) AB_CUDA(h, cudaStreamWaitEvent(h->stream, c->peer_lower->comm->ev_consumed, 0));
     if (c->peer_upper) AB_CUDA(h, cudaStreamWaitEvent(h->stream, c->peer_upper->comm->ev_consumed, 0));
