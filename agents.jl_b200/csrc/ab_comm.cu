@@ -560,7 +560,8 @@ int ab_comm_ipc_export(ab_handle* h, void* out64) {
     if (c->ipc_block) return ab_fail(h, AB_ERR_STATE, "already exported");
     AB_CUDA(h, cudaSetDevice(h->device));
     const int64_t C = (c->want_cap + 63) / 64 * 64;
-    const int ksh_max = ((h->ncells << h->D) <= h->nfine_cap) ? h->D : 0;            // finest refinement a step may choose
+    int ksh_max = ((h->ncells << h->D) <= h->nfine_cap) ? h->D : 0;                  // finest refinement a step may choose
+    if (h->D == 2 && (h->ncells << 4) <= h->nfine_cap) ksh_max = 4;
     const uint32_t ncs_max = (uint32_t)(AB_HALO_W * ((h->ncells << ksh_max) / h->dims[h->D - 1]));
     c->ipc_stride = (msg_layout(h->D, h->tsize, C, ncs_max).bytes + 255) / 256 * 256;
     c->ipc_cap = C;

@@ -404,13 +404,14 @@ int ab_ensure_index(ab_handle* h) {
 // Pure layout choice: every query walks reference cells, so results do not
 // depend on it; the fused sweeps use the sub-cells to cut candidate counts.
 int ab_set_refine(ab_handle* h, int K) {
-    if (K != 1 && K != 2) return ab_fail(h, AB_ERR_INVALID, "refinement must be 1 or 2");
+    if (K != 1 && K != 2 && !(K == 4 && h->D == 2)) return ab_fail(h, AB_ERR_INVALID, "refinement must be 1, 2 or (2-D only) 4");
     if (h->desc.kind != AB_SPACE_CONTINUOUS && K != 1) return ab_fail(h, AB_ERR_INVALID, "grid spaces are not refined");
-    const int ksh = K == 2 ? h->D : 0;
+    const int kb = K == 4 ? 2 : (K == 2 ? 1 : 0);
+    const int ksh = kb * h->D;
     if ((h->ncells << ksh) > h->nfine_cap) return ab_fail(h, AB_ERR_INVALID, "grid too large to refine");
     if (K == h->K) return AB_OK;
     h->K = K;
-    h->kb = K == 2 ? 1 : 0;
+    h->kb = kb;
     h->ksh = ksh;
     h->nfine = h->ncells << ksh;
     h->index_valid = false;
@@ -468,6 +469,7 @@ int ab_create(ab_space_desc* desc, int device, ab_handle** out) {
     if (desc->D < 2 || desc->D > 3) return ab_fail(nullptr, AB_ERR_INVALID, "D must be 2 or 3 on the device");
     ab_handle* h = new ab_handle();
     h->device = device;
+    if (const char* e = getenv("AB_FINE4")) h->fine4 = atoi(e) != 0;     // A/B experiments
     if (const char* e = getenv("AB_RS_TARGET")) { int v = atoi(e); if (v >= 4 && v <= 2048) h->rs_target = v; }   // tuning experiments
     h->D = desc->D;
     int64_t ncells = 1;
@@ -497,7 +499,9 @@ int ab_create(ab_space_desc* desc, int device, ab_handle** out) {
     h->ncells = ncells;
     h->nfine = ncells;
     // continuous spaces may refine every reference cell into 2^D sub-cells (ab_set_refine)
-    const int max_ksh = (desc->kind == AB_SPACE_CONTINUOUS && (ncells << desc->D) < 4000000000LL) ? desc->D : 0;
+    // finest refinement a fused step may choose: K = 4 in 2-D (while the fine grid stays below 2^26 keys), K = 2 otherwise
+    int max_ksh = (desc->kind == AB_SPACE_CONTINUOUS && (ncells << desc->D) < 4000000000LL) ? desc->D : 0;
+    if (max_ksh && desc->D == 2 && (ncells << 4) <= (1LL << 26)) max_ksh = 4;
     h->tsize = ab_dtype_size(h->dtype);
     h->desc = *desc;
 

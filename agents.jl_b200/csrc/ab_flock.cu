@@ -25,6 +25,7 @@ template <class T> struct FlockU {
     double visual_distance;
     T thr;      // exact_threshold<T>(visual_distance), computed once on the host for uniform parameters
     double gr_t1, gr_t2;   // (spacing - r)², (2 spacing - r)² (negative: never) — grid_radius_12
+    int reach;             // fine-cell reach of the separation sweep on the fine path (FinePlan::R)
 };
 
 // host twin of exact_threshold (ab_internal.cuh): IEEE sqrt on both sides, same result
@@ -318,6 +319,7 @@ static int flock_prepare(ab_handle* h, const ab_flock_params* p, FlockCtx<T, D>*
     if (p->kernel == 2 && !fine) return ab_fail(h, AB_ERR_INVALID, "fine-grid flock kernel not applicable to this configuration");
     if (h->win_W && !fine) return ab_fail(h, AB_ERR_INVALID, "a sharded handle runs the fine-grid flock step only (uniform parameters, visual_distance <= spacing, >= 6 cells per axis)");
     cx->fine = fine;
+    u.reach = fine ? plan.R : 1;
     if (fine) AB_TRY(ab_set_refine(h, plan.K));
     AB_TRY(ab_ensure_index(h));
     cx->sp = make_space<T, D>(h);

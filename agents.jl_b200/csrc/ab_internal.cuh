@@ -102,6 +102,7 @@ struct ab_handle {
     // sums of those aggregates over the reference's offset tables of radius 1 and 2 (k_cell_M)
     void* cell_M = nullptr;
     size_t cell_M_bytes = 0;
+    bool fine4 = false;                // quarter-cell refinement (K = 4) on the 2-D flock path: correct, measured slower (AB_FINE4=1 enables)
     int rs_target = 100;               // average agents per re-sort tile (tuning knob)
 
     // single-pass scan state
@@ -364,9 +365,16 @@ __device__ __forceinline__ uint32_t device_key(const SpaceDev<T, D>& sp, const T
     for (int d = 0; d < D; ++d) {
         const int cl = d == D - 1 ? global_to_local_last<T, D>(sp, c[d], &ok) : c[d];
         f[d] = (uint32_t)cl << sp.kb;
-        if (sp.K == 2) {
-            T centre = sp.spacing * ((T)(c[d] + 1) - T(0.5));
-            f[d] |= (p[d] > centre ? 1u : 0u);
+        if (sp.K >= 2) {
+            const T centre = sp.spacing * ((T)(c[d] + 1) - T(0.5));
+            const bool up = p[d] > centre;
+            if (sp.K == 2) f[d] |= up ? 1u : 0u;
+            else {
+                // K = 4: halves split at the centre, quarters at centre -+ spacing/4 (any monotone split works:
+                // the sweeps only need fine cells no narrower than ~spacing/4, with a 1e-9 margin in the plan)
+                const T quarter = up ? centre + sp.spacing * T(0.25) : centre - sp.spacing * T(0.25);
+                f[d] |= (up ? 2u : 0u) | (p[d] > quarter ? 1u : 0u);
+            }
         }
     }
     uint32_t lin = f[D - 1];
