@@ -79,6 +79,8 @@ _SIGS = {
     "ab_pairs_nearest": (C.c_int, [_H, C.c_double, C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]),
     "ab_pairs_nearest_fill": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_int64]),
     "ab_elastic_collisions": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.POINTER(C.c_int64)]),
+    "ab_spatial_lookup": (C.c_int, [_H, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "ab_update_vel_field": (C.c_int, [_H, C.c_void_p, C.c_int, C.c_void_p, C.c_double, C.c_void_p, C.c_int64]),
     "ab_move": (C.c_int, [_H, C.c_double, C.c_void_p, C.c_int64]),
     "ab_walk": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_int64, C.c_int]),
     "ab_step_flock": (C.c_int, [_H, C.POINTER(FlockParams), C.c_int64]),

@@ -337,6 +337,45 @@ class StandardABM:
         self._ck(self.lib.ab_nearest_neighbor(self.h, float(r), self._ptr(out), n))
         return out
 
+    # -- spatial fields ---------------------------------------------------------
+    def _field_args(self, prop):
+        prop = np.asarray(prop, dtype=np.float64)
+        return prop, np.ascontiguousarray(prop.shape, dtype=np.int64)
+
+    def get_spatial_index(self, shape, positions=None):
+        """get_spatial_index(pos, property, model) (continuous.jl:566-573) for all agents (id order) or for
+        `positions`: (n, len(shape)) 1-based indices into an array of `shape`."""
+        dims = np.ascontiguousarray(shape, dtype=np.int64)
+        q = None if positions is None else np.ascontiguousarray(positions, dtype=self.space.dtype).reshape(-1, self.D)
+        n = self.nagents() if q is None else len(q)
+        out = np.zeros((max(n, 1), len(dims)), dtype=np.int64)
+        self._ck(self.lib.ab_spatial_lookup(self.h, self._ptr(dims), len(dims), None, 0, self._ptr(q) if q is not None else None,
+                                            n, self._ptr(out), None))
+        return out[:n]
+
+    def get_spatial_property(self, prop, positions=None):
+        """get_spatial_property(pos, property::AbstractArray, model) (continuous.jl:545-548), batched."""
+        prop, dims = self._field_args(prop)
+        flat = np.ascontiguousarray(prop.ravel(order="F"))
+        q = None if positions is None else np.ascontiguousarray(positions, dtype=self.space.dtype).reshape(-1, self.D)
+        n = self.nagents() if q is None else len(q)
+        out = np.zeros(max(n, 1), dtype=np.float64)
+        self._ck(self.lib.ab_spatial_lookup(self.h, self._ptr(dims), len(dims), self._ptr(flat), 1,
+                                            self._ptr(q) if q is not None else None, n, None, self._ptr(out)))
+        return out[:n]
+
+    def update_vel_field(self, field, scale=1.0, ids=None):
+        """The force-field `update_vel!` hook (continuous.jl:86-91): vel += scale * field[index(pos)], where
+        `field` has shape property_shape + (D,)."""
+        field = np.asarray(field, dtype=np.float64)
+        dims = np.ascontiguousarray(field.shape[:-1], dtype=np.int64)
+        assert field.shape[-1] == self.D
+        flat = np.ascontiguousarray(np.concatenate([field[..., d].ravel(order="F") for d in range(self.D)]))
+        a = np.ascontiguousarray(ids, dtype=np.int64) if ids is not None else None
+        self._ck(self.lib.ab_update_vel_field(self.h, self._ptr(dims), len(dims), self._ptr(flat), float(scale),
+                                              self._ptr(a) if a is not None else None, 0 if a is None else len(a)))
+        return self
+
     # -- movement --------------------------------------------------------------
     def move_agent(self, dt, ids=None):
         """move_agent!(agent, model, dt) for `ids` (all agents when None) — continuous.jl:186-194."""

@@ -177,6 +177,19 @@ int ab_pairs_nearest_fill(ab_handle* h, int64_t* lo, int64_t* hi, int64_t npairs
 int ab_elastic_collisions(ab_handle* h, const int64_t* a, const int64_t* b, int64_t npairs, int mass_field,
                           uint8_t* happened, int64_t* ncollided);
 
+/* get_spatial_index / get_spatial_property, continuous.jl:536-573, for all agents (qpos == NULL, rows in
+ * id order) or for nq query positions (nq x D of the space's element type).  `property` is a column-major
+ * array of prop_dims[0..pd) (pd <= D: the front dimensions of pos index it) with ncomp components stored as
+ * ncomp consecutive arrays.  out_index (optional): nq x pd, 1-based; out_value (optional): nq x ncomp.
+ * An index outside the array (the reference's BoundsError, pos == extent) fails with AB_ERR_OUTSIDE. */
+int ab_spatial_lookup(ab_handle* h, const int64_t* prop_dims, int pd, const double* property, int ncomp,
+                      const void* qpos, int64_t nq, int64_t* out_index, double* out_value);
+/* The force-field form of the `update_vel!` hook (continuous.jl:86-91; called by move_agent!(agent, model, dt)
+ * :186-194 before the move): vel += scale * field[get_spatial_index(pos)] for the scheduled agents
+ * (active_ids == NULL: all).  `field` has D components over prop_dims. */
+int ab_update_vel_field(ab_handle* h, const int64_t* prop_dims, int pd, const double* field, double scale,
+                        const int64_t* active_ids, int64_t nactive);
+
 /* ---- movement ---------------------------------------------------------------
  * move_agent!(agent, model, dt) continuous.jl:186-194 → walk! walk.jl:58-66 →
  * normalize_position walk.jl:77-91, for `active_ids` (NULL = all agents). */

@@ -291,6 +291,15 @@ class ContinuousOracle:
 
 
 
+def spatial_index(pos, extent, shape, dtype=np.float64):
+    """get_spatial_index (src/spaces/continuous.jl:566-573): εs = spacesize[1:Dp] ./ size(property);
+    idxs = floor.(Int, pos[1:Dp] ./ εs) .+ 1, in the space's element type.  Returns (n, Dp) 1-based indices."""
+    pos = np.asarray(pos, dtype=dtype).reshape(-1, len(extent))
+    Dp = len(shape)
+    eps = np.asarray(extent[:Dp], dtype=dtype) / np.asarray(shape, dtype=dtype)
+    return np.floor(pos[:, :Dp] / eps[None, :]).astype(np.int64) + 1
+
+
 def elastic_collision(x1, v1, x2, v2, m1=1.0, m2=1.0):
     """elastic_collision!(a, b, f) (src/spaces/continuous.jl:333-366) on plain floats, same operation order.
     Returns (happened, v1_new, v2_new)."""
