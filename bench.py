@@ -14,15 +14,20 @@ value  : agents*steps / device time of ONE step!(model, K) call after W warm-up
          steps, state resident in HBM (CUDA events on the library's stream,
          max over ranks; the per-step working set exceeds L2, no flush).
 e2e    : same metric through the public API with HOST (pinned) buffers: every
-         step uploads pos+vel, steps once, downloads pos+vel.
+         model step uploads pos+vel, steps once, downloads pos+vel; an ensemble of
+         4 independent models is kept in flight through the asynchronous C ABI
+         (the one-synchronous-model figure is reported beside it).
 roofline: dominant kernel (the sweep) — algorithmic 128 B/agent-update
           x agents per launch / its CUDA-event duration, against the
-         measured HBM copy bandwidth in MEASURED_PEAKS.json.
+         measured HBM copy bandwidth in MEASURED_PEAKS.json.  The per-launch events
+         are recorded in a twin pass over the same steps (they cost ~22 us per step,
+         so the timed region carries none).
 cpu_baseline: the CPU oracle's reference-faithful asynchronous step
          (vector-per-cell index, in-place sequential update, 1 thread — the
          reference's step! is single-threaded) on a bounded sample.
 With --gpus N > 1 (torchrun): weak scaling, 1M boids per GPU, slab decomposition
-along y with NCCL halo / migration exchange.
+along y, halo / migration exchange by direct peer-memory stores (AB_HALO=nccl:
+ncclSend/ncclRecv).
 """
 import argparse
 import ctypes as C
@@ -233,11 +238,11 @@ def run_gpu(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def kernel_table():
+    def kernel_table(m):
         names = (C.c_char_p * 32)()
         kms = (C.c_double * 32)()
         kl = (C.c_int64 * 32)()
-        nk = lib.ab_kernel_times(model.h, names, kms, kl, 32)
+        nk = lib.ab_kernel_times(m.h, names, kms, kl, 32)
         return {names[i].decode(): {"ms_per_launch": kms[i] / max(kl[i], 1), "launches": int(kl[i]), "ms": kms[i]}
                 for i in range(min(nk, 32))}
 
@@ -245,18 +250,33 @@ def run_gpu(args):
     # (K fused steps back to back on the library's stream, no host work in between; the state a step
     #  streams — 2 x (pos, vel, id, key) + step scratch = 130 MB per 1 M boids — exceeds the 126 MB L2, so
     #  there is no flush between steps; the flushed per-step figure is reported beside it.)
+    # Per-launch CUDA events cost ~5 us per launch (22 us of a 260 us step), so the timed region runs
+    # WITHOUT them and the per-kernel durations come from a twin pass over the SAME steps (W..W+K from the
+    # same initial state; N = 1) with the events on; with several ranks the twin pass is the next K steps.
     model.step(args.warmup)
     barrier()
     sampler.start()
-    lib.ab_set_profiling(model.h, 1)        # events recorded around every launch, resolved after the region
     launches0 = model.launch_count()
     model.step(args.steps)
     ms = model.last_step_ms()               # CUDA events around the K steps on the library's stream
     launches = model.launch_count() - launches0
     barrier()
     clocks = sampler.stop()
-    kernels = kernel_table()
-    lib.ab_set_profiling(model.h, 0)
+    if world == 1:
+        twin = ab.StandardABM(ab.ContinuousSpace(extent, spacing=SPACING, periodic=True), model_step=rule, device=local)
+        twin.add_agents(pos, vel)
+        twin.step(args.warmup)
+    else:
+        twin = model
+    barrier()
+    lib.ab_set_profiling(twin.h, 1)         # events recorded around every launch, resolved after the call
+    twin.step(args.steps)
+    ms_profiled = twin.last_step_ms()
+    barrier()
+    kernels = kernel_table(twin)
+    lib.ab_set_profiling(twin.h, 0)
+    if twin is not model:
+        twin.close()
     t = torch.tensor([ms], dtype=torch.float64, device="cuda")
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -293,7 +313,9 @@ def run_gpu(args):
                     "kernel_share_of_step": kernels[dom]["ms"] / max(sum(v["ms"] for v in kernels.values()), 1e-12),
                     "whole_step": {"achieved": alg * nloc / (ms / args.steps * 1e-3) / 1e9,
                                    "frac": alg * nloc / (ms / args.steps * 1e-3) / 1e9 / peak},
-                    "note": "launch durations from CUDA events recorded inside the timed region (rank 0)"}
+                    "profiled_pass_ms_per_step": ms_profiled / args.steps,
+                    "note": "launch durations from CUDA events around every launch in a twin pass over the same steps "
+                            "(rank 0); the timed region itself carries no per-launch events (they cost ~22 us per step)"}
         tpath = os.path.join(ROOT, "profiles", "traffic.json")      # dram bytes per launch from an ncu --set full capture
         if os.path.exists(tpath):
             try:
@@ -386,7 +408,7 @@ def run_gpu(args):
                        "spacing": SPACING, "periodic": True, "search": search, "update": "synchronous",
                        "l2": "no flush: one call of K fused steps; per-step working set (130 MB per 1 M boids) exceeds the 126 MB L2",
                        "kernel": args.kernel,
-                       "parallelism": "single GPU" if world == 1 else f"{world} slabs along y, NCCL halo+migration"},
+                       "parallelism": "single GPU" if world == 1 else f"{world} slabs along y, halo+migration by " + ("direct peer-memory stores" if slabs.direct else "NCCL send/recv")},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
             "l2_flushed_per_step": flushed,
             "kernels": kernels, "kernel_ms_per_step": step_kernel_ms,
