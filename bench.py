@@ -166,6 +166,24 @@ def cpu_flock_rate(n, extent, steps, warmup=0):
     return n * steps / dt, dt
 
 
+def cpu_flock_rate_sync_all_cores(n, extent, steps):
+    """The synchronous CPU formulation (the parity oracle) with its gather phase on all host cores — NOT the
+    reference (Agents.jl's step! is single-task); reported beside the single-thread baseline."""
+    from oracle.pyoracle import ContinuousOracle, set_threads
+
+    cores = set_threads(0)
+    pos, vel = flock_state(n, extent)
+    o = ContinuousOracle(extent, spacing=SPACING)
+    o.add_agents(pos, vel)
+    t0 = time.perf_counter()
+    o.flock_step_sync(FLOCK, nsteps=steps)
+    dt = time.perf_counter() - t0
+    set_threads(1)
+    return {"value": n * steps / dt, "unit": "agent-updates/s", "cores": cores, "kind": "port",
+            "sample": f"{n} boids x {steps} synchronous steps, gather phase on {cores} threads, {dt:.1f} s",
+            "note": "CPU restatement with the synchronous update, not Agents.jl"}
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -187,6 +205,7 @@ def run_reference(args):
                                  "(single-threaded by design: src/simulations/step_standard.jl:9-23)"},
         "e2e": {"value": rate, "unit": "agent-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
+    line["cpu_baseline"]["sync_all_cores"] = cpu_flock_rate_sync_all_cores(n, EXTENT, 2)
     print(json.dumps(line))
     return 0
 
@@ -397,7 +416,8 @@ def run_gpu(args):
         csteps = 2
         rate, dt = cpu_flock_rate(n, EXTENT, csteps)
         cpu = {"value": rate, "unit": "agent-updates/s", "cores": 1, "kind": "port",
-               "sample": f"{n} boids x {csteps} asynchronous steps (reference semantics), {dt:.1f} s, 1 thread"}
+               "sample": f"{n} boids x {csteps} asynchronous steps (reference semantics), {dt:.1f} s, 1 thread",
+               "sync_all_cores": cpu_flock_rate_sync_all_cores(n, EXTENT, 2)}
 
     if rank == 0:
         line = {

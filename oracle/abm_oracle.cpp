@@ -23,6 +23,8 @@
 // Every function cites the reference file:line it restates
 // (paths relative to the Agents.jl tree).
 
+#include <atomic>
+#include <thread>
 #include <algorithm>
 #include <array>
 #include <cmath>
@@ -558,6 +560,8 @@ template <class T> int flock_step_async(CModel<T>* m, const FlockParams* up, con
     return 0;
 }
 
+static int g_threads = 1;     // orc_set_threads
+
 // Synchronous formulation: all new velocities from the
 // old state, then every bird moves.  Equivalent Julia: a model_step! that
 // gathers new velocities into a temporary vector before a second loop applies
@@ -565,11 +569,30 @@ template <class T> int flock_step_async(CModel<T>* m, const FlockParams* up, con
 template <class T> int flock_step_sync(CModel<T>* m, const FlockParams* up, const double* pa, int exact,
                                        int64_t* ncount) {
     std::vector<T> nvel(m->vel.size());
-    for (int64_t id = 1; id <= m->n; ++id) {
-        FlockParams fp = params_for(up, pa, m->n, id);
-        int64_t N;
-        m->flock_new_vel(id, fp, exact != 0, &nvel[(id - 1) * m->D], &N);
-        if (ncount) ncount[id - 1] = N;
+    // every bird reads the old state only: the gather parallelises over the host cores (orc_set_threads;
+    // default 1).  Each bird's arithmetic is untouched, so the results do not depend on the thread count.
+    auto gather = [&](int64_t lo, int64_t hi) {
+        for (int64_t id = lo; id < hi; ++id) {
+            FlockParams fp = params_for(up, pa, m->n, id);
+            int64_t N;
+            m->flock_new_vel(id, fp, exact != 0, &nvel[(id - 1) * m->D], &N);
+            if (ncount) ncount[id - 1] = N;
+        }
+    };
+    if (g_threads <= 1 || m->n < 4096) gather(1, m->n + 1);
+    else {
+        std::atomic<int64_t> next(1);
+        auto work = [&]() {
+            for (;;) {
+                const int64_t lo = next.fetch_add(2048);
+                if (lo > m->n) break;
+                gather(lo, std::min<int64_t>(lo + 2048, m->n + 1));
+            }
+        };
+        std::vector<std::thread> pool;
+        for (int t = 1; t < g_threads; ++t) pool.emplace_back(work);
+        work();
+        for (auto& th : pool) th.join();
     }
     m->vel = nvel;
     for (int64_t id = 1; id <= m->n; ++id) {
@@ -796,6 +819,13 @@ int orc_flock_step_async(void* h, const double* params, const double* per_agent,
     }
     return 0;
 }
+// threads of the synchronous step's gather phase (the asynchronous, reference-faithful step is sequential)
+int orc_set_threads(int n) {
+    if (n < 1) n = (int)std::thread::hardware_concurrency();
+    g_threads = n < 1 ? 1 : n;
+    return g_threads;
+}
+
 int orc_flock_step_sync(void* h, const double* params, const double* per_agent, int exact, int64_t nsteps,
                         int64_t* ncount) {
     FlockParams fp{params[0], params[1], params[2], params[3], params[4], params[5]};

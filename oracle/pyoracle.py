@@ -54,6 +54,14 @@ def lib():
     return _lib
 
 
+def set_threads(n=0):
+    """Threads of the synchronous flock step's gather phase (0 = all host cores).  The asynchronous,
+    reference-faithful step is sequential like the reference's step!."""
+    L = lib()
+    L.orc_set_threads.restype = C.c_int
+    return int(L.orc_set_threads(C.c_int(int(n))))
+
+
 def _p(a):
     return a.ctypes.data_as(C.c_void_p) if a is not None else None
 
