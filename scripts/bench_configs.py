@@ -86,7 +86,7 @@ def particles(n, extent, seed=42, max_radius=10.0, vscale=100.0):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--only", default="f2d_exact,f2d_f32,pf2d,sch,f3d")
+    ap.add_argument("--only", default="f2d_exact,f2d_f32,pf2d,pf2d_pairs,sch,f3d")
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
@@ -118,6 +118,25 @@ def main():
         t0 = time.perf_counter()
         m.add_agents(pos, vel, r=rad, k=k, mass=mass)
         run(m, "PF2D-10M", n, a.steps, a.warmup, 104.0, {"setup_s": time.perf_counter() - t0}, profile=a.profile)
+        if "pf2d_pairs" in only:
+            # the separate row of SURVEY §8d: materialising interacting_pairs(model, cutoff, :all; search = :exact)
+            # (continuous.jl:418-452) — 16 B per pair on the device, copied to two host Int64 vectors
+            import ctypes as C
+
+            lib = m.lib
+            npairs = C.c_int64(0)
+            t0 = time.perf_counter()
+            m._ck(lib.ab_pairs_count(m.h, 20.0, 1, C.byref(npairs)))
+            t_count = time.perf_counter() - t0
+            P = npairs.value
+            lo, hi = np.empty(P, dtype=np.int64), np.empty(P, dtype=np.int64)
+            t0 = time.perf_counter()
+            m._ck(lib.ab_pairs_fill(m.h, m._ptr(lo), m._ptr(hi), P))
+            t_fill = time.perf_counter() - t0
+            ok = bool(np.all(lo < hi))
+            print(json.dumps({"config": "PF2D-10M interacting_pairs(:all, exact, r = 20) materialised", "agents": n, "pairs": P,
+                              "pairs_per_agent": 2.0 * P / n, "count_s": t_count, "fill_and_copy_s": t_fill,
+                              "pairs_per_s": P / (t_count + t_fill), "bytes": 16 * P, "sorted_pairs": ok}), flush=True)
         m.close()
 
     if "sch" in only:
