@@ -76,6 +76,8 @@ _SIGS = {
     "ab_pairs_count": (C.c_int, [_H, C.c_double, C.c_int, C.POINTER(C.c_int64)]),
     "ab_pairs_fill": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_int64]),
     "ab_nearest_neighbor": (C.c_int, [_H, C.c_double, C.c_void_p, C.c_int64]),
+    "ab_nearby_positions_count": (C.c_int, [_H, C.c_void_p, C.c_int64, C.c_double, C.c_int, C.c_void_p]),
+    "ab_nearby_positions_fill": (C.c_int, [_H, C.c_void_p, C.c_int64, C.c_double, C.c_int, C.c_void_p, C.c_void_p]),
     "ab_pairs_nearest": (C.c_int, [_H, C.c_double, C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]),
     "ab_pairs_nearest_fill": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_int64]),
     "ab_elastic_collisions": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.POINTER(C.c_int64)]),

@@ -224,6 +224,94 @@ int ab_grid_nearby(ab_handle* h, const void* qpos, const int64_t* qids, int64_t 
     return e;
 }
 
+// nearby_positions(pos, model, r) — grid_general.jl:185-232: the cells of offsets_within_radius_no_0 around
+// `pos` (wrapped with mod1 on periodic axes, skipped outside the grid otherwise; the origin itself excluded);
+// empty_nearby_positions — discrete.jl:116-129: those of them that hold no agent.
+template <int D, bool SINGLE, bool FILL>
+__global__ void k_gpositions(GridDev<D> g, const int32_t* __restrict__ qpos, int nq, int r0, int empty_only,
+                             const uint32_t* __restrict__ cell_start, const int32_t* __restrict__ grid_ids,
+                             int64_t* __restrict__ counts, const int64_t* __restrict__ offsets, int32_t* __restrict__ out,
+                             int* __restrict__ err) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= nq) return;
+    int c[D];
+    bool ok = true;
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        c[d] = qpos[(size_t)q * D + d] - 1;
+        if (c[d] < 0 || c[d] >= g.dims[d]) ok = false;
+    }
+    if (!ok) { atomicOr(err, AB_EF_OUTSIDE); if (!FILL) counts[q] = 0; return; }
+    int64_t k = 0;
+    const int64_t base = FILL ? offsets[q] : 0;
+    auto visit = [&](uint32_t b, uint32_t e, int) {
+        for (uint32_t j = b; j < e; ++j) {                       // j = linear (column-major) cell
+            if (empty_only) {
+                const bool occupied = SINGLE ? grid_ids[j] != 0 : cell_start[j + 1] != cell_start[j];
+                if (occupied) continue;
+            }
+            if (FILL) {
+                uint32_t rest = j;
+#pragma unroll
+                for (int d = 0; d < D; ++d) {
+                    const uint32_t qd = rest / (uint32_t)g.dims[d];
+                    out[(size_t)(base + k) * D + d] = (int32_t)(rest - qd * (uint32_t)g.dims[d]) + 1;
+                    rest = qd;
+                }
+            }
+            ++k;
+        }
+    };
+    for_each_run_cs<D>(g.dims, g.periodic, g.metric, c, r0, CellIdentity{}, 0, true, visit);
+    if (!FILL) counts[q] = k;
+}
+
+int ab_grid_positions(ab_handle* h, const int32_t* qpos, int64_t nq, double r, int empty_only, int64_t* counts,
+                      const int64_t* offsets, int32_t* pos_out) {
+    if (nq == 0) return AB_OK;
+    if (!qpos) return ab_fail(h, AB_ERR_INVALID, "null query positions");
+    if (h->grid_cols_dirty) AB_TRY(ab_grid_sync_columns(h));
+    if (empty_only) AB_TRY(grid_ensure_index(h));
+    double fr = floor(r + 1.0) - 1.0;                     // offsets_within_radius: r0 = floor(Int, r + 1) - 1
+    if (!(fr < 1.0e9)) fr = 1.0e9;
+    if (!(fr > -1.0e9)) fr = -1.0e9;
+    const int r0 = (int)fr;
+    const bool fill = pos_out != nullptr;
+    const size_t qbytes = (size_t)nq * h->D * sizeof(int32_t);
+    const size_t o1 = (qbytes + 255) / 256 * 256;
+    const size_t cbytes = (size_t)(nq + 1) * sizeof(int64_t);
+    const size_t o2 = o1 + (cbytes + 255) / 256 * 256;
+    int64_t total = 0;
+    if (fill) {
+        if (!offsets) return ab_fail(h, AB_ERR_INVALID, "null offsets");
+        total = offsets[nq];
+        if (total < 0) return ab_fail(h, AB_ERR_INVALID, "bad offsets");
+    } else if (!counts) return ab_fail(h, AB_ERR_INVALID, "null counts");
+    char* base;
+    AB_TRY(ab_scratch(h, o2 + (size_t)total * h->D * sizeof(int32_t) + 256, (void**)&base));
+    AB_CUDA(h, cudaMemcpyAsync(base, qpos, qbytes, cudaMemcpyHostToDevice, h->stream));
+    int64_t* cdev = (int64_t*)(base + o1);
+    int32_t* odev = (int32_t*)(base + o2);
+    if (fill) AB_CUDA(h, cudaMemcpyAsync(cdev, offsets, cbytes, cudaMemcpyHostToDevice, h->stream));
+    const bool single = h->desc.kind == AB_SPACE_GRID_SINGLE;
+    {
+        AB_LAUNCH(h, fill ? "k_gpositions_fill" : "k_gpositions_count");
+        const int TB = 128, nb = ab_blocks(nq, TB);
+#define GP(DD, S, F) k_gpositions<DD, S, F><<<nb, TB, 0, h->stream>>>(make_grid<DD>(h), (const int32_t*)base, (int)nq, r0, empty_only, \
+        h->cell_start, h->grid_ids, F ? nullptr : cdev, F ? cdev : nullptr, F ? odev : nullptr, h->d_err)
+        if (h->D == 2) { if (single) { if (fill) GP(2, true, true); else GP(2, true, false); } else { if (fill) GP(2, false, true); else GP(2, false, false); } }
+        else { if (single) { if (fill) GP(3, true, true); else GP(3, true, false); } else { if (fill) GP(3, false, true); else GP(3, false, false); } }
+#undef GP
+    }
+    if (fill) { if (total > 0) AB_CUDA(h, cudaMemcpyAsync(pos_out, odev, (size_t)total * h->D * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream)); }
+    else AB_CUDA(h, cudaMemcpyAsync(counts, cdev, (size_t)nq * sizeof(int64_t), cudaMemcpyDeviceToHost, h->stream));
+    const bool was_valid = h->index_valid;
+    int e = ab_check_device_errors(h);
+    h->index_valid = was_valid;                          // a bad query does not invalidate the index
+    if (e == AB_ERR_OUTSIDE) return ab_fail(h, AB_ERR_OUTSIDE, "BoundsError: query position outside the grid");
+    return e;
+}
+
 // ---------------------------------------------------------------------------
 // walk!(agent, direction, model; ifempty) — walk.jl:33-56; normalize_position walk.jl:112-126
 // (periodic: mod1, else clamp).  GridSpaceSingle always behaves as ifempty = true (walk.jl:46-56).
@@ -625,6 +713,20 @@ void ab_grid_free(ab_handle* h) {
     if (h->grid_mood) cudaFree(h->grid_mood);
     if (h->h_moved) cudaFreeHost(h->h_moved);
     h->grid_group = nullptr; h->grid_mood = nullptr; h->h_moved = nullptr;
+}
+
+extern "C" int ab_nearby_positions_count(ab_handle* h, const int32_t* qpos, int64_t nq, double r, int empty_only, int64_t* counts) {
+    if (h->desc.kind == AB_SPACE_CONTINUOUS) return ab_fail(h, AB_ERR_INVALID, "nearby_positions is for GridSpace / GridSpaceSingle handles");
+    AB_CUDA(h, cudaSetDevice(h->device));
+    return ab_grid_positions(h, qpos, nq, r, empty_only, counts, nullptr, nullptr);
+}
+extern "C" int ab_nearby_positions_fill(ab_handle* h, const int32_t* qpos, int64_t nq, double r, int empty_only,
+                                        const int64_t* offsets, int32_t* pos_out) {
+    if (h->desc.kind == AB_SPACE_CONTINUOUS) return ab_fail(h, AB_ERR_INVALID, "nearby_positions is for GridSpace / GridSpaceSingle handles");
+    if (!pos_out && nq > 0 && offsets && offsets[nq] > 0) return ab_fail(h, AB_ERR_INVALID, "null output");
+    AB_CUDA(h, cudaSetDevice(h->device));
+    if (nq > 0 && offsets && offsets[nq] == 0) return AB_OK;
+    return ab_grid_positions(h, qpos, nq, r, empty_only, nullptr, offsets, pos_out);
 }
 
 extern "C" int ab_step_schelling(ab_handle* h, const ab_schelling_params* p, int64_t nsteps, int64_t* n_moved) {

@@ -337,6 +337,25 @@ class StandardABM:
         self._ck(self.lib.ab_nearest_neighbor(self.h, float(r), self._ptr(out), n))
         return out
 
+    def nearby_positions_batch(self, positions, r=1, empty=False):
+        """nearby_positions(pos, model, r) (grid_general.jl:185-232) / empty_nearby_positions (discrete.jl:116-129)
+        for a batch of grid positions: CSR (offsets, (total, D) positions)."""
+        q = np.ascontiguousarray(positions, dtype=np.int32).reshape(-1, self.D)
+        nq = len(q)
+        counts = np.zeros(max(nq, 1), dtype=np.int64)
+        self._ck(self.lib.ab_nearby_positions_count(self.h, self._ptr(q), nq, float(r), int(bool(empty)), self._ptr(counts)))
+        off = np.zeros(nq + 1, dtype=np.int64)
+        np.cumsum(counts[:nq], out=off[1:])
+        out = np.zeros((max(int(off[-1]), 1), self.D), dtype=np.int32)
+        self._ck(self.lib.ab_nearby_positions_fill(self.h, self._ptr(q), nq, float(r), int(bool(empty)), self._ptr(off), self._ptr(out)))
+        return off, out[: int(off[-1])]
+
+    def nearby_positions(self, pos, r=1):
+        return self.nearby_positions_batch([pos], r)[1]
+
+    def empty_nearby_positions(self, pos, r=1):
+        return self.nearby_positions_batch([pos], r, empty=True)[1]
+
     # -- spatial fields ---------------------------------------------------------
     def _field_args(self, prop):
         prop = np.asarray(prop, dtype=np.float64)

@@ -154,6 +154,14 @@ int ab_nearby_fill(ab_handle* h, const void* qpos, const int64_t* qids, int64_t 
 
 /* interacting_pairs(model, r, :all; search) continuous.jl:418-452: unique
  * (lo, hi) id pairs; count then fill (fill re-runs the last counted query). */
+/* nearby_positions(pos, model, r) grid_general.jl:185-232 and empty_nearby_positions discrete.jl:116-129 on
+ * GridSpace / GridSpaceSingle handles: for nq query positions (nq x D int32, 1-based) the positions of the
+ * offset table of radius r around each (origin excluded; wrapped on periodic axes, skipped outside the grid
+ * otherwise), optionally only the empty ones.  Count, then fill (CSR offsets from the counts; nq x D rows out). */
+int ab_nearby_positions_count(ab_handle* h, const int32_t* qpos, int64_t nq, double r, int empty_only, int64_t* counts);
+int ab_nearby_positions_fill(ab_handle* h, const int32_t* qpos, int64_t nq, double r, int empty_only,
+                             const int64_t* offsets, int32_t* pos_out);
+
 int ab_pairs_count(ab_handle* h, double r, int search, int64_t* npairs);
 int ab_pairs_fill(ab_handle* h, int64_t* lo, int64_t* hi, int64_t npairs);
 

@@ -219,3 +219,34 @@ def test_schelling_relocation_invariants(dims, periodic, occupancy):
     # segregation progresses: fewer unhappy agents than at the start
     assert (m.column("mood") == 0).sum() <= (mood_exp == 0).sum()
     m.close(); m2.close()
+
+
+@pytest.mark.parametrize("single", [False, True])
+@pytest.mark.parametrize("dims,periodic", [((12, 9), True), ((12, 9), False), ((7, 5, 6), (True, False, True)), ((5, 5), True)])
+@pytest.mark.parametrize("metric", ["chebyshev", "manhattan", "euclidean"])
+def test_nearby_positions_and_empty_positions(single, dims, periodic, metric):
+    """nearby_positions (grid_general.jl:185-232; golden vectors grid_space_tests.jl:168-257 pin the oracle) and
+    empty_nearby_positions (discrete.jl:116-129) — position SETS exact."""
+    ncell = int(np.prod(dims))
+    n = ncell // 2
+    pos = random_positions(dims, n, 5, single=True)            # distinct cells, so both space kinds accept them
+    n = len(pos)
+    Space = ab.GridSpaceSingle if single else ab.GridSpace
+    m = ab.StandardABM(Space(dims, periodic=periodic, metric=metric))
+    m.add_agents(pos.astype(np.int32))
+    o = GridOracle(dims, periodic=periodic, metric=metric, single=single)
+    o.add_agents(pos)
+    occupied = {tuple(p) for p in pos}
+    D = len(dims)
+    qs = np.array([[1] * D, list(dims), [max(1, d // 2) for d in dims], [2] * D, [d - 1 for d in dims]], dtype=np.int32)
+    for r in (1, 2, 3.4, 6):
+        off, got = m.nearby_positions_batch(qs, r)
+        offe, gote = m.nearby_positions_batch(qs, r, empty=True)
+        for i, q in enumerate(qs):
+            want = sorted(map(tuple, o.nearby_positions(q, r)))
+            assert sorted(map(tuple, got[off[i]:off[i + 1]])) == want
+            assert sorted(map(tuple, gote[offe[i]:offe[i + 1]])) == [p for p in want if p not in occupied]
+    assert sorted(map(tuple, m.nearby_positions(qs[2], 1))) == sorted(map(tuple, o.nearby_positions(qs[2], 1)))
+    with pytest.raises(ab.AgentsError):
+        m.nearby_positions([0] * D, 1)
+    m.close()
