@@ -469,6 +469,7 @@ int ab_create(ab_space_desc* desc, int device, ab_handle** out) {
     if (desc->D < 2 || desc->D > 3) return ab_fail(nullptr, AB_ERR_INVALID, "D must be 2 or 3 on the device");
     ab_handle* h = new ab_handle();
     h->device = device;
+    if (const char* e = getenv("AB_OVERLAP")) h->overlap_halo = atoi(e) != 0;
     if (const char* e = getenv("AB_FINE4")) h->fine4 = atoi(e) != 0;     // A/B experiments
     if (const char* e = getenv("AB_RS_TARGET")) { int v = atoi(e); if (v >= 4 && v <= 2048) h->rs_target = v; }   // tuning experiments
     h->D = desc->D;
@@ -560,6 +561,9 @@ int ab_destroy(ab_handle* h) {
     if (h->h_err) cudaFreeHost(h->h_err);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_join) cudaEventDestroy(h->ev_join);
+    if (h->stream2) cudaStreamDestroy(h->stream2);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return AB_OK;

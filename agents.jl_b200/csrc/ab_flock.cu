@@ -254,33 +254,45 @@ static int move_common(ab_handle* h, double dt, const void* directions, const in
     return e;
 }
 
+// part: 0 = all cell rows; 1 = the rows of the interior layers [2, nl - 2) of a slab window (they depend on owned
+// aggregates only); 2 = all the other rows (after the halo aggregates are in place).
 template <class T, int D>
-static int launch_cell_M(ab_handle* h, const SpaceDev<T, D>& sp) {
+static int launch_cell_M(ab_handle* h, const SpaceDev<T, D>& sp, int part = 0) {
     const size_t need = (size_t)2 * FineCfg<D>::NC * h->ncells * sizeof(T);
     if (h->cell_M_bytes < need) {
         if (h->cell_M) { AB_CUDA(h, cudaStreamSynchronize(h->stream)); AB_CUDA(h, cudaFree(h->cell_M)); h->cell_M = nullptr; }
         AB_CUDA(h, cudaMalloc(&h->cell_M, need));
         h->cell_M_bytes = need;
     }
-    AB_LAUNCH(h, "k_cell_M");
     const int wpr = (h->dims[0] + CM_OUT - 1) / CM_OUT;                  // warps per reference cell row
-    const int64_t nwarps = (h->ncells / h->dims[0]) * wpr;
+    const int rows_all = (int)(h->ncells / h->dims[0]);
+    const int rpl = D == 3 ? h->dims[1] : 1;                             // cell rows per layer
+    int skip0 = 0x7fffffff, skiplen = 0, rows = rows_all;
+    if (part != 0) {
+        const int r0 = 2 * rpl, r1 = std::max(r0, (h->win_nl - 2) * rpl);  // interior rows [r0, r1)
+        if (part == 1) { skip0 = 0; skiplen = r0; rows = r1 - r0; }
+        else { skip0 = r0; skiplen = r1 - r0; rows = rows_all - (r1 - r0); }
+    }
+    if (part != 1) h->M_epoch = h->agg_epoch;                            // complete after this launch
+    if (rows <= 0) return AB_OK;
+    AB_LAUNCH(h, "k_cell_M");
+    const int64_t nwarps = (int64_t)rows * wpr;
     k_cell_M<T, D><<<ab_blocks(nwarps * 32, 128), 128, 0, h->stream>>>(sp, (const T*)h->cell_agg, (int64_t)h->ncells, wpr,
-                                                                       (int)nwarps, (T*)h->cell_M);
-    h->M_epoch = h->agg_epoch;
+                                                                       (int)nwarps, (T*)h->cell_M, skip0, skiplen);
     return AB_OK;
 }
 
 template <class T, int D, bool EXACT>
-static int launch_fine(ab_handle* h, const SpaceDev<T, D>& sp, const FlockU<T>& u, int32_t* ncount) {
+static int launch_fine(ab_handle* h, const SpaceDev<T, D>& sp, const FlockU<T>& u, int32_t* ncount, int phase = 0) {
     const int cur = h->cur;
     const int n = h->win_W ? (int)h->cap : (int)h->n;      // slab window: grid over the capacity, live count read on the device
     const int TB = FINE_TB;
     AB_LAUNCH(h, EXACT ? "k_flock_fine_exact" : "k_flock_fine");
+    const uint32_t own_keys = h->win_W ? (uint32_t)((h->nfine / h->dims[D - 1]) * h->win_nl) : 0u;
     k_flock_fine<T, D, EXACT><<<ab_blocks(n, TB), TB, 0, h->stream>>>(
         sp, u, (const T*)h->fields[0].buf[cur], (const T*)h->fields[1].buf[cur], h->key[cur], h->cell_start,
         (const T*)h->cell_M, (int64_t)h->ncells, h->cap, n, (T*)h->tmp_pos, (T*)h->tmp_vel, h->newkey, h->cell_count,
-        h->id[cur], ncount, h->d_err, h->win_W ? h->cell_start + h->nfine : nullptr);
+        h->id[cur], ncount, h->d_err, h->win_W ? h->cell_start + h->nfine : nullptr, phase, own_keys);
     return AB_OK;
 }
 
@@ -374,6 +386,49 @@ static int flock_steps_t(ab_handle* h, const ab_flock_params* p, int64_t nsteps)
     AB_TRY((flock_prepare<T, D>(h, p, &cx)));
     if (ab_comm_local(h)) return ab_fail(h, AB_ERR_STATE, "in-process slabs are stepped together: ab_step_flock_group");
     AB_CUDA(h, cudaEventRecord(h->ev0, h->stream));
+    if (h->win_W && cx.fine && h->overlap_halo) {
+        // Sharded handle: the boundary messages of a step travel while the NEXT step's interior layers are swept.
+        //   sweep(interior)  -  install the halo sent at the end of the previous step, halo aggregates, M of the
+        //   boundary rows  -  sweep(boundary + first halo layers)  -  scan, re-sort, pack + send  -  M of the interior rows
+        // The interior birds read no halo data (aggregates within 2 layers, pairs within 1), so the only thing that
+        // waits for the neighbours is the thin boundary sweep.  The call ends with the state complete.
+        // The halo install and the boundary sweep are short, latency-bound kernels (a few hundred warps): they run on
+        // a side stream CONCURRENTLY with the interior sweep (disjoint slots, disjoint cell rows, shared histogram).
+        auto install = [&]() -> int {
+            AB_TRY(ab_comm_transfer(h));
+            AB_TRY(ab_comm_unpack(h, !cx.exact));
+            if (!cx.exact) AB_TRY((launch_cell_M<T, D>(h, cx.sp, 2)));
+            return AB_OK;
+        };
+        if (!h->stream2) {
+            // highest priority: its CTAs are dispatched as soon as interior-sweep CTAs retire, not after the last one
+            int prio_lo = 0, prio_hi = 0;
+            AB_CUDA(h, cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+            AB_CUDA(h, cudaStreamCreateWithPriority(&h->stream2, cudaStreamNonBlocking, prio_hi));
+            AB_CUDA(h, cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+            AB_CUDA(h, cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
+        }
+        for (int64_t st = 0; st < nsteps; ++st) {
+            AB_CUDA(h, cudaEventRecord(h->ev_fork, h->stream));
+            AB_CUDA(h, cudaStreamWaitEvent(h->stream2, h->ev_fork, 0));
+            if (cx.exact) AB_TRY((launch_fine<T, D, true>(h, cx.sp, cx.u, nullptr, 1)));
+            else AB_TRY((launch_fine<T, D, false>(h, cx.sp, cx.u, nullptr, 1)));
+            std::swap(h->stream, h->stream2);                    // everything queued below goes to the side stream
+            int rc = st > 0 ? install() : AB_OK;
+            if (rc == AB_OK) rc = cx.exact ? launch_fine<T, D, true>(h, cx.sp, cx.u, nullptr, 2) : launch_fine<T, D, false>(h, cx.sp, cx.u, nullptr, 2);
+            cudaError_t ce = cudaEventRecord(h->ev_join, h->stream);
+            std::swap(h->stream, h->stream2);
+            AB_TRY(rc);
+            AB_CUDA(h, ce);
+            AB_CUDA(h, cudaStreamWaitEvent(h->stream, h->ev_join, 0));
+            AB_TRY(ab_resort_tiled(h, h->tmp_pos, h->tmp_vel, !cx.exact));
+            AB_TRY(ab_comm_pack(h));
+            if (!cx.exact) AB_TRY((launch_cell_M<T, D>(h, cx.sp, 1)));
+        }
+        AB_TRY(install());
+        AB_CUDA(h, cudaEventRecord(h->ev1, h->stream));
+        return AB_OK;
+    }
     for (int64_t st = 0; st < nsteps; ++st) {
         AB_TRY((flock_half_A<T, D>(h, cx, st == nsteps - 1)));
         if (h->win_W) AB_TRY(ab_comm_transfer(h));

@@ -75,13 +75,16 @@ __device__ __forceinline__ int wrap_coord(int c, int n, bool periodic) {
 template <class T> __device__ __forceinline__ T shfl_T(T v, int src) { return __shfl_sync(0xffffffffu, v, src); }
 template <class T, int D>
 __global__ void __launch_bounds__(128)
-k_cell_M(SpaceDev<T, D> sp, const T* __restrict__ aggp, int64_t ncells, int wpr, int nwarps, T* __restrict__ M) {
+k_cell_M(SpaceDev<T, D> sp, const T* __restrict__ aggp, int64_t ncells, int wpr, int nwarps, T* __restrict__ M,
+         int skip0, int skiplen) {
     constexpr int NC = FineCfg<D>::NC;
     constexpr int NRO = D == 2 ? 5 : 13;
     const int warp = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     if (warp >= nwarps) return;
     const int lane = threadIdx.x & 31;
-    const int row = warp / wpr, seg = warp - row * wpr;
+    // launched rows r map to cell rows r (r < skip0) or r + skiplen: all rows, the interior rows only, or all but them
+    const int r_ = warp / wpr, seg = warp - r_ * wpr;
+    const int row = r_ < skip0 ? r_ : r_ + skiplen;
     const int cy = D == 2 ? row : row % sp.dims[1];
     const int cz = D == 2 ? 0 : row / sp.dims[1];
     const int xout = seg * CM_OUT + lane - 2;                                  // this lane's output cell (lanes 2..29)
@@ -197,11 +200,14 @@ k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T
              const uint32_t* __restrict__ key, const uint32_t* __restrict__ cs, const T* __restrict__ M,
              int64_t ncells, int64_t cap, int n, T* __restrict__ npos, T* __restrict__ nvel,
              uint32_t* __restrict__ newkey, uint32_t* __restrict__ cell_count, const int32_t* __restrict__ ids,
-             int32_t* __restrict__ ncount, int* __restrict__ err, const uint32_t* __restrict__ nslots) {
+             int32_t* __restrict__ ncount, int* __restrict__ err, const uint32_t* __restrict__ nslots, int phase,
+             uint32_t own_keys) {
     constexpr int NC = FineCfg<D>::NC;
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
-    // slab window: the slot count lives on the device (migration changes it without a host round trip)
-    if (s >= (nslots ? (int)*nslots : n)) return;
+    // slab window: the slot count lives on the device (migration changes it without a host round trip).
+    // phase 1 (interior layers, swept while the halo of this state may still be arriving): owned slots only —
+    // the halo slots and the halo part of cell_start are not valid yet.
+    if (s >= (phase == 1 ? (int)cs[own_keys] : (nslots ? (int)*nslots : n))) return;
     const int K = sp.K, kb = sp.kb;
     int f[D], c[D], cg[D];
     const uint32_t k = key[s];
@@ -213,6 +219,9 @@ k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T
         // received: its birds may enter the owned layers in this step); outer halo slots are skipped
         const int l = c[D - 1];
         if (!(l <= sp.nl || l == sp.nl + 2 * sp.W - 1)) return;
+        // interior = layers whose birds read no halo data: aggregates within 2 layers, pair sweep within 1
+        const bool interior = l >= 2 && l < sp.nl - 2;
+        if ((phase == 1 && !interior) || (phase == 2 && interior)) return;
         cg[D - 1] = local_to_global_last<T, D>(sp, l);
     }
     T p[D], v[D];

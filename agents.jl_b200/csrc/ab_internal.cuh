@@ -102,6 +102,9 @@ struct ab_handle {
     // sums of those aggregates over the reference's offset tables of radius 1 and 2 (k_cell_M)
     void* cell_M = nullptr;
     size_t cell_M_bytes = 0;
+    cudaStream_t stream2 = nullptr;    // side stream of the overlapped sharded step (halo install + boundary sweep)
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    bool overlap_halo = false;         // sharded flock step: interior sweep while the halo travels — measured slower, AB_OVERLAP=1 enables
     bool fine4 = false;                // quarter-cell refinement (K = 4) on the 2-D flock path: correct, measured slower (AB_FINE4=1 enables)
     int rs_target = 100;               // average agents per re-sort tile (tuning knob)
 

@@ -19,8 +19,8 @@ def _ngpu():
         return 0
 
 
-def _run(world, port, *wargs, halo="direct"):
-    env = dict(os.environ, AB_HALO=halo)
+def _run(world, port, *wargs, halo="direct", overlap="0"):
+    env = dict(os.environ, AB_HALO=halo, AB_OVERLAP=overlap)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "mgpu_worker.py"), *wargs]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT, env=env)
@@ -64,3 +64,16 @@ def test_four_gpus_bitwise_equal_to_one():
         pytest.skip("needs >= 4 GPUs")
     r = _run(4, 29533, "--agents", "120000", "--extent", "400", "800", "--steps", "10")
     assert r["conserved"] and r["pos_bitwise_equal"] and r["vel_bitwise_equal"], r
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("wargs", [["--agents", "60000", "--extent", "400", "400", "--steps", "12"],
+                                   ["--agents", "40000", "--extent", "60", "60", "120", "--steps", "8"],
+                                   ["--agents", "60000", "--extent", "400", "400", "--steps", "9", "--search", "exact", "--chunk", "3"]],
+                         ids=["2d", "3d", "2d-exact"])
+def test_overlapped_step_order_gives_the_same_bits(wargs):
+    """AB_OVERLAP=1: interior layers swept while the halo travels, halo install + boundary sweep on a side stream."""
+    if _ngpu() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    r = _run(2, 29537, *wargs, overlap="1")
+    assert r["conserved"] and r["pos_bitwise_equal"] and r["vel_bitwise_equal"] and r["direct"], r
