@@ -50,8 +50,14 @@ struct ResortArgs {
     int has_vel, want_agg;
 };
 
+#ifndef RS_MINB
+#define RS_MINB 1
+#endif
+#ifndef RS_G2D
+#define RS_G2D 4
+#endif
 template <class T, int D, int G>
-__global__ void __launch_bounds__(RS_THREADS)
+__global__ void __launch_bounds__(RS_THREADS, RS_MINB)
 k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, const uint32_t* __restrict__ newkey,
          const int32_t* __restrict__ id_old, const T* __restrict__ src_pos, const T* __restrict__ src_vel,
          int64_t cap, T* dst_pos, T* dst_vel, int32_t* __restrict__ id_new,
@@ -386,7 +392,7 @@ static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool
     const bool extra = h->fields.size() > 2u;
     {
         AB_LAUNCH(h, "k_resort");
-        constexpr int G = (D == 2) ? 4 : 2;           // source chunks in flight per warp
+        constexpr int G = (D == 2) ? RS_G2D : 2;           // source chunks in flight per warp
         k_resort<T, D, G><<<(a.ntiles + RS_WARPS - 1) / RS_WARPS, RS_THREADS, 0, h->stream>>>(
             sp, a, h->cell_start, h->newkey, h->id[cur], (const T*)src_pos, (const T*)src_vel, h->cap,
             (T*)h->fields[0].buf[nxt], (T*)h->fields[1].buf[nxt], h->id[nxt], h->key[nxt], h->cell_start_alt,
