@@ -275,10 +275,28 @@ static int launch_cell_M(ab_handle* h, const SpaceDev<T, D>& sp, int part = 0) {
     }
     if (part != 1) h->M_epoch = h->agg_epoch;                            // complete after this launch
     if (rows <= 0) return AB_OK;
+    int nfr = D == 2 ? h->K : h->K * h->K;
+    const T* aggp = (const T*)h->cell_agg;
+    if (nfr == 4) {
+        // 4 partials per cell: collapse them once instead of reading all four from every neighbour row
+        const int64_t total = (int64_t)FineCfg<D>::NC * h->ncells;
+        const size_t need1 = (size_t)total * sizeof(T);
+        if (h->cell_agg1_bytes < need1) {
+            if (h->cell_agg1) { AB_CUDA(h, cudaStreamSynchronize(h->stream)); AB_CUDA(h, cudaFree(h->cell_agg1)); h->cell_agg1 = nullptr; }
+            AB_CUDA(h, cudaMalloc(&h->cell_agg1, need1));
+            h->cell_agg1_bytes = need1;
+        }
+        {
+            AB_LAUNCH(h, "k_agg_collapse");
+            k_agg_collapse<T><<<ab_blocks(total, 256), 256, 0, h->stream>>>(aggp, total, (T*)h->cell_agg1);
+        }
+        aggp = (const T*)h->cell_agg1;
+        nfr = 1;
+    }
     AB_LAUNCH(h, "k_cell_M");
     const int64_t nwarps = (int64_t)rows * wpr;
-    k_cell_M<T, D><<<ab_blocks(nwarps * 32, 128), 128, 0, h->stream>>>(sp, (const T*)h->cell_agg, (int64_t)h->ncells, wpr,
-                                                                       (int)nwarps, (T*)h->cell_M, skip0, skiplen);
+    k_cell_M<T, D><<<ab_blocks(nwarps * 32, 128), 128, 0, h->stream>>>(sp, aggp, (int64_t)h->ncells, wpr,
+                                                                       (int)nwarps, (T*)h->cell_M, skip0, skiplen, nfr);
     return AB_OK;
 }
 

@@ -71,12 +71,25 @@ __device__ __forceinline__ int wrap_coord(int c, int n, bool periodic) {
 // A warp covers CM_OUT consecutive cells of one reference cell row plus 2 halo cells per side:
 // each lane loads the aggregates of ONE cell per neighbour row and the ±1, ±2 x-neighbours
 // come from warp shuffles, so every aggregate is read once per row offset, not once per offset.
+// One aggregate per reference cell out of its 4 fine-row partials (3-D K = 2, 2-D K = 4), summed in the order
+// k_cell_M would use — so that its 13 (5) neighbour-row reads per cell touch a quarter of the data.
+template <class T>
+__global__ void k_agg_collapse(const T* __restrict__ aggp, int64_t total, T* __restrict__ out) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;       // total = NC * ncells
+    if (t >= total) return;
+    T v = aggp[t];
+    v += aggp[total + t];
+    v += aggp[2 * total + t];
+    v += aggp[3 * total + t];
+    out[t] = v;
+}
+
 #define CM_OUT 28
 template <class T> __device__ __forceinline__ T shfl_T(T v, int src) { return __shfl_sync(0xffffffffu, v, src); }
 template <class T, int D>
 __global__ void __launch_bounds__(128)
 k_cell_M(SpaceDev<T, D> sp, const T* __restrict__ aggp, int64_t ncells, int wpr, int nwarps, T* __restrict__ M,
-         int skip0, int skiplen) {
+         int skip0, int skiplen, int nfr) {
     constexpr int NC = FineCfg<D>::NC;
     constexpr int NRO = D == 2 ? 5 : 13;
     const int warp = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
@@ -89,7 +102,7 @@ k_cell_M(SpaceDev<T, D> sp, const T* __restrict__ aggp, int64_t ncells, int wpr,
     const int cz = D == 2 ? 0 : row / sp.dims[1];
     const int xout = seg * CM_OUT + lane - 2;                                  // this lane's output cell (lanes 2..29)
     const int xl = xout > sp.dims[0] + 1 ? -1 : wrap_coord(xout, sp.dims[0], sp.periodic[0]);   // cell whose aggregates this lane loads
-    const int nfr = D == 2 ? sp.K : sp.K * sp.K;
+    // nfr = partials per cell in aggp: K^(D-1) as written by the re-sort, or 1 after k_agg_collapse
     T acc1[NC], acc2[NC];
     int cb1[D], cb2[D];
 #pragma unroll

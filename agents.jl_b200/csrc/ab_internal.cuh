@@ -99,6 +99,8 @@ struct ab_handle {
     // (SoA: [part][1+2D][ncells] of T) — input of the aggregated approximate-search sweep (ab_flock.cu)
     void* cell_agg = nullptr;
     size_t cell_agg_bytes = 0;
+    void* cell_agg1 = nullptr;         // the 4 fine-row partials of cell_agg collapsed to one (k_agg_collapse)
+    size_t cell_agg1_bytes = 0;
     // sums of those aggregates over the reference's offset tables of radius 1 and 2 (k_cell_M)
     void* cell_M = nullptr;
     size_t cell_M_bytes = 0;

@@ -50,14 +50,16 @@ struct ResortArgs {
     int has_vel, want_agg;
 };
 
-#ifndef RS_MINB
-#define RS_MINB 1
+#ifdef RS_MINB
+#define RS_BOUNDS __launch_bounds__(RS_THREADS, RS_MINB)
+#else
+#define RS_BOUNDS __launch_bounds__(RS_THREADS)      // (an explicit minimum of 1 block lets ptxas take 91-104 registers: slower)
 #endif
 #ifndef RS_G2D
 #define RS_G2D 4
 #endif
 template <class T, int D, int G>
-__global__ void __launch_bounds__(RS_THREADS, RS_MINB)
+__global__ void RS_BOUNDS
 k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, const uint32_t* __restrict__ newkey,
          const int32_t* __restrict__ id_old, const T* __restrict__ src_pos, const T* __restrict__ src_vel,
          int64_t cap, T* dst_pos, T* dst_vel, int32_t* __restrict__ id_new,
