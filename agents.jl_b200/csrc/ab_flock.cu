@@ -307,10 +307,15 @@ static int launch_fine(ab_handle* h, const SpaceDev<T, D>& sp, const FlockU<T>& 
     const int TB = FINE_TB;
     AB_LAUNCH(h, EXACT ? "k_flock_fine_exact" : "k_flock_fine");
     const uint32_t own_keys = h->win_W ? (uint32_t)((h->nfine / h->dims[D - 1]) * h->win_nl) : 0u;
-    k_flock_fine<T, D, EXACT><<<ab_blocks(n, TB), TB, 0, h->stream>>>(
-        sp, u, (const T*)h->fields[0].buf[cur], (const T*)h->fields[1].buf[cur], h->key[cur], h->cell_start,
-        (const T*)h->cell_M, (int64_t)h->ncells, h->cap, n, (T*)h->tmp_pos, (T*)h->tmp_vel, h->newkey, h->cell_count,
-        h->id[cur], ncount, h->d_err, h->win_W ? h->cell_start + h->nfine : nullptr, phase, own_keys);
+#define FINE_ARGS sp, u, (const T*)h->fields[0].buf[cur], (const T*)h->fields[1].buf[cur], h->key[cur], h->cell_start, \
+        (const T*)h->cell_M, (int64_t)h->ncells, h->cap, n, (T*)h->tmp_pos, (T*)h->tmp_vel, h->newkey, h->cell_count, \
+        h->id[cur], ncount, h->d_err, h->win_W ? h->cell_start + h->nfine : nullptr, phase, own_keys
+    bool done = false;
+    if constexpr (!EXACT && D == 2) {
+        if (u.reach == 2) { k_flock_fine<T, D, false, true><<<ab_blocks(n, TB), TB, 0, h->stream>>>(FINE_ARGS); done = true; }
+    }
+    if (!done) k_flock_fine<T, D, EXACT><<<ab_blocks(n, TB), TB, 0, h->stream>>>(FINE_ARGS);
+#undef FINE_ARGS
     return AB_OK;
 }
 

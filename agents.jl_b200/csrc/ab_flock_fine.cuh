@@ -207,7 +207,9 @@ __device__ __forceinline__ bool pos2cell0_fast(const SpaceDev<T, D>& sp, const T
     return pos2cell0<T, D>(sp, p, c);
 }
 
-template <class T, int D, bool EXACT>
+// REACH2: quarter cells (K = 4) with a reach-2 separation sweep — a separate instantiation, so that the common
+// reach-1 sweep keeps its compile-time trip counts (a run-time reach cost the 3-D sweep 13 %).
+template <class T, int D, bool EXACT, bool REACH2 = false>
 __global__ void __launch_bounds__(FINE_TB, FINE_MINB)
 k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T* __restrict__ vel,
              const uint32_t* __restrict__ key, const uint32_t* __restrict__ cs, const T* __restrict__ M,
@@ -274,7 +276,7 @@ k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T
             }
         }
         const T thr = fp.thr;
-        const int R = EXACT ? K : fp.reach;            // fine-cell reach of the sweep (1 or 2)
+        const int R = EXACT ? K : (REACH2 ? 2 : 1);    // fine-cell reach of the sweep
         const int fd0 = sp.dims[0] << kb, fd1 = sp.dims[1] << kb, fd2 = D == 3 ? (sp.dims[2] << kb) : 1;
         // slab window: rows are indexed in the local (window-periodic) frame, but whether a row lies across
         // the space's periodic boundary — i.e. needs the minimum image — is decided on GLOBAL fine rows
@@ -312,7 +314,7 @@ k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T
             if (wrap == 0) sweep_t(jb, je, 0, std::false_type{});
             else sweep_t(jb, je, wrap, std::true_type{});
         };
-        constexpr int NROW = 5;                        // fine rows per z-slab: 2R+1, R <= 2
+        constexpr int NROW = (EXACT || REACH2) ? 5 : 3; // fine rows per z-slab: 2R+1
         for (int rz = (D == 3 ? -R : 0); rz <= (D == 3 ? R : 0); ++rz) {
             int fz = 0, wz = 0, dz = 0;
             if (D == 3) {
