@@ -21,9 +21,10 @@ from .model import (  # noqa: F401
     PairForceRule,
     SchellingRule,
     StandardABM,
+    load_checkpoint,
 )
 
 __all__ = [
     "AgentsError", "ContinuousSpace", "GridSpace", "GridSpaceSingle", "StandardABM", "FlockRule",
-    "PairForceRule", "SchellingRule", "build", "lib", "declared_symbols",
+    "PairForceRule", "SchellingRule", "load_checkpoint", "build", "lib", "declared_symbols",
 ]

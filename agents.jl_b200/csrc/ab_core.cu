@@ -102,6 +102,7 @@ int ab_check_device_errors(ab_handle* h) {
     if (e & AB_EF_NUMERIC) return ab_fail(h, AB_ERR_NUMERIC, "InexactError: a NaN/Inf position reached a cell computation");
     if (e & AB_EF_OUTSIDE) return ab_fail(h, AB_ERR_OUTSIDE, "position is outside space extent!");
     if (e & AB_EF_OCCUPIED) return ab_fail(h, AB_ERR_OCCUPIED, "Cannot add agent to occupied position");
+    if (e & AB_EF_ARG) return ab_fail(h, AB_ERR_INVALID, "ArgumentError: The displacement must be larger than 0.");
     if (e & AB_EF_COMM) return ab_fail(h, AB_ERR_COMM, "halo exchange overflow: more agents in the boundary layers than the message capacity (ab_comm_set_capacity) or than the handle's capacity (ab_resize)");
     if (e & AB_EF_OVERFLOW) return ab_fail(h, AB_ERR_INVALID, "device-side failure: id out of range, or an agent left its cell neighbourhood in one tiled step");
     return ab_fail(h, AB_ERR_INVALID, "device-side failure");
@@ -230,14 +231,18 @@ __global__ void k_place(const uint32_t* __restrict__ newkey, const uint32_t* __r
                         const int32_t* __restrict__ idtmp, const T* __restrict__ src_pos,
                         const T* __restrict__ src_vel, int64_t cap, int n, T* __restrict__ dst_pos,
                         T* __restrict__ dst_vel, int32_t* __restrict__ id_new, uint32_t* __restrict__ key_new,
-                        int32_t* __restrict__ perm, int32_t* __restrict__ slot_of_id) {
+                        int32_t* __restrict__ perm, int32_t* __restrict__ slot_of_id, const int32_t* __restrict__ prio) {
     int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
     const uint32_t k = newkey[s];
     const uint32_t b = cell_start[k], e = cell_start[k + 1];
     const int32_t me = id_old[s];
     uint32_t r;
-    if (e - b <= AB_CANON_MAX) {
+    if (prio) {                       // restored layout (ab_layout_set): in-cell order of the checkpoint
+        r = 0;
+        const int32_t mine = prio[me];
+        for (uint32_t t = b; t < e; ++t) r += (prio[idtmp[t]] < mine) ? 1u : 0u;
+    } else if (e - b <= AB_CANON_MAX) {
         r = 0;
         for (uint32_t t = b; t < e; ++t) r += (idtmp[t] < me) ? 1u : 0u;
     } else r = rank[s];
@@ -365,11 +370,11 @@ static int reindex_t(ab_handle* h, const void* src_pos, const void* src_vel, boo
                 k_place<T, D, true><<<ab_blocks(n, TB), TB, 0, h->stream>>>(
                     h->newkey, h->rank, h->cell_start, h->id[cur], h->idtmp, (const T*)src_pos, (const T*)src_vel,
                     h->cap, n, (T*)h->fields[0].buf[nxt], (T*)h->fields[1].buf[nxt], h->id[nxt], h->key[nxt],
-                    extra ? h->perm : nullptr, nullptr);
+                    extra ? h->perm : nullptr, nullptr, h->place_prio);
             else
                 k_place<T, D, false><<<ab_blocks(n, TB), TB, 0, h->stream>>>(
                     h->newkey, h->rank, h->cell_start, h->id[cur], h->idtmp, (const T*)src_pos, nullptr, h->cap, n,
-                    (T*)h->fields[0].buf[nxt], nullptr, h->id[nxt], h->key[nxt], extra ? h->perm : nullptr, nullptr);
+                    (T*)h->fields[0].buf[nxt], nullptr, h->id[nxt], h->key[nxt], extra ? h->perm : nullptr, nullptr, h->place_prio);
         }
         AB_TRY(ab_permute_extra_fields(h));
     }
@@ -736,6 +741,66 @@ int ab_build_index(ab_handle* h) {
     }
     h->index_valid = false;
     return ab_ensure_index(h);
+}
+
+// Checkpoint support — AgentsIO.save_checkpoint / load_checkpoint (src/submodules/io/jld2_integration.jl:85-135,
+// :196-223) keep the space's stored_ids, i.e. the order of the agents inside every cell, and a resumed run
+// continues exactly.  The device equivalent of that order is the slot order: floating-point sums over a cell
+// follow it, so a run restored with ab_layout_set continues bit for bit.
+int ab_layout_get(ab_handle* h, int64_t* slot_ids, int64_t n, int32_t* refinement, int64_t* tick) {
+    if (h->win_W) return ab_fail(h, AB_ERR_STATE, "not available on a sharded handle");
+    if (n != h->n) return ab_fail(h, AB_ERR_INVALID, "length must equal the agent count");
+    AB_CUDA(h, cudaSetDevice(h->device));
+    if (refinement) *refinement = h->K;
+    if (tick) *tick = (int64_t)h->sch_tick;
+    if (!slot_ids || n == 0) return AB_OK;
+    if (h->desc.kind != AB_SPACE_CONTINUOUS) {               // grid columns stay in id order
+        for (int64_t i = 0; i < n; ++i) slot_ids[i] = i + 1;
+        return AB_OK;
+    }
+    AB_TRY(ab_ensure_index(h));
+    std::vector<int32_t> ids((size_t)n);
+    AB_CUDA(h, cudaMemcpyAsync(ids.data(), h->id[h->cur], (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
+    AB_CUDA(h, cudaStreamSynchronize(h->stream));
+    for (int64_t i = 0; i < n; ++i) slot_ids[i] = (int64_t)ids[(size_t)i] + 1;
+    return AB_OK;
+}
+
+int ab_layout_set(ab_handle* h, const int64_t* slot_ids, int64_t n, int32_t refinement, int64_t tick) {
+    if (h->win_W) return ab_fail(h, AB_ERR_STATE, "not available on a sharded handle");
+    if (n != h->n) return ab_fail(h, AB_ERR_INVALID, "length must equal the agent count");
+    if (tick < 0) return ab_fail(h, AB_ERR_INVALID, "negative tick");
+    AB_CUDA(h, cudaSetDevice(h->device));
+    AB_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->sch_tick = (uint64_t)tick;
+    if (h->desc.kind != AB_SPACE_CONTINUOUS) return AB_OK;
+    AB_TRY(ab_set_refine(h, refinement));
+    if (!slot_ids || n == 0) return AB_OK;
+    std::vector<int32_t> prio((size_t)n, -1);
+    for (int64_t i = 0; i < n; ++i) {
+        const int64_t id = slot_ids[i];
+        if (id < 1 || id > n || prio[(size_t)id - 1] >= 0) return ab_fail(h, AB_ERR_INVALID, "slot order is not a permutation of 1..n");
+        prio[(size_t)id - 1] = (int32_t)i;
+    }
+    int32_t* dprio = nullptr;
+    AB_CUDA(h, cudaMalloc(&dprio, (size_t)n * 4));
+    cudaError_t ce = cudaMemcpyAsync(dprio, prio.data(), (size_t)n * 4, cudaMemcpyHostToDevice, h->stream);
+    int rc = AB_OK;
+    if (ce == cudaSuccess) {
+        h->place_prio = dprio;
+        h->index_valid = false;
+        rc = ab_reindex_from(h, h->fields[0].buf[h->cur], h->fields[1].buf[h->cur], false);
+        h->place_prio = nullptr;
+        if (rc == AB_OK) {
+            const bool was_async = h->async_mode;
+            h->async_mode = false;
+            rc = ab_check_device_errors(h);                    // synchronises: prio and dprio may go
+            h->async_mode = was_async;
+        } else cudaStreamSynchronize(h->stream);
+    }
+    cudaFree(dprio);
+    AB_CUDA(h, ce);
+    return rc;
 }
 
 int ab_cells(ab_handle* h, int32_t* out_cells, int64_t n) {

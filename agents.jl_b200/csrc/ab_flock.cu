@@ -200,6 +200,59 @@ __global__ void k_ids_to_slots(const int64_t* __restrict__ ids, const int32_t* _
     slots[t] = slot_of_id[id - 1];
 }
 
+// uniform_randomwalk!(agent, model, r) — src/spaces/walk.jl:389-408: v = D standard normals, direction =
+// v ./ norm(v) .* r (r = norm(agent.vel) when not given), or (±1, …) * r / sqrt(D) if the normals are all zero;
+// agent.vel = direction; then walk!(agent, direction, model).  The normals are Box–Muller pairs on the
+// counter stream of ab_internal.cuh (draws 0..3), the signs of the degenerate branch draws 8..8+D-1.
+struct RwArgs { double r; uint64_t seed; };
+
+template <class T, int D>
+__global__ void k_rw_dirs(T* __restrict__ vel, int64_t cap, int n, const int32_t* __restrict__ slots,
+                          const int64_t* __restrict__ ids, int nactive, RwArgs rw, T* __restrict__ dirs, int* __restrict__ err) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nactive) return;
+    const int s = slots ? slots[t] : t;
+    const int64_t id = ids ? ids[t] : (int64_t)t + 1;
+    if (s < 0 || s >= n) {
+#pragma unroll
+        for (int d = 0; d < D; ++d) dirs[(size_t)t * D + d] = T(0);
+        return;
+    }
+    double r = rw.r;
+    if (r < 0.0) {                                            // default r = sqrt(sum(abs2.(agent.vel)))
+        T q = T(0);
+#pragma unroll
+        for (int d = 0; d < D; ++d) { const T v = vel[(size_t)d * cap + s]; q += v * v; }
+        r = (double)sqrt(q);
+    }
+    if (!(r > 0.0)) {
+        atomicOr(err, AB_EF_ARG);
+#pragma unroll
+        for (int d = 0; d < D; ++d) dirs[(size_t)t * D + d] = T(0);
+        return;
+    }
+    T v[D];
+#pragma unroll
+    for (int pr = 0; pr < (D + 1) / 2; ++pr) {
+        const double u1 = ab_rw_u01(rw.seed, id, 2 * pr), u2 = ab_rw_u01(rw.seed, id, 2 * pr + 1);
+        const double R = sqrt(-2.0 * log(1.0 - u1)), a = 6.283185307179586 * u2;
+        v[2 * pr] = (T)(R * cos(a));
+        if (2 * pr + 1 < D) v[2 * pr + 1] = (T)(R * sin(a));
+    }
+    T q = T(0);
+#pragma unroll
+    for (int d = 0; d < D; ++d) q += v[d] * v[d];
+    const T nv = sqrt(q);
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        T dir;
+        if (nv != T(0)) dir = (T)((double)(v[d] / nv) * r);
+        else dir = (T)((ab_rw_u01(rw.seed, id, 8 + d) < 0.5 ? -1.0 : 1.0) * r / sqrt((double)D));
+        vel[(size_t)d * cap + s] = dir;
+        dirs[(size_t)t * D + d] = dir;
+    }
+}
+
 template <class T, int D>
 static int move_t(ab_handle* h, double dt, const void* directions_dev, const int32_t* slots, int nactive) {
     if (nactive == 0) return AB_OK;
@@ -210,7 +263,8 @@ static int move_t(ab_handle* h, double dt, const void* directions_dev, const int
     return AB_OK;
 }
 
-static int move_common(ab_handle* h, double dt, const void* directions, const int64_t* active_ids, int64_t nactive) {
+static int move_common(ab_handle* h, double dt, const void* directions, const int64_t* active_ids, int64_t nactive,
+                       const RwArgs* rw = nullptr) {
     if (h->desc.kind != AB_SPACE_CONTINUOUS) return ab_fail(h, AB_ERR_INVALID, "continuous-space call on a grid handle");
     if (h->win_W) return ab_fail(h, AB_ERR_STATE, "bulk moves are not available on a sharded (slab-window) handle");
     AB_CUDA(h, cudaSetDevice(h->device));
@@ -219,8 +273,9 @@ static int move_common(ab_handle* h, double dt, const void* directions, const in
     void* dir_dev = nullptr;
     int na = active_ids ? (int)nactive : (int)h->n;
     if (active_ids && nactive < 0) return ab_fail(h, AB_ERR_INVALID, "negative nactive");
-    size_t dir_bytes = directions ? (size_t)na * h->D * h->tsize : 0;
-    if (active_ids || directions) {
+    size_t dir_bytes = (directions || rw) ? (size_t)na * h->D * h->tsize : 0;
+    const int64_t* ids_dev = nullptr;
+    if (active_ids || directions || rw) {
         size_t ids_bytes = active_ids ? (size_t)na * sizeof(int64_t) : 0;
         size_t slots_bytes = active_ids ? (size_t)na * sizeof(int32_t) : 0;
         size_t o1 = (ids_bytes + 255) / 256 * 256, o2 = o1 + (slots_bytes + 255) / 256 * 256;
@@ -230,6 +285,7 @@ static int move_common(ab_handle* h, double dt, const void* directions, const in
             AB_CUDA(h, cudaMemcpyAsync(base, active_ids, ids_bytes, cudaMemcpyHostToDevice, h->stream));
             AB_TRY(ab_ensure_slot_map(h));
             slots = (int32_t*)(base + o1);
+            ids_dev = (const int64_t*)base;
             AB_LAUNCH(h, "k_ids_to_slots");
             k_ids_to_slots<<<ab_blocks(na, 256), 256, 0, h->stream>>>((const int64_t*)base, h->slot_of_id, (int)h->n, na, slots, h->d_err);
         }
@@ -237,11 +293,22 @@ static int move_common(ab_handle* h, double dt, const void* directions, const in
             dir_dev = base + o2;
             AB_CUDA(h, cudaMemcpyAsync(dir_dev, directions, dir_bytes, cudaMemcpyHostToDevice, h->stream));
         }
+        if (rw && na > 0) dir_dev = base + o2;
     }
-    if (directions && !active_ids) {
+    if ((directions || rw) && !active_ids) {
         // directions are given in id order: address slots through the id→slot map
         AB_TRY(ab_ensure_slot_map(h));
         slots = h->slot_of_id;
+    }
+    if (rw && na > 0) {
+        AB_LAUNCH(h, "k_rw_dirs");
+        const int nb = (int)ab_blocks(na, 256);
+        void* vel = h->fields[1].buf[h->cur];
+#define RWD(T, DD) k_rw_dirs<T, DD><<<nb, 256, 0, h->stream>>>((T*)vel, h->cap, (int)h->n, slots, ids_dev, na, *rw, (T*)dir_dev, h->d_err)
+        if (h->dtype == AB_F64) { if (h->D == 2) RWD(double, 2); else RWD(double, 3); }
+        else { if (h->D == 2) RWD(float, 2); else RWD(float, 3); }
+#undef RWD
+        h->agg_valid = false;                                 // Σ vel per cell changed
     }
     int rc;
     if (h->dtype == AB_F64) rc = h->D == 2 ? move_t<double, 2>(h, dt, dir_dev, slots, na) : move_t<double, 3>(h, dt, dir_dev, slots, na);
@@ -250,7 +317,7 @@ static int move_common(ab_handle* h, double dt, const void* directions, const in
     h->index_valid = false;
     h->pairs_n = -1;
     int e = ab_check_device_errors(h);
-    if (e == AB_ERR_INVALID) return ab_fail(h, AB_ERR_INVALID, "agent id out of range");
+    if (e == AB_ERR_INVALID && !rw) return ab_fail(h, AB_ERR_INVALID, "agent id out of range");
     return e;
 }
 
@@ -501,6 +568,14 @@ int ab_walk(ab_handle* h, const void* directions, const int64_t* active_ids, int
     }
     if (!directions) return ab_fail(h, AB_ERR_INVALID, "null directions");
     return move_common(h, 0.0, directions, active_ids, nactive);
+}
+
+int ab_randomwalk(ab_handle* h, double r, uint64_t seed, const int64_t* active_ids, int64_t nactive, int ifempty,
+                  int force_motion) {
+    if (h->desc.kind != AB_SPACE_CONTINUOUS) return ab_grid_randomwalk(h, r, seed, active_ids, nactive, ifempty, force_motion);
+    if (r == 0.0) return ab_fail(h, AB_ERR_INVALID, "ArgumentError: The displacement must be larger than 0.");
+    RwArgs rw{r, seed};                                       // r < 0: the agent's own speed
+    return move_common(h, 0.0, nullptr, active_ids, nactive, &rw);
 }
 
 int ab_step_flock(ab_handle* h, const ab_flock_params* p, int64_t nsteps) {

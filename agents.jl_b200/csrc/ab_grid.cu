@@ -373,8 +373,138 @@ __global__ void k_copy_counts(const uint32_t* __restrict__ cs, int64_t ncells, i
     if (i < ncells) occ[i] = (int32_t)(cs[i + 1] - cs[i]);
 }
 
+// randomwalk!(agent, model::ABM{<:AbstractGridSpace}, r; ifempty, force_motion) — src/spaces/walk.jl:154-214.
+// Without force_motion the step is one uniformly chosen entry of offsets_at_radius(model, r)
+// (grid_general.jl:119-136), then the ordinary walk!: the directions are drawn in parallel (draw 0 of the
+// agent's counter stream) and handed to the walk kernels above.  With force_motion the choice is made among
+// the EMPTY targets (random_empty_pos_in_offsets, walk.jl:200-214): up to 2L random probes (draws 0..2L-1),
+// then one uniform pick (draw 2L) among the empty targets in table order; the agent stays when there is none.
+// Emptiness depends on the walks before it, so that form runs in the sequential replay like walk!(ifempty).
+// The reference hands the chosen POSITION to walk! as if it were a direction (walk.jl:170, :193); the device
+// rule implements the documented behaviour — the agent moves to the chosen empty position.
+struct GridRw {
+    const int32_t* offs;     // L x D offsets at radius, table order of the reference (first dimension fastest)
+    int L;
+    uint64_t seed;
+};
+
+template <int D>
+__global__ void k_grw_dirs(int n, const int64_t* __restrict__ ids, int nactive, GridRw rw, int32_t* __restrict__ dirs) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nactive) return;
+    const int64_t id = ids ? ids[t] : (int64_t)t + 1;
+    int j = (int)floor(ab_rw_u01(rw.seed, id, 0) * (double)rw.L);
+    j = min(j, rw.L - 1);
+#pragma unroll
+    for (int d = 0; d < D; ++d) dirs[(size_t)t * D + d] = rw.offs[(size_t)j * D + d];
+}
+
+template <int D, bool SINGLE>
+__global__ void k_grw_force_seq(GridDev<D> g, int32_t* __restrict__ pos, int64_t cap, int n, const int64_t* __restrict__ ids,
+                                int nactive, GridRw rw, int32_t* __restrict__ occ, int* __restrict__ err) {
+    if (blockIdx.x != 0 || threadIdx.x != 0) return;
+    for (int t = 0; t < nactive; ++t) {
+        int i = t;
+        if (ids) {
+            const int64_t id = ids[t];
+            if (id < 1 || id > n) { atomicOr(err, AB_EF_OVERFLOW); continue; }
+            i = (int)id - 1;
+        }
+        int c0[D], c1[D];
+#pragma unroll
+        for (int d = 0; d < D; ++d) c0[d] = pos[(size_t)d * cap + i] - 1;
+        auto target = [&](int j) {
+#pragma unroll
+            for (int d = 0; d < D; ++d) c1[d] = grid_norm(c0[d] + 1 + rw.offs[(size_t)j * D + d], g.dims[d], g.periodic[d]) - 1;
+            return lin_cell<D>(g.dims, c1);
+        };
+        bool found = false;
+        uint32_t k1 = 0;
+        for (int a = 0; a < 2 * rw.L && !found; ++a) {
+            int j = (int)floor(ab_rw_u01(rw.seed, i + 1, (uint32_t)a) * (double)rw.L);
+            j = min(j, rw.L - 1);
+            k1 = target(j);
+            found = occ[k1] == 0;
+        }
+        if (!found) {
+            int cnt = 0;
+            for (int j = 0; j < rw.L; ++j) cnt += occ[target(j)] == 0 ? 1 : 0;
+            if (cnt == 0) continue;                                       // nothing empty around: the agent stays
+            int pick = (int)floor(ab_rw_u01(rw.seed, i + 1, (uint32_t)(2 * rw.L)) * (double)cnt);
+            pick = min(pick, cnt - 1);
+            for (int j = 0; j < rw.L; ++j) {
+                k1 = target(j);
+                if (occ[k1] == 0 && pick-- == 0) break;
+            }
+        }
+        const uint32_t k0 = lin_cell<D>(g.dims, c0);
+        if (SINGLE) { occ[k0] = 0; occ[k1] = i + 1; }
+        else { occ[k0] -= 1; occ[k1] += 1; }
+#pragma unroll
+        for (int d = 0; d < D; ++d) pos[(size_t)d * cap + i] = c1[d] + 1;
+    }
+}
+
+// offsets_at_radius(space, r) — grid_general.jl:119-136 over calculate_offsets (:138-151) and the
+// periodicity-aware hyperrectangle (:47-89)
+static int host_offsets_at_radius(ab_handle* h, double r, std::vector<int32_t>* out) {
+    const int D = h->D;
+    const double fr = floor(r + 1.0) - 1.0;
+    if (!(fr >= 0.0) || fr > 30000.0) return ab_fail(h, AB_ERR_INVALID, "bad random-walk radius");
+    const int64_t r0 = (int64_t)fr;
+    bool notover = true;
+    for (int d = 0; d < D; ++d) notover = notover && (h->desc.periodic[d] ? r0 < h->dims[d] / 2 : r0 < h->dims[d]);
+    int64_t lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
+    for (int d = 0; d < D; ++d) {
+        if (notover) { lo[d] = -r0; hi[d] = r0; }
+        else if (h->desc.periodic[d]) {
+            const int64_t half = h->dims[d] / 2, rm = std::min<int64_t>(r0, half);
+            lo[d] = -rm;
+            hi[d] = rm - ((rm == half && h->dims[d] % 2 == 0) ? 1 : 0);
+        } else {
+            const int64_t rm = std::min<int64_t>(r0, h->dims[d]);
+            lo[d] = -rm; hi[d] = rm;
+        }
+    }
+    out->clear();
+    for (int64_t z = lo[2]; z <= hi[2]; ++z)
+        for (int64_t y = lo[1]; y <= hi[1]; ++y)
+            for (int64_t x = lo[0]; x <= hi[0]; ++x) {
+                const int64_t b[3] = {x, y, z};
+                int64_t l1 = 0, linf = 0;
+                for (int d = 0; d < D; ++d) { l1 += std::llabs(b[d]); linf = std::max<int64_t>(linf, std::llabs(b[d])); }
+                const bool keep = h->desc.metric == AB_METRIC_MANHATTAN ? l1 == r0 : linf == r0;
+                if (!keep) continue;
+                if (out->size() / D >= 60000) return ab_fail(h, AB_ERR_INVALID, "random-walk radius too large");
+                for (int d = 0; d < D; ++d) out->push_back((int32_t)b[d]);
+            }
+    if (out->empty()) return ab_fail(h, AB_ERR_INVALID, "ArgumentError: no offsets at this radius");
+    return AB_OK;
+}
+
+static int grid_walk_impl(ab_handle* h, const void* directions, const int64_t* active_ids, int64_t nactive, int ifempty,
+                          const std::vector<int32_t>* rw_offs, uint64_t rw_seed, bool rw_force);
+
 int ab_grid_walk(ab_handle* h, const void* directions, const int64_t* active_ids, int64_t nactive, int ifempty) {
     if (!directions) return ab_fail(h, AB_ERR_INVALID, "null directions");
+    return grid_walk_impl(h, directions, active_ids, nactive, ifempty, nullptr, 0, false);
+}
+
+int ab_grid_randomwalk(ab_handle* h, double r, uint64_t seed, const int64_t* active_ids, int64_t nactive, int ifempty,
+                       int force_motion) {
+    if (h->desc.metric == AB_METRIC_EUCLIDEAN)
+        return ab_fail(h, AB_ERR_INVALID, "ArgumentError: Random walks on a `GridSpace` with Euclidean metric are not defined.");
+    std::vector<int32_t> offs;
+    AB_TRY(host_offsets_at_radius(h, r, &offs));
+    const bool single = h->desc.kind == AB_SPACE_GRID_SINGLE;
+    if (single) ifempty = 1;                                              // no effect on GridSpaceSingle (walk.jl:141-143)
+    const bool force = force_motion && (single || ifempty);              // walk.jl:165, :189
+    if (!active_ids) nactive = h->n;
+    return grid_walk_impl(h, nullptr, active_ids, nactive, ifempty, &offs, seed, force);
+}
+
+static int grid_walk_impl(ab_handle* h, const void* directions, const int64_t* active_ids, int64_t nactive, int ifempty,
+                          const std::vector<int32_t>* rw_offs, uint64_t rw_seed, bool rw_force) {
     if (nactive < 0) return ab_fail(h, AB_ERR_INVALID, "negative nactive");
     const int na = active_ids ? (int)nactive : (int)h->n;
     if (!active_ids && nactive != h->n && nactive != 0) return ab_fail(h, AB_ERR_INVALID, "directions for all agents need nactive == n");
@@ -388,19 +518,45 @@ int ab_grid_walk(ab_handle* h, const void* directions, const int64_t* active_ids
     const size_t dir_bytes = (size_t)na * h->D * sizeof(int32_t);
     const size_t o2 = o1 + (dir_bytes + 255) / 256 * 256;
     const size_t occ_bytes = (seq && !single) ? (size_t)h->ncells * sizeof(int32_t) : 0;
+    const size_t o3 = o2 + (occ_bytes + 255) / 256 * 256;
+    const size_t offs_bytes = rw_offs ? rw_offs->size() * sizeof(int32_t) : 0;
     char* base;
-    AB_TRY(ab_scratch(h, o2 + occ_bytes + 256, (void**)&base));
+    AB_TRY(ab_scratch(h, o3 + offs_bytes + 256, (void**)&base));
     if (active_ids) AB_CUDA(h, cudaMemcpyAsync(base, active_ids, ids_bytes, cudaMemcpyHostToDevice, h->stream));
-    AB_CUDA(h, cudaMemcpyAsync(base + o1, directions, dir_bytes, cudaMemcpyHostToDevice, h->stream));
     const int64_t* ids = active_ids ? (const int64_t*)base : nullptr;
     const int32_t* dirs = (const int32_t*)(base + o1);
+    GridRw rw{nullptr, 0, rw_seed};
+    if (rw_offs) {
+        // the table lives in a vector of the caller: the copy is complete before this function returns
+        // (ab_check_device_errors below synchronises; in asynchronous mode synchronise here)
+        AB_CUDA(h, cudaMemcpyAsync(base + o3, rw_offs->data(), offs_bytes, cudaMemcpyHostToDevice, h->stream));
+        if (h->async_mode) AB_CUDA(h, cudaStreamSynchronize(h->stream));
+        rw.offs = (const int32_t*)(base + o3);
+        rw.L = (int)(rw_offs->size() / h->D);
+        if (!rw_force) {
+            AB_LAUNCH(h, "k_grw_dirs");
+            if (h->D == 2) k_grw_dirs<2><<<ab_blocks(na, 256), 256, 0, h->stream>>>((int)h->n, ids, na, rw, (int32_t*)(base + o1));
+            else k_grw_dirs<3><<<ab_blocks(na, 256), 256, 0, h->stream>>>((int)h->n, ids, na, rw, (int32_t*)(base + o1));
+        }
+    } else {
+        AB_CUDA(h, cudaMemcpyAsync(base + o1, directions, dir_bytes, cudaMemcpyHostToDevice, h->stream));
+    }
     int32_t* pos = (int32_t*)h->fields[0].buf[h->cur];
     int32_t* occ = single ? h->grid_ids : (int32_t*)(base + o2);
     if (seq && !single) {
         AB_LAUNCH(h, "k_copy_counts");
         k_copy_counts<<<ab_blocks(h->ncells, 256), 256, 0, h->stream>>>(h->cell_start, h->ncells, occ);
     }
-    {
+    if (rw_force) {
+        AB_LAUNCH(h, "k_grw_force_seq");
+        if (h->D == 2) {
+            if (single) k_grw_force_seq<2, true><<<1, 32, 0, h->stream>>>(make_grid<2>(h), pos, h->cap, (int)h->n, ids, na, rw, occ, h->d_err);
+            else k_grw_force_seq<2, false><<<1, 32, 0, h->stream>>>(make_grid<2>(h), pos, h->cap, (int)h->n, ids, na, rw, occ, h->d_err);
+        } else {
+            if (single) k_grw_force_seq<3, true><<<1, 32, 0, h->stream>>>(make_grid<3>(h), pos, h->cap, (int)h->n, ids, na, rw, occ, h->d_err);
+            else k_grw_force_seq<3, false><<<1, 32, 0, h->stream>>>(make_grid<3>(h), pos, h->cap, (int)h->n, ids, na, rw, occ, h->d_err);
+        }
+    } else {
         AB_LAUNCH(h, seq ? "k_gwalk_seq" : "k_gwalk_all");
         if (h->D == 2) {
             if (!seq) k_gwalk_all<2><<<ab_blocks(na, 256), 256, 0, h->stream>>>(make_grid<2>(h), pos, h->cap, (int)h->n, ids, na, dirs, h->d_err);

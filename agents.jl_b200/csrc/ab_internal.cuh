@@ -36,7 +36,21 @@
 #define AB_VERSION 100
 
 #define AB_SCH_EMPTY INT32_MIN
-enum { AB_EF_OUTSIDE = 1, AB_EF_NUMERIC = 2, AB_EF_OCCUPIED = 4, AB_EF_OVERFLOW = 8, AB_EF_COMM = 16 };
+enum { AB_EF_OUTSIDE = 1, AB_EF_NUMERIC = 2, AB_EF_OCCUPIED = 4, AB_EF_OVERFLOW = 8, AB_EF_COMM = 16, AB_EF_ARG = 32 };
+
+// Counter-based random stream of the bulk randomwalk! calls (the reference draws from the model's RNG,
+// src/spaces/walk.jl:154-214, 389-408; its stream is not reproduced — SURVEY §8c(iv) — so the device rule is
+// defined on a counter: draw c of agent `id` under `seed` is u = (splitmix64(seed ^ ((id << 16) + c)) >> 11) * 2^-53.
+__host__ __device__ __forceinline__ uint64_t ab_splitmix64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ull;
+    uint64_t z = x;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+__host__ __device__ __forceinline__ double ab_rw_u01(uint64_t seed, int64_t id, uint32_t c) {
+    return (double)(ab_splitmix64(seed ^ (((uint64_t)id << 16) + c)) >> 11) * (1.0 / 9007199254740992.0);
+}
 
 struct ab_field {
     std::string name;
@@ -118,6 +132,7 @@ struct ab_handle {
 
     int* d_err = nullptr;              // device error flag word
     int* h_err = nullptr;              // pinned mirror
+    const int32_t* place_prio = nullptr;   // ab_layout_set: in-cell order of a restored checkpoint (rank per id)
 
     void* scratch = nullptr;           // grow-only device scratch for uploads / queries
     size_t scratch_bytes = 0;
@@ -209,6 +224,7 @@ int ab_grid_build(ab_handle* h);
 int ab_grid_sync_columns(ab_handle* h);   // cell-major Schelling state -> agent columns (pos, mood)
 void ab_grid_free(ab_handle* h);
 int ab_grid_walk(ab_handle* h, const void* directions, const int64_t* active_ids, int64_t nactive, int ifempty);
+int ab_grid_randomwalk(ab_handle* h, double r, uint64_t seed, const int64_t* active_ids, int64_t nactive, int ifempty, int force_motion);
 int ab_grid_nearby(ab_handle* h, const void* qpos, const int64_t* qids, int64_t nq, double r, int exclude_self,
                    int64_t* counts, const int64_t* offsets, int64_t* ids_out);
 

@@ -408,6 +408,18 @@ class StandardABM:
         a = np.ascontiguousarray(ids, dtype=np.int64) if ids is not None else None
         self._ck(self.lib.ab_walk(self.h, self._ptr(d), self._ptr(a), d.shape[0] if a is None else a.shape[0], int(ifempty)))
 
+    def randomwalk(self, r=None, seed=0, ids=None, ifempty=True, force_motion=False):
+        """randomwalk!(agent, model, r; ifempty, force_motion) for `ids` (all agents when None) — walk.jl:154-214 on
+        grids (r defaults to 1), walk.jl:389-408 on a ContinuousSpace (r defaults to the agent's speed).  `seed`
+        selects the counter stream of this call (see ab_randomwalk in include/agents_b200.h)."""
+        if r is None:
+            r = -1.0 if isinstance(self.space, ContinuousSpace) else 1.0
+        elif isinstance(self.space, ContinuousSpace) and r <= 0:
+            raise AgentsError(-1, "ArgumentError: The displacement must be larger than 0.")
+        a = np.ascontiguousarray(ids, dtype=np.int64) if ids is not None else None
+        self._ck(self.lib.ab_randomwalk(self.h, float(r), int(seed) & 0xFFFFFFFFFFFFFFFF, self._ptr(a),
+                                        0 if a is None else a.shape[0], int(ifempty), int(force_motion)))
+
     # -- stepping (src/simulations/step_standard.jl:24-31) --------------------
     def step(self, n=1):
         if self.model_step is None:
@@ -472,6 +484,48 @@ class StandardABM:
                 take()
         return cols
 
+    # -- checkpoints (AgentsIO, src/submodules/io/jld2_integration.jl:85-135, 196-223) ----------
+    def save_checkpoint(self, path):
+        """AgentsIO.save_checkpoint(filename, model): every column in id order, the space, the rule, the model
+        properties, the time, and the device layout a bit-for-bit continuation needs (ab_layout_get: the order of
+        the agents inside the cells — the reference's stored_ids — the grid refinement, the relocation counter).
+        Written as one .npz; properties must be JSON-serialisable, as JLD2 needs them serialisable."""
+        import json
+        n = self.nagents()
+        sp = self.space
+        rule = self.model_step
+        meta = {"format": "agents_b200-checkpoint-1", "time": int(self.time), "n": n, "properties": self.properties,
+                "space": {"kind": type(sp).__name__, "periodic": [bool(x) for x in sp.periodic], "metric": sp.metric},
+                "columns": [[name, str(self._dtypes[name]), int(self._ncomp[name])]
+                            for name, _ in sorted(self._columns.items(), key=lambda kv: kv[1])],
+                "rule": None}
+        if isinstance(sp, ContinuousSpace):
+            meta["space"].update(extent=list(sp.extent), spacing=sp.spacing, dtype=str(sp.dtype))
+        else:
+            meta["space"].update(dims=[int(x) for x in sp.dims])
+        arrays = {}
+        if isinstance(rule, FlockRule):
+            meta["rule"] = {"type": "FlockRule", "p": rule.p, "search": rule.search, "kernel": rule.kernel,
+                            "field": rule._field}
+            if rule.per_agent is not None and rule._field < 0:
+                arrays["rule_per_agent"] = np.asarray(rule.per_agent)
+        elif isinstance(rule, PairForceRule):
+            meta["rule"] = {"type": "PairForceRule", "dt": rule.dt, "cutoff": rule.cutoff}
+        elif isinstance(rule, SchellingRule):
+            meta["rule"] = {"type": "SchellingRule", "min_to_be_happy": rule.min_to_be_happy,
+                            "relocate": bool(rule.relocate), "seed": int(rule.seed)}
+        elif rule is not None:
+            raise TypeError("only the device rules can be checkpointed")
+        for name in self._columns:
+            arrays["col_" + name] = self.column(name)
+        order = np.zeros(n, dtype=np.int64)
+        K, tick = C.c_int32(1), C.c_int64(0)
+        self._ck(self.lib.ab_layout_get(self.h, self._ptr(order), n, C.byref(K), C.byref(tick)))
+        meta["refinement"], meta["tick"] = int(K.value), int(tick.value)
+        arrays["slot_order"] = order
+        with open(path, "wb") as f:
+            np.savez(f, meta=np.frombuffer(json.dumps(meta).encode(), dtype=np.uint8), **arrays)
+
     def last_neighbor_counts(self):
         n = self.nagents()
         out = np.zeros(n, dtype=np.int32)
@@ -504,3 +558,43 @@ class StandardABM:
 
     def last_step_ms(self):
         return float(self.lib.ab_last_step_ms(self.h))
+
+
+def load_checkpoint(path, device=0):
+    """AgentsIO.load_checkpoint(filename) (jld2_integration.jl:196-223): a StandardABM on `device` whose state, rule,
+    properties and time equal the saved model's, and whose continuation equals the uninterrupted run bit for bit."""
+    import json
+    with np.load(path, allow_pickle=False) as z:
+        meta = json.loads(bytes(z["meta"]).decode())
+        if meta.get("format") != "agents_b200-checkpoint-1":
+            raise ValueError("not a checkpoint of this library")
+        arrays = {k: z[k] for k in z.files if k != "meta"}
+    sm = meta["space"]
+    if sm["kind"] == "ContinuousSpace":
+        space = ContinuousSpace(sm["extent"], spacing=sm["spacing"], periodic=tuple(sm["periodic"]), dtype=np.dtype(sm["dtype"]))
+    else:
+        space = {"GridSpace": GridSpace, "GridSpaceSingle": GridSpaceSingle}[sm["kind"]](
+            tuple(sm["dims"]), periodic=tuple(sm["periodic"]), metric=sm["metric"])
+    rm, rule = meta["rule"], None
+    if rm is not None:
+        if rm["type"] == "FlockRule":
+            kern = {0: "auto", 1: "generic", 2: "tiled"}[rm["kernel"]]
+            rule = FlockRule(search=rm["search"], kernel=kern, per_agent=arrays.get("rule_per_agent"), **rm["p"])
+        elif rm["type"] == "PairForceRule":
+            rule = PairForceRule(dt=rm["dt"], cutoff=rm["cutoff"])
+        else:
+            rule = SchellingRule(min_to_be_happy=rm["min_to_be_happy"], relocate=rm["relocate"], seed=rm["seed"])
+    m = StandardABM(space, model_step=rule, properties=meta["properties"], device=device)
+    n = meta["n"]
+    vel = arrays.get("col_vel")
+    m.add_agents(arrays["col_pos"].reshape(n, space.D), None if vel is None else vel.reshape(n, space.D))
+    for name, _, _ in meta["columns"]:                       # registration order = field ids of the saved model
+        if name not in ("pos", "vel"):
+            m.add_column(name, arrays["col_" + name])
+    if rm is not None and rm["type"] == "FlockRule" and rm["field"] >= 0:
+        rule._field = m.field_id("_flock_params")
+        rule.per_agent = arrays["col__flock_params"]
+    m._ck(m.lib.ab_layout_set(m.h, m._ptr(np.ascontiguousarray(arrays["slot_order"], dtype=np.int64)), n,
+                              int(meta["refinement"]), int(meta["tick"])))
+    m.time = int(meta["time"])
+    return m

@@ -136,6 +136,16 @@ int ab_build_index(ab_handle* h);
  * (default 1; the fused steps pick it themselves).  A pure layout choice —
  * neighbour sets and cells are defined on the reference cells either way. */
 int ab_set_refinement(ab_handle* h, int K);
+/* Checkpoint support: AgentsIO.save_checkpoint / load_checkpoint (src/submodules/io/jld2_integration.jl:85-135,
+ * :196-223) serialise the agents AND the space's stored_ids (the order of the agents inside every cell), so a
+ * restored model continues exactly.  The columns travel through ab_download / ab_upload; these two calls carry the
+ * rest of the device state a bit-for-bit continuation needs: the slot order (1-based ids in device order; on grid
+ * handles 1..n), the device-grid refinement and the step counter that decorrelates the Schelling relocations.
+ * ab_layout_set is called after the columns of the restored model have been uploaded; it rebuilds the index with
+ * the agents of every cell in the saved order. */
+int ab_layout_get(ab_handle* h, int64_t* slot_ids, int64_t n, int32_t* refinement, int64_t* tick);
+int ab_layout_set(ab_handle* h, const int64_t* slot_ids, int64_t n, int32_t refinement, int64_t tick);
+
 /* pos2cell for every agent, id order, n x D int32, 1-based (continuous.jl:112-113) */
 int ab_cells(ab_handle* h, int32_t* out_cells, int64_t n);
 
@@ -205,6 +215,19 @@ int ab_move(ab_handle* h, double dt, const int64_t* active_ids, int64_t nactive)
 /* walk!(agent, direction, model): per-agent displacement, nactive x D of T
  * (continuous) or int32 (grids, walk.jl:33-56 with ifempty). */
 int ab_walk(ab_handle* h, const void* directions, const int64_t* active_ids, int64_t nactive, int ifempty);
+/* randomwalk!(agent, model, r) for the agents of `active_ids` (all when NULL), src/spaces/walk.jl:154-214 (grids)
+ * and :389-408 (ContinuousSpace, uniform_randomwalk!).  The reference draws from the model's RNG; its stream is not
+ * reproduced: draw c of agent id is u = (splitmix64(seed ^ ((id << 16) + c)) >> 11) * 2^-53, so a call is a pure
+ * function of (state, seed) and the caller passes a fresh seed per tick.
+ *   ContinuousSpace: direction = v / |v| * r with v = D standard normals (Box-Muller on draws 0..3); r < 0 takes
+ *     the agent's own speed (the reference's default r); vel = direction; then walk!.  r == 0 (or a resting agent
+ *     with the default r) fails with AB_ERR_INVALID like the reference's ArgumentError.  ifempty / force_motion ignored.
+ *   GridSpace / GridSpaceSingle: one entry of offsets_at_radius(model, r) (grid_general.jl:119-136; floor(r) steps under
+ *     :chebyshev / :manhattan, :euclidean fails with AB_ERR_INVALID), index floor(u0 * L); with force_motion (and
+ *     ifempty, or a GridSpaceSingle) the choice is made among the empty targets (walk.jl:200-214) in the sequential
+ *     order of `active_ids`, and the agent moves to the chosen empty position. */
+int ab_randomwalk(ab_handle* h, double r, uint64_t seed, const int64_t* active_ids, int64_t nactive, int ifempty,
+                  int force_motion);
 
 /* ---- fused rules (synchronous update) ---------------
  * step!(model, n) with a B200Step model_step! (step_standard.jl:24-31). */

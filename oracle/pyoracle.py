@@ -428,3 +428,103 @@ class GridOracle:
         if lib().orc_schelling_step_async(self.h, _p(g), int(min_to_be_happy), _p(mood), C.c_uint64(seed), C.c_int64(nsteps)):
             raise OracleError(self._err())
         return mood
+
+
+# ---------------------------------------------------------------------------
+# randomwalk! — src/spaces/walk.jl:154-214 (grids), :389-408 (uniform_randomwalk!).  The reference draws from the
+# model RNG; the counter stream below is the one the device rule is defined on (include/agents_b200.h,
+# ab_randomwalk), so the oracle and the device see the same random numbers.
+# ---------------------------------------------------------------------------
+_M64 = (1 << 64) - 1
+
+
+def _splitmix64_int(x):
+    x = (x + 0x9E3779B97F4A7C15) & _M64
+    z = x
+    z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & _M64
+    z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & _M64
+    return z ^ (z >> 31)
+
+
+def rw_u01(seed, id, c):
+    return (_splitmix64_int((seed ^ (((id << 16) + c) & _M64)) & _M64) >> 11) * 2.0 ** -53
+
+
+def grid_offsets_at_radius(dims, periodic, metric, r):
+    """offsets_at_radius(space, r) — grid_general.jl:119-136."""
+    r0 = int(np.floor(r + 1)) - 1
+    offs = grid_offsets(dims, periodic, metric, r)
+    if metric == "manhattan":
+        keep = np.abs(offs).sum(axis=1) == r0
+    elif metric == "chebyshev":
+        keep = np.abs(offs).max(axis=1) == r0
+    else:
+        raise OracleError("Random walks on a `GridSpace` with Euclidean metric are not defined.")
+    return offs[keep]
+
+
+def grid_randomwalk(o, ids, r, seed, ifempty=True, force_motion=False):
+    """randomwalk!(agent, model, r; ifempty, force_motion) agent after agent on a GridOracle (walk.jl:154-214).
+    With force_motion the agent moves TO the chosen empty position (the documented behaviour; the reference
+    passes that position on to walk! as a direction, walk.jl:170 / :193)."""
+    offs = grid_offsets_at_radius(o.dims, o.periodic, o.metric, r)
+    L = len(offs)
+    dims = np.asarray(o.dims, dtype=np.int64)
+    per = _periodic(o.periodic, o.D)
+
+    def norm(p):
+        return tuple(int((x - 1) % s + 1) if pd else int(min(max(x, 1), s)) for x, s, pd in zip(p, dims, per))
+
+    force = force_motion and (o.single or ifempty)
+    occ = {}
+    cur = [tuple(int(x) for x in p) for p in o.positions()]
+    for p in cur:
+        occ[p] = occ.get(p, 0) + 1
+    for id in ids:
+        p = cur[id - 1]
+        if not force:
+            j = min(int(np.floor(rw_u01(seed, id, 0) * L)), L - 1)
+            tgt = norm(np.add(p, offs[j]))
+            if (o.single or ifempty) and occ.get(tgt, 0) != 0:
+                continue
+        else:
+            tgt = None
+            for a in range(2 * L):
+                j = min(int(np.floor(rw_u01(seed, id, a) * L)), L - 1)
+                t = norm(np.add(p, offs[j]))
+                if occ.get(t, 0) == 0:
+                    tgt = t
+                    break
+            if tgt is None:
+                empties = [t for t in (norm(np.add(p, b)) for b in offs) if occ.get(t, 0) == 0]
+                if not empties:
+                    continue
+                tgt = empties[min(int(np.floor(rw_u01(seed, id, 2 * L) * len(empties))), len(empties) - 1)]
+        o.move_agent_to(id, tgt)
+        occ[p] -= 1
+        occ[tgt] = occ.get(tgt, 0) + 1
+        cur[id - 1] = tgt
+
+
+def continuous_randomwalk_directions(vel, ids, r, seed, dtype=np.float64):
+    """direction of uniform_randomwalk!(agent, model, r) (walk.jl:389-408) for each id; r=None: the agent's speed."""
+    T = np.dtype(dtype).type
+    D = vel.shape[1]
+    out = np.zeros((len(ids), D), dtype=dtype)
+    for k, id in enumerate(ids):
+        rr = float(np.sqrt(np.sum(vel[id - 1].astype(dtype) ** 2, dtype=dtype))) if r is None else float(r)
+        if not rr > 0:
+            raise OracleError("The displacement must be larger than 0.")
+        v = np.zeros(D, dtype=dtype)
+        for pr in range((D + 1) // 2):
+            u1, u2 = rw_u01(seed, id, 2 * pr), rw_u01(seed, id, 2 * pr + 1)
+            R, a = np.sqrt(-2.0 * np.log(1.0 - u1)), 6.283185307179586 * u2
+            v[2 * pr] = T(R * np.cos(a))
+            if 2 * pr + 1 < D:
+                v[2 * pr + 1] = T(R * np.sin(a))
+        nv = T(np.sqrt(np.sum(v * v, dtype=dtype)))
+        if nv != 0:
+            out[k] = ((v / nv).astype(np.float64) * rr).astype(dtype)
+        else:
+            out[k] = [(-1.0 if rw_u01(seed, id, 8 + d) < 0.5 else 1.0) * rr / np.sqrt(float(D)) for d in range(D)]
+    return out

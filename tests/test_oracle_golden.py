@@ -428,3 +428,40 @@ def test_schelling_happiness_small():
     cnt, mood = g.schelling_happiness(grp, 2)
     assert list(cnt) == [2, 2, 2, 1, 2, 1]
     assert list(mood) == [1, 1, 1, 0, 1, 0]
+
+
+def test_randomwalk_restatement_reference_scenarios():
+    # test/grid_space_tests.jl:407-431, 462-489 on the oracle's restatement of randomwalk! (walk.jl:154-214)
+    from oracle.pyoracle import grid_offsets_at_radius, grid_randomwalk
+    assert len(grid_offsets_at_radius((20, 20), True, "chebyshev", 1)) == 8
+    assert len(grid_offsets_at_radius((20, 20), True, "manhattan", 1)) == 4
+    assert len(grid_offsets_at_radius((20, 20, 20), False, "chebyshev", 1)) == 26
+    for metric, r in (("chebyshev", 1), ("manhattan", 1), ("chebyshev", 3), ("manhattan", 2)):
+        g = GridOracle((100, 100), periodic=True, metric=metric)
+        g.add_agents([(50, 50)])
+        for k in range(20):
+            p0 = g.positions()[0]
+            grid_randomwalk(g, [1], r, k)
+            d = np.abs(g.positions()[0] - p0)
+            assert (d.max() if metric == "chebyshev" else d.sum()) == r
+    ring = [(49, 49), (50, 49), (51, 49), (49, 50), (51, 50), (49, 51), (50, 51), (51, 51)]
+    for single in (True, False):
+        g = GridOracle((100, 100), periodic=True, metric="chebyshev", single=single)
+        g.add_agents([(50, 50), (49, 50)] + [p for p in ring if p != (49, 50)])
+        grid_randomwalk(g, [1], 1, 1, True, True)
+        assert tuple(g.positions()[0]) == (50, 50)
+        grid_randomwalk(g, [2], 1, 2, True, True)
+        assert tuple(g.positions()[1]) != (49, 50)
+        grid_randomwalk(g, [1], 1, 3, True, True)
+        assert tuple(g.positions()[0]) == (49, 50)
+
+
+def test_randomwalk_continuous_restatement():
+    # walk.jl:389-408: |direction| == r, isotropic (mean of many directions near zero)
+    from oracle.pyoracle import continuous_randomwalk_directions
+    vel = np.ones((4000, 2))
+    d = continuous_randomwalk_directions(vel, list(range(1, 4001)), 0.5, 11)
+    assert np.allclose(np.sqrt((d ** 2).sum(axis=1)), 0.5, rtol=1e-14)
+    assert np.abs(d.mean(axis=0)).max() < 0.03
+    d2 = continuous_randomwalk_directions(vel, [1, 2], None, 11)
+    assert np.allclose(np.sqrt((d2 ** 2).sum(axis=1)), np.sqrt(2.0), rtol=1e-14)
