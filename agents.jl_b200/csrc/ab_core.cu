@@ -151,6 +151,7 @@ k_scan(uint32_t* __restrict__ count, uint32_t* __restrict__ start, uint32_t n, u
     __shared__ uint32_t s_red[SCAN_THREADS / 32];
     __shared__ int s_first[SCAN_THREADS / 32];
     __shared__ uint32_t s_excl;
+    ab_dep_wait();
     if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
     __syncthreads();
     const uint32_t tile = s_tile;
@@ -324,7 +325,7 @@ int ab_scan_u32(ab_handle* h, uint32_t* count, uint32_t* start, uint32_t n) {
         h->scan_epoch = 1;
     }
     AB_LAUNCH(h, "k_scan");
-    k_scan<<<ntiles, SCAN_THREADS, 0, h->stream>>>(count, start, n, ntiles, h->scan_status, h->scan_ticket, h->scan_epoch);
+    AB_CUDA(h, ab_launch_chain(h->pdl, k_scan, dim3(ntiles), dim3(SCAN_THREADS), h->stream, count, start, n, ntiles, h->scan_status, h->scan_ticket, h->scan_epoch));
     return AB_OK;
 }
 int ab_run_scan(ab_handle* h, uint32_t* dst) { return ab_scan_u32(h, h->cell_count, dst, (uint32_t)h->nfine); }
@@ -475,6 +476,7 @@ int ab_create(ab_space_desc* desc, int device, ab_handle** out) {
     ab_handle* h = new ab_handle();
     h->device = device;
     if (const char* e = getenv("AB_OVERLAP")) h->overlap_halo = atoi(e) != 0;
+    if (const char* e = getenv("AB_PDL")) h->pdl = atoi(e) != 0;
     if (const char* e = getenv("AB_FINE4")) h->fine4 = atoi(e) != 0;     // A/B experiments
     if (const char* e = getenv("AB_RS_TARGET")) { int v = atoi(e); if (v >= 4 && v <= 2048) h->rs_target = v; }   // tuning experiments
     h->D = desc->D;

@@ -355,15 +355,15 @@ static int launch_cell_M(ab_handle* h, const SpaceDev<T, D>& sp, int part = 0) {
         }
         {
             AB_LAUNCH(h, "k_agg_collapse");
-            k_agg_collapse<T><<<ab_blocks(total, 256), 256, 0, h->stream>>>(aggp, total, (T*)h->cell_agg1);
+            AB_CUDA(h, ab_launch_chain(h->pdl, k_agg_collapse<T>, dim3(ab_blocks(total, 256)), dim3(256), h->stream, aggp, total, (T*)h->cell_agg1));
         }
         aggp = (const T*)h->cell_agg1;
         nfr = 1;
     }
     AB_LAUNCH(h, "k_cell_M");
     const int64_t nwarps = (int64_t)rows * wpr;
-    k_cell_M<T, D><<<ab_blocks(nwarps * 32, 128), 128, 0, h->stream>>>(sp, aggp, (int64_t)h->ncells, wpr,
-                                                                       (int)nwarps, (T*)h->cell_M, skip0, skiplen, nfr);
+    AB_CUDA(h, ab_launch_chain(h->pdl, k_cell_M<T, D>, dim3(ab_blocks(nwarps * 32, 128)), dim3(128), h->stream, sp, aggp,
+                               (int64_t)h->ncells, wpr, (int)nwarps, (T*)h->cell_M, skip0, skiplen, nfr));
     return AB_OK;
 }
 
@@ -379,9 +379,12 @@ static int launch_fine(ab_handle* h, const SpaceDev<T, D>& sp, const FlockU<T>& 
         h->id[cur], ncount, h->d_err, h->win_W ? h->cell_start + h->nfine : nullptr, phase, own_keys
     bool done = false;
     if constexpr (!EXACT && D == 2) {
-        if (u.reach == 2) { k_flock_fine<T, D, false, true><<<ab_blocks(n, TB), TB, 0, h->stream>>>(FINE_ARGS); done = true; }
+        if (u.reach == 2) {
+            AB_CUDA(h, ab_launch_chain(h->pdl, k_flock_fine<T, D, false, true>, dim3(ab_blocks(n, TB)), dim3(TB), h->stream, FINE_ARGS));
+            done = true;
+        }
     }
-    if (!done) k_flock_fine<T, D, EXACT><<<ab_blocks(n, TB), TB, 0, h->stream>>>(FINE_ARGS);
+    if (!done) AB_CUDA(h, ab_launch_chain(h->pdl, k_flock_fine<T, D, EXACT, false>, dim3(ab_blocks(n, TB)), dim3(TB), h->stream, FINE_ARGS));
 #undef FINE_ARGS
     return AB_OK;
 }

@@ -75,6 +75,7 @@ __device__ __forceinline__ int wrap_coord(int c, int n, bool periodic) {
 // k_cell_M would use — so that its 13 (5) neighbour-row reads per cell touch a quarter of the data.
 template <class T>
 __global__ void k_agg_collapse(const T* __restrict__ aggp, int64_t total, T* __restrict__ out) {
+    ab_dep_wait();
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;       // total = NC * ncells
     if (t >= total) return;
     T v = aggp[t];
@@ -92,6 +93,7 @@ k_cell_M(SpaceDev<T, D> sp, const T* __restrict__ aggp, int64_t ncells, int wpr,
          int skip0, int skiplen, int nfr) {
     constexpr int NC = FineCfg<D>::NC;
     constexpr int NRO = D == 2 ? 5 : 13;
+    ab_dep_wait();
     const int warp = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     if (warp >= nwarps) return;
     const int lane = threadIdx.x & 31;
@@ -218,6 +220,7 @@ k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T
              int32_t* __restrict__ ncount, int* __restrict__ err, const uint32_t* __restrict__ nslots, int phase,
              uint32_t own_keys) {
     constexpr int NC = FineCfg<D>::NC;
+    ab_dep_wait();
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     // slab window: the slot count lives on the device (migration changes it without a host round trip).
     // phase 1 (interior layers, swept while the halo of this state may still be arriving): owned slots only —

@@ -120,6 +120,7 @@ struct ab_handle {
     size_t cell_M_bytes = 0;
     cudaStream_t stream2 = nullptr;    // side stream of the overlapped sharded step (halo install + boundary sweep)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    bool pdl = false;                  // programmatic dependent launch of the step kernels (AB_PDL=1)
     bool overlap_halo = false;         // sharded flock step: interior sweep while the halo travels — measured slower, AB_OVERLAP=1 enables
     bool fine4 = false;                // quarter-cell refinement (K = 4) on the 2-D flock path: correct, measured slower (AB_FINE4=1 enables)
     int rs_target = 100;               // average agents per re-sort tile (tuning knob)
@@ -241,6 +242,29 @@ struct ab_launch_scope {
 #define AB_LAUNCH(h, name) ab_launch_scope AB_CAT(_scope_, __LINE__)((h), (name))
 
 static inline int ab_blocks(int64_t n, int threads) { return (int)((n + threads - 1) / threads); }
+
+// Programmatic dependent launch for the kernels of the fused step (they form one dependency chain on one stream:
+// sweep -> scan -> re-sort -> aggregates -> sweep).  Every such kernel begins with ab_dep_wait(): nothing of it
+// touches memory before the kernel in front of it has completed and flushed, so the only thing that overlaps is
+// the launch itself and the residency of its first CTAs — the gap between two dependent kernels.
+__device__ __forceinline__ void ab_dep_wait() {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+template <class... KArgs, class... Args>
+static inline cudaError_t ab_launch_chain(bool pdl, void (*kern)(KArgs...), dim3 grid, dim3 block, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
 
 // ---------------------------------------------------------------------------
 // device-side space description and reference arithmetic

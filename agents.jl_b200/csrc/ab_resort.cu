@@ -69,6 +69,7 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, c
     __shared__ uint32_t s_pre[RS_WARPS][RS_MAXSEG + 1];
     __shared__ uint32_t s_cur[RS_WARPS][RS_TW_MAX];
 
+    ab_dep_wait();
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int tile = blockIdx.x * RS_WARPS + w;
@@ -395,10 +396,10 @@ static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool
     {
         AB_LAUNCH(h, "k_resort");
         constexpr int G = (D == 2) ? RS_G2D : 2;           // source chunks in flight per warp
-        k_resort<T, D, G><<<(a.ntiles + RS_WARPS - 1) / RS_WARPS, RS_THREADS, 0, h->stream>>>(
+        AB_CUDA(h, ab_launch_chain(h->pdl, k_resort<T, D, G>, dim3((a.ntiles + RS_WARPS - 1) / RS_WARPS), dim3(RS_THREADS), h->stream,
             sp, a, h->cell_start, h->newkey, h->id[cur], (const T*)src_pos, (const T*)src_vel, h->cap,
             (T*)h->fields[0].buf[nxt], (T*)h->fields[1].buf[nxt], h->id[nxt], h->key[nxt], h->cell_start_alt,
-            extra ? h->perm : nullptr, (T*)h->cell_agg, (int64_t)h->ncells, h->d_err);
+            extra ? h->perm : nullptr, (T*)h->cell_agg, (int64_t)h->ncells, h->d_err));
     }
     std::swap(h->cell_start, h->cell_start_alt);
     AB_TRY(ab_permute_extra_fields(h));
