@@ -15,7 +15,7 @@ value  : agents*steps / device time of ONE step!(model, K) call after W warm-up
          max over ranks; the per-step working set exceeds L2, no flush).
 e2e    : same metric through the public API with HOST (pinned) buffers: every
          model step uploads pos+vel, steps once, downloads pos+vel; an ensemble of
-         4 independent models is kept in flight through the asynchronous C ABI
+         6 independent models is kept in flight through the asynchronous C ABI
          (the one-synchronous-model figure is reported beside it).
 roofline: dominant kernel (the sweep) — algorithmic 128 B/agent-update
           x agents per launch / its CUDA-event duration, against the
@@ -448,7 +448,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--search", default="approximate", choices=["approximate", "exact"])
     ap.add_argument("--kernel", default="auto", choices=["auto", "generic", "fine"])
-    ap.add_argument("--ensemble", type=int, default=4, help="independent models in flight in the e2e leg")
+    ap.add_argument("--ensemble", type=int, default=6, help="independent models in flight in the e2e leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
     args = ap.parse_args()
     if args.impl == "reference":
