@@ -58,6 +58,10 @@ struct ResortArgs {
 #ifndef RS_G2D
 #define RS_G2D 4
 #endif
+#ifndef RS_AGG_UNROLL
+#define RS_AGG_UNROLL 4
+#endif
+constexpr int kRsAggUnroll = RS_AGG_UNROLL;     // crowded-cell aggregate loop: loads of several iterations in flight
 template <class T, int D, int G>
 __global__ void RS_BOUNDS
 k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, const uint32_t* __restrict__ newkey,
@@ -275,6 +279,7 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, c
 #pragma unroll
                 for (int d = 0; d < 2 * D; ++d) acc[d] = T(0);
                 if (src >= 0) {
+#pragma unroll kRsAggUnroll
                     for (uint32_t t = gb + gl; t < ge; t += 8) {
 #pragma unroll
                         for (int d = 0; d < D; ++d) {
