@@ -204,7 +204,66 @@ __global__ void k_ids_to_slots(const int64_t* __restrict__ ids, const int32_t* _
 // v ./ norm(v) .* r (r = norm(agent.vel) when not given), or (±1, …) * r / sqrt(D) if the normals are all zero;
 // agent.vel = direction; then walk!(agent, direction, model).  The normals are Box–Muller pairs on the
 // counter stream of ab_internal.cuh (draws 0..3), the signs of the degenerate branch draws 8..8+D-1.
-struct RwArgs { double r; uint64_t seed; };
+struct RwArgs { double r; uint64_t seed; const double* polar = nullptr; const double* azim = nullptr; };
+
+// randomwalk!(agent, model, r; polar, azimuthal) with angle distributions — src/spaces/walk.jl:236-330.  The host
+// draws the angles (anything that supports `rand` in the reference); the device rotates the velocity:
+//   2-D: direction = Angle2d(θ) * vel;   3-D: rotate(w, θ, ϕ) of walk.jl:347-357 — w turned by θ about a vector u
+//   normal to it (u[n] = w[m], u[m] = -w[n], m the first nonzero component, n = m % 3 + 1), the result turned by ϕ
+//   about w.  Rotations.jl (not in the tree; Project.toml compat "1") supplies Angle2d / AngleAxis: an AngleAxis
+//   normalises its axis and acts as the Rodrigues rotation v cosθ + (k × v) sinθ + k (k · v)(1 - cosθ).
+// Then direction .*= r / norm(vel) when r is given, vel = direction, walk!.  Arithmetic in f64, stored as T.
+__device__ __forceinline__ void rodrigues(const double* k_unnorm, double ang, const double* v, double* out) {
+    const double kn = sqrt(k_unnorm[0] * k_unnorm[0] + k_unnorm[1] * k_unnorm[1] + k_unnorm[2] * k_unnorm[2]);
+    const double k[3] = {k_unnorm[0] / kn, k_unnorm[1] / kn, k_unnorm[2] / kn};
+    const double c = cos(ang), s = sin(ang);
+    const double kv = k[0] * v[0] + k[1] * v[1] + k[2] * v[2];
+    const double cr[3] = {k[1] * v[2] - k[2] * v[1], k[2] * v[0] - k[0] * v[2], k[0] * v[1] - k[1] * v[0]};
+#pragma unroll
+    for (int d = 0; d < 3; ++d) out[d] = v[d] * c + cr[d] * s + k[d] * kv * (1.0 - c);
+}
+
+template <class T, int D>
+__global__ void k_rw_rotate(T* __restrict__ vel, int64_t cap, int n, const int32_t* __restrict__ slots, int nactive,
+                            double r, const double* __restrict__ polar, const double* __restrict__ azim,
+                            T* __restrict__ dirs, int* __restrict__ err) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nactive) return;
+    const int s = slots ? slots[t] : t;
+    double w[3] = {0.0, 0.0, 0.0}, out[3] = {0.0, 0.0, 0.0};
+    bool ok = s >= 0 && s < n;
+    if (ok) {
+#pragma unroll
+        for (int d = 0; d < D; ++d) w[d] = (double)vel[(size_t)d * cap + s];
+        const double nv = sqrt(w[0] * w[0] + w[1] * w[1] + w[2] * w[2]);
+        if (!(nv > 0.0)) { atomicOr(err, AB_EF_ARG); ok = false; }
+        else {
+            if (D == 2) {
+                const double c = cos(polar[t]), sn = sin(polar[t]);
+                out[0] = c * w[0] - sn * w[1];
+                out[1] = sn * w[0] + c * w[1];
+            } else {
+                const int m = w[0] != 0.0 ? 0 : (w[1] != 0.0 ? 1 : 2), nn = (m + 1) % 3;
+                double u[3] = {0.0, 0.0, 0.0}, a[3];
+                u[nn] = w[m];
+                u[m] = -w[nn];
+                rodrigues(u, polar[t], w, a);
+                rodrigues(w, azim[t], a, out);
+            }
+            if (r > 0.0) {
+                const double rel = r / nv;
+#pragma unroll
+                for (int d = 0; d < D; ++d) out[d] *= rel;
+            }
+        }
+    }
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        const T dir = ok ? (T)out[d] : T(0);
+        if (ok) vel[(size_t)d * cap + s] = dir;
+        dirs[(size_t)t * D + d] = dir;
+    }
+}
 
 template <class T, int D>
 __global__ void k_rw_dirs(T* __restrict__ vel, int64_t cap, int n, const int32_t* __restrict__ slots,
@@ -275,12 +334,23 @@ static int move_common(ab_handle* h, double dt, const void* directions, const in
     if (active_ids && nactive < 0) return ab_fail(h, AB_ERR_INVALID, "negative nactive");
     size_t dir_bytes = (directions || rw) ? (size_t)na * h->D * h->tsize : 0;
     const int64_t* ids_dev = nullptr;
+    const double *d_polar = nullptr, *d_azim = nullptr;
     if (active_ids || directions || rw) {
         size_t ids_bytes = active_ids ? (size_t)na * sizeof(int64_t) : 0;
         size_t slots_bytes = active_ids ? (size_t)na * sizeof(int32_t) : 0;
         size_t o1 = (ids_bytes + 255) / 256 * 256, o2 = o1 + (slots_bytes + 255) / 256 * 256;
         char* base;
-        AB_TRY(ab_scratch(h, o2 + dir_bytes + 256, (void**)&base));
+        const size_t o3 = o2 + (dir_bytes + 255) / 256 * 256;
+        const size_t ang_bytes = (rw && rw->polar) ? (size_t)na * sizeof(double) : 0, ang_stride = (ang_bytes + 255) / 256 * 256;
+        AB_TRY(ab_scratch(h, o3 + 2 * ang_stride + 256, (void**)&base));
+        if (ang_bytes && na > 0) {
+            d_polar = (const double*)(base + o3);
+            AB_CUDA(h, cudaMemcpyAsync(base + o3, rw->polar, ang_bytes, cudaMemcpyHostToDevice, h->stream));
+            if (rw->azim) {
+                d_azim = (const double*)(base + o3 + ang_stride);
+                AB_CUDA(h, cudaMemcpyAsync(base + o3 + ang_stride, rw->azim, ang_bytes, cudaMemcpyHostToDevice, h->stream));
+            }
+        }
         if (active_ids && na > 0) {
             AB_CUDA(h, cudaMemcpyAsync(base, active_ids, ids_bytes, cudaMemcpyHostToDevice, h->stream));
             AB_TRY(ab_ensure_slot_map(h));
@@ -304,7 +374,8 @@ static int move_common(ab_handle* h, double dt, const void* directions, const in
         AB_LAUNCH(h, "k_rw_dirs");
         const int nb = (int)ab_blocks(na, 256);
         void* vel = h->fields[1].buf[h->cur];
-#define RWD(T, DD) k_rw_dirs<T, DD><<<nb, 256, 0, h->stream>>>((T*)vel, h->cap, (int)h->n, slots, ids_dev, na, *rw, (T*)dir_dev, h->d_err)
+#define RWD(T, DD) do { if (d_polar) k_rw_rotate<T, DD><<<nb, 256, 0, h->stream>>>((T*)vel, h->cap, (int)h->n, slots, na, rw->r, d_polar, d_azim, (T*)dir_dev, h->d_err); \
+                        else k_rw_dirs<T, DD><<<nb, 256, 0, h->stream>>>((T*)vel, h->cap, (int)h->n, slots, ids_dev, na, *rw, (T*)dir_dev, h->d_err); } while (0)
         if (h->dtype == AB_F64) { if (h->D == 2) RWD(double, 2); else RWD(double, 3); }
         else { if (h->D == 2) RWD(float, 2); else RWD(float, 3); }
 #undef RWD
@@ -579,6 +650,20 @@ int ab_randomwalk(ab_handle* h, double r, uint64_t seed, const int64_t* active_i
     if (r == 0.0) return ab_fail(h, AB_ERR_INVALID, "ArgumentError: The displacement must be larger than 0.");
     RwArgs rw{r, seed};                                       // r < 0: the agent's own speed
     return move_common(h, 0.0, nullptr, active_ids, nactive, &rw);
+}
+
+int ab_randomwalk_angles(ab_handle* h, double r, const double* polar, const double* azimuthal, const int64_t* active_ids,
+                         int64_t nactive) {
+    if (h->desc.kind != AB_SPACE_CONTINUOUS) return ab_fail(h, AB_ERR_INVALID, "angle distributions are for ContinuousSpace random walks");
+    if (!polar) return ab_fail(h, AB_ERR_INVALID, "null polar angles");
+    if (h->D == 3 && !azimuthal) return ab_fail(h, AB_ERR_INVALID, "3-D random walks need azimuthal angles");
+    if (r == 0.0) return ab_fail(h, AB_ERR_INVALID, "ArgumentError: The displacement must be larger than 0.");
+    RwArgs rw{r, 0, polar, h->D == 3 ? azimuthal : nullptr};
+    const bool was_async = h->async_mode;
+    h->async_mode = false;                                    // the angle arrays belong to the caller: finish before returning
+    const int rc = move_common(h, 0.0, nullptr, active_ids, nactive, &rw);
+    h->async_mode = was_async;
+    return rc;
 }
 
 int ab_step_flock(ab_handle* h, const ab_flock_params* p, int64_t nsteps) {

@@ -408,6 +408,24 @@ class StandardABM:
         a = np.ascontiguousarray(ids, dtype=np.int64) if ids is not None else None
         self._ck(self.lib.ab_walk(self.h, self._ptr(d), self._ptr(a), d.shape[0] if a is None else a.shape[0], int(ifempty)))
 
+    def randomwalk_angles(self, polar, azimuthal=None, r=None, ids=None):
+        """randomwalk!(agent, model[, r]; polar, azimuthal) on a ContinuousSpace (walk.jl:236-330): `polar` /
+        `azimuthal` are the angles drawn for the walking agents (arrays, or callables k -> k angles, e.g. a
+        distribution's sampler); the velocity is rotated by them, scaled to length r when r is given, and walked."""
+        n = self.nagents()
+        a = np.ascontiguousarray(ids, dtype=np.int64) if ids is not None else None
+        k = n if a is None else a.shape[0]
+        th = np.ascontiguousarray(polar(k) if callable(polar) else polar, dtype=np.float64).reshape(k)
+        ph = None
+        if self.D == 3:
+            if azimuthal is None:
+                raise AgentsError(-1, "3-D random walks need azimuthal angles")
+            ph = np.ascontiguousarray(azimuthal(k) if callable(azimuthal) else azimuthal, dtype=np.float64).reshape(k)
+        if r is not None and r <= 0:
+            raise AgentsError(-1, "ArgumentError: The displacement must be larger than 0.")
+        self._ck(self.lib.ab_randomwalk_angles(self.h, -1.0 if r is None else float(r), self._ptr(th), self._ptr(ph),
+                                               self._ptr(a), 0 if a is None else k))
+
     def randomwalk(self, r=None, seed=0, ids=None, ifempty=True, force_motion=False):
         """randomwalk!(agent, model, r; ifempty, force_motion) for `ids` (all agents when None) — walk.jl:154-214 on
         grids (r defaults to 1), walk.jl:389-408 on a ContinuousSpace (r defaults to the agent's speed).  `seed`

@@ -228,6 +228,13 @@ int ab_walk(ab_handle* h, const void* directions, const int64_t* active_ids, int
  *     order of `active_ids`, and the agent moves to the chosen empty position. */
 int ab_randomwalk(ab_handle* h, double r, uint64_t seed, const int64_t* active_ids, int64_t nactive, int ifempty,
                   int force_motion);
+/* randomwalk!(agent, model[, r]; polar, azimuthal) on a ContinuousSpace{2} / {3} with angle distributions
+ * (src/spaces/walk.jl:236-330): the host draws one polar angle (and in 3-D one azimuthal angle) per walking agent from
+ * whatever distribution it likes; the device turns the agent's velocity by them (rotate, walk.jl:332-357), scales it to
+ * length r (r < 0: keeps its length), stores it as the new velocity and walks.  A resting agent has no direction to
+ * rotate: AB_ERR_INVALID. */
+int ab_randomwalk_angles(ab_handle* h, double r, const double* polar, const double* azimuthal, const int64_t* active_ids,
+                         int64_t nactive);
 
 /* ---- fused rules (synchronous update) ---------------
  * step!(model, n) with a B200Step model_step! (step_standard.jl:24-31). */

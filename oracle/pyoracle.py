@@ -528,3 +528,40 @@ def continuous_randomwalk_directions(vel, ids, r, seed, dtype=np.float64):
         else:
             out[k] = [(-1.0 if rw_u01(seed, id, 8 + d) < 0.5 else 1.0) * rr / np.sqrt(float(D)) for d in range(D)]
     return out
+
+
+def rotate2(w, theta):
+    """rotate(w::SVector{2}, θ) = Angle2d(θ) * w (walk.jl:332-337)."""
+    c, s = np.cos(theta), np.sin(theta)
+    return np.array([c * w[0] - s * w[1], s * w[0] + c * w[1]])
+
+
+def _angle_axis(axis, ang, v):
+    k = np.asarray(axis, dtype=np.float64)
+    k = k / np.sqrt(np.sum(k * k))
+    return v * np.cos(ang) + np.cross(k, v) * np.sin(ang) + k * np.dot(k, v) * (1.0 - np.cos(ang))
+
+
+def rotate3(w, theta, phi):
+    """rotate(w::SVector{3}, θ, ϕ) (walk.jl:347-357): θ about a vector normal to w, then ϕ about w."""
+    w = np.asarray(w, dtype=np.float64)
+    m = int(np.flatnonzero(w != 0)[0])
+    n = (m + 1) % 3
+    u = np.zeros(3)
+    u[n] = w[m]
+    u[m] = -w[n]
+    a = _angle_axis(u, theta, w)
+    return _angle_axis(w, phi, a)
+
+
+def continuous_randomwalk_angle_directions(vel, ids, polar, azimuthal=None, r=None):
+    """direction of randomwalk!(agent, model[, r]; polar, azimuthal) (walk.jl:236-330) for the given angles."""
+    vel = np.asarray(vel, dtype=np.float64)
+    out = np.zeros((len(ids), vel.shape[1]))
+    for k, id in enumerate(ids):
+        w = vel[id - 1]
+        d = rotate2(w, polar[k]) if vel.shape[1] == 2 else rotate3(w, polar[k], azimuthal[k])
+        if r is not None:
+            d = d * (r / np.sqrt(np.sum(w * w)))
+        out[k] = d
+    return out

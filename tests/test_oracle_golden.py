@@ -465,3 +465,19 @@ def test_randomwalk_continuous_restatement():
     assert np.abs(d.mean(axis=0)).max() < 0.03
     d2 = continuous_randomwalk_directions(vel, [1, 2], None, 11)
     assert np.allclose(np.sqrt((d2 ** 2).sum(axis=1)), np.sqrt(2.0), rtol=1e-14)
+
+
+def test_rotate_restatement():
+    # walk.jl:347-357 docstring: the rotated vector v satisfies (v·w)/(|v||w|) = cos(θ) for every ϕ, and |v| = |w|
+    from oracle.pyoracle import rotate2, rotate3
+    rng = np.random.default_rng(3)
+    for _ in range(50):
+        w = rng.normal(size=3)
+        if rng.random() < 0.3:
+            w[0] = 0.0
+        th, ph = rng.uniform(-np.pi, np.pi), rng.uniform(0, np.pi)
+        v = rotate3(w, th, ph)
+        assert abs(np.dot(v, w) / (np.linalg.norm(v) * np.linalg.norm(w)) - np.cos(th)) < 1e-12
+        assert abs(np.linalg.norm(v) - np.linalg.norm(w)) < 1e-12
+    assert np.allclose(rotate2(np.array([1.0, 0.0]), np.pi / 2), [0.0, 1.0], atol=1e-15)
+    assert np.allclose(rotate3(np.array([0.0, 0.0, 2.0]), 0.0, 1.3), [0.0, 0.0, 2.0], atol=1e-15)

@@ -136,3 +136,55 @@ def test_continuous_randomwalk_errors():
     with pytest.raises(ab.AgentsError, match="displacement must be larger than 0"):
         m.randomwalk()                                          # agent 1 is at rest: default r = 0 (walk.jl:394-396)
     m.close()
+
+
+@pytest.mark.parametrize("D", [2, 3])
+@pytest.mark.parametrize("dtype,tol", [(np.float64, 1e-13), (np.float32, 1e-5)])
+@pytest.mark.parametrize("r", [None, 1.3])
+def test_continuous_randomwalk_with_angles(D, dtype, tol, r):
+    # walk.jl:236-330: velocity rotated by the drawn angles, scaled to r, stored, walked
+    from oracle.pyoracle import continuous_randomwalk_angle_directions
+    n = 400
+    extent = (10.0,) * D
+    pos = (uniform(n, D, 3) * 10.0).astype(dtype)
+    vel = (uniform(n, D, 4) * 2.0 - 1.0).astype(dtype)
+    vel[5, 0] = 0.0                                            # first nonzero component is not the first one
+    m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=1.0, dtype=dtype))
+    m.add_agents(pos, vel)
+    o = ContinuousOracle(extent, spacing=1.0, dtype=dtype)
+    o.add_agents(pos, vel)
+    ids = np.arange(1, n + 1, 2)
+    th = (uniform(len(ids), 1, 8)[:, 0] * 2 - 1) * np.pi       # Uniform(-π, π)
+    ph = np.arccos(uniform(len(ids), 1, 9)[:, 0] * 2 - 1)      # Arccos(-1, 1), walk.jl:359-376
+    want = continuous_randomwalk_angle_directions(vel, [int(i) for i in ids], th, ph, r).astype(dtype)
+    m.randomwalk_angles(th, ph if D == 3 else None, r=r, ids=ids)
+    got_v, got_p = m.vel, m.pos
+    sel = ids - 1
+    assert np.max(np.abs(got_v[sel] - want)) <= tol * max(1.0, np.abs(want).max())
+    speed = np.sqrt((got_v[sel].astype(np.float64) ** 2).sum(axis=1))
+    want_speed = np.sqrt((vel[sel].astype(np.float64) ** 2).sum(axis=1)) if r is None else r
+    assert np.allclose(speed, want_speed, rtol=20 * tol)
+    # the polar angle is the angle between the old and the new velocity (walk.jl:347-357 docstring)
+    cosang = (got_v[sel].astype(np.float64) * vel[sel]).sum(axis=1) / (speed * np.sqrt((vel[sel].astype(np.float64) ** 2).sum(axis=1)))
+    assert np.allclose(cosang, np.cos(th), atol=50 * tol)
+    for i, d in zip(ids, want):
+        o.walk(int(i), d)
+    err = np.abs(got_p - o.state()[0])
+    err = np.minimum(err, 10.0 - err)
+    assert err.max() <= 2 * tol * 10.0
+    rest = np.setdiff1d(np.arange(n), sel)
+    assert np.array_equal(got_p[rest], pos[rest]) and np.array_equal(got_v[rest], vel[rest])
+    # callables as distributions, all agents
+    m.randomwalk_angles(lambda k: np.zeros(k), (lambda k: np.zeros(k)) if D == 3 else None)
+    assert np.max(np.abs(m.vel - got_v)) <= tol              # zero angles: the velocity is kept
+    m.close()
+
+
+def test_randomwalk_angles_errors():
+    m = ab.StandardABM(ab.ContinuousSpace((10.0, 10.0, 10.0), spacing=1.0))
+    m.add_agents(np.full((2, 3), 5.0), np.array([[0.0, 0.0, 0.0], [1.0, 0.0, 0.0]]))
+    with pytest.raises(ab.AgentsError, match="azimuthal"):
+        m.randomwalk_angles(np.zeros(2))
+    with pytest.raises(ab.AgentsError, match="resting agent"):
+        m.randomwalk_angles(np.zeros(2), np.zeros(2))
+    m.close()
