@@ -91,6 +91,14 @@ int ab_scratch2(ab_handle* h, size_t bytes, void** out) {
     return AB_OK;
 }
 
+int ab_check_device_errors_now(ab_handle* h) {
+    const bool was_async = h->async_mode;
+    h->async_mode = false;
+    const int rc = ab_check_device_errors(h);
+    h->async_mode = was_async;
+    return rc;
+}
+
 int ab_check_device_errors(ab_handle* h) {
     if (h->async_mode) return AB_OK;      // deferred to ab_sync
     AB_CUDA(h, cudaMemcpyAsync(h->h_err, h->d_err, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
@@ -794,10 +802,7 @@ int ab_layout_set(ab_handle* h, const int64_t* slot_ids, int64_t n, int32_t refi
         rc = ab_reindex_from(h, h->fields[0].buf[h->cur], h->fields[1].buf[h->cur], false);
         h->place_prio = nullptr;
         if (rc == AB_OK) {
-            const bool was_async = h->async_mode;
-            h->async_mode = false;
-            rc = ab_check_device_errors(h);                    // synchronises: prio and dprio may go
-            h->async_mode = was_async;
+            rc = ab_check_device_errors_now(h);                // synchronises: prio and dprio may go
         } else cudaStreamSynchronize(h->stream);
     }
     cudaFree(dprio);

@@ -129,11 +129,7 @@ int ab_spatial_lookup(ab_handle* h, const int64_t* prop_dims, int pd, const doub
     }
     if (out_index) AB_CUDA(h, cudaMemcpyAsync(out_index, di, bi, cudaMemcpyDeviceToHost, h->stream));
     if (out_value) AB_CUDA(h, cudaMemcpyAsync(out_value, dv, bv, cudaMemcpyDeviceToHost, h->stream));
-    const bool was_async = h->async_mode;
-    h->async_mode = false;
-    const int rc = ab_check_device_errors(h);            // synchronises; BoundsError of the reference -> AB_ERR_OUTSIDE
-    h->async_mode = was_async;
-    return rc;
+    return ab_check_device_errors_now(h);                 // synchronises; BoundsError of the reference -> AB_ERR_OUTSIDE
 }
 
 int ab_update_vel_field(ab_handle* h, const int64_t* prop_dims, int pd, const double* field, double scale,
@@ -168,11 +164,7 @@ int ab_update_vel_field(ab_handle* h, const int64_t* prop_dims, int pd, const do
 #undef FK
     }
     h->agg_valid = false;                                 // Σ vel per cell changed
-    const bool was_async = h->async_mode;
-    h->async_mode = false;
-    const int rc = ab_check_device_errors(h);            // also keeps `mask` alive until the copy is done
-    h->async_mode = was_async;
-    return rc;
+    return ab_check_device_errors_now(h);                 // also keeps `mask` alive until the copy is done
 }
 
 }  // extern "C"

@@ -192,6 +192,7 @@ int ab_cuda_fail(ab_handle* h, cudaError_t e, const char* what);
 int ab_scratch(ab_handle* h, size_t bytes, void** out);     // scratch  (grow-only)
 int ab_scratch2(ab_handle* h, size_t bytes, void** out);    // scratch2 (grow-only)
 int ab_check_device_errors(ab_handle* h);                   // reads + clears d_err
+int ab_check_device_errors_now(ab_handle* h);               // same, also in asynchronous mode (calls that hand back host data)
 int ab_ensure_index(ab_handle* h);
 int ab_ensure_slot_map(ab_handle* h);
 int ab_set_refine(ab_handle* h, int K);
