@@ -11,6 +11,9 @@ the live oracle.  Everything is derived from the counter-based generator of SURV
                   (approximate + exact, r = 5), per-agent neighbour counts of step 1, pos/vel after 1 and 10 steps
   pairs300.npz    interacting_pairs(:all, exact / approximate, r = 3) and (:nearest, r = 3, ByID) of that state
   grid_sch.npz    Schelling happiness pass on a 40 x 30 GridSpaceSingle (periodic and not), 70 % occupancy
+  randomwalk.npz  randomwalk! on the counter stream of include/agents_b200.h: first draws of the stream, positions of a
+                  60-agent GridSpaceSingle / GridSpace (11 x 8) after 3 calls (plain, ifempty, force_motion), and the
+                  directions of a ContinuousSpace uniform walk (2-D, 3-D)
 """
 import os
 import sys
@@ -66,7 +69,35 @@ def grid_sch():
     np.savez_compressed(os.path.join(HERE, "grid_sch.npz"), **out)
 
 
+def randomwalk():
+    from oracle.pyoracle import continuous_randomwalk_directions, grid_randomwalk, rw_u01
+
+    out = {"u01": np.array([[rw_u01(s, i, c) for c in range(4)] for s in (0, 42, 2 ** 63 + 5) for i in (1, 2, 1000000)])}
+    dims = (11, 8)
+    u = uniform(180, 2, 4)
+    p = np.floor(u * np.asarray(dims)[None, :]).astype(np.int64) + 1
+    _, idx = np.unique(p, axis=0, return_index=True)
+    pos = p[np.sort(idx)][:60]
+    out["grid_pos"] = pos
+    for single in (True, False):
+        for periodic in (True, False):
+            g = GridOracle(dims, periodic=periodic, metric="chebyshev", single=single)
+            g.add_agents(pos)
+            ids = list(range(1, len(pos) + 1))
+            grid_randomwalk(g, ids, 1, 11, ifempty=False, force_motion=False)
+            grid_randomwalk(g, ids[::2], 2, 12, ifempty=True, force_motion=False)
+            grid_randomwalk(g, ids, 1, 13, ifempty=True, force_motion=True)
+            out[f"grid_single{int(single)}_periodic{int(periodic)}"] = g.positions()
+    for D in (2, 3):
+        vel = uniform(200, D, 4) * 2.0 - 1.0
+        out[f"cont_vel{D}"] = vel
+        out[f"cont_dir{D}_r"] = continuous_randomwalk_directions(vel, list(range(1, 201)), 0.7, 21)
+        out[f"cont_dir{D}_speed"] = continuous_randomwalk_directions(vel, list(range(1, 201)), None, 22)
+    np.savez_compressed(os.path.join(HERE, "randomwalk.npz"), **out)
+
+
 if __name__ == "__main__":
     flock300()
     grid_sch()
+    randomwalk()
     print("written:", sorted(f for f in os.listdir(HERE) if f.endswith(".npz")))

@@ -75,3 +75,54 @@ def test_device_matches_fixtures():
         g.step(1)
         assert np.array_equal(g.column("mood").ravel(), s[f"mood_periodic{int(periodic)}"].ravel())
         g.close()
+
+
+def _rw_grid_cases():
+    return [(single, periodic) for single in (True, False) for periodic in (True, False)]
+
+
+def test_oracle_reproduces_randomwalk_fixture():
+    from oracle.pyoracle import GridOracle, continuous_randomwalk_directions, grid_randomwalk, rw_u01
+
+    f = np.load(os.path.join(G, "randomwalk.npz"))
+    u = np.array([[rw_u01(s, i, c) for c in range(4)] for s in (0, 42, 2 ** 63 + 5) for i in (1, 2, 1000000)])
+    assert np.array_equal(u, f["u01"]) and np.all((u >= 0) & (u < 1))
+    pos = f["grid_pos"]
+    ids = list(range(1, len(pos) + 1))
+    for single, periodic in _rw_grid_cases():
+        g = GridOracle((11, 8), periodic=periodic, metric="chebyshev", single=single)
+        g.add_agents(pos)
+        grid_randomwalk(g, ids, 1, 11, ifempty=False, force_motion=False)
+        grid_randomwalk(g, ids[::2], 2, 12, ifempty=True, force_motion=False)
+        grid_randomwalk(g, ids, 1, 13, ifempty=True, force_motion=True)
+        assert np.array_equal(g.positions(), f[f"grid_single{int(single)}_periodic{int(periodic)}"])
+    for D in (2, 3):
+        vel = f[f"cont_vel{D}"]
+        assert np.array_equal(continuous_randomwalk_directions(vel, list(range(1, 201)), 0.7, 21), f[f"cont_dir{D}_r"])
+        assert np.array_equal(continuous_randomwalk_directions(vel, list(range(1, 201)), None, 22), f[f"cont_dir{D}_speed"])
+
+
+@pytest.mark.gpu
+def test_device_matches_randomwalk_fixture():
+    import agents_jl_b200 as ab
+
+    f = np.load(os.path.join(G, "randomwalk.npz"))
+    pos = f["grid_pos"]
+    ids = np.arange(1, len(pos) + 1)
+    for single, periodic in _rw_grid_cases():
+        sp = (ab.GridSpaceSingle if single else ab.GridSpace)((11, 8), periodic=periodic, metric="chebyshev")
+        m = ab.StandardABM(sp)
+        m.add_agents(pos.astype(np.int32))
+        m.randomwalk(1, seed=11, ifempty=False, force_motion=False)
+        m.randomwalk(2, seed=12, ids=ids[::2], ifempty=True, force_motion=False)
+        m.randomwalk(1, seed=13, ifempty=True, force_motion=True)
+        assert np.array_equal(m.pos, f[f"grid_single{int(single)}_periodic{int(periodic)}"])
+        m.close()
+    for D in (2, 3):
+        vel = f[f"cont_vel{D}"]
+        for r, seed, key in ((0.7, 21, "r"), (None, 22, "speed")):
+            m = ab.StandardABM(ab.ContinuousSpace((10.0,) * D, spacing=1.0))
+            m.add_agents(np.full((200, D), 5.0), vel)
+            m.randomwalk(r, seed=seed)
+            assert np.max(np.abs(m.vel - f[f"cont_dir{D}_{key}"])) <= 1e-13
+            m.close()
