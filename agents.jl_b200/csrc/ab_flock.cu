@@ -26,6 +26,7 @@ template <class T> struct FlockU {
     T thr;      // exact_threshold<T>(visual_distance), computed once on the host for uniform parameters
     double gr_t1, gr_t2;   // (spacing - r)², (2 spacing - r)² (negative: never) — grid_radius_12
     int reach;             // fine-cell reach of the separation sweep on the fine path (FinePlan::R)
+    const uint8_t* active; // scheduled agents by id (Schedulers.Partially / an id list); nullptr: every agent steps
 };
 
 // host twin of exact_threshold (ab_internal.cuh): IEEE sqrt on both sides, same result
@@ -147,6 +148,16 @@ k_flock_generic(SpaceDev<T, D> sp, FlockU<T> uni, const T* __restrict__ per_agen
     int c[D];
 #pragma unroll
     for (int d = 0; d < D; ++d) { p[d] = pos[(size_t)d * cap + s]; v[d] = vel[(size_t)d * cap + s]; }
+    if (uni.active && !uni.active[ids[s]]) {
+        // not scheduled this tick: the agent keeps its state and stays a neighbour of the others
+#pragma unroll
+        for (int d = 0; d < D; ++d) { npos[(size_t)d * cap + s] = p[d]; nvel[(size_t)d * cap + s] = v[d]; }
+        const uint32_t k0 = key[s];
+        newkey[s] = k0;
+        rank[s] = atomicAdd(&cell_count[k0], 1u);
+        if (ncount) ncount[ids[s]] = 0;
+        return;
+    }
     key_to_cell<T, D>(sp, key[s], c);
     const int gr = grid_radius<T, D>(sp, p, c, fp.visual_distance);
     T cohere[D], separate[D], match[D];
@@ -496,6 +507,7 @@ static int flock_prepare(ab_handle* h, const ab_flock_params* p, FlockCtx<T, D>*
     if (h->win_W && !fine) return ab_fail(h, AB_ERR_INVALID, "a sharded handle runs the fine-grid flock step only (uniform parameters, visual_distance <= spacing, >= 6 cells per axis)");
     cx->fine = fine;
     u.reach = fine ? plan.R : 1;
+    u.active = h->step_mask_cur;
     if (fine) AB_TRY(ab_set_refine(h, plan.K));
     AB_TRY(ab_ensure_index(h));
     cx->sp = make_space<T, D>(h);
@@ -683,6 +695,30 @@ int ab_step_flock(ab_handle* h, const ab_flock_params* p, int64_t nsteps) {
     AB_CUDA(h, cudaEventElapsedTime(&ms, h->ev0, h->ev1));
     h->last_step_ms = ms;
     return AB_OK;
+}
+
+int ab_step_flock_active(ab_handle* h, const ab_flock_params* p, int64_t nsteps, const int64_t* active_ids, int64_t nactive) {
+    if (!active_ids) return ab_step_flock(h, p, nsteps);
+    if (h->win_W) return ab_fail(h, AB_ERR_STATE, "a scheduled subset is not available on a sharded handle");
+    if (nactive < 0) return ab_fail(h, AB_ERR_INVALID, "negative nactive");
+    if (h->n == 0 || nsteps == 0) return AB_OK;
+    AB_CUDA(h, cudaSetDevice(h->device));
+    std::vector<uint8_t> mask((size_t)h->n, 0);
+    for (int64_t k = 0; k < nactive; ++k) {
+        if (active_ids[k] < 1 || active_ids[k] > h->n) return ab_fail(h, AB_ERR_INVALID, "active id out of range");
+        mask[(size_t)active_ids[k] - 1] = 1;
+    }
+    if (h->step_mask_bytes < (size_t)h->n) {
+        if (h->step_mask) { AB_CUDA(h, cudaStreamSynchronize(h->stream)); AB_CUDA(h, cudaFree(h->step_mask)); h->step_mask = nullptr; }
+        AB_CUDA(h, cudaMalloc(&h->step_mask, (size_t)h->cap));
+        h->step_mask_bytes = (size_t)h->cap;
+    }
+    // pageable source: the copy has left `mask` when the call returns; stream order protects the device buffer
+    AB_CUDA(h, cudaMemcpyAsync(h->step_mask, mask.data(), (size_t)h->n, cudaMemcpyHostToDevice, h->stream));
+    h->step_mask_cur = h->step_mask;
+    const int rc = ab_step_flock(h, p, nsteps);
+    h->step_mask_cur = nullptr;
+    return rc;
 }
 
 int ab_step_flock_group(ab_handle** hs, int nh, const ab_flock_params* p, int64_t nsteps) {

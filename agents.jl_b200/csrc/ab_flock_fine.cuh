@@ -245,6 +245,15 @@ k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T
     T p[D], v[D];
 #pragma unroll
     for (int d = 0; d < D; ++d) { p[d] = pos[(size_t)d * cap + s]; v[d] = vel[(size_t)d * cap + s]; }
+    if (fp.active && !fp.active[ids[s]]) {
+        // not scheduled this tick: the agent keeps its state and stays a neighbour of the others
+#pragma unroll
+        for (int d = 0; d < D; ++d) { npos[(size_t)d * cap + s] = p[d]; nvel[(size_t)d * cap + s] = v[d]; }
+        newkey[s] = k;
+        atomicAdd(&cell_count[k], 1u);
+        if (ncount) ncount[ids[s]] = 0;
+        return;
+    }
     const int gr = grid_radius_12<T, D>(sp, p, cg, fp);
     const T sep2 = fp.separation * fp.separation;
     T cohere[D], separate[D], match[D];

@@ -133,6 +133,9 @@ struct ab_handle {
 
     int* d_err = nullptr;              // device error flag word
     int* h_err = nullptr;              // pinned mirror
+    uint8_t* step_mask = nullptr;          // ab_step_flock_active: 1 per scheduled agent, by id (device, n bytes)
+    size_t step_mask_bytes = 0;
+    const uint8_t* step_mask_cur = nullptr; // set for the duration of a masked step call
     const int32_t* place_prio = nullptr;   // ab_layout_set: in-cell order of a restored checkpoint (rank per id)
 
     void* scratch = nullptr;           // grow-only device scratch for uploads / queries

@@ -114,10 +114,14 @@ class FlockRule:
         if self.per_agent is not None and self._field < 0:
             self._field = model.add_column("_flock_params", np.asarray(self.per_agent, dtype=model.space.dtype))
 
-    def __call__(self, model, nsteps=1):
+    def __call__(self, model, nsteps=1, ids=None):
         self._bind(model)
         fp = L.FlockParams(search=L.SEARCH[self.search], per_agent_field=self._field, kernel=self.kernel, **self.p)
-        model._ck(L.lib().ab_step_flock(model.h, C.byref(fp), int(nsteps)))
+        if ids is None:
+            model._ck(L.lib().ab_step_flock(model.h, C.byref(fp), int(nsteps)))
+        else:       # schedule(model) returned a subset (Schedulers.Partially, a custom scheduler): schedulers.jl:68-120
+            a = np.ascontiguousarray(ids, dtype=np.int64)
+            model._ck(L.lib().ab_step_flock_active(model.h, C.byref(fp), int(nsteps), model._ptr(a), a.shape[0]))
 
 
 class PairForceRule:
@@ -439,9 +443,19 @@ class StandardABM:
                                         0 if a is None else a.shape[0], int(ifempty), int(force_motion)))
 
     # -- stepping (src/simulations/step_standard.jl:24-31) --------------------
-    def step(self, n=1):
+    def step(self, n=1, scheduler=None):
+        """step!(model, n).  `scheduler`: None (every agent: fastest / ByID / Randomly are equivalent under the
+        synchronous update), an id list, or a callable model -> id list evaluated every tick (Schedulers.Partially
+        and custom schedulers, schedulers.jl:8, 68-120) — flock rule only."""
         if self.model_step is None:
             raise AgentsError(L.ERR_STATE, "no model_step! rule")
+        if scheduler is not None:
+            if not isinstance(self.model_step, FlockRule):
+                raise AgentsError(L.ERR_INVALID, "a scheduled subset is available for the flock rule")
+            for _ in range(int(n)):
+                self.model_step(self, 1, ids=scheduler(self) if callable(scheduler) else scheduler)
+                self.time += 1
+            return self
         self.model_step(self, int(n))      # n ticks batched into one ccall
         self.time += int(n)
         return self

@@ -239,6 +239,12 @@ int ab_randomwalk_angles(ab_handle* h, double r, const double* polar, const doub
 /* ---- fused rules (synchronous update) ---------------
  * step!(model, n) with a B200Step model_step! (step_standard.jl:24-31). */
 int ab_step_flock(ab_handle* h, const ab_flock_params* p, int64_t nsteps);           /* examples/flock.jl:79-108 */
+/* The same step for a scheduled subset (Schedulers.Partially or any id list from schedule(model),
+ * src/submodules/schedulers.jl:8, 68-120): only the agents of `active_ids` update; the others keep their state and
+ * remain neighbours of the rest (synchronous update: everybody reads the state at the start of the tick).  The list
+ * applies to each of the nsteps ticks; a scheduler that draws a new subset per tick calls with nsteps = 1.
+ * NULL = every agent (ab_step_flock).  Not available on a sharded handle. */
+int ab_step_flock_active(ab_handle* h, const ab_flock_params* p, int64_t nsteps, const int64_t* active_ids, int64_t nactive);
 int ab_step_pairforce(ab_handle* h, const ab_pairforce_params* p, int64_t nsteps);   /* examples/celllistmap.jl:143-191 */
 /* Schelling on GridSpaceSingle.  Columns "group" (i32) and "mood" (u8) must be
  * registered.  n_moved (optional) receives the movers of the last step. */

@@ -473,3 +473,43 @@ def test_refinement_does_not_change_queries():
     want = o.interacting_pairs_all(3.0)
     assert np.array_equal(np.unique(got, axis=0), np.unique(want, axis=0))
     assert np.array_equal(m.cells(), o.pos2cell(pos))
+
+
+@pytest.mark.parametrize("search", ["approximate", "exact"])
+@pytest.mark.parametrize("kernel", ["generic", "auto"])
+def test_flock_scheduled_subset(search, kernel):
+    """Schedulers.Partially / an id list from schedule(model) (schedulers.jl:8, 68-120): only the scheduled agents
+    update, the others keep their state and stay neighbours.  Under the synchronous update the expected state is the
+    oracle's full step for the scheduled agents and the old state for the rest."""
+    extent, n = (100.0, 100.0), 3000
+    o, m, pos, vel = make_pair(extent, 5.0, True, n, seed=42)
+    m.model_step = ab.FlockRule(search=search, kernel=kernel, **FLOCK)
+    rng = np.random.default_rng(4)
+    for tick in range(3):
+        ids = np.sort(rng.permutation(n)[: n // 3]) + 1
+        p0, v0 = o.state()
+        cnt = o.flock_step_sync(FLOCK, nsteps=1, search=search, return_counts=True)
+        p1, v1 = o.state()
+        mask = np.zeros(n, dtype=bool)
+        mask[ids - 1] = True
+        want_p, want_v = np.where(mask[:, None], p1, p0), np.where(mask[:, None], v1, v0)
+        m.step(1, scheduler=ids)
+        got_p, got_v = m.pos, m.vel
+        assert np.array_equal(got_p[~mask], p0[~mask]) and np.array_equal(got_v[~mask], v0[~mask])     # untouched, bit for bit
+        assert periodic_rel_err(got_p, want_p, extent) <= ONE_STEP_TOL_F64
+        assert rel_err(got_v, want_v) <= ONE_STEP_TOL_F64
+        assert np.array_equal(m.last_neighbor_counts()[mask], cnt[mask])
+        # the oracle continues from the masked state
+        o = ContinuousOracle(extent, spacing=5.0, periodic=True)
+        o.add_agents(got_p, got_v)
+    assert m.time == 3
+    # a callable scheduler is evaluated every tick; the index stays consistent
+    m.step(2, scheduler=lambda mod: np.arange(1, n + 1, 2))
+    off, idl = m.nearby_ids_batch(ids=np.array([1, 2, 3]), r=5.0, search="exact")
+    o2 = ContinuousOracle(extent, spacing=5.0, periodic=True)
+    o2.add_agents(m.pos, m.vel)
+    for k, i in enumerate((1, 2, 3)):
+        assert np.array_equal(np.sort(idl[off[k]:off[k + 1]]), np.sort(o2.nearby_ids_agent(i, 5.0, "exact")))
+    with pytest.raises(ab.AgentsError):
+        m.step(1, scheduler=[0])
+    m.close()
