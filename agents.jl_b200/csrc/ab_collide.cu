@@ -67,6 +67,7 @@ static int launch_round(ab_handle* h, const int64_t* da, const int64_t* db, cons
     const T* pos = (const T*)h->fields[0].buf[cur];
     T* vel = (T*)h->fields[1].buf[cur];
     AB_LAUNCH(h, "k_elastic");
+    h->agg_valid = false;                                     // velocities change in place: Σ vel per cell is stale
     const int nb = (int)ab_blocks(np, 128);
     if (mass_field < 0)
         k_elastic<T, double><<<nb, 128, 0, h->stream>>>(da, db, dix, np, h->slot_of_id, pos, vel, (const double*)nullptr, h->cap, dhap, h->d_err);

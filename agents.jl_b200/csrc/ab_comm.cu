@@ -641,8 +641,9 @@ int ab_upload_local(ab_handle* h, int field, const void* host, const int64_t* gl
         AB_CUDA(h, cudaMemcpyAsync(ids_dev, global_ids, idb, cudaMemcpyHostToDevice, h->stream));
         AB_LAUNCH(h, "k_gids_in");
         k_gids_in<<<ab_blocks(n, 256), 256, 0, h->stream>>>((const int64_t*)ids_dev, h->id[h->cur], (int)n, h->d_err);
-        h->index_valid = false; h->agg_valid = false; h->pairs_n = -1;
+        h->index_valid = false; h->pairs_n = -1;
     }
+    if (field <= 1) h->agg_valid = false;                      // Σ(pos - centre) / Σ vel per cell are stale
     AB_CUDA(h, cudaStreamSynchronize(h->stream));
     return ab_check_device_errors(h);
 }

@@ -718,6 +718,8 @@ int ab_upload(ab_handle* h, int field, const void* host, int64_t n) {
     }
     if (!h->async_mode) AB_CUDA(h, cudaStreamSynchronize(h->stream));
     if (field == 0) { h->index_valid = false; h->pairs_n = -1; }
+    // the per-cell sums Σ(pos - centre), Σ vel of the approximate flock sweep were built from the old columns
+    if (field <= 1 && h->desc.kind == AB_SPACE_CONTINUOUS) h->agg_valid = false;
     return AB_OK;
 }
 

@@ -343,6 +343,8 @@ static int move_common(ab_handle* h, double dt, const void* directions, const in
     void* dir_dev = nullptr;
     int na = active_ids ? (int)nactive : (int)h->n;
     if (active_ids && nactive < 0) return ab_fail(h, AB_ERR_INVALID, "negative nactive");
+    if (!active_ids && directions && nactive != 0 && nactive != h->n)
+        return ab_fail(h, AB_ERR_INVALID, "directions for all agents: nactive must be 0 or the agent count");
     size_t dir_bytes = (directions || rw) ? (size_t)na * h->D * h->tsize : 0;
     const int64_t* ids_dev = nullptr;
     const double *d_polar = nullptr, *d_azim = nullptr;
@@ -398,7 +400,7 @@ static int move_common(ab_handle* h, double dt, const void* directions, const in
     AB_TRY(rc);
     h->index_valid = false;
     h->pairs_n = -1;
-    int e = ab_check_device_errors(h);
+    int e = ab_check_device_errors_now(h);                    // directions / ids belong to the caller: synchronous in every mode
     if (e == AB_ERR_INVALID && !rw) return ab_fail(h, AB_ERR_INVALID, "agent id out of range");
     return e;
 }

@@ -217,7 +217,7 @@ int ab_grid_nearby(ab_handle* h, const void* qpos, const int64_t* qids, int64_t 
     }
     if (fill) { if (total > 0) AB_CUDA(h, cudaMemcpyAsync(ids_out, odev, (size_t)total * sizeof(int64_t), cudaMemcpyDeviceToHost, h->stream)); }
     else AB_CUDA(h, cudaMemcpyAsync(counts, cdev, (size_t)nq * sizeof(int64_t), cudaMemcpyDeviceToHost, h->stream));
-    int e = ab_check_device_errors(h);
+    int e = ab_check_device_errors_now(h);               // hands back host data: synchronous in every mode
     h->index_valid = true;                               // a bad query does not invalidate the index
     if (e == AB_ERR_INVALID) return ab_fail(h, AB_ERR_INVALID, "agent id out of range");
     if (e == AB_ERR_OUTSIDE) return ab_fail(h, AB_ERR_OUTSIDE, "BoundsError: query position outside the grid");
@@ -306,7 +306,7 @@ int ab_grid_positions(ab_handle* h, const int32_t* qpos, int64_t nq, double r, i
     if (fill) { if (total > 0) AB_CUDA(h, cudaMemcpyAsync(pos_out, odev, (size_t)total * h->D * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream)); }
     else AB_CUDA(h, cudaMemcpyAsync(counts, cdev, (size_t)nq * sizeof(int64_t), cudaMemcpyDeviceToHost, h->stream));
     const bool was_valid = h->index_valid;
-    int e = ab_check_device_errors(h);
+    int e = ab_check_device_errors_now(h);
     h->index_valid = was_valid;                          // a bad query does not invalidate the index
     if (e == AB_ERR_OUTSIDE) return ab_fail(h, AB_ERR_OUTSIDE, "BoundsError: query position outside the grid");
     return e;
@@ -570,7 +570,7 @@ static int grid_walk_impl(ab_handle* h, const void* directions, const int64_t* a
     }
     const bool keep_index = single;        // grid_ids was updated in place
     h->grid_cells_valid = false;
-    int e = ab_check_device_errors(h);
+    int e = ab_check_device_errors_now(h);
     h->index_valid = keep_index && e == AB_OK;
     if (e == AB_ERR_INVALID) return ab_fail(h, AB_ERR_INVALID, "agent id out of range");
     return e;
@@ -945,7 +945,7 @@ extern "C" int ab_step_schelling(ab_handle* h, const ab_schelling_params* p, int
     AB_CUDA(h, cudaEventRecord(h->ev1, h->stream));
     if (p->relocate) AB_CUDA(h, cudaMemcpyAsync(h->h_moved, d_moved, sizeof(long long), cudaMemcpyDeviceToHost, h->stream));
     h->grid_cols_dirty = true;
-    AB_TRY(ab_check_device_errors(h));
+    AB_TRY(ab_check_device_errors_now(h));               // synchronous call: *h_moved and the events are read below
     h->index_valid = true;
     float ms = 0;
     AB_CUDA(h, cudaEventElapsedTime(&ms, h->ev0, h->ev1));

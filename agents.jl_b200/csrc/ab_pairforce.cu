@@ -11,8 +11,9 @@
 //            lies in the 3^D block of reference cells around either agent, so each agent sums its
 //            own force over that block (every pair is evaluated from both sides — no atomics, no
 //            force array, one canonical summation order) and integrates in the same kernel.
-//            Followed by k_scan + k_resort (or, if some agent moved further than one cell, by the
-//            generic bucket/place kernels — decided on the device, no host round trip).
+//            Followed by k_scan + k_resort; a device flag says whether some agent moved further than one
+//            cell, and such a step is re-indexed by the generic bucket/place kernels instead (the flag is read
+//            back once per step: one 4-byte copy + stream synchronisation).
 //   generic  anything else: one walk per agent over the reference's offset table; pairs that only one
 //            side sees hand the reaction to the other side through a floating-point atomicAdd
 //            (the only non-deterministic sum in the library, and only for such one-sided pairs).
@@ -365,7 +366,7 @@ extern "C" int ab_step_pairforce(ab_handle* h, const ab_pairforce_params* p, int
     if (h->dtype == AB_F64) rc = h->D == 2 ? pf_steps_t<double, 2>(h, p, nsteps) : pf_steps_t<double, 3>(h, p, nsteps);
     else rc = h->D == 2 ? pf_steps_t<float, 2>(h, p, nsteps) : pf_steps_t<float, 3>(h, p, nsteps);
     AB_TRY(rc);
-    AB_TRY(ab_check_device_errors(h));
+    AB_TRY(ab_check_device_errors_now(h));      // synchronous call (also in asynchronous mode): the events below must have completed
     float ms = 0;
     AB_CUDA(h, cudaEventElapsedTime(&ms, h->ev0, h->ev1));
     h->last_step_ms = ms;

@@ -258,7 +258,7 @@ static int nearby_common(ab_handle* h, const void* qpos, const int64_t* qids, in
     AB_TRY(rc);
     if (fill) { if (total > 0) AB_CUDA(h, cudaMemcpyAsync(ids_out, odev, (size_t)total * sizeof(int64_t), cudaMemcpyDeviceToHost, h->stream)); }
     else AB_CUDA(h, cudaMemcpyAsync(counts, cdev, (size_t)nq * sizeof(int64_t), cudaMemcpyDeviceToHost, h->stream));
-    int e = ab_check_device_errors(h);
+    int e = ab_check_device_errors_now(h);               // hands back host data: synchronous in every mode
     if (e == AB_ERR_INVALID) return ab_fail(h, AB_ERR_INVALID, "agent id out of range");
     return e;
 }

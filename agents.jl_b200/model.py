@@ -410,6 +410,8 @@ class StandardABM:
         dt = self.space.dtype
         d = np.ascontiguousarray(directions, dtype=dt).reshape(-1, self.D)
         a = np.ascontiguousarray(ids, dtype=np.int64) if ids is not None else None
+        if d.shape[0] != (self.nagents() if a is None else a.shape[0]):
+            raise AgentsError(L.ERR_INVALID, "walk!: one direction per walking agent")
         self._ck(self.lib.ab_walk(self.h, self._ptr(d), self._ptr(a), d.shape[0] if a is None else a.shape[0], int(ifempty)))
 
     def randomwalk_angles(self, polar, azimuthal=None, r=None, ids=None):

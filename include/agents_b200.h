@@ -210,10 +210,12 @@ int ab_update_vel_field(ab_handle* h, const int64_t* prop_dims, int pd, const do
 
 /* ---- movement ---------------------------------------------------------------
  * move_agent!(agent, model, dt) continuous.jl:186-194 → walk! walk.jl:58-66 →
- * normalize_position walk.jl:77-91, for `active_ids` (NULL = all agents). */
+ * normalize_position walk.jl:77-91, for `active_ids` (NULL = all agents).  The ids of a list must be
+ * unique (one thread per entry; the reference would move a repeated agent twice — call twice for that). */
 int ab_move(ab_handle* h, double dt, const int64_t* active_ids, int64_t nactive);
 /* walk!(agent, direction, model): per-agent displacement, nactive x D of T
- * (continuous) or int32 (grids, walk.jl:33-56 with ifempty). */
+ * (continuous) or int32 (grids, walk.jl:33-56 with ifempty).  With active_ids == NULL the rows are
+ * in id order and nactive must be the agent count (or 0): AB_ERR_INVALID otherwise. */
 int ab_walk(ab_handle* h, const void* directions, const int64_t* active_ids, int64_t nactive, int ifempty);
 /* randomwalk!(agent, model, r) for the agents of `active_ids` (all when NULL), src/spaces/walk.jl:154-214 (grids)
  * and :389-408 (ContinuousSpace, uniform_randomwalk!).  The reference draws from the model's RNG; its stream is not
