@@ -103,6 +103,9 @@ _SIGS = {
     "ab_comm_ipc_export": (C.c_int, [_H, C.c_void_p]),
     "ab_comm_ipc_import": (C.c_int, [_H, C.c_void_p, C.c_void_p]),
     "ab_comm_direct": (C.c_int, [_H]),
+    "ab_comm_align": (C.c_int, [_H]),
+    "ab_comm_exchange": (C.c_int, [_H]),
+    "ab_comm_wait_stats": (C.c_int, [_H, C.POINTER(C.c_double), C.POINTER(C.c_int64), C.c_int]),
     "ab_comm_slab": (C.c_int, [_H, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "ab_comm_halo": (C.c_int, [_H]),
     "ab_nlocal": (C.c_int64, [_H]),

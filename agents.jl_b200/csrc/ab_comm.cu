@@ -49,6 +49,7 @@ struct nccl_api {
     int (*GroupEnd)() = nullptr;
     int (*Send)(const void*, size_t, int, int, nccl_comm_t, cudaStream_t) = nullptr;
     int (*Recv)(void*, size_t, int, int, nccl_comm_t, cudaStream_t) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, nccl_comm_t, cudaStream_t) = nullptr;
     const char* (*GetErrorString)(int) = nullptr;
 };
 static nccl_api g_nccl;
@@ -73,6 +74,7 @@ static bool nccl_load() {
     SYM(GroupEnd, "ncclGroupEnd");
     SYM(Send, "ncclSend");
     SYM(Recv, "ncclRecv");
+    SYM(AllReduce, "ncclAllReduce");
     SYM(GetErrorString, "ncclGetErrorString");
 #undef SYM
     g_nccl.lib = lib;
@@ -104,6 +106,8 @@ struct ab_comm {
     char *ipc_lower = nullptr, *ipc_upper = nullptr;     // the neighbours' blocks
     bool ipc_on = false;
     int cur_par = 0;                 // parity of the exchange in flight (pack -> transfer -> unpack)
+    unsigned long long* d_wait = nullptr;    // [0] ns spent waiting for the neighbours' flags (k_halo_unpack), [1] waits counted
+    int32_t* d_align = nullptr;      // operand of the start-alignment all-reduce (ab_comm_align)
 };
 static inline char* ipc_slot(char* block, size_t stride, int par, int side) { return block + (size_t)(par * 2 + side) * stride; }
 static inline uint32_t* ipc_flag(char* block, size_t stride, int par, int side) {
@@ -187,11 +191,12 @@ k_halo_pack(MsgLayout m, uint32_t kown, const uint32_t* __restrict__ cs, const E
         mkey[t] = key[s];
     }
     if (flag0) {
-        // direct exchange: the LAST CTA to finish publishes the exchange number in the neighbours' flags
-        // (every thread fences its peer-memory stores at system scope before its CTA is counted)
-        __threadfence_system();
+        // direct exchange: the LAST CTA to finish publishes the exchange number in the neighbours' flags.
+        // The CTA barrier orders every thread's peer-memory stores before thread 0's system-scope fence
+        // (fences are cumulative), so one fence per CTA — not one per thread — precedes the count.
         __syncthreads();
         if (threadIdx.x == 0) {
+            __threadfence_system();
             const uint32_t total = gridDim.x * gridDim.y;
             if (atomicAdd(done_ctr, 1u) == total - 1) {
                 __threadfence_system();
@@ -217,32 +222,39 @@ __device__ __forceinline__ bool wait_flag(const uint32_t* f, uint32_t epoch) {
     }
 }
 
-// Installs the received layers as this rank's halo: blockIdx.y = 0 the upper neighbour's bottom layers
-// (keys [kown, kown + ncs)), 1 = the lower neighbour's top layers (keys [kown + ncs, kown + 2 ncs)).
+// Installs the received layers as this rank's halo.  Blocks [0, nbc) copy the upper neighbour's bottom layers
+// (keys [kown, kown + ncs)), blocks [nbc, 2 nbc) the lower neighbour's top layers (keys [kown + ncs, kown + 2 ncs)).
 // Halo slots follow the owned ones: [n_own, n_own + cnt_u) and [n_own + cnt_u, n_own + cnt_u + cnt_l).
-template <class E, int D>
+// Blocks from 2 nbc on (approximate search) build the halo cells' aggregates — count, Σ(pos - centre), Σ vel per
+// fine row of a reference cell, the canonical 8-strided sum of k_resort / k_cell_agg — straight from the messages,
+// so no separate aggregate launch follows the install.
+template <class T, int D>
 __global__ void __launch_bounds__(256)
-k_halo_unpack(MsgLayout m, uint32_t kown, uint32_t* __restrict__ cs, E* __restrict__ pos, E* __restrict__ vel,
+k_halo_unpack(SpaceDev<T, D> sp, MsgLayout m, uint32_t kown, uint32_t* __restrict__ cs, T* __restrict__ pos, T* __restrict__ vel,
               int32_t* __restrict__ id, uint32_t* __restrict__ key, int64_t cap, const char* __restrict__ buf0,
               const char* __restrict__ buf1, int* __restrict__ err, const uint32_t* wflag0, const uint32_t* wflag1,
-              uint32_t epoch) {
+              uint32_t epoch, int nbc, int nba, T* __restrict__ agg, int64_t agg_stride, uint32_t halo_cell0,
+              uint32_t cells_per_side, unsigned long long* wait_stat) {
     if (wflag0) {
         // direct exchange: both messages were stored into our memory by the neighbours' pack kernels; they
         // never wait for us in return (their pack depends only on their own steps; slots alternate by parity)
         __shared__ int s_ok;
-        if (threadIdx.x == 0) s_ok = wait_flag(wflag0, epoch) && wait_flag(wflag1, epoch);
+        if (threadIdx.x == 0) {
+            unsigned long long t0, t1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+            s_ok = wait_flag(wflag0, epoch) && wait_flag(wflag1, epoch);
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (blockIdx.x == 0 && wait_stat) { atomicAdd(&wait_stat[0], t1 - t0); atomicAdd(&wait_stat[1], 1ull); }
+        }
         __syncthreads();
         if (!s_ok) {
-            if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) atomicOr(err, AB_EF_COMM);
+            if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(err, AB_EF_COMM);
             return;
         }
     }
-    const int src = blockIdx.y;
     const uint32_t* h0 = reinterpret_cast<const uint32_t*>(buf0);
     const uint32_t* h1 = reinterpret_cast<const uint32_t*>(buf1);
-    const char* buf = src == 0 ? buf0 : buf1;
-    const uint32_t* hdr = src == 0 ? h0 : h1;
-    const uint32_t n_own = cs[kown];                     // written by the scan of this step; never rewritten here
+    const uint32_t n_own = cs[kown];                     // written by the re-sort of this step; never rewritten here
     uint32_t cnt_u = h0[0], cnt_l = h1[0];
     bool bad = h0[3] != 0xAB200u || h1[3] != 0xAB200u || h0[2] != m.ncs || h1[2] != m.ncs;
     if ((uint64_t)n_own + cnt_u + cnt_l > (uint64_t)cap) bad = true;       // window does not fit the handle's capacity
@@ -250,26 +262,80 @@ k_halo_unpack(MsgLayout m, uint32_t kown, uint32_t* __restrict__ cs, E* __restri
         if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(err, AB_EF_COMM);
         cnt_u = cnt_l = 0;
     }
+    const bool agg_role = (int)blockIdx.x >= 2 * nbc;
+    const int rb = agg_role ? (int)blockIdx.x - 2 * nbc : (int)blockIdx.x;
+    const int per = agg_role ? nba : nbc;
+    const int src = rb >= per ? 1 : 0;
+    const int bx = rb - src * per;                       // block index within the role and side
+    const char* buf = src == 0 ? buf0 : buf1;
+    const uint32_t* hdr = src == 0 ? h0 : h1;
     const uint32_t cnt = src == 0 ? cnt_u : cnt_l;
-    const uint32_t base = src == 0 ? n_own : n_own + cnt_u;
     const uint32_t kdst = src == 0 ? kown : kown + m.ncs;
-    const uint32_t kdelta = kdst - hdr[1];               // sender's key frame -> this window's (mod 2^32)
-    const uint32_t t0 = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
     const uint32_t* mcs = reinterpret_cast<const uint32_t*>(buf + m.off_cs);
-    for (uint32_t i = t0 + 1; i <= m.ncs; i += stride) cs[kdst + i] = base + (bad ? 0u : mcs[i]);
-    const E* mpos = reinterpret_cast<const E*>(buf + m.off_pos);
-    const E* mvel = reinterpret_cast<const E*>(buf + m.off_vel);
-    const int32_t* mid = reinterpret_cast<const int32_t*>(buf + m.off_id);
-    const uint32_t* mkey = reinterpret_cast<const uint32_t*>(buf + m.off_key);
-    for (uint32_t t = t0; t < cnt; t += stride) {
-        const size_t s = (size_t)base + t;
+    const T* mpos = reinterpret_cast<const T*>(buf + m.off_pos);
+    const T* mvel = reinterpret_cast<const T*>(buf + m.off_vel);
+    if (!agg_role) {
+        const uint32_t base = src == 0 ? n_own : n_own + cnt_u;
+        const uint32_t kdelta = kdst - hdr[1];               // sender's key frame -> this window's (mod 2^32)
+        const uint32_t t0 = bx * blockDim.x + threadIdx.x, stride = per * blockDim.x;
+        for (uint32_t i = t0 + 1; i <= m.ncs; i += stride) cs[kdst + i] = base + (bad ? 0u : mcs[i]);
+        const int32_t* mid = reinterpret_cast<const int32_t*>(buf + m.off_id);
+        const uint32_t* mkey = reinterpret_cast<const uint32_t*>(buf + m.off_key);
+        for (uint32_t t = t0; t < cnt; t += stride) {
+            const size_t s = (size_t)base + t;
 #pragma unroll
-        for (int d = 0; d < D; ++d) {
-            pos[(size_t)d * cap + s] = mpos[(size_t)d * m.C + t];
-            vel[(size_t)d * cap + s] = mvel[(size_t)d * m.C + t];
+            for (int d = 0; d < D; ++d) {
+                pos[(size_t)d * cap + s] = mpos[(size_t)d * m.C + t];
+                vel[(size_t)d * cap + s] = mvel[(size_t)d * m.C + t];
+            }
+            id[s] = mid[t];
+            key[s] = mkey[t] + kdelta;
         }
-        id[s] = mid[t];
-        key[s] = mkey[t] + kdelta;
+        return;
+    }
+    // ---- aggregates of the halo cells of this side: one 8-lane group per (reference cell, fine row of it) ----
+    constexpr int NC = 1 + 2 * D;
+    const int K = sp.K, kb = sp.kb;
+    const int nfr = D == 2 ? K : K * K;
+    const int gl = threadIdx.x & 7;
+    const uint32_t ngroups = cells_per_side * (uint32_t)nfr;
+    // g0 = first group of this warp (4 groups per warp): the loop condition is warp-uniform, the shuffles below full-mask
+    for (uint32_t g0 = ((uint32_t)bx * blockDim.x + (threadIdx.x & ~31u)) >> 3; g0 < ngroups; g0 += ((uint32_t)per * blockDim.x) >> 3) {
+        const uint32_t g = g0 + ((threadIdx.x & 31u) >> 3);
+        const bool live = g < ngroups;
+        const uint32_t cl = live ? g / (uint32_t)nfr : 0u;
+        const int part = live ? (int)(g - cl * (uint32_t)nfr) : 0;
+        const uint32_t c = halo_cell0 + (uint32_t)src * cells_per_side + cl;
+        int cc[D];
+        unlin_cell<D>(sp.dims, c, cc);
+        const FineRows fr = fine_rows<D>(sp.dims, kb, cc[1], D == 3 ? cc[2] : 0);
+        const uint32_t i0 = fr.base[part] + ((uint32_t)cc[0] << kb) - kdst;     // index into the message's cell_start slice
+        uint32_t b = 0, e = 0;
+        if (live && !bad) { b = min(mcs[i0], cnt); e = min(mcs[i0 + (uint32_t)K], cnt); }
+        cc[D - 1] = local_to_global_last<T, D>(sp, cc[D - 1]);                   // centres are global
+        T acc[2 * D];
+#pragma unroll
+        for (int d = 0; d < 2 * D; ++d) acc[d] = T(0);
+        for (uint32_t t = b + gl; t < e; t += 8) {
+#pragma unroll
+            for (int d = 0; d < D; ++d) {
+                const T centre = sp.spacing * ((T)(cc[d] + 1) - T(0.5));
+                acc[d] += mpos[(size_t)d * m.C + t] - centre;
+                acc[D + d] += mvel[(size_t)d * m.C + t];
+            }
+        }
+#pragma unroll
+        for (int d = 0; d < 2 * D; ++d) {
+            acc[d] += __shfl_xor_sync(0xffffffffu, acc[d], 4);
+            acc[d] += __shfl_xor_sync(0xffffffffu, acc[d], 2);
+            acc[d] += __shfl_xor_sync(0xffffffffu, acc[d], 1);
+        }
+        if (live && gl == 0) {
+            T* dst = agg + (size_t)part * NC * agg_stride + c;
+            dst[0] = (T)(e - b);
+#pragma unroll
+            for (int d = 0; d < 2 * D; ++d) dst[(size_t)(1 + d) * agg_stride] = acc[d];
+        }
     }
 }
 
@@ -287,6 +353,8 @@ void ab_comm_free(ab_handle* h) {
     if (c->ipc_upper && c->ipc_upper != c->ipc_lower) cudaIpcCloseMemHandle(c->ipc_upper);
     if (c->ipc_block) cudaFree(c->ipc_block);
     if (c->h_counts) cudaFreeHost(c->h_counts);
+    if (c->d_wait) cudaFree(c->d_wait);
+    if (c->d_align) cudaFree(c->d_align);
     if (c->ev_packed) cudaEventDestroy(c->ev_packed);
     if (c->ev_consumed) cudaEventDestroy(c->ev_consumed);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
@@ -390,27 +458,32 @@ static int transfer(ab_handle* h) {
     return AB_OK;
 }
 
-template <class E, int D>
+template <class T, int D>
 static int unpack_t(ab_handle* h, bool want_agg) {
     ab_comm* c = h->comm;
     const int cur = h->cur;
     const uint32_t ncs = (uint32_t)(AB_HALO_W * keys_per_layer(h));
     const uint32_t kown = (uint32_t)(h->win_nl * keys_per_layer(h));
-    const MsgLayout m = msg_layout(D, sizeof(E), c->cap_agents, ncs);
-    const int nb = (int)std::min<int64_t>(std::max<int64_t>((std::max<int64_t>(c->cap_agents / 4, ncs) + 255) / 256, 1), 592);
+    const MsgLayout m = msg_layout(D, sizeof(T), c->cap_agents, ncs);
+    const int nbc = (int)std::min<int64_t>(std::max<int64_t>((std::max<int64_t>(c->cap_agents / 4, ncs) + 255) / 256, 1), 592);
+    const int64_t cpl = cells_per_layer(h);
+    const int nfr = D == 2 ? h->K : h->K * h->K;
+    int nba = 0;
+    if (want_agg) {
+        if (!h->cell_agg) return ab_fail(h, AB_ERR_STATE, "halo aggregates requested before the re-sort produced the owned ones");
+        nba = (int)std::min<int64_t>(std::max<int64_t>((AB_HALO_W * cpl * nfr * 8 + 255) / 256, 1), 1184);
+        h->agg_epoch++;
+    }
     {
         AB_LAUNCH(h, "k_halo_unpack");
-        k_halo_unpack<E, D><<<dim3(nb, 2), 256, 0, h->stream>>>(m, kown, h->cell_start, (E*)h->fields[0].buf[cur],
-                                                               (E*)h->fields[1].buf[cur], h->id[cur], h->key[cur], h->cap,
+        k_halo_unpack<T, D><<<dim3(2 * nbc + 2 * nba), 256, 0, h->stream>>>(make_space<T, D>(h), m, kown, h->cell_start, (T*)h->fields[0].buf[cur],
+                                                               (T*)h->fields[1].buf[cur], h->id[cur], h->key[cur], h->cap,
                                                                c->ipc_on ? ipc_slot(c->ipc_block, c->ipc_stride, c->cur_par, 0) : (const char*)c->recvbuf[0],
                                                                c->ipc_on ? ipc_slot(c->ipc_block, c->ipc_stride, c->cur_par, 1) : (const char*)c->recvbuf[1], h->d_err,
                                                                c->ipc_on ? ipc_flag(c->ipc_block, c->ipc_stride, c->cur_par, 0) : nullptr,
                                                                c->ipc_on ? ipc_flag(c->ipc_block, c->ipc_stride, c->cur_par, 1) : nullptr,
-                                                               (uint32_t)c->exchanges);
-    }
-    if (want_agg) {
-        const int64_t cpl = cells_per_layer(h);
-        AB_TRY(ab_agg_range(h, (int64_t)h->win_nl * cpl, (int64_t)2 * AB_HALO_W * cpl));
+                                                               (uint32_t)c->exchanges, nbc, nba, (T*)h->cell_agg, (int64_t)h->ncells,
+                                                               (uint32_t)(h->win_nl * cpl), (uint32_t)(AB_HALO_W * cpl), c->d_wait);
     }
     return AB_OK;
 }
@@ -422,8 +495,8 @@ int ab_comm_pack(ab_handle* h) {
 }
 int ab_comm_transfer(ab_handle* h) { return transfer(h); }
 int ab_comm_unpack(ab_handle* h, bool want_agg) {
-    if (h->tsize == 8) return h->D == 2 ? unpack_t<uint64_t, 2>(h, want_agg) : unpack_t<uint64_t, 3>(h, want_agg);
-    return h->D == 2 ? unpack_t<uint32_t, 2>(h, want_agg) : unpack_t<uint32_t, 3>(h, want_agg);
+    if (h->tsize == 8) return h->D == 2 ? unpack_t<double, 2>(h, want_agg) : unpack_t<double, 3>(h, want_agg);
+    return h->D == 2 ? unpack_t<float, 2>(h, want_agg) : unpack_t<float, 3>(h, want_agg);
 }
 bool ab_comm_local(const ab_handle* h) { return h->comm && h->comm->peer_lower; }
 
@@ -498,12 +571,17 @@ int ab_comm_init(ab_handle* h, int rank, int nranks, const void* nccl_unique_id)
     c->lower = (rank + nranks - 1) % nranks;
     c->upper = (rank + 1) % nranks;
     if (cudaMallocHost((void**)&c->h_counts, 2 * sizeof(uint32_t)) != cudaSuccess) { delete c; return ab_fail(h, AB_ERR_CUDA, "cudaMallocHost failed"); }
+    if (cudaMalloc((void**)&c->d_wait, 2 * sizeof(unsigned long long)) != cudaSuccess || cudaMemset(c->d_wait, 0, 2 * sizeof(unsigned long long)) != cudaSuccess ||
+        cudaMalloc((void**)&c->d_align, 2 * sizeof(int32_t)) != cudaSuccess || cudaMemset(c->d_align, 0, 2 * sizeof(int32_t)) != cudaSuccess) {
+        cudaFreeHost(c->h_counts); if (c->d_wait) cudaFree(c->d_wait); if (c->d_align) cudaFree(c->d_align); delete c;
+        return ab_fail(h, AB_ERR_CUDA, "cudaMalloc failed");
+    }
     if (nccl_unique_id) {
-        if (!nccl_load()) { cudaFreeHost(c->h_counts); delete c; return ab_fail(h, AB_ERR_COMM, g_nccl_err); }
+        if (!nccl_load()) { cudaFreeHost(c->h_counts); cudaFree(c->d_wait); cudaFree(c->d_align); delete c; return ab_fail(h, AB_ERR_COMM, g_nccl_err); }
         nccl_uid_t id;
         memcpy(&id, nccl_unique_id, 128);
         int r = g_nccl.CommInitRank(&c->comm, nranks, id, rank);
-        if (r != 0) { cudaFreeHost(c->h_counts); delete c; return ab_fail(h, AB_ERR_COMM, std::string("ncclCommInitRank: ") + g_nccl.GetErrorString(r)); }
+        if (r != 0) { cudaFreeHost(c->h_counts); cudaFree(c->d_wait); cudaFree(c->d_align); delete c; return ab_fail(h, AB_ERR_COMM, std::string("ncclCommInitRank: ") + g_nccl.GetErrorString(r)); }
     }
     h->comm = c;
     h->win_gdl = gdl; h->win_goff = first; h->win_nl = nl; h->win_W = AB_HALO_W;
@@ -595,6 +673,51 @@ int ab_comm_ipc_import(ab_handle* h, const void* lower64, const void* upper64) {
     return AB_OK;
 }
 int ab_comm_direct(const ab_handle* h) { return h && h->comm && h->comm->ipc_on ? 1 : 0; }
+
+// Halo refresh outside a step (collective: every rank calls it): after ab_upload_local replaced the owned agents'
+// columns from the host, the window's halo layers are rebuilt from the neighbours' boundary layers — index build on
+// what the handle holds, then the same pack / transfer / unpack as inside a step.
+int ab_comm_exchange(ab_handle* h) {
+    if (!h || !h->comm || !h->win_W) return ab_fail(h, AB_ERR_STATE, "handle is not sharded");
+    if (ab_comm_local(h)) return ab_fail(h, AB_ERR_STATE, "in-process slabs exchange inside ab_step_flock_group");
+    AB_CUDA(h, cudaSetDevice(h->device));
+    h->index_valid = false;
+    AB_TRY(ab_ensure_index(h));
+    AB_TRY(ab_comm_pack(h));
+    AB_TRY(ab_comm_transfer(h));
+    AB_TRY(ab_comm_unpack(h, false));
+    h->agg_valid = false;
+    h->pairs_n = -1;
+    AB_TRY(ab_check_device_errors_now(h));
+    return ab_comm_refresh_counts(h);
+}
+
+// Start alignment for timed multi-rank runs: queues a one-word all-reduce on the handle's stream, so whatever the
+// caller queues next starts on every rank when the LAST rank has reached this point on the device (a host-side
+// barrier leaves the ranks' launch skew inside the timed region).  No-op without a communicator.
+int ab_comm_align(ab_handle* h) {
+    if (!h || !h->comm || !h->win_W) return ab_fail(h, AB_ERR_STATE, "handle is not sharded");
+    ab_comm* c = h->comm;
+    if (!c->comm) return AB_OK;
+    AB_CUDA(h, cudaSetDevice(h->device));
+    AB_NCCL(h, g_nccl.AllReduce(c->d_align, c->d_align + 1, 1, 2 /* ncclInt32 */, 0 /* ncclSum */, c->comm, h->stream));
+    return AB_OK;
+}
+
+// Time this rank's k_halo_unpack launches have spent waiting for the neighbours' "message delivered" flags since
+// the last reset (direct exchange only): tells rank skew from work in a multi-GPU step time.
+int ab_comm_wait_stats(ab_handle* h, double* wait_us, int64_t* exchanges, int reset) {
+    if (!h || !h->comm || !h->win_W) return ab_fail(h, AB_ERR_STATE, "handle is not sharded");
+    ab_comm* c = h->comm;
+    AB_CUDA(h, cudaSetDevice(h->device));
+    unsigned long long v[2] = {0, 0};
+    AB_CUDA(h, cudaMemcpyAsync(v, c->d_wait, sizeof(v), cudaMemcpyDeviceToHost, h->stream));
+    if (reset) AB_CUDA(h, cudaMemsetAsync(c->d_wait, 0, sizeof(v), h->stream));
+    AB_CUDA(h, cudaStreamSynchronize(h->stream));
+    if (wait_us) *wait_us = (double)v[0] * 1e-3;
+    if (exchanges) *exchanges = (int64_t)v[1];
+    return AB_OK;
+}
 
 int ab_comm_set_capacity(ab_handle* h, int64_t halo_agents) {
     if (!h || !h->comm) return ab_fail(h, AB_ERR_STATE, "handle is not sharded");

@@ -571,7 +571,8 @@ int ab_destroy(ab_handle* h) {
     ab_grid_free(h);
     free_population(h);
     void* ptrs[] = {h->cell_count, h->cell_start, h->scan_status, h->scan_ticket, h->d_err, h->scratch, h->scratch2,
-                    h->cell_agg, h->cell_agg1, h->cell_M, h->pairs_offsets, h->grid_ids, h->cell_start_alt, h->step_mask};
+                    h->cell_agg, h->cell_agg1, h->cell_M, h->pairs_offsets, h->grid_ids, h->cell_start_alt, h->step_mask,
+                    h->tile_count, h->tile_base};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (h->h_err) cudaFreeHost(h->h_err);
     if (h->ev0) cudaEventDestroy(h->ev0);

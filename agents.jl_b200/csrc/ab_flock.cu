@@ -459,7 +459,7 @@ static int launch_fine(ab_handle* h, const SpaceDev<T, D>& sp, const FlockU<T>& 
     AB_LAUNCH(h, EXACT ? "k_flock_fine_exact" : "k_flock_fine");
     const uint32_t own_keys = h->win_W ? (uint32_t)((h->nfine / h->dims[D - 1]) * h->win_nl) : 0u;
 #define FINE_ARGS sp, u, (const T*)h->fields[0].buf[cur], (const T*)h->fields[1].buf[cur], h->key[cur], h->cell_start, \
-        (const T*)h->cell_M, (int64_t)h->ncells, h->cap, n, (T*)h->tmp_pos, (T*)h->tmp_vel, h->newkey, h->cell_count, \
+        (const T*)h->cell_M, (int64_t)h->ncells, h->cap, n, (T*)h->tmp_pos, (T*)h->tmp_vel, h->newkey, make_tilegeo(h), \
         h->id[cur], ncount, h->d_err, h->win_W ? h->cell_start + h->nfine : nullptr, phase, own_keys
     bool done = false;
     if constexpr (!EXACT && D == 2) {
@@ -512,6 +512,7 @@ static int flock_prepare(ab_handle* h, const ab_flock_params* p, FlockCtx<T, D>*
     u.active = h->step_mask_cur;
     if (fine) AB_TRY(ab_set_refine(h, plan.K));
     AB_TRY(ab_ensure_index(h));
+    if (fine) AB_TRY(ab_resort_plan(h));
     cx->sp = make_space<T, D>(h);
     if (fine && !exact) {
         AB_TRY(ab_ensure_agg(h));

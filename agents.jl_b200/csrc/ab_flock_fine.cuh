@@ -178,8 +178,9 @@ __device__ __forceinline__ int grid_radius_12(const SpaceDev<T, D>& sp, const T*
 #pragma unroll
     for (int d = 0; d < D; ++d) {
         const double centre = sp.spacing_d * ((double)(c0[d] + 1) - 0.5);
-        const double direct = fabs((double)p[d] - centre);
-        const double m = sp.periodic[d] ? fmin(direct, sp.extent_d[d] - direct) : direct;
+        // c0 is the bird's own cell: direct <= spacing / 2 (+ rounding) and the plan guarantees >= 6 cells per axis,
+        // so min(direct, extent - direct) of continuous.jl:119-121 is `direct`, bit for bit
+        const double m = fabs((double)p[d] - centre);
         const double sq = m * m;
         s2 = (d == 0) ? sq : s2 + sq;
     }
@@ -213,10 +214,10 @@ __device__ __forceinline__ bool pos2cell0_fast(const SpaceDev<T, D>& sp, const T
 // reach-1 sweep keeps its compile-time trip counts (a run-time reach cost the 3-D sweep 13 %).
 template <class T, int D, bool EXACT, bool REACH2 = false>
 __global__ void __launch_bounds__(FINE_TB, FINE_MINB)
-k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T* __restrict__ vel,
+k_flock_fine(const __grid_constant__ SpaceDev<T, D> sp, const __grid_constant__ FlockU<T> fp, const T* __restrict__ pos, const T* __restrict__ vel,
              const uint32_t* __restrict__ key, const uint32_t* __restrict__ cs, const T* __restrict__ M,
              int64_t ncells, int64_t cap, int n, T* __restrict__ npos, T* __restrict__ nvel,
-             uint32_t* __restrict__ newkey, uint32_t* __restrict__ cell_count, const int32_t* __restrict__ ids,
+             uint32_t* __restrict__ newkey, TileGeo tg, const int32_t* __restrict__ ids,
              int32_t* __restrict__ ncount, int* __restrict__ err, const uint32_t* __restrict__ nslots, int phase,
              uint32_t own_keys) {
     constexpr int NC = FineCfg<D>::NC;
@@ -229,7 +230,7 @@ k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T
     const int K = sp.K, kb = sp.kb;
     int f[D], c[D], cg[D];
     const uint32_t k = key[s];
-    key_to_fine<T, D>(sp, k, f);
+    key_to_fine_fast<T, D>(sp, k, f);
 #pragma unroll
     for (int d = 0; d < D; ++d) cg[d] = c[d] = f[d] >> kb;
     if (sp.W) {
@@ -250,7 +251,7 @@ k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T
 #pragma unroll
         for (int d = 0; d < D; ++d) { npos[(size_t)d * cap + s] = p[d]; nvel[(size_t)d * cap + s] = v[d]; }
         newkey[s] = k;
-        atomicAdd(&cell_count[k], 1u);
+        count_new_key(tg, k, D == 3 ? (uint32_t)f[D - 1] * (uint32_t)(sp.dims[1] << kb) + (uint32_t)f[1] : (uint32_t)f[1], (uint32_t)f[0]);
         if (ncount) ncount[ids[s]] = 0;
         return;
     }
@@ -315,11 +316,12 @@ k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T
 #pragma unroll
                     for (int d = 0; d < D; ++d) { cohere[d] += h[d]; match[d] += vel[(size_t)d * cap + j]; }
                 }
-                // the bird itself (h == 0) passes this test and contributes exactly nothing
-                if (d2 < sep2) {                                                         // flock.jl:93
+                // the bird itself (h == 0) passes this test and contributes exactly nothing.
+                // separate -= h  as  fma(-w, h, separate), w = 1 or 0: one rounding, the same value as the subtraction
+                // (w * h is exact), without the select pairs a predicated update compiles to
+                const T wgt = d2 < sep2 ? T(1) : T(0);                                   // flock.jl:93
 #pragma unroll
-                    for (int d = 0; d < D; ++d) separate[d] -= h[d];
-                }
+                for (int d = 0; d < D; ++d) separate[d] = fma(-wgt, h[d], separate[d]);
             }
         };
         auto sweep = [&](uint32_t jb, uint32_t je, int wrap) {
@@ -390,12 +392,14 @@ k_flock_fine(SpaceDev<T, D> sp, FlockU<T> fp, const T* __restrict__ pos, const T
     int nc[D];
     if (!pos2cell0_fast<T, D>(sp, np_, nc)) atomicOr(err, AB_EF_NUMERIC);
     bool inwin = true;
-    uint32_t nk = device_key<T, D>(sp, np_, nc, &inwin);
-    if (!inwin) { atomicOr(err, AB_EF_OVERFLOW); nk = 0; }
+    uint32_t nfrow = 0;
+    uint32_t nk = device_key<T, D>(sp, np_, nc, &inwin, &nfrow);
+    if (!inwin) { atomicOr(err, AB_EF_OVERFLOW); nk = 0; nfrow = 0; }
 #pragma unroll
     for (int d = 0; d < D; ++d) { npos[(size_t)d * cap + s] = np_[d]; nvel[(size_t)d * cap + s] = nv[d]; }
     newkey[s] = nk;
-    atomicAdd(&cell_count[nk], 1u);       // histogram of the new keys (k_scan turns it into the next cell_start)
+    // histogram of the new keys per fine cell and per re-sort tile (the re-sort turns them into the next cell_start)
+    count_new_key(tg, nk, nfrow, nk - nfrow * (uint32_t)(sp.dims[0] << kb));
     if (ncount) ncount[ids[s]] = N;
 }
 

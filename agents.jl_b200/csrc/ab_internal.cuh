@@ -124,6 +124,14 @@ struct ab_handle {
     bool overlap_halo = false;         // sharded flock step: interior sweep while the halo travels — measured slower, AB_OVERLAP=1 enables
     bool fine4 = false;                // quarter-cell refinement (K = 4) on the 2-D flock path: correct, measured slower (AB_FINE4=1 enables)
     int rs_target = 100;               // average agents per re-sort tile (tuning knob)
+    // re-sort tiles (ab_resort_plan): the fused step kernels count the new keys per fine cell AND per tile, a small
+    // scan of the tile totals gives every tile its output range, and the tile's own warp turns its cell counts into
+    // the new cell_start (there is no scan over the fine cells on this path)
+    int rs_tw = 0, rs_tpr = 0, rs_ntiles = 0, rs_nrows = 0;
+    uint32_t rs_magic = 0;             // ceil(2^32 / rs_tw): fx / tw == umulhi(fx, magic) for fx < 65536
+    uint32_t* tile_count = nullptr;    // rs_ntiles (padded to the scan tile; zero between uses)
+    uint32_t* tile_base = nullptr;     // rs_ntiles + 1
+    size_t tile_cap = 0;
 
     // single-pass scan state
     unsigned long long* scan_status = nullptr;
@@ -203,6 +211,7 @@ int ab_reindex_from(ab_handle* h, const void* src_pos, const void* src_vel, bool
 int ab_permute_extra_fields(ab_handle* h);     // applies h->perm (new slot -> old slot) to user columns, cur -> cur^1
 bool ab_resort_applicable(const ab_handle* h);
 int ab_resort_tiled(ab_handle* h, const void* src_pos, const void* src_vel, bool want_agg);
+int ab_resort_plan(ab_handle* h);              // tile geometry of the next tiled re-sort (before the step kernel that counts the keys)
 int ab_ensure_agg(ab_handle* h);
 int ab_agg_range(ab_handle* h, int64_t cell0, int64_t ncell);
 int ab_run_scan(ab_handle* h, uint32_t* dst);
@@ -255,6 +264,33 @@ __device__ __forceinline__ void ab_dep_wait() {
     asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
+// Tile geometry of the re-sort as the fused step kernels see it: they histogram the new keys per fine cell
+// (cell_count) and per tile (tile_count).  Tile = tw consecutive fine cells of one fine row; only the first
+// `nrows` fine rows are re-sorted (all of them, or the owned ones of a slab window).
+struct TileGeo {
+    uint32_t* cell_count;
+    uint32_t* tile_count;
+    uint32_t tpr, magic, nrows;
+};
+static inline TileGeo make_tilegeo(const ab_handle* h) {
+    TileGeo g;
+    g.cell_count = h->cell_count; g.tile_count = h->tile_count;
+    g.tpr = (uint32_t)h->rs_tpr; g.magic = h->rs_magic; g.nrows = (uint32_t)h->rs_nrows;
+    return g;
+}
+#ifdef __CUDACC__
+// one agent's new key: fine row `frow`, fine x `fx` (< 65536).  The tile counter is bumped once per group of lanes
+// that share the tile (lanes of a warp are neighbours in space: one or two groups).
+__device__ __forceinline__ void count_new_key(const TileGeo& g, uint32_t key, uint32_t frow, uint32_t fx) {
+    if (frow >= g.nrows) return;                              // not re-sorted here (halo rows of a slab window)
+    atomicAdd(&g.cell_count[key], 1u);
+    const uint32_t tile = frow * g.tpr + __umulhi(fx, g.magic);
+    const unsigned act = __activemask();
+    const unsigned m = __match_any_sync(act, tile);
+    if ((m & (0u - m)) == (1u << (threadIdx.x & 31))) atomicAdd(&g.tile_count[tile], (uint32_t)__popc(m));
+}
+#endif
+
 template <class... KArgs, class... Args>
 static inline cudaError_t ab_launch_chain(bool pdl, void (*kern)(KArgs...), dim3 grid, dim3 block, cudaStream_t st, Args... args) {
     cudaLaunchConfig_t cfg = {};
@@ -289,6 +325,10 @@ template <class T, int D> struct SpaceDev {
     // STORES: nl owned layers, then W upper-halo layers, then W lower-halo layers, so local layer
     // l = (global layer - goff) mod (nl + 2W) and the ordinary periodic index arithmetic on dims[]
     // finds every neighbour.  Positions, extents and cell centres stay GLOBAL (bit-exact pos2cell).
+    // division of a device key by the fine row lengths (dims[d] << kb, d < D-1) without a divide instruction
+    // (Granlund-Montgomery round-up multiplier): q = (t + ((n - t) >> s1)) >> s2 with t = umulhi(m, n)
+    uint32_t div_m[D];
+    uint8_t div_s1[D], div_s2[D];
     int gdl;      // global number of layers (== dims[D-1] when W == 0)
     int goff;     // global layer of local layer 0
     int nl;       // owned layers (== dims[D-1] when W == 0)
@@ -310,6 +350,14 @@ template <class T, int D> static inline SpaceDev<T, D> make_space(const ab_handl
     s.K = h->K;
     s.kb = h->kb;
     s.ksh = h->ksh;
+    for (int d = 0; d < D; ++d) {
+        const uint32_t dv = (uint32_t)h->dims[d] << h->kb;
+        int l = 0;
+        while ((1ull << l) < dv) ++l;                                   // ceil(log2 dv)
+        s.div_m[d] = (uint32_t)(((1ull << 32) * ((1ull << l) - dv)) / dv + 1);
+        s.div_s1[d] = (uint8_t)(l < 1 ? l : 1);
+        s.div_s2[d] = (uint8_t)(l > 1 ? l - 1 : 0);
+    }
     s.W = h->win_W;
     s.gdl = h->win_W ? h->win_gdl : h->dims[D - 1];
     s.goff = h->win_W ? h->win_goff : 0;
@@ -407,7 +455,8 @@ template <class T, int D> __device__ __forceinline__ int global_to_local_last(co
 // `c` are GLOBAL reference-cell coordinates (pos2cell0); *inwin (optional) reports whether the cell lies in
 // this handle's slab window.
 template <class T, int D>
-__device__ __forceinline__ uint32_t device_key(const SpaceDev<T, D>& sp, const T* p, const int* c, bool* inwin = nullptr) {
+__device__ __forceinline__ uint32_t device_key(const SpaceDev<T, D>& sp, const T* p, const int* c, bool* inwin = nullptr,
+                                               uint32_t* frow = nullptr) {
     uint32_t f[D];
     bool ok = true;
 #pragma unroll
@@ -428,7 +477,10 @@ __device__ __forceinline__ uint32_t device_key(const SpaceDev<T, D>& sp, const T
     }
     uint32_t lin = f[D - 1];
 #pragma unroll
-    for (int d = D - 2; d >= 0; --d) lin = lin * ((uint32_t)sp.dims[d] << sp.kb) + f[d];
+    for (int d = D - 2; d >= 0; --d) {
+        if (d == 0 && frow) *frow = lin;                     // fine row = key / fd0, fine x = f[0] = key - frow * fd0
+        lin = lin * ((uint32_t)sp.dims[d] << sp.kb) + f[d];
+    }
     if (inwin) *inwin = ok;
     return lin;
 }
@@ -439,6 +491,19 @@ __device__ __forceinline__ void key_to_fine(const SpaceDev<T, D>& sp, uint32_t k
     for (int d = 0; d < D - 1; ++d) {
         const uint32_t fd = (uint32_t)sp.dims[d] << sp.kb;
         const uint32_t q = key / fd;
+        f[d] = (int)(key - q * fd);
+        key = q;
+    }
+    f[D - 1] = (int)key;
+}
+// the same with multiply-high instead of the divide (hot kernels)
+template <class T, int D>
+__device__ __forceinline__ void key_to_fine_fast(const SpaceDev<T, D>& sp, uint32_t key, int* f) {
+#pragma unroll
+    for (int d = 0; d < D - 1; ++d) {
+        const uint32_t fd = (uint32_t)sp.dims[d] << sp.kb;
+        const uint32_t t = __umulhi(sp.div_m[d], key);
+        const uint32_t q = (t + ((key - t) >> sp.div_s1[d])) >> sp.div_s2[d];
         f[d] = (int)(key - q * fd);
         key = q;
     }

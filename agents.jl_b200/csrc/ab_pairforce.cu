@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(128, PF_MINB)
 k_pf_fine(SpaceDev<T, D> sp, PfU<T> u, const T* __restrict__ pos, const T* __restrict__ vel, const T* __restrict__ rad,
           const T* __restrict__ kk, const T* __restrict__ mass, const uint32_t* __restrict__ key,
           const uint32_t* __restrict__ cs, int64_t cap, int n, T* __restrict__ npos, T* __restrict__ nvel,
-          uint32_t* __restrict__ newkey, uint32_t* __restrict__ rank, uint32_t* __restrict__ cell_count,
+          uint32_t* __restrict__ newkey, uint32_t* __restrict__ rank, TileGeo tg,
           int* __restrict__ far, int* __restrict__ err) {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
@@ -215,11 +215,18 @@ k_pf_fine(SpaceDev<T, D> sp, PfU<T> u, const T* __restrict__ pos, const T* __res
         if (dc > 1) moved_far = true;
     }
     if (moved_far) atomicOr(far, 1);
-    const uint32_t nk = device_key<T, D>(sp, np_, nc);
+    uint32_t nfrow = 0;
+    const uint32_t nk = device_key<T, D>(sp, np_, nc, nullptr, &nfrow);
 #pragma unroll
     for (int d = 0; d < D; ++d) { npos[(size_t)d * cap + s] = np_[d]; nvel[(size_t)d * cap + s] = nv[d]; }
     newkey[s] = nk;
-    rank[s] = atomicAdd(&cell_count[nk], 1u);
+    // arrival rank (used only when the step falls back to the generic re-index) + per-tile histogram of the tiled re-sort
+    rank[s] = atomicAdd(&tg.cell_count[nk], 1u);
+    {
+        const uint32_t tile = nfrow * tg.tpr + __umulhi(nk - nfrow * (uint32_t)sp.dims[0], tg.magic);
+        const unsigned m = __match_any_sync(__activemask(), tile);
+        if ((m & (0u - m)) == (1u << (threadIdx.x & 31))) atomicAdd(&tg.tile_count[tile], (uint32_t)__popc(m));
+    }
 }
 
 // generic path, kernel 1: own force into fown, one-sided reactions into freact (atomics)
@@ -306,6 +313,7 @@ static int pf_steps_t(ab_handle* h, const ab_pairforce_params* p, int64_t nsteps
     for (int d = 0; d < D; ++d) if (h->dims[d] < 3) fine = false;
     if (fine) AB_TRY(ab_set_refine(h, 1));
     AB_TRY(ab_ensure_index(h));
+    if (fine) AB_TRY(ab_resort_plan(h));
     SpaceDev<T, D> sp = make_space<T, D>(h);
     AB_CUDA(h, cudaEventRecord(h->ev0, h->stream));
     for (int64_t st = 0; st < nsteps; ++st) {
@@ -319,7 +327,7 @@ static int pf_steps_t(ab_handle* h, const ab_pairforce_params* p, int64_t nsteps
             {
                 AB_LAUNCH(h, "k_pf_fine");
                 k_pf_fine<T, D><<<ab_blocks(n, TB), TB, 0, h->stream>>>(sp, u, pos, vel, rad, kk, mass, h->key[cur], h->cell_start, h->cap, n,
-                                                                        (T*)h->tmp_pos, (T*)h->tmp_vel, h->newkey, h->rank, h->cell_count,
+                                                                        (T*)h->tmp_pos, (T*)h->tmp_vel, h->newkey, h->rank, make_tilegeo(h),
                                                                         h->d_err + 1, h->d_err);
             }
             // did anybody move further than one cell?  (then the tiled re-sort cannot find it)
@@ -327,6 +335,7 @@ static int pf_steps_t(ab_handle* h, const ab_pairforce_params* p, int64_t nsteps
             AB_CUDA(h, cudaStreamSynchronize(h->stream));
             if (h->h_err[1]) {
                 AB_CUDA(h, cudaMemsetAsync(h->d_err + 1, 0, sizeof(int), h->stream));
+                AB_CUDA(h, cudaMemsetAsync(h->tile_count, 0, (size_t)h->rs_ntiles * sizeof(uint32_t), h->stream));   // not consumed by a tiled re-sort
                 AB_TRY(ab_reindex_from(h, h->tmp_pos, h->tmp_vel, true));
             } else {
                 AB_TRY(ab_resort_tiled(h, h->tmp_pos, h->tmp_vel, false));

@@ -44,6 +44,7 @@
 #define RS_THREADS (RS_WARPS * 32)
 #define RS_MAXSEG 27            // 9 source rows x (main run + 2 periodic wrap cells)
 #define RS_TW_MAX 256           // fine cells per tile (cursor array per warp)
+#define RS_RING 64              // (source slot, output slot) pairs waiting to be moved, per warp
 
 struct ResortArgs {
     int tw, tpr, ntiles, nrows;
@@ -53,7 +54,7 @@ struct ResortArgs {
 #ifdef RS_MINB
 #define RS_BOUNDS __launch_bounds__(RS_THREADS, RS_MINB)
 #else
-#define RS_BOUNDS __launch_bounds__(RS_THREADS)      // (an explicit minimum of 1 block lets ptxas take 91-104 registers: slower)
+#define RS_BOUNDS __launch_bounds__(RS_THREADS)
 #endif
 #ifndef RS_G2D
 #define RS_G2D 4
@@ -62,20 +63,30 @@ struct ResortArgs {
 #define RS_AGG_UNROLL 4
 #endif
 constexpr int kRsAggUnroll = RS_AGG_UNROLL;     // crowded-cell aggregate loop: loads of several iterations in flight
+// Phases of a tile (one warp):
+//   0  output range from the scanned tile totals; the tile's cell counts -> cursors (warp scan) -> new cell_start;
+//      the counts are zeroed behind the read (the histogram is ready for the next step)
+//   1  stream the keys of the 3^D source rows (G chunks of 32 in flight), rank the agents that fall into the tile
+//      (match.any + per-cell cursor: final output slot at once) and queue (source slot, output slot) in a ring
+//   2  whenever 32 pairs wait: move 32 agents with all lanes busy (gathered loads, stores clustered by cell)
+//   3  aggregates of the tile's cells
 template <class T, int D, int G>
 __global__ void RS_BOUNDS
 k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, const uint32_t* __restrict__ newkey,
          const int32_t* __restrict__ id_old, const T* __restrict__ src_pos, const T* __restrict__ src_vel,
          int64_t cap, T* dst_pos, T* dst_vel, int32_t* __restrict__ id_new,
-         uint32_t* __restrict__ key_new, const uint32_t* __restrict__ cs_new, int32_t* __restrict__ perm,
+         uint32_t* __restrict__ key_new, uint32_t* __restrict__ cell_count, const uint32_t* __restrict__ tile_base,
+         uint32_t* __restrict__ cs_new, int32_t* __restrict__ perm,
          T* __restrict__ agg, int64_t agg_stride, int* __restrict__ err) {
     __shared__ uint32_t s_beg[RS_WARPS][RS_MAXSEG];
     __shared__ uint32_t s_pre[RS_WARPS][RS_MAXSEG + 1];
     __shared__ uint32_t s_cur[RS_WARPS][RS_TW_MAX];
+    __shared__ uint2 s_ring[RS_WARPS][RS_RING];
 
     ab_dep_wait();
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const unsigned lt = (1u << lane) - 1u;
     const int tile = blockIdx.x * RS_WARPS + w;
     if (tile >= a.ntiles) return;                                  // warp-uniform; no CTA barriers below
     const int frow = tile / a.tpr, seg_x = tile - frow * a.tpr;    // fine row, segment of it
@@ -88,10 +99,40 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, c
     const uint32_t kend = kbeg + (uint32_t)fc;
     const int fy0 = D == 2 ? frow : frow % fd1;
     const int fz0 = D == 2 ? 0 : frow / fd1;
-    const uint32_t base = cs_new[kbeg];
-    const uint32_t total = cs_new[kend] - base;
+    const uint32_t base = tile_base[tile];
+    const uint32_t total = tile_base[tile + 1] - base;
+    if (tile == a.ntiles - 1 && lane == 0) cs_new[kend] = base + total;      // end of the re-sorted key range
 
-    if (total != 0) {
+    if (total == 0) {
+        for (int i = lane; i < fc; i += 32) cs_new[(size_t)kbeg + i] = base;
+    } else {
+    // ---- phase 0: lane l owns the cells [l * ch, (l + 1) * ch) of the tile ----
+    {
+        const int ch = (fc + 31) >> 5;                             // <= 8
+        const int i0 = lane * ch;
+        uint32_t cnt[RS_TW_MAX / 32];
+        uint32_t sum = 0;
+#pragma unroll
+        for (int q = 0; q < RS_TW_MAX / 32; ++q) {
+            cnt[q] = 0;
+            if (q < ch && i0 + q < fc) cnt[q] = cell_count[(size_t)kbeg + i0 + q];
+        }
+#pragma unroll
+        for (int q = 0; q < RS_TW_MAX / 32; ++q) sum += cnt[q];
+        uint32_t inc = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(FULL, inc, o); if (lane >= o) inc += t; }
+        uint32_t run = inc - sum;                                  // agents of the tile in the cells before mine
+#pragma unroll
+        for (int q = 0; q < RS_TW_MAX / 32; ++q) {
+            if (q < ch && i0 + q < fc) {
+                s_cur[w][i0 + q] = run;
+                cs_new[(size_t)kbeg + i0 + q] = base + run;
+                if (cnt[q]) cell_count[(size_t)kbeg + i0 + q] = 0;
+                run += cnt[q];
+            }
+        }
+    }
     // ---- source segments: lane i describes segment i = 3*row + {main, left wrap, right wrap} ----
     constexpr int NROW = D == 2 ? 3 : 9;
     constexpr int NSEG = 3 * NROW;
@@ -119,14 +160,40 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, c
     const uint32_t L = __shfl_sync(FULL, inc, 31);                 // length of the concatenated source sequence
     if (lane < NSEG) { s_beg[w][lane] = sb; s_pre[w][lane] = inc - sl; }
     if (lane == 0) s_pre[w][NSEG] = L;
-    for (int i = lane; i < fc; i += 32) s_cur[w][i] = cs_new[(size_t)kbeg + i] - base;   // cursor = start
     __syncwarp();
 
-    uint32_t found = 0;
+    // moves the agents of ring entries [d0, d0 + nv): all lanes busy
+    auto flush = [&](uint32_t d0, uint32_t nv) {
+        if ((uint32_t)lane < nv) {
+            const uint2 e = s_ring[w][(d0 + lane) & (RS_RING - 1)];
+            const size_t si = e.x, oo = e.y;
+            T pv[2 * D];
+#pragma unroll
+            for (int d = 0; d < D; ++d) pv[d] = src_pos[(size_t)d * cap + si];
+            if (a.has_vel) {
+#pragma unroll
+                for (int d = 0; d < D; ++d) pv[D + d] = src_vel[(size_t)d * cap + si];
+            }
+            const int32_t idv = id_old[si];
+            const uint32_t kv = newkey[si];
+#pragma unroll
+            for (int d = 0; d < D; ++d) dst_pos[(size_t)d * cap + oo] = pv[d];
+            if (a.has_vel) {
+#pragma unroll
+                for (int d = 0; d < D; ++d) dst_vel[(size_t)d * cap + oo] = pv[D + d];
+            }
+            id_new[oo] = idv;
+            key_new[oo] = kv;
+            if (perm) perm[oo] = (int32_t)si;
+        }
+        __syncwarp();                                              // ring entries may be overwritten from here on
+    };
+
+    uint32_t queued = 0, moved = 0;                                // ring counters (warp-uniform)
     int sg = 0;                                                    // this lane's current segment (monotone)
     for (uint32_t v0 = 0; v0 < L; v0 += 32u * G) {
-        uint32_t k[G], s[G], o[G];
-        // phase 1: keys of G chunks (independent coalesced loads)
+        uint32_t k[G], s[G];
+        // keys of G chunks (independent coalesced loads)
 #pragma unroll
         for (int g = 0; g < G; ++g) {
             const uint32_t v = v0 + 32u * g + lane;
@@ -138,57 +205,28 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, c
                 k[g] = newkey[s[g]];
             }
         }
-        // phase 2: stable rank inside the warp + per-cell cursor
+        // stable rank inside the warp + per-cell cursor -> final slot; queue the pair
 #pragma unroll
         for (int g = 0; g < G; ++g) {
             const bool in = k[g] >= kbeg && k[g] < kend;
+            const unsigned bal = __ballot_sync(FULL, in);
+            if (bal == 0) continue;                                // warp-uniform
             const uint32_t lc = in ? k[g] - kbeg : 0xffffffffu;
             const unsigned m = __match_any_sync(FULL, lc);
-            o[g] = 0xffffffffu;
             if (in) {
-                const uint32_t cur = s_cur[w][lc];
-                o[g] = base + cur + __popc(m & ((1u << lane) - 1u));
-                ++found;
+                const uint32_t o = base + s_cur[w][lc] + __popc(m & lt);
+                s_ring[w][(queued + __popc(bal & lt)) & (RS_RING - 1)] = make_uint2(s[g], o);
             }
             __syncwarp();
             if (in && (m >> lane) == 1u) s_cur[w][lc] += __popc(m);      // highest lane of the group advances the cursor
+            queued += __popc(bal);
             __syncwarp();
-        }
-        // phase 3: rows of the matching agents (reads coalesced in s), phase 4: stores
-        T pv[G][2 * D];
-        int32_t idv[G];
-#pragma unroll
-        for (int g = 0; g < G; ++g) {
-            if (o[g] != 0xffffffffu) {
-#pragma unroll
-                for (int d = 0; d < D; ++d) pv[g][d] = src_pos[(size_t)d * cap + s[g]];
-                if (a.has_vel) {
-#pragma unroll
-                    for (int d = 0; d < D; ++d) pv[g][D + d] = src_vel[(size_t)d * cap + s[g]];
-                }
-                idv[g] = id_old[s[g]];
-            }
-        }
-#pragma unroll
-        for (int g = 0; g < G; ++g) {
-            if (o[g] != 0xffffffffu) {
-                const size_t oo = o[g];
-#pragma unroll
-                for (int d = 0; d < D; ++d) dst_pos[(size_t)d * cap + oo] = pv[g][d];
-                if (a.has_vel) {
-#pragma unroll
-                    for (int d = 0; d < D; ++d) dst_vel[(size_t)d * cap + oo] = pv[g][D + d];
-                }
-                id_new[oo] = idv[g];
-                key_new[oo] = k[g];
-                if (perm) perm[oo] = (int32_t)s[g];
-            }
+            if (queued - moved >= 32u) { flush(moved, 32u); moved += 32u; }
         }
     }
+    if (queued != moved) flush(moved, queued - moved);
     // every agent counted into this tile must have been found in the 3^D neighbourhood
-#pragma unroll
-    for (int o2 = 16; o2 > 0; o2 >>= 1) found += __shfl_xor_sync(FULL, found, o2);
-    if (found != total) {
+    if (queued != total) {
         if (lane == 0) atomicOr(err, AB_EF_OVERFLOW);              // an agent left its 3^D neighbourhood
         return;
     }
@@ -369,33 +407,57 @@ static int ensure_agg(ab_handle* h) {
     return AB_OK;
 }
 
-template <class T, int D>
-static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool want_agg) {
-    const int cur = h->cur, nxt = cur ^ 1;
-    SpaceDev<T, D> sp = make_space<T, D>(h);
-    ResortArgs a;
-    // tile width (fine cells of one fine row): ~rs_target agents per tile on average, at most
-    // RS_TW_MAX fine cells, a multiple of K so that tiles hold whole reference cells
+// Tile geometry of the next tiled re-sort: ~rs_target agents per tile on average, at most RS_TW_MAX fine cells, a
+// multiple of K so that tiles hold whole reference cells.  Fixed before the step kernel runs (it counts per tile).
+int ab_resort_plan(ab_handle* h) {
+    const int D = h->D;
     const int fd0 = h->dims[0] << h->kb;
+    if (fd0 > 65536) return ab_fail(h, AB_ERR_INVALID, "more than 65536 fine cells per row");
     const double dens = (double)h->n / (double)h->nfine;
     int tw = (int)((double)h->rs_target / (dens > 1e-9 ? dens : 1e-9));
     if (tw > RS_TW_MAX) tw = RS_TW_MAX;
     if (tw < 4) tw = 4;
     if (tw > fd0) tw = fd0;
-    a.tpr = (fd0 + tw - 1) / tw;
-    a.tw = (fd0 + a.tpr - 1) / a.tpr;                 // even split of the row
-    a.tw = (a.tw + h->K - 1) / h->K * h->K;
-    if (a.tw > RS_TW_MAX) a.tw = RS_TW_MAX / h->K * h->K;
-    a.tpr = (fd0 + a.tw - 1) / a.tw;
-    a.nrows = (int)(h->nfine / fd0);
+    int tpr = (fd0 + tw - 1) / tw;
+    tw = (fd0 + tpr - 1) / tpr;                       // even split of the row
+    tw = (tw + h->K - 1) / h->K * h->K;
+    if (tw > RS_TW_MAX) tw = RS_TW_MAX / h->K * h->K;
+    tpr = (fd0 + tw - 1) / tw;
+    int64_t nrows = h->nfine / fd0;
     // slab window: only the owned fine rows (they come first in key order) are re-sorted here; the halo
     // rows are replaced wholesale by the neighbours' boundary layers (ab_comm.cu)
-    if (h->win_W) a.nrows = (int)((int64_t)a.nrows * h->win_nl / h->dims[D - 1]);
-    a.ntiles = a.nrows * a.tpr;
+    if (h->win_W) nrows = nrows * h->win_nl / h->dims[D - 1];
+    const int64_t ntiles = nrows * tpr;
+    if (ntiles > 0x7fffffffLL) return ab_fail(h, AB_ERR_INVALID, "too many re-sort tiles");
+    const size_t need = ((size_t)ntiles + SCAN_TILE - 1) / SCAN_TILE * SCAN_TILE;
+    if (need > h->tile_cap) {
+        AB_CUDA(h, cudaStreamSynchronize(h->stream));
+        if (h->tile_count) AB_CUDA(h, cudaFree(h->tile_count));
+        if (h->tile_base) AB_CUDA(h, cudaFree(h->tile_base));
+        h->tile_count = h->tile_base = nullptr;
+        AB_CUDA(h, cudaMalloc((void**)&h->tile_count, need * sizeof(uint32_t)));
+        AB_CUDA(h, cudaMalloc((void**)&h->tile_base, (need + 1) * sizeof(uint32_t)));
+        AB_CUDA(h, cudaMemsetAsync(h->tile_count, 0, need * sizeof(uint32_t), h->stream));
+        h->tile_cap = need;
+        if (need / SCAN_TILE + 1 > h->scan_status_len) return ab_fail(h, AB_ERR_INVALID, "tile scan larger than the handle's status buffer");
+    }
+    h->rs_tw = tw; h->rs_tpr = tpr; h->rs_nrows = (int)nrows; h->rs_ntiles = (int)ntiles;
+    h->rs_magic = (uint32_t)((0x100000000ULL + (uint64_t)tw - 1) / (uint64_t)tw);
+    return AB_OK;
+}
+
+template <class T, int D>
+static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool want_agg) {
+    const int cur = h->cur, nxt = cur ^ 1;
+    SpaceDev<T, D> sp = make_space<T, D>(h);
+    ResortArgs a;
+    a.tw = h->rs_tw; a.tpr = h->rs_tpr; a.nrows = h->rs_nrows; a.ntiles = h->rs_ntiles;
+    if (a.ntiles <= 0 || a.tw <= 0) return ab_fail(h, AB_ERR_STATE, "ab_resort_plan must precede the step kernel");
     a.has_vel = h->desc.kind == AB_SPACE_CONTINUOUS;
     a.want_agg = want_agg ? 1 : 0;
-    // the step kernel has counted the new keys into cell_count: scan them into the new cell_start
-    AB_TRY(ab_run_scan(h, h->cell_start_alt));
+    // the step kernel has counted the new keys per fine cell and per tile: scan the tile totals; every tile turns
+    // its own cell counts into its slice of the new cell_start
+    AB_TRY(ab_scan_u32(h, h->tile_count, h->tile_base, (uint32_t)a.ntiles));
     if (want_agg) AB_TRY(ensure_agg(h));
     const bool extra = h->fields.size() > 2u;
     {
@@ -403,8 +465,8 @@ static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool
         constexpr int G = (D == 2) ? RS_G2D : 2;           // source chunks in flight per warp
         AB_CUDA(h, ab_launch_chain(h->pdl, k_resort<T, D, G>, dim3((a.ntiles + RS_WARPS - 1) / RS_WARPS), dim3(RS_THREADS), h->stream,
             sp, a, h->cell_start, h->newkey, h->id[cur], (const T*)src_pos, (const T*)src_vel, h->cap,
-            (T*)h->fields[0].buf[nxt], (T*)h->fields[1].buf[nxt], h->id[nxt], h->key[nxt], h->cell_start_alt,
-            extra ? h->perm : nullptr, (T*)h->cell_agg, (int64_t)h->ncells, h->d_err));
+            (T*)h->fields[0].buf[nxt], (T*)h->fields[1].buf[nxt], h->id[nxt], h->key[nxt], h->cell_count, h->tile_base,
+            h->cell_start_alt, extra ? h->perm : nullptr, (T*)h->cell_agg, (int64_t)h->ncells, h->d_err));
     }
     std::swap(h->cell_start, h->cell_start_alt);
     AB_TRY(ab_permute_extra_fields(h));
@@ -418,8 +480,8 @@ static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool
 }
 
 // Re-sorts from (src_pos, src_vel, h->newkey) — all in the CURRENT slot order —
-// into the other buffer.  Requires the new keys counted into h->cell_count and
-// that no agent moved further than one fine cell (checked on the device:
+// into the other buffer.  Requires the new keys counted into h->cell_count / h->tile_count (count_new_key,
+// geometry of ab_resort_plan) and that no agent moved further than one fine cell (checked on the device:
 // AB_EF_OVERFLOW otherwise).
 int ab_resort_tiled(ab_handle* h, const void* src_pos, const void* src_vel, bool want_agg) {
     if (h->dtype == AB_F64) return h->D == 2 ? resort_t<double, 2>(h, src_pos, src_vel, want_agg) : resort_t<double, 3>(h, src_pos, src_vel, want_agg);

@@ -176,6 +176,40 @@ class Slabs:
     def n_owned(self):
         return int(self.model.lib.ab_nlocal(self.model.h))
 
+    # -- host-buffer stepping (the end-to-end path of a sharded model) ---------------------------
+    def host_state(self, slack=1.5):
+        """Pinned host rows (global ids, pos, vel) of the agents this rank owns now."""
+        import torch
+
+        m = self.model
+        ids, pos, vel = self.local_state()
+        rows = int(len(ids) * slack) + 4096
+        tdt = torch.float64 if m.space.dtype == np.float64 else torch.float32
+        st = {"ids": torch.empty(rows, dtype=torch.int64, pin_memory=True).numpy(),
+              "pos": torch.empty((rows, m.D), dtype=tdt, pin_memory=True).numpy(),
+              "vel": torch.empty((rows, m.D), dtype=tdt, pin_memory=True).numpy(), "n": len(ids), "rows": rows}
+        st["ids"][: len(ids)] = ids
+        st["pos"][: len(ids)] = pos
+        st["vel"][: len(ids)] = vel
+        st["bytes_up"] = st["bytes_down"] = 0
+        return st
+
+    def host_step(self, st, nsteps=1):
+        """upload the owned rows -> halo refresh from the neighbours (collective) -> step!(model, nsteps) -> download
+        the rows owned afterwards (migration changes which)."""
+        m, lib = self.model, self.model.lib
+        n = st["n"]
+        m._ck(lib.ab_upload_local(m.h, 0, m._ptr(st["pos"]), m._ptr(st["ids"]), n))
+        m._ck(lib.ab_upload_local(m.h, 1, m._ptr(st["vel"]), m._ptr(st["ids"]), n))
+        m._ck(lib.ab_comm_exchange(m.h))
+        m.step(nsteps)
+        k = C.c_int64(0)
+        m._ck(lib.ab_download_local(m.h, 0, m._ptr(st["pos"]), m._ptr(st["ids"]), st["rows"], C.byref(k)))
+        m._ck(lib.ab_download_local(m.h, 1, m._ptr(st["vel"]), None, st["rows"], C.byref(k)))
+        row = (2 * m.D * st["pos"].itemsize + 8)
+        st["bytes_up"], st["bytes_down"] = n * row, k.value * row
+        st["n"] = k.value
+
     def gather(self):
         """Global id-ordered (pos, vel) on every rank (all_gather of the owned parts)."""
         ids, pos, vel = self.local_state()

@@ -14,20 +14,31 @@ value  : agents*steps / device time of ONE step!(model, K) call after W warm-up
          steps, state resident in HBM (CUDA events on the library's stream,
          max over ranks; the per-step working set exceeds L2, no flush).
 e2e    : same metric through the public API with HOST (pinned) buffers: every
-         model step uploads pos+vel, steps once, downloads pos+vel; an ensemble of
-         6 independent models is kept in flight through the asynchronous C ABI
-         (the one-synchronous-model figure is reported beside it).
+         model step uploads pos+vel, steps once, downloads pos+vel.  `e2e.value`
+         is ONE model, one synchronisation per step (like for like with the
+         single-model reference arm); `e2e.ensemble` is the throughput of several
+         independent models in flight through the asynchronous C ABI.
 roofline: dominant kernel (the sweep) — algorithmic 128 B/agent-update
           x agents per launch / its CUDA-event duration, against the
          measured HBM copy bandwidth in MEASURED_PEAKS.json.  The per-launch events
-         are recorded in a twin pass over the same steps (they cost ~22 us per step,
-         so the timed region carries none).
+         are recorded in a twin pass over the SAME steps (same initial state, same
+         warm-up; also with several ranks), so the timed region carries none.
+configs: (N = 1) driver-timed rows for the other BASELINE configurations on one
+         GPU: F2D-1M :exact, F2D-1M Float32, PF2D-10M, SCH-8192 (happiness pass and
+         full step), F3D-12.5M (one GPU's share of F3D-100M) — each with its own
+         ms_per_step, roofline fraction and NVML clock sample.
 cpu_baseline: the CPU oracle's reference-faithful asynchronous step
          (vector-per-cell index, in-place sequential update, 1 thread — the
          reference's step! is single-threaded) on a bounded sample.
 With --gpus N > 1 (torchrun): weak scaling, 1M boids per GPU, slab decomposition
 along y, halo / migration exchange by direct peer-memory stores (AB_HALO=nccl:
-ncclSend/ncclRecv).
+ncclSend/ncclRecv).  Before the timed region the ranks run a reduced sharded case
+(2-D and 3-D) and compare the gathered state with an unsharded run on rank 0:
+`parity_check.bitwise_equal` (the process exits non-zero on a mismatch).  The timed
+call starts behind a device-side all-reduce (ab_comm_align) so rank launch skew is
+not charged to the K steps; `halo_wait_us_per_step` says how long each rank's halo
+install waited for its neighbours.  `f3d_weak` is the F3D row of BASELINE configs[4]:
+12.5 M boids per GPU, slabs along z (8 GPUs = F3D-100M).
 """
 import argparse
 import ctypes as C
@@ -44,7 +55,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-ALG_BYTES = {"flock2d_f64": 128.0, "flock3d_f64": 160.0, "flock2d_f32": 72.0}
+ALG_BYTES = {"flock2d_f64": 128.0, "flock3d_f64": 160.0, "flock2d_f32": 72.0, "pairforce2d_f64": 104.0, "schelling": 10.33}
 N_PER_GPU = 1_000_000
 EXTENT = (2000.0, 2000.0)
 SPACING = 5.0
@@ -126,6 +137,7 @@ class ClockSampler:
             self.source = "nvidia-smi"
             self._thread = threading.Thread(target=self._smi_loop, daemon=True)
         self._thread.start()
+        return self
 
     def stop(self):
         self._stop.set()
@@ -145,6 +157,35 @@ def flock_state(n, extent, seed=42):
     from helpers import flock_init
 
     return flock_init(n, extent, seed)
+
+
+def flock_chunks(n, extent, seed, step):
+    """The counter-based initial state in id chunks (no rank ever holds a 100 M-boid array)."""
+    from helpers import splitmix64
+
+    ext = np.asarray(extent, dtype=np.float64)[None, :]
+    D = len(extent)
+    for first in range(0, n, step):
+        m = min(step, n - first)
+        with np.errstate(over="ignore"):
+            i = np.arange(first, first + m, dtype=np.uint64)[:, None] * np.uint64(8)
+            cp = np.arange(D, dtype=np.uint64)[None, :]
+            up = (splitmix64(np.uint64(seed) ^ (i + cp)) >> np.uint64(11)).astype(np.float64) * 2.0 ** -53
+            uv = (splitmix64(np.uint64(seed) ^ (i + cp + np.uint64(4))) >> np.uint64(11)).astype(np.float64) * 2.0 ** -53
+        yield first, up * ext, uv * 2.0 - 1.0
+
+
+def particles(n, extent, seed=42, max_radius=10.0, vscale=100.0):
+    """examples/celllistmap.jl:73-128-style particles: uniform positions, normal velocities, radius / k / mass columns."""
+    from helpers import uniform
+
+    D = len(extent)
+    pos = uniform(n, D, seed, 0) * np.asarray(extent)[None, :]
+    u1 = np.maximum(uniform(n, D, seed, 1), 1e-300)
+    u2 = uniform(n, D, seed, 2)
+    vel = vscale * np.sqrt(-2.0 * np.log(u1)) * np.cos(2.0 * np.pi * u2)
+    w = uniform(n, 3, seed, 3)
+    return pos, vel, (0.5 + 0.9 * w[:, 0]) * max_radius, 10.0 + 20.0 * w[:, 1], 10.0 + 100.0 * w[:, 2]
 
 
 # ---------------------------------------------------------------------------
@@ -189,11 +230,11 @@ def run_reference(args):
     if rank != 0:
         return 0
     n = N_PER_GPU
-    # bounded sample: the full 1M-boid population, few steps (each ~10 s on one core)
-    steps = max(1, min(args.steps, 3))
+    # bounded sample: the full 1M-boid population, 1 warm-up + 5 timed steps (each 2-4 s on one core)
+    steps = max(1, min(args.steps, 5))
     warm = 1 if args.warmup > 0 else 0
     rate, dt = cpu_flock_rate(n, EXTENT, steps, warm)
-    sample = f"{n} boids x {steps} asynchronous steps (Schedulers.Randomly order), 1 thread"
+    sample = f"{n} boids x {steps} asynchronous steps after {warm} warm-up step (Schedulers.Randomly order), 1 thread"
     line = {
         "impl": "reference", "metric": "agent-updates/sec", "value": rate, "unit": "agent-updates/s",
         "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": dt / steps * 1e3,
@@ -213,6 +254,186 @@ def run_reference(args):
 # ---------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------
+def kernel_table(lib, m):
+    names = (C.c_char_p * 32)()
+    kms = (C.c_double * 32)()
+    kl = (C.c_int64 * 32)()
+    nk = lib.ab_kernel_times(m.h, names, kms, kl, 32)
+    return {names[i].decode(): {"ms_per_launch": kms[i] / max(kl[i], 1), "launches": int(kl[i]), "ms": kms[i]}
+            for i in range(min(nk, 32))}
+
+
+def timed_row(lib, m, name, n, steps, warmup, alg_bytes, local, peak, extra=None):
+    """One driver-timed row of `configs`: W warm-up steps, ONE call of K fused steps timed by CUDA events on the
+    library's stream (state resident), NVML clock samples inside the timed region; then the per-kernel durations of
+    the NEXT min(K, 5) steps (per-launch events cost a few us each, so the timed call carries none)."""
+    import torch
+
+    m.step(warmup)
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local).start()
+    l0 = m.launch_count()
+    m.step(steps)
+    ms = m.last_step_ms() / steps
+    launches = m.launch_count() - l0
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    lib.ab_set_profiling(m.h, 1)
+    kp = min(steps, 5)
+    m.step(kp)
+    kern = kernel_table(lib, m)
+    lib.ab_set_profiling(m.h, 0)
+    dom = max(kern, key=lambda k: kern[k]["ms"]) if kern else None
+    rate = n / (ms * 1e-3)
+    row = {"config": name, "agents": int(n), "steps": steps, "warmup": warmup, "ms_per_step": ms, "value": rate,
+           "unit": "agent-updates/s", "algorithmic_bytes_per_agent_update": alg_bytes,
+           "roofline": {"bound": "hbm", "peak": peak, "unit": "GB/s",
+                        "whole_step": {"achieved": rate * alg_bytes / 1e9, "frac": rate * alg_bytes / 1e9 / peak},
+                        "kernel": dom,
+                        "achieved": (alg_bytes * n / (kern[dom]["ms_per_launch"] * 1e-3) / 1e9) if dom else None,
+                        "frac": (alg_bytes * n / (kern[dom]["ms_per_launch"] * 1e-3) / 1e9 / peak) if dom else None},
+           "kernels_us_per_launch": {k: round(v["ms_per_launch"] * 1e3, 2) for k, v in kern.items()},
+           "gpu_launches": int(launches), "clocks": clocks}
+    if extra:
+        row.update(extra)
+    return row
+
+
+def config_rows(ab, lib, local, peak, scale=1.0):
+    """BASELINE.json configs other than the headline, on one GPU (SURVEY §8d sizes)."""
+    from helpers import flock_init, uniform
+
+    rows = []
+    sc = scale
+    side = int(round(400 * sc ** 0.5))
+    extent = (5.0 * side, 5.0 * side)
+    n = int(6.25 * side * side)
+    for name, dt, search, alg in (("F2D-1M exact f64", np.float64, "exact", ALG_BYTES["flock2d_f64"]),
+                                  ("F2D-1M approximate f32", np.float32, "approximate", ALG_BYTES["flock2d_f32"])):
+        pos, vel = flock_init(n, extent, 42, dtype=dt)
+        m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=5.0, dtype=dt), model_step=ab.FlockRule(search=search, **FLOCK), device=local)
+        m.add_agents(pos, vel)
+        rows.append(timed_row(lib, m, name, n, 20, 5, alg, local, peak))
+        m.close()
+
+    side = int(round(791 * sc ** 0.5))
+    extent = (20.0 * side, 20.0 * side)
+    n = int(0.04 * extent[0] * extent[1])
+    pos, vel, rad, k, mass = particles(n, extent)
+    m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=20.0), model_step=ab.PairForceRule(dt=0.001, cutoff=20.0), device=local)
+    m.add_agents(pos, vel, r=rad, k=k, mass=mass)
+    rows.append(timed_row(lib, m, "PF2D-10M (celllistmap.jl-style pair force, cutoff 20, interacting_pairs(:all) exact set)", n, 10, 3,
+                          ALG_BYTES["pairforce2d_f64"], local, peak))
+    m.close()
+    del pos, vel, rad, k, mass
+
+    side = int(round(8192 * sc ** 0.5))
+    ncell = side * side
+    n = int(ncell * 0.75)
+    perm = np.argsort(uniform(ncell, 1, 42)[:, 0], kind="stable")[:n]
+    pos = np.stack([perm % side + 1, perm // side + 1], axis=1).astype(np.int32)
+    group = (np.arange(n) % 2 + 1).astype(np.int32)
+    for relocate in (False, True):
+        m = ab.StandardABM(ab.GridSpaceSingle((side, side), periodic=False),
+                           model_step=ab.SchellingRule(min_to_be_happy=3, relocate=relocate, seed=42), device=local)
+        m.add_agents(pos, group=group, mood=np.zeros(n, dtype=np.uint8))
+        rows.append(timed_row(lib, m, "SCH-8192 " + ("full step (happiness + relocation)" if relocate else "happiness pass (nearby_ids radius 1)"),
+                              n, 10, 3, ALG_BYTES["schelling"], local, peak))
+        m.close()
+    del pos, group, perm
+
+    side = int(round(280 * sc ** (1.0 / 3.0)))
+    layers = max(8, int(round(35 * sc ** (1.0 / 3.0))))
+    extent = (5.0 * side, 5.0 * side, 5.0 * layers)
+    n = int(4.5554 * side * side * layers)
+    pos, vel = flock_init(n, extent, 42)
+    m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=5.0), model_step=ab.FlockRule(**FLOCK), device=local)
+    m.add_agents(pos, vel)
+    rows.append(timed_row(lib, m, "F3D-12.5M (one GPU's share of F3D-100M, periodic box)", n, 10, 3, ALG_BYTES["flock3d_f64"], local, peak))
+    m.close()
+    return rows
+
+
+def parity_check(ab, dist, local, rank, world):
+    """Reduced sharded cases (the cases of tests/test_multigpu.py, stretched so every rank owns >= 4 cell layers):
+    after 8 fused steps the gathered state must be BITWISE equal to the unsharded run of the same library on rank 0."""
+    from agents_jl_b200.parallel import Slabs
+    from helpers import flock_init
+
+    cases = [("2d", (400.0, float(max(400, 100 * world))), 0.375),
+             ("3d", (60.0, 60.0, float(max(120, 40 * world))), 0.0926)]
+    out = {"bitwise_equal": True, "migrated": 0, "direct": True, "cases": []}
+    for name, extent, dens in cases:
+        n = int(dens * float(np.prod(extent)))
+        pos, vel = flock_init(n, extent, 42)
+        rule = ab.FlockRule(kernel="fine", **FLOCK)
+        m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=SPACING), model_step=rule, device=local)
+        s = Slabs(m, dist)
+        own0 = s.scatter(pos, vel)
+        m.step(4)
+        own1 = s.n_owned()
+        m.step(4)
+        gp, gv = s.gather()                                   # raises if an agent was lost or duplicated
+        direct = bool(s.direct)
+        m.close()
+        ok, migrated = True, abs(own1 - own0)
+        if rank == 0:
+            ref = ab.StandardABM(ab.ContinuousSpace(extent, spacing=SPACING), model_step=ab.FlockRule(kernel="fine", **FLOCK), device=local)
+            ref.add_agents(pos, vel)
+            ref.step(4)
+            ref.step(4)
+            ok = bool(np.array_equal(gp, ref.pos) and np.array_equal(gv, ref.vel))
+            ref.close()
+        flags = [None] * world
+        dist.all_gather_object(flags, (ok, migrated, direct))
+        ok = all(f[0] for f in flags)
+        out["cases"].append({"case": name, "agents": n, "extent": list(extent), "steps": 8, "bitwise_equal": ok,
+                             "rank_population_change": [int(f[1]) for f in flags], "direct": all(f[2] for f in flags)})
+        out["bitwise_equal"] = out["bitwise_equal"] and ok
+        out["migrated"] += int(sum(f[1] for f in flags))
+        out["direct"] = out["direct"] and all(f[2] for f in flags)
+    return out
+
+
+def f3d_weak(ab, lib, dist, local, rank, world, peak, steps=10, warmup=3, per_gpu=12_500_000):
+    """BASELINE configs[4]: 3-D flock, 12.5 M boids per GPU, slabs along z (world = 8: F3D-100M)."""
+    import torch
+    from agents_jl_b200.parallel import Slabs, default_halo_capacity
+
+    n = per_gpu * world
+    extent = (1400.0, 1400.0, 175.0 * world)
+    m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=5.0, periodic=True), model_step=ab.FlockRule(kernel="fine", **FLOCK), device=local)
+    s = Slabs(m, dist)
+    cap = default_halo_capacity(n, s.n_layers, factor=1.25)
+    s.scatter_chunks(flock_chunks(n, extent, 42, 4_000_000), n, halo_capacity=cap)
+    m.step(warmup)
+    torch.cuda.synchronize()
+    dist.barrier()
+    sampler = ClockSampler(local).start()
+    lib.ab_comm_wait_stats(m.h, None, None, 1)
+    lib.ab_comm_align(m.h)
+    m.step(steps)
+    ms = m.last_step_ms()
+    wait_us, nex = C.c_double(0), C.c_int64(0)
+    lib.ab_comm_wait_stats(m.h, C.byref(wait_us), C.byref(nex), 1)
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t[0])
+    waits = [None] * world
+    dist.all_gather_object(waits, wait_us.value / max(steps, 1))
+    m.close()
+    rate = n * steps / (ms * 1e-3)
+    return {"config": "F3D-100M" if world == 8 else f"F3D-{n / 1e6:g}M ({world} x 12.5M, weak scaling of F3D-100M)", "agents": n,
+            "n_gpus": world, "extent": list(extent), "steps": steps, "warmup": warmup, "ms_per_step": ms / steps, "value": rate,
+            "unit": "agent-updates/s", "direct": bool(s.direct), "halo_wait_us_per_step": [round(w, 1) for w in waits],
+            "roofline": {"bound": "hbm", "peak": peak, "unit": "GB/s",
+                         "whole_step_per_gpu": {"achieved": ALG_BYTES["flock3d_f64"] * rate / world / 1e9,
+                                                "frac": ALG_BYTES["flock3d_f64"] * rate / world / 1e9 / peak}},
+            "clocks_rank0": clocks}
+
+
 def run_gpu(args):
     import torch
 
@@ -235,20 +456,38 @@ def run_gpu(args):
     search = args.search
     extent = EXTENT if world == 1 else (EXTENT[0], EXTENT[1] * world)     # weak scaling: slabs along y
     lib = L.lib()
-    sampler = ClockSampler(local)
+    peak, peak_src = measured_peaks()
+
+    # ---- multi-GPU parity gate (before anything is timed) ------------------------
+    parity = None
+    if world > 1 and not args.no_parity:
+        parity = parity_check(ab, dist, local, rank, world)
+        if not parity["bitwise_equal"]:
+            if rank == 0:
+                print(json.dumps({"error": "sharded run differs from the unsharded run", "parity_check": parity}))
+            dist.destroy_process_group()
+            return 3
 
     rule = ab.FlockRule(search=search, kernel=args.kernel, **FLOCK)
-    space = ab.ContinuousSpace(extent, spacing=SPACING, periodic=True)
-    model = ab.StandardABM(space, model_step=rule, device=local)
+    pos = vel = None
     if world == 1:
         pos, vel = flock_state(n, extent)
-        model.add_agents(pos, vel)
     else:
-        from agents_jl_b200.parallel import init_slabs
+        gpos, gvel = flock_state(n * world, extent)
 
-        slabs = init_slabs(model, dist, n * world, extent, flock_state)
+    def make_model():
+        m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=SPACING, periodic=True), model_step=rule, device=local)
+        if world == 1:
+            m.add_agents(pos, vel)
+            return m, None
+        from agents_jl_b200.parallel import Slabs
+
+        s = Slabs(m, dist)
+        s.scatter(gpos, gvel)
+        return m, s
+
+    model, slabs = make_model()
     nloc = n
-
     flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device="cuda")
 
     def barrier():
@@ -257,51 +496,54 @@ def run_gpu(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def kernel_table(m):
-        names = (C.c_char_p * 32)()
-        kms = (C.c_double * 32)()
-        kl = (C.c_int64 * 32)()
-        nk = lib.ab_kernel_times(m.h, names, kms, kl, 32)
-        return {names[i].decode(): {"ms_per_launch": kms[i] / max(kl[i], 1), "launches": int(kl[i]), "ms": kms[i]}
-                for i in range(min(nk, 32))}
-
     # ---- device-resident throughput: the timed region is ONE step!(model, K) call ---------------
     # (K fused steps back to back on the library's stream, no host work in between; the state a step
     #  streams — 2 x (pos, vel, id, key) + step scratch = 130 MB per 1 M boids — exceeds the 126 MB L2, so
     #  there is no flush between steps; the flushed per-step figure is reported beside it.)
-    # Per-launch CUDA events cost ~5 us per launch (22 us of a 260 us step), so the timed region runs
-    # WITHOUT them and the per-kernel durations come from a twin pass over the SAME steps (W..W+K from the
-    # same initial state; N = 1) with the events on; with several ranks the twin pass is the next K steps.
+    # Per-launch CUDA events cost a few us per launch, so the timed region runs WITHOUT them and the per-kernel
+    # durations come from a twin pass over the SAME steps (W..W+K from the same initial state) with the events on.
+    # N > 1: the timed call is queued behind a device-side all-reduce (ab_comm_align): every rank's K steps start
+    # when the slowest rank has arrived, so host launch skew after the barrier is not charged to them.
     model.step(args.warmup)
     barrier()
-    sampler.start()
+    sampler = ClockSampler(local).start()
     launches0 = model.launch_count()
+    if world > 1:
+        lib.ab_comm_wait_stats(model.h, None, None, 1)
+        lib.ab_comm_align(model.h)
     model.step(args.steps)
     ms = model.last_step_ms()               # CUDA events around the K steps on the library's stream
     launches = model.launch_count() - launches0
+    halo_wait = None
+    if world > 1:
+        wait_us, nex = C.c_double(0), C.c_int64(0)
+        lib.ab_comm_wait_stats(model.h, C.byref(wait_us), C.byref(nex), 1)
+        halo_wait = wait_us.value / max(args.steps, 1)
     barrier()
     clocks = sampler.stop()
-    if world == 1:
-        twin = ab.StandardABM(ab.ContinuousSpace(extent, spacing=SPACING, periodic=True), model_step=rule, device=local)
-        twin.add_agents(pos, vel)
-        twin.step(args.warmup)
-    else:
-        twin = model
+    twin, _tw_slabs = make_model()
+    twin.step(args.warmup)
     barrier()
     lib.ab_set_profiling(twin.h, 1)         # events recorded around every launch, resolved after the call
+    if world > 1:
+        lib.ab_comm_align(twin.h)
     twin.step(args.steps)
     ms_profiled = twin.last_step_ms()
     barrier()
-    kernels = kernel_table(twin)
+    kernels = kernel_table(lib, twin)
     lib.ab_set_profiling(twin.h, 0)
-    if twin is not model:
-        twin.close()
+    twin.close()
     t = torch.tensor([ms], dtype=torch.float64, device="cuda")
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_rank = ms
     ms = float(t[0])
     total_agents = n * world
     value = total_agents * args.steps / (ms * 1e-3)
+    per_rank = None
+    if dist is not None:
+        per_rank = [None] * world
+        dist.all_gather_object(per_rank, {"ms_per_step": ms_rank / args.steps, "halo_wait_us_per_step": round(halo_wait, 2)})
 
     # per-step calls with an L2 flush (256 MB write) before each one; N = 1 only: with several ranks the
     # unsynchronised host-side flushes would be timed as waiting for the neighbour
@@ -320,7 +562,6 @@ def run_gpu(args):
 
     step_kernel_ms = sum(v["ms"] for v in kernels.values()) / args.steps
     dom = max(kernels, key=lambda k: kernels[k]["ms"]) if kernels else None
-    peak, peak_src = measured_peaks()
     alg = ALG_BYTES["flock2d_f64"]
     roofline = None
     if dom:
@@ -333,8 +574,8 @@ def run_gpu(args):
                     "whole_step": {"achieved": alg * nloc / (ms / args.steps * 1e-3) / 1e9,
                                    "frac": alg * nloc / (ms / args.steps * 1e-3) / 1e9 / peak},
                     "profiled_pass_ms_per_step": ms_profiled / args.steps,
-                    "note": "launch durations from CUDA events around every launch in a twin pass over the same steps "
-                            "(rank 0); the timed region itself carries no per-launch events (they cost ~22 us per step)"}
+                    "note": "launch durations from CUDA events around every launch in a twin pass over the SAME steps "
+                            "(same initial state and warm-up, rank 0); the timed region itself carries no per-launch events"}
         tpath = os.path.join(ROOT, "profiles", "traffic.json")      # dram bytes per launch from an ncu --set full capture
         if os.path.exists(tpath):
             try:
@@ -344,9 +585,9 @@ def run_gpu(args):
 
     # ---- end to end through the public API with host buffers --------------------
     # Every model step = upload pos+vel from pinned host rows, step!(model, 1), download pos+vel into
-    # the same rows (the next step uploads what this one downloaded).  `single_model`: one model, one
-    # ab_sync per step.  `value`: an ensemble of R independent models (ensemblerun!-style) queued
-    # asynchronously on their own streams, so one model's download overlaps the other's upload and step.
+    # the same rows (the next step uploads what this one downloaded).  `value`: ONE model, one ab_sync per
+    # step.  `ensemble`: R independent models (ensemblerun!-style) queued asynchronously on their own
+    # streams, so one model's download overlaps another's upload and step.
     e2e = None
     if world == 1:
         def pinned_rows(m):
@@ -401,22 +642,42 @@ def run_gpu(args):
         for m, _, _ in ens:
             m.set_async(False)
         nb = int(hp0.nbytes + hv0.nbytes)
-        e2e = {"value": R * n * args.steps / dt2, "unit": "agent-updates/s", "h2d_bytes_per_step": nb,
-               "d2h_bytes_per_step": nb, "ms_per_step": dt2 / (R * args.steps) * 1e3,
-               "mode": f"ensemble of {R} independent F2D-1M models, asynchronous C-ABI calls, one stream per model; every model "
-                       "step uploads and downloads pos+vel (pinned host rows); ms_per_step is per model step",
-               "single_model": {"value": n * args.steps / dt1, "ms_per_step": dt1 / args.steps * 1e3,
-                                "note": "one model, upload -> step -> download -> ab_sync every step"}}
+        e2e = {"value": n * args.steps / dt1, "unit": "agent-updates/s", "h2d_bytes_per_step": nb,
+               "d2h_bytes_per_step": nb, "ms_per_step": dt1 / args.steps * 1e3,
+               "mode": "ONE F2D-1M model: upload pos+vel (pinned host rows) -> step!(model, 1) -> download pos+vel -> ab_sync, every step",
+               "ensemble": {"value": R * n * args.steps / dt2, "models": R, "ms_per_model_step": dt2 / (R * args.steps) * 1e3,
+                            "note": f"{R} independent F2D-1M models in flight (ensemblerun!-style), asynchronous C-ABI calls, one stream "
+                                    "per model; every model step uploads and downloads pos+vel"}}
         for m, _, _ in ens[1:]:
             m.close()
+    else:
+        # sharded model: every rank keeps pinned host rows of the agents it owns; a step uploads them (in slot
+        # order, global ids attached), refreshes the halo from the neighbours, steps once and downloads the owned rows
+        e2e = e2e_sharded(torch, dist, lib, model, slabs, args, total_agents)
+
+    # ---- the other BASELINE configurations, one GPU (N = 1 only) ----------------
+    configs = None
+    if world == 1 and not args.no_configs:
+        model.close()
+        model = None
+        del flush
+        torch.cuda.empty_cache()
+        configs = config_rows(ab, lib, local, peak, args.config_scale)
+    f3d = None
+    if world > 1 and not args.no_f3d:
+        model.close()
+        model = None
+        del flush
+        torch.cuda.empty_cache()
+        f3d = f3d_weak(ab, lib, dist, local, rank, world, peak)
 
     # ---- CPU baseline on this box's host cores (rank 0, N = 1 only) ------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        csteps = 2
-        rate, dt = cpu_flock_rate(n, EXTENT, csteps)
+        csteps = 5
+        rate, dt = cpu_flock_rate(n, EXTENT, csteps, 1)
         cpu = {"value": rate, "unit": "agent-updates/s", "cores": 1, "kind": "port",
-               "sample": f"{n} boids x {csteps} asynchronous steps (reference semantics), {dt:.1f} s, 1 thread",
+               "sample": f"{n} boids x {csteps} asynchronous steps after 1 warm-up step (reference semantics), {dt:.1f} s, 1 thread",
                "sync_all_cores": cpu_flock_rate_sync_all_cores(n, EXTENT, 2)}
 
     if rank == 0:
@@ -431,15 +692,50 @@ def run_gpu(args):
                        "parallelism": "single GPU" if world == 1 else f"{world} slabs along y, halo+migration by " + ("direct peer-memory stores" if slabs.direct else "NCCL send/recv")},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
             "l2_flushed_per_step": flushed,
-            **({} if world == 1 else {"e2e_note": "the host-buffer leg is measured at N = 1 (one model per handle); a sharded model "
-                                                  "stays resident across steps, its halo and migration travel over NVLink, not PCIe"}),
             "kernels": kernels, "kernel_ms_per_step": step_kernel_ms,
         }
+        if world > 1:
+            line["parity_check"] = parity
+            line["per_rank"] = per_rank
+            line["halo_wait_us_per_step"] = [p["halo_wait_us_per_step"] for p in per_rank]
+            line["start_alignment"] = "device-side all-reduce on the library's stream before the first timed step (ab_comm_align)"
+            line["f3d_weak"] = f3d
+        if configs is not None:
+            line["configs"] = configs
         print(json.dumps(line))
-    model.close()
+    if model is not None:
+        model.close()
     if dist is not None:
         dist.destroy_process_group()
     return 0
+
+
+def e2e_sharded(torch, dist, lib, model, slabs, args, total_agents):
+    """Host-buffer leg of a sharded model (every rank, its own slab)."""
+    if not hasattr(slabs, "host_step"):
+        return None
+    try:
+        st = slabs.host_state()
+        for _ in range(3):
+            slabs.host_step(st, 1)
+        torch.cuda.synchronize()
+        dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            slabs.host_step(st, 1)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        t = torch.tensor([dt], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t[0])
+        nb = torch.tensor([float(st["bytes_up"]), float(st["bytes_down"])], dtype=torch.float64, device="cuda")
+        dist.all_reduce(nb)
+        return {"value": total_agents * args.steps / dt, "unit": "agent-updates/s", "h2d_bytes_per_step": int(nb[0].item()),
+                "d2h_bytes_per_step": int(nb[1].item()), "ms_per_step": dt / args.steps * 1e3,
+                "mode": "every rank: upload the pos+vel rows it owns (pinned host memory) -> halo refresh from the neighbours -> "
+                        "step!(model, 1) -> download the owned rows; wall clock, max over ranks; bytes summed over ranks"}
+    except Exception as e:                                   # the device-resident figures above stay valid
+        return {"value": None, "error": str(e)[:300]}
 
 
 def main():
@@ -450,8 +746,12 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--search", default="approximate", choices=["approximate", "exact"])
     ap.add_argument("--kernel", default="auto", choices=["auto", "generic", "fine"])
-    ap.add_argument("--ensemble", type=int, default=6, help="independent models in flight in the e2e leg")
+    ap.add_argument("--ensemble", type=int, default=6, help="independent models in flight in the e2e ensemble figure")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    ap.add_argument("--no-configs", action="store_true", help="skip the rows of the other BASELINE configurations (N = 1)")
+    ap.add_argument("--config-scale", type=float, default=1.0, help="shrink the populations of the config rows (smoke runs)")
+    ap.add_argument("--no-parity", action="store_true", help="skip the sharded-vs-unsharded parity gate (N > 1)")
+    ap.add_argument("--no-f3d", action="store_true", help="skip the F3D weak-scaling row (N > 1)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

@@ -305,6 +305,15 @@ int ab_comm_set_capacity(ab_handle* h, int64_t halo_agents);
 int ab_comm_ipc_export(ab_handle* h, void* out64);
 int ab_comm_ipc_import(ab_handle* h, const void* lower64, const void* upper64);
 int ab_comm_direct(const ab_handle* h);                    /* 1 when the direct exchange is active */
+/* Timed multi-rank runs: ab_comm_align queues a one-word all-reduce on the handle's stream, so the calls queued
+ * after it start on every rank once the slowest rank has arrived ON THE DEVICE; ab_comm_wait_stats returns the
+ * time k_halo_unpack spent waiting for the neighbours' flags (direct exchange) and the exchanges counted since
+ * the last reset.  Neither has a counterpart in the reference (single task, step_standard.jl:9-23). */
+int ab_comm_align(ab_handle* h);
+/* Collective halo refresh outside a step: after ab_upload_local replaced the owned agents from the host, rebuild the
+ * window's halo layers from the neighbours (index build + the step's own pack / transfer / unpack). */
+int ab_comm_exchange(ab_handle* h);
+int ab_comm_wait_stats(ab_handle* h, double* wait_us, int64_t* exchanges, int reset);
 /* owned layers of this rank: global index of the first one (0-based) and how many */
 int ab_comm_slab(const ab_handle* h, int64_t* first_layer, int64_t* n_layers);
 int ab_comm_halo(const ab_handle* h);                      /* halo layers per side */
