@@ -92,7 +92,9 @@ _SIGS = {
     "ab_step_flock": (C.c_int, [_H, C.POINTER(FlockParams), C.c_int64]),
     "ab_step_flock_active": (C.c_int, [_H, C.POINTER(FlockParams), C.c_int64, C.c_void_p, C.c_int64]),
     "ab_step_pairforce": (C.c_int, [_H, C.POINTER(PairForceParams), C.c_int64]),
+    "ab_step_pairforce_active": (C.c_int, [_H, C.POINTER(PairForceParams), C.c_int64, C.c_void_p, C.c_int64]),
     "ab_step_schelling": (C.c_int, [_H, C.POINTER(SchellingParams), C.c_int64, C.POINTER(C.c_int64)]),
+    "ab_step_schelling_active": (C.c_int, [_H, C.POINTER(SchellingParams), C.c_int64, C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]),
     "ab_flock_last_counts": (C.c_int, [_H, C.c_void_p, C.c_int64]),
     "ab_reduce": (C.c_int, [_H, C.POINTER(ReduceSpec), C.c_int, C.c_void_p, C.c_void_p]),
     "ab_comm_unique_id": (C.c_int, [C.c_void_p]),

@@ -645,6 +645,27 @@ static int flock_group_t(ab_handle** hs, int nh, const ab_flock_params* p, int64
     return AB_OK;
 }
 
+// By-id mask of the agents a scheduler returned (Schedulers.Partially, a custom id list — schedulers.jl:68-120):
+// h->step_mask[id - 1] = 1 for the scheduled ones.  Shared by the flock, pair-force and Schelling steps.
+int ab_set_step_mask(ab_handle* h, const int64_t* active_ids, int64_t nactive) {
+    if (h->win_W) return ab_fail(h, AB_ERR_STATE, "a scheduled subset is not available on a sharded handle");
+    if (nactive < 0) return ab_fail(h, AB_ERR_INVALID, "negative nactive");
+    AB_CUDA(h, cudaSetDevice(h->device));
+    std::vector<uint8_t> mask((size_t)h->n, 0);
+    for (int64_t k = 0; k < nactive; ++k) {
+        if (active_ids[k] < 1 || active_ids[k] > h->n) return ab_fail(h, AB_ERR_INVALID, "active id out of range");
+        mask[(size_t)active_ids[k] - 1] = 1;
+    }
+    if (h->step_mask_bytes < (size_t)h->n) {
+        if (h->step_mask) { AB_CUDA(h, cudaStreamSynchronize(h->stream)); AB_CUDA(h, cudaFree(h->step_mask)); h->step_mask = nullptr; }
+        AB_CUDA(h, cudaMalloc(&h->step_mask, (size_t)h->cap));
+        h->step_mask_bytes = (size_t)h->cap;
+    }
+    // pageable source: the copy has left `mask` when the call returns; stream order protects the device buffer
+    AB_CUDA(h, cudaMemcpyAsync(h->step_mask, mask.data(), (size_t)h->n, cudaMemcpyHostToDevice, h->stream));
+    return AB_OK;
+}
+
 extern "C" {
 
 int ab_move(ab_handle* h, double dt, const int64_t* active_ids, int64_t nactive) {
@@ -702,22 +723,8 @@ int ab_step_flock(ab_handle* h, const ab_flock_params* p, int64_t nsteps) {
 
 int ab_step_flock_active(ab_handle* h, const ab_flock_params* p, int64_t nsteps, const int64_t* active_ids, int64_t nactive) {
     if (!active_ids) return ab_step_flock(h, p, nsteps);
-    if (h->win_W) return ab_fail(h, AB_ERR_STATE, "a scheduled subset is not available on a sharded handle");
-    if (nactive < 0) return ab_fail(h, AB_ERR_INVALID, "negative nactive");
     if (h->n == 0 || nsteps == 0) return AB_OK;
-    AB_CUDA(h, cudaSetDevice(h->device));
-    std::vector<uint8_t> mask((size_t)h->n, 0);
-    for (int64_t k = 0; k < nactive; ++k) {
-        if (active_ids[k] < 1 || active_ids[k] > h->n) return ab_fail(h, AB_ERR_INVALID, "active id out of range");
-        mask[(size_t)active_ids[k] - 1] = 1;
-    }
-    if (h->step_mask_bytes < (size_t)h->n) {
-        if (h->step_mask) { AB_CUDA(h, cudaStreamSynchronize(h->stream)); AB_CUDA(h, cudaFree(h->step_mask)); h->step_mask = nullptr; }
-        AB_CUDA(h, cudaMalloc(&h->step_mask, (size_t)h->cap));
-        h->step_mask_bytes = (size_t)h->cap;
-    }
-    // pageable source: the copy has left `mask` when the call returns; stream order protects the device buffer
-    AB_CUDA(h, cudaMemcpyAsync(h->step_mask, mask.data(), (size_t)h->n, cudaMemcpyHostToDevice, h->stream));
+    AB_TRY(ab_set_step_mask(h, active_ids, nactive));
     h->step_mask_cur = h->step_mask;
     const int rc = ab_step_flock(h, p, nsteps);
     h->step_mask_cur = nullptr;

@@ -380,12 +380,14 @@ __global__ void k_copy_counts(const uint32_t* __restrict__ cs, int64_t ncells, i
 // the EMPTY targets (random_empty_pos_in_offsets, walk.jl:200-214): up to 2L random probes (draws 0..2L-1),
 // then one uniform pick (draw 2L) among the empty targets in table order; the agent stays when there is none.
 // Emptiness depends on the walks before it, so that form runs in the sequential replay like walk!(ifempty).
-// The reference hands the chosen POSITION to walk! as if it were a direction (walk.jl:170, :193); the device
-// rule implements the documented behaviour — the agent moves to the chosen empty position.
+// The reference hands the chosen POSITION to walk! as if it were a direction (walk.jl:170, :193).  Both readings are
+// offered: force_motion = 1 is the documented behaviour — the agent moves to the chosen empty position —
+// force_motion = 2 the code as written (target = normalize_position(pos .+ choice), taken only if empty).
 struct GridRw {
     const int32_t* offs;     // L x D offsets at radius, table order of the reference (first dimension fastest)
     int L;
     uint64_t seed;
+    int literal;             // force_motion = 2: the chosen POSITION is handed to walk! as a direction (walk.jl:170, :193 as written)
 };
 
 template <int D>
@@ -437,6 +439,15 @@ __global__ void k_grw_force_seq(GridDev<D> g, int32_t* __restrict__ pos, int64_t
                 if (occ[k1] == 0 && pick-- == 0) break;
             }
         }
+        if (rw.literal) {
+            // walk!(agent, choice, model; ifempty = true) with choice = the empty POSITION found above, used as a
+            // direction (the reference's code as written): target = normalize_position(agent.pos .+ choice); the agent
+            // moves only if that target is empty (walk.jl:118-128, :141-149)
+#pragma unroll
+            for (int d = 0; d < D; ++d) c1[d] = grid_norm((c0[d] + 1) + (c1[d] + 1), g.dims[d], g.periodic[d]) - 1;
+            k1 = lin_cell<D>(g.dims, c1);
+            if (occ[k1] != 0) continue;
+        }
         const uint32_t k0 = lin_cell<D>(g.dims, c0);
         if (SINGLE) { occ[k0] = 0; occ[k1] = i + 1; }
         else { occ[k0] -= 1; occ[k1] += 1; }
@@ -483,11 +494,11 @@ static int host_offsets_at_radius(ab_handle* h, double r, std::vector<int32_t>* 
 }
 
 static int grid_walk_impl(ab_handle* h, const void* directions, const int64_t* active_ids, int64_t nactive, int ifempty,
-                          const std::vector<int32_t>* rw_offs, uint64_t rw_seed, bool rw_force);
+                          const std::vector<int32_t>* rw_offs, uint64_t rw_seed, int rw_force);
 
 int ab_grid_walk(ab_handle* h, const void* directions, const int64_t* active_ids, int64_t nactive, int ifempty) {
     if (!directions) return ab_fail(h, AB_ERR_INVALID, "null directions");
-    return grid_walk_impl(h, directions, active_ids, nactive, ifempty, nullptr, 0, false);
+    return grid_walk_impl(h, directions, active_ids, nactive, ifempty, nullptr, 0, 0);
 }
 
 int ab_grid_randomwalk(ab_handle* h, double r, uint64_t seed, const int64_t* active_ids, int64_t nactive, int ifempty,
@@ -498,13 +509,14 @@ int ab_grid_randomwalk(ab_handle* h, double r, uint64_t seed, const int64_t* act
     AB_TRY(host_offsets_at_radius(h, r, &offs));
     const bool single = h->desc.kind == AB_SPACE_GRID_SINGLE;
     if (single) ifempty = 1;                                              // no effect on GridSpaceSingle (walk.jl:141-143)
-    const bool force = force_motion && (single || ifempty);              // walk.jl:165, :189
+    if (force_motion < 0 || force_motion > 2) return ab_fail(h, AB_ERR_INVALID, "force_motion must be 0, 1 or 2");
+    const int force = (force_motion && (single || ifempty)) ? force_motion : 0;     // walk.jl:165, :189
     if (!active_ids) nactive = h->n;
     return grid_walk_impl(h, nullptr, active_ids, nactive, ifempty, &offs, seed, force);
 }
 
 static int grid_walk_impl(ab_handle* h, const void* directions, const int64_t* active_ids, int64_t nactive, int ifempty,
-                          const std::vector<int32_t>* rw_offs, uint64_t rw_seed, bool rw_force) {
+                          const std::vector<int32_t>* rw_offs, uint64_t rw_seed, int rw_force) {
     if (nactive < 0) return ab_fail(h, AB_ERR_INVALID, "negative nactive");
     const int na = active_ids ? (int)nactive : (int)h->n;
     if (!active_ids && nactive != h->n && nactive != 0) return ab_fail(h, AB_ERR_INVALID, "directions for all agents need nactive == n");
@@ -525,7 +537,7 @@ static int grid_walk_impl(ab_handle* h, const void* directions, const int64_t* a
     if (active_ids) AB_CUDA(h, cudaMemcpyAsync(base, active_ids, ids_bytes, cudaMemcpyHostToDevice, h->stream));
     const int64_t* ids = active_ids ? (const int64_t*)base : nullptr;
     const int32_t* dirs = (const int32_t*)(base + o1);
-    GridRw rw{nullptr, 0, rw_seed};
+    GridRw rw{nullptr, 0, rw_seed, rw_force == 2 ? 1 : 0};
     if (rw_offs) {
         // the table lives in a vector of the caller: the copy is complete before this function returns
         // (ab_check_device_errors below synchronises; in asynchronous mode synchronise here)
@@ -615,7 +627,7 @@ __global__ void k_sch_gather(GridDev<2> g, const int32_t* __restrict__ grid_ids,
     const int y = (int)(k / g.dims[0]), x = (int)(k - (int64_t)y * g.dims[0]);
     pos[id - 1] = x + 1;
     pos[cap + id - 1] = y + 1;
-    mood[id - 1] = grid_mood[k];
+    mood[id - 1] = grid_mood[k] == 1 ? 1 : 0;       // cell codes: 1 happy, 0 unhappy, 2 empty, 3 unhappy and not scheduled
 }
 
 // Happiness pass.  One thread per cell; a lane loads its own column of the three rows and takes the
@@ -777,6 +789,25 @@ k_sch_compact4(const uint8_t* __restrict__ grid_mood, int64_t nchunks, const uin
     }
 }
 
+// Scheduled subset (Schedulers.Partially / an id list): after the happiness pass, the agents that were NOT scheduled
+// get their previous mood back — coded 1 (happy) or 3 (unhappy, not a mover) — and the unhappy count of the chunk
+// (one CTA = one chunk of the compaction: 128 or SCH_TB cells) is recounted.
+__global__ void k_sch_mask(const int32_t* __restrict__ grid_ids, const uint8_t* __restrict__ old_mood, uint8_t* __restrict__ grid_mood,
+                           int64_t ncells, const uint8_t* __restrict__ active, uint32_t* __restrict__ chunkU) {
+    const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    bool unhappy = false;
+    if (k < ncells) {
+        const int id = grid_ids[k];
+        if (id != 0) {
+            uint8_t m = grid_mood[k];
+            if (!active[id - 1]) { m = old_mood[k] == 1 ? 1 : 3; grid_mood[k] = m; }
+            unhappy = m == 0;
+        }
+    }
+    const int nu = __syncthreads_count(unhappy);
+    if (threadIdx.x == 0 && chunkU) chunkU[blockIdx.x] = (uint32_t)nu;
+}
+
 // Seeded pseudo-random permutation of [0, n): 4-round Feistel network on 2*hb bits, cycle-walked into range.
 __device__ __forceinline__ uint32_t sch_mix(uint32_t x, uint64_t key) {
     uint64_t z = (uint64_t)x + key + 0x9E3779B97F4A7C15ull;
@@ -885,6 +916,22 @@ extern "C" int ab_nearby_positions_fill(ab_handle* h, const int32_t* qpos, int64
     return ab_grid_positions(h, qpos, nq, r, empty_only, nullptr, offsets, pos_out);
 }
 
+extern "C" int ab_step_schelling(ab_handle* h, const ab_schelling_params* p, int64_t nsteps, int64_t* n_moved);
+// The Schelling step for a scheduled subset (schedulers.jl:68-120): only the scheduled agents run schelling_step!
+// (tutorial.jl:351-376) — the others keep their mood and their position, and stay neighbours of everyone.
+extern "C" int ab_step_schelling_active(ab_handle* h, const ab_schelling_params* p, int64_t nsteps, const int64_t* active_ids,
+                                        int64_t nactive, int64_t* n_moved) {
+    if (!active_ids) return ab_step_schelling(h, p, nsteps, n_moved);
+    if (h->desc.kind != AB_SPACE_GRID_SINGLE) return ab_fail(h, AB_ERR_INVALID, "the Schelling rule needs a 2-D GridSpaceSingle handle");
+    if (n_moved) *n_moved = 0;
+    if (h->n == 0 || nsteps == 0) return AB_OK;
+    AB_TRY(ab_set_step_mask(h, active_ids, nactive));
+    h->step_mask_cur = h->step_mask;
+    const int rc = ab_step_schelling(h, p, nsteps, n_moved);
+    h->step_mask_cur = nullptr;
+    return rc;
+}
+
 extern "C" int ab_step_schelling(ab_handle* h, const ab_schelling_params* p, int64_t nsteps, int64_t* n_moved) {
     if (!p) return ab_fail(h, AB_ERR_INVALID, "null params");
     if (h->desc.kind != AB_SPACE_GRID_SINGLE || h->D != 2) return ab_fail(h, AB_ERR_INVALID, "the Schelling rule needs a 2-D GridSpaceSingle handle");
@@ -916,8 +963,11 @@ extern "C" int ab_step_schelling(ab_handle* h, const ab_schelling_params* p, int
         AB_CUDA(h, cudaMemsetAsync(base, 0, 256 + 2 * nbpad * sizeof(uint32_t), h->stream));
     }
     GridDev<2> g = make_grid<2>(h);
+    uint8_t* old_mood = nullptr;
+    if (h->step_mask_cur) AB_TRY(ab_scratch(h, (size_t)ncells, (void**)&old_mood));
     AB_CUDA(h, cudaEventRecord(h->ev0, h->stream));
     for (int64_t st = 0; st < nsteps; ++st) {
+        if (old_mood) AB_CUDA(h, cudaMemcpyAsync(old_mood, h->grid_mood, (size_t)ncells, cudaMemcpyDeviceToDevice, h->stream));
         {
             AB_LAUNCH(h, fast ? "k_sch_happy4" : "k_sch_happy");
             const dim3 g4((h->dims[0] + 1023) / 1024, (h->dims[1] + SCH4_R - 1) / SCH4_R);
@@ -925,6 +975,11 @@ extern "C" int ab_step_schelling(ab_handle* h, const ab_schelling_params* p, int
             else if (fast) k_sch_happy4<false><<<g4, 256, 0, h->stream>>>(g, h->grid_group, h->grid_mood, p->min_to_be_happy, diag, nullptr, nullptr);
             else if (p->relocate) k_sch_happy<true><<<nblocks, SCH_TB, 0, h->stream>>>(g, h->grid_group, h->grid_mood, ncells, p->min_to_be_happy, diag, blockU, blockE);
             else k_sch_happy<false><<<nblocks, SCH_TB, 0, h->stream>>>(g, h->grid_group, h->grid_mood, ncells, p->min_to_be_happy, diag, nullptr, nullptr);
+        }
+        if (old_mood) {
+            AB_LAUNCH(h, "k_sch_mask");
+            k_sch_mask<<<nblocks, fast ? 128 : SCH_TB, 0, h->stream>>>(h->grid_ids, old_mood, h->grid_mood, ncells, h->step_mask_cur,
+                                                                     p->relocate ? blockU : nullptr);
         }
         if (p->relocate) {
             AB_TRY(ab_scan_u32(h, blockU, baseU, (uint32_t)nblocks));

@@ -234,6 +234,7 @@ int ab_comm_transfer(ab_handle* h);
 int ab_comm_unpack(ab_handle* h, bool want_agg);
 bool ab_comm_local(const ab_handle* h);              // linked to in-process peers (ab_comm_link_local)
 int ab_comm_refresh_counts(ab_handle* h);            // owned / window agent counts back to the host
+int ab_set_step_mask(ab_handle* h, const int64_t* active_ids, int64_t nactive);   // by-id mask of a scheduled subset -> h->step_mask
 int ab_grid_build(ab_handle* h);
 int ab_grid_sync_columns(ab_handle* h);   // cell-major Schelling state -> agent columns (pos, mood)
 void ab_grid_free(ab_handle* h);

@@ -27,6 +27,7 @@ template <class T> struct PfU {
     T dt, half_dt2;
     double cutoff;
     T thr;          // exact_threshold<T>(cutoff): d <= cutoff  <=>  d² <= thr
+    const uint8_t* active;   // scheduled agents by id (Schedulers.Partially / an id list); nullptr: every agent moves
 };
 
 template <class T> static T pf_threshold_host(double r) {
@@ -119,7 +120,7 @@ __global__ void __launch_bounds__(128, PF_MINB)
 k_pf_fine(SpaceDev<T, D> sp, PfU<T> u, const T* __restrict__ pos, const T* __restrict__ vel, const T* __restrict__ rad,
           const T* __restrict__ kk, const T* __restrict__ mass, const uint32_t* __restrict__ key,
           const uint32_t* __restrict__ cs, int64_t cap, int n, T* __restrict__ npos, T* __restrict__ nvel,
-          uint32_t* __restrict__ newkey, uint32_t* __restrict__ rank, TileGeo tg,
+          uint32_t* __restrict__ newkey, uint32_t* __restrict__ rank, TileGeo tg, const int32_t* __restrict__ ids,
           int* __restrict__ far, int* __restrict__ err) {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
@@ -127,6 +128,20 @@ k_pf_fine(SpaceDev<T, D> sp, PfU<T> u, const T* __restrict__ pos, const T* __res
     int c[D];
 #pragma unroll
     for (int d = 0; d < D; ++d) { p[d] = pos[(size_t)d * cap + s]; v[d] = vel[(size_t)d * cap + s]; f[d] = T(0); }
+    if (u.active && !u.active[ids[s]]) {
+        // not scheduled this tick (agent_step! of celllistmap.jl:176-191 does not run for it): the particle keeps its
+        // state and remains a force partner of the others
+        const uint32_t k0 = key[s];
+#pragma unroll
+        for (int d = 0; d < D; ++d) { npos[(size_t)d * cap + s] = p[d]; nvel[(size_t)d * cap + s] = v[d]; }
+        newkey[s] = k0;
+        rank[s] = atomicAdd(&tg.cell_count[k0], 1u);
+        const uint32_t fr0 = k0 / (uint32_t)sp.dims[0];
+        const uint32_t tile = fr0 * tg.tpr + __umulhi(k0 - fr0 * (uint32_t)sp.dims[0], tg.magic);
+        const unsigned m = __match_any_sync(__activemask(), tile);
+        if ((m & (0u - m)) == (1u << (threadIdx.x & 31))) atomicAdd(&tg.tile_count[tile], (uint32_t)__popc(m));
+        return;
+    }
     const T ri = rad[s], ki = kk[s], mi = mass[s];
     key_to_cell<T, D>(sp, key[s], c);        // K == 1 on this path: fine cell == reference cell
     const int d0 = sp.dims[0], d1 = sp.dims[1], d2n = D == 3 ? sp.dims[2] : 1;
@@ -283,7 +298,7 @@ k_pf_generic(SpaceDev<T, D> sp, PfU<T> u, const T* __restrict__ pos, const T* __
 template <class T, int D>
 __global__ void k_pf_integrate(SpaceDev<T, D> sp, PfU<T> u, const T* __restrict__ pos, const T* __restrict__ vel,
                                const T* __restrict__ mass, int64_t cap, int n, T* __restrict__ a_pos /*fown -> npos*/,
-                               T* __restrict__ a_vel /*freact -> nvel*/, int* __restrict__ err) {
+                               T* __restrict__ a_vel /*freact -> nvel*/, const int32_t* __restrict__ ids, int* __restrict__ err) {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
     T p[D], v[D], f[D], np_[D], nv[D];
@@ -291,6 +306,11 @@ __global__ void k_pf_integrate(SpaceDev<T, D> sp, PfU<T> u, const T* __restrict_
     for (int d = 0; d < D; ++d) {
         p[d] = pos[(size_t)d * cap + s]; v[d] = vel[(size_t)d * cap + s];
         f[d] = a_pos[(size_t)d * cap + s] + a_vel[(size_t)d * cap + s];
+    }
+    if (u.active && !u.active[ids[s]]) {                  // not scheduled: keeps its state
+#pragma unroll
+        for (int d = 0; d < D; ++d) { a_pos[(size_t)d * cap + s] = p[d]; a_vel[(size_t)d * cap + s] = v[d]; }
+        return;
     }
     if (!pf_integrate<T, D>(sp, u, p, v, f, mass[s], np_, nv)) atomicOr(err, AB_EF_OUTSIDE);
 #pragma unroll
@@ -308,6 +328,7 @@ static int pf_steps_t(ab_handle* h, const ab_pairforce_params* p, int64_t nsteps
     u.half_dt2 = T(0);
     u.cutoff = p->cutoff;
     u.thr = pf_threshold_host<T>(p->cutoff);
+    u.active = h->step_mask_cur;
     const double s = (double)(T)h->desc.spacing;
     bool fine = p->cutoff > 0 && p->cutoff <= s && ab_resort_applicable(h);
     for (int d = 0; d < D; ++d) if (h->dims[d] < 3) fine = false;
@@ -327,7 +348,7 @@ static int pf_steps_t(ab_handle* h, const ab_pairforce_params* p, int64_t nsteps
             {
                 AB_LAUNCH(h, "k_pf_fine");
                 k_pf_fine<T, D><<<ab_blocks(n, TB), TB, 0, h->stream>>>(sp, u, pos, vel, rad, kk, mass, h->key[cur], h->cell_start, h->cap, n,
-                                                                        (T*)h->tmp_pos, (T*)h->tmp_vel, h->newkey, h->rank, make_tilegeo(h),
+                                                                        (T*)h->tmp_pos, (T*)h->tmp_vel, h->newkey, h->rank, make_tilegeo(h), h->id[cur],
                                                                         h->d_err + 1, h->d_err);
             }
             // did anybody move further than one cell?  (then the tiled re-sort cannot find it)
@@ -350,13 +371,27 @@ static int pf_steps_t(ab_handle* h, const ab_pairforce_params* p, int64_t nsteps
             {
                 AB_LAUNCH(h, "k_pf_integrate");
                 k_pf_integrate<T, D><<<ab_blocks(n, 256), 256, 0, h->stream>>>(sp, u, pos, vel, mass, h->cap, n, (T*)h->tmp_pos,
-                                                                             (T*)h->tmp_vel, h->d_err);
+                                                                             (T*)h->tmp_vel, h->id[cur], h->d_err);
             }
             AB_TRY(ab_reindex_from(h, h->tmp_pos, h->tmp_vel, false));
         }
     }
     AB_CUDA(h, cudaEventRecord(h->ev1, h->stream));
     return AB_OK;
+}
+
+extern "C" int ab_step_pairforce(ab_handle* h, const ab_pairforce_params* p, int64_t nsteps);
+// The pair-force step for a scheduled subset (Schedulers.Partially / an id list, schedulers.jl:68-120): model_step!
+// computes the forces of every particle, agent_step! (the integrator, celllistmap.jl:176-191) runs for the scheduled ones.
+extern "C" int ab_step_pairforce_active(ab_handle* h, const ab_pairforce_params* p, int64_t nsteps, const int64_t* active_ids,
+                                        int64_t nactive) {
+    if (!active_ids) return ab_step_pairforce(h, p, nsteps);
+    if (h->n == 0 || nsteps == 0) return AB_OK;
+    AB_TRY(ab_set_step_mask(h, active_ids, nactive));
+    h->step_mask_cur = h->step_mask;
+    const int rc = ab_step_pairforce(h, p, nsteps);
+    h->step_mask_cur = nullptr;
+    return rc;
 }
 
 extern "C" int ab_step_pairforce(ab_handle* h, const ab_pairforce_params* p, int64_t nsteps) {

@@ -130,10 +130,14 @@ class PairForceRule:
     def __init__(self, dt=0.001, cutoff=20.0):
         self.dt, self.cutoff = dt, cutoff
 
-    def __call__(self, model, nsteps=1):
+    def __call__(self, model, nsteps=1, ids=None):
         pp = L.PairForceParams(dt=self.dt, cutoff=self.cutoff, field_r=model.field_id("r"),
                                field_k=model.field_id("k"), field_mass=model.field_id("mass"))
-        model._ck(L.lib().ab_step_pairforce(model.h, C.byref(pp), int(nsteps)))
+        if ids is None:
+            model._ck(L.lib().ab_step_pairforce(model.h, C.byref(pp), int(nsteps)))
+        else:       # the forces of all particles (model_step!), the integrator (agent_step!) for the scheduled ones
+            a = np.ascontiguousarray(ids, dtype=np.int64)
+            model._ck(L.lib().ab_step_pairforce_active(model.h, C.byref(pp), int(nsteps), model._ptr(a), a.shape[0]))
 
 
 class SchellingRule:
@@ -143,10 +147,14 @@ class SchellingRule:
         self.min_to_be_happy, self.relocate, self.seed = min_to_be_happy, relocate, seed
         self.last_moved = 0
 
-    def __call__(self, model, nsteps=1):
+    def __call__(self, model, nsteps=1, ids=None):
         sp = L.SchellingParams(min_to_be_happy=self.min_to_be_happy, relocate=int(self.relocate), seed=self.seed)
         moved = C.c_int64(0)
-        model._ck(L.lib().ab_step_schelling(model.h, C.byref(sp), int(nsteps), C.byref(moved)))
+        if ids is None:
+            model._ck(L.lib().ab_step_schelling(model.h, C.byref(sp), int(nsteps), C.byref(moved)))
+        else:       # only the scheduled agents run schelling_step!; the others keep mood and position
+            a = np.ascontiguousarray(ids, dtype=np.int64)
+            model._ck(L.lib().ab_step_schelling_active(model.h, C.byref(sp), int(nsteps), model._ptr(a), a.shape[0], C.byref(moved)))
         self.last_moved = moved.value
 
 
@@ -445,15 +453,28 @@ class StandardABM:
                                         0 if a is None else a.shape[0], int(ifempty), int(force_motion)))
 
     # -- stepping (src/simulations/step_standard.jl:24-31) --------------------
-    def step(self, n=1, scheduler=None):
-        """step!(model, n).  `scheduler`: None (every agent: fastest / ByID / Randomly are equivalent under the
-        synchronous update), an id list, or a callable model -> id list evaluated every tick (Schedulers.Partially
-        and custom schedulers, schedulers.jl:8, 68-120) — flock rule only."""
+    def step(self, n=1, scheduler=None, check_every=1):
+        """step!(model, n) or step!(model, f) (src/simulations/step.jl:7-27, step_standard.jl:9-31).
+
+        `n`: an integer — exactly n ticks, batched into one ccall — or a predicate f(model, t): the model steps until
+        f(model, t) returns true, t = ticks taken by this call (`until(t1, t0, f, model) = !f(model, t1 - t0)`,
+        step.jl:38).  The predicate runs on the host between device calls of `check_every` ticks (1 = the reference's
+        tick-by-tick evaluation).
+        `scheduler`: None (every agent: fastest / ByID / Randomly / ByProperty are equivalent under the synchronous
+        update), an id list, or a callable model -> id list evaluated every tick (Schedulers.Partially and custom
+        schedulers, schedulers.jl:8, 68-120); a scheduled subset steps, the other agents keep their state."""
         if self.model_step is None:
             raise AgentsError(L.ERR_STATE, "no model_step! rule")
+        if callable(n):
+            t0 = self.time
+            while not n(self, self.time - t0):
+                if scheduler is not None:
+                    self.step(1, scheduler=scheduler)
+                else:
+                    self.model_step(self, int(check_every))
+                    self.time += int(check_every)
+            return self
         if scheduler is not None:
-            if not isinstance(self.model_step, FlockRule):
-                raise AgentsError(L.ERR_INVALID, "a scheduled subset is available for the flock rule")
             for _ in range(int(n)):
                 self.model_step(self, 1, ids=scheduler(self) if callable(scheduler) else scheduler)
                 self.time += 1
@@ -461,6 +482,22 @@ class StandardABM:
         self.model_step(self, int(n))      # n ticks batched into one ccall
         self.time += int(n)
         return self
+
+    # -- schedulers (src/submodules/schedulers.jl) ------------------------------
+    def schedule_by_property(self, field, comp=0):
+        """Schedulers.ByProperty(field)(model) — schedulers.jl:130-151: the agent ids ordered by `sortperm` of the
+        property column (ascending, stable: Julia's default sort algorithm for sortperm is stable).  The column is
+        read from the device; the order is built on the host."""
+        col = self.column(field)
+        if col.ndim > 1:
+            col = col[:, comp]
+        return np.argsort(col, kind="stable").astype(np.int64) + 1
+
+    def schedule_partially(self, p, rng):
+        """Schedulers.Partially(p)(model) — schedulers.jl:109-120: randsubseq of the ids with probability p (each id is
+        kept independently; the reference draws from abmrng(model), whose stream is not reproduced: pass a numpy Generator)."""
+        n = self.nagents()
+        return (np.nonzero(rng.random(n) < p)[0] + 1).astype(np.int64)
 
     # -- data collection (src/simulations/collect.jl:154-183, 466-502) ----------
     def collect(self, adata):

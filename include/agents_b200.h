@@ -227,7 +227,9 @@ int ab_walk(ab_handle* h, const void* directions, const int64_t* active_ids, int
  *   GridSpace / GridSpaceSingle: one entry of offsets_at_radius(model, r) (grid_general.jl:119-136; floor(r) steps under
  *     :chebyshev / :manhattan, :euclidean fails with AB_ERR_INVALID), index floor(u0 * L); with force_motion (and
  *     ifempty, or a GridSpaceSingle) the choice is made among the empty targets (walk.jl:200-214) in the sequential
- *     order of `active_ids`, and the agent moves to the chosen empty position. */
+ *     order of `active_ids`.  force_motion = 1: the agent moves to the chosen empty position (the docstring's
+ *     behaviour); force_motion = 2: the reference's code as written — the chosen POSITION is handed to walk! as a
+ *     direction (walk.jl:170-172, :193-195), i.e. target = normalize_position(pos .+ choice), taken only if empty. */
 int ab_randomwalk(ab_handle* h, double r, uint64_t seed, const int64_t* active_ids, int64_t nactive, int ifempty,
                   int force_motion);
 /* randomwalk!(agent, model[, r]; polar, azimuthal) on a ContinuousSpace{2} / {3} with angle distributions
@@ -248,9 +250,16 @@ int ab_step_flock(ab_handle* h, const ab_flock_params* p, int64_t nsteps);      
  * NULL = every agent (ab_step_flock).  Not available on a sharded handle. */
 int ab_step_flock_active(ab_handle* h, const ab_flock_params* p, int64_t nsteps, const int64_t* active_ids, int64_t nactive);
 int ab_step_pairforce(ab_handle* h, const ab_pairforce_params* p, int64_t nsteps);   /* examples/celllistmap.jl:143-191 */
+/* Scheduled subset for the pair-force rule: model_step! computes the forces of every particle, agent_step! (the
+ * integrator, celllistmap.jl:176-191) runs for the agents of `active_ids`; the others keep position and velocity. */
+int ab_step_pairforce_active(ab_handle* h, const ab_pairforce_params* p, int64_t nsteps, const int64_t* active_ids, int64_t nactive);
 /* Schelling on GridSpaceSingle.  Columns "group" (i32) and "mood" (u8) must be
  * registered.  n_moved (optional) receives the movers of the last step. */
 int ab_step_schelling(ab_handle* h, const ab_schelling_params* p, int64_t nsteps, int64_t* n_moved);
+/* Scheduled subset for the Schelling rule (schedulers.jl:68-120): only the agents of `active_ids` run schelling_step!
+ * (docs/src/tutorial.jl:351-376); the others keep their mood and position and stay neighbours of everyone. */
+int ab_step_schelling_active(ab_handle* h, const ab_schelling_params* p, int64_t nsteps, const int64_t* active_ids,
+                             int64_t nactive, int64_t* n_moved);
 
 /* neighbour count N seen by every bird in the last flock step (id order);
  * diagnostic used by the parity tests (neighbour-set flips). */

@@ -463,10 +463,11 @@ def grid_offsets_at_radius(dims, periodic, metric, r):
     return offs[keep]
 
 
-def grid_randomwalk(o, ids, r, seed, ifempty=True, force_motion=False):
+def grid_randomwalk(o, ids, r, seed, ifempty=True, force_motion=False, literal=False):
     """randomwalk!(agent, model, r; ifempty, force_motion) agent after agent on a GridOracle (walk.jl:154-214).
-    With force_motion the agent moves TO the chosen empty position (the documented behaviour; the reference
-    passes that position on to walk! as a direction, walk.jl:170 / :193)."""
+    With force_motion the agent moves TO the chosen empty position (the documented behaviour); `literal=True`
+    follows the reference's code as written instead: the chosen position is passed on to walk! as a direction
+    (walk.jl:170-172 / :193-195), target = normalize_position(pos .+ choice), taken only if it is empty."""
     offs = grid_offsets_at_radius(o.dims, o.periodic, o.metric, r)
     L = len(offs)
     dims = np.asarray(o.dims, dtype=np.int64)
@@ -500,6 +501,10 @@ def grid_randomwalk(o, ids, r, seed, ifempty=True, force_motion=False):
                 if not empties:
                     continue
                 tgt = empties[min(int(np.floor(rw_u01(seed, id, 2 * L) * len(empties))), len(empties) - 1)]
+            if literal:
+                tgt = norm(np.add(p, tgt))
+                if occ.get(tgt, 0) != 0:
+                    continue
         o.move_agent_to(id, tgt)
         occ[p] -= 1
         occ[tgt] = occ.get(tgt, 0) + 1

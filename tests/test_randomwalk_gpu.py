@@ -47,6 +47,29 @@ def test_grid_randomwalk_equals_oracle(single, ifempty, force, metric, periodic,
     m.close()
 
 
+@pytest.mark.parametrize("single", [False, True])
+@pytest.mark.parametrize("metric,periodic", [("chebyshev", True), ("manhattan", (True, False)), ("chebyshev", False)])
+def test_grid_randomwalk_force_motion_as_written(single, metric, periodic):
+    """force_motion = 2: the reference's code as written — the empty POSITION found by random_empty_pos_in_offsets is
+    passed to walk! as a direction (walk.jl:170-172, :193-195).  Both readings are offered; both are checked."""
+    dims = (11, 8)
+    pos = random_positions(dims, 60, 4, single)
+    m, o = make(dims, periodic, metric, single, pos)
+    m2, o2 = make(dims, periodic, metric, single, pos)
+    n = len(pos)
+    for tick in range(3):
+        m.randomwalk(1, seed=77 + tick, ifempty=True, force_motion=2)
+        grid_randomwalk(o, range(1, n + 1), 1, 77 + tick, True, True, literal=True)
+        assert np.array_equal(m.pos, o.positions())
+        m2.randomwalk(1, seed=77 + tick, ifempty=True, force_motion=1)
+        grid_randomwalk(o2, range(1, n + 1), 1, 77 + tick, True, True)
+        assert np.array_equal(m2.pos, o2.positions())
+        if single:
+            assert len({tuple(p) for p in m.pos}) == n
+    assert not np.array_equal(m.pos, m2.pos)                  # the two readings are different rules
+    m.close(); m2.close()
+
+
 def test_grid_randomwalk_3d_and_errors():
     dims = (6, 5, 4)
     pos = random_positions(dims, 30, 2, True)
