@@ -134,12 +134,21 @@ static int64_t cells_per_layer(const ab_handle* h) { return (h->ncells / h->dims
 // ---------------------------------------------------------------------------------------------------
 // message: [hdr 16 B][cs slice (ncs + 1) u32, padded to 16 B][pos D x C][vel D x C][id C][key C]
 // ---------------------------------------------------------------------------------------------------
+// ... followed by the user columns (every registered field beyond pos / vel: the r, k, mass of the pair-force rule,
+// per-bird parameters, ...), each [ncomp x C] of its element size
+#define AB_MSG_MAXF 8
 struct MsgLayout {
     size_t off_cs, off_pos, off_vel, off_id, off_key, bytes;
     uint32_t ncs;
     int64_t C;
+    int nx;                              // user columns in the message
+    size_t off_x[AB_MSG_MAXF];
+    int x_ncomp[AB_MSG_MAXF], x_esize[AB_MSG_MAXF];
 };
-static MsgLayout msg_layout(int D, size_t tsize, int64_t C, uint32_t ncs) {
+struct MsgCols { char* p[AB_MSG_MAXF]; };   // the columns' device arrays (current buffer), same order
+static MsgLayout msg_layout(const ab_handle* h, int64_t C, uint32_t ncs) {
+    const int D = h->D;
+    const size_t tsize = h->tsize;
     MsgLayout m;
     m.ncs = ncs;
     m.C = C;
@@ -148,15 +157,38 @@ static MsgLayout msg_layout(int D, size_t tsize, int64_t C, uint32_t ncs) {
     m.off_vel = m.off_pos + (size_t)D * C * tsize;
     m.off_id = m.off_vel + (size_t)D * C * tsize;
     m.off_key = m.off_id + (size_t)C * 4;
-    m.bytes = (m.off_key + (size_t)C * 4 + 15) / 16 * 16;
+    size_t end = (m.off_key + (size_t)C * 4 + 15) / 16 * 16;
+    m.nx = 0;
+    for (size_t f = 2; f < h->fields.size() && m.nx < AB_MSG_MAXF; ++f) {
+        m.off_x[m.nx] = end;
+        m.x_ncomp[m.nx] = h->fields[f].ncomp;
+        m.x_esize[m.nx] = (int)h->fields[f].esize;
+        end = (end + (size_t)h->fields[f].ncomp * C * h->fields[f].esize + 15) / 16 * 16;
+        m.nx++;
+    }
+    for (int i = m.nx; i < AB_MSG_MAXF; ++i) { m.off_x[i] = 0; m.x_ncomp[i] = 0; m.x_esize[i] = 0; }
+    m.bytes = end;
     return m;
+}
+static MsgCols msg_cols(const ab_handle* h) {
+    MsgCols c;
+    int k = 0;
+    for (size_t f = 2; f < h->fields.size() && k < AB_MSG_MAXF; ++f) c.p[k++] = (char*)h->fields[f].buf[h->cur];
+    for (; k < AB_MSG_MAXF; ++k) c.p[k] = nullptr;
+    return c;
+}
+// one element of a user column: agent slot `s` of a [ncomp x cap] array <-> message row `t` of a [ncomp x C] array
+__device__ __forceinline__ void copy_elem(char* dst, const char* src, int esize) {
+    if (esize == 8) *reinterpret_cast<uint64_t*>(dst) = *reinterpret_cast<const uint64_t*>(src);
+    else if (esize == 4) *reinterpret_cast<uint32_t*>(dst) = *reinterpret_cast<const uint32_t*>(src);
+    else *dst = *src;
 }
 
 // Packs the boundary layers of the CURRENT sorted state: blockIdx.y = 0 bottom W owned layers (keys
 // [0, ncs)), 1 = top W owned layers (keys [kown - ncs, kown)).
 template <class E, int D>
 __global__ void __launch_bounds__(256)
-k_halo_pack(MsgLayout m, uint32_t kown, const uint32_t* __restrict__ cs, const E* __restrict__ pos,
+k_halo_pack(MsgLayout m, MsgCols xc, uint32_t kown, const uint32_t* __restrict__ cs, const E* __restrict__ pos,
             const E* __restrict__ vel, const int32_t* __restrict__ id, const uint32_t* __restrict__ key, int64_t cap,
             char* __restrict__ buf0, char* __restrict__ buf1, int* __restrict__ err,
             uint32_t* done_ctr, uint32_t* flag0, uint32_t* flag1, uint32_t epoch) {
@@ -189,6 +221,11 @@ k_halo_pack(MsgLayout m, uint32_t kown, const uint32_t* __restrict__ cs, const E
         }
         mid[t] = id[s];
         mkey[t] = key[s];
+        for (int f = 0; f < m.nx; ++f) {
+            const int es = m.x_esize[f];
+            for (int c = 0; c < m.x_ncomp[f]; ++c)
+                copy_elem(buf + m.off_x[f] + ((size_t)c * m.C + t) * es, xc.p[f] + ((size_t)c * cap + s) * es, es);
+        }
     }
     if (flag0) {
         // direct exchange: the LAST CTA to finish publishes the exchange number in the neighbours' flags.
@@ -230,7 +267,7 @@ __device__ __forceinline__ bool wait_flag(const uint32_t* f, uint32_t epoch) {
 // so no separate aggregate launch follows the install.
 template <class T, int D>
 __global__ void __launch_bounds__(256)
-k_halo_unpack(SpaceDev<T, D> sp, MsgLayout m, uint32_t kown, uint32_t* __restrict__ cs, T* __restrict__ pos, T* __restrict__ vel,
+k_halo_unpack(SpaceDev<T, D> sp, MsgLayout m, MsgCols xc, uint32_t kown, uint32_t* __restrict__ cs, T* __restrict__ pos, T* __restrict__ vel,
               int32_t* __restrict__ id, uint32_t* __restrict__ key, int64_t cap, const char* __restrict__ buf0,
               const char* __restrict__ buf1, int* __restrict__ err, const uint32_t* wflag0, const uint32_t* wflag1,
               uint32_t epoch, int nbc, int nba, T* __restrict__ agg, int64_t agg_stride, uint32_t halo_cell0,
@@ -290,6 +327,11 @@ k_halo_unpack(SpaceDev<T, D> sp, MsgLayout m, uint32_t kown, uint32_t* __restric
             }
             id[s] = mid[t];
             key[s] = mkey[t] + kdelta;
+            for (int f = 0; f < m.nx; ++f) {
+                const int es = m.x_esize[f];
+                for (int c = 0; c < m.x_ncomp[f]; ++c)
+                    copy_elem(xc.p[f] + ((size_t)c * cap + s) * es, buf + m.off_x[f] + ((size_t)c * m.C + t) * es, es);
+            }
         }
         return;
     }
@@ -374,14 +416,14 @@ static int ensure_buffers(ab_handle* h) {
     C = (C + 63) / 64 * 64;
     if (c->ipc_on) {
         if (C != c->ipc_cap) return ab_fail(h, AB_ERR_STATE, "message capacity changed after ab_comm_ipc_export");
-        const MsgLayout mi = msg_layout(h->D, h->tsize, C, ncs);
+        const MsgLayout mi = msg_layout(h, C, ncs);
         if (mi.bytes > c->ipc_stride) return ab_fail(h, AB_ERR_STATE, "message does not fit the exported block");
         c->cap_agents = C; c->msg_bytes = mi.bytes; c->msg_K = h->K;
         return AB_OK;
     }
-    if (c->cap_agents == C && c->msg_K == h->K && c->sendbuf[0]) return AB_OK;
+    const MsgLayout m = msg_layout(h, C, ncs);
+    if (c->cap_agents == C && c->msg_K == h->K && c->sendbuf[0] && c->msg_bytes == m.bytes) return AB_OK;
     AB_CUDA(h, cudaStreamSynchronize(h->stream));
-    const MsgLayout m = msg_layout(h->D, h->tsize, C, ncs);
     for (int i = 0; i < 2; ++i) {
         if (c->sendbuf[i]) { AB_CUDA(h, cudaFree(c->sendbuf[i])); c->sendbuf[i] = nullptr; }
         if (c->recvbuf[i]) { AB_CUDA(h, cudaFree(c->recvbuf[i])); c->recvbuf[i] = nullptr; }
@@ -401,7 +443,8 @@ static int pack_t(ab_handle* h) {
     const int cur = h->cur;
     const uint32_t ncs = (uint32_t)(AB_HALO_W * keys_per_layer(h));
     const uint32_t kown = (uint32_t)(h->win_nl * keys_per_layer(h));
-    const MsgLayout m = msg_layout(D, sizeof(E), c->cap_agents, ncs);
+    const MsgLayout m = msg_layout(h, c->cap_agents, ncs);
+    if (h->fields.size() > 2u + AB_MSG_MAXF) return ab_fail(h, AB_ERR_INVALID, "too many user columns for the halo message");
     // one item per thread (up to 592 CTAs per side): the stores are posted writes, the cost is latency
     const int nb = (int)std::min<int64_t>(std::max<int64_t>((std::max<int64_t>(c->cap_agents, ncs) + 255) / 256, 1), 592);
     // in-process peers: they must have consumed the previous message before it is overwritten
@@ -414,7 +457,7 @@ static int pack_t(ab_handle* h) {
     char* dst1 = c->ipc_on ? ipc_slot(c->ipc_upper, c->ipc_stride, c->cur_par, 1) : (char*)c->sendbuf[1];
     {
         AB_LAUNCH(h, "k_halo_pack");
-        k_halo_pack<E, D><<<dim3(nb, 2), 256, 0, h->stream>>>(m, kown, h->cell_start, (const E*)h->fields[0].buf[cur],
+        k_halo_pack<E, D><<<dim3(nb, 2), 256, 0, h->stream>>>(m, msg_cols(h), kown, h->cell_start, (const E*)h->fields[0].buf[cur],
                                                              (const E*)h->fields[1].buf[cur], h->id[cur], h->key[cur], h->cap,
                                                              dst0, dst1, h->d_err,
                                                              c->ipc_on ? ipc_flag(c->ipc_block, c->ipc_stride, 2, 0) : nullptr,
@@ -464,7 +507,7 @@ static int unpack_t(ab_handle* h, bool want_agg) {
     const int cur = h->cur;
     const uint32_t ncs = (uint32_t)(AB_HALO_W * keys_per_layer(h));
     const uint32_t kown = (uint32_t)(h->win_nl * keys_per_layer(h));
-    const MsgLayout m = msg_layout(D, sizeof(T), c->cap_agents, ncs);
+    const MsgLayout m = msg_layout(h, c->cap_agents, ncs);
     const int nbc = (int)std::min<int64_t>(std::max<int64_t>((std::max<int64_t>(c->cap_agents / 4, ncs) + 255) / 256, 1), 592);
     const int64_t cpl = cells_per_layer(h);
     const int nfr = D == 2 ? h->K : h->K * h->K;
@@ -476,7 +519,7 @@ static int unpack_t(ab_handle* h, bool want_agg) {
     }
     {
         AB_LAUNCH(h, "k_halo_unpack");
-        k_halo_unpack<T, D><<<dim3(2 * nbc + 2 * nba), 256, 0, h->stream>>>(make_space<T, D>(h), m, kown, h->cell_start, (T*)h->fields[0].buf[cur],
+        k_halo_unpack<T, D><<<dim3(2 * nbc + 2 * nba), 256, 0, h->stream>>>(make_space<T, D>(h), m, msg_cols(h), kown, h->cell_start, (T*)h->fields[0].buf[cur],
                                                                (T*)h->fields[1].buf[cur], h->id[cur], h->key[cur], h->cap,
                                                                c->ipc_on ? ipc_slot(c->ipc_block, c->ipc_stride, c->cur_par, 0) : (const char*)c->recvbuf[0],
                                                                c->ipc_on ? ipc_slot(c->ipc_block, c->ipc_stride, c->cur_par, 1) : (const char*)c->recvbuf[1], h->d_err,
@@ -641,7 +684,7 @@ int ab_comm_ipc_export(ab_handle* h, void* out64) {
     int ksh_max = ((h->ncells << h->D) <= h->nfine_cap) ? h->D : 0;                  // finest refinement a step may choose
     if (h->D == 2 && (h->ncells << 4) <= h->nfine_cap) ksh_max = 4;
     const uint32_t ncs_max = (uint32_t)(AB_HALO_W * ((h->ncells << ksh_max) / h->dims[h->D - 1]));
-    c->ipc_stride = (msg_layout(h->D, h->tsize, C, ncs_max).bytes + 255) / 256 * 256;
+    c->ipc_stride = (msg_layout(h, C, ncs_max).bytes + 255) / 256 * 256;       // user columns must be registered before the export
     c->ipc_cap = C;
     AB_CUDA(h, cudaMalloc((void**)&c->ipc_block, 4 * c->ipc_stride + 4096));
     AB_CUDA(h, cudaMemset(c->ipc_block, 0, 4 * c->ipc_stride + 4096));

@@ -270,9 +270,9 @@ __global__ void k_place(const uint32_t* __restrict__ newkey, const uint32_t* __r
 
 template <class E>
 __global__ void k_permute(const E* __restrict__ src, E* __restrict__ dst, const int32_t* __restrict__ perm,
-                          int64_t cap, int n, int ncomp) {
+                          int64_t cap, int n, int ncomp, const uint32_t* __restrict__ nlive) {
     int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= n) return;
+    if (s >= (nlive ? (int)*nlive : n)) return;        // slab window: the owned count lives on the device
     int o = perm[s];
     for (int c = 0; c < ncomp; ++c) dst[(size_t)c * cap + s] = src[(size_t)c * cap + o];
 }
@@ -338,18 +338,23 @@ int ab_scan_u32(ab_handle* h, uint32_t* count, uint32_t* start, uint32_t n) {
 }
 int ab_run_scan(ab_handle* h, uint32_t* dst) { return ab_scan_u32(h, h->cell_count, dst, (uint32_t)h->nfine); }
 
-int ab_permute_extra_fields(ab_handle* h) {
-    const int n = (int)h->n, cur = h->cur, nxt = cur ^ 1, TB = 256;
+int ab_permute_extra_fields(ab_handle* h, bool owned_only) {
+    const int cur = h->cur, nxt = cur ^ 1, TB = 256;
+    // slab window: only the owned slots were re-sorted (the halo columns arrive with the neighbours' messages); their
+    // number is the new cell_start entry behind the owned keys
+    const bool live = owned_only && h->win_W;
+    const int n = live ? (int)h->cap : (int)h->n;
+    const uint32_t* nlive = live ? h->cell_start + (h->nfine / h->dims[h->D - 1]) * h->win_nl : nullptr;
     const size_t first = h->desc.kind == AB_SPACE_CONTINUOUS ? 2 : 1;
     for (size_t f = first; f < h->fields.size(); ++f) {
         ab_field& fl = h->fields[f];
         AB_LAUNCH(h, "k_permute");
         if (fl.esize == 8)
-            k_permute<uint64_t><<<ab_blocks(n, TB), TB, 0, h->stream>>>((const uint64_t*)fl.buf[cur], (uint64_t*)fl.buf[nxt], h->perm, h->cap, n, fl.ncomp);
+            k_permute<uint64_t><<<ab_blocks(n, TB), TB, 0, h->stream>>>((const uint64_t*)fl.buf[cur], (uint64_t*)fl.buf[nxt], h->perm, h->cap, n, fl.ncomp, nlive);
         else if (fl.esize == 4)
-            k_permute<uint32_t><<<ab_blocks(n, TB), TB, 0, h->stream>>>((const uint32_t*)fl.buf[cur], (uint32_t*)fl.buf[nxt], h->perm, h->cap, n, fl.ncomp);
+            k_permute<uint32_t><<<ab_blocks(n, TB), TB, 0, h->stream>>>((const uint32_t*)fl.buf[cur], (uint32_t*)fl.buf[nxt], h->perm, h->cap, n, fl.ncomp, nlive);
         else
-            k_permute<uint8_t><<<ab_blocks(n, TB), TB, 0, h->stream>>>((const uint8_t*)fl.buf[cur], (uint8_t*)fl.buf[nxt], h->perm, h->cap, n, fl.ncomp);
+            k_permute<uint8_t><<<ab_blocks(n, TB), TB, 0, h->stream>>>((const uint8_t*)fl.buf[cur], (uint8_t*)fl.buf[nxt], h->perm, h->cap, n, fl.ncomp, nlive);
     }
     return AB_OK;
 }
@@ -385,7 +390,7 @@ static int reindex_t(ab_handle* h, const void* src_pos, const void* src_vel, boo
                     h->newkey, h->rank, h->cell_start, h->id[cur], h->idtmp, (const T*)src_pos, nullptr, h->cap, n,
                     (T*)h->fields[0].buf[nxt], nullptr, h->id[nxt], h->key[nxt], extra ? h->perm : nullptr, nullptr, h->place_prio);
         }
-        AB_TRY(ab_permute_extra_fields(h));
+        AB_TRY(ab_permute_extra_fields(h, false));
     }
     h->cur = nxt;
     h->slot_map_valid = false;

@@ -208,7 +208,7 @@ int ab_ensure_index(ab_handle* h);
 int ab_ensure_slot_map(ab_handle* h);
 int ab_set_refine(ab_handle* h, int K);
 int ab_reindex_from(ab_handle* h, const void* src_pos, const void* src_vel, bool count_done);
-int ab_permute_extra_fields(ab_handle* h);     // applies h->perm (new slot -> old slot) to user columns, cur -> cur^1
+int ab_permute_extra_fields(ab_handle* h, bool owned_only);   // applies h->perm (new slot -> old slot) to user columns, cur -> cur^1
 bool ab_resort_applicable(const ab_handle* h);
 int ab_resort_tiled(ab_handle* h, const void* src_pos, const void* src_vel, bool want_agg);
 int ab_resort_plan(ab_handle* h);              // tile geometry of the next tiled re-sort (before the step kernel that counts the keys)

@@ -86,9 +86,10 @@ __device__ __forceinline__ bool pf_integrate(const SpaceDev<T, D>& sp, const PfU
 // (in floating point) one cell beyond the 3^D block.
 template <class T, int D>
 __device__ __noinline__ void pf_accumulate_walk(const SpaceDev<T, D>& sp, const PfU<T>& u, int s, const T* p, const int* c,
-                                                T ri, T ki, const T* __restrict__ pos, const T* __restrict__ rad,
+                                                const int* cg, T ri, T ki, const T* __restrict__ pos, const T* __restrict__ rad,
                                                 const T* __restrict__ kk, const uint32_t* __restrict__ cs, int64_t cap, T* f) {
-    const int gr = grid_radius<T, D>(sp, p, c, u.cutoff);
+    // c: the agent's cell in this handle's (window) frame — the walk; cg: its global cell — the cell centre of grid_r
+    const int gr = grid_radius<T, D>(sp, p, cg, u.cutoff);
     for_each_run<D>(sp.dims, sp.periodic, AB_METRIC_EUCLIDEAN, c, gr, cs, sp.kb, false, [&](uint32_t b, uint32_t e, int) {
         for (uint32_t j = b; j < e; ++j) {
             if ((int)j == s) continue;
@@ -121,9 +122,9 @@ k_pf_fine(SpaceDev<T, D> sp, PfU<T> u, const T* __restrict__ pos, const T* __res
           const T* __restrict__ kk, const T* __restrict__ mass, const uint32_t* __restrict__ key,
           const uint32_t* __restrict__ cs, int64_t cap, int n, T* __restrict__ npos, T* __restrict__ nvel,
           uint32_t* __restrict__ newkey, uint32_t* __restrict__ rank, TileGeo tg, const int32_t* __restrict__ ids,
-          int* __restrict__ far, int* __restrict__ err) {
+          int* __restrict__ far, int* __restrict__ err, const uint32_t* __restrict__ nslots) {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= n) return;
+    if (s >= (nslots ? (int)*nslots : n)) return;            // slab window: the slot count lives on the device
     T p[D], v[D], f[D];
     int c[D];
 #pragma unroll
@@ -135,8 +136,9 @@ k_pf_fine(SpaceDev<T, D> sp, PfU<T> u, const T* __restrict__ pos, const T* __res
 #pragma unroll
         for (int d = 0; d < D; ++d) { npos[(size_t)d * cap + s] = p[d]; nvel[(size_t)d * cap + s] = v[d]; }
         newkey[s] = k0;
-        rank[s] = atomicAdd(&tg.cell_count[k0], 1u);
         const uint32_t fr0 = k0 / (uint32_t)sp.dims[0];
+        if (fr0 >= tg.nrows) return;
+        rank[s] = atomicAdd(&tg.cell_count[k0], 1u);
         const uint32_t tile = fr0 * tg.tpr + __umulhi(k0 - fr0 * (uint32_t)sp.dims[0], tg.magic);
         const unsigned m = __match_any_sync(__activemask(), tile);
         if ((m & (0u - m)) == (1u << (threadIdx.x & 31))) atomicAdd(&tg.tile_count[tile], (uint32_t)__popc(m));
@@ -144,6 +146,16 @@ k_pf_fine(SpaceDev<T, D> sp, PfU<T> u, const T* __restrict__ pos, const T* __res
     }
     const T ri = rad[s], ki = kk[s], mi = mass[s];
     key_to_cell<T, D>(sp, key[s], c);        // K == 1 on this path: fine cell == reference cell
+    int cg[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d) cg[d] = c[d];
+    if (sp.W) {
+        // slab window: owned layers plus the first halo layer on each side (its particles may enter the owned layers
+        // in this step: they are this step's immigrants, computed here instead of being received)
+        const int l = c[D - 1];
+        if (!(l <= sp.nl || l == sp.nl + 2 * sp.W - 1)) return;
+        cg[D - 1] = local_to_global_last<T, D>(sp, l);
+    }
     const int d0 = sp.dims[0], d1 = sp.dims[1], d2n = D == 3 ? sp.dims[2] : 1;
     // cutoff may equal the spacing: a partner at distance ~cutoff can then sit (by rounding) two cells away,
     // but only if BOTH agents are within rounding distance of a cell boundary — those take the reference walk
@@ -153,7 +165,7 @@ k_pf_fine(SpaceDev<T, D> sp, PfU<T> u, const T* __restrict__ pos, const T* __res
 #pragma unroll
         for (int d = 0; d < D; ++d) {
             const T tau = sp.extent[d] * eps;
-            const T a = p[d] - sp.spacing * (T)c[d];
+            const T a = p[d] - sp.spacing * (T)cg[d];
             if (a < tau || sp.spacing - a < tau) near = true;
         }
     }
@@ -179,7 +191,7 @@ k_pf_fine(SpaceDev<T, D> sp, PfU<T> u, const T* __restrict__ pos, const T* __res
         if (wrap == 0) sweep_t(jb, je, 0, std::false_type{});
         else sweep_t(jb, je, wrap, std::true_type{});
     };
-    if (near) pf_accumulate_walk<T, D>(sp, u, s, p, c, ri, ki, pos, rad, kk, cs, cap, f);
+    if (near) pf_accumulate_walk<T, D>(sp, u, s, p, c, cg, ri, ki, pos, rad, kk, cs, cap, f);
     else
     for (int rz = (D == 3 ? -1 : 0); rz <= (D == 3 ? 1 : 0); ++rz) {
         int cz = 0, wz = 0;
@@ -190,6 +202,8 @@ k_pf_fine(SpaceDev<T, D> sp, PfU<T> u, const T* __restrict__ pos, const T* __res
                 cz = cz < 0 ? cz + d2n : cz - d2n;
                 wz = 4;
             }
+            // slab window: whether the row lies across the space's periodic boundary is decided on GLOBAL layers
+            if (sp.W) { const int g = cg[2] + rz; wz = (g < 0 || g >= sp.gdl) ? 4 : 0; }
         }
         uint32_t rbv[3], jb[3], je[3];
         int wrv[3];
@@ -202,6 +216,7 @@ k_pf_fine(SpaceDev<T, D> sp, PfU<T> u, const T* __restrict__ pos, const T* __res
                 cy = cy < 0 ? cy + d1 : cy - d1;
                 wy = 2;
             }
+            if (D == 2 && sp.W) { const int g = cg[1] + i - 1; wy = (g < 0 || g >= sp.gdl) ? 2 : 0; }
             const uint32_t rb = (D == 3 ? ((uint32_t)cz * (uint32_t)d1 + (uint32_t)cy) : (uint32_t)cy) * (uint32_t)d0;
             rbv[i] = rb; wrv[i] = wy | wz;
             const int a0 = max(c[0] - 1, 0), a1 = min(c[0] + 1, d0 - 1);
@@ -224,18 +239,24 @@ k_pf_fine(SpaceDev<T, D> sp, PfU<T> u, const T* __restrict__ pos, const T* __res
     bool moved_far = false;
 #pragma unroll
     for (int d = 0; d < D; ++d) {
-        int dc = nc[d] - c[d];
+        int dc = nc[d] - cg[d];
         if (dc < 0) dc = -dc;
-        if (sp.periodic[d] && dc == sp.dims[d] - 1) dc = 1;
+        const int lim = d == D - 1 ? sp.gdl : sp.dims[d];
+        if (sp.periodic[d] && dc == lim - 1) dc = 1;
         if (dc > 1) moved_far = true;
     }
-    if (moved_far) atomicOr(far, 1);
+    // further than one cell: the tiled re-sort cannot find it — the step falls back to the generic re-index
+    // (a slab window has no such fallback: device error)
+    if (moved_far) { if (sp.W) atomicOr(err, AB_EF_OVERFLOW); else atomicOr(far, 1); }
     uint32_t nfrow = 0;
-    const uint32_t nk = device_key<T, D>(sp, np_, nc, nullptr, &nfrow);
+    bool inwin = true;
+    uint32_t nk = device_key<T, D>(sp, np_, nc, &inwin, &nfrow);
+    if (!inwin) { atomicOr(err, AB_EF_OVERFLOW); nk = 0; nfrow = 0; }
 #pragma unroll
     for (int d = 0; d < D; ++d) { npos[(size_t)d * cap + s] = np_[d]; nvel[(size_t)d * cap + s] = nv[d]; }
     newkey[s] = nk;
     // arrival rank (used only when the step falls back to the generic re-index) + per-tile histogram of the tiled re-sort
+    if (nfrow >= tg.nrows) return;                           // a row this handle does not re-sort (halo rows of a slab window)
     rank[s] = atomicAdd(&tg.cell_count[nk], 1u);
     {
         const uint32_t tile = nfrow * tg.tpr + __umulhi(nk - nfrow * (uint32_t)sp.dims[0], tg.magic);
@@ -322,7 +343,7 @@ __global__ void k_pf_integrate(SpaceDev<T, D> sp, PfU<T> u, const T* __restrict_
 // ---------------------------------------------------------------------------
 template <class T, int D>
 static int pf_steps_t(ab_handle* h, const ab_pairforce_params* p, int64_t nsteps) {
-    const int n = (int)h->n, TB = 128;
+    const int n = h->win_W ? (int)h->cap : (int)h->n, TB = 128;     // slab window: grid over the capacity, live count on the device
     PfU<T> u;
     u.dt = (T)p->dt;
     u.half_dt2 = T(0);
@@ -332,6 +353,8 @@ static int pf_steps_t(ab_handle* h, const ab_pairforce_params* p, int64_t nsteps
     const double s = (double)(T)h->desc.spacing;
     bool fine = p->cutoff > 0 && p->cutoff <= s && ab_resort_applicable(h);
     for (int d = 0; d < D; ++d) if (h->dims[d] < 3) fine = false;
+    if (h->win_W && !fine) return ab_fail(h, AB_ERR_INVALID, "a sharded handle runs the fine pair-force step only (cutoff <= spacing, >= 3 cells per axis)");
+    if (h->win_W && ab_comm_local(h)) return ab_fail(h, AB_ERR_STATE, "in-process slabs step the flock rule only (ab_step_flock_group)");
     if (fine) AB_TRY(ab_set_refine(h, 1));
     AB_TRY(ab_ensure_index(h));
     if (fine) AB_TRY(ab_resort_plan(h));
@@ -349,7 +372,16 @@ static int pf_steps_t(ab_handle* h, const ab_pairforce_params* p, int64_t nsteps
                 AB_LAUNCH(h, "k_pf_fine");
                 k_pf_fine<T, D><<<ab_blocks(n, TB), TB, 0, h->stream>>>(sp, u, pos, vel, rad, kk, mass, h->key[cur], h->cell_start, h->cap, n,
                                                                         (T*)h->tmp_pos, (T*)h->tmp_vel, h->newkey, h->rank, make_tilegeo(h), h->id[cur],
-                                                                        h->d_err + 1, h->d_err);
+                                                                        h->d_err + 1, h->d_err, h->win_W ? h->cell_start + h->nfine : nullptr);
+            }
+            if (h->win_W) {
+                // slab window: re-sort of the owned rows, then the boundary layers (with the r, k, mass columns) replace
+                // the neighbours' halo layers — refresh and migration in one message, as in the flock step
+                AB_TRY(ab_resort_tiled(h, h->tmp_pos, h->tmp_vel, false));
+                AB_TRY(ab_comm_pack(h));
+                AB_TRY(ab_comm_transfer(h));
+                AB_TRY(ab_comm_unpack(h, false));
+                continue;
             }
             // did anybody move further than one cell?  (then the tiled re-sort cannot find it)
             AB_CUDA(h, cudaMemcpyAsync(h->h_err + 1, h->d_err + 1, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
@@ -398,7 +430,6 @@ extern "C" int ab_step_pairforce(ab_handle* h, const ab_pairforce_params* p, int
     if (!p) return ab_fail(h, AB_ERR_INVALID, "null params");
     if (h->desc.kind != AB_SPACE_CONTINUOUS) return ab_fail(h, AB_ERR_INVALID, "pair-force rule needs a ContinuousSpace handle");
     if (nsteps < 0) return ab_fail(h, AB_ERR_INVALID, "negative nsteps");
-    if (h->win_W) return ab_fail(h, AB_ERR_STATE, "the pair-force rule does not run on a sharded (slab-window) handle yet");
     const int fs[3] = {p->field_r, p->field_k, p->field_mass};
     for (int f : fs)
         if (f < 2 || f >= (int)h->fields.size() || h->fields[f].ncomp != 1 || h->fields[f].dtype != h->dtype)
@@ -411,6 +442,7 @@ extern "C" int ab_step_pairforce(ab_handle* h, const ab_pairforce_params* p, int
     else rc = h->D == 2 ? pf_steps_t<float, 2>(h, p, nsteps) : pf_steps_t<float, 3>(h, p, nsteps);
     AB_TRY(rc);
     AB_TRY(ab_check_device_errors_now(h));      // synchronous call (also in asynchronous mode): the events below must have completed
+    if (h->win_W) AB_TRY(ab_comm_refresh_counts(h));
     float ms = 0;
     AB_CUDA(h, cudaEventElapsedTime(&ms, h->ev0, h->ev1));
     h->last_step_ms = ms;

@@ -469,7 +469,7 @@ static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool
             h->cell_start_alt, extra ? h->perm : nullptr, (T*)h->cell_agg, (int64_t)h->ncells, h->d_err));
     }
     std::swap(h->cell_start, h->cell_start_alt);
-    AB_TRY(ab_permute_extra_fields(h));
+    AB_TRY(ab_permute_extra_fields(h, true));
     h->cur = nxt;
     h->slot_map_valid = false;
     h->index_valid = true;

@@ -111,13 +111,24 @@ class Slabs:
         return True
 
     # -- population -----------------------------------------------------------------------------
-    def scatter(self, pos, vel, halo_capacity=None, capacity_factor=1.6):
-        """Every rank passes the same global, id-ordered (1..N) state and keeps its window of it."""
+    def scatter(self, pos, vel, halo_capacity=None, capacity_factor=1.6, columns=None):
+        """Every rank passes the same global, id-ordered (1..N) state and keeps its window of it.  `columns`:
+        {name: global id-ordered array} of user columns (the r / k / mass of the pair-force rule, ...); they are
+        registered BEFORE the receive block is exported, because they travel in the boundary messages."""
+        from .model import _NP2AB
+
         m, lib = self.model, self.model.lib
         dt = m.space.dtype
         pos = np.ascontiguousarray(pos, dtype=dt).reshape(-1, m.D)
         vel = np.ascontiguousarray(vel, dtype=dt).reshape(-1, m.D)
         self.n_global = pos.shape[0]
+        cols = {}
+        for name, a in (columns or {}).items():
+            a = np.ascontiguousarray(a).reshape(self.n_global, -1)
+            if name not in m._columns:
+                fid = m._ck(lib.ab_register_field(m.h, name.encode(), _NP2AB[a.dtype], a.shape[1]))
+                m._columns[name], m._dtypes[name], m._ncomp[name] = fid, a.dtype, a.shape[1]
+            cols[name] = np.ascontiguousarray(a, dtype=m._dtypes[name])
         layer = cell_layer(pos[:, -1], m.space.spacing, self.n_layers)
         idx, owned = select_window(layer, self.first, self.count, self.n_layers)
         cap = halo_capacity or default_halo_capacity(self.n_global, self.n_layers)
@@ -129,8 +140,21 @@ class Slabs:
         v = np.ascontiguousarray(vel[idx])
         m._ck(lib.ab_upload_local(m.h, 0, m._ptr(p), m._ptr(gids), len(idx)))
         m._ck(lib.ab_upload_local(m.h, 1, m._ptr(v), m._ptr(gids), len(idx)))
+        for name, a in cols.items():
+            c = np.ascontiguousarray(a[idx])
+            m._ck(lib.ab_upload_local(m.h, m._columns[name], m._ptr(c), m._ptr(gids), len(idx)))
         m._ck(lib.ab_build_index(m.h))
         return int(owned.sum())
+
+    def local_column(self, name):
+        """(global ids, values) of a user column for the agents this rank owns now."""
+        m, lib = self.model, self.model.lib
+        cap = int(lib.ab_nagents(m.h)) + 1
+        ids = np.zeros(cap, dtype=np.int64)
+        out = np.zeros((cap, m._ncomp[name]), dtype=m._dtypes[name])
+        n = C.c_int64(0)
+        m._ck(lib.ab_download_local(m.h, m._columns[name], m._ptr(out), m._ptr(ids), cap, C.byref(n)))
+        return ids[: n.value], out[: n.value]
 
     def scatter_chunks(self, chunks, n_global, halo_capacity=None, capacity_factor=1.6):
         """Like `scatter` for populations too large to materialise on every rank: `chunks` yields

@@ -360,16 +360,23 @@ def parity_check(ab, dist, local, rank, world):
     from agents_jl_b200.parallel import Slabs
     from helpers import flock_init
 
-    cases = [("2d", (400.0, float(max(400, 100 * world))), 0.375),
-             ("3d", (60.0, 60.0, float(max(120, 40 * world))), 0.0926)]
+    cases = [("flock 2d", (400.0, float(max(400, 100 * world))), 0.375, SPACING),
+             ("flock 3d", (60.0, 60.0, float(max(120, 40 * world))), 0.0926, SPACING),
+             ("pairforce 2d", (400.0, float(max(400, 100 * world))), 0.0375, 20.0)]
     out = {"bitwise_equal": True, "migrated": 0, "direct": True, "cases": []}
-    for name, extent, dens in cases:
+    for name, extent, dens, spacing in cases:
         n = int(dens * float(np.prod(extent)))
-        pos, vel = flock_init(n, extent, 42)
-        rule = ab.FlockRule(kernel="fine", **FLOCK)
-        m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=SPACING), model_step=rule, device=local)
+        cols = None
+        if name.startswith("flock"):
+            pos, vel = flock_init(n, extent, 42)
+            make_rule = lambda: ab.FlockRule(kernel="fine", **FLOCK)
+        else:
+            pos, vel, rad, kk, mass = particles(n, extent, vscale=300.0)
+            cols = {"r": rad, "k": kk, "mass": mass}
+            make_rule = lambda: ab.PairForceRule(dt=0.005, cutoff=20.0)
+        m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=spacing), model_step=make_rule(), device=local)
         s = Slabs(m, dist)
-        own0 = s.scatter(pos, vel)
+        own0 = s.scatter(pos, vel, columns=cols)
         m.step(4)
         own1 = s.n_owned()
         m.step(4)
@@ -378,8 +385,8 @@ def parity_check(ab, dist, local, rank, world):
         m.close()
         ok, migrated = True, abs(own1 - own0)
         if rank == 0:
-            ref = ab.StandardABM(ab.ContinuousSpace(extent, spacing=SPACING), model_step=ab.FlockRule(kernel="fine", **FLOCK), device=local)
-            ref.add_agents(pos, vel)
+            ref = ab.StandardABM(ab.ContinuousSpace(extent, spacing=spacing), model_step=make_rule(), device=local)
+            ref.add_agents(pos, vel, **(cols or {}))
             ref.step(4)
             ref.step(4)
             ok = bool(np.array_equal(gp, ref.pos) and np.array_equal(gv, ref.vel))

@@ -30,6 +30,7 @@ def main():
     ap.add_argument("--search", default="approximate")
     ap.add_argument("--dtype", default="float64")
     ap.add_argument("--seed", type=int, default=42)
+    ap.add_argument("--rule", default="flock", choices=["flock", "pairforce"])
     args = ap.parse_args()
 
     import torch
@@ -45,12 +46,22 @@ def main():
     rank, world = dist.get_rank(), dist.get_world_size()
     extent = tuple(args.extent)
     dt = np.dtype(args.dtype)
-    pos, vel = flock_init(args.n, extent, args.seed, dtype=dt)
+    cols = None
+    if args.rule == "flock":
+        pos, vel = flock_init(args.n, extent, args.seed, dtype=dt)
+        make_rule = lambda: ab.FlockRule(search=args.search, kernel="fine", **FLOCK)
+    else:
+        # examples/celllistmap.jl-style particles; the velocity scale makes particles cross slab boundaries within a few steps
+        from test_pairforce_gpu import particles
 
-    rule = ab.FlockRule(search=args.search, kernel="fine", **FLOCK)
+        pos, vel, rad, kk, mass = (a.astype(dt) for a in particles(args.n, extent, seed=args.seed, vscale=300.0))
+        cols = {"r": rad, "k": kk, "mass": mass}
+        make_rule = lambda: ab.PairForceRule(dt=0.005, cutoff=args.spacing)
+
+    rule = make_rule()
     m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=args.spacing, dtype=dt), model_step=rule, device=local)
     slabs = Slabs(m, dist)
-    owned0 = slabs.scatter(pos, vel)
+    owned0 = slabs.scatter(pos, vel, columns=cols)
     done, owned_hist = 0, [owned0]
     while done < args.steps:
         k = min(args.chunk, args.steps - done)
@@ -62,9 +73,8 @@ def main():
     dist.all_reduce(tot)
     result = None
     if rank == 0:
-        ref = ab.StandardABM(ab.ContinuousSpace(extent, spacing=args.spacing, dtype=dt),
-                             model_step=ab.FlockRule(search=args.search, kernel="fine", **FLOCK), device=local)
-        ref.add_agents(pos, vel)
+        ref = ab.StandardABM(ab.ContinuousSpace(extent, spacing=args.spacing, dtype=dt), model_step=make_rule(), device=local)
+        ref.add_agents(pos, vel, **(cols or {}))
         done = 0
         while done < args.steps:
             k = min(args.chunk, args.steps - done)
@@ -77,7 +87,7 @@ def main():
             "pos_bitwise_equal": bool(np.array_equal(gp, rp)), "vel_bitwise_equal": bool(np.array_equal(gv, rv)),
             "max_abs_pos_diff": float(np.max(np.abs(gp - rp))), "owned_rank0": owned_hist,
             "migrated": bool(len(set(owned_hist)) > 1), "launches": m.launch_count(),
-            "direct": bool(slabs.direct),
+            "direct": bool(slabs.direct), "rule": args.rule,
         }
         ref.close()
         print("MGPU_RESULT " + json.dumps(result), flush=True)

@@ -59,6 +59,19 @@ def test_two_gpus_nccl_exchange():
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("wargs", [["--agents", "6000", "--extent", "400", "400", "--spacing", "20", "--steps", "10"],
+                                   ["--agents", "8000", "--extent", "120", "120", "240", "--spacing", "20", "--steps", "8"]],
+                         ids=["2d", "3d"])
+def test_two_gpus_pairforce_bitwise_equal_to_one(wargs):
+    """The pair-force rule on slabs: the r / k / mass columns travel in the boundary messages."""
+    if _ngpu() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    r = _run(2, 29539, *wargs, "--rule", "pairforce")
+    assert r["conserved"] and r["pos_bitwise_equal"] and r["vel_bitwise_equal"], r
+    assert r["migrated"] and r["direct"], r
+
+
+@pytest.mark.gpu
 def test_four_gpus_bitwise_equal_to_one():
     if _ngpu() < 4:
         pytest.skip("needs >= 4 GPUs")
