@@ -93,6 +93,8 @@ struct ab_comm {
     int64_t n_own = 0;
     // in-process peers (ab_comm_link_local): slabs of one process, on the same or on different devices
     ab_handle *peer_lower = nullptr, *peer_upper = nullptr;
+    bool linked_local = false;       // ab_comm_link_local done (an end slab of a non-periodic axis has one peer only)
+    bool has_lower = true, has_upper = true;   // false on the end ranks of a non-periodic last axis
     cudaEvent_t ev_packed = nullptr, ev_consumed = nullptr;
     uint32_t* h_counts = nullptr;    // pinned {n_own, n_window}
     int64_t exchanges = 0;
@@ -193,21 +195,21 @@ k_halo_pack(MsgLayout m, MsgCols xc, uint32_t kown, const uint32_t* __restrict__
             char* __restrict__ buf0, char* __restrict__ buf1, int* __restrict__ err,
             uint32_t* done_ctr, uint32_t* flag0, uint32_t* flag1, uint32_t epoch) {
     const int dir = blockIdx.y;
-    char* buf = dir == 0 ? buf0 : buf1;
+    char* buf = dir == 0 ? buf0 : buf1;                  // nullptr: no neighbour on this side (non-periodic last axis, end rank)
     const uint32_t k0 = dir == 0 ? 0u : kown - m.ncs;
     const uint32_t s0 = cs[k0], s1 = cs[k0 + m.ncs];
-    uint32_t cnt = s1 - s0;
+    uint32_t cnt = buf ? s1 - s0 : 0u;
     if (cnt > (uint32_t)m.C) {
         if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(err, AB_EF_COMM);
         cnt = (uint32_t)m.C;
     }
     const uint32_t t0 = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
-    if (t0 == 0) {
+    if (t0 == 0 && buf) {
         uint32_t* hdr = reinterpret_cast<uint32_t*>(buf);
         hdr[0] = cnt; hdr[1] = k0; hdr[2] = m.ncs; hdr[3] = 0xAB200u;
     }
     uint32_t* mcs = reinterpret_cast<uint32_t*>(buf + m.off_cs);
-    for (uint32_t i = t0; i <= m.ncs; i += stride) mcs[i] = min(cs[k0 + i] - s0, cnt);
+    if (buf) for (uint32_t i = t0; i <= m.ncs; i += stride) mcs[i] = min(cs[k0 + i] - s0, cnt);
     E* mpos = reinterpret_cast<E*>(buf + m.off_pos);
     E* mvel = reinterpret_cast<E*>(buf + m.off_vel);
     int32_t* mid = reinterpret_cast<int32_t*>(buf + m.off_id);
@@ -227,7 +229,7 @@ k_halo_pack(MsgLayout m, MsgCols xc, uint32_t kown, const uint32_t* __restrict__
                 copy_elem(buf + m.off_x[f] + ((size_t)c * m.C + t) * es, xc.p[f] + ((size_t)c * cap + s) * es, es);
         }
     }
-    if (flag0) {
+    if (done_ctr) {
         // direct exchange: the LAST CTA to finish publishes the exchange number in the neighbours' flags.
         // The CTA barrier orders every thread's peer-memory stores before thread 0's system-scope fence
         // (fences are cumulative), so one fence per CTA — not one per thread — precedes the count.
@@ -238,8 +240,8 @@ k_halo_pack(MsgLayout m, MsgCols xc, uint32_t kown, const uint32_t* __restrict__
             if (atomicAdd(done_ctr, 1u) == total - 1) {
                 __threadfence_system();
                 *done_ctr = 0;
-                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag0), "r"(epoch) : "memory");
-                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag1), "r"(epoch) : "memory");
+                if (flag0) asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag0), "r"(epoch) : "memory");
+                if (flag1) asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag1), "r"(epoch) : "memory");
             }
         }
     }
@@ -272,14 +274,14 @@ k_halo_unpack(SpaceDev<T, D> sp, MsgLayout m, MsgCols xc, uint32_t kown, uint32_
               const char* __restrict__ buf1, int* __restrict__ err, const uint32_t* wflag0, const uint32_t* wflag1,
               uint32_t epoch, int nbc, int nba, T* __restrict__ agg, int64_t agg_stride, uint32_t halo_cell0,
               uint32_t cells_per_side, unsigned long long* wait_stat) {
-    if (wflag0) {
+    if (wflag0 || wflag1) {
         // direct exchange: both messages were stored into our memory by the neighbours' pack kernels; they
         // never wait for us in return (their pack depends only on their own steps; slots alternate by parity)
         __shared__ int s_ok;
         if (threadIdx.x == 0) {
             unsigned long long t0, t1;
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-            s_ok = wait_flag(wflag0, epoch) && wait_flag(wflag1, epoch);
+            s_ok = (!wflag0 || wait_flag(wflag0, epoch)) && (!wflag1 || wait_flag(wflag1, epoch));
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
             if (blockIdx.x == 0 && wait_stat) { atomicAdd(&wait_stat[0], t1 - t0); atomicAdd(&wait_stat[1], 1ull); }
         }
@@ -289,11 +291,12 @@ k_halo_unpack(SpaceDev<T, D> sp, MsgLayout m, MsgCols xc, uint32_t kown, uint32_
             return;
         }
     }
+    // buf0 / buf1 == nullptr: no neighbour on that side (non-periodic last axis, end rank) — its halo layers stay empty
     const uint32_t* h0 = reinterpret_cast<const uint32_t*>(buf0);
     const uint32_t* h1 = reinterpret_cast<const uint32_t*>(buf1);
     const uint32_t n_own = cs[kown];                     // written by the re-sort of this step; never rewritten here
-    uint32_t cnt_u = h0[0], cnt_l = h1[0];
-    bool bad = h0[3] != 0xAB200u || h1[3] != 0xAB200u || h0[2] != m.ncs || h1[2] != m.ncs;
+    uint32_t cnt_u = buf0 ? h0[0] : 0u, cnt_l = buf1 ? h1[0] : 0u;
+    bool bad = (buf0 && (h0[3] != 0xAB200u || h0[2] != m.ncs)) || (buf1 && (h1[3] != 0xAB200u || h1[2] != m.ncs));
     if ((uint64_t)n_own + cnt_u + cnt_l > (uint64_t)cap) bad = true;       // window does not fit the handle's capacity
     if (bad) {
         if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(err, AB_EF_COMM);
@@ -313,8 +316,12 @@ k_halo_unpack(SpaceDev<T, D> sp, MsgLayout m, MsgCols xc, uint32_t kown, uint32_
     const T* mvel = reinterpret_cast<const T*>(buf + m.off_vel);
     if (!agg_role) {
         const uint32_t base = src == 0 ? n_own : n_own + cnt_u;
-        const uint32_t kdelta = kdst - hdr[1];               // sender's key frame -> this window's (mod 2^32)
         const uint32_t t0 = bx * blockDim.x + threadIdx.x, stride = per * blockDim.x;
+        if (!buf) {                                          // no neighbour: empty halo cells
+            for (uint32_t i = t0 + 1; i <= m.ncs; i += stride) cs[kdst + i] = base;
+            return;
+        }
+        const uint32_t kdelta = kdst - hdr[1];               // sender's key frame -> this window's (mod 2^32)
         for (uint32_t i = t0 + 1; i <= m.ncs; i += stride) cs[kdst + i] = base + (bad ? 0u : mcs[i]);
         const int32_t* mid = reinterpret_cast<const int32_t*>(buf + m.off_id);
         const uint32_t* mkey = reinterpret_cast<const uint32_t*>(buf + m.off_key);
@@ -353,7 +360,7 @@ k_halo_unpack(SpaceDev<T, D> sp, MsgLayout m, MsgCols xc, uint32_t kown, uint32_
         const FineRows fr = fine_rows<D>(sp.dims, kb, cc[1], D == 3 ? cc[2] : 0);
         const uint32_t i0 = fr.base[part] + ((uint32_t)cc[0] << kb) - kdst;     // index into the message's cell_start slice
         uint32_t b = 0, e = 0;
-        if (live && !bad) { b = min(mcs[i0], cnt); e = min(mcs[i0 + (uint32_t)K], cnt); }
+        if (live && !bad && buf) { b = min(mcs[i0], cnt); e = min(mcs[i0 + (uint32_t)K], cnt); }
         cc[D - 1] = local_to_global_last<T, D>(sp, cc[D - 1]);                   // centres are global
         T acc[2 * D];
 #pragma unroll
@@ -448,24 +455,26 @@ static int pack_t(ab_handle* h) {
     // one item per thread (up to 592 CTAs per side): the stores are posted writes, the cost is latency
     const int nb = (int)std::min<int64_t>(std::max<int64_t>((std::max<int64_t>(c->cap_agents, ncs) + 255) / 256, 1), 592);
     // in-process peers: they must have consumed the previous message before it is overwritten
-    if (c->peer_lower) AB_CUDA(h, cudaStreamWaitEvent(h->stream, c->peer_lower->comm->ev_consumed, 0));
-    if (c->peer_upper) AB_CUDA(h, cudaStreamWaitEvent(h->stream, c->peer_upper->comm->ev_consumed, 0));
+    if (c->linked_local && c->peer_lower) AB_CUDA(h, cudaStreamWaitEvent(h->stream, c->peer_lower->comm->ev_consumed, 0));
+    if (c->linked_local && c->peer_upper) AB_CUDA(h, cudaStreamWaitEvent(h->stream, c->peer_upper->comm->ev_consumed, 0));
     // my bottom layers are the lower neighbour's "from upper" message (side 0), my top layers the upper
     // neighbour's "from lower" one (side 1)
     c->cur_par = (int)(c->exchanges & 1);
     char* dst0 = c->ipc_on ? ipc_slot(c->ipc_lower, c->ipc_stride, c->cur_par, 0) : (char*)c->sendbuf[0];
     char* dst1 = c->ipc_on ? ipc_slot(c->ipc_upper, c->ipc_stride, c->cur_par, 1) : (char*)c->sendbuf[1];
+    if (!c->has_lower) dst0 = nullptr;                   // end rank of a non-periodic axis: nothing to send that way
+    if (!c->has_upper) dst1 = nullptr;
     {
         AB_LAUNCH(h, "k_halo_pack");
         k_halo_pack<E, D><<<dim3(nb, 2), 256, 0, h->stream>>>(m, msg_cols(h), kown, h->cell_start, (const E*)h->fields[0].buf[cur],
                                                              (const E*)h->fields[1].buf[cur], h->id[cur], h->key[cur], h->cap,
                                                              dst0, dst1, h->d_err,
                                                              c->ipc_on ? ipc_flag(c->ipc_block, c->ipc_stride, 2, 0) : nullptr,
-                                                             c->ipc_on ? ipc_flag(c->ipc_lower, c->ipc_stride, c->cur_par, 0) : nullptr,
-                                                             c->ipc_on ? ipc_flag(c->ipc_upper, c->ipc_stride, c->cur_par, 1) : nullptr,
+                                                             c->ipc_on && c->has_lower ? ipc_flag(c->ipc_lower, c->ipc_stride, c->cur_par, 0) : nullptr,
+                                                             c->ipc_on && c->has_upper ? ipc_flag(c->ipc_upper, c->ipc_stride, c->cur_par, 1) : nullptr,
                                                              (uint32_t)(c->exchanges + 1));
     }
-    if (c->peer_lower) AB_CUDA(h, cudaEventRecord(c->ev_packed, h->stream));
+    if (c->linked_local) AB_CUDA(h, cudaEventRecord(c->ev_packed, h->stream));
     return AB_OK;
 }
 
@@ -473,16 +482,20 @@ static int pack_t(ab_handle* h) {
 static int transfer(ab_handle* h) {
     ab_comm* c = h->comm;
     const size_t bytes = c->msg_bytes;
-    if (c->peer_lower) {
+    if (c->linked_local) {
         ab_handle *lo = c->peer_lower, *up = c->peer_upper;
-        AB_CUDA(h, cudaStreamWaitEvent(h->stream, up->comm->ev_packed, 0));
-        AB_CUDA(h, cudaStreamWaitEvent(h->stream, lo->comm->ev_packed, 0));
-        if (up->comm->msg_bytes != bytes || lo->comm->msg_bytes != bytes) return ab_fail(h, AB_ERR_COMM, "peers disagree on the message capacity");
+        if (up) AB_CUDA(h, cudaStreamWaitEvent(h->stream, up->comm->ev_packed, 0));
+        if (lo) AB_CUDA(h, cudaStreamWaitEvent(h->stream, lo->comm->ev_packed, 0));
+        if ((up && up->comm->msg_bytes != bytes) || (lo && lo->comm->msg_bytes != bytes)) return ab_fail(h, AB_ERR_COMM, "peers disagree on the message capacity");
         // my upper halo = the upper peer's bottom layers (its sendbuf[0]); my lower halo = the lower peer's top layers
-        if (up->device == h->device) AB_CUDA(h, cudaMemcpyAsync(c->recvbuf[0], up->comm->sendbuf[0], bytes, cudaMemcpyDeviceToDevice, h->stream));
-        else AB_CUDA(h, cudaMemcpyPeerAsync(c->recvbuf[0], h->device, up->comm->sendbuf[0], up->device, bytes, h->stream));
-        if (lo->device == h->device) AB_CUDA(h, cudaMemcpyAsync(c->recvbuf[1], lo->comm->sendbuf[1], bytes, cudaMemcpyDeviceToDevice, h->stream));
-        else AB_CUDA(h, cudaMemcpyPeerAsync(c->recvbuf[1], h->device, lo->comm->sendbuf[1], lo->device, bytes, h->stream));
+        if (up) {
+            if (up->device == h->device) AB_CUDA(h, cudaMemcpyAsync(c->recvbuf[0], up->comm->sendbuf[0], bytes, cudaMemcpyDeviceToDevice, h->stream));
+            else AB_CUDA(h, cudaMemcpyPeerAsync(c->recvbuf[0], h->device, up->comm->sendbuf[0], up->device, bytes, h->stream));
+        }
+        if (lo) {
+            if (lo->device == h->device) AB_CUDA(h, cudaMemcpyAsync(c->recvbuf[1], lo->comm->sendbuf[1], bytes, cudaMemcpyDeviceToDevice, h->stream));
+            else AB_CUDA(h, cudaMemcpyPeerAsync(c->recvbuf[1], h->device, lo->comm->sendbuf[1], lo->device, bytes, h->stream));
+        }
         AB_CUDA(h, cudaEventRecord(c->ev_consumed, h->stream));
     } else if (c->ipc_on) {
         // nothing to move: the neighbours' pack kernels store into our block; k_halo_unpack waits for their flags
@@ -491,10 +504,10 @@ static int transfer(ab_handle* h) {
         // one group: bottom layers -> lower neighbour, top layers -> upper neighbour; receives in the matching
         // order (with 2 ranks both neighbours are the same peer: first send pairs with first receive)
         AB_NCCL(h, g_nccl.GroupStart());
-        AB_NCCL(h, g_nccl.Send(c->sendbuf[0], bytes, NCCL_UINT8, c->lower, c->comm, h->stream));
-        AB_NCCL(h, g_nccl.Send(c->sendbuf[1], bytes, NCCL_UINT8, c->upper, c->comm, h->stream));
-        AB_NCCL(h, g_nccl.Recv(c->recvbuf[0], bytes, NCCL_UINT8, c->upper, c->comm, h->stream));
-        AB_NCCL(h, g_nccl.Recv(c->recvbuf[1], bytes, NCCL_UINT8, c->lower, c->comm, h->stream));
+        if (c->has_lower) AB_NCCL(h, g_nccl.Send(c->sendbuf[0], bytes, NCCL_UINT8, c->lower, c->comm, h->stream));
+        if (c->has_upper) AB_NCCL(h, g_nccl.Send(c->sendbuf[1], bytes, NCCL_UINT8, c->upper, c->comm, h->stream));
+        if (c->has_upper) AB_NCCL(h, g_nccl.Recv(c->recvbuf[0], bytes, NCCL_UINT8, c->upper, c->comm, h->stream));
+        if (c->has_lower) AB_NCCL(h, g_nccl.Recv(c->recvbuf[1], bytes, NCCL_UINT8, c->lower, c->comm, h->stream));
         AB_NCCL(h, g_nccl.GroupEnd());
     }
     c->exchanges++;
@@ -521,10 +534,10 @@ static int unpack_t(ab_handle* h, bool want_agg) {
         AB_LAUNCH(h, "k_halo_unpack");
         k_halo_unpack<T, D><<<dim3(2 * nbc + 2 * nba), 256, 0, h->stream>>>(make_space<T, D>(h), m, msg_cols(h), kown, h->cell_start, (T*)h->fields[0].buf[cur],
                                                                (T*)h->fields[1].buf[cur], h->id[cur], h->key[cur], h->cap,
-                                                               c->ipc_on ? ipc_slot(c->ipc_block, c->ipc_stride, c->cur_par, 0) : (const char*)c->recvbuf[0],
-                                                               c->ipc_on ? ipc_slot(c->ipc_block, c->ipc_stride, c->cur_par, 1) : (const char*)c->recvbuf[1], h->d_err,
-                                                               c->ipc_on ? ipc_flag(c->ipc_block, c->ipc_stride, c->cur_par, 0) : nullptr,
-                                                               c->ipc_on ? ipc_flag(c->ipc_block, c->ipc_stride, c->cur_par, 1) : nullptr,
+                                                               !c->has_upper ? nullptr : c->ipc_on ? ipc_slot(c->ipc_block, c->ipc_stride, c->cur_par, 0) : (const char*)c->recvbuf[0],
+                                                               !c->has_lower ? nullptr : c->ipc_on ? ipc_slot(c->ipc_block, c->ipc_stride, c->cur_par, 1) : (const char*)c->recvbuf[1], h->d_err,
+                                                               c->ipc_on && c->has_upper ? ipc_flag(c->ipc_block, c->ipc_stride, c->cur_par, 0) : nullptr,
+                                                               c->ipc_on && c->has_lower ? ipc_flag(c->ipc_block, c->ipc_stride, c->cur_par, 1) : nullptr,
                                                                (uint32_t)c->exchanges, nbc, nba, (T*)h->cell_agg, (int64_t)h->ncells,
                                                                (uint32_t)(h->win_nl * cpl), (uint32_t)(AB_HALO_W * cpl), c->d_wait);
     }
@@ -541,7 +554,7 @@ int ab_comm_unpack(ab_handle* h, bool want_agg) {
     if (h->tsize == 8) return h->D == 2 ? unpack_t<double, 2>(h, want_agg) : unpack_t<double, 3>(h, want_agg);
     return h->D == 2 ? unpack_t<float, 2>(h, want_agg) : unpack_t<float, 3>(h, want_agg);
 }
-bool ab_comm_local(const ab_handle* h) { return h->comm && h->comm->peer_lower; }
+bool ab_comm_local(const ab_handle* h) { return h->comm && h->comm->linked_local; }
 
 int ab_comm_refresh_counts(ab_handle* h) {
     ab_comm* c = h->comm;
@@ -601,18 +614,21 @@ int ab_comm_init(ab_handle* h, int rank, int nranks, const void* nccl_unique_id)
     if (h->n != 0) return ab_fail(h, AB_ERR_STATE, "ab_comm_init must come before the agents are added");
     if (nranks < 2 || rank < 0 || rank >= nranks) return ab_fail(h, AB_ERR_INVALID, "need nranks >= 2 and 0 <= rank < nranks");
     const int D = h->D, gdl = h->dims[D - 1];
-    if (!h->desc.periodic[D - 1]) return ab_fail(h, AB_ERR_INVALID, "slab decomposition needs a periodic last axis");
+    const bool per_last = h->desc.periodic[D - 1] != 0;
     int first, nl;
     slab_of(gdl, nranks, rank, &first, &nl);
     const int minl = gdl / nranks;
     // every slab holds its own boundary layers (W) and the window must not overlap itself
-    if (minl < AB_HALO_W + 1 || minl + 2 * AB_HALO_W + (gdl % nranks ? 1 : 0) > gdl)
+    if (minl < AB_HALO_W + 1 || (per_last && minl + 2 * AB_HALO_W + (gdl % nranks ? 1 : 0) > gdl))
         return ab_fail(h, AB_ERR_INVALID, "too few cell layers per rank for the halo width (need >= 4 layers per rank and >= 2 ranks' worth of space)");
     AB_CUDA(h, cudaSetDevice(h->device));
     ab_comm* c = new ab_comm();
     c->rank = rank; c->nranks = nranks;
     c->lower = (rank + nranks - 1) % nranks;
     c->upper = (rank + 1) % nranks;
+    // non-periodic last axis: the end slabs have one neighbour; the halo layers beyond the space stay empty
+    c->has_lower = per_last || rank > 0;
+    c->has_upper = per_last || rank < nranks - 1;
     if (cudaMallocHost((void**)&c->h_counts, 2 * sizeof(uint32_t)) != cudaSuccess) { delete c; return ab_fail(h, AB_ERR_CUDA, "cudaMallocHost failed"); }
     if (cudaMalloc((void**)&c->d_wait, 2 * sizeof(unsigned long long)) != cudaSuccess || cudaMemset(c->d_wait, 0, 2 * sizeof(unsigned long long)) != cudaSuccess ||
         cudaMalloc((void**)&c->d_align, 2 * sizeof(int32_t)) != cudaSuccess || cudaMemset(c->d_align, 0, 2 * sizeof(int32_t)) != cudaSuccess) {
@@ -653,13 +669,14 @@ int ab_comm_link_local(ab_handle** hs, int n) {
         ab_handle* h = hs[r];
         ab_comm* c = h->comm;
         AB_CUDA(h, cudaSetDevice(h->device));
-        c->peer_lower = hs[(r + n - 1) % n];
-        c->peer_upper = hs[(r + 1) % n];
+        c->peer_lower = c->has_lower ? hs[(r + n - 1) % n] : nullptr;
+        c->peer_upper = c->has_upper ? hs[(r + 1) % n] : nullptr;
+        c->linked_local = true;
         if (!c->ev_packed) AB_CUDA(h, cudaEventCreateWithFlags(&c->ev_packed, cudaEventDisableTiming));
         if (!c->ev_consumed) AB_CUDA(h, cudaEventCreateWithFlags(&c->ev_consumed, cudaEventDisableTiming));
         AB_CUDA(h, cudaEventRecord(c->ev_consumed, h->stream));      // "nothing pending" for the first pack
         for (ab_handle* peer : {c->peer_lower, c->peer_upper})
-            if (peer->device != h->device) {
+            if (peer && peer->device != h->device) {
                 int can = 0;
                 cudaDeviceCanAccessPeer(&can, h->device, peer->device);
                 if (can) { cudaError_t e = cudaDeviceEnablePeerAccess(peer->device, 0); if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError(); }
@@ -676,7 +693,7 @@ int ab_comm_ipc_export(ab_handle* h, void* out64) {
     if (!h || !h->comm || !h->win_W) return ab_fail(h, AB_ERR_STATE, "handle is not sharded");
     if (!out64) return ab_fail(h, AB_ERR_INVALID, "null output");
     ab_comm* c = h->comm;
-    if (c->peer_lower) return ab_fail(h, AB_ERR_STATE, "in-process slabs exchange by device copies");
+    if (c->linked_local) return ab_fail(h, AB_ERR_STATE, "in-process slabs exchange by device copies");
     if (c->want_cap <= 0) return ab_fail(h, AB_ERR_STATE, "ab_comm_set_capacity first");
     if (c->ipc_block) return ab_fail(h, AB_ERR_STATE, "already exported");
     AB_CUDA(h, cudaSetDevice(h->device));
@@ -698,19 +715,23 @@ int ab_comm_ipc_import(ab_handle* h, const void* lower64, const void* upper64) {
     if (!h || !h->comm || !h->win_W) return ab_fail(h, AB_ERR_STATE, "handle is not sharded");
     ab_comm* c = h->comm;
     if (!c->ipc_block) return ab_fail(h, AB_ERR_STATE, "ab_comm_ipc_export first");
-    if (!lower64 || !upper64) return ab_fail(h, AB_ERR_INVALID, "null handle");
+    if ((c->has_lower && !lower64) || (c->has_upper && !upper64)) return ab_fail(h, AB_ERR_INVALID, "null handle");
     if (c->ipc_on) return ab_fail(h, AB_ERR_STATE, "already imported");
     AB_CUDA(h, cudaSetDevice(h->device));
     cudaIpcMemHandle_t ml, mu;
-    memcpy(&ml, lower64, 64);
-    memcpy(&mu, upper64, 64);
     void* p = nullptr;
-    AB_CUDA(h, cudaIpcOpenMemHandle(&p, ml, cudaIpcMemLazyEnablePeerAccess));
-    c->ipc_lower = (char*)p;
-    if (c->lower == c->upper) c->ipc_upper = c->ipc_lower;          // two ranks: one neighbour, one mapping
-    else {
-        AB_CUDA(h, cudaIpcOpenMemHandle(&p, mu, cudaIpcMemLazyEnablePeerAccess));
-        c->ipc_upper = (char*)p;
+    if (c->has_lower) {
+        memcpy(&ml, lower64, 64);
+        AB_CUDA(h, cudaIpcOpenMemHandle(&p, ml, cudaIpcMemLazyEnablePeerAccess));
+        c->ipc_lower = (char*)p;
+    }
+    if (c->has_upper) {
+        if (c->has_lower && c->lower == c->upper) c->ipc_upper = c->ipc_lower;          // two ranks, periodic: one neighbour, one mapping
+        else {
+            memcpy(&mu, upper64, 64);
+            AB_CUDA(h, cudaIpcOpenMemHandle(&p, mu, cudaIpcMemLazyEnablePeerAccess));
+            c->ipc_upper = (char*)p;
+        }
     }
     c->ipc_on = true;
     return AB_OK;

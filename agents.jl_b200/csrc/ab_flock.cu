@@ -69,7 +69,7 @@ __device__ __forceinline__ void flock_epilogue(const SpaceDev<T, D>& sp, const T
         nv[d] = nv[d] * rnrm;
         // move_agent!(bird, model, speed): continuous.jl:186-194, walk.jl:58-66
         T t = p[d] + fp.speed * nv[d];
-        t = normalize_coord(t, sp.extent[d], sp.periodic[d]);
+        t = normalize_coord(t, sp.extent[d], d == D - 1 ? sp.gper_last : sp.periodic[d]);
         if (!(t >= T(0) && t <= sp.extent[d])) bad = true;    // continuous.jl:160 (NaN lands here too)
         np[d] = t;
     }

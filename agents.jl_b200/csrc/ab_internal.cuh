@@ -334,6 +334,10 @@ template <class T, int D> struct SpaceDev {
     int goff;     // global layer of local layer 0
     int nl;       // owned layers (== dims[D-1] when W == 0)
     int W;        // halo layers on each side; 0 = not windowed
+    // Periodicity of the last axis of the SPACE.  periodic[D-1] steers the cell-index arithmetic and is always true on
+    // a slab window (the window wraps onto its own halo layers; beyond a non-periodic edge those layers are empty);
+    // positions are normalised (walk.jl:77-91) with this flag.
+    bool gper_last;
 };
 
 template <class T, int D> static inline SpaceDev<T, D> make_space(const ab_handle* h) {
@@ -360,6 +364,8 @@ template <class T, int D> static inline SpaceDev<T, D> make_space(const ab_handl
         s.div_s2[d] = (uint8_t)(l > 1 ? l - 1 : 0);
     }
     s.W = h->win_W;
+    s.gper_last = s.periodic[D - 1];
+    if (h->win_W) s.periodic[D - 1] = true;
     s.gdl = h->win_W ? h->win_gdl : h->dims[D - 1];
     s.goff = h->win_W ? h->win_goff : 0;
     s.nl = h->win_W ? h->win_nl : h->dims[D - 1];

@@ -74,7 +74,7 @@ __device__ __forceinline__ bool pf_integrate(const SpaceDev<T, D>& sp, const PfU
         const T a = f[d] / mass;
         nv[d] = v[d] + a * u.dt;
         T x = (p[d] + nv[d] * u.dt) + (a / T(2)) * (u.dt * u.dt);
-        x = normalize_coord(x, sp.extent[d], sp.periodic[d]);
+        x = normalize_coord(x, sp.extent[d], d == D - 1 ? sp.gper_last : sp.periodic[d]);
         if (!(x >= T(0) && x <= sp.extent[d])) bad = true;
         np[d] = x;
     }

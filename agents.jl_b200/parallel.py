@@ -28,11 +28,12 @@ def slab_layout(n_layers: int, nranks: int):
     return out
 
 
-def window_layers(first: int, count: int, n_layers: int, W: int = HALO_W):
-    """Global layers a rank stores, in its local order: owned, upper halo, lower halo."""
+def window_layers(first: int, count: int, n_layers: int, W: int = HALO_W, periodic: bool = True):
+    """Global layers a rank stores, in its local order: owned, upper halo, lower halo.  On a non-periodic axis the
+    halo layers beyond the space do not exist (None)."""
     own = [(first + i) % n_layers for i in range(count)]
-    up = [(first + count + i) % n_layers for i in range(W)]
-    lo = [(first - W + i) % n_layers for i in range(W)]
+    up = [(first + count + i) % n_layers if periodic or first + count + i < n_layers else None for i in range(W)]
+    lo = [(first - W + i) % n_layers if periodic or first - W + i >= 0 else None for i in range(W)]
     return own, up, lo
 
 
@@ -44,11 +45,16 @@ def cell_layer(pos_last, spacing, n_layers):
     return np.clip(np.maximum(c, 1) - 1, 0, n_layers - 1)
 
 
-def select_window(layer, first, count, n_layers, W: int = HALO_W):
+def select_window(layer, first, count, n_layers, W: int = HALO_W, periodic: bool = True):
     """Indices (into the global arrays) of the agents a rank must hold, and the owned subset mask."""
-    rel = (np.asarray(layer, dtype=np.int64) - first) % n_layers          # 0 .. n_layers-1
-    owned = rel < count
-    halo = ((rel >= count) & (rel < count + W)) | (rel >= n_layers - W)
+    if periodic:
+        rel = (np.asarray(layer, dtype=np.int64) - first) % n_layers      # 0 .. n_layers-1
+        owned = rel < count
+        halo = ((rel >= count) & (rel < count + W)) | (rel >= n_layers - W)
+    else:                                                                 # no wrap: the end slabs have one halo only
+        rel = np.asarray(layer, dtype=np.int64) - first
+        owned = (rel >= 0) & (rel < count)
+        halo = ((rel >= count) & (rel < count + W)) | ((rel < 0) & (rel >= -W))
     idx = np.nonzero(owned | halo)[0]
     return idx, owned[idx]
 
@@ -82,6 +88,7 @@ class Slabs:
         model._ck(lib.ab_comm_slab(model.h, C.byref(first), C.byref(count)))
         self.first, self.count = first.value, count.value
         self.n_layers = model.space.dims[-1]
+        self.periodic_last = bool(model.space.periodic[-1])
         assert (self.first, self.count) == slab_layout(self.n_layers, self.world)[self.rank]
         assert lib.ab_comm_halo(model.h) == HALO_W
         self.n_global = 0
@@ -101,8 +108,10 @@ class Slabs:
         self.dist.all_gather_object(handles, bytes(mine) if rc == 0 else None)
         if any(h is None for h in handles):
             return False                                    # some rank could not export: everyone stays on NCCL
-        lo = (C.c_ubyte * 64).from_buffer_copy(handles[(self.rank - 1) % self.world])
-        up = (C.c_ubyte * 64).from_buffer_copy(handles[(self.rank + 1) % self.world])
+        has_lo = self.periodic_last or self.rank > 0                 # end slabs of a non-periodic axis have one neighbour
+        has_up = self.periodic_last or self.rank < self.world - 1
+        lo = (C.c_ubyte * 64).from_buffer_copy(handles[(self.rank - 1) % self.world]) if has_lo else None
+        up = (C.c_ubyte * 64).from_buffer_copy(handles[(self.rank + 1) % self.world]) if has_up else None
         rc = lib.ab_comm_ipc_import(m.h, lo, up)
         oks = [None] * self.world
         self.dist.all_gather_object(oks, rc == 0)
@@ -130,7 +139,7 @@ class Slabs:
                 m._columns[name], m._dtypes[name], m._ncomp[name] = fid, a.dtype, a.shape[1]
             cols[name] = np.ascontiguousarray(a, dtype=m._dtypes[name])
         layer = cell_layer(pos[:, -1], m.space.spacing, self.n_layers)
-        idx, owned = select_window(layer, self.first, self.count, self.n_layers)
+        idx, owned = select_window(layer, self.first, self.count, self.n_layers, periodic=self.periodic_last)
         cap = halo_capacity or default_halo_capacity(self.n_global, self.n_layers)
         m._ck(lib.ab_comm_set_capacity(m.h, int(cap)))
         self.direct = self._link_direct()
@@ -168,7 +177,7 @@ class Slabs:
             pos = np.ascontiguousarray(pos, dtype=dt).reshape(-1, m.D)
             vel = np.ascontiguousarray(vel, dtype=dt).reshape(-1, m.D)
             layer = cell_layer(pos[:, -1], m.space.spacing, self.n_layers)
-            idx, owned = select_window(layer, self.first, self.count, self.n_layers)
+            idx, owned = select_window(layer, self.first, self.count, self.n_layers, periodic=self.periodic_last)
             keep_ids.append((idx + first + 1).astype(np.int64))
             keep_p.append(pos[idx])
             keep_v.append(vel[idx])

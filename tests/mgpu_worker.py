@@ -31,6 +31,7 @@ def main():
     ap.add_argument("--dtype", default="float64")
     ap.add_argument("--seed", type=int, default=42)
     ap.add_argument("--rule", default="flock", choices=["flock", "pairforce"])
+    ap.add_argument("--walls", action="store_true", help="non-periodic last axis (the end slabs have one neighbour)")
     args = ap.parse_args()
 
     import torch
@@ -59,7 +60,8 @@ def main():
         make_rule = lambda: ab.PairForceRule(dt=0.005, cutoff=args.spacing)
 
     rule = make_rule()
-    m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=args.spacing, dtype=dt), model_step=rule, device=local)
+    periodic = tuple([True] * (len(extent) - 1) + [not args.walls])
+    m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=args.spacing, dtype=dt, periodic=periodic), model_step=rule, device=local)
     slabs = Slabs(m, dist)
     owned0 = slabs.scatter(pos, vel, columns=cols)
     done, owned_hist = 0, [owned0]
@@ -73,7 +75,7 @@ def main():
     dist.all_reduce(tot)
     result = None
     if rank == 0:
-        ref = ab.StandardABM(ab.ContinuousSpace(extent, spacing=args.spacing, dtype=dt), model_step=make_rule(), device=local)
+        ref = ab.StandardABM(ab.ContinuousSpace(extent, spacing=args.spacing, dtype=dt, periodic=periodic), model_step=make_rule(), device=local)
         ref.add_agents(pos, vel, **(cols or {}))
         done = 0
         while done < args.steps:

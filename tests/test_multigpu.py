@@ -35,6 +35,8 @@ CASES = [
     ("2d-uneven-layers", ["--agents", "50000", "--extent", "300", "405", "--steps", "9", "--chunk", "3"]),
     ("3d-approx", ["--agents", "40000", "--extent", "60", "60", "120", "--steps", "8"]),
     ("2d-f32", ["--agents", "60000", "--extent", "400", "400", "--steps", "6", "--dtype", "float32"]),
+    ("2d-walls", ["--agents", "60000", "--extent", "400", "400", "--steps", "12", "--walls"]),
+    ("3d-walls-exact", ["--agents", "40000", "--extent", "60", "60", "120", "--steps", "8", "--walls", "--search", "exact"]),
 ]
 
 

@@ -55,6 +55,24 @@ def test_select_window_owned_sets_partition_and_halo_is_complete(nranks):
     assert np.all(owned_total == 1)
 
 
+@pytest.mark.parametrize("nranks", [2, 3, 5])
+def test_select_window_without_wrap_on_a_non_periodic_axis(nranks):
+    """Non-periodic last axis: the end slabs have ONE halo (no layers beyond the space), owned sets still partition."""
+    extent, spacing = (200.0, 400.0), 5.0
+    pos, _ = flock_init(20000, extent, 5)
+    n_layers = 80
+    layer = P.cell_layer(pos[:, 1], spacing, n_layers)
+    owned_total = np.zeros(len(pos), dtype=int)
+    for r, (first, count) in enumerate(P.slab_layout(n_layers, nranks)):
+        idx, owned = P.select_window(layer, first, count, n_layers, periodic=False)
+        owned_total[idx[owned]] += 1
+        own, up, lo = P.window_layers(first, count, n_layers, periodic=False)
+        assert (r == 0) == all(l is None for l in lo) and (r == nranks - 1) == all(u is None for u in up)
+        layers = own + [l for l in up + lo if l is not None]
+        assert np.array_equal(np.sort(idx), np.nonzero(np.isin(layer, layers))[0])
+    assert np.all(owned_total == 1)
+
+
 def test_merge_parts_detects_loss_and_duplication():
     ids = np.arange(1, 11)
     p = np.zeros((10, 2))

@@ -11,8 +11,11 @@ from helpers import FLOCK, flock_init
 pytestmark = pytest.mark.gpu
 
 CASES = [
-    # extent, nslabs, n, search, dtype, steps
+    # extent, nslabs, n, search, dtype, steps[, periodic]
     ((400.0, 400.0), 2, 60000, "approximate", np.float64, 12),
+    ((400.0, 400.0), 2, 60000, "approximate", np.float64, 12, (True, False)),     # non-periodic last axis: end slabs have one neighbour
+    ((400.0, 400.0), 3, 60000, "exact", np.float64, 9, False),                    # walls everywhere
+    ((60.0, 60.0, 120.0), 2, 40000, "approximate", np.float64, 6, (True, True, False)),
     ((400.0, 400.0), 4, 60000, "exact", np.float64, 9),
     ((300.0, 405.0), 3, 50000, "approximate", np.float64, 9),      # 81 layers over 3 slabs
     ((300.0, 415.0), 4, 50000, "approximate", np.float64, 8),      # 83 layers: uneven slabs (21,21,21,20)
@@ -22,11 +25,13 @@ CASES = [
 ]
 
 
-@pytest.mark.parametrize("extent,nslabs,n,search,dtype,steps", CASES)
-def test_local_slabs_bitwise_equal_to_unsharded(extent, nslabs, n, search, dtype, steps):
+@pytest.mark.parametrize("case", CASES)
+def test_local_slabs_bitwise_equal_to_unsharded(case):
+    extent, nslabs, n, search, dtype, steps = case[:6]
+    periodic = case[6] if len(case) > 6 else True
     pos, vel = flock_init(n, extent, 42, dtype=dtype)
     rule = ab.FlockRule(search=search, kernel="fine", **FLOCK)
-    mk = lambda: ab.ContinuousSpace(extent, spacing=5.0, dtype=dtype)
+    mk = lambda: ab.ContinuousSpace(extent, spacing=5.0, dtype=dtype, periodic=periodic)
     ls = LocalSlabs(mk, rule, nslabs)
     owned0 = ls.scatter(pos, vel)
     assert sum(owned0) == n
@@ -59,8 +64,6 @@ def test_sharded_handle_refuses_id_addressed_calls_and_bad_layouts():
     ls.close()
     with pytest.raises(ab.AgentsError):                  # 20 layers over 8 slabs: fewer than 4 per slab
         LocalSlabs(lambda: ab.ContinuousSpace((100.0, 100.0), spacing=5.0), rule, 8)
-    with pytest.raises(ab.AgentsError):                  # non-periodic last axis
-        LocalSlabs(lambda: ab.ContinuousSpace(extent, spacing=5.0, periodic=(True, False)), rule, 2)
 
 
 def test_halo_capacity_overflow_is_an_error():
