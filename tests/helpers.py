@@ -39,13 +39,17 @@ def csr_sets(offsets, ids):
 
 
 def rel_err(a, b):
+    """max |a - b| / max(1, |b|): RELATIVE for |b| > 1, ABSOLUTE below.  For velocities (|v| = 1) "1e-13" is an
+    absolute 1e-13; for a coordinate near 2000 (F2D-1M) the same bound admits 2e-10 absolute — about one ulp
+    (2.3e-13) times the few hundred roundings of a step, stated here so that nobody reads it as 1e-13 absolute."""
     a = np.asarray(a, dtype=np.float64)
     b = np.asarray(b, dtype=np.float64)
     return float(np.max(np.abs(a - b) / np.maximum(1.0, np.abs(b))))
 
 
 def periodic_rel_err(a, b, extent):
-    """max |a-b| with the periodic image removed (a bird that wraps one ulp apart lands L away)."""
+    """max |a-b| / max(1, |b|) with the periodic image removed (a bird that wraps one ulp apart lands L away).
+    Same scaling as rel_err: absolute below 1, relative above."""
     a = np.asarray(a, dtype=np.float64)
     b = np.asarray(b, dtype=np.float64)
     L = np.asarray(extent, dtype=np.float64)[None, :]
