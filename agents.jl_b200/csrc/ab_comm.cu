@@ -30,6 +30,7 @@
 #include <dlfcn.h>
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #include "ab_internal.cuh"
@@ -95,6 +96,7 @@ struct ab_comm {
     ab_handle *peer_lower = nullptr, *peer_upper = nullptr;
     bool linked_local = false;       // ab_comm_link_local done (an end slab of a non-periodic axis has one peer only)
     bool has_lower = true, has_upper = true;   // false on the end ranks of a non-periodic last axis
+    bool no_fused_pack = false;      // AB_FUSED_PACK=0: always pack with the separate k_halo_pack launch (A/B experiments)
     cudaEvent_t ev_packed = nullptr, ev_consumed = nullptr;
     uint32_t* h_counts = nullptr;    // pinned {n_own, n_window}
     int64_t exchanges = 0;
@@ -136,17 +138,6 @@ static int64_t cells_per_layer(const ab_handle* h) { return (h->ncells / h->dims
 // ---------------------------------------------------------------------------------------------------
 // message: [hdr 16 B][cs slice (ncs + 1) u32, padded to 16 B][pos D x C][vel D x C][id C][key C]
 // ---------------------------------------------------------------------------------------------------
-// ... followed by the user columns (every registered field beyond pos / vel: the r, k, mass of the pair-force rule,
-// per-bird parameters, ...), each [ncomp x C] of its element size
-#define AB_MSG_MAXF 8
-struct MsgLayout {
-    size_t off_cs, off_pos, off_vel, off_id, off_key, bytes;
-    uint32_t ncs;
-    int64_t C;
-    int nx;                              // user columns in the message
-    size_t off_x[AB_MSG_MAXF];
-    int x_ncomp[AB_MSG_MAXF], x_esize[AB_MSG_MAXF];
-};
 struct MsgCols { char* p[AB_MSG_MAXF]; };   // the columns' device arrays (current buffer), same order
 static MsgLayout msg_layout(const ab_handle* h, int64_t C, uint32_t ncs) {
     const int D = h->D;
@@ -443,36 +434,53 @@ static int ensure_buffers(ab_handle* h) {
     return AB_OK;
 }
 
-template <class E, int D>
-static int pack_t(ab_handle* h) {
+// Destinations of this step's boundary messages (parity slot of the neighbours' blocks, or the send buffers), the
+// waits that protect them, and — direct exchange — the flags to publish.  out->enabled says whether the tiled
+// re-sort may deliver the messages itself (no user columns travel: those are permuted after the re-sort).
+int ab_comm_pack_begin(ab_handle* h, HaloOut* out) {
     ab_comm* c = h->comm;
+    out->enabled = 0;
+    if (!c || !h->win_W) return ab_fail(h, AB_ERR_STATE, "handle is not sharded");
     AB_TRY(ensure_buffers(h));
-    const int cur = h->cur;
-    const uint32_t ncs = (uint32_t)(AB_HALO_W * keys_per_layer(h));
-    const uint32_t kown = (uint32_t)(h->win_nl * keys_per_layer(h));
-    const MsgLayout m = msg_layout(h, c->cap_agents, ncs);
     if (h->fields.size() > 2u + AB_MSG_MAXF) return ab_fail(h, AB_ERR_INVALID, "too many user columns for the halo message");
-    // one item per thread (up to 592 CTAs per side): the stores are posted writes, the cost is latency
-    const int nb = (int)std::min<int64_t>(std::max<int64_t>((std::max<int64_t>(c->cap_agents, ncs) + 255) / 256, 1), 592);
+    const uint32_t ncs = (uint32_t)(AB_HALO_W * keys_per_layer(h));
+    out->ncs = ncs;
+    out->kown = (uint32_t)(h->win_nl * keys_per_layer(h));
+    out->m = msg_layout(h, c->cap_agents, ncs);
     // in-process peers: they must have consumed the previous message before it is overwritten
     if (c->linked_local && c->peer_lower) AB_CUDA(h, cudaStreamWaitEvent(h->stream, c->peer_lower->comm->ev_consumed, 0));
     if (c->linked_local && c->peer_upper) AB_CUDA(h, cudaStreamWaitEvent(h->stream, c->peer_upper->comm->ev_consumed, 0));
     // my bottom layers are the lower neighbour's "from upper" message (side 0), my top layers the upper
     // neighbour's "from lower" one (side 1)
     c->cur_par = (int)(c->exchanges & 1);
-    char* dst0 = c->ipc_on ? ipc_slot(c->ipc_lower, c->ipc_stride, c->cur_par, 0) : (char*)c->sendbuf[0];
-    char* dst1 = c->ipc_on ? ipc_slot(c->ipc_upper, c->ipc_stride, c->cur_par, 1) : (char*)c->sendbuf[1];
-    if (!c->has_lower) dst0 = nullptr;                   // end rank of a non-periodic axis: nothing to send that way
-    if (!c->has_upper) dst1 = nullptr;
+    out->buf[0] = !c->has_lower ? nullptr : c->ipc_on ? ipc_slot(c->ipc_lower, c->ipc_stride, c->cur_par, 0) : (char*)c->sendbuf[0];
+    out->buf[1] = !c->has_upper ? nullptr : c->ipc_on ? ipc_slot(c->ipc_upper, c->ipc_stride, c->cur_par, 1) : (char*)c->sendbuf[1];
+    out->done_ctr = c->ipc_on ? ipc_flag(c->ipc_block, c->ipc_stride, 2, 0) : nullptr;
+    out->flag[0] = c->ipc_on && c->has_lower ? ipc_flag(c->ipc_lower, c->ipc_stride, c->cur_par, 0) : nullptr;
+    out->flag[1] = c->ipc_on && c->has_upper ? ipc_flag(c->ipc_upper, c->ipc_stride, c->cur_par, 1) : nullptr;
+    out->epoch = (uint32_t)(c->exchanges + 1);
+    out->enabled = (out->m.nx == 0 && !c->no_fused_pack) ? 1 : 0;
+    return AB_OK;
+}
+
+template <class E, int D>
+static int pack_t(ab_handle* h) {
+    ab_comm* c = h->comm;
+    if (h->halo_packed) {                                // delivered by the re-sort of this step (HaloOut)
+        h->halo_packed = false;
+        if (c->linked_local) AB_CUDA(h, cudaEventRecord(c->ev_packed, h->stream));
+        return AB_OK;
+    }
+    HaloOut ho;
+    AB_TRY(ab_comm_pack_begin(h, &ho));
+    const int cur = h->cur;
+    // one item per thread (up to 592 CTAs per side): the stores are posted writes, the cost is latency
+    const int nb = (int)std::min<int64_t>(std::max<int64_t>((std::max<int64_t>(c->cap_agents, ho.ncs) + 255) / 256, 1), 592);
     {
         AB_LAUNCH(h, "k_halo_pack");
-        k_halo_pack<E, D><<<dim3(nb, 2), 256, 0, h->stream>>>(m, msg_cols(h), kown, h->cell_start, (const E*)h->fields[0].buf[cur],
+        k_halo_pack<E, D><<<dim3(nb, 2), 256, 0, h->stream>>>(ho.m, msg_cols(h), ho.kown, h->cell_start, (const E*)h->fields[0].buf[cur],
                                                              (const E*)h->fields[1].buf[cur], h->id[cur], h->key[cur], h->cap,
-                                                             dst0, dst1, h->d_err,
-                                                             c->ipc_on ? ipc_flag(c->ipc_block, c->ipc_stride, 2, 0) : nullptr,
-                                                             c->ipc_on && c->has_lower ? ipc_flag(c->ipc_lower, c->ipc_stride, c->cur_par, 0) : nullptr,
-                                                             c->ipc_on && c->has_upper ? ipc_flag(c->ipc_upper, c->ipc_stride, c->cur_par, 1) : nullptr,
-                                                             (uint32_t)(c->exchanges + 1));
+                                                             ho.buf[0], ho.buf[1], h->d_err, ho.done_ctr, ho.flag[0], ho.flag[1], ho.epoch);
     }
     if (c->linked_local) AB_CUDA(h, cudaEventRecord(c->ev_packed, h->stream));
     return AB_OK;
@@ -627,6 +635,7 @@ int ab_comm_init(ab_handle* h, int rank, int nranks, const void* nccl_unique_id)
     c->lower = (rank + nranks - 1) % nranks;
     c->upper = (rank + 1) % nranks;
     // non-periodic last axis: the end slabs have one neighbour; the halo layers beyond the space stay empty
+    if (const char* e = getenv("AB_FUSED_PACK")) c->no_fused_pack = atoi(e) == 0;
     c->has_lower = per_last || rank > 0;
     c->has_upper = per_last || rank < nranks - 1;
     if (cudaMallocHost((void**)&c->h_counts, 2 * sizeof(uint32_t)) != cudaSuccess) { delete c; return ab_fail(h, AB_ERR_CUDA, "cudaMallocHost failed"); }

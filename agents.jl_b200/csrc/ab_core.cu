@@ -225,6 +225,44 @@ k_scan(uint32_t* __restrict__ count, uint32_t* __restrict__ start, uint32_t n, u
         if (base + i < n) start[base + i] = off + v[i];
 }
 
+// Small scans (the tile totals of the tiled re-sort: ~10 k entries) in ONE CTA: no ticket, no status words, no
+// look-back — thread t owns the items [t * ipt, (t + 1) * ipt), ipt <= 32.  Zeroes count behind itself like k_scan.
+#define SCAN_SMALL_MAX 32768u
+__global__ void __launch_bounds__(1024)
+k_scan_small(uint32_t* __restrict__ count, uint32_t* __restrict__ start, uint32_t n) {
+    __shared__ uint32_t s_w[32];
+    ab_dep_wait();
+    const uint32_t ipt = (n + 1023u) >> 10;
+    const uint32_t b = threadIdx.x * ipt;
+    uint32_t v[32];
+    uint32_t sum = 0;
+#pragma unroll
+    for (uint32_t q = 0; q < 32; ++q) {
+        v[q] = 0;
+        if (q < ipt && b + q < n) { v[q] = count[b + q]; count[b + q] = 0; }
+        sum += v[q];
+    }
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint32_t inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+    if (lane == 31) s_w[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        uint32_t w = s_w[lane], wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, wi, o); if (lane >= o) wi += t; }
+        s_w[lane] = wi - w;                                   // exclusive prefix of the warp totals
+        if (lane == 31) start[n] = wi;
+    }
+    __syncthreads();
+    uint32_t run = s_w[wid] + (inc - sum);
+#pragma unroll
+    for (uint32_t q = 0; q < 32; ++q) {
+        if (q < ipt && b + q < n) { start[b + q] = run; run += v[q]; }
+    }
+}
+
 __global__ void k_bucket(const uint32_t* __restrict__ newkey, const uint32_t* __restrict__ rank,
                          const uint32_t* __restrict__ cell_start, const int32_t* __restrict__ id_old, int n,
                          int32_t* __restrict__ idtmp) {
@@ -324,6 +362,11 @@ __global__ void k_cells(SpaceDev<T, D> sp, const T* __restrict__ pos, const int3
 // Exclusive scan of count[0..n) into start[0..n] (start[n] = total); zeroes count.  `count` must be
 // readable / writable up to the next multiple of SCAN_TILE.
 int ab_scan_u32(ab_handle* h, uint32_t* count, uint32_t* start, uint32_t n) {
+    if (n > 0 && n <= SCAN_SMALL_MAX && h->small_scan) {      // measured slower than three look-back tiles (18.7 vs 10.5 us): off
+        AB_LAUNCH(h, "k_scan");
+        AB_CUDA(h, ab_launch_chain(h->pdl, k_scan_small, dim3(1), dim3(1024), h->stream, count, start, n));
+        return AB_OK;
+    }
     uint32_t ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
     if (ntiles == 0) ntiles = 1;
     if (ntiles > h->scan_status_len) return ab_fail(h, AB_ERR_INVALID, "scan larger than the handle's status buffer");
@@ -491,6 +534,7 @@ int ab_create(ab_space_desc* desc, int device, ab_handle** out) {
     if (const char* e = getenv("AB_OVERLAP")) h->overlap_halo = atoi(e) != 0;
     if (const char* e = getenv("AB_PDL")) h->pdl = atoi(e) != 0;
     if (const char* e = getenv("AB_FINE4")) h->fine4 = atoi(e) != 0;     // A/B experiments
+    if (const char* e = getenv("AB_SMALL_SCAN")) h->small_scan = atoi(e) != 0;
     if (const char* e = getenv("AB_RS_TARGET")) { int v = atoi(e); if (v >= 4 && v <= 2048) h->rs_target = v; }   // tuning experiments
     h->D = desc->D;
     int64_t ncells = 1;

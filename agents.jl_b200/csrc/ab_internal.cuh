@@ -169,6 +169,8 @@ struct ab_handle {
     uint64_t sch_tick = 0;             // steps taken so far (decorrelates the per-step permutations)
 
     ab_comm* comm = nullptr;
+    bool small_scan = false;           // AB_SMALL_SCAN=1: single-CTA scan of the tile totals (A/B experiments)
+    bool halo_packed = false;          // the re-sort of this step already delivered the boundary messages
     // slab window along the last axis (multi-GPU, ab_comm.cu); W == 0: the handle holds the whole space
     int win_gdl = 0, win_goff = 0, win_nl = 0, win_W = 0;
 
@@ -242,6 +244,33 @@ int ab_grid_walk(ab_handle* h, const void* directions, const int64_t* active_ids
 int ab_grid_randomwalk(ab_handle* h, double r, uint64_t seed, const int64_t* active_ids, int64_t nactive, int ifempty, int force_motion);
 int ab_grid_nearby(ab_handle* h, const void* qpos, const int64_t* qids, int64_t nq, double r, int exclude_self,
                    int64_t* counts, const int64_t* offsets, int64_t* ids_out);
+
+// ---- boundary messages of a slab window (ab_comm.cu) ----------------------------------------------
+// [hdr 16 B][cs slice (ncs + 1) u32, padded to 16 B][pos D x C][vel D x C][id C][key C]
+// ... followed by the user columns (every registered field beyond pos / vel: the r, k, mass of the pair-force rule,
+// per-bird parameters, ...), each [ncomp x C] of its element size
+#define AB_MSG_MAXF 8
+struct MsgLayout {
+    size_t off_cs, off_pos, off_vel, off_id, off_key, bytes;
+    uint32_t ncs;
+    int64_t C;
+    int nx;                              // user columns in the message
+    size_t off_x[AB_MSG_MAXF];
+    int x_ncomp[AB_MSG_MAXF], x_esize[AB_MSG_MAXF];
+};
+// Where the tiled re-sort of a slab window delivers its boundary layers while it places them (ab_comm_pack_begin):
+// the W bottom owned layers go to the lower neighbour's message, the W top ones to the upper neighbour's — into
+// the neighbour's memory (direct exchange) or into this rank's send buffers.  The last boundary tile to finish
+// publishes the exchange number in the neighbours' flags.  enabled == 0: a separate k_halo_pack launch packs.
+struct HaloOut {
+    int enabled;
+    char* buf[2];              // nullptr: no neighbour on that side
+    uint32_t* flag[2];         // direct exchange only
+    uint32_t* done_ctr;        // direct exchange only
+    uint32_t epoch, ncs, kown;
+    MsgLayout m;
+};
+int ab_comm_pack_begin(ab_handle* h, HaloOut* out);
 
 // launch bookkeeping: every kernel launch of the library goes through this
 struct ab_launch_scope {
@@ -385,14 +414,19 @@ __device__ __forceinline__ float ab_next(float x, float dir) { return nextafterf
 
 // Julia mod(x::T, y::T) for floats — base/float.jl; used by normalize_position
 // (src/spaces/walk.jl:77-79).  Can return exactly y.
-template <class T> __device__ __forceinline__ T jl_mod(T x, T y) {
-    // fast exact cases for 0 <= x < 2y (the common Euler step): fmod(x,y) == x or x - y
+template <class T> __device__ __noinline__ T jl_mod_slow(T x, T y) {
     T r;
     if (x >= T(0) && x < y) r = x;
     else r = ab_fmod(x, y);
     if (r == T(0)) return copysign(r, y);
     if ((r > T(0)) != (y > T(0))) return r + y;
     return r;
+}
+template <class T> __device__ __forceinline__ T jl_mod(T x, T y) {
+    // the common Euler step stays inside (0, y): mod(x, y) == x exactly; everything else (wraps, zeros, negative
+    // moduli, NaN) takes the out-of-line general form
+    if (x > T(0) && x < y) return x;
+    return jl_mod_slow<T>(x, y);
 }
 template <class T> __device__ __forceinline__ T jl_sign(T x) { return x > T(0) ? T(1) : (x < T(0) ? T(-1) : x); }
 __device__ __forceinline__ int jl_mod1(int x, int y) {

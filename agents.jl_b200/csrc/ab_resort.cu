@@ -70,9 +70,12 @@ constexpr int kRsAggUnroll = RS_AGG_UNROLL;     // crowded-cell aggregate loop: 
 //      (match.any + per-cell cursor: final output slot at once) and queue (source slot, output slot) in a ring
 //   2  whenever 32 pairs wait: move 32 agents with all lanes busy (gathered loads, stores clustered by cell)
 //   3  aggregates of the tile's cells
-template <class T, int D, int G>
+//   HALO (slab window, no user columns): tiles of the W bottom / top owned layers also deliver what they place into
+//      the boundary messages of the lower / upper neighbour (HaloOut) — there is no separate pack launch; those
+//      tiles run first, and the last of them publishes the exchange number in the neighbours' flags
+template <class T, int D, int G, bool HALO>
 __global__ void RS_BOUNDS
-k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, const uint32_t* __restrict__ newkey,
+k_resort(SpaceDev<T, D> sp, ResortArgs a, const __grid_constant__ HaloOut ho, const uint32_t* __restrict__ cs_old, const uint32_t* __restrict__ newkey,
          const int32_t* __restrict__ id_old, const T* __restrict__ src_pos, const T* __restrict__ src_vel,
          int64_t cap, T* dst_pos, T* dst_vel, int32_t* __restrict__ id_new,
          uint32_t* __restrict__ key_new, uint32_t* __restrict__ cell_count, const uint32_t* __restrict__ tile_base,
@@ -87,11 +90,38 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, c
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const unsigned lt = (1u << lane) - 1u;
-    const int tile = blockIdx.x * RS_WARPS + w;
+    int tile = blockIdx.x * RS_WARPS + w;
     if (tile >= a.ntiles) return;                                  // warp-uniform; no CTA barriers below
-    const int frow = tile / a.tpr, seg_x = tile - frow * a.tpr;    // fine row, segment of it
     const int kb = sp.kb;
     const int fd0 = sp.dims[0] << kb, fd1 = sp.dims[1] << kb, fd2 = D == 3 ? (sp.dims[2] << kb) : 1;
+    int frow = tile / a.tpr;
+    const int seg_x = tile - frow * a.tpr;                         // fine row, segment of it
+    // HALO: nb fine rows per message; launch order = top boundary rows, bottom boundary rows, interior
+    const int nb = HALO ? (int)(ho.ncs / (uint32_t)fd0) : 0;
+    bool reg[2] = {false, false};                                  // this tile feeds the bottom / top message
+    uint32_t s0[2] = {0, 0}, cntc[2] = {0, 0}, k0[2] = {0, 0};
+    if (HALO) {
+        frow = frow < nb ? a.nrows - nb + frow : frow - nb;
+        tile = frow * a.tpr + seg_x;
+        reg[0] = frow < nb && ho.buf[0] != nullptr;
+        reg[1] = frow >= a.nrows - nb && ho.buf[1] != nullptr;
+        const int t0b[2] = {0, (a.nrows - nb) * a.tpr}, t1b[2] = {nb * a.tpr, a.ntiles};
+        k0[1] = ho.kown - ho.ncs;
+#pragma unroll
+        for (int dir = 0; dir < 2; ++dir) {
+            if (!reg[dir]) continue;
+            s0[dir] = tile_base[t0b[dir]];
+            const uint32_t cnt = tile_base[t1b[dir]] - s0[dir];
+            cntc[dir] = min(cnt, (uint32_t)ho.m.C);
+            if (tile == t0b[dir] && lane == 0) {                   // the region's first tile: header (and the capacity check)
+                uint32_t* hdr = reinterpret_cast<uint32_t*>(ho.buf[dir]);
+                hdr[0] = cntc[dir]; hdr[1] = k0[dir]; hdr[2] = ho.ncs; hdr[3] = 0xAB200u;
+                if (cnt > (uint32_t)ho.m.C) atomicOr(err, AB_EF_COMM);
+            }
+            if (tile == t1b[dir] - 1 && lane == 0)                 // the region's last tile: closing entry of the cell_start slice
+                reinterpret_cast<uint32_t*>(ho.buf[dir] + ho.m.off_cs)[ho.ncs] = cntc[dir];
+        }
+    }
     const int x0 = seg_x * a.tw;
     const int x1 = min(fd0, x0 + a.tw);          // exclusive, fine cells
     const uint32_t kbeg = (uint32_t)frow * (uint32_t)fd0 + (uint32_t)x0;
@@ -102,9 +132,19 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, c
     const uint32_t base = tile_base[tile];
     const uint32_t total = tile_base[tile + 1] - base;
     if (tile == a.ntiles - 1 && lane == 0) cs_new[kend] = base + total;      // end of the re-sorted key range
+    bool lost = false;
 
+    // HALO: entry of the message's cell_start slice for the tile's cell i, whose first output slot is `slot`
+    auto msg_cs = [&](int i, uint32_t slot) {
+#pragma unroll
+        for (int dir = 0; dir < 2; ++dir)
+            if (reg[dir]) reinterpret_cast<uint32_t*>(ho.buf[dir] + ho.m.off_cs)[kbeg + (uint32_t)i - k0[dir]] = min(slot - s0[dir], cntc[dir]);
+    };
     if (total == 0) {
-        for (int i = lane; i < fc; i += 32) cs_new[(size_t)kbeg + i] = base;
+        for (int i = lane; i < fc; i += 32) {
+            cs_new[(size_t)kbeg + i] = base;
+            if (HALO) msg_cs(i, base);
+        }
     } else {
     // ---- phase 0: lane l owns the cells [l * ch, (l + 1) * ch) of the tile ----
     {
@@ -128,6 +168,7 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, c
             if (q < ch && i0 + q < fc) {
                 s_cur[w][i0 + q] = run;
                 cs_new[(size_t)kbeg + i0 + q] = base + run;
+                if (HALO) msg_cs(i0 + q, base + run);
                 if (cnt[q]) cell_count[(size_t)kbeg + i0 + q] = 0;
                 run += cnt[q];
             }
@@ -185,6 +226,21 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, c
             id_new[oo] = idv;
             key_new[oo] = kv;
             if (perm) perm[oo] = (int32_t)si;
+            if (HALO) {
+#pragma unroll
+                for (int dir = 0; dir < 2; ++dir) {
+                    const uint32_t t = (uint32_t)oo - s0[dir];
+                    if (reg[dir] && t < cntc[dir]) {
+                        char* mb = ho.buf[dir];
+                        T* mpos = reinterpret_cast<T*>(mb + ho.m.off_pos);
+                        T* mvel = reinterpret_cast<T*>(mb + ho.m.off_vel);
+#pragma unroll
+                        for (int d = 0; d < D; ++d) { mpos[(size_t)d * ho.m.C + t] = pv[d]; mvel[(size_t)d * ho.m.C + t] = pv[D + d]; }
+                        reinterpret_cast<int32_t*>(mb + ho.m.off_id)[t] = idv;
+                        reinterpret_cast<uint32_t*>(mb + ho.m.off_key)[t] = kv;
+                    }
+                }
+            }
         }
         __syncwarp();                                              // ring entries may be overwritten from here on
     };
@@ -228,9 +284,27 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, c
     // every agent counted into this tile must have been found in the 3^D neighbourhood
     if (queued != total) {
         if (lane == 0) atomicOr(err, AB_EF_OVERFLOW);              // an agent left its 3^D neighbourhood
-        return;
+        lost = true;
     }
     }   // total != 0
+
+    if (HALO && ho.done_ctr && (frow < nb || frow >= a.nrows - nb)) {
+        // direct exchange: this boundary tile's part of the messages is stored (peer memory); the LAST boundary tile
+        // to get here publishes the exchange number in the neighbours' flags.  __syncwarp orders the lanes' stores
+        // before lane 0's system-scope fence (fences are cumulative).
+        __syncwarp();
+        if (lane == 0) {
+            __threadfence_system();
+            const uint32_t nbt = (uint32_t)(min(2 * nb, a.nrows) * a.tpr);
+            if (atomicAdd(ho.done_ctr, 1u) == nbt - 1u) {
+                __threadfence_system();
+                *ho.done_ctr = 0;
+                if (ho.flag[0]) asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(ho.flag[0]), "r"(ho.epoch) : "memory");
+                if (ho.flag[1]) asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(ho.flag[1]), "r"(ho.epoch) : "memory");
+            }
+        }
+    }
+    if (lost) return;
 
     // ---- per reference cell: count, Σ(pos - centre), Σ vel of this fine row's part, canonical order ---
     // Canonical sum of a cell's n agents (shared with k_cell_agg): 8 strided partials a_g = Σ_i x[g + 8 i]
@@ -239,6 +313,10 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, c
     if (a.want_agg) {
         __syncwarp();        // the tile's output slots were written by this warp; read them back through L2
         constexpr int NC = 1 + 2 * D;
+        // component c (pos 0..D-1, vel D..2D-1) of output slot t
+        auto row = [&](int c, uint32_t t) -> T {
+            return c < D ? __ldcg(dst_pos + (size_t)c * cap + t) : __ldcg(dst_vel + (size_t)(c - D) * cap + t);
+        };
         const int K = sp.K;
         const int ncell = fc >> kb;                           // x0 and tw are multiples of K
         const int cy = fy0 >> kb, cz = fz0 >> kb;
@@ -274,15 +352,15 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, c
                     if ((uint32_t)i < n) {
 #pragma unroll
                         for (int d = 0; d < D; ++d) {
-                            u[d] += __ldcg(dst_pos + (size_t)d * cap + b + i) - ctr[d];
-                            u[D + d] += __ldcg(dst_vel + (size_t)d * cap + b + i);
+                            u[d] += row(d, b + i) - ctr[d];
+                            u[D + d] += row(D + d, b + i);
                         }
                     }
                     if ((uint32_t)(i + 4) < n) {
 #pragma unroll
                         for (int d = 0; d < D; ++d) {
-                            v[d] += __ldcg(dst_pos + (size_t)d * cap + b + i + 4) - ctr[d];
-                            v[D + d] += __ldcg(dst_vel + (size_t)d * cap + b + i + 4);
+                            v[d] += row(d, b + i + 4) - ctr[d];
+                            v[D + d] += row(D + d, b + i + 4);
                         }
                     }
 #pragma unroll
@@ -321,8 +399,8 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const uint32_t* __restrict__ cs_old, c
                     for (uint32_t t = gb + gl; t < ge; t += 8) {
 #pragma unroll
                         for (int d = 0; d < D; ++d) {
-                            acc[d] += __ldcg(dst_pos + (size_t)d * cap + t) - ctr[d];
-                            acc[D + d] += __ldcg(dst_vel + (size_t)d * cap + t);
+                            acc[d] += row(d, t) - ctr[d];
+                            acc[D + d] += row(D + d, t);
                         }
                     }
                 }
@@ -460,11 +538,17 @@ static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool
     AB_TRY(ab_scan_u32(h, h->tile_count, h->tile_base, (uint32_t)a.ntiles));
     if (want_agg) AB_TRY(ensure_agg(h));
     const bool extra = h->fields.size() > 2u;
+    // slab window: the boundary tiles deliver the neighbours' messages while they place their agents
+    HaloOut ho;
+    ho.enabled = 0;
+    if (h->win_W && h->comm) AB_TRY(ab_comm_pack_begin(h, &ho));
+    h->halo_packed = ho.enabled != 0;
     {
         AB_LAUNCH(h, "k_resort");
         constexpr int G = (D == 2) ? RS_G2D : 2;           // source chunks in flight per warp
-        AB_CUDA(h, ab_launch_chain(h->pdl, k_resort<T, D, G>, dim3((a.ntiles + RS_WARPS - 1) / RS_WARPS), dim3(RS_THREADS), h->stream,
-            sp, a, h->cell_start, h->newkey, h->id[cur], (const T*)src_pos, (const T*)src_vel, h->cap,
+        auto kern = ho.enabled ? k_resort<T, D, G, true> : k_resort<T, D, G, false>;
+        AB_CUDA(h, ab_launch_chain(h->pdl, kern, dim3((a.ntiles + RS_WARPS - 1) / RS_WARPS), dim3(RS_THREADS), h->stream,
+            sp, a, ho, h->cell_start, h->newkey, h->id[cur], (const T*)src_pos, (const T*)src_vel, h->cap,
             (T*)h->fields[0].buf[nxt], (T*)h->fields[1].buf[nxt], h->id[nxt], h->key[nxt], h->cell_count, h->tile_base,
             h->cell_start_alt, extra ? h->perm : nullptr, (T*)h->cell_agg, (int64_t)h->ncells, h->d_err));
     }
