@@ -329,6 +329,15 @@ k_flock_fine(const __grid_constant__ SpaceDev<T, D> sp, const __grid_constant__ 
             else sweep_t(jb, je, wrap, std::true_type{});
         };
         constexpr int NROW = (EXACT || REACH2) ? 5 : 3; // fine rows per z-slab: 2R+1
+        // REACH2 (2-D quarter cells): every row is trimmed to the cells that can hold a partner closer than
+        // `separation` — a superset of the disc, from the bird's offset inside its quarter cell in f32 with a margin
+        float tq_h = 0.f, tq_x = 0.f, tq_y = 0.f, tq_s = 0.f;
+        if (REACH2) {
+            tq_h = (float)sp.spacing * 0.25f;
+            tq_x = (float)(p[0] - (sp.spacing * T(0.25)) * (T)f[0]);
+            tq_y = (float)(p[D - 1] - (sp.spacing * T(0.25)) * (T)gf_last);
+            tq_s = (float)fp.separation * 1.00001f + 1e-4f * tq_h;
+        }
         for (int rz = (D == 3 ? -R : 0); rz <= (D == 3 ? R : 0); ++rz) {
             int fz = 0, wz = 0, dz = 0;
             if (D == 3) {
@@ -353,6 +362,13 @@ k_flock_fine(const __grid_constant__ SpaceDev<T, D> sp, const __grid_constant__ 
                 int fy = f[1] + ry;
                 const int dy = (fy >> kb) - c[1];
                 int ulo = f[0] - R, uhi = f[0] + R;          // inclusive fine cells, unwrapped
+                if (REACH2) {
+                    const float dym = ry > 0 ? (float)ry * tq_h - tq_y : (ry < 0 ? tq_y + (float)(-ry - 1) * tq_h : 0.f);
+                    if (dym >= tq_s) continue;               // the whole row is farther than `separation`
+                    const float wq = sqrtf(tq_s * tq_s - fmaxf(dym, 0.f) * fmaxf(dym, 0.f));
+                    ulo = f[0] + max((int)floorf((tq_x - wq) / tq_h), -R);
+                    uhi = f[0] + min((int)floorf((tq_x + wq) / tq_h), R);
+                }
                 if (EXACT) {
                     // only cells of the bird's offset table (Σβ² ≤ grid_r²)
                     const int rem2 = gr * gr - dy * dy - dz * dz;
