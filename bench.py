@@ -338,7 +338,7 @@ def config_rows(ab, lib, local, peak, scale=1.0):
                            model_step=ab.SchellingRule(min_to_be_happy=3, relocate=relocate, seed=42), device=local)
         m.add_agents(pos, group=group, mood=np.zeros(n, dtype=np.uint8))
         rows.append(timed_row(lib, m, "SCH-8192 " + ("full step (happiness + relocation)" if relocate else "happiness pass (nearby_ids radius 1)"),
-                              n, 10, 3, ALG_BYTES["schelling"], local, peak))
+                              n, 20, 5, ALG_BYTES["schelling"], local, peak))
         m.close()
     del pos, group, perm
 
