@@ -535,6 +535,7 @@ int ab_create(ab_space_desc* desc, int device, ab_handle** out) {
     if (const char* e = getenv("AB_PDL")) h->pdl = atoi(e) != 0;
     if (const char* e = getenv("AB_FINE4")) h->fine4 = atoi(e) != 0;     // A/B experiments
     if (const char* e = getenv("AB_SMALL_SCAN")) h->small_scan = atoi(e) != 0;
+    if (const char* e = getenv("AB_CELLM_OLD")) h->cellm_old = atoi(e) != 0;
     if (const char* e = getenv("AB_RS_TARGET")) { int v = atoi(e); if (v >= 4 && v <= 2048) h->rs_target = v; }   // tuning experiments
     h->D = desc->D;
     int64_t ncells = 1;
@@ -621,7 +622,7 @@ int ab_destroy(ab_handle* h) {
     free_population(h);
     void* ptrs[] = {h->cell_count, h->cell_start, h->scan_status, h->scan_ticket, h->d_err, h->scratch, h->scratch2,
                     h->cell_agg, h->cell_agg1, h->cell_M, h->pairs_offsets, h->grid_ids, h->cell_start_alt, h->step_mask,
-                    h->tile_count, h->tile_base};
+                    h->tile_count, h->tile_base, h->row_count};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (h->h_err) cudaFreeHost(h->h_err);
     if (h->ev0) cudaEventDestroy(h->ev0);

@@ -445,6 +445,22 @@ static int launch_cell_M(ab_handle* h, const SpaceDev<T, D>& sp, int part = 0) {
         nfr = 1;
     }
     AB_LAUNCH(h, "k_cell_M");
+    if constexpr (D == 2) {
+        if (!h->cellm_old) {
+            // rolling window: 4 output rows per warp when every row is launched, single rows for the row subsets of
+            // the overlapped sharded step (same association: bitwise equal)
+            if (part == 0) {
+                const int64_t nw = (int64_t)((rows + 3) / 4) * wpr;
+                AB_CUDA(h, ab_launch_chain(h->pdl, k_cell_M2<T, 4>, dim3(ab_blocks(nw * 32, 128)), dim3(128), h->stream, sp, aggp,
+                                           (int64_t)h->ncells, wpr, (int)nw, (T*)h->cell_M, 0x7fffffff, 0, nfr, rows));
+            } else {
+                const int64_t nw = (int64_t)rows * wpr;
+                AB_CUDA(h, ab_launch_chain(h->pdl, k_cell_M2<T, 1>, dim3(ab_blocks(nw * 32, 128)), dim3(128), h->stream, sp, aggp,
+                                           (int64_t)h->ncells, wpr, (int)nw, (T*)h->cell_M, skip0, skiplen, nfr, rows));
+            }
+            return AB_OK;
+        }
+    }
     const int64_t nwarps = (int64_t)rows * wpr;
     AB_CUDA(h, ab_launch_chain(h->pdl, k_cell_M<T, D>, dim3(ab_blocks(nwarps * 32, 128)), dim3(128), h->stream, sp, aggp,
                                (int64_t)h->ncells, wpr, (int)nwarps, (T*)h->cell_M, skip0, skiplen, nfr));

@@ -169,6 +169,99 @@ k_cell_M(SpaceDev<T, D> sp, const T* __restrict__ aggp, int64_t ncells, int wpr,
     }
 }
 
+// 2-D variant with a rolling window: a warp produces R consecutive cell rows of one 28-cell strip.  Every input row
+// is loaded ONCE per warp; its 3-wide and 5-wide horizontal sums (H1, H2) are built once with four shuffles per
+// component and serve all the output rows the input row belongs to:
+//     M1(y) = (A(y-1) + H1(y)) + A(y+1)          M2(y) = (((A(y-2) + H1(y-1)) + H2(y)) + H1(y+1)) + A(y+2)
+// with H1 = (a[x-1] + a[x]) + a[x+1], H2 = (a[x-2] + H1) + a[x+2].  The association is the same for every R, so
+// launches with different R (whole grid: R = 4; row subsets of the overlapped sharded step: R = 1) agree bit for bit.
+template <class T, int R>
+__global__ void __launch_bounds__(128)
+k_cell_M2(SpaceDev<T, 2> sp, const T* __restrict__ aggp, int64_t ncells, int wpr, int nwarps, T* __restrict__ M,
+          int skip0, int skiplen, int nfr, int nrows_launch) {
+    constexpr int NC = 5;
+    ab_dep_wait();
+    const int warp = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    if (warp >= nwarps) return;
+    const int lane = threadIdx.x & 31;
+    const int rb = warp / wpr, seg = warp - rb * wpr;
+    const int r0_ = rb * R;                                           // first launched row of this warp
+    const int row0 = r0_ < skip0 ? r0_ : r0_ + skiplen;               // R > 1 is only launched with skiplen == 0
+    const int xout = seg * CM_OUT + lane - 2;
+    const int xl = xout > sp.dims[0] + 1 ? -1 : wrap_coord(xout, sp.dims[0], sp.periodic[0]);
+    T acc1[R][NC], acc2[R][NC];
+    int c1x[R], c1y[R], c2x[R], c2y[R];
+#pragma unroll
+    for (int j = 0; j < R; ++j) {
+        c1x[j] = c1y[j] = c2x[j] = c2y[j] = 0;
+#pragma unroll
+        for (int i = 0; i < NC; ++i) acc1[j][i] = acc2[j][i] = T(0);
+    }
+#pragma unroll
+    for (int k = 0; k < R + 4; ++k) {
+        const int y = wrap_coord(row0 - 2 + k, sp.dims[1], sp.periodic[1]);
+        T a[NC], h1[NC], h2[NC];
+#pragma unroll
+        for (int i = 0; i < NC; ++i) a[i] = T(0);
+        if (y >= 0 && xl >= 0) {
+            const size_t nb = (size_t)(uint32_t)y * (uint32_t)sp.dims[0] + (uint32_t)xl;
+#pragma unroll
+            for (int i = 0; i < NC; ++i) {
+                T v = aggp[(size_t)i * ncells + nb];
+                if (nfr >= 2) v += aggp[((size_t)NC + i) * ncells + nb];
+                if (nfr == 4) {
+                    v += aggp[((size_t)2 * NC + i) * ncells + nb];
+                    v += aggp[((size_t)3 * NC + i) * ncells + nb];
+                }
+                a[i] = v;
+            }
+        }
+        int cl1, cr1, cl2, cr2;
+#pragma unroll
+        for (int i = 0; i < NC; ++i) {
+            const T l1 = shfl_T(a[i], lane - 1), r1 = shfl_T(a[i], lane + 1);
+            const T l2 = shfl_T(a[i], lane - 2), r2 = shfl_T(a[i], lane + 2);
+            h1[i] = (l1 + a[i]) + r1;
+            h2[i] = (l2 + h1[i]) + r2;
+            if (i == 0) { cl1 = (int)l1; cr1 = (int)r1; cl2 = (int)l2; cr2 = (int)r2; }
+        }
+        const int ca = (int)a[0], n1 = cl1 + ca + cr1;
+        const int cx1 = cr1 - cl1, cx2 = cx1 + 2 * (cr2 - cl2);
+#pragma unroll
+        for (int j = 0; j < R; ++j) {
+            const int dy = k - 2 - j;                                  // input row relative to output row j (compile time)
+            if (dy == -2 || dy == 2) {
+#pragma unroll
+                for (int i = 0; i < NC; ++i) acc2[j][i] += a[i];
+                c2y[j] += dy * ca;
+            } else if (dy == -1 || dy == 1) {
+#pragma unroll
+                for (int i = 0; i < NC; ++i) { acc2[j][i] += h1[i]; acc1[j][i] += a[i]; }
+                c2x[j] += cx1; c2y[j] += dy * n1; c1y[j] += dy * ca;
+            } else if (dy == 0) {
+#pragma unroll
+                for (int i = 0; i < NC; ++i) { acc2[j][i] += h2[i]; acc1[j][i] += h1[i]; }
+                c2x[j] += cx2; c1x[j] += cx1;
+            }
+        }
+    }
+    if (lane >= 2 && lane < 2 + CM_OUT && xout < sp.dims[0]) {
+#pragma unroll
+        for (int j = 0; j < R; ++j) {
+            if (r0_ + j >= nrows_launch) break;
+            const int cy = row0 + j;
+            const size_t cell = (size_t)(uint32_t)cy * (uint32_t)sp.dims[0] + (uint32_t)xout;
+            acc1[j][1] += (T)c1x[j] * sp.spacing; acc1[j][2] += (T)c1y[j] * sp.spacing;
+            acc2[j][1] += (T)c2x[j] * sp.spacing; acc2[j][2] += (T)c2y[j] * sp.spacing;
+#pragma unroll
+            for (int i = 0; i < NC; ++i) {
+                M[(size_t)i * ncells + cell] = acc1[j][i];
+                M[((size_t)NC + i) * ncells + cell] = acc2[j][i];
+            }
+        }
+    }
+}
+
 // grid_r (continuous.jl:221-225) when the plan guarantees it is 1 or 2: ceil((r + δ)/spacing) is 1 iff
 // δ <= spacing - r and 2 iff δ <= 2 spacing - r, so δ² is compared with the squared thresholds; a bird
 // whose δ² lies within 1e-9 (relative) of a threshold takes the reference arithmetic instead.

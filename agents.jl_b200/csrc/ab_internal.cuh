@@ -129,9 +129,16 @@ struct ab_handle {
     // the new cell_start (there is no scan over the fine cells on this path)
     int rs_tw = 0, rs_tpr = 0, rs_ntiles = 0, rs_nrows = 0;
     uint32_t rs_magic = 0;             // ceil(2^32 / rs_tw): fx / tw == umulhi(fx, magic) for fx < 65536
-    uint32_t* tile_count = nullptr;    // rs_ntiles (padded to the scan tile; zero between uses)
-    uint32_t* tile_base = nullptr;     // rs_ntiles + 1
+    uint32_t* tile_count = nullptr;    // [2 parities][tile_cap]: rs_ntiles entries each (zero between uses)
+    uint32_t* tile_base = nullptr;     // rs_ntiles + 1 (scan path only)
     size_t tile_cap = 0;
+    // scan-free path (few fine rows: 2-D spaces): the step kernels also count per fine ROW; a re-sort tile sums the
+    // rows before its own and the tiles before it in its row — no scan launch at all.  The counters alternate by
+    // parity: step t accumulates into [t & 1], re-sort t reads them and zeroes the other half behind the previous one.
+    uint32_t* row_count = nullptr;     // [2][row_cap]
+    size_t row_cap = 0;
+    bool rs_scanfree = false;
+    int rs_par = 0;
 
     // single-pass scan state
     unsigned long long* scan_status = nullptr;
@@ -169,6 +176,7 @@ struct ab_handle {
     uint64_t sch_tick = 0;             // steps taken so far (decorrelates the per-step permutations)
 
     ab_comm* comm = nullptr;
+    bool cellm_old = false;            // AB_CELLM_OLD=1: the one-row-per-warp k_cell_M in 2-D too (A/B experiments)
     bool small_scan = false;           // AB_SMALL_SCAN=1: single-CTA scan of the tile totals (A/B experiments)
     bool halo_packed = false;          // the re-sort of this step already delivered the boundary messages
     // slab window along the last axis (multi-GPU, ab_comm.cu); W == 0: the handle holds the whole space
@@ -300,24 +308,35 @@ __device__ __forceinline__ void ab_dep_wait() {
 struct TileGeo {
     uint32_t* cell_count;
     uint32_t* tile_count;
+    uint32_t* row_count;      // nullptr: the tile totals are scanned (many fine rows)
     uint32_t tpr, magic, nrows;
 };
 static inline TileGeo make_tilegeo(const ab_handle* h) {
     TileGeo g;
-    g.cell_count = h->cell_count; g.tile_count = h->tile_count;
+    g.cell_count = h->cell_count;
+    g.tile_count = h->tile_count + (size_t)h->rs_par * h->tile_cap;
+    g.row_count = h->rs_scanfree ? h->row_count + (size_t)h->rs_par * h->row_cap : nullptr;
     g.tpr = (uint32_t)h->rs_tpr; g.magic = h->rs_magic; g.nrows = (uint32_t)h->rs_nrows;
     return g;
 }
 #ifdef __CUDACC__
 // one agent's new key: fine row `frow`, fine x `fx` (< 65536).  The tile counter is bumped once per group of lanes
 // that share the tile (lanes of a warp are neighbours in space: one or two groups).
+__device__ __forceinline__ void count_tile(const TileGeo& g, uint32_t frow, uint32_t fx) {
+    const uint32_t tile = frow * g.tpr + __umulhi(fx, g.magic);
+    const unsigned act = __activemask();
+    const unsigned me = 1u << (threadIdx.x & 31);
+    const unsigned m = __match_any_sync(act, tile);
+    if ((m & (0u - m)) == me) atomicAdd(&g.tile_count[tile], (uint32_t)__popc(m));
+    if (g.row_count) {
+        const unsigned mr = __match_any_sync(act, frow);
+        if ((mr & (0u - mr)) == me) atomicAdd(&g.row_count[frow], (uint32_t)__popc(mr));
+    }
+}
 __device__ __forceinline__ void count_new_key(const TileGeo& g, uint32_t key, uint32_t frow, uint32_t fx) {
     if (frow >= g.nrows) return;                              // not re-sorted here (halo rows of a slab window)
     atomicAdd(&g.cell_count[key], 1u);
-    const uint32_t tile = frow * g.tpr + __umulhi(fx, g.magic);
-    const unsigned act = __activemask();
-    const unsigned m = __match_any_sync(act, tile);
-    if ((m & (0u - m)) == (1u << (threadIdx.x & 31))) atomicAdd(&g.tile_count[tile], (uint32_t)__popc(m));
+    count_tile(g, frow, fx);
 }
 #endif
 

@@ -139,9 +139,7 @@ k_pf_fine(SpaceDev<T, D> sp, PfU<T> u, const T* __restrict__ pos, const T* __res
         const uint32_t fr0 = k0 / (uint32_t)sp.dims[0];
         if (fr0 >= tg.nrows) return;
         rank[s] = atomicAdd(&tg.cell_count[k0], 1u);
-        const uint32_t tile = fr0 * tg.tpr + __umulhi(k0 - fr0 * (uint32_t)sp.dims[0], tg.magic);
-        const unsigned m = __match_any_sync(__activemask(), tile);
-        if ((m & (0u - m)) == (1u << (threadIdx.x & 31))) atomicAdd(&tg.tile_count[tile], (uint32_t)__popc(m));
+        count_tile(tg, fr0, k0 - fr0 * (uint32_t)sp.dims[0]);
         return;
     }
     const T ri = rad[s], ki = kk[s], mi = mass[s];
@@ -258,11 +256,7 @@ k_pf_fine(SpaceDev<T, D> sp, PfU<T> u, const T* __restrict__ pos, const T* __res
     // arrival rank (used only when the step falls back to the generic re-index) + per-tile histogram of the tiled re-sort
     if (nfrow >= tg.nrows) return;                           // a row this handle does not re-sort (halo rows of a slab window)
     rank[s] = atomicAdd(&tg.cell_count[nk], 1u);
-    {
-        const uint32_t tile = nfrow * tg.tpr + __umulhi(nk - nfrow * (uint32_t)sp.dims[0], tg.magic);
-        const unsigned m = __match_any_sync(__activemask(), tile);
-        if ((m & (0u - m)) == (1u << (threadIdx.x & 31))) atomicAdd(&tg.tile_count[tile], (uint32_t)__popc(m));
-    }
+    count_tile(tg, nfrow, nk - nfrow * (uint32_t)sp.dims[0]);
 }
 
 // generic path, kernel 1: own force into fown, one-sided reactions into freact (atomics)
@@ -388,7 +382,9 @@ static int pf_steps_t(ab_handle* h, const ab_pairforce_params* p, int64_t nsteps
             AB_CUDA(h, cudaStreamSynchronize(h->stream));
             if (h->h_err[1]) {
                 AB_CUDA(h, cudaMemsetAsync(h->d_err + 1, 0, sizeof(int), h->stream));
-                AB_CUDA(h, cudaMemsetAsync(h->tile_count, 0, (size_t)h->rs_ntiles * sizeof(uint32_t), h->stream));   // not consumed by a tiled re-sort
+                // the per-tile / per-row histograms are not consumed by a tiled re-sort this time
+                AB_CUDA(h, cudaMemsetAsync(h->tile_count, 0, 2 * h->tile_cap * sizeof(uint32_t), h->stream));
+                if (h->row_count) AB_CUDA(h, cudaMemsetAsync(h->row_count, 0, 2 * h->row_cap * sizeof(uint32_t), h->stream));
                 AB_TRY(ab_reindex_from(h, h->tmp_pos, h->tmp_vel, true));
             } else {
                 AB_TRY(ab_resort_tiled(h, h->tmp_pos, h->tmp_vel, false));

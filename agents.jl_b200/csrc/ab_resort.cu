@@ -38,6 +38,9 @@
 //
 // Nothing here is specific to the flock rule: any fused rule that bounds the
 // per-step displacement by one fine cell can use it.
+#include <algorithm>
+#include <cstdlib>
+
 #include "ab_internal.cuh"
 
 #define RS_WARPS 4
@@ -49,6 +52,11 @@
 struct ResortArgs {
     int tw, tpr, ntiles, nrows;
     int has_vel, want_agg;
+    int scanfree;                    // tile bases from the per-row / per-tile counters instead of a scanned array
+    const uint32_t* tile_cnt;        // this step's counters (scan-free path)
+    const uint32_t* row_cnt;
+    uint32_t* tile_other;            // the other parity: consumed by the previous re-sort, zeroed here
+    uint32_t* row_other;
 };
 
 #ifdef RS_MINB
@@ -110,8 +118,19 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const __grid_constant__ HaloOut ho, co
 #pragma unroll
         for (int dir = 0; dir < 2; ++dir) {
             if (!reg[dir]) continue;
-            s0[dir] = tile_base[t0b[dir]];
-            const uint32_t cnt = tile_base[t1b[dir]] - s0[dir];
+            uint32_t cnt;
+            if (a.scanfree) {
+                uint32_t part0 = 0, part1 = 0;                      // rows before the region / rows of the region
+                const int ra = dir == 0 ? 0 : a.nrows - nb, rb = dir == 0 ? nb : a.nrows;
+                for (int r = lane; r < rb; r += 32) { const uint32_t v = a.row_cnt[r]; if (r < ra) part0 += v; else part1 += v; }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) { part0 += __shfl_xor_sync(FULL, part0, o); part1 += __shfl_xor_sync(FULL, part1, o); }
+                s0[dir] = part0;
+                cnt = part1;
+            } else {
+                s0[dir] = tile_base[t0b[dir]];
+                cnt = tile_base[t1b[dir]] - s0[dir];
+            }
             cntc[dir] = min(cnt, (uint32_t)ho.m.C);
             if (tile == t0b[dir] && lane == 0) {                   // the region's first tile: header (and the capacity check)
                 uint32_t* hdr = reinterpret_cast<uint32_t*>(ho.buf[dir]);
@@ -129,8 +148,28 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const __grid_constant__ HaloOut ho, co
     const uint32_t kend = kbeg + (uint32_t)fc;
     const int fy0 = D == 2 ? frow : frow % fd1;
     const int fz0 = D == 2 ? 0 : frow / fd1;
-    const uint32_t base = tile_base[tile];
-    const uint32_t total = tile_base[tile + 1] - base;
+    // sum of the row counters [r0, r1) over the warp (scan-free path)
+    auto rows_sum = [&](int r0, int r1) -> uint32_t {
+        uint32_t part = 0;
+        for (int r = r0 + lane; r < r1; r += 32) part += a.row_cnt[r];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(FULL, part, o);
+        return part;
+    };
+    uint32_t base, total;
+    if (a.scanfree) {
+        // agents in the fine rows before mine + in the tiles before me in my row
+        uint32_t part = 0;
+        for (int t = lane; t < seg_x; t += 32) part += a.tile_cnt[frow * a.tpr + t];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(FULL, part, o);
+        base = rows_sum(0, frow) + part;
+        total = a.tile_cnt[tile];
+        if (lane == 0) { a.tile_other[tile] = 0; if (seg_x == 0) a.row_other[frow] = 0; }
+    } else {
+        base = tile_base[tile];
+        total = tile_base[tile + 1] - base;
+    }
     if (tile == a.ntiles - 1 && lane == 0) cs_new[kend] = base + total;      // end of the re-sorted key range
     bool lost = false;
 
@@ -508,17 +547,31 @@ int ab_resort_plan(ab_handle* h) {
     const int64_t ntiles = nrows * tpr;
     if (ntiles > 0x7fffffffLL) return ab_fail(h, AB_ERR_INVALID, "too many re-sort tiles");
     const size_t need = ((size_t)ntiles + SCAN_TILE - 1) / SCAN_TILE * SCAN_TILE;
-    if (need > h->tile_cap) {
+    const size_t need_rows = ((size_t)nrows + 63) / 64 * 64;
+    // few fine rows (2-D spaces): no scan launch — the re-sort tiles sum the per-row and per-tile counters themselves
+    bool scanfree = nrows <= 4096 && tpr <= 4096;
+    if (const char* e = getenv("AB_SCANFREE")) scanfree = scanfree && atoi(e) != 0;
+    const bool changed = tw != h->rs_tw || tpr != h->rs_tpr || (int)nrows != h->rs_nrows || scanfree != h->rs_scanfree;
+    if (need > h->tile_cap || need_rows > h->row_cap) {
         AB_CUDA(h, cudaStreamSynchronize(h->stream));
         if (h->tile_count) AB_CUDA(h, cudaFree(h->tile_count));
         if (h->tile_base) AB_CUDA(h, cudaFree(h->tile_base));
-        h->tile_count = h->tile_base = nullptr;
-        AB_CUDA(h, cudaMalloc((void**)&h->tile_count, need * sizeof(uint32_t)));
-        AB_CUDA(h, cudaMalloc((void**)&h->tile_base, (need + 1) * sizeof(uint32_t)));
-        AB_CUDA(h, cudaMemsetAsync(h->tile_count, 0, need * sizeof(uint32_t), h->stream));
-        h->tile_cap = need;
-        if (need / SCAN_TILE + 1 > h->scan_status_len) return ab_fail(h, AB_ERR_INVALID, "tile scan larger than the handle's status buffer");
+        if (h->row_count) AB_CUDA(h, cudaFree(h->row_count));
+        h->tile_count = h->tile_base = h->row_count = nullptr;
+        h->tile_cap = std::max(need, h->tile_cap);
+        h->row_cap = std::max(need_rows, h->row_cap);
+        AB_CUDA(h, cudaMalloc((void**)&h->tile_count, 2 * h->tile_cap * sizeof(uint32_t)));
+        AB_CUDA(h, cudaMalloc((void**)&h->tile_base, (h->tile_cap + 1) * sizeof(uint32_t)));
+        AB_CUDA(h, cudaMalloc((void**)&h->row_count, 2 * h->row_cap * sizeof(uint32_t)));
+        if (h->tile_cap / SCAN_TILE + 1 > h->scan_status_len) return ab_fail(h, AB_ERR_INVALID, "tile scan larger than the handle's status buffer");
     }
+    if (changed || !h->rs_ntiles) {
+        // a new geometry: both halves of the counters start from zero (stream order: after everything queued so far)
+        AB_CUDA(h, cudaMemsetAsync(h->tile_count, 0, 2 * h->tile_cap * sizeof(uint32_t), h->stream));
+        AB_CUDA(h, cudaMemsetAsync(h->row_count, 0, 2 * h->row_cap * sizeof(uint32_t), h->stream));
+        h->rs_par = 0;
+    }
+    h->rs_scanfree = scanfree;
     h->rs_tw = tw; h->rs_tpr = tpr; h->rs_nrows = (int)nrows; h->rs_ntiles = (int)ntiles;
     h->rs_magic = (uint32_t)((0x100000000ULL + (uint64_t)tw - 1) / (uint64_t)tw);
     return AB_OK;
@@ -533,9 +586,15 @@ static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool
     if (a.ntiles <= 0 || a.tw <= 0) return ab_fail(h, AB_ERR_STATE, "ab_resort_plan must precede the step kernel");
     a.has_vel = h->desc.kind == AB_SPACE_CONTINUOUS;
     a.want_agg = want_agg ? 1 : 0;
-    // the step kernel has counted the new keys per fine cell and per tile: scan the tile totals; every tile turns
-    // its own cell counts into its slice of the new cell_start
-    AB_TRY(ab_scan_u32(h, h->tile_count, h->tile_base, (uint32_t)a.ntiles));
+    // the step kernel has counted the new keys per fine cell, per tile (and per fine row): every tile finds its output
+    // range from those (scan-free path) or from the scanned tile totals, and turns its own cell counts into its slice
+    // of the new cell_start
+    a.scanfree = h->rs_scanfree ? 1 : 0;
+    a.tile_cnt = h->tile_count + (size_t)h->rs_par * h->tile_cap;
+    a.row_cnt = h->row_count + (size_t)h->rs_par * h->row_cap;
+    a.tile_other = h->tile_count + (size_t)(h->rs_par ^ 1) * h->tile_cap;
+    a.row_other = h->row_count + (size_t)(h->rs_par ^ 1) * h->row_cap;
+    if (!h->rs_scanfree) AB_TRY(ab_scan_u32(h, h->tile_count, h->tile_base, (uint32_t)a.ntiles));
     if (want_agg) AB_TRY(ensure_agg(h));
     const bool extra = h->fields.size() > 2u;
     // slab window: the boundary tiles deliver the neighbours' messages while they place their agents
@@ -552,6 +611,7 @@ static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool
             (T*)h->fields[0].buf[nxt], (T*)h->fields[1].buf[nxt], h->id[nxt], h->key[nxt], h->cell_count, h->tile_base,
             h->cell_start_alt, extra ? h->perm : nullptr, (T*)h->cell_agg, (int64_t)h->ncells, h->d_err));
     }
+    if (h->rs_scanfree) h->rs_par ^= 1;                // the next step accumulates into the other half
     std::swap(h->cell_start, h->cell_start_alt);
     AB_TRY(ab_permute_extra_fields(h, true));
     h->cur = nxt;
