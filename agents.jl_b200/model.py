@@ -39,15 +39,27 @@ class ContinuousSpace:
     kind = L.SPACE_CONTINUOUS
 
     def __init__(self, extent, spacing=None, periodic=True, dtype=np.float64):
-        self.D = len(extent)
+        self.user_D = len(extent)
         self.extent = tuple(float(x) for x in extent)
         self.spacing = float(min(self.extent) / 20.0 if spacing is None else spacing)
-        self.periodic = _periodic(periodic, self.D)
-        self.dtype = np.dtype(dtype)
+        self.periodic = _periodic(periodic, self.user_D)
+        # Float16 agents (test/continuous_space_tests.jl:606-637): the device computes and stores them in Float32 (every
+        # Float16 is a Float32); columns are rounded to Float16 when they are read back.  The reference rounds after every
+        # operation instead: identical for one operation per read-back (a move_agent!, a walk!), last-digit differences
+        # for longer chains.
+        self.user_dtype = np.dtype(dtype)
+        self.dtype = np.dtype(np.float32) if self.user_dtype == np.float16 else self.user_dtype
         if self.dtype not in (np.dtype(np.float64), np.dtype(np.float32)):
-            raise TypeError("eltype must be Float64 or Float32 on the device")
+            raise TypeError("eltype must be Float64, Float32 or Float16")
         self.metric = "euclidean"
         self.dims = None
+        # A 1-D space is embedded in a 2-D one: a single non-periodic row of cells of height `spacing`, every agent at
+        # mid-height with zero velocity in the second coordinate.  Distances, cells (first coordinate), grid_r and the
+        # cells of the offset tables are those of the 1-D space (the second coordinate contributes exactly 0).
+        self.D = max(self.user_D, 2)
+        if self.user_D == 1:
+            self.extent = (self.extent[0], self.spacing)
+            self.periodic = (self.periodic[0], False)
 
     def _desc(self):
         d = L.SpaceDesc()
@@ -206,6 +218,26 @@ class StandardABM:
     def _ptr(a):
         return a.ctypes.data_as(C.c_void_p) if a is not None else None
 
+    # -- 1-D spaces embedded in 2-D, Float16 columns held as Float32 (ContinuousSpace docstring) --------------
+    def _rows_in(self, a, fill=0.0):
+        """caller's (n, user_D) rows -> the device's (n, D) rows of the device float type."""
+        sp = self.space
+        ud = getattr(sp, "user_D", self.D)
+        a = np.asarray(a, dtype=sp.dtype).reshape(-1, ud)
+        if ud == self.D:
+            return np.ascontiguousarray(a)
+        out = np.full((a.shape[0], self.D), fill, dtype=sp.dtype)
+        out[:, :ud] = a
+        return out
+
+    def _rows_out(self, a):
+        sp = self.space
+        ud = getattr(sp, "user_D", self.D)
+        if ud != self.D:
+            a = a[:, :ud]
+        udt = getattr(sp, "user_dtype", a.dtype)
+        return a.astype(udt) if udt != a.dtype else a
+
     # -- population (add_agent! at setup; src/core/space_interaction_API.jl:174-179) ----
     def nagents(self):
         return int(self.lib.ab_nagents(self.h))
@@ -218,12 +250,15 @@ class StandardABM:
     def add_agents(self, pos, vel=None, **columns):
         """Bulk add_agent!: ids 1..n in the given order; replaces the population."""
         dt = self.space.dtype
-        pos = np.ascontiguousarray(pos, dtype=dt).reshape(-1, self.D)
+        if self.space.kind == L.SPACE_CONTINUOUS:
+            pos = self._rows_in(pos, fill=0.5 * self.space.spacing)
+        else:
+            pos = np.ascontiguousarray(pos, dtype=dt).reshape(-1, self.D)
         n = pos.shape[0]
         self._ck(self.lib.ab_resize(self.h, n))
         self._ck(self.lib.ab_upload(self.h, 0, self._ptr(pos), n))
         if "vel" in self._columns:
-            v = np.zeros((n, self.D), dtype=dt) if vel is None else np.ascontiguousarray(vel, dtype=dt).reshape(n, self.D)
+            v = np.zeros((n, self.D), dtype=dt) if vel is None else self._rows_in(vel)
             self._ck(self.lib.ab_upload(self.h, 1, self._ptr(v), n))
         for name, col in columns.items():
             self.add_column(name, col)
@@ -259,11 +294,12 @@ class StandardABM:
 
     @property
     def pos(self):
-        return self.column("pos")
+        p = self.column("pos")
+        return self._rows_out(p) if self.space.kind == L.SPACE_CONTINUOUS else p
 
     @property
     def vel(self):
-        return self.column("vel")
+        return self._rows_out(self.column("vel"))
 
     def set_refinement(self, K):
         """Device-grid refinement (1 or 2 sub-cells per reference cell and dimension); results do not depend on it."""
@@ -274,7 +310,7 @@ class StandardABM:
         n = self.nagents()
         out = np.zeros((n, self.D), dtype=np.int32)
         self._ck(self.lib.ab_cells(self.h, self._ptr(out), n))
-        return out
+        return out[:, : getattr(self.space, "user_D", self.D)]
 
     # -- neighbour queries ---------------------------------------------------
     def nearby_ids_batch(self, positions=None, ids=None, r=1.0, search="approximate", exclude_self=True):
@@ -284,7 +320,10 @@ class StandardABM:
         if search not in L.SEARCH:
             raise AgentsError(L.ERR_INVALID, "`search` keyword should be either `:approximate` or `:exact`")
         if positions is not None:
-            q = np.ascontiguousarray(positions, dtype=self.space.dtype).reshape(-1, self.D)
+            if self.space.kind == L.SPACE_CONTINUOUS:
+                q = self._rows_in(positions, fill=0.5 * self.space.spacing)
+            else:
+                q = np.ascontiguousarray(positions, dtype=self.space.dtype).reshape(-1, self.D)
             nq, qp, qi = q.shape[0], self._ptr(q), None
         else:
             q = np.ascontiguousarray(ids, dtype=np.int64).reshape(-1)
@@ -416,7 +455,10 @@ class StandardABM:
     def walk(self, directions, ids=None, ifempty=True):
         """walk!(agent, direction, model) — walk.jl:33-66."""
         dt = self.space.dtype
-        d = np.ascontiguousarray(directions, dtype=dt).reshape(-1, self.D)
+        if self.space.kind == L.SPACE_CONTINUOUS:
+            d = self._rows_in(directions)
+        else:
+            d = np.ascontiguousarray(directions, dtype=dt).reshape(-1, self.D)
         a = np.ascontiguousarray(ids, dtype=np.int64) if ids is not None else None
         if d.shape[0] != (self.nagents() if a is None else a.shape[0]):
             raise AgentsError(L.ERR_INVALID, "walk!: one direction per walking agent")
@@ -444,6 +486,8 @@ class StandardABM:
         """randomwalk!(agent, model, r; ifempty, force_motion) for `ids` (all agents when None) — walk.jl:154-214 on
         grids (r defaults to 1), walk.jl:389-408 on a ContinuousSpace (r defaults to the agent's speed).  `seed`
         selects the counter stream of this call (see ab_randomwalk in include/agents_b200.h)."""
+        if getattr(self.space, "user_D", self.D) == 1:
+            raise AgentsError(L.ERR_INVALID, "randomwalk! on an embedded 1-D ContinuousSpace is not built (the device draws D = 2 normals)")
         if r is None:
             r = -1.0 if isinstance(self.space, ContinuousSpace) else 1.0
         elif isinstance(self.space, ContinuousSpace) and r <= 0:
