@@ -104,6 +104,7 @@ _SIGS = {
     "ab_comm_set_capacity": (C.c_int, [_H, C.c_int64]),
     "ab_comm_ipc_export": (C.c_int, [_H, C.c_void_p]),
     "ab_comm_ipc_import": (C.c_int, [_H, C.c_void_p, C.c_void_p]),
+    "ab_index_canonical": (C.c_int, [_H]),
     "ab_comm_direct": (C.c_int, [_H]),
     "ab_comm_align": (C.c_int, [_H]),
     "ab_comm_exchange": (C.c_int, [_H]),

@@ -278,7 +278,8 @@ __global__ void k_place(const uint32_t* __restrict__ newkey, const uint32_t* __r
                         const int32_t* __restrict__ idtmp, const T* __restrict__ src_pos,
                         const T* __restrict__ src_vel, int64_t cap, int n, T* __restrict__ dst_pos,
                         T* __restrict__ dst_vel, int32_t* __restrict__ id_new, uint32_t* __restrict__ key_new,
-                        int32_t* __restrict__ perm, int32_t* __restrict__ slot_of_id, const int32_t* __restrict__ prio) {
+                        int32_t* __restrict__ perm, int32_t* __restrict__ slot_of_id, const int32_t* __restrict__ prio,
+                        int* __restrict__ noncanon) {
     int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
     const uint32_t k = newkey[s];
@@ -292,7 +293,10 @@ __global__ void k_place(const uint32_t* __restrict__ newkey, const uint32_t* __r
     } else if (e - b <= AB_CANON_MAX) {
         r = 0;
         for (uint32_t t = b; t < e; ++t) r += (idtmp[t] < me) ? 1u : 0u;
-    } else r = rank[s];
+    } else {
+        r = rank[s];                  // arrival order: correct, but not a function of the state alone
+        if (s == 0 || newkey[s - 1] != k) atomicOr(noncanon, 1);      // flagged once per crowded cell or so (ab_index_canonical)
+    }
     const uint32_t dst = b + r;
 #pragma unroll
     for (int d = 0; d < D; ++d) dst_pos[(size_t)d * cap + dst] = src_pos[(size_t)d * cap + s];
@@ -427,11 +431,11 @@ static int reindex_t(ab_handle* h, const void* src_pos, const void* src_vel, boo
                 k_place<T, D, true><<<ab_blocks(n, TB), TB, 0, h->stream>>>(
                     h->newkey, h->rank, h->cell_start, h->id[cur], h->idtmp, (const T*)src_pos, (const T*)src_vel,
                     h->cap, n, (T*)h->fields[0].buf[nxt], (T*)h->fields[1].buf[nxt], h->id[nxt], h->key[nxt],
-                    extra ? h->perm : nullptr, nullptr, h->place_prio);
+                    extra ? h->perm : nullptr, nullptr, h->place_prio, h->d_err + 2);
             else
                 k_place<T, D, false><<<ab_blocks(n, TB), TB, 0, h->stream>>>(
                     h->newkey, h->rank, h->cell_start, h->id[cur], h->idtmp, (const T*)src_pos, nullptr, h->cap, n,
-                    (T*)h->fields[0].buf[nxt], nullptr, h->id[nxt], h->key[nxt], extra ? h->perm : nullptr, nullptr, h->place_prio);
+                    (T*)h->fields[0].buf[nxt], nullptr, h->id[nxt], h->key[nxt], extra ? h->perm : nullptr, nullptr, h->place_prio, h->d_err + 2);
         }
         AB_TRY(ab_permute_extra_fields(h, false));
     }
@@ -861,6 +865,20 @@ int ab_layout_set(ab_handle* h, const int64_t* slot_ids, int64_t n, int32_t refi
     cudaFree(dprio);
     AB_CUDA(h, ce);
     return rc;
+}
+
+// 1 when every index build so far ordered every cell canonically (by id, or by the restored checkpoint order) — the
+// premise of bitwise reproducible runs, N-GPU == 1-GPU equality and bit-for-bit checkpoint resume.  A cell holding
+// more than AB_CANON_MAX (4096) agents at an index BUILD keeps the arrival order of the atomics instead (ranking is
+// O(m^2) per cell); results stay correct within rounding, the flag says the guarantee is gone.  The tiled re-sort of the
+// fused steps is canonical for any occupancy.
+int ab_index_canonical(ab_handle* h) {
+    if (!h) return AB_ERR_INVALID;
+    AB_CUDA(h, cudaSetDevice(h->device));
+    int v = 0;
+    AB_CUDA(h, cudaMemcpyAsync(&v, h->d_err + 2, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    AB_CUDA(h, cudaStreamSynchronize(h->stream));
+    return v ? 0 : 1;
 }
 
 int ab_cells(ab_handle* h, int32_t* out_cells, int64_t n) {

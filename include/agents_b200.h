@@ -144,6 +144,12 @@ int ab_set_refinement(ab_handle* h, int K);
  * ab_layout_set is called after the columns of the restored model have been uploaded; it rebuilds the index with
  * the agents of every cell in the saved order. */
 int ab_layout_get(ab_handle* h, int64_t* slot_ids, int64_t n, int32_t* refinement, int64_t* tick);
+/* 1 while every index build of this handle ordered every cell canonically (by id / by the restored order): the premise
+ * of bitwise reproducible runs, N-GPU == 1-GPU equality and bit-for-bit resume.  0 once a cell held more than 4096
+ * agents at an index BUILD (it keeps the arrival order of the atomics; results stay correct within rounding).  The
+ * reference's `stored_ids` vectors (grid_multi.jl:68-105) are ordered by insertion history, which the device does not
+ * keep. */
+int ab_index_canonical(ab_handle* h);
 int ab_layout_set(ab_handle* h, const int64_t* slot_ids, int64_t n, int32_t refinement, int64_t tick);
 
 /* pos2cell for every agent, id order, n x D int32, 1-based (continuous.jl:112-113) */

@@ -117,3 +117,22 @@ def test_async_mode_pairforce_and_schelling_return_valid_timing():
     assert g.last_step_ms() > 0
     g.set_async(False)
     g.close()
+
+
+def test_index_canonical_flag():
+    """ab_index_canonical: 1 while every cell of every index build was ordered by id; 0 once a cell held more than 4096
+    agents at a build (it keeps arrival order: correct, but not bitwise reproducible — ADVICE round 1)."""
+    extent = (100.0, 100.0)
+    pos, vel = flock_init(20000, extent, 3)
+    m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=5.0), model_step=ab.FlockRule(**FLOCK))
+    m.add_agents(pos, vel)
+    m.step(3)
+    assert m.lib.ab_index_canonical(m.h) == 1
+    m.close()
+    crowd = pos.copy()
+    crowd[:6000] = 52.0 + 0.4 * crowd[:6000] / 100.0            # 6000 agents inside one reference cell
+    m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=5.0), model_step=ab.FlockRule(**FLOCK))
+    m.add_agents(crowd, vel)
+    assert m.lib.ab_index_canonical(m.h) == 0
+    assert len(m.nearby_ids(1, 1.0)) >= 5999                    # still a correct index
+    m.close()
