@@ -264,7 +264,7 @@ k_halo_unpack(SpaceDev<T, D> sp, MsgLayout m, MsgCols xc, uint32_t kown, uint32_
               int32_t* __restrict__ id, uint32_t* __restrict__ key, int64_t cap, const char* __restrict__ buf0,
               const char* __restrict__ buf1, int* __restrict__ err, const uint32_t* wflag0, const uint32_t* wflag1,
               uint32_t epoch, int nbc, int nba, T* __restrict__ agg, int64_t agg_stride, uint32_t halo_cell0,
-              uint32_t cells_per_side, unsigned long long* wait_stat) {
+              uint32_t cells_per_side, unsigned long long* wait_stat, const uint32_t* __restrict__ row_cnt, int nrows) {
     if (wflag0 || wflag1) {
         // direct exchange: both messages were stored into our memory by the neighbours' pack kernels; they
         // never wait for us in return (their pack depends only on their own steps; slots alternate by parity)
@@ -285,7 +285,21 @@ k_halo_unpack(SpaceDev<T, D> sp, MsgLayout m, MsgCols xc, uint32_t kown, uint32_
     // buf0 / buf1 == nullptr: no neighbour on that side (non-periodic last axis, end rank) — its halo layers stay empty
     const uint32_t* h0 = reinterpret_cast<const uint32_t*>(buf0);
     const uint32_t* h1 = reinterpret_cast<const uint32_t*>(buf1);
-    const uint32_t n_own = cs[kown];                     // written by the re-sort of this step; never rewritten here
+    // owned agents after this step's re-sort: the cell_start entry behind the owned keys — or, when this launch runs
+    // CONCURRENTLY with that re-sort (side stream), the sum of the step's per-row counters, complete since the sweep
+    uint32_t n_own;
+    if (row_cnt) {
+        __shared__ uint32_t s_nown;
+        if (threadIdx.x == 0) s_nown = 0;
+        __syncthreads();
+        uint32_t part = 0;
+        for (int r = threadIdx.x; r < nrows; r += blockDim.x) part += row_cnt[r];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+        if ((threadIdx.x & 31) == 0 && part) atomicAdd(&s_nown, part);
+        __syncthreads();
+        n_own = s_nown;
+    } else n_own = cs[kown];
     uint32_t cnt_u = buf0 ? h0[0] : 0u, cnt_l = buf1 ? h1[0] : 0u;
     bool bad = (buf0 && (h0[3] != 0xAB200u || h0[2] != m.ncs)) || (buf1 && (h1[3] != 0xAB200u || h1[2] != m.ncs));
     if ((uint64_t)n_own + cnt_u + cnt_l > (uint64_t)cap) bad = true;       // window does not fit the handle's capacity
@@ -547,7 +561,9 @@ static int unpack_t(ab_handle* h, bool want_agg) {
                                                                c->ipc_on && c->has_upper ? ipc_flag(c->ipc_block, c->ipc_stride, c->cur_par, 0) : nullptr,
                                                                c->ipc_on && c->has_lower ? ipc_flag(c->ipc_block, c->ipc_stride, c->cur_par, 1) : nullptr,
                                                                (uint32_t)c->exchanges, nbc, nba, (T*)h->cell_agg, (int64_t)h->ncells,
-                                                               (uint32_t)(h->win_nl * cpl), (uint32_t)(AB_HALO_W * cpl), c->d_wait);
+                                                               (uint32_t)(h->win_nl * cpl), (uint32_t)(AB_HALO_W * cpl), c->d_wait,
+                                                               h->unpack_rows ? h->row_count + (size_t)(h->rs_par ^ 1) * h->row_cap : nullptr, h->rs_nrows);
+        h->unpack_rows = false;
     }
     return AB_OK;
 }
@@ -563,6 +579,7 @@ int ab_comm_unpack(ab_handle* h, bool want_agg) {
     return h->D == 2 ? unpack_t<float, 2>(h, want_agg) : unpack_t<float, 3>(h, want_agg);
 }
 bool ab_comm_local(const ab_handle* h) { return h->comm && h->comm->linked_local; }
+bool ab_comm_direct_on(const ab_handle* h) { return h->comm && h->comm->ipc_on; }
 
 int ab_comm_refresh_counts(ab_handle* h) {
     ab_comm* c = h->comm;
@@ -755,6 +772,7 @@ int ab_comm_exchange(ab_handle* h) {
     if (ab_comm_local(h)) return ab_fail(h, AB_ERR_STATE, "in-process slabs exchange inside ab_step_flock_group");
     AB_CUDA(h, cudaSetDevice(h->device));
     h->index_valid = false;
+    h->unpack_rows = false;
     AB_TRY(ab_ensure_index(h));
     AB_TRY(ab_comm_pack(h));
     AB_TRY(ab_comm_transfer(h));

@@ -178,6 +178,8 @@ struct ab_handle {
     ab_comm* comm = nullptr;
     bool cellm_old = false;            // AB_CELLM_OLD=1: the one-row-per-warp k_cell_M in 2-D too (A/B experiments)
     bool small_scan = false;           // AB_SMALL_SCAN=1: single-CTA scan of the tile totals (A/B experiments)
+    bool no_side_unpack = false;       // AB_SIDE_UNPACK=0: halo install after the re-sort on the same stream (A/B experiments)
+    bool unpack_rows = false;          // this step's per-row counters give the owned count (set by a scan-free re-sort)
     bool halo_packed = false;          // the re-sort of this step already delivered the boundary messages
     // slab window along the last axis (multi-GPU, ab_comm.cu); W == 0: the handle holds the whole space
     int win_gdl = 0, win_goff = 0, win_nl = 0, win_W = 0;
@@ -243,6 +245,7 @@ int ab_comm_pack(ab_handle* h);
 int ab_comm_transfer(ab_handle* h);
 int ab_comm_unpack(ab_handle* h, bool want_agg);
 bool ab_comm_local(const ab_handle* h);              // linked to in-process peers (ab_comm_link_local)
+bool ab_comm_direct_on(const ab_handle* h);          // boundary messages travel by peer-memory stores + flags
 int ab_comm_refresh_counts(ab_handle* h);            // owned / window agent counts back to the host
 int ab_set_step_mask(ab_handle* h, const int64_t* active_ids, int64_t nactive);   // by-id mask of a scheduled subset -> h->step_mask
 int ab_grid_build(ab_handle* h);

@@ -612,6 +612,7 @@ static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool
             h->cell_start_alt, extra ? h->perm : nullptr, (T*)h->cell_agg, (int64_t)h->ncells, h->d_err));
     }
     if (h->rs_scanfree) h->rs_par ^= 1;                // the next step accumulates into the other half
+    h->unpack_rows = h->rs_scanfree && h->win_W;
     std::swap(h->cell_start, h->cell_start_alt);
     AB_TRY(ab_permute_extra_fields(h, true));
     h->cur = nxt;
