@@ -191,7 +191,7 @@ k_halo_pack(MsgLayout m, MsgCols xc, uint32_t kown, const uint32_t* __restrict__
     const uint32_t s0 = cs[k0], s1 = cs[k0 + m.ncs];
     uint32_t cnt = buf ? s1 - s0 : 0u;
     if (cnt > (uint32_t)m.C) {
-        if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(err, AB_EF_COMM);
+        if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(err, AB_EF_COMM | AB_EF_COMM_CAP);
         cnt = (uint32_t)m.C;
     }
     const uint32_t t0 = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
@@ -252,6 +252,20 @@ __device__ __forceinline__ bool wait_flag(const uint32_t* f, uint32_t epoch) {
     }
 }
 
+// Side-stream install: ONE thread waits for the neighbours' flags, so that the wait occupies one SM and not a CTA on every
+// SM (a grid of spinning CTAs next to the re-sort that must publish the neighbour's flag dead-locked two ranks: the
+// resident spinners kept the SMs from taking the re-sort's CTAs).  k_halo_unpack then finds both flags set.
+__global__ void k_halo_wait(const uint32_t* wflag0, const uint32_t* wflag1, uint32_t epoch, int* __restrict__ err,
+                            unsigned long long* wait_stat) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    unsigned long long t0, t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    const bool ok = (!wflag0 || wait_flag(wflag0, epoch)) && (!wflag1 || wait_flag(wflag1, epoch));
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    if (wait_stat) { atomicAdd(&wait_stat[0], t1 - t0); atomicAdd(&wait_stat[1], 1ull); }
+    if (!ok) atomicOr(err, AB_EF_COMM | AB_EF_COMM_TIMEOUT);
+}
+
 // Installs the received layers as this rank's halo.  Blocks [0, nbc) copy the upper neighbour's bottom layers
 // (keys [kown, kown + ncs)), blocks [nbc, 2 nbc) the lower neighbour's top layers (keys [kown + ncs, kown + 2 ncs)).
 // Halo slots follow the owned ones: [n_own, n_own + cnt_u) and [n_own + cnt_u, n_own + cnt_u + cnt_l).
@@ -278,7 +292,7 @@ k_halo_unpack(SpaceDev<T, D> sp, MsgLayout m, MsgCols xc, uint32_t kown, uint32_
         }
         __syncthreads();
         if (!s_ok) {
-            if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(err, AB_EF_COMM);
+            if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(err, AB_EF_COMM | AB_EF_COMM_TIMEOUT);
             return;
         }
     }
@@ -302,9 +316,10 @@ k_halo_unpack(SpaceDev<T, D> sp, MsgLayout m, MsgCols xc, uint32_t kown, uint32_
     } else n_own = cs[kown];
     uint32_t cnt_u = buf0 ? h0[0] : 0u, cnt_l = buf1 ? h1[0] : 0u;
     bool bad = (buf0 && (h0[3] != 0xAB200u || h0[2] != m.ncs)) || (buf1 && (h1[3] != 0xAB200u || h1[2] != m.ncs));
-    if ((uint64_t)n_own + cnt_u + cnt_l > (uint64_t)cap) bad = true;       // window does not fit the handle's capacity
-    if (bad) {
-        if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(err, AB_EF_COMM);
+    const bool nofit = (uint64_t)n_own + cnt_u + cnt_l > (uint64_t)cap;   // window does not fit the handle's capacity
+    if (bad || nofit) {
+        if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(err, AB_EF_COMM | (bad ? AB_EF_COMM_HDR : 0) | (nofit ? AB_EF_COMM_WINDOW : 0));
+        bad = true;
         cnt_u = cnt_l = 0;
     }
     const bool agg_role = (int)blockIdx.x >= 2 * nbc;
@@ -552,16 +567,22 @@ static int unpack_t(ab_handle* h, bool want_agg) {
         nba = (int)std::min<int64_t>(std::max<int64_t>((AB_HALO_W * cpl * nfr * 8 + 255) / 256, 1), 1184);
         h->agg_epoch++;
     }
+    const uint32_t* wf0 = c->ipc_on && c->has_upper ? ipc_flag(c->ipc_block, c->ipc_stride, c->cur_par, 0) : nullptr;
+    const uint32_t* wf1 = c->ipc_on && c->has_lower ? ipc_flag(c->ipc_block, c->ipc_stride, c->cur_par, 1) : nullptr;
+    const bool prewait = h->unpack_rows && (wf0 || wf1) && h->side_unpack_now;
+    if (prewait) {
+        AB_LAUNCH(h, "k_halo_wait");
+        k_halo_wait<<<1, 32, 0, h->stream>>>(wf0, wf1, (uint32_t)c->exchanges, h->d_err, c->d_wait);
+    }
     {
         AB_LAUNCH(h, "k_halo_unpack");
         k_halo_unpack<T, D><<<dim3(2 * nbc + 2 * nba), 256, 0, h->stream>>>(make_space<T, D>(h), m, msg_cols(h), kown, h->cell_start, (T*)h->fields[0].buf[cur],
                                                                (T*)h->fields[1].buf[cur], h->id[cur], h->key[cur], h->cap,
                                                                !c->has_upper ? nullptr : c->ipc_on ? ipc_slot(c->ipc_block, c->ipc_stride, c->cur_par, 0) : (const char*)c->recvbuf[0],
                                                                !c->has_lower ? nullptr : c->ipc_on ? ipc_slot(c->ipc_block, c->ipc_stride, c->cur_par, 1) : (const char*)c->recvbuf[1], h->d_err,
-                                                               c->ipc_on && c->has_upper ? ipc_flag(c->ipc_block, c->ipc_stride, c->cur_par, 0) : nullptr,
-                                                               c->ipc_on && c->has_lower ? ipc_flag(c->ipc_block, c->ipc_stride, c->cur_par, 1) : nullptr,
+                                                               wf0, wf1,
                                                                (uint32_t)c->exchanges, nbc, nba, (T*)h->cell_agg, (int64_t)h->ncells,
-                                                               (uint32_t)(h->win_nl * cpl), (uint32_t)(AB_HALO_W * cpl), c->d_wait,
+                                                               (uint32_t)(h->win_nl * cpl), (uint32_t)(AB_HALO_W * cpl), prewait ? nullptr : c->d_wait,
                                                                h->unpack_rows ? h->row_count + (size_t)(h->rs_par ^ 1) * h->row_cap : nullptr, h->rs_nrows);
         h->unpack_rows = false;
     }

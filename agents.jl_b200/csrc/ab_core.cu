@@ -111,7 +111,14 @@ int ab_check_device_errors(ab_handle* h) {
     if (e & AB_EF_OUTSIDE) return ab_fail(h, AB_ERR_OUTSIDE, "position is outside space extent!");
     if (e & AB_EF_OCCUPIED) return ab_fail(h, AB_ERR_OCCUPIED, "Cannot add agent to occupied position");
     if (e & AB_EF_ARG) return ab_fail(h, AB_ERR_INVALID, "ArgumentError: The displacement must be larger than 0 (a resting agent has no direction to take it from).");
-    if (e & AB_EF_COMM) return ab_fail(h, AB_ERR_COMM, "halo exchange overflow: more agents in the boundary layers than the message capacity (ab_comm_set_capacity) or than the handle's capacity (ab_resize)");
+    if (e & AB_EF_COMM) {
+        std::string m = "halo exchange failed:";
+        if (e & AB_EF_COMM_CAP) m += " more agents in the boundary layers than the message capacity (ab_comm_set_capacity);";
+        if (e & AB_EF_COMM_WINDOW) m += " owned + halo agents exceed the handle's capacity (ab_resize);";
+        if (e & AB_EF_COMM_HDR) m += " a neighbour's message has a foreign header (ranks disagree on refinement or capacity);";
+        if (e & AB_EF_COMM_TIMEOUT) m += " a neighbour's message did not arrive within 10 s;";
+        return ab_fail(h, AB_ERR_COMM, m);
+    }
     if (e & AB_EF_OVERFLOW) return ab_fail(h, AB_ERR_INVALID, "device-side failure: id out of range, or an agent left its cell neighbourhood in one tiled step");
     return ab_fail(h, AB_ERR_INVALID, "device-side failure");
 }

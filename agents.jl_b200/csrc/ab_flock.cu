@@ -645,7 +645,9 @@ static int flock_steps_t(ab_handle* h, const ab_flock_params* p, int64_t nsteps)
             AB_TRY(ab_comm_transfer(h));
             AB_CUDA(h, cudaStreamWaitEvent(h->stream2, h->ev_fork, 0));
             std::swap(h->stream, h->stream2);                                // the install is queued on the side stream
+            h->side_unpack_now = true;
             const int rc = h->unpack_rows ? ab_comm_unpack(h, !cx.exact) : AB_ERR_STATE;
+            h->side_unpack_now = false;
             const cudaError_t ce = cudaEventRecord(h->ev_join, h->stream);
             std::swap(h->stream, h->stream2);
             if (rc == AB_ERR_STATE) return ab_fail(h, AB_ERR_STATE, "side-stream halo install without row counters");

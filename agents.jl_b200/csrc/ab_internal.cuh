@@ -36,7 +36,9 @@
 #define AB_VERSION 100
 
 #define AB_SCH_EMPTY INT32_MIN
-enum { AB_EF_OUTSIDE = 1, AB_EF_NUMERIC = 2, AB_EF_OCCUPIED = 4, AB_EF_OVERFLOW = 8, AB_EF_COMM = 16, AB_EF_ARG = 32 };
+enum { AB_EF_OUTSIDE = 1, AB_EF_NUMERIC = 2, AB_EF_OCCUPIED = 4, AB_EF_OVERFLOW = 8, AB_EF_COMM = 16, AB_EF_ARG = 32,
+       // what went wrong in the exchange (reported with AB_ERR_COMM)
+       AB_EF_COMM_CAP = 1 << 8, AB_EF_COMM_HDR = 1 << 9, AB_EF_COMM_WINDOW = 1 << 10, AB_EF_COMM_TIMEOUT = 1 << 11 };
 
 // Counter-based random stream of the bulk randomwalk! calls (the reference draws from the model's RNG,
 // src/spaces/walk.jl:154-214, 389-408; its stream is not reproduced — SURVEY §8c(iv) — so the device rule is
@@ -179,6 +181,7 @@ struct ab_handle {
     bool cellm_old = false;            // AB_CELLM_OLD=1: the one-row-per-warp k_cell_M in 2-D too (A/B experiments)
     bool small_scan = false;           // AB_SMALL_SCAN=1: single-CTA scan of the tile totals (A/B experiments)
     bool no_side_unpack = false;       // AB_SIDE_UNPACK=0: halo install after the re-sort on the same stream (A/B experiments)
+    bool side_unpack_now = false;      // the halo install being queued runs beside the re-sort (one-thread flag wait first)
     bool unpack_rows = false;          // this step's per-row counters give the owned count (set by a scan-free re-sort)
     bool halo_packed = false;          // the re-sort of this step already delivered the boundary messages
     // slab window along the last axis (multi-GPU, ab_comm.cu); W == 0: the handle holds the whole space

@@ -135,7 +135,7 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const __grid_constant__ HaloOut ho, co
             if (tile == t0b[dir] && lane == 0) {                   // the region's first tile: header (and the capacity check)
                 uint32_t* hdr = reinterpret_cast<uint32_t*>(ho.buf[dir]);
                 hdr[0] = cntc[dir]; hdr[1] = k0[dir]; hdr[2] = ho.ncs; hdr[3] = 0xAB200u;
-                if (cnt > (uint32_t)ho.m.C) atomicOr(err, AB_EF_COMM);
+                if (cnt > (uint32_t)ho.m.C) atomicOr(err, AB_EF_COMM | AB_EF_COMM_CAP);
             }
             if (tile == t1b[dir] - 1 && lane == 0)                 // the region's last tile: closing entry of the cell_start slice
                 reinterpret_cast<uint32_t*>(ho.buf[dir] + ho.m.off_cs)[ho.ncs] = cntc[dir];

@@ -36,6 +36,9 @@ CASES = [
     ("3d-approx", ["--agents", "40000", "--extent", "60", "60", "120", "--steps", "8"]),
     ("2d-f32", ["--agents", "60000", "--extent", "400", "400", "--steps", "6", "--dtype", "float32"]),
     ("2d-walls", ["--agents", "60000", "--extent", "400", "400", "--steps", "12", "--walls"]),
+    # large enough for the halo install to cover every SM: with a grid of spinning CTAs beside the re-sort this size
+    # dead-locked two ranks (the install now waits in ONE thread, k_halo_wait)
+    ("2d-1M", ["--agents", "1000000", "--extent", "2000", "2000", "--steps", "6", "--chunk", "3"]),
     ("3d-walls-exact", ["--agents", "40000", "--extent", "60", "60", "120", "--steps", "8", "--walls", "--search", "exact"]),
 ]
 
