@@ -278,7 +278,8 @@ k_halo_unpack(SpaceDev<T, D> sp, MsgLayout m, MsgCols xc, uint32_t kown, uint32_
               int32_t* __restrict__ id, uint32_t* __restrict__ key, int64_t cap, const char* __restrict__ buf0,
               const char* __restrict__ buf1, int* __restrict__ err, const uint32_t* wflag0, const uint32_t* wflag1,
               uint32_t epoch, int nbc, int nba, T* __restrict__ agg, int64_t agg_stride, uint32_t halo_cell0,
-              uint32_t cells_per_side, unsigned long long* wait_stat, const uint32_t* __restrict__ row_cnt, int nrows) {
+              uint32_t cells_per_side, unsigned long long* wait_stat, const uint32_t* __restrict__ row_cnt, int nrows,
+              const uint32_t* __restrict__ nown_ptr) {
     if (wflag0 || wflag1) {
         // direct exchange: both messages were stored into our memory by the neighbours' pack kernels; they
         // never wait for us in return (their pack depends only on their own steps; slots alternate by parity)
@@ -313,7 +314,7 @@ k_halo_unpack(SpaceDev<T, D> sp, MsgLayout m, MsgCols xc, uint32_t kown, uint32_
         if ((threadIdx.x & 31) == 0 && part) atomicAdd(&s_nown, part);
         __syncthreads();
         n_own = s_nown;
-    } else n_own = cs[kown];
+    } else n_own = nown_ptr ? *nown_ptr : cs[kown];      // nown_ptr: the scanned tile totals' last entry (scan path)
     uint32_t cnt_u = buf0 ? h0[0] : 0u, cnt_l = buf1 ? h1[0] : 0u;
     bool bad = (buf0 && (h0[3] != 0xAB200u || h0[2] != m.ncs)) || (buf1 && (h1[3] != 0xAB200u || h1[2] != m.ncs));
     const bool nofit = (uint64_t)n_own + cnt_u + cnt_l > (uint64_t)cap;   // window does not fit the handle's capacity
@@ -569,7 +570,7 @@ static int unpack_t(ab_handle* h, bool want_agg) {
     }
     const uint32_t* wf0 = c->ipc_on && c->has_upper ? ipc_flag(c->ipc_block, c->ipc_stride, c->cur_par, 0) : nullptr;
     const uint32_t* wf1 = c->ipc_on && c->has_lower ? ipc_flag(c->ipc_block, c->ipc_stride, c->cur_par, 1) : nullptr;
-    const bool prewait = h->unpack_rows && (wf0 || wf1) && h->side_unpack_now;
+    const bool prewait = (h->unpack_rows || h->unpack_tb) && (wf0 || wf1) && h->side_unpack_now;
     if (prewait) {
         AB_LAUNCH(h, "k_halo_wait");
         k_halo_wait<<<1, 32, 0, h->stream>>>(wf0, wf1, (uint32_t)c->exchanges, h->d_err, c->d_wait);
@@ -583,8 +584,9 @@ static int unpack_t(ab_handle* h, bool want_agg) {
                                                                wf0, wf1,
                                                                (uint32_t)c->exchanges, nbc, nba, (T*)h->cell_agg, (int64_t)h->ncells,
                                                                (uint32_t)(h->win_nl * cpl), (uint32_t)(AB_HALO_W * cpl), prewait ? nullptr : c->d_wait,
-                                                               h->unpack_rows ? h->row_count + (size_t)(h->rs_par ^ 1) * h->row_cap : nullptr, h->rs_nrows);
-        h->unpack_rows = false;
+                                                               h->unpack_rows ? h->row_count + (size_t)(h->rs_par ^ 1) * h->row_cap : nullptr, h->rs_nrows,
+                                                               h->unpack_tb ? h->tile_base + h->rs_ntiles : nullptr);
+        h->unpack_rows = h->unpack_tb = false;
     }
     return AB_OK;
 }
@@ -793,7 +795,7 @@ int ab_comm_exchange(ab_handle* h) {
     if (ab_comm_local(h)) return ab_fail(h, AB_ERR_STATE, "in-process slabs exchange inside ab_step_flock_group");
     AB_CUDA(h, cudaSetDevice(h->device));
     h->index_valid = false;
-    h->unpack_rows = false;
+    h->unpack_rows = h->unpack_tb = false;
     AB_TRY(ab_ensure_index(h));
     AB_TRY(ab_comm_pack(h));
     AB_TRY(ab_comm_transfer(h));

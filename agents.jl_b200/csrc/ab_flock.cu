@@ -624,11 +624,12 @@ static int flock_steps_t(ab_handle* h, const ab_flock_params* p, int64_t nsteps)
         AB_CUDA(h, cudaEventRecord(h->ev1, h->stream));
         return AB_OK;
     }
-    // Direct exchange on a scan-free space: the halo install of a step runs on a side stream CONCURRENTLY with the
-    // step's own re-sort.  It needs (i) the neighbours' messages — their boundary tiles run first in THEIR re-sort —,
-    // (ii) the owned count, which the step's per-row counters give since the sweep, and it writes only halo slots,
+    // Direct exchange: the halo install of a step runs on a side stream CONCURRENTLY with the step's own re-sort.
+    // It needs (i) the neighbours' messages — their boundary tiles run first in THEIR re-sort —, (ii) the owned count,
+    // which the step's per-row counters give since the sweep (scan-free spaces) or the scanned tile totals since the
+    // small scan in front of the re-sort (the event is recorded between the two), and it writes only halo slots,
     // halo cell_start entries and halo aggregates, none of which the re-sort touches.  k_cell_M joins both.
-    const bool side_unpack = h->win_W && cx.fine && ab_comm_direct_on(h) && h->rs_scanfree && !h->no_side_unpack;
+    const bool side_unpack = h->win_W && cx.fine && ab_comm_direct_on(h) && !h->no_side_unpack;
     if (side_unpack && !h->stream2) {
         AB_CUDA(h, cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking));
         AB_CUDA(h, cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
@@ -639,14 +640,14 @@ static int flock_steps_t(ab_handle* h, const ab_flock_params* p, int64_t nsteps)
             int32_t* ncount = nullptr;
             if (cx.exact) AB_TRY((launch_fine<T, D, true>(h, cx.sp, cx.u, ncount)));
             else AB_TRY((launch_fine<T, D, false>(h, cx.sp, cx.u, ncount)));
-            AB_CUDA(h, cudaEventRecord(h->ev_fork, h->stream));              // the counters of this step are complete
-            AB_TRY(ab_resort_tiled(h, h->tmp_pos, h->tmp_vel, !cx.exact));   // delivers the boundary messages too
+            if (h->rs_scanfree) AB_CUDA(h, cudaEventRecord(h->ev_fork, h->stream));   // the counters of this step are complete
+            AB_TRY(ab_resort_tiled(h, h->tmp_pos, h->tmp_vel, !cx.exact, h->rs_scanfree ? nullptr : h->ev_fork));   // delivers the boundary messages too
             AB_TRY(ab_comm_pack(h));                                         // (a launch only when user columns travel)
             AB_TRY(ab_comm_transfer(h));
             AB_CUDA(h, cudaStreamWaitEvent(h->stream2, h->ev_fork, 0));
             std::swap(h->stream, h->stream2);                                // the install is queued on the side stream
             h->side_unpack_now = true;
-            const int rc = h->unpack_rows ? ab_comm_unpack(h, !cx.exact) : AB_ERR_STATE;
+            const int rc = (h->unpack_rows || h->unpack_tb) ? ab_comm_unpack(h, !cx.exact) : AB_ERR_STATE;
             h->side_unpack_now = false;
             const cudaError_t ce = cudaEventRecord(h->ev_join, h->stream);
             std::swap(h->stream, h->stream2);

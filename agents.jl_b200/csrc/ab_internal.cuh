@@ -182,6 +182,7 @@ struct ab_handle {
     bool small_scan = false;           // AB_SMALL_SCAN=1: single-CTA scan of the tile totals (A/B experiments)
     bool no_side_unpack = false;       // AB_SIDE_UNPACK=0: halo install after the re-sort on the same stream (A/B experiments)
     bool side_unpack_now = false;      // the halo install being queued runs beside the re-sort (one-thread flag wait first)
+    bool unpack_tb = false;            // ... or the scanned tile totals do (scan path)
     bool unpack_rows = false;          // this step's per-row counters give the owned count (set by a scan-free re-sort)
     bool halo_packed = false;          // the re-sort of this step already delivered the boundary messages
     // slab window along the last axis (multi-GPU, ab_comm.cu); W == 0: the handle holds the whole space
@@ -225,7 +226,7 @@ int ab_set_refine(ab_handle* h, int K);
 int ab_reindex_from(ab_handle* h, const void* src_pos, const void* src_vel, bool count_done);
 int ab_permute_extra_fields(ab_handle* h, bool owned_only);   // applies h->perm (new slot -> old slot) to user columns, cur -> cur^1
 bool ab_resort_applicable(const ab_handle* h);
-int ab_resort_tiled(ab_handle* h, const void* src_pos, const void* src_vel, bool want_agg);
+int ab_resort_tiled(ab_handle* h, const void* src_pos, const void* src_vel, bool want_agg, cudaEvent_t after_scan = nullptr);
 int ab_resort_plan(ab_handle* h);              // tile geometry of the next tiled re-sort (before the step kernel that counts the keys)
 int ab_ensure_agg(ab_handle* h);
 int ab_agg_range(ab_handle* h, int64_t cell0, int64_t ncell);

@@ -578,7 +578,7 @@ int ab_resort_plan(ab_handle* h) {
 }
 
 template <class T, int D>
-static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool want_agg) {
+static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool want_agg, cudaEvent_t after_scan) {
     const int cur = h->cur, nxt = cur ^ 1;
     SpaceDev<T, D> sp = make_space<T, D>(h);
     ResortArgs a;
@@ -595,6 +595,7 @@ static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool
     a.tile_other = h->tile_count + (size_t)(h->rs_par ^ 1) * h->tile_cap;
     a.row_other = h->row_count + (size_t)(h->rs_par ^ 1) * h->row_cap;
     if (!h->rs_scanfree) AB_TRY(ab_scan_u32(h, h->tile_count, h->tile_base, (uint32_t)a.ntiles));
+    if (after_scan) AB_CUDA(h, cudaEventRecord(after_scan, h->stream));     // tile_base is complete: a side-stream halo install may start
     if (want_agg) AB_TRY(ensure_agg(h));
     const bool extra = h->fields.size() > 2u;
     // slab window: the boundary tiles deliver the neighbours' messages while they place their agents
@@ -613,6 +614,7 @@ static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool
     }
     if (h->rs_scanfree) h->rs_par ^= 1;                // the next step accumulates into the other half
     h->unpack_rows = h->rs_scanfree && h->win_W;
+    h->unpack_tb = !h->rs_scanfree && h->win_W;
     std::swap(h->cell_start, h->cell_start_alt);
     AB_TRY(ab_permute_extra_fields(h, true));
     h->cur = nxt;
@@ -628,9 +630,9 @@ static int resort_t(ab_handle* h, const void* src_pos, const void* src_vel, bool
 // into the other buffer.  Requires the new keys counted into h->cell_count / h->tile_count (count_new_key,
 // geometry of ab_resort_plan) and that no agent moved further than one fine cell (checked on the device:
 // AB_EF_OVERFLOW otherwise).
-int ab_resort_tiled(ab_handle* h, const void* src_pos, const void* src_vel, bool want_agg) {
-    if (h->dtype == AB_F64) return h->D == 2 ? resort_t<double, 2>(h, src_pos, src_vel, want_agg) : resort_t<double, 3>(h, src_pos, src_vel, want_agg);
-    return h->D == 2 ? resort_t<float, 2>(h, src_pos, src_vel, want_agg) : resort_t<float, 3>(h, src_pos, src_vel, want_agg);
+int ab_resort_tiled(ab_handle* h, const void* src_pos, const void* src_vel, bool want_agg, cudaEvent_t after_scan) {
+    if (h->dtype == AB_F64) return h->D == 2 ? resort_t<double, 2>(h, src_pos, src_vel, want_agg, after_scan) : resort_t<double, 3>(h, src_pos, src_vel, want_agg, after_scan);
+    return h->D == 2 ? resort_t<float, 2>(h, src_pos, src_vel, want_agg, after_scan) : resort_t<float, 3>(h, src_pos, src_vel, want_agg, after_scan);
 }
 
 template <class T, int D>
