@@ -184,3 +184,77 @@ extern "C" int ab_reduce(ab_handle* h, const ab_reduce_spec* specs, int nspec, d
     if (counts) for (int i = 0; i < nspec; ++i) counts[i] = cnt[i];
     return AB_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------
+// Schedulers.ByProperty(field)(model) — src/submodules/schedulers.jl:130-151: the agent ids in `sortperm` order of
+// a property column (ascending, stable: ties keep id order).  Under the synchronous update an ordering of ALL agents
+// changes nothing, so this is a helper for host-side loops: the sort runs on the device — a bitonic network over
+// (sortable key, id) pairs, the id in the low word making the order total and therefore stable — and only the n
+// sorted ids cross PCIe.
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long sort_key_f64(double v) {
+    if (v != v) return 0xFFFFFFFFFFFFFFF0ull;                      // NaN last (isless), below the padding
+    unsigned long long b = (unsigned long long)__double_as_longlong(v);
+    return (b & 0x8000000000000000ull) ? ~b : (b | 0x8000000000000000ull);
+}
+__global__ void k_sort_fill(const void* __restrict__ col, int dtype, const int32_t* __restrict__ id, int n, int npad,
+                            ulonglong2* __restrict__ P) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= npad) return;
+    if (s >= n) { P[s] = make_ulonglong2(~0ull, ~0ull); return; }  // padding sorts to the end
+    const int i = id ? id[s] : s;                                  // grids keep their columns in id order
+    unsigned long long k;
+    if (dtype == AB_I64) k = (unsigned long long)(((const long long*)col)[s]) ^ 0x8000000000000000ull;
+    else k = sort_key_f64(red_load(col, dtype, s));                // f64 / f32 / i32 / u8: exact in a double
+    P[s] = make_ulonglong2(k, (unsigned long long)i);
+}
+__global__ void k_sort_step(ulonglong2* __restrict__ P, int npad, int k, int j) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npad) return;
+    const int l = i ^ j;
+    if (l <= i) return;
+    const ulonglong2 a = P[i], b = P[l];
+    const bool a_gt_b = a.x > b.x || (a.x == b.x && a.y > b.y);
+    const bool up = (i & k) == 0;
+    if (a_gt_b == up) { P[i] = b; P[l] = a; }
+}
+__global__ void k_sort_out(const ulonglong2* __restrict__ P, int n, int descending, int64_t* __restrict__ out) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    out[descending ? n - 1 - s : s] = (int64_t)P[s].y + 1;
+}
+
+extern "C" int ab_ids_by_property(ab_handle* h, int field, int comp, int descending, int64_t* out_ids, int64_t n) {
+    if (!h || field < 0 || field >= (int)h->fields.size()) return ab_fail(h, AB_ERR_INVALID, "bad field id");
+    if (h->win_W) return ab_fail(h, AB_ERR_STATE, "not available on a sharded handle");
+    if (n != h->n) return ab_fail(h, AB_ERR_INVALID, "length must equal the agent count");
+    const ab_field& f = h->fields[field];
+    if (comp < 0 || comp >= f.ncomp) return ab_fail(h, AB_ERR_INVALID, "bad component");
+    if (n == 0) return AB_OK;
+    if (!out_ids) return ab_fail(h, AB_ERR_INVALID, "null output");
+    AB_CUDA(h, cudaSetDevice(h->device));
+    if (h->grid_cols_dirty) AB_TRY(ab_grid_sync_columns(h));
+    int npad = 1;
+    while (npad < n) npad <<= 1;
+    char* base;
+    AB_TRY(ab_scratch2(h, (size_t)npad * sizeof(ulonglong2) + (size_t)n * sizeof(int64_t) + 256, (void**)&base));
+    ulonglong2* P = (ulonglong2*)base;
+    int64_t* dout = (int64_t*)(base + (size_t)npad * sizeof(ulonglong2));
+    const char* col = (const char*)f.buf[h->cur] + (size_t)comp * h->cap * f.esize;
+    const bool cont = h->desc.kind == AB_SPACE_CONTINUOUS;         // continuous handles keep columns in slot order
+    {
+        AB_LAUNCH(h, "k_sort_fill");
+        k_sort_fill<<<ab_blocks(npad, 256), 256, 0, h->stream>>>(col, f.dtype, cont ? h->id[h->cur] : nullptr, (int)n, npad, P);
+    }
+    for (int k = 2; k <= npad; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            AB_LAUNCH(h, "k_sort_step");
+            k_sort_step<<<ab_blocks(npad, 256), 256, 0, h->stream>>>(P, npad, k, j);
+        }
+    {
+        AB_LAUNCH(h, "k_sort_out");
+        k_sort_out<<<ab_blocks(n, 256), 256, 0, h->stream>>>(P, (int)n, descending, dout);
+    }
+    AB_CUDA(h, cudaMemcpyAsync(out_ids, dout, (size_t)n * sizeof(int64_t), cudaMemcpyDeviceToHost, h->stream));
+    return ab_check_device_errors_now(h);
+}

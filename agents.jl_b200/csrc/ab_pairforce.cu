@@ -181,8 +181,23 @@ k_pf_fine(SpaceDev<T, D> sp, PfU<T> u, const T* __restrict__ pos, const T* __res
                 const T sq = direct * direct;
                 dd = (d == 0) ? sq : dd + sq;
             }
-            if ((int)j == s || !(dd <= u.thr)) continue;                                      // continuous.jl:237-238
-            pf_pair<T, D>(dr, dd, ri, ki, rad[j], kk[j], f);
+            // Branch-free form of "pair within the cutoff (continuous.jl:237-238) and within r_i + r_j
+            // (celllistmap.jl:147): add fij" — the lanes of a warp disagree on almost every candidate, so a
+            // branchy body runs most of its paths for most candidates with half the lanes idle (measured: 89 warp
+            // instructions per candidate, 15.6 of 32 lanes active).  Excluded pairs get the weight 0 and a
+            // harmless d² = 1 for the rsqrt; included pairs are evaluated exactly as pf_pair does.
+            const T rj = rad[j], kj = kk[j];
+            const T rs = ri + rj;
+            const T rs2 = rs * rs;
+            const T band = sizeof(T) == 8 ? T(1e-14) : T(1e-5);
+            bool in = dd < rs2 * (T(1) - band);
+            if (!in && !(dd > rs2 * (T(1) + band))) in = ab_sqrt(dd) <= rs;                   // inside the rounding band: the reference's own comparison
+            in = in && (int)j != s && dd <= u.thr;
+            const T dsafe = in ? dd : T(1);
+            const T pref = in ? (T(2) * (ki * kj)) * (dd - rs2) : T(0);
+            const T rinv = ab_rsqrt(dsafe);
+#pragma unroll
+            for (int d = 0; d < D; ++d) f[d] += pref * (dr[d] * rinv);
         }
     };
     auto sweep = [&](uint32_t jb, uint32_t je, int wrap) {

@@ -530,12 +530,12 @@ class StandardABM:
     # -- schedulers (src/submodules/schedulers.jl) ------------------------------
     def schedule_by_property(self, field, comp=0):
         """Schedulers.ByProperty(field)(model) — schedulers.jl:130-151: the agent ids ordered by `sortperm` of the
-        property column (ascending, stable: Julia's default sort algorithm for sortperm is stable).  The column is
-        read from the device; the order is built on the host."""
-        col = self.column(field)
-        if col.ndim > 1:
-            col = col[:, comp]
-        return np.argsort(col, kind="stable").astype(np.int64) + 1
+        property column (ascending, stable: Julia's default sort algorithm for sortperm is stable).  Sorted on the
+        device (ab_ids_by_property); only the ids come back."""
+        n = self.nagents()
+        out = np.zeros(n, dtype=np.int64)
+        self._ck(self.lib.ab_ids_by_property(self.h, self.field_id(field), int(comp), 0, self._ptr(out), n))
+        return out
 
     def schedule_partially(self, p, rng):
         """Schedulers.Partially(p)(model) — schedulers.jl:109-120: randsubseq of the ids with probability p (each id is

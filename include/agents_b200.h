@@ -287,6 +287,10 @@ typedef struct {
     double filter_value;
 } ab_reduce_spec;
 int ab_reduce(ab_handle* h, const ab_reduce_spec* specs, int nspec, double* out, int64_t* counts_or_null);
+/* Schedulers.ByProperty(field)(model) — src/submodules/schedulers.jl:130-151: the 1-based agent ids in `sortperm`
+ * order of component `comp` of a column (ascending, stable: ties keep id order; NaN last; `descending` reverses the
+ * result).  Sorted on the device (bitonic network over (key, id) pairs); n ids come back. */
+int ab_ids_by_property(ab_handle* h, int field, int comp, int descending, int64_t* out_ids, int64_t n);
 
 /* ---- multi-GPU slabs (one process per GPU) -----------------------------------
  * The reference is single-task (step_standard.jl:9-23); this is its scale-out

@@ -119,3 +119,31 @@ def test_schedule_by_property_is_sortperm():
     m.step(1, scheduler=ids)
     assert np.array_equal(m.pos, ref.pos) and np.array_equal(m.vel, ref.vel)
     m.close(); ref.close()
+
+
+def test_ids_by_property_device_sort():
+    """ab_ids_by_property: stable ascending sortperm on the device for float / integer columns, NaN last, descending
+    = the reversed result; grid handles too (columns in id order there)."""
+    rng = np.random.default_rng(11)
+    n = 3001                                                             # not a power of two: the network is padded
+    extent = (100.0, 100.0)
+    pos, vel = flock_init(n, extent, 9)
+    w = np.round(rng.standard_normal(n) * 3.0)                           # ties and negative values
+    w[::97] = np.nan
+    lvl = rng.integers(-5, 6, n).astype(np.int32)
+    m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=5.0), model_step=ab.FlockRule(**FLOCK))
+    m.add_agents(pos, vel, weight=w, level=lvl)
+    m.step(2)
+    assert np.array_equal(m.schedule_by_property("weight"), np.argsort(w, kind="stable") + 1)      # numpy sorts NaN last too
+    assert np.array_equal(m.schedule_by_property("level"), np.argsort(lvl, kind="stable") + 1)
+    assert np.array_equal(m.schedule_by_property("pos", comp=1), np.argsort(m.pos[:, 1], kind="stable") + 1)
+    out = np.zeros(n, dtype=np.int64)
+    m._ck(m.lib.ab_ids_by_property(m.h, m.field_id("level"), 0, 1, m._ptr(out), n))
+    assert np.array_equal(out, (np.argsort(lvl, kind="stable") + 1)[::-1])
+    m.close()
+    g = ab.StandardABM(ab.GridSpace((20, 20)))
+    gp = rng.integers(1, 21, (500, 2)).astype(np.int32)
+    g.add_agents(gp, energy=rng.random(500))
+    e = g.column("energy")
+    assert np.array_equal(g.schedule_by_property("energy"), np.argsort(e, kind="stable") + 1)
+    g.close()
