@@ -128,7 +128,7 @@ def test_ids_by_property_device_sort():
     n = 3001                                                             # not a power of two: the network is padded
     extent = (100.0, 100.0)
     pos, vel = flock_init(n, extent, 9)
-    w = np.round(rng.standard_normal(n) * 3.0)                           # ties and negative values
+    w = np.round(rng.standard_normal(n) * 3.0) + 0.0                     # ties and negative values (+ 0.0: no -0.0, see below)
     w[::97] = np.nan
     lvl = rng.integers(-5, 6, n).astype(np.int32)
     m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=5.0), model_step=ab.FlockRule(**FLOCK))
@@ -140,6 +140,11 @@ def test_ids_by_property_device_sort():
     out = np.zeros(n, dtype=np.int64)
     m._ck(m.lib.ab_ids_by_property(m.h, m.field_id("level"), 0, 1, m._ptr(out), n))
     assert np.array_equal(out, (np.argsort(lvl, kind="stable") + 1)[::-1])
+    m.close()
+    # isless(-0.0, 0.0) is true in Julia (sortperm orders by isless): -0.0 sorts before 0.0 — numpy would call them equal
+    m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=5.0), model_step=ab.FlockRule(**FLOCK))
+    m.add_agents(pos[:4], vel[:4], weight=np.array([0.0, -0.0, 1.0, -1.0]))
+    assert m.schedule_by_property("weight").tolist() == [4, 2, 1, 3]
     m.close()
     g = ab.StandardABM(ab.GridSpace((20, 20)))
     gp = rng.integers(1, 21, (500, 2)).astype(np.int32)
