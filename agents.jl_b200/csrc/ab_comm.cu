@@ -97,6 +97,7 @@ struct ab_comm {
     bool linked_local = false;       // ab_comm_link_local done (an end slab of a non-periodic axis has one peer only)
     bool has_lower = true, has_upper = true;   // false on the end ranks of a non-periodic last axis
     bool no_fused_pack = false;      // AB_FUSED_PACK=0: always pack with the separate k_halo_pack launch (A/B experiments)
+    size_t fused_pack_max_bytes = (size_t)8 << 20;   // AB_FUSED_PACK_MAXMB: largest message the re-sort delivers itself
     cudaEvent_t ev_packed = nullptr, ev_consumed = nullptr;
     uint32_t* h_counts = nullptr;    // pinned {n_own, n_window}
     int64_t exchanges = 0;
@@ -489,7 +490,13 @@ int ab_comm_pack_begin(ab_handle* h, HaloOut* out) {
     out->flag[0] = c->ipc_on && c->has_lower ? ipc_flag(c->ipc_lower, c->ipc_stride, c->cur_par, 0) : nullptr;
     out->flag[1] = c->ipc_on && c->has_upper ? ipc_flag(c->ipc_upper, c->ipc_stride, c->cur_par, 1) : nullptr;
     out->epoch = (uint32_t)(c->exchanges + 1);
-    out->enabled = (out->m.nx == 0 && !c->no_fused_pack) ? 1 : 0;
+    // The re-sort delivers the messages itself when they are SMALL (2-D slabs: a few thousand agents per side — the pack
+    // launch and its latency are what there is to save).  Large messages (3-D: tens of MB per side) go through
+    // k_halo_pack: it reads the sorted state sequentially and stores 256-byte runs over NVLink, where the re-sort's
+    // boundary tiles would store 8 bytes at a time (measured, F3D-12.5M per GPU: k_resort 1.66 ms with the fused
+    // delivery against 1.04 ms unsharded).
+    const bool small = out->m.bytes <= c->fused_pack_max_bytes;
+    out->enabled = (out->m.nx == 0 && !c->no_fused_pack && small) ? 1 : 0;
     return AB_OK;
 }
 
@@ -676,6 +683,7 @@ int ab_comm_init(ab_handle* h, int rank, int nranks, const void* nccl_unique_id)
     c->upper = (rank + 1) % nranks;
     // non-periodic last axis: the end slabs have one neighbour; the halo layers beyond the space stay empty
     if (const char* e = getenv("AB_FUSED_PACK")) c->no_fused_pack = atoi(e) == 0;
+    if (const char* e = getenv("AB_FUSED_PACK_MAXMB")) c->fused_pack_max_bytes = (size_t)atol(e) << 20;
     c->has_lower = per_last || rank > 0;
     c->has_upper = per_last || rank < nranks - 1;
     if (cudaMallocHost((void**)&c->h_counts, 2 * sizeof(uint32_t)) != cudaSuccess) { delete c; return ab_fail(h, AB_ERR_CUDA, "cudaMallocHost failed"); }
