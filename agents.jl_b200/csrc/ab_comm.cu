@@ -364,18 +364,21 @@ k_halo_unpack(SpaceDev<T, D> sp, MsgLayout m, MsgCols xc, uint32_t kown, uint32_
         }
         return;
     }
-    // ---- aggregates of the halo cells of this side: one 8-lane group per (reference cell, fine row of it) ----
+    // ---- aggregates of the halo cells of this side: one LANE per (fine row of a reference cell, reference cell) ----
+    // Canonical sum of a cell's n agents (k_resort / k_cell_agg): 8 strided partials a_g = Σ_i x[g + 8 i] combined as
+    // ((a0+a4)+(a2+a6)) + ((a1+a5)+(a3+a7)).  Cells with n <= 8 — nearly all of them in a dilute state, 1.1 agents per
+    // item at F3D's density — are summed by their own lane (each partial is one term); fuller cells by lanes 0..7 of
+    // the warp, one cell at a time.
     constexpr int NC = 1 + 2 * D;
     const int K = sp.K, kb = sp.kb;
     const int nfr = D == 2 ? K : K * K;
-    const int gl = threadIdx.x & 7;
-    const uint32_t ngroups = cells_per_side * (uint32_t)nfr;
-    // g0 = first group of this warp (4 groups per warp): the loop condition is warp-uniform, the shuffles below full-mask
-    for (uint32_t g0 = ((uint32_t)bx * blockDim.x + (threadIdx.x & ~31u)) >> 3; g0 < ngroups; g0 += ((uint32_t)per * blockDim.x) >> 3) {
-        const uint32_t g = g0 + ((threadIdx.x & 31u) >> 3);
-        const bool live = g < ngroups;
-        const uint32_t cl = live ? g / (uint32_t)nfr : 0u;
-        const int part = live ? (int)(g - cl * (uint32_t)nfr) : 0;
+    const int lane = threadIdx.x & 31;
+    const uint32_t nitems = cells_per_side * (uint32_t)nfr;
+    for (uint32_t g0 = (uint32_t)bx * blockDim.x + (threadIdx.x & ~31u); g0 < nitems; g0 += (uint32_t)per * blockDim.x) {
+        const uint32_t g = g0 + (uint32_t)lane;                     // the loop condition is warp-uniform
+        const bool live = g < nitems;
+        const int part = live ? (int)(g / cells_per_side) : 0;      // cells fastest: neighbouring lanes, neighbouring cells
+        const uint32_t cl = live ? g - (uint32_t)part * cells_per_side : 0u;
         const uint32_t c = halo_cell0 + (uint32_t)src * cells_per_side + cl;
         int cc[D];
         unlin_cell<D>(sp.dims, c, cc);
@@ -384,28 +387,58 @@ k_halo_unpack(SpaceDev<T, D> sp, MsgLayout m, MsgCols xc, uint32_t kown, uint32_
         uint32_t b = 0, e = 0;
         if (live && !bad && buf) { b = min(mcs[i0], cnt); e = min(mcs[i0 + (uint32_t)K], cnt); }
         cc[D - 1] = local_to_global_last<T, D>(sp, cc[D - 1]);                   // centres are global
-        T acc[2 * D];
+        T ctr[D];
 #pragma unroll
-        for (int d = 0; d < 2 * D; ++d) acc[d] = T(0);
-        for (uint32_t t = b + gl; t < e; t += 8) {
+        for (int d = 0; d < D; ++d) ctr[d] = sp.spacing * ((T)(cc[d] + 1) - T(0.5));
+        const uint32_t n = e - b;
+        T* dst = agg + (size_t)part * NC * agg_stride + c;
+        if (live && n <= 8u) {
+            // term i of component d (0 beyond n): the 8-lane path's partial a_i
+            auto term = [&](int d, uint32_t i) -> T {
+                if (i >= n) return T(0);
+                return d < D ? T(0) + (mpos[(size_t)d * m.C + b + i] - ctr[d]) : T(0) + mvel[(size_t)(d - D) * m.C + b + i];
+            };
+            dst[0] = (T)n;
 #pragma unroll
-            for (int d = 0; d < D; ++d) {
-                const T centre = sp.spacing * ((T)(cc[d] + 1) - T(0.5));
-                acc[d] += mpos[(size_t)d * m.C + t] - centre;
-                acc[D + d] += mvel[(size_t)d * m.C + t];
+            for (int d = 0; d < 2 * D; ++d) {
+                const T q = (term(d, 0) + term(d, 4)) + (term(d, 2) + term(d, 6));
+                dst[(size_t)(1 + d) * agg_stride] = q + ((term(d, 1) + term(d, 5)) + (term(d, 3) + term(d, 7)));
             }
         }
+        unsigned big = __ballot_sync(0xffffffffu, live && n > 8u);
+        while (big) {
+            const int srcl = __ffs(big) - 1;
+            big &= big - 1;
+            const uint32_t gb = __shfl_sync(0xffffffffu, b, srcl), ge = __shfl_sync(0xffffffffu, e, srcl);
+            T gctr[D];
 #pragma unroll
-        for (int d = 0; d < 2 * D; ++d) {
-            acc[d] += __shfl_xor_sync(0xffffffffu, acc[d], 4);
-            acc[d] += __shfl_xor_sync(0xffffffffu, acc[d], 2);
-            acc[d] += __shfl_xor_sync(0xffffffffu, acc[d], 1);
-        }
-        if (live && gl == 0) {
-            T* dst = agg + (size_t)part * NC * agg_stride + c;
-            dst[0] = (T)(e - b);
+            for (int d = 0; d < D; ++d) gctr[d] = __shfl_sync(0xffffffffu, ctr[d], srcl);
+            T acc[2 * D];
 #pragma unroll
-            for (int d = 0; d < 2 * D; ++d) dst[(size_t)(1 + d) * agg_stride] = acc[d];
+            for (int d = 0; d < 2 * D; ++d) acc[d] = T(0);
+            if (lane < 8) {
+                for (uint32_t t = gb + (uint32_t)lane; t < ge; t += 8) {
+#pragma unroll
+                    for (int d = 0; d < D; ++d) {
+                        acc[d] += mpos[(size_t)d * m.C + t] - gctr[d];
+                        acc[D + d] += mvel[(size_t)d * m.C + t];
+                    }
+                }
+            }
+#pragma unroll
+            for (int d = 0; d < 2 * D; ++d) {
+                acc[d] += __shfl_xor_sync(0xffffffffu, acc[d], 4);
+                acc[d] += __shfl_xor_sync(0xffffffffu, acc[d], 2);
+                acc[d] += __shfl_xor_sync(0xffffffffu, acc[d], 1);
+            }
+            // the owner lane holds the destination; lane 0 holds the sums
+            const unsigned long long dptr = __shfl_sync(0xffffffffu, (unsigned long long)dst, srcl);
+            if (lane == 0) {
+                T* gd = reinterpret_cast<T*>(dptr);
+                gd[0] = (T)(ge - gb);
+#pragma unroll
+                for (int d = 0; d < 2 * D; ++d) gd[(size_t)(1 + d) * agg_stride] = acc[d];
+            }
         }
     }
 }
@@ -572,7 +605,7 @@ static int unpack_t(ab_handle* h, bool want_agg) {
     int nba = 0;
     if (want_agg) {
         if (!h->cell_agg) return ab_fail(h, AB_ERR_STATE, "halo aggregates requested before the re-sort produced the owned ones");
-        nba = (int)std::min<int64_t>(std::max<int64_t>((AB_HALO_W * cpl * nfr * 8 + 255) / 256, 1), 1184);
+        nba = (int)std::min<int64_t>(std::max<int64_t>((AB_HALO_W * cpl * nfr + 255) / 256, 1), 1184);
         h->agg_epoch++;
     }
     const uint32_t* wf0 = c->ipc_on && c->has_upper ? ipc_flag(c->ipc_block, c->ipc_stride, c->cur_par, 0) : nullptr;

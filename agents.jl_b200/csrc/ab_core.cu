@@ -548,6 +548,7 @@ int ab_create(ab_space_desc* desc, int device, ab_handle** out) {
     if (const char* e = getenv("AB_SMALL_SCAN")) h->small_scan = atoi(e) != 0;
     if (const char* e = getenv("AB_CELLM_OLD")) h->cellm_old = atoi(e) != 0;
     if (const char* e = getenv("AB_SIDE_UNPACK")) h->no_side_unpack = atoi(e) == 0;
+    if (const char* e = getenv("AB_SPLIT_M")) h->no_split_M = atoi(e) == 0;
     if (const char* e = getenv("AB_RS_TARGET")) { int v = atoi(e); if (v >= 4 && v <= 2048) h->rs_target = v; }   // tuning experiments
     h->D = desc->D;
     int64_t ncells = 1;

@@ -438,8 +438,15 @@ static int launch_cell_M(ab_handle* h, const SpaceDev<T, D>& sp, int part = 0) {
             h->cell_agg1_bytes = need1;
         }
         {
-            AB_LAUNCH(h, "k_agg_collapse");
-            AB_CUDA(h, ab_launch_chain(h->pdl, k_agg_collapse<T>, dim3(ab_blocks(total, 256)), dim3(256), h->stream, aggp, total, (T*)h->cell_agg1));
+            // all cells; on a slab window with the split schedule: the owned cells with part 1 (they are final after
+            // the re-sort), the halo cells with part 2 (after the install)
+            const int64_t own = h->win_W ? (h->ncells / h->dims[D - 1]) * h->win_nl : h->ncells;
+            const int64_t c0 = part == 2 ? own : 0, nc = part == 1 ? own : h->ncells - c0;
+            if (nc > 0) {
+                AB_LAUNCH(h, "k_agg_collapse");
+                AB_CUDA(h, ab_launch_chain(h->pdl, k_agg_collapse<T>, dim3(ab_blocks(FineCfg<D>::NC * nc, 256)), dim3(256), h->stream, aggp,
+                                           (int64_t)h->ncells, c0, nc, (int)FineCfg<D>::NC, (T*)h->cell_agg1));
+            }
         }
         aggp = (const T*)h->cell_agg1;
         nfr = 1;
@@ -641,8 +648,13 @@ static int flock_steps_t(ab_handle* h, const ab_flock_params* p, int64_t nsteps)
             if (cx.exact) AB_TRY((launch_fine<T, D, true>(h, cx.sp, cx.u, ncount)));
             else AB_TRY((launch_fine<T, D, false>(h, cx.sp, cx.u, ncount)));
             if (h->rs_scanfree) AB_CUDA(h, cudaEventRecord(h->ev_fork, h->stream));   // the counters of this step are complete
-            AB_TRY(ab_resort_tiled(h, h->tmp_pos, h->tmp_vel, !cx.exact, h->rs_scanfree ? nullptr : h->ev_fork));   // delivers the boundary messages too
-            AB_TRY(ab_comm_pack(h));                                         // (a launch only when user columns travel)
+            AB_TRY(ab_resort_tiled(h, h->tmp_pos, h->tmp_vel, !cx.exact, h->rs_scanfree ? nullptr : h->ev_fork));   // delivers small boundary messages too
+            // Large messages (3-D) are packed by a launch of their own; the install then cannot hide behind the re-sort,
+            // so it hides behind the cell sums of the INTERIOR rows instead (they need no halo aggregate):
+            //   main: pack - M(interior rows)            side: wait for the flags - install
+            //   join - M(boundary rows)
+            const bool split_M = !h->halo_packed && !cx.exact && !h->no_split_M;
+            AB_TRY(ab_comm_pack(h));
             AB_TRY(ab_comm_transfer(h));
             AB_CUDA(h, cudaStreamWaitEvent(h->stream2, h->ev_fork, 0));
             std::swap(h->stream, h->stream2);                                // the install is queued on the side stream
@@ -654,8 +666,9 @@ static int flock_steps_t(ab_handle* h, const ab_flock_params* p, int64_t nsteps)
             if (rc == AB_ERR_STATE) return ab_fail(h, AB_ERR_STATE, "side-stream halo install without row counters");
             AB_TRY(rc);
             AB_CUDA(h, ce);
+            if (split_M) AB_TRY((launch_cell_M<T, D>(h, cx.sp, 1)));
             AB_CUDA(h, cudaStreamWaitEvent(h->stream, h->ev_join, 0));
-            if (!cx.exact) AB_TRY((launch_cell_M<T, D>(h, cx.sp)));
+            if (!cx.exact) AB_TRY((launch_cell_M<T, D>(h, cx.sp, split_M ? 2 : 0)));
             continue;
         }
         AB_TRY((flock_half_A<T, D>(h, cx, st == nsteps - 1)));

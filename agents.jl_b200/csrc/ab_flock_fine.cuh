@@ -74,15 +74,18 @@ __device__ __forceinline__ int wrap_coord(int c, int n, bool periodic) {
 // One aggregate per reference cell out of its 4 fine-row partials (3-D K = 2, 2-D K = 4), summed in the order
 // k_cell_M would use — so that its 13 (5) neighbour-row reads per cell touch a quarter of the data.
 template <class T>
-__global__ void k_agg_collapse(const T* __restrict__ aggp, int64_t total, T* __restrict__ out) {
+__global__ void k_agg_collapse(const T* __restrict__ aggp, int64_t ncells, int64_t c0, int64_t nc, int ncomp, T* __restrict__ out) {
     ab_dep_wait();
-    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;       // total = NC * ncells
-    if (t >= total) return;
-    T v = aggp[t];
-    v += aggp[total + t];
-    v += aggp[2 * total + t];
-    v += aggp[3 * total + t];
-    out[t] = v;
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;       // (component, cell of [c0, c0 + nc))
+    if (t >= (int64_t)ncomp * nc) return;
+    const int64_t i = t / nc;
+    const int64_t idx = i * ncells + c0 + (t - i * nc);
+    const int64_t total = (int64_t)ncomp * ncells;
+    T v = aggp[idx];
+    v += aggp[total + idx];
+    v += aggp[2 * total + idx];
+    v += aggp[3 * total + idx];
+    out[idx] = v;
 }
 
 #define CM_OUT 28

@@ -180,6 +180,7 @@ struct ab_handle {
     ab_comm* comm = nullptr;
     bool cellm_old = false;            // AB_CELLM_OLD=1: the one-row-per-warp k_cell_M in 2-D too (A/B experiments)
     bool small_scan = false;           // AB_SMALL_SCAN=1: single-CTA scan of the tile totals (A/B experiments)
+    bool no_split_M = false;           // AB_SPLIT_M=0: cell sums in one launch after the install (A/B experiments)
     bool no_side_unpack = false;       // AB_SIDE_UNPACK=0: halo install after the re-sort on the same stream (A/B experiments)
     bool side_unpack_now = false;      // the halo install being queued runs beside the re-sort (one-thread flag wait first)
     bool unpack_tb = false;            // ... or the scanned tile totals do (scan path)

@@ -19,8 +19,8 @@ def _ngpu():
         return 0
 
 
-def _run(world, port, *wargs, halo="direct", overlap="0"):
-    env = dict(os.environ, AB_HALO=halo, AB_OVERLAP=overlap)
+def _run(world, port, *wargs, halo="direct", overlap="0", **extra_env):
+    env = dict(os.environ, AB_HALO=halo, AB_OVERLAP=overlap, **extra_env)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "mgpu_worker.py"), *wargs]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT, env=env)
@@ -74,6 +74,18 @@ def test_two_gpus_pairforce_bitwise_equal_to_one(wargs):
     r = _run(2, 29539, *wargs, "--rule", "pairforce")
     assert r["conserved"] and r["pos_bitwise_equal"] and r["vel_bitwise_equal"], r
     assert r["migrated"] and r["direct"], r
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("wargs", [["--agents", "60000", "--extent", "400", "400", "--steps", "12"],
+                                   ["--agents", "40000", "--extent", "60", "60", "120", "--steps", "8"]], ids=["2d", "3d"])
+def test_two_gpus_separate_pack_and_split_cell_sums(wargs):
+    """Large boundary messages (F3D) are packed by k_halo_pack instead of the re-sort, and the halo install then hides
+    behind the cell sums of the interior rows (k_cell_M split in two launches): forced here on small cases."""
+    if _ngpu() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    r = _run(2, 29541, *wargs, AB_FUSED_PACK="0")
+    assert r["conserved"] and r["pos_bitwise_equal"] and r["vel_bitwise_equal"] and r["direct"], r
 
 
 @pytest.mark.gpu
