@@ -167,13 +167,17 @@ class Slabs:
 
     def scatter_chunks(self, chunks, n_global, halo_capacity=None, capacity_factor=1.6):
         """Like `scatter` for populations too large to materialise on every rank: `chunks` yields
-        (first_id0, pos_chunk, vel_chunk) pieces of the global id-ordered state; only this rank's window
-        of each piece is kept."""
+        (first_id0, pos_chunk, vel_chunk[, {column: chunk}]) pieces of the global id-ordered state; only this rank's
+        window of each piece is kept.  User columns are registered before the receive block is exported."""
+        from .model import _NP2AB
+
         m, lib = self.model, self.model.lib
         dt = m.space.dtype
         self.n_global = int(n_global)
-        keep_ids, keep_p, keep_v, owned_n = [], [], [], 0
-        for first, pos, vel in chunks:
+        keep_ids, keep_p, keep_v, keep_c, owned_n = [], [], [], {}, 0
+        for piece in chunks:
+            first, pos, vel = piece[:3]
+            cols = piece[3] if len(piece) > 3 else {}
             pos = np.ascontiguousarray(pos, dtype=dt).reshape(-1, m.D)
             vel = np.ascontiguousarray(vel, dtype=dt).reshape(-1, m.D)
             layer = cell_layer(pos[:, -1], m.space.spacing, self.n_layers)
@@ -181,16 +185,26 @@ class Slabs:
             keep_ids.append((idx + first + 1).astype(np.int64))
             keep_p.append(pos[idx])
             keep_v.append(vel[idx])
+            for name, a in cols.items():
+                keep_c.setdefault(name, []).append(np.asarray(a).reshape(pos.shape[0], -1)[idx])
             owned_n += int(owned.sum())
         gids = np.concatenate(keep_ids)
         p = np.ascontiguousarray(np.concatenate(keep_p))
         v = np.ascontiguousarray(np.concatenate(keep_v))
+        cols = {name: np.concatenate(parts) for name, parts in keep_c.items()}
+        for name, a in cols.items():
+            if name not in m._columns:
+                fid = m._ck(lib.ab_register_field(m.h, name.encode(), _NP2AB[a.dtype], a.shape[1]))
+                m._columns[name], m._dtypes[name], m._ncomp[name] = fid, a.dtype, a.shape[1]
         cap = halo_capacity or default_halo_capacity(self.n_global, self.n_layers)
         m._ck(lib.ab_comm_set_capacity(m.h, int(cap)))
         self.direct = self._link_direct()
         m._ck(lib.ab_resize(m.h, int(len(gids) * capacity_factor) + 2 * int(cap) + 1024))
         m._ck(lib.ab_upload_local(m.h, 0, m._ptr(p), m._ptr(gids), len(gids)))
         m._ck(lib.ab_upload_local(m.h, 1, m._ptr(v), m._ptr(gids), len(gids)))
+        for name, a in cols.items():
+            c = np.ascontiguousarray(a, dtype=m._dtypes[name])
+            m._ck(lib.ab_upload_local(m.h, m._columns[name], m._ptr(c), m._ptr(gids), len(gids)))
         m._ck(lib.ab_build_index(m.h))
         return owned_n
 

@@ -188,6 +188,28 @@ def particles(n, extent, seed=42, max_radius=10.0, vscale=100.0):
     return pos, vel, (0.5 + 0.9 * w[:, 0]) * max_radius, 10.0 + 20.0 * w[:, 1], 10.0 + 100.0 * w[:, 2]
 
 
+def particle_chunks(n, extent, seed, step, max_radius=10.0, vscale=100.0):
+    """`particles` in id chunks: (first id, pos, vel, {r, k, mass}) — the same numbers for the same ids."""
+    from helpers import splitmix64
+
+    D = len(extent)
+    ext = np.asarray(extent, dtype=np.float64)[None, :]
+
+    def u(first, m, ncomp, stream):
+        with np.errstate(over="ignore"):
+            i = np.arange(first, first + m, dtype=np.uint64)[:, None]
+            c = (np.arange(ncomp, dtype=np.uint64) + np.uint64(stream * 4))[None, :]
+            z = splitmix64(np.uint64(seed) ^ (i * np.uint64(8) + c))
+        return (z >> np.uint64(11)).astype(np.float64) * (2.0 ** -53)
+
+    for first in range(0, n, step):
+        m = min(step, n - first)
+        pos = u(first, m, D, 0) * ext
+        vel = vscale * np.sqrt(-2.0 * np.log(np.maximum(u(first, m, D, 1), 1e-300))) * np.cos(2.0 * np.pi * u(first, m, D, 2))
+        w = u(first, m, 3, 3)
+        yield first, pos, vel, {"r": (0.5 + 0.9 * w[:, 0]) * max_radius, "k": 10.0 + 20.0 * w[:, 1], "mass": 10.0 + 100.0 * w[:, 2]}
+
+
 # ---------------------------------------------------------------------------
 # CPU arm: the oracle port of the reference's own (asynchronous, 1-thread) step
 # ---------------------------------------------------------------------------
@@ -441,6 +463,41 @@ def f3d_weak(ab, lib, dist, local, rank, world, peak, steps=10, warmup=3, per_gp
             "clocks_rank0": clocks}
 
 
+def pf2d_weak(ab, lib, dist, local, rank, world, peak, steps=10, warmup=3):
+    """Pair-force weak-scaling row (the pair-force rule shards too): ~10 M particles per GPU, slabs along y,
+    the r / k / mass columns travel in the boundary messages."""
+    import torch
+    from agents_jl_b200.parallel import Slabs, default_halo_capacity
+
+    side = 791
+    extent = (20.0 * side, 20.0 * side * world)
+    n = int(0.04 * extent[0] * extent[1])
+    m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=20.0, periodic=True), model_step=ab.PairForceRule(dt=0.001, cutoff=20.0), device=local)
+    s = Slabs(m, dist)
+    cap = default_halo_capacity(n, s.n_layers, factor=1.5)
+    s.scatter_chunks(particle_chunks(n, extent, 42, 4_000_000), n, halo_capacity=cap)
+    m.step(warmup)
+    torch.cuda.synchronize()
+    dist.barrier()
+    sampler = ClockSampler(local).start()
+    lib.ab_comm_align(m.h)
+    m.step(steps)
+    ms = m.last_step_ms()
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t[0])
+    m.close()
+    rate = n * steps / (ms * 1e-3)
+    return {"config": f"PF2D-{n / 1e6:.0f}M ({world} x 10M, pair-force rule on slabs)", "agents": n, "n_gpus": world, "extent": list(extent),
+            "steps": steps, "warmup": warmup, "ms_per_step": ms / steps, "value": rate, "unit": "agent-updates/s", "direct": bool(s.direct),
+            "roofline": {"bound": "hbm", "peak": peak, "unit": "GB/s",
+                         "whole_step_per_gpu": {"achieved": ALG_BYTES["pairforce2d_f64"] * rate / world / 1e9,
+                                                "frac": ALG_BYTES["pairforce2d_f64"] * rate / world / 1e9 / peak}},
+            "clocks_rank0": clocks}
+
+
 def run_gpu(args):
     import torch
 
@@ -670,13 +727,14 @@ def run_gpu(args):
         del flush
         torch.cuda.empty_cache()
         configs = config_rows(ab, lib, local, peak, args.config_scale)
-    f3d = None
+    f3d = pf_weak = None
     if world > 1 and not args.no_f3d:
         model.close()
         model = None
         del flush
         torch.cuda.empty_cache()
         f3d = f3d_weak(ab, lib, dist, local, rank, world, peak)
+        pf_weak = pf2d_weak(ab, lib, dist, local, rank, world, peak) if not args.no_pf else None
 
     # ---- CPU baseline on this box's host cores (rank 0, N = 1 only) ------------
     cpu = None
@@ -707,6 +765,7 @@ def run_gpu(args):
             line["halo_wait_us_per_step"] = [p["halo_wait_us_per_step"] for p in per_rank]
             line["start_alignment"] = "device-side all-reduce on the library's stream before the first timed step (ab_comm_align)"
             line["f3d_weak"] = f3d
+            line["pf2d_weak"] = pf_weak
         if configs is not None:
             line["configs"] = configs
         print(json.dumps(line))
@@ -758,7 +817,8 @@ def main():
     ap.add_argument("--no-configs", action="store_true", help="skip the rows of the other BASELINE configurations (N = 1)")
     ap.add_argument("--config-scale", type=float, default=1.0, help="shrink the populations of the config rows (smoke runs)")
     ap.add_argument("--no-parity", action="store_true", help="skip the sharded-vs-unsharded parity gate (N > 1)")
-    ap.add_argument("--no-f3d", action="store_true", help="skip the F3D weak-scaling row (N > 1)")
+    ap.add_argument("--no-f3d", action="store_true", help="skip the F3D and PF2D weak-scaling rows (N > 1)")
+    ap.add_argument("--no-pf", action="store_true", help="skip the PF2D weak-scaling row (N > 1)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
