@@ -148,6 +148,28 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const __grid_constant__ HaloOut ho, co
     const uint32_t kend = kbeg + (uint32_t)fc;
     const int fy0 = D == 2 ? frow : frow % fd1;
     const int fz0 = D == 2 ? 0 : frow / fd1;
+    // ---- source segments: lane i describes segment i = 3*row + {main, left wrap, right wrap} ----
+    // (loaded first: these two reads depend on nothing, and the key stream below depends on them)
+    constexpr int NROW = D == 2 ? 3 : 9;
+    constexpr int NSEG = 3 * NROW;
+    uint32_t sb = 0, sl = 0;
+    if (lane < NSEG) {
+        const int r = lane / 3, j = lane - 3 * r;
+        const int dy = r % 3 - 1, dz = D == 3 ? r / 3 - 1 : 0;
+        int y = fy0 + dy, z = fz0 + dz;
+        bool ok = true;
+        if (y < 0 || y >= fd1) { if (!sp.periodic[1]) ok = false; y = y < 0 ? y + fd1 : y - fd1; }
+        if (D == 3 && (z < 0 || z >= fd2)) { if (!sp.periodic[2]) ok = false; z = z < 0 ? z + fd2 : z - fd2; }
+        const int lo = max(x0 - 1, 0), hi = min(x1, fd0 - 1);      // inclusive fine cells of the main run
+        int c0 = lo, c1 = hi + 1;                                  // [c0, c1) cells of this segment
+        if (j == 1) { ok = ok && sp.periodic[0] && x0 == 0 && hi < fd0 - 1; c0 = fd0 - 1; c1 = fd0; }
+        if (j == 2) { ok = ok && sp.periodic[0] && x1 == fd0 && lo > 0; c0 = 0; c1 = 1; }
+        if (ok) {
+            const size_t rb = (size_t)(D == 3 ? (uint32_t)z * (uint32_t)fd1 + (uint32_t)y : (uint32_t)y) * (uint32_t)fd0;
+            sb = cs_old[rb + c0];
+            sl = cs_old[rb + c1] - sb;
+        }
+    }
     // sum of the row counters [r0, r1) over the warp (scan-free path)
     auto rows_sum = [&](int r0, int r1) -> uint32_t {
         uint32_t part = 0;
@@ -211,27 +233,6 @@ k_resort(SpaceDev<T, D> sp, ResortArgs a, const __grid_constant__ HaloOut ho, co
                 if (cnt[q]) cell_count[(size_t)kbeg + i0 + q] = 0;
                 run += cnt[q];
             }
-        }
-    }
-    // ---- source segments: lane i describes segment i = 3*row + {main, left wrap, right wrap} ----
-    constexpr int NROW = D == 2 ? 3 : 9;
-    constexpr int NSEG = 3 * NROW;
-    uint32_t sb = 0, sl = 0;
-    if (lane < NSEG) {
-        const int r = lane / 3, j = lane - 3 * r;
-        const int dy = r % 3 - 1, dz = D == 3 ? r / 3 - 1 : 0;
-        int y = fy0 + dy, z = fz0 + dz;
-        bool ok = true;
-        if (y < 0 || y >= fd1) { if (!sp.periodic[1]) ok = false; y = y < 0 ? y + fd1 : y - fd1; }
-        if (D == 3 && (z < 0 || z >= fd2)) { if (!sp.periodic[2]) ok = false; z = z < 0 ? z + fd2 : z - fd2; }
-        const int lo = max(x0 - 1, 0), hi = min(x1, fd0 - 1);      // inclusive fine cells of the main run
-        int c0 = lo, c1 = hi + 1;                                  // [c0, c1) cells of this segment
-        if (j == 1) { ok = ok && sp.periodic[0] && x0 == 0 && hi < fd0 - 1; c0 = fd0 - 1; c1 = fd0; }
-        if (j == 2) { ok = ok && sp.periodic[0] && x1 == fd0 && lo > 0; c0 = 0; c1 = 1; }
-        if (ok) {
-            const size_t rb = (size_t)(D == 3 ? (uint32_t)z * (uint32_t)fd1 + (uint32_t)y : (uint32_t)y) * (uint32_t)fd0;
-            sb = cs_old[rb + c0];
-            sl = cs_old[rb + c1] - sb;
         }
     }
     uint32_t inc = sl;
