@@ -32,13 +32,16 @@ cpu_baseline: the CPU oracle's reference-faithful asynchronous step
          reference's step! is single-threaded) on a bounded sample.
 With --gpus N > 1 (torchrun): weak scaling, 1M boids per GPU, slab decomposition
 along y, halo / migration exchange by direct peer-memory stores (AB_HALO=nccl:
-ncclSend/ncclRecv).  Before the timed region the ranks run a reduced sharded case
-(2-D and 3-D) and compare the gathered state with an unsharded run on rank 0:
-`parity_check.bitwise_equal` (the process exits non-zero on a mismatch).  The timed
-call starts behind a device-side all-reduce (ab_comm_align) so rank launch skew is
-not charged to the K steps; `halo_wait_us_per_step` says how long each rank's halo
-install waited for its neighbours.  `f3d_weak` is the F3D row of BASELINE configs[4]:
-12.5 M boids per GPU, slabs along z (8 GPUs = F3D-100M).
+ncclSend/ncclRecv).  Before the timed region the ranks run reduced sharded cases
+(flock 2-D, flock 3-D, pair force 2-D) and compare the gathered state with an
+unsharded run on rank 0: `parity_check.bitwise_equal` (the process exits non-zero
+on a mismatch).  The timed call starts behind a device-side all-reduce
+(ab_comm_align) so rank launch skew is not charged to the K steps;
+`halo_wait_us_per_step` says how long each rank's halo install waited for its
+neighbours.  `f3d_weak` is the F3D row of BASELINE configs[4]: 12.5 M boids per
+GPU, slabs along z (8 GPUs = F3D-100M); `pf2d_weak` the pair-force rule on slabs,
+10 M particles per GPU; `e2e` the host-buffer leg of the sharded model (every rank
+uploads / downloads the rows it owns, collective halo refresh in between).
 """
 import argparse
 import ctypes as C
