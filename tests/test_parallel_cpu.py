@@ -121,3 +121,22 @@ def test_gather_over_gloo_world_size_2():
         assert p.exitcode == 0
     assert sorted(r[0] for r in res) == [0, 1]
     assert all(r[1] and r[2] == 128 for r in res)
+
+
+def test_chunked_generators_equal_the_whole_state():
+    """bench.py builds the 100 M-boid / 80 M-particle states in id chunks: the chunks must be the same numbers as the
+    one-shot generators the single-GPU rows and the parity tests use."""
+    import bench
+
+    extent = (100.0, 200.0)
+    a = bench.particles(1000, extent)
+    parts = list(bench.particle_chunks(1000, extent, 42, 300))
+    assert [p[0] for p in parts] == [0, 300, 600, 900]
+    assert np.array_equal(np.concatenate([p[1] for p in parts]), a[0])
+    assert np.array_equal(np.concatenate([p[2] for p in parts]), a[1])
+    for name, col in zip(("r", "k", "mass"), a[2:]):
+        assert np.array_equal(np.concatenate([p[3][name] for p in parts]), col)
+    pos, vel = flock_init(1000, (50.0, 60.0, 70.0), 42)
+    fparts = list(bench.flock_chunks(1000, (50.0, 60.0, 70.0), 42, 256))
+    assert np.array_equal(np.concatenate([p[1] for p in fparts]), pos)
+    assert np.array_equal(np.concatenate([p[2] for p in fparts]), vel)
