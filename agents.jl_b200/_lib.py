@@ -97,6 +97,8 @@ _SIGS = {
     "ab_step_schelling_active": (C.c_int, [_H, C.POINTER(SchellingParams), C.c_int64, C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]),
     "ab_flock_last_counts": (C.c_int, [_H, C.c_void_p, C.c_int64]),
     "ab_reduce": (C.c_int, [_H, C.POINTER(ReduceSpec), C.c_int, C.c_void_p, C.c_void_p]),
+    "ab_reduce_static": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_int, C.c_void_p, C.c_int, C.c_int,
+                                   C.c_double, C.c_void_p, C.c_void_p]),
     "ab_ids_by_property": (C.c_int, [_H, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int64]),
     "ab_comm_unique_id": (C.c_int, [C.c_void_p]),
     "ab_comm_init": (C.c_int, [_H, C.c_int, C.c_int, C.c_void_p]),

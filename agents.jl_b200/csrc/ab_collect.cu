@@ -14,6 +14,7 @@
 // results exactly.  On a sharded handle the aggregate covers the OWNED agents of the rank (the host adds
 // the ranks' partial results).
 #include <algorithm>
+#include <mutex>
 
 #include "ab_internal.cuh"
 
@@ -257,4 +258,161 @@ extern "C" int ab_ids_by_property(ab_handle* h, int field, int comp, int descend
     }
     AB_CUDA(h, cudaMemcpyAsync(out_ids, dout, (size_t)n * sizeof(int64_t), cudaMemcpyDeviceToHost, h->stream));
     return ab_check_device_errors_now(h);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// ab_reduce_static — the chunked reduction above for callers that must not allocate device memory.
+//
+// Who that is: a Julia session whose CUDA.jl pool (or a Python process whose torch caching allocator)
+// already owns nearly all of the GPU, so that a cudaMalloc made behind the pool's back can fail although
+// the pool still has free blocks; an ensemble driver with several models in flight, where the implicit
+// device-wide synchronisation of cudaMalloc / cudaFree would stall every other model's stream; a process
+// confined to a fixed memory budget (a MIG slice, an MPS client with a memory limit).  Such a caller
+// holds its columns in memory it got from its own pool and cannot create an ab_handle (ab_create and the
+// handle's grow-only scratch allocate).  Here it passes device pointers for the column and for the two
+// results; the per-chunk partial results — the only scratch this reduction needs — live in the array
+// below, which is part of the library image: every GPU that loads libagents_b200.so carries these
+// 256 KiB from the moment the module is loaded until the process exits, whether or not this entry point
+// is ever called.
+//
+// The array is shared by every call on a device.  It keeps whatever the previous call left there; that
+// is harmless because the first kernel writes partial[0 .. nchunks) and the second reads exactly that
+// range — nothing has to start at zero, nothing is cleared.  Two calls whose kernels can run at the same
+// time on one GPU (different streams, or different host threads using different streams) would write
+// the same partials: the caller has to order them (same stream, or an event between them).
+// ---------------------------------------------------------------------------------------------------
+#define AB_STATIC_MAX_N (1 << 26)                                   // 67 108 864 values per call
+#define AB_STATIC_MAX_CHUNKS (AB_STATIC_MAX_N / RED_CHUNK)          // 16 384 partials
+#define AB_STATIC_BYTES ((size_t)AB_STATIC_MAX_CHUNKS * 16)         // value + count per partial: 256 KiB
+#define AB_STATIC_MAX_DEVICES 64
+
+static __device__ __align__(256) unsigned char g_reduce_static_scratch[AB_STATIC_BYTES];
+
+// In host code the name g_reduce_static_scratch is only a token the runtime maps to the device copies; its
+// host-side address is not device memory.  The address a kernel may use is asked for once per device, with
+// that device current, and remembered here.
+static void* g_static_addr[AB_STATIC_MAX_DEVICES];
+static std::mutex g_static_mu;
+
+static int static_scratch_address(int device, void** out) {
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_addr[device]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_reduce_static_scratch);   // the current device's copy
+        if (e != cudaSuccess) return ab_cuda_fail(nullptr, e, "cudaGetSymbolAddress(g_reduce_static_scratch)");
+        if (!p) return ab_fail(nullptr, AB_ERR_CUDA, "ab_reduce_static: the scratch array has no device address");
+        g_static_addr[device] = p;
+    }
+    *out = g_static_addr[device];
+    return AB_OK;
+}
+
+// k_reduce_chunks for one triple handed over as a kernel argument (no spec table in device memory)
+__global__ void __launch_bounds__(RED_THREADS)
+k_reduce_chunks_static(const RedSpecDev sp, int n, double* __restrict__ pval, unsigned long long* __restrict__ pcnt) {
+    __shared__ double s_v[RED_THREADS / 32];
+    __shared__ unsigned long long s_c[RED_THREADS / 32];
+    const int base = blockIdx.x * RED_CHUNK + threadIdx.x;
+    double acc = red_identity(sp.op);
+    unsigned long long cnt = 0;
+#pragma unroll 4
+    for (int i = 0; i < RED_ITEMS; ++i) {
+        const int s = base + i * RED_THREADS;
+        if (s < n && red_pass(sp, s)) {
+            ++cnt;
+            if (sp.op != AB_RED_COUNT) acc = red_combine(sp.op, acc, red_load(sp.col, sp.dtype, s));
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        acc = red_combine(sp.op, acc, __shfl_xor_sync(0xffffffffu, acc, o));
+        cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    }
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (lane == 0) { s_v[wid] = acc; s_c[wid] = cnt; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = s_v[0];
+        unsigned long long c = s_c[0];
+        for (int w = 1; w < RED_THREADS / 32; ++w) { a = red_combine(sp.op, a, s_v[w]); c += s_c[w]; }
+        pval[blockIdx.x] = a;
+        pcnt[blockIdx.x] = c;
+    }
+}
+
+// k_reduce_final for that triple: one block, partials in chunk order, results to the caller's device words
+__global__ void __launch_bounds__(RED_THREADS)
+k_reduce_final_static(int op, int nchunks, const double* __restrict__ pval, const unsigned long long* __restrict__ pcnt,
+                      double* __restrict__ out, long long* __restrict__ ocnt) {
+    __shared__ double s_v[RED_THREADS];
+    __shared__ unsigned long long s_c[RED_THREADS];
+    double acc = red_identity(op);
+    unsigned long long cnt = 0;
+    for (int i = threadIdx.x; i < nchunks; i += RED_THREADS) {
+        acc = red_combine(op, acc, pval[i]);
+        cnt += pcnt[i];
+    }
+    s_v[threadIdx.x] = acc;
+    s_c[threadIdx.x] = cnt;
+    __syncthreads();
+    for (int o = RED_THREADS / 2; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) {
+            s_v[threadIdx.x] = red_combine(op, s_v[threadIdx.x], s_v[threadIdx.x + o]);
+            s_c[threadIdx.x] += s_c[threadIdx.x + o];
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        double v = s_v[0];
+        const unsigned long long c = s_c[0];
+        if (op == AB_RED_COUNT) v = (double)c;
+        else if (op == AB_RED_MEAN) v = c ? v / (double)c : __longlong_as_double(0x7ff8000000000000LL);
+        *out = v;
+        if (ocnt) *ocnt = (long long)c;
+    }
+}
+
+// Everything is queued on `stream` (NULL: the default stream) and the call returns without waiting: *d_out and
+// *d_count are valid once the stream has reached this point.  The first call on a device looks up the device
+// address of the scratch array (see above) — make that first call before starting any stream capture.  No
+// cudaMalloc, cudaFree or other allocating routine is called; messages of failures are read with
+// ab_last_error(NULL).
+extern "C" int ab_reduce_static(int device, void* stream, const void* d_col, int dtype, int64_t n, int op,
+                                const void* d_filter_col, int filter_dtype, int filter_cmp, double filter_value,
+                                double* d_out, int64_t* d_count) {
+    if (!d_out) return ab_fail(nullptr, AB_ERR_INVALID, "ab_reduce_static: d_out is NULL");
+    if (device < 0 || device >= AB_STATIC_MAX_DEVICES) return ab_fail(nullptr, AB_ERR_INVALID, "ab_reduce_static: device must be 0..63");
+    if (n < 0) return ab_fail(nullptr, AB_ERR_INVALID, "ab_reduce_static: negative length");
+    if (n > AB_STATIC_MAX_N)
+        return ab_fail(nullptr, AB_ERR_INVALID, "ab_reduce_static: " + std::to_string(n) + " values exceed the fixed scratch of this entry point (" +
+                       std::to_string((long long)AB_STATIC_MAX_N) + " values, 2^26); split the column or use ab_reduce on a handle");
+    if (op < AB_RED_SUM || op > AB_RED_COUNT) return ab_fail(nullptr, AB_ERR_INVALID, "ab_reduce_static: unknown aggregator");
+    if (dtype < AB_F64 || dtype > AB_U8) return ab_fail(nullptr, AB_ERR_INVALID, "ab_reduce_static: unknown column dtype");
+    if (n > 0 && !d_col && op != AB_RED_COUNT) return ab_fail(nullptr, AB_ERR_INVALID, "ab_reduce_static: d_col is NULL");
+    if (filter_cmp != AB_CMP_NONE) {
+        if (filter_cmp < AB_CMP_EQ || filter_cmp > AB_CMP_GE) return ab_fail(nullptr, AB_ERR_INVALID, "ab_reduce_static: unknown filter comparison");
+        if (filter_dtype < AB_F64 || filter_dtype > AB_U8) return ab_fail(nullptr, AB_ERR_INVALID, "ab_reduce_static: unknown filter dtype");
+        if (n > 0 && !d_filter_col) return ab_fail(nullptr, AB_ERR_INVALID, "ab_reduce_static: filter comparison without a filter column");
+    }
+    int prev = -1;
+    AB_CUDA(nullptr, cudaGetDevice(&prev));
+    if (prev != device) AB_CUDA(nullptr, cudaSetDevice(device));
+    void* scratch = nullptr;
+    int rc = static_scratch_address(device, &scratch);
+    if (rc == AB_OK) {
+        RedSpecDev sp;
+        sp.col = d_col; sp.dtype = dtype; sp.op = op;
+        sp.fcol = filter_cmp != AB_CMP_NONE ? d_filter_col : nullptr;
+        sp.fdtype = filter_dtype; sp.fcmp = filter_cmp; sp.fval = filter_value;
+        const int nchunks = (int)std::max<int64_t>((n + RED_CHUNK - 1) / RED_CHUNK, 1);
+        double* pval = (double*)scratch;
+        unsigned long long* pcnt = (unsigned long long*)((char*)scratch + (size_t)AB_STATIC_MAX_CHUNKS * 8);
+        const cudaStream_t st = (cudaStream_t)stream;
+        k_reduce_chunks_static<<<nchunks, RED_THREADS, 0, st>>>(sp, (int)n, pval, pcnt);
+        k_reduce_final_static<<<1, RED_THREADS, 0, st>>>(op, nchunks, pval, pcnt, d_out, (long long*)d_count);
+        const cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) rc = ab_cuda_fail(nullptr, e, "ab_reduce_static launches");
+    }
+    if (prev != device) cudaSetDevice(prev);
+    return rc;
 }

@@ -292,6 +292,32 @@ int ab_reduce(ab_handle* h, const ab_reduce_spec* specs, int nspec, double* out,
  * result).  Sorted on the device (bitonic network over (key, id) pairs); n ids come back. */
 int ab_ids_by_property(ab_handle* h, int field, int comp, int descending, int64_t* out_ids, int64_t n);
 
+/* The chunked reduction of ab_reduce for ONE (column, aggregator, filter) triple, for callers that must not
+ * allocate device memory.  It has no counterpart in the reference (Agents.jl aggregates on the host heap,
+ * collect.jl:466-502) and exists for hosts that cannot afford a cudaMalloc: a Julia session whose CUDA.jl pool (or a
+ * Python process whose torch allocator) already owns almost the whole GPU, so an allocation made behind the pool's
+ * back may fail while the pool still has room; an ensemble driver whose other models would all stall on the
+ * device-wide synchronisation a cudaMalloc / cudaFree implies; a process inside a fixed memory budget (MIG slice,
+ * MPS memory limit).  Such a caller cannot create a handle either (ab_create and a handle's scratch allocate), so
+ * this call takes no handle:
+ *   d_col        n values of `dtype` (AB_F64 .. AB_U8) in DEVICE memory of `device`, from the caller's own pool;
+ *   d_filter_col n values of `filter_dtype`, or NULL with filter_cmp = AB_CMP_NONE;
+ *   d_out        one double in device memory: the aggregate (mean over no value: NaN);
+ *   d_count      one int64 in device memory or NULL: how many values passed the filter;
+ *   stream       a cudaStream_t of that device (NULL: the default stream).  The work is queued there and the call
+ *                returns without waiting; the results are valid in stream order.
+ * The per-chunk partial results sit in a fixed 256 KiB array inside the library image — every GPU that loads the
+ * library holds it until the process exits — which bounds n at 2^26 = 67 108 864 values per call; a longer column is
+ * refused with AB_ERR_INVALID (split it, or use ab_reduce).  The call itself performs no cudaMalloc, cudaFree or any
+ * other allocation.  All calls on one GPU share that array: calls that may overlap on the device (different streams
+ * without an event between them) race and must be ordered by the caller; nothing in it needs clearing between
+ * calls.  The first call on each device looks up the array's device address — make that call before any stream
+ * capture begins.  Failure text: ab_last_error(NULL).  Same value as ab_reduce up to the order of the sum (ab_reduce
+ * walks the handle's slot order, this walks the caller's array order). */
+int ab_reduce_static(int device, void* stream, const void* d_col, int dtype, int64_t n, int op,
+                     const void* d_filter_col, int filter_dtype, int filter_cmp, double filter_value,
+                     double* d_out, int64_t* d_count);
+
 /* ---- multi-GPU slabs (one process per GPU) -----------------------------------
  * The reference is single-task (step_standard.jl:9-23); this is its scale-out
  * (SURVEY 8e).  Slabs of whole cell layers along the LAST axis (periodic); each
