@@ -24,6 +24,8 @@
 // (paths relative to the Agents.jl tree).
 
 #include <atomic>
+#include <mutex>
+#include <memory>
 #include <thread>
 #include <algorithm>
 #include <array>
@@ -171,12 +173,15 @@ template <class T> struct CModel : ModelBase {
     int64_t n = 0;
     // space.offsets_within_radius: tables cached by floor(r+1) like the reference
     // (grid_general.jl:98-110) so the timed CPU baseline does not rebuild them per query
-    mutable std::vector<std::vector<Off>> offs_cache;
+    // The workers of flock_step_sync call this concurrently on a fresh model: the table of a radius is built exactly
+    // once (call_once) into a slot that never moves (the outer vector is sized up front, never resized).
+    static constexpr size_t OFFS_SLOTS = 4097;
+    mutable std::vector<std::vector<Off>> offs_cache = std::vector<std::vector<Off>>(OFFS_SLOTS);
+    mutable std::unique_ptr<std::once_flag[]> offs_once{new std::once_flag[OFFS_SLOTS]};
     const std::vector<Off>& cached_offsets(int64_t gr) const {
         size_t i = (size_t)std::max<int64_t>(gr, 0);
-        if (gr < 0 || i > 4096) { static thread_local std::vector<Off> tmp; tmp = offsets_within_radius(D, dims, periodic, 2, (double)gr, false); return tmp; }
-        if (offs_cache.size() <= i) offs_cache.resize(i + 1);
-        if (offs_cache[i].empty()) offs_cache[i] = offsets_within_radius(D, dims, periodic, 2, (double)gr, false);
+        if (gr < 0 || i >= OFFS_SLOTS) { static thread_local std::vector<Off> tmp; tmp = offsets_within_radius(D, dims, periodic, 2, (double)gr, false); return tmp; }
+        std::call_once(offs_once[i], [&] { offs_cache[i] = offsets_within_radius(D, dims, periodic, 2, (double)gr, false); });
         return offs_cache[i];
     }
 
