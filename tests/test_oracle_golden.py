@@ -481,3 +481,28 @@ def test_rotate_restatement():
         assert abs(np.linalg.norm(v) - np.linalg.norm(w)) < 1e-12
     assert np.allclose(rotate2(np.array([1.0, 0.0]), np.pi / 2), [0.0, 1.0], atol=1e-15)
     assert np.allclose(rotate3(np.array([0.0, 0.0, 2.0]), 0.0, 1.3), [0.0, 0.0, 2.0], atol=1e-15)
+
+
+# ---- rows without a vector in the reference's test-suite: known answers worked out by hand from the source ----------
+def test_pairforce_known_answers():
+    """examples/celllistmap.jl:143-155 (calc_forces!) + :176-191 (agent_step!): two- and three-particle systems, one
+    pair across the periodic edge, one pair beyond r_i + r_j (tests/known_answers.py has the arithmetic)."""
+    import known_answers as ka
+
+    for k, pos1, vel1 in ((2, ka.PF2_POS1, ka.PF2_VEL1), (3, ka.PF3_POS1, ka.PF3_VEL1)):
+        o = ContinuousOracle(ka.PF_EXTENT, spacing=ka.PF_SPACING)
+        o.add_agents(ka.PF_POS[:k], ka.PF_VEL[:k])
+        o.pairforce_step(ka.PF_R[:k], ka.PF_K[:k], ka.PF_MASS[:k], ka.PF_DT, ka.PF_CUTOFF, nsteps=1)
+        pos, vel = o.state()[:2]
+        assert np.max(np.abs(pos - pos1)) <= ka.PF_TOL and np.max(np.abs(vel - vel1)) <= ka.PF_TOL
+
+
+def test_spatial_index_known_answers():
+    """get_spatial_index, src/spaces/continuous.jl:566-573: positions on property-cell edges, a property of lower
+    dimension than the space, and pos == extent (index size + 1: the reference's BoundsError)."""
+    import known_answers as ka
+    from oracle.pyoracle import spatial_index
+
+    assert np.array_equal(spatial_index(ka.SI_POS, ka.SI_EXTENT, (5, 3)), ka.SI_IDX_5x3)
+    assert np.array_equal(spatial_index(ka.SI_POS, ka.SI_EXTENT, (4,)), ka.SI_IDX_4)
+    assert spatial_index(ka.SI_POS_AT_EXTENT, ka.SI_EXTENT, (5, 3))[0, 0] == 6      # one past the property's 5 rows
