@@ -281,16 +281,31 @@ class StandardABM:
         self._ck(self.lib.ab_upload(self.h, self._columns[name], self._ptr(a), n))
         return self._columns[name]
 
+    def _is_spatial_column(self, name):
+        return self.space.kind == L.SPACE_CONTINUOUS and name in ("pos", "vel")
+
     def set_column(self, name, values):
         n = self.nagents()
-        a = np.ascontiguousarray(values, dtype=self._dtypes[name]).reshape(n, self._ncomp[name])
+        if self._is_spatial_column(name):
+            a = self._rows_in(values, fill=0.5 * self.space.spacing if name == "pos" else 0.0)
+            if a.shape[0] != n:
+                raise AgentsError(L.ERR_INVALID, f"set_column({name!r}): one row per agent")
+        else:
+            a = np.ascontiguousarray(values, dtype=self._dtypes[name]).reshape(n, self._ncomp[name])
         self._ck(self.lib.ab_upload(self.h, self._columns[name], self._ptr(a), n))
 
-    def column(self, name):
+    def _column_raw(self, name):
+        """the device column as stored (checkpoints: D device components, Float16 agents still in Float32)."""
         n = self.nagents()
         out = np.zeros((n, self._ncomp[name]), dtype=self._dtypes[name])
         self._ck(self.lib.ab_download(self.h, self._columns[name], self._ptr(out), n))
         return out if self._ncomp[name] > 1 else out[:, 0]
+
+    def column(self, name):
+        out = self._column_raw(name)
+        if self._is_spatial_column(name):
+            return self._rows_out(out)            # (n, user_D) of the caller's float type, also on an embedded 1-D space
+        return out
 
     @property
     def pos(self):
@@ -410,13 +425,28 @@ class StandardABM:
     # -- spatial fields ---------------------------------------------------------
     def _field_args(self, prop):
         prop = np.asarray(prop, dtype=np.float64)
-        return prop, np.ascontiguousarray(prop.shape, dtype=np.int64)
+        return prop, self._field_dims(prop.shape)
+
+    def _field_dims(self, shape):
+        """dimensions of a spatial property: at most the space's own D (1 on an embedded 1-D space)."""
+        dims = np.ascontiguousarray(shape, dtype=np.int64).reshape(-1)
+        ud = getattr(self.space, "user_D", self.D)
+        if not 1 <= len(dims) <= ud:
+            raise AgentsError(L.ERR_INVALID, f"a spatial property of a {ud}-D space has 1..{ud} dimensions, got {len(dims)}")
+        return dims
+
+    def _query_rows(self, positions):
+        if positions is None:
+            return None
+        if self.space.kind == L.SPACE_CONTINUOUS:
+            return self._rows_in(positions, fill=0.5 * self.space.spacing)
+        return np.ascontiguousarray(positions, dtype=self.space.dtype).reshape(-1, self.D)
 
     def get_spatial_index(self, shape, positions=None):
         """get_spatial_index(pos, property, model) (continuous.jl:566-573) for all agents (id order) or for
         `positions`: (n, len(shape)) 1-based indices into an array of `shape`."""
-        dims = np.ascontiguousarray(shape, dtype=np.int64)
-        q = None if positions is None else np.ascontiguousarray(positions, dtype=self.space.dtype).reshape(-1, self.D)
+        dims = self._field_dims(shape)
+        q = self._query_rows(positions)
         n = self.nagents() if q is None else len(q)
         out = np.zeros((max(n, 1), len(dims)), dtype=np.int64)
         self._ck(self.lib.ab_spatial_lookup(self.h, self._ptr(dims), len(dims), None, 0, self._ptr(q) if q is not None else None,
@@ -427,7 +457,7 @@ class StandardABM:
         """get_spatial_property(pos, property::AbstractArray, model) (continuous.jl:545-548), batched."""
         prop, dims = self._field_args(prop)
         flat = np.ascontiguousarray(prop.ravel(order="F"))
-        q = None if positions is None else np.ascontiguousarray(positions, dtype=self.space.dtype).reshape(-1, self.D)
+        q = self._query_rows(positions)
         n = self.nagents() if q is None else len(q)
         out = np.zeros(max(n, 1), dtype=np.float64)
         self._ck(self.lib.ab_spatial_lookup(self.h, self._ptr(dims), len(dims), self._ptr(flat), 1,
@@ -438,9 +468,13 @@ class StandardABM:
         """The force-field `update_vel!` hook (continuous.jl:86-91): vel += scale * field[index(pos)], where
         `field` has shape property_shape + (D,)."""
         field = np.asarray(field, dtype=np.float64)
-        dims = np.ascontiguousarray(field.shape[:-1], dtype=np.int64)
-        assert field.shape[-1] == self.D
-        flat = np.ascontiguousarray(np.concatenate([field[..., d].ravel(order="F") for d in range(self.D)]))
+        ud = getattr(self.space, "user_D", self.D)
+        if field.ndim < 2 or field.shape[-1] != ud:
+            raise AgentsError(L.ERR_INVALID, f"update_vel!: the field's last axis holds the {ud} velocity components")
+        dims = self._field_dims(field.shape[:-1])
+        comps = [field[..., d].ravel(order="F") for d in range(ud)]
+        comps += [np.zeros_like(comps[0])] * (self.D - ud)        # embedded 1-D space: no force across the row
+        flat = np.ascontiguousarray(np.concatenate(comps))
         a = np.ascontiguousarray(ids, dtype=np.int64) if ids is not None else None
         self._ck(self.lib.ab_update_vel_field(self.h, self._ptr(dims), len(dims), self._ptr(flat), float(scale),
                                               self._ptr(a) if a is not None else None, 0 if a is None else len(a)))
@@ -468,6 +502,8 @@ class StandardABM:
         """randomwalk!(agent, model[, r]; polar, azimuthal) on a ContinuousSpace (walk.jl:236-330): `polar` /
         `azimuthal` are the angles drawn for the walking agents (arrays, or callables k -> k angles, e.g. a
         distribution's sampler); the velocity is rotated by them, scaled to length r when r is given, and walked."""
+        if getattr(self.space, "user_D", self.D) == 1:
+            raise AgentsError(L.ERR_INVALID, "randomwalk! with angles needs a 2-D or 3-D ContinuousSpace (walk.jl:236-330)")
         n = self.nagents()
         a = np.ascontiguousarray(ids, dtype=np.int64) if ids is not None else None
         k = n if a is None else a.shape[0]
@@ -632,7 +668,7 @@ class StandardABM:
         elif rule is not None:
             raise TypeError("only the device rules can be checkpointed")
         for name in self._columns:
-            arrays["col_" + name] = self.column(name)
+            arrays["col_" + name] = self._column_raw(name)
         order = np.zeros(n, dtype=np.int64)
         K, tick = C.c_int32(1), C.c_int64(0)
         self._ck(self.lib.ab_layout_get(self.h, self._ptr(order), n, C.byref(K), C.byref(tick)))

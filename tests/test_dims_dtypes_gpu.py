@@ -80,6 +80,37 @@ def test_one_dimensional_space(periodic):
     m.close()
 
 
+def test_one_dimensional_space_spatial_fields():
+    """get_spatial_index / get_spatial_property / the update_vel! field (continuous.jl:86-91, 545-573) on a 1-D space:
+    rows are (n, 1) like every other 1-D call — the device's padded second coordinate never shows."""
+    L, spacing, n, cells = 100.0, 2.5, 1501, 8                     # odd n: a (n, 1) array cannot be read as (n / 2, 2)
+    pos = uniform(n, 1, 21, 0) * L
+    vel = uniform(n, 1, 21, 1) - 0.5
+    m = ab.StandardABM(ab.ContinuousSpace((L,), spacing=spacing))
+    m.add_agents(pos, vel)
+    assert m.column("pos").shape == (n, 1) and np.array_equal(m.column("pos"), pos)
+    want = np.floor(pos[:, 0] / (L / cells)).astype(np.int64) + 1   # floor(Int, pos / eps) + 1, continuous.jl:566-573
+    assert np.array_equal(m.get_spatial_index((cells,))[:, 0], want)
+    q = uniform(333, 1, 22, 0) * L
+    wq = np.floor(q[:, 0] / (L / cells)).astype(np.int64) + 1
+    assert np.array_equal(m.get_spatial_index((cells,), positions=q)[:, 0], wq)
+    prop = uniform(cells, 1, 23)[:, 0]
+    assert np.array_equal(m.get_spatial_property(prop), prop[want - 1])
+    assert np.array_equal(m.get_spatial_property(prop, positions=q), prop[wq - 1])
+    field = (uniform(cells, 1, 24) - 0.5).reshape(cells, 1)
+    m.update_vel_field(field, 0.5)
+    assert np.array_equal(m.vel, vel + 0.5 * field[want - 1])
+    m.set_column("vel", vel)
+    assert np.array_equal(m.vel, vel)
+    with pytest.raises(ab.AgentsError):
+        m.get_spatial_index((cells, 2))                             # a 2-D property over a 1-D space
+    with pytest.raises(ab.AgentsError):
+        m.update_vel_field(np.zeros((cells, 2)), 1.0)               # two velocity components
+    with pytest.raises(ab.AgentsError):
+        m.randomwalk_angles(np.zeros(n))
+    m.close()
+
+
 def test_float16_agents_reference_testset():
     """test/continuous_space_tests.jl:606-637 ("different continuous agent types") for T = Float16."""
     T = np.float16
