@@ -119,6 +119,7 @@ _SIGS = {
     "ab_upload_local": (C.c_int, [_H, C.c_int, C.c_void_p, C.c_void_p, C.c_int64]),
     "ab_launch_count": (C.c_int64, [_H]),
     "ab_last_step_ms": (C.c_double, [_H]),
+    "ab_fp64_peak": (C.c_int, [C.c_int, C.POINTER(C.c_double)]),
     "ab_set_profiling": (C.c_int, [_H, C.c_int]),
     "ab_kernel_times": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
 }

@@ -233,6 +233,7 @@ extern "C" int ab_ids_by_property(ab_handle* h, int field, int comp, int descend
     if (comp < 0 || comp >= f.ncomp) return ab_fail(h, AB_ERR_INVALID, "bad component");
     if (n == 0) return AB_OK;
     if (!out_ids) return ab_fail(h, AB_ERR_INVALID, "null output");
+    if (n > ((int64_t)1 << 30)) return ab_fail(h, AB_ERR_INVALID, "ab_ids_by_property sorts at most 2^30 agents (32-bit padded network)");
     AB_CUDA(h, cudaSetDevice(h->device));
     if (h->grid_cols_dirty) AB_TRY(ab_grid_sync_columns(h));
     int npad = 1;

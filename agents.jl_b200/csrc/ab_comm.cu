@@ -239,8 +239,14 @@ k_halo_pack(MsgLayout m, MsgCols xc, uint32_t kown, const uint32_t* __restrict__
     }
 }
 
-// Spins until *f == epoch (a neighbour's k_halo_pack has delivered); gives up after ~10 s (dead peer).
+// How long a rank waits for a neighbour's message before it calls the peer dead.  A neighbour that is merely busy on the
+// host (a checkpoint, a collect, the chunked scatter of a 100 M-agent state) must not trip it, so the default is generous;
+// AB_HALO_TIMEOUT_S (seconds, read when the direct exchange is set up) overrides it.
+__device__ unsigned long long g_halo_timeout_ns = 120000000000ull;
+
+// Spins until *f == epoch (a neighbour's k_halo_pack has delivered); gives up after g_halo_timeout_ns (dead peer).
 __device__ __forceinline__ bool wait_flag(const uint32_t* f, uint32_t epoch) {
+    const unsigned long long limit = g_halo_timeout_ns;
     unsigned long long t0, t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
     for (;;) {
@@ -248,7 +254,7 @@ __device__ __forceinline__ bool wait_flag(const uint32_t* f, uint32_t epoch) {
         asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
         if (v == epoch) return true;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-        if (t - t0 > 10000000000ull) return false;
+        if (t - t0 > limit) return false;
         __nanosleep(100);
     }
 }
@@ -505,6 +511,8 @@ int ab_comm_pack_begin(ab_handle* h, HaloOut* out) {
     ab_comm* c = h->comm;
     out->enabled = 0;
     if (!c || !h->win_W) return ab_fail(h, AB_ERR_STATE, "handle is not sharded");
+    if (h->halo_stale)
+        return ab_fail(h, AB_ERR_COMM, "a halo message timed out earlier: the window's halo layers are stale; every rank must call ab_comm_exchange before stepping again");
     AB_TRY(ensure_buffers(h));
     if (h->fields.size() > 2u + AB_MSG_MAXF) return ab_fail(h, AB_ERR_INVALID, "too many user columns for the halo message");
     const uint32_t ncs = (uint32_t)(AB_HALO_W * keys_per_layer(h));
@@ -823,6 +831,13 @@ int ab_comm_ipc_import(ab_handle* h, const void* lower64, const void* upper64) {
             c->ipc_upper = (char*)p;
         }
     }
+    if (const char* e = getenv("AB_HALO_TIMEOUT_S")) {
+        const double s = atof(e);
+        if (s > 0) {
+            const unsigned long long ns = (unsigned long long)(s * 1e9);
+            AB_CUDA(h, cudaMemcpyToSymbol(g_halo_timeout_ns, &ns, sizeof ns));
+        }
+    }
     c->ipc_on = true;
     return AB_OK;
 }
@@ -837,6 +852,7 @@ int ab_comm_exchange(ab_handle* h) {
     AB_CUDA(h, cudaSetDevice(h->device));
     h->index_valid = false;
     h->unpack_rows = h->unpack_tb = false;
+    h->halo_stale = false;             // set again below if this exchange times out as well
     AB_TRY(ab_ensure_index(h));
     AB_TRY(ab_comm_pack(h));
     AB_TRY(ab_comm_transfer(h));

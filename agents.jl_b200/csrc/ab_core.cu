@@ -99,6 +99,24 @@ int ab_check_device_errors_now(ab_handle* h) {
     return rc;
 }
 
+int ab_step_failed(ab_handle* h, int rc) {
+    h->rs_ntiles = 0;
+    h->index_valid = false;
+    h->agg_valid = false;
+    if (h->cell_count) cudaMemsetAsync(h->cell_count, 0, (size_t)h->nfine_cap * sizeof(uint32_t), h->stream);   // best effort
+    return rc;
+}
+
+__global__ void k_iota(int32_t* a, int32_t* b, int n);
+int ab_step_state_lost(ab_handle* h, int rc) {
+    ab_step_failed(h, rc);
+    if (!h->win_W && h->n > 0 && h->desc.kind == AB_SPACE_CONTINUOUS && h->id[h->cur] && h->slot_of_id) {
+        k_iota<<<ab_blocks(h->n, 256), 256, 0, h->stream>>>(h->id[h->cur], h->slot_of_id, (int)h->n);
+        h->slot_map_valid = true;
+    }
+    return rc;
+}
+
 int ab_check_device_errors(ab_handle* h) {
     if (h->async_mode) return AB_OK;      // deferred to ab_sync
     AB_CUDA(h, cudaMemcpyAsync(h->h_err, h->d_err, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
@@ -106,7 +124,7 @@ int ab_check_device_errors(ab_handle* h) {
     int e = *h->h_err;
     if (!e) return AB_OK;
     AB_CUDA(h, cudaMemsetAsync(h->d_err, 0, sizeof(int), h->stream));
-    h->index_valid = false;
+    ab_step_failed(h, 0);                 // index invalid, re-sort histograms cleared by the next plan
     if (e & AB_EF_NUMERIC) return ab_fail(h, AB_ERR_NUMERIC, "InexactError: a NaN/Inf position reached a cell computation");
     if (e & AB_EF_OUTSIDE) return ab_fail(h, AB_ERR_OUTSIDE, "position is outside space extent!");
     if (e & AB_EF_OCCUPIED) return ab_fail(h, AB_ERR_OCCUPIED, "Cannot add agent to occupied position");
@@ -116,7 +134,10 @@ int ab_check_device_errors(ab_handle* h) {
         if (e & AB_EF_COMM_CAP) m += " more agents in the boundary layers than the message capacity (ab_comm_set_capacity);";
         if (e & AB_EF_COMM_WINDOW) m += " owned + halo agents exceed the handle's capacity (ab_resize);";
         if (e & AB_EF_COMM_HDR) m += " a neighbour's message has a foreign header (ranks disagree on refinement or capacity);";
-        if (e & AB_EF_COMM_TIMEOUT) m += " a neighbour's message did not arrive within 10 s;";
+        if (e & AB_EF_COMM_TIMEOUT) {
+            m += " a neighbour's message did not arrive within the halo timeout (AB_HALO_TIMEOUT_S, default 120 s): the halo was not installed, call ab_comm_exchange on every rank before the next step;";
+            h->halo_stale = true;
+        }
         return ab_fail(h, AB_ERR_COMM, m);
     }
     if (e & AB_EF_OVERFLOW) return ab_fail(h, AB_ERR_INVALID, "device-side failure: id out of range, or an agent left its cell neighbourhood in one tiled step");
@@ -651,6 +672,7 @@ int ab_destroy(ab_handle* h) {
 int ab_sync(ab_handle* h) {
     AB_CUDA(h, cudaSetDevice(h->device));
     AB_CUDA(h, cudaStreamSynchronize(h->stream));
+    const bool stepped = h->step_pending;
     if (h->step_pending) {
         float ms = 0;
         if (cudaEventElapsedTime(&ms, h->ev0, h->ev1) == cudaSuccess) h->last_step_ms = ms;
@@ -660,7 +682,7 @@ int ab_sync(ab_handle* h) {
         h->async_mode = false;
         const int rc = ab_check_device_errors(h);
         h->async_mode = true;
-        return rc;
+        return rc != AB_OK && stepped ? ab_step_state_lost(h, rc) : rc;
     }
     return AB_OK;
 }
@@ -913,3 +935,56 @@ int ab_cells(ab_handle* h, int32_t* out_cells, int64_t n) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------
+// FP64 FMA peak of the device, measured: the denominator for every "FP64-pipe bound" statement about the pair sweeps
+// (secondary limiter).  8 independent fma chains per thread, 1024 threads per SM resident, CUDA events
+// around the launch; best of 3.  Nothing is allocated: the sink is a device global that is never actually written
+// (the condition cannot hold), it only keeps the chains alive.
+// ---------------------------------------------------------------------------
+__device__ double g_fp64_sink;
+#define FP64_PEAK_ITERS 8192
+#define FP64_PEAK_CHAINS 8
+__global__ void __launch_bounds__(256) k_fp64_peak(double x, double y) {
+    double a[FP64_PEAK_CHAINS];
+#pragma unroll
+    for (int k = 0; k < FP64_PEAK_CHAINS; ++k) a[k] = (double)(threadIdx.x + k) * 1e-3;
+#pragma unroll 1
+    for (int it = 0; it < FP64_PEAK_ITERS / 4; ++it) {
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+#pragma unroll
+            for (int k = 0; k < FP64_PEAK_CHAINS; ++k) a[k] = fma(a[k], x, y);
+    }
+    double s = 0;
+#pragma unroll
+    for (int k = 0; k < FP64_PEAK_CHAINS; ++k) s += a[k];
+    if (s == 1.2345e300) g_fp64_sink = s;
+}
+
+extern "C" int ab_fp64_peak(int device, double* tflops) {
+    if (!tflops) return ab_fail(nullptr, AB_ERR_INVALID, "ab_fp64_peak: null output");
+    AB_CUDA(nullptr, cudaSetDevice(device));
+    cudaDeviceProp pr;
+    AB_CUDA(nullptr, cudaGetDeviceProperties(&pr, device));
+    const int blocks = pr.multiProcessorCount * 4 * 4;             // 4 resident CTAs of 256 threads per SM, 4 waves
+    cudaEvent_t e0, e1;
+    AB_CUDA(nullptr, cudaEventCreate(&e0));
+    AB_CUDA(nullptr, cudaEventCreate(&e1));
+    double best = 0;
+    for (int rep = 0; rep < 4; ++rep) {                            // rep 0 warms up
+        cudaEventRecord(e0, 0);
+        k_fp64_peak<<<blocks, 256>>>(0.999999, 1e-9);
+        cudaEventRecord(e1, 0);
+        const cudaError_t e = cudaEventSynchronize(e1);
+        if (e != cudaSuccess) { cudaEventDestroy(e0); cudaEventDestroy(e1); return ab_cuda_fail(nullptr, e, "k_fp64_peak"); }
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        const double flop = 2.0 * FP64_PEAK_ITERS * FP64_PEAK_CHAINS * 256.0 * blocks;
+        if (rep > 0 && ms > 0) best = std::max(best, flop / (ms * 1e-3) / 1e12);
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *tflops = best;
+    return AB_OK;
+}

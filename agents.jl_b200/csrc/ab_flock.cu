@@ -659,11 +659,12 @@ static int flock_steps_t(ab_handle* h, const ab_flock_params* p, int64_t nsteps)
             AB_CUDA(h, cudaStreamWaitEvent(h->stream2, h->ev_fork, 0));
             std::swap(h->stream, h->stream2);                                // the install is queued on the side stream
             h->side_unpack_now = true;
-            const int rc = (h->unpack_rows || h->unpack_tb) ? ab_comm_unpack(h, !cx.exact) : AB_ERR_STATE;
+            const bool have_counters = h->unpack_rows || h->unpack_tb;       // what the install sums the owned count from
+            const int rc = have_counters ? ab_comm_unpack(h, !cx.exact) : AB_OK;
             h->side_unpack_now = false;
             const cudaError_t ce = cudaEventRecord(h->ev_join, h->stream);
             std::swap(h->stream, h->stream2);
-            if (rc == AB_ERR_STATE) return ab_fail(h, AB_ERR_STATE, "side-stream halo install without row counters");
+            if (!have_counters) return ab_fail(h, AB_ERR_STATE, "side-stream halo install without row counters");
             AB_TRY(rc);
             AB_CUDA(h, ce);
             if (split_M) AB_TRY((launch_cell_M<T, D>(h, cx.sp, 1)));
@@ -773,9 +774,9 @@ int ab_step_flock(ab_handle* h, const ab_flock_params* p, int64_t nsteps) {
     int rc;
     if (h->dtype == AB_F64) rc = h->D == 2 ? flock_steps_t<double, 2>(h, p, nsteps) : flock_steps_t<double, 3>(h, p, nsteps);
     else rc = h->D == 2 ? flock_steps_t<float, 2>(h, p, nsteps) : flock_steps_t<float, 3>(h, p, nsteps);
-    AB_TRY(rc);
+    if (rc != AB_OK) return ab_step_failed(h, rc);
     if (h->async_mode) { h->step_pending = true; return AB_OK; }     // errors and timing: ab_sync
-    AB_TRY(ab_check_device_errors(h));
+    if ((rc = ab_check_device_errors(h)) != AB_OK) return ab_step_state_lost(h, rc);
     if (h->win_W) AB_TRY(ab_comm_refresh_counts(h));
     float ms = 0;
     AB_CUDA(h, cudaEventElapsedTime(&ms, h->ev0, h->ev1));
@@ -805,6 +806,7 @@ int ab_step_flock_group(ab_handle** hs, int nh, const ab_flock_params* p, int64_
     int rc;
     if (h0->dtype == AB_F64) rc = h0->D == 2 ? flock_group_t<double, 2>(hs, nh, p, nsteps) : flock_group_t<double, 3>(hs, nh, p, nsteps);
     else rc = h0->D == 2 ? flock_group_t<float, 2>(hs, nh, p, nsteps) : flock_group_t<float, 3>(hs, nh, p, nsteps);
+    if (rc != AB_OK) for (int r = 0; r < nh; ++r) ab_step_failed(hs[r], rc);
     if (rc != AB_OK) { if (h0->err.empty()) for (int r = 0; r < nh; ++r) if (!hs[r]->err.empty()) { h0->err = hs[r]->err; break; } return rc; }
     double worst = 0;
     for (int r = 0; r < nh; ++r) {

@@ -414,7 +414,9 @@ k_flock_fine(const __grid_constant__ SpaceDev<T, D> sp, const __grid_constant__ 
                 }
                 // the bird itself (h == 0) passes this test and contributes exactly nothing.
                 // separate -= h  as  fma(-w, h, separate), w = 1 or 0: one rounding, the same value as the subtraction
-                // (w * h is exact), without the select pairs a predicated update compiles to
+                // (w * h is exact), without the select pairs a predicated update compiles to.  With a non-finite h
+                // (a NaN / Inf position) 0 * h is NaN where the predicated form skipped the bird; such a step has
+                // already raised AB_EF_NUMERIC and its result is discarded (AB_ERR_NUMERIC), so nothing visible differs
                 const T wgt = d2 < sep2 ? T(1) : T(0);                                   // flock.jl:93
 #pragma unroll
                 for (int d = 0; d < D; ++d) separate[d] = fma(-wgt, h[d], separate[d]);

@@ -182,6 +182,7 @@ struct ab_handle {
     bool small_scan = false;           // AB_SMALL_SCAN=1: single-CTA scan of the tile totals (A/B experiments)
     bool no_split_M = false;           // AB_SPLIT_M=0: cell sums in one launch after the install (A/B experiments)
     bool no_side_unpack = false;       // AB_SIDE_UNPACK=0: halo install after the re-sort on the same stream (A/B experiments)
+    bool halo_stale = false;           // a halo message timed out: the window is half-updated until ab_comm_exchange has run
     bool side_unpack_now = false;      // the halo install being queued runs beside the re-sort (one-thread flag wait first)
     bool unpack_tb = false;            // ... or the scanned tile totals do (scan path)
     bool unpack_rows = false;          // this step's per-row counters give the owned count (set by a scan-free re-sort)
@@ -299,6 +300,19 @@ struct ab_launch_scope {
 #define AB_CAT2(a, b) a##b
 #define AB_CAT(a, b) AB_CAT2(a, b)
 #define AB_LAUNCH(h, name) ab_launch_scope AB_CAT(_scope_, __LINE__)((h), (name))
+
+// A fused step that ends early (a failing call between the sweep and the re-sort, or a device error flag) leaves the
+// per-tile / per-row histograms of that step half-consumed and rs_par possibly out of phase with the data: the next
+// ab_resort_plan must clear both halves, and the index is rebuilt from the positions the handle holds.
+// The per-cell counts (cell_count: zero between uses, the sweep adds the new keys, the re-sort / scan consumes them) are
+// cleared as well — the index build counts into them.  Returns rc.
+int ab_step_failed(ab_handle* h, int rc);
+// A fused step that failed ON THE DEVICE has also run its re-sort on incomplete keys (a bird whose new position is NaN
+// or outside the space has no cell): some agents were not placed, so the columns and the slot -> id table of the handle
+// no longer describe the population.  Like a reference model whose step! threw half way, the state is undefined; what
+// the handle guarantees is that it can be repaired: the slot order is reset to id order, so the caller's next
+// ab_upload of pos, vel and the user columns lands every row where its id says, and the index is rebuilt from them.
+int ab_step_state_lost(ab_handle* h, int rc);
 
 static inline int ab_blocks(int64_t n, int threads) { return (int)((n + threads - 1) / threads); }
 

@@ -451,8 +451,8 @@ extern "C" int ab_step_pairforce(ab_handle* h, const ab_pairforce_params* p, int
     int rc;
     if (h->dtype == AB_F64) rc = h->D == 2 ? pf_steps_t<double, 2>(h, p, nsteps) : pf_steps_t<double, 3>(h, p, nsteps);
     else rc = h->D == 2 ? pf_steps_t<float, 2>(h, p, nsteps) : pf_steps_t<float, 3>(h, p, nsteps);
-    AB_TRY(rc);
-    AB_TRY(ab_check_device_errors_now(h));      // synchronous call (also in asynchronous mode): the events below must have completed
+    if (rc != AB_OK) return ab_step_failed(h, rc);
+    if ((rc = ab_check_device_errors_now(h)) != AB_OK) return ab_step_state_lost(h, rc);   // synchronous call (also in asynchronous mode): the events below must have completed
     if (h->win_W) AB_TRY(ab_comm_refresh_counts(h));
     float ms = 0;
     AB_CUDA(h, cudaEventElapsedTime(&ms, h->ev0, h->ev1));

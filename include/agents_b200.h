@@ -289,7 +289,11 @@ typedef struct {
 int ab_reduce(ab_handle* h, const ab_reduce_spec* specs, int nspec, double* out, int64_t* counts_or_null);
 /* Schedulers.ByProperty(field)(model) — src/submodules/schedulers.jl:130-151: the 1-based agent ids in `sortperm`
  * order of component `comp` of a column (ascending, stable: ties keep id order; NaN last; `descending` reverses the
- * result).  Sorted on the device (bitonic network over (key, id) pairs); n ids come back. */
+ * result).  Sorted on the device (bitonic network over (key, id) pairs); n ids come back; n <= 2^30.
+ * Ties: always by ascending id.  The reference keeps ties in the order of its `sched.ids` — the container's key order on
+ * the first call (id order for the Vector containers this ABI mirrors, arbitrary for Dict-backed models) and, on later
+ * calls, the PREVIOUS permutation (`sortperm!(...; initialized = true)`, schedulers.jl:144-149) — so agents with equal
+ * property values can come out in a different relative order there from the second call on. */
 int ab_ids_by_property(ab_handle* h, int field, int comp, int descending, int64_t* out_ids, int64_t n);
 
 /* The chunked reduction of ab_reduce for ONE (column, aggregator, filter) triple, for callers that must not
@@ -377,6 +381,9 @@ int64_t ab_launch_count(const ab_handle* h);
 double ab_last_step_ms(const ab_handle* h);
 /* per-kernel device time of the last ab_step_* call when profiling is on:
  * names[i] (static strings), ms[i] summed over the steps; returns how many. */
+/* Measured FP64 FMA throughput of `device` in TFLOP/s (independent fma chains on every SM, CUDA events, best of 3): the
+ * denominator bench.py reports the FP64-heavy pair sweeps against.  No counterpart in the reference. */
+int ab_fp64_peak(int device, double* tflops);
 int ab_set_profiling(ab_handle* h, int on);
 int ab_kernel_times(ab_handle* h, const char** names, double* ms, int64_t* launches, int cap);
 

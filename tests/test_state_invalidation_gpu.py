@@ -136,3 +136,33 @@ def test_index_canonical_flag():
     assert m.lib.ab_index_canonical(m.h) == 0
     assert len(m.nearby_ids(1, 1.0)) >= 5999                    # still a correct index
     m.close()
+
+
+@pytest.mark.parametrize("search", ["approximate", "exact"])
+def test_step_after_a_failed_step_starts_from_clean_counters(search):
+    """A step that fails on the device (here: a NaN velocity makes a position NaN — the reference's InexactError in
+    pos2cell, continuous.jl:112-113) leaves the re-sort's per-tile histograms of that step behind.  The next step on the
+    repaired state must not see them: it equals, bit for bit, the same step on a fresh model."""
+    extent, spacing, n = (300.0, 300.0), 5.0, 40000
+    pos, vel = flock_init(n, extent, 17)
+    rule = dict(search=search, **FLOCK)
+    m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=spacing), model_step=ab.FlockRule(**rule))
+    m.add_agents(pos, vel)
+    m.step(2)
+    P, V = m.pos.copy(), m.vel.copy()
+    bad = V.copy()
+    bad[[7, 20003]] = np.nan
+    m.set_column("vel", bad)
+    with pytest.raises(ab.AgentsError) as ei:
+        m.step(1)
+    assert ei.value.code == ab._lib.ERR_NUMERIC
+    m.set_column("pos", P)
+    m.set_column("vel", V)
+    m.step(3)
+    f = ab.StandardABM(ab.ContinuousSpace(extent, spacing=spacing), model_step=ab.FlockRule(**rule))
+    f.add_agents(P, V)
+    f.step(3)
+    assert np.array_equal(m.pos, f.pos) and np.array_equal(m.vel, f.vel)
+    assert np.array_equal(m.last_neighbor_counts(), f.last_neighbor_counts())
+    m.close()
+    f.close()
