@@ -59,6 +59,10 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 ALG_BYTES = {"flock2d_f64": 128.0, "flock3d_f64": 160.0, "flock2d_f32": 72.0, "pairforce2d_f64": 104.0, "schelling": 10.33}
+# what the fast path really moves per agent-update when the six rule parameters are uniform (they travel as kernel
+# arguments, not as the 48 B of per-agent fields SURVEY 8(d) counts): read pos + vel 32 + key 4, write pos + vel 32 + key 4,
+# id read + write 8
+ALG_BYTES_MOVED = {"flock2d_f64_uniform": 80.0}
 N_PER_GPU = 1_000_000
 EXTENT = (2000.0, 2000.0)
 SPACING = 5.0
@@ -250,6 +254,21 @@ def cpu_flock_rate_sync_all_cores(n, extent, steps):
             "note": "CPU restatement with the synchronous update, not Agents.jl"}
 
 
+def sync_all_cores_guarded(n, extent, steps):
+    """The all-cores leg in a child process: it is optional context, so a crash or a hang in it (round 2: a data race in
+    the oracle's offset-table cache aborted the N = 8 reference arm) must not take the result line with it."""
+    code = ("import json, bench; print('SYNCLEG ' + json.dumps(bench.cpu_flock_rate_sync_all_cores(%d, %r, %d)))"
+            % (n, tuple(extent), steps))
+    try:
+        r = subprocess.run([sys.executable, "-c", code], cwd=ROOT, capture_output=True, text=True, timeout=600)
+        for ln in r.stdout.splitlines():
+            if ln.startswith("SYNCLEG "):
+                return json.loads(ln[8:])
+        return {"unavailable": f"child exited with {r.returncode}: {r.stderr.strip()[-200:]}"}
+    except Exception as e:                                     # timeout, spawn failure
+        return {"unavailable": f"{type(e).__name__}: {e}"[:240]}
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -271,7 +290,7 @@ def run_reference(args):
                                  "(single-threaded by design: src/simulations/step_standard.jl:9-23)"},
         "e2e": {"value": rate, "unit": "agent-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    line["cpu_baseline"]["sync_all_cores"] = cpu_flock_rate_sync_all_cores(n, EXTENT, 2)
+    line["cpu_baseline"]["sync_all_cores"] = sync_all_cores_guarded(n, EXTENT, 2)
     print(json.dumps(line))
     return 0
 
@@ -288,7 +307,36 @@ def kernel_table(lib, m):
             for i in range(min(nk, 32))}
 
 
-def timed_row(lib, m, name, n, steps, warmup, alg_bytes, local, peak, extra=None):
+FLOP_PER_CANDIDATE = 20.0          # min-image difference, d2, compare, masked accumulate
+_FP64_PEAK = {}
+
+
+def fp64_peak(lib, local):
+    """Measured FP64 FMA peak of this GPU in TFLOP/s (ab_fp64_peak: independent fma chains, CUDA events), once per run."""
+    if local not in _FP64_PEAK:
+        t = C.c_double(0)
+        rc = lib.ab_fp64_peak(int(local), C.byref(t))
+        _FP64_PEAK[local] = t.value if rc == 0 and t.value > 0 else None
+    return _FP64_PEAK[local]
+
+
+def fp64_roofline(lib, local, candidates, updates_per_s, kernel_updates_per_s=None):
+    """Secondary roofline: flop per agent-update = expected candidates per agent at the row's uniform
+    density x 20 flop, against the measured FP64 peak."""
+    pk = fp64_peak(lib, local)
+    if not pk:
+        return None
+    f = candidates * FLOP_PER_CANDIDATE
+    out = {"candidates_per_agent": candidates, "flops_per_agent_update": f, "peak_tflops": pk,
+           "peak_source": "ab_fp64_peak, measured in this run",
+           "whole_step": {"achieved_tflops": f * updates_per_s / 1e12, "frac": f * updates_per_s / 1e12 / pk}}
+    if kernel_updates_per_s:
+        out["achieved_tflops"] = f * kernel_updates_per_s / 1e12
+        out["frac"] = out["achieved_tflops"] / pk
+    return out
+
+
+def timed_row(lib, m, name, n, steps, warmup, alg_bytes, local, peak, extra=None, candidates=None):
     """One driver-timed row of `configs`: W warm-up steps, ONE call of K fused steps timed by CUDA events on the
     library's stream (state resident), NVML clock samples inside the timed region; then the per-kernel durations of
     the NEXT min(K, 5) steps (per-launch events cost a few us each, so the timed call carries none)."""
@@ -319,6 +367,9 @@ def timed_row(lib, m, name, n, steps, warmup, alg_bytes, local, peak, extra=None
                         "frac": (alg_bytes * n / (kern[dom]["ms_per_launch"] * 1e-3) / 1e9 / peak) if dom else None},
            "kernels_us_per_launch": {k: round(v["ms_per_launch"] * 1e3, 2) for k, v in kern.items()},
            "gpu_launches": int(launches), "clocks": clocks}
+    if candidates:
+        row["roofline"]["fp64"] = fp64_roofline(lib, local, candidates, rate,
+                                                n / (kern[dom]["ms_per_launch"] * 1e-3) if dom else None)
     if extra:
         row.update(extra)
     return row
@@ -333,12 +384,14 @@ def config_rows(ab, lib, local, peak, scale=1.0):
     side = int(round(400 * sc ** 0.5))
     extent = (5.0 * side, 5.0 * side)
     n = int(6.25 * side * side)
-    for name, dt, search, alg in (("F2D-1M exact f64", np.float64, "exact", ALG_BYTES["flock2d_f64"]),
-                                  ("F2D-1M approximate f32", np.float32, "approximate", ALG_BYTES["flock2d_f32"])):
+    # expected candidates per agent at the row's uniform density: exact 2-D sweep 5 x 5 fine cells of 2.5 x 2.5 at
+    # 0.25 / unit^2 = 39; pair force 3 x 3 cells of 20 x 20 at 0.04 = 144; 3-D sweep 27 fine cells of 2.5^3 at 0.0364 = 15.4
+    for name, dt, search, alg, cand in (("F2D-1M exact f64", np.float64, "exact", ALG_BYTES["flock2d_f64"], 39.0),
+                                        ("F2D-1M approximate f32", np.float32, "approximate", ALG_BYTES["flock2d_f32"], None)):
         pos, vel = flock_init(n, extent, 42, dtype=dt)
         m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=5.0, dtype=dt), model_step=ab.FlockRule(search=search, **FLOCK), device=local)
         m.add_agents(pos, vel)
-        rows.append(timed_row(lib, m, name, n, 20, 5, alg, local, peak))
+        rows.append(timed_row(lib, m, name, n, 20, 5, alg, local, peak, candidates=cand))
         m.close()
 
     side = int(round(791 * sc ** 0.5))
@@ -348,7 +401,27 @@ def config_rows(ab, lib, local, peak, scale=1.0):
     m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=20.0), model_step=ab.PairForceRule(dt=0.001, cutoff=20.0), device=local)
     m.add_agents(pos, vel, r=rad, k=k, mass=mass)
     rows.append(timed_row(lib, m, "PF2D-10M (celllistmap.jl-style pair force, cutoff 20, interacting_pairs(:all) exact set)", n, 10, 3,
-                          ALG_BYTES["pairforce2d_f64"], local, peak))
+                          ALG_BYTES["pairforce2d_f64"], local, peak, candidates=144.0))
+    # SURVEY 8(d)'s separate row: materialising interacting_pairs(model, cutoff, :all; search = :exact)
+    # (continuous.jl:418-452) on the stepped state — count on the device, then fill and copy 16 B per pair to two host
+    # Int64 vectors (the caller-owned result of the two-phase ABI)
+    try:
+        npairs = C.c_int64(0)
+        t0 = time.perf_counter()
+        m._ck(lib.ab_pairs_count(m.h, 20.0, 1, C.byref(npairs)))
+        t_count = time.perf_counter() - t0
+        P = npairs.value
+        lo, hi = np.empty(P, dtype=np.int64), np.empty(P, dtype=np.int64)
+        t0 = time.perf_counter()
+        m._ck(lib.ab_pairs_fill(m.h, m._ptr(lo), m._ptr(hi), P))
+        t_fill = time.perf_counter() - t0
+        rows.append({"config": "PF2D-10M interacting_pairs(:all, exact, r = 20) materialised", "agents": int(n), "pairs": int(P),
+                     "pairs_per_agent": 2.0 * P / n, "count_s": t_count, "fill_and_copy_s": t_fill,
+                     "value": P / (t_count + t_fill), "unit": "pairs/s", "bytes_to_host": 16 * P,
+                     "every_pair_lo_lt_hi": bool(np.all(lo < hi)), "timing": "host wall clock around the two synchronous calls"})
+        del lo, hi
+    except Exception as e:                                    # host memory for 2 x 8 B x 250 M pairs may be missing
+        rows.append({"config": "PF2D-10M interacting_pairs(:all, exact, r = 20) materialised", "unavailable": str(e)[:200]})
     m.close()
     del pos, vel, rad, k, mass
 
@@ -374,7 +447,7 @@ def config_rows(ab, lib, local, peak, scale=1.0):
     pos, vel = flock_init(n, extent, 42)
     m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=5.0), model_step=ab.FlockRule(**FLOCK), device=local)
     m.add_agents(pos, vel)
-    rows.append(timed_row(lib, m, "F3D-12.5M (one GPU's share of F3D-100M, periodic box)", n, 10, 3, ALG_BYTES["flock3d_f64"], local, peak))
+    rows.append(timed_row(lib, m, "F3D-12.5M (one GPU's share of F3D-100M, periodic box)", n, 10, 3, ALG_BYTES["flock3d_f64"], local, peak, candidates=15.4))
     m.close()
     return rows
 
@@ -385,11 +458,17 @@ def parity_check(ab, dist, local, rank, world):
     from agents_jl_b200.parallel import Slabs
     from helpers import flock_init
 
-    cases = [("flock 2d", (400.0, float(max(400, 100 * world))), 0.375, SPACING),
-             ("flock 3d", (60.0, 60.0, float(max(120, 40 * world))), 0.0926, SPACING),
-             ("pairforce 2d", (400.0, float(max(400, 100 * world))), 0.0375, 20.0)]
+    # the last case forces the path the timed F3D-100M row takes (messages too large for the re-sort to deliver:
+    # k_halo_pack launch, cell sums split around the side-stream install) onto a state small enough to compare
+    cases = [("flock 2d", (400.0, float(max(400, 100 * world))), 0.375, SPACING, {}),
+             ("flock 3d", (60.0, 60.0, float(max(120, 40 * world))), 0.0926, SPACING, {}),
+             ("pairforce 2d", (400.0, float(max(400, 100 * world))), 0.0375, 20.0, {}),
+             ("flock 3d, large-message path (AB_FUSED_PACK_MAXMB=0)", (60.0, 60.0, float(max(120, 40 * world))), 0.0926, SPACING,
+              {"AB_FUSED_PACK_MAXMB": "0"})]
     out = {"bitwise_equal": True, "migrated": 0, "direct": True, "cases": []}
-    for name, extent, dens, spacing in cases:
+    for name, extent, dens, spacing, env in cases:
+        saved = {k: os.environ.get(k) for k in env}
+        os.environ.update(env)                                # read by ab_comm_init (Slabs) of this case only
         n = int(dens * float(np.prod(extent)))
         cols = None
         if name.startswith("flock"):
@@ -401,6 +480,8 @@ def parity_check(ab, dist, local, rank, world):
             make_rule = lambda: ab.PairForceRule(dt=0.005, cutoff=20.0)
         m = ab.StandardABM(ab.ContinuousSpace(extent, spacing=spacing), model_step=make_rule(), device=local)
         s = Slabs(m, dist)
+        for k, v in saved.items():
+            os.environ.pop(k, None) if v is None else os.environ.__setitem__(k, v)
         own0 = s.scatter(pos, vel, columns=cols)
         m.step(4)
         own1 = s.n_owned()
@@ -588,6 +669,32 @@ def run_gpu(args):
         halo_wait = wait_us.value / max(args.steps, 1)
     barrier()
     clocks = sampler.stop()
+    # ---- the timed configuration itself, compared bit for bit (N > 1): the state after W + K steps of the sharded run,
+    # gathered by global id, against the unsharded run of the same steps on rank 0 (N x 1 M boids fit one GPU)
+    if world > 1 and parity is not None and not args.no_fullsize_parity:
+        gp, gv = slabs.gather()
+        ok = True
+        if rank == 0:
+            ref = ab.StandardABM(ab.ContinuousSpace(extent, spacing=SPACING, periodic=True), model_step=rule, device=local)
+            ref.add_agents(gpos, gvel)
+            ref.step(args.warmup)
+            ref.step(args.steps)
+            ok = bool(np.array_equal(gp, ref.pos) and np.array_equal(gv, ref.vel))
+            ref.close()
+        del gp, gv
+        flags = [None] * world
+        dist.all_gather_object(flags, ok)
+        ok = bool(flags[0])
+        parity["cases"].append({"case": "flock 2d, 1M per GPU (the timed run itself)", "agents": int(n * world),
+                                "extent": list(extent), "steps": int(args.warmup + args.steps), "bitwise_equal": ok,
+                                "direct": bool(slabs.direct)})
+        parity["bitwise_equal"] = parity["bitwise_equal"] and ok
+        if not ok:
+            if rank == 0:
+                print(json.dumps({"error": "the timed sharded run differs from the unsharded run", "parity_check": parity}))
+            dist.destroy_process_group()
+            return 3
+        barrier()
     twin, _tw_slabs = make_model()
     twin.step(args.warmup)
     barrier()
@@ -616,16 +723,19 @@ def run_gpu(args):
     # unsynchronised host-side flushes would be timed as waiting for the neighbour
     flushed = None
     if world == 1:
-        kf = min(args.steps, 20)
+        kf = args.steps
+        fm, _ = make_model()                                  # the SAME steps as `value`: same initial state, same warm-up
+        fm.step(args.warmup)
         tot = 0.0
         for _ in range(kf):
             flush.add_(1.0)
             torch.cuda.synchronize()
-            model.step(1)
-            tot += model.last_step_ms()
+            fm.step(1)
+            tot += fm.last_step_ms()
+        fm.close()
         flushed = {"value": n * kf / (tot * 1e-3), "ms_per_step": tot / kf, "steps": kf,
-                   "note": "the steps after the timed region (the flock is more clustered there), one call per step, "
-                           "L2 flushed before each"}
+                   "note": "steps W..W+K of a re-created model (the steps `value` is timed on), one call per step, "
+                           "L2 flushed (256 MB write) before each"}
 
     step_kernel_ms = sum(v["ms"] for v in kernels.values()) / args.steps
     dom = max(kernels, key=lambda k: kernels[k]["ms"]) if kernels else None
@@ -636,17 +746,26 @@ def run_gpu(args):
         ach = alg * nloc / dur / 1e9
         roofline = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
                     "frac": ach / peak, "traffic": None, "peak_source": peak_src,
-                    "algorithmic_bytes_per_agent_update": alg, "kernel_ms": kernels[dom]["ms_per_launch"],
+                    "algorithmic_bytes_per_agent_update": alg,
+                    "algorithmic_bytes_moved_per_agent_update": ALG_BYTES_MOVED["flock2d_f64_uniform"],
+                    "frac_on_bytes_moved": ALG_BYTES_MOVED["flock2d_f64_uniform"] * nloc / dur / 1e9 / peak,
+                    "kernel_ms": kernels[dom]["ms_per_launch"],
                     "kernel_share_of_step": kernels[dom]["ms"] / max(sum(v["ms"] for v in kernels.values()), 1e-12),
                     "whole_step": {"achieved": alg * nloc / (ms / args.steps * 1e-3) / 1e9,
-                                   "frac": alg * nloc / (ms / args.steps * 1e-3) / 1e9 / peak},
+                                   "frac": alg * nloc / (ms / args.steps * 1e-3) / 1e9 / peak,
+                                   "frac_on_bytes_moved": ALG_BYTES_MOVED["flock2d_f64_uniform"] * nloc / (ms / args.steps * 1e-3) / 1e9 / peak},
                     "profiled_pass_ms_per_step": ms_profiled / args.steps,
                     "note": "launch durations from CUDA events around every launch in a twin pass over the SAME steps "
                             "(same initial state and warm-up, rank 0); the timed region itself carries no per-launch events"}
+        # 3 x 3 fine cells of 2.5 x 2.5 at 0.25 / unit^2 = 14 candidates per bird in the separation sweep
+        roofline["fp64"] = fp64_roofline(lib, local, 14.0, value / world, nloc / dur)
         tpath = os.path.join(ROOT, "profiles", "traffic.json")      # dram bytes per launch from an ncu --set full capture
         if os.path.exists(tpath):
             try:
-                roofline["traffic"] = json.load(open(tpath)).get(dom)
+                tj = json.load(open(tpath))
+                roofline["traffic"] = tj.get(dom)
+                roofline["traffic_source"] = ("profiles/traffic.json (committed; not measured in this run): "
+                                              + str(tj.get("_note", "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full")))
             except Exception:
                 pass
 
@@ -746,7 +865,7 @@ def run_gpu(args):
         rate, dt = cpu_flock_rate(n, EXTENT, csteps, 1)
         cpu = {"value": rate, "unit": "agent-updates/s", "cores": 1, "kind": "port",
                "sample": f"{n} boids x {csteps} asynchronous steps after 1 warm-up step (reference semantics), {dt:.1f} s, 1 thread",
-               "sync_all_cores": cpu_flock_rate_sync_all_cores(n, EXTENT, 2)}
+               "sync_all_cores": sync_all_cores_guarded(n, EXTENT, 2)}
 
     if rank == 0:
         line = {
@@ -819,6 +938,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
     ap.add_argument("--no-configs", action="store_true", help="skip the rows of the other BASELINE configurations (N = 1)")
     ap.add_argument("--config-scale", type=float, default=1.0, help="shrink the populations of the config rows (smoke runs)")
+    ap.add_argument("--no-fullsize-parity", action="store_true", help="skip the bitwise check of the timed sharded run (N > 1)")
     ap.add_argument("--no-parity", action="store_true", help="skip the sharded-vs-unsharded parity gate (N > 1)")
     ap.add_argument("--no-f3d", action="store_true", help="skip the F3D and PF2D weak-scaling rows (N > 1)")
     ap.add_argument("--no-pf", action="store_true", help="skip the PF2D weak-scaling row (N > 1)")

@@ -1,7 +1,8 @@
 """Spatial fields: get_spatial_index / get_spatial_property (src/spaces/continuous.jl:536-573)
 and the force-field form of the update_vel! hook (continuous.jl:86-91, :186-194) against the numpy restatement.
 Indices: exact.  Velocities after the kick: bitwise (one multiply and one add per component, no contraction).
-The reference holds no test for these functions (test/continuous_space_tests.jl:5): parity unpinned."""
+The reference holds no test for these functions (test/continuous_space_tests.jl:5): unpinned by the reference; the
+last test holds the device to known answers worked out by hand from the source (tests/known_answers.py)."""
 import numpy as np
 import pytest
 
@@ -59,4 +60,21 @@ def test_update_vel_field_then_move():
     m.move_agent(0.5)                                               # move_agent!(agent, model, dt) after update_vel!
     moved = np.mod(pos + 0.5 * want, np.asarray(extent)[None, :])
     assert np.max(np.abs(m.pos - moved)) <= 1e-12
+    m.close()
+
+
+def test_spatial_index_known_answers():
+    """The device against indices worked out by hand from src/spaces/continuous.jl:566-573 (tests/known_answers.py)."""
+    import known_answers as ka
+
+    m = ab.StandardABM(ab.ContinuousSpace(ka.SI_EXTENT, spacing=1.0, periodic=False))
+    m.add_agents(ka.SI_POS, np.zeros_like(ka.SI_POS))
+    assert np.array_equal(m.get_spatial_index((5, 3)), ka.SI_IDX_5x3)
+    assert np.array_equal(m.get_spatial_index((4,)), ka.SI_IDX_4)
+    prop = np.arange(15, dtype=np.float64).reshape((5, 3), order="F")           # property[i, j] = (i - 1) + 5 (j - 1)
+    want = (ka.SI_IDX_5x3[:, 0] - 1) + 5.0 * (ka.SI_IDX_5x3[:, 1] - 1)
+    assert np.array_equal(m.get_spatial_property(prop), want)
+    assert np.array_equal(m.get_spatial_index((5, 3), positions=ka.SI_POS[2:5]), ka.SI_IDX_5x3[2:5])
+    with pytest.raises(ab.AgentsError):                                          # BoundsError in the reference
+        m.get_spatial_index((5, 3), positions=ka.SI_POS_AT_EXTENT)
     m.close()

@@ -115,3 +115,18 @@ def test_pairforce_needs_its_columns():
     with pytest.raises(KeyError):
         m.step(1)
     m.close()
+
+
+@pytest.mark.parametrize("k", [2, 3])
+def test_pairforce_known_answers(k):
+    """The device against numbers worked out by hand from examples/celllistmap.jl:143-155, 176-191
+    (tests/known_answers.py) — not against the oracle."""
+    import known_answers as ka
+
+    m = ab.StandardABM(ab.ContinuousSpace(ka.PF_EXTENT, spacing=ka.PF_SPACING),
+                       model_step=ab.PairForceRule(dt=ka.PF_DT, cutoff=ka.PF_CUTOFF))
+    m.add_agents(ka.PF_POS[:k], ka.PF_VEL[:k], r=ka.PF_R[:k], k=ka.PF_K[:k], mass=ka.PF_MASS[:k])
+    m.step(1)
+    pos1, vel1 = (ka.PF2_POS1, ka.PF2_VEL1) if k == 2 else (ka.PF3_POS1, ka.PF3_VEL1)
+    assert np.max(np.abs(m.pos - pos1)) <= ka.PF_TOL and np.max(np.abs(m.vel - vel1)) <= ka.PF_TOL
+    m.close()
